@@ -1,0 +1,101 @@
+/*
+ * oracle/ovis_oracle.h - the flat "checker" API shared by BOTH CPU oracles.
+ *
+ * TEST INFRASTRUCTURE ONLY. Only tests/, __graft_entry__.smoke() and bench.py's CPU legs may load
+ * the libraries that export these symbols; nothing under orion_b200/ does.
+ *
+ *   oracle/libovis_oracle.so      (ovis_oracle.c)   plain-C restatement, prefix orc_
+ *   oracle/_ref/liborion_ref.so   (ref_harness.cc)  the same orc_ entry points implemented by calling
+ *                                                   the reference's own compiled classes, plus the
+ *                                                   object-world oref_ entry points (tier A)
+ *
+ * Conventions (identical in include/orion_vis.h):
+ *   TRS    = 10 floats: position xyz, orientation w x y z, scale xyz
+ *   AABB   = 6 floats:  minimum xyz, maximum xyz
+ *   planes = 24 floats: 6 x (normal xyz, distance), order Left Right Top Bottom Near Far
+ *            (engine/runtime/core/include/math/frustum.h:39-47)
+ *   mat4   = 16 floats column-major (GLM: m[col][row])
+ */
+#ifndef OVIS_ORACLE_H
+#define OVIS_ORACLE_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* RenderLight::Type, engine/runtime/render/include/render_light.h:52-58 */
+enum { ORC_LIGHT_AMBIENT = 0, ORC_LIGHT_DIRECTIONAL = 1, ORC_LIGHT_POINT = 2, ORC_LIGHT_SPOT = 3 };
+/* RenderLight::kCastsShadows (render_light.h:61-64), RenderEntity::kCastsShadow (render_entity.h:50-53) */
+enum { ORC_CASTS_SHADOW = 1u };
+/* RenderWorld::CullFlags::kCullLights, engine/runtime/render/include/render_world.h:43-46 */
+enum { ORC_CULL_LIGHTS = 1u };
+
+typedef struct OrcLight {
+    int32_t  type;
+    uint32_t flags;
+    float    position[3];
+    float    direction[3];   /* normalised by the light, as RenderLight::setDirection does */
+    float    colour[3];
+    float    intensity;
+    float    range;
+    float    cutoff;         /* degrees, spot only, <= 45 */
+} OrcLight;                   /* 56 bytes */
+
+typedef struct OrcView {
+    float   position[3];
+    float   orientation[4];  /* w x y z */
+    float   hfov_deg;
+    float   znear;
+    float   zfar;
+    int32_t vp_width;        /* aspect = (float)vp_width / (float)vp_height, render_view.cc:84 */
+    int32_t vp_height;
+} OrcView;                    /* 48 bytes */
+
+/* ---- view / frustum (render_view.cc:102-135, frustum.cc:27-85) ---- */
+void orc_view_planes(const OrcView *view, float out_planes[24]);
+/* out_mats = view, projection, viewProjection, inverseViewProjection (4 x 16); corners = 8 x 3 */
+void orc_view_matrices(const OrcView *view, float out_mats[64], float out_corners[24]);
+
+/* ---- transform propagation (entity.cc:382-411) over depth-sorted nodes: parent[i] < i, -1 = root child of identity ---- */
+void orc_world_trs(int64_t n, const int32_t *parent, const float *local_trs, float *out_world_trs);
+/* Transform::matrix (transform.cc:26-35) */
+void orc_trs_matrix(int64_t n, const float *trs, float *out_mat16);
+/* RenderEntity::updateWorld (render_entity.cc:90-93) = BoundingBox::transform(Transform::matrix()) */
+void orc_world_aabb(int64_t n, const float *world_trs, const float *local_aabb, float *out_aabb);
+
+/* ---- entity cull over flat AABBs (simple_render_world.cc:38-41 + intersection.cc:42-57) ----
+ * flags may be NULL. An entity is emitted iff it intersects and (flags[i] & require) == require.
+ * Returns the number of indices written to out_idx (capacity n). */
+int64_t orc_cull_aabb(int64_t n, const float *aabb, const float planes[24],
+                      const uint32_t *flags, uint32_t require, uint32_t *out_idx);
+/* Same result, index range split over nthreads host threads (CPU baseline "all cores"). */
+int64_t orc_cull_aabb_mt(int64_t n, const float *aabb, const float planes[24],
+                         const uint32_t *flags, uint32_t require, uint32_t *out_idx, int nthreads);
+
+/* ---- lights ---- */
+/* RenderLight::updateVolumeTransform, spot branch (render_light.cc:227-249): cone-fitted AABB */
+void orc_light_spot_aabb(const OrcLight *light, float out_aabb[6]);
+/* RenderLight::cull (render_light.cc:187-209): writes indices of lights that are NOT culled */
+int32_t orc_light_cull(int32_t n, const OrcLight *lights, const float planes[24], uint32_t *out_idx);
+/* RenderLight::updateShadowViews (render_light.cc:258-332) with the square shadow-map viewport of
+ * deferred_render_pipeline.cc:261-265. Returns the number of shadow views (0, 1 or 6). */
+int32_t orc_light_shadow_views(const OrcLight *light, OrcView out_views[6]);
+
+/* ---- per-light shadow-caster lists (deferred_render_pipeline.cc:207,247,257-284) ----
+ * For every light NOT culled by main_planes that casts shadows, for each of its shadow views:
+ * the ordered list of entities that intersect that view and have ORC_CASTS_SHADOW.
+ * out_list_light[k], out_list_view[k] identify list k; out_offsets has n_lists + 1 entries.
+ * Returns n_lists, or -1 if a capacity is too small. */
+int32_t orc_shadow_lists(int64_t n, const float *aabb, const uint32_t *flags,
+                         int32_t n_lights, const OrcLight *lights, const float main_planes[24],
+                         int32_t cap_lists, int32_t *out_list_light, int32_t *out_list_view,
+                         int64_t *out_offsets, int64_t cap_entities, uint32_t *out_entities);
+
+const char *orc_name(void);   /* "port" or "reference" */
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,301 @@
+"""ctypes front-end for the two CPU oracles (TEST INFRASTRUCTURE ONLY).
+
+Only ``tests/``, ``__graft_entry__.smoke()`` and ``bench.py``'s CPU legs import this module; nothing
+under ``orion_b200/`` does.  ``load("port")`` is the plain-C restatement (``oracle/ovis_oracle.c``),
+``load("reference")`` is the reference's own sources compiled in place (``oracle/_ref``); both export
+the flat ``orc_*`` API declared in ``oracle/ovis_oracle.h``, the reference build additionally exports
+the object-world ``oref_world_*`` API (tier A: SimpleRenderWorld/RenderEntity/RenderLight as shipped).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+PORT_SO = os.path.join(HERE, "libovis_oracle.so")
+REF_SO = os.path.join(HERE, "_ref", "liborion_ref.so")
+
+LIGHT_AMBIENT, LIGHT_DIRECTIONAL, LIGHT_POINT, LIGHT_SPOT = 0, 1, 2, 3
+CASTS_SHADOW = 1
+CULL_LIGHTS = 1
+
+
+class OrcLight(C.Structure):
+    _fields_ = [("type", C.c_int32), ("flags", C.c_uint32), ("position", C.c_float * 3),
+                ("direction", C.c_float * 3), ("colour", C.c_float * 3), ("intensity", C.c_float),
+                ("range", C.c_float), ("cutoff", C.c_float)]
+
+
+class OrcView(C.Structure):
+    _fields_ = [("position", C.c_float * 3), ("orientation", C.c_float * 4), ("hfov_deg", C.c_float),
+                ("znear", C.c_float), ("zfar", C.c_float), ("vp_width", C.c_int32), ("vp_height", C.c_int32)]
+
+
+LIGHT_DTYPE = np.dtype([("type", "<i4"), ("flags", "<u4"), ("position", "<f4", 3), ("direction", "<f4", 3),
+                        ("colour", "<f4", 3), ("intensity", "<f4"), ("range", "<f4"), ("cutoff", "<f4")])
+VIEW_DTYPE = np.dtype([("position", "<f4", 3), ("orientation", "<f4", 4), ("hfov_deg", "<f4"),
+                       ("znear", "<f4"), ("zfar", "<f4"), ("vp_width", "<i4"), ("vp_height", "<i4")])
+assert LIGHT_DTYPE.itemsize == C.sizeof(OrcLight) == 56
+assert VIEW_DTYPE.itemsize == C.sizeof(OrcView) == 48
+
+
+def make_view(position, orientation, hfov_deg, znear, zfar, vp_width, vp_height) -> np.ndarray:
+    v = np.zeros((), dtype=VIEW_DTYPE)
+    v["position"] = position
+    v["orientation"] = orientation
+    v["hfov_deg"], v["znear"], v["zfar"] = hfov_deg, znear, zfar
+    v["vp_width"], v["vp_height"] = vp_width, vp_height
+    return v
+
+
+def make_light(type, position=(0, 0, 0), direction=(0, 0, -1), colour=(1, 1, 1), intensity=1.0, range=0.0,
+               cutoff=0.0, flags=0) -> np.ndarray:
+    l = np.zeros((), dtype=LIGHT_DTYPE)
+    l["type"], l["flags"] = type, flags
+    l["position"], l["direction"], l["colour"] = position, direction, colour
+    l["intensity"], l["range"], l["cutoff"] = intensity, range, cutoff
+    return l
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p) if a is not None else None
+
+
+def _f32(a, shape=None):
+    a = np.ascontiguousarray(a, dtype=np.float32)
+    if shape is not None:
+        a = a.reshape(shape)
+    return a
+
+
+def build(reference_root: str = "/root/reference") -> None:
+    """Compile the C restatement (always) and, when the reference tree is present, oracle/_ref."""
+    subprocess.run(["make", "-s", "-C", HERE, "libovis_oracle.so"], check=True)
+    if os.path.isdir(os.path.join(reference_root, "engine", "runtime")):
+        subprocess.run(["make", "-s", "-C", HERE, f"REF={reference_root}", "ref"], check=True)
+
+
+def available(kind: str) -> bool:
+    return os.path.exists(PORT_SO if kind == "port" else REF_SO)
+
+
+class Oracle:
+    def __init__(self, path: str):
+        self.lib = C.CDLL(path)
+        L = self.lib
+        L.orc_name.restype = C.c_char_p
+        L.orc_cull_aabb.restype = C.c_int64
+        L.orc_cull_aabb_mt.restype = C.c_int64
+        L.orc_light_cull.restype = C.c_int32
+        L.orc_light_shadow_views.restype = C.c_int32
+        L.orc_shadow_lists.restype = C.c_int32
+        self.name = L.orc_name().decode()
+        self.has_world = hasattr(L, "oref_world_create")
+        if self.has_world:
+            L.oref_world_create.restype = C.c_void_p
+            L.oref_world_add_entities.restype = C.c_int64
+            L.oref_world_add_lights.restype = C.c_int32
+            L.oref_world_cull.restype = C.c_int64
+            L.oref_world_shadow_lists.restype = C.c_int32
+
+    # ---- views
+    def view_planes(self, view: np.ndarray) -> np.ndarray:
+        out = np.zeros(24, dtype=np.float32)
+        self.lib.orc_view_planes(_p(view), _p(out))
+        return out.reshape(6, 4)
+
+    def view_matrices(self, view: np.ndarray):
+        mats = np.zeros(64, dtype=np.float32)
+        corners = np.zeros(24, dtype=np.float32)
+        self.lib.orc_view_matrices(_p(view), _p(mats), _p(corners))
+        return mats.reshape(4, 16), corners.reshape(8, 3)
+
+    # ---- transforms
+    def world_trs(self, parent, local_trs) -> np.ndarray:
+        parent = np.ascontiguousarray(parent, dtype=np.int32)
+        local_trs = _f32(local_trs, (-1, 10))
+        out = np.zeros_like(local_trs)
+        self.lib.orc_world_trs(C.c_int64(len(parent)), _p(parent), _p(local_trs), _p(out))
+        return out
+
+    def trs_matrix(self, trs) -> np.ndarray:
+        trs = _f32(trs, (-1, 10))
+        out = np.zeros((len(trs), 16), dtype=np.float32)
+        self.lib.orc_trs_matrix(C.c_int64(len(trs)), _p(trs), _p(out))
+        return out
+
+    def world_aabb(self, world_trs, local_aabb) -> np.ndarray:
+        world_trs = _f32(world_trs, (-1, 10))
+        local_aabb = _f32(local_aabb, (-1, 6))
+        out = np.zeros_like(local_aabb)
+        self.lib.orc_world_aabb(C.c_int64(len(world_trs)), _p(world_trs), _p(local_aabb), _p(out))
+        return out
+
+    # ---- cull
+    def cull_aabb(self, aabb, planes, flags=None, require=0, threads=1) -> np.ndarray:
+        aabb = _f32(aabb, (-1, 6))
+        planes = _f32(planes, (24,))
+        n = len(aabb)
+        if flags is not None:
+            flags = np.ascontiguousarray(flags, dtype=np.uint32)
+        out = np.empty(max(n, 1), dtype=np.uint32)
+        if threads > 1:
+            c = self.lib.orc_cull_aabb_mt(C.c_int64(n), _p(aabb), _p(planes), _p(flags), C.c_uint32(require),
+                                          _p(out), C.c_int(threads))
+        else:
+            c = self.lib.orc_cull_aabb(C.c_int64(n), _p(aabb), _p(planes), _p(flags), C.c_uint32(require), _p(out))
+        return out[:c].copy()
+
+    # ---- lights
+    def light_spot_aabb(self, light: np.ndarray) -> np.ndarray:
+        out = np.zeros(6, dtype=np.float32)
+        self.lib.orc_light_spot_aabb(_p(light), _p(out))
+        return out
+
+    def light_cull(self, lights: np.ndarray, planes) -> np.ndarray:
+        lights = np.ascontiguousarray(lights, dtype=LIGHT_DTYPE).reshape(-1)
+        planes = _f32(planes, (24,))
+        out = np.empty(max(len(lights), 1), dtype=np.uint32)
+        c = self.lib.orc_light_cull(C.c_int32(len(lights)), _p(lights), _p(planes), _p(out))
+        return out[:c].copy()
+
+    def light_shadow_views(self, light: np.ndarray) -> np.ndarray:
+        out = np.zeros(6, dtype=VIEW_DTYPE)
+        c = self.lib.orc_light_shadow_views(_p(light), _p(out))
+        return out[:c].copy()
+
+    def shadow_lists(self, aabb, flags, lights, main_planes):
+        aabb = _f32(aabb, (-1, 6))
+        n = len(aabb)
+        flags = np.ascontiguousarray(flags, dtype=np.uint32) if flags is not None else None
+        lights = np.ascontiguousarray(lights, dtype=LIGHT_DTYPE).reshape(-1)
+        main_planes = _f32(main_planes, (24,))
+        cap_lists = 6 * max(len(lights), 1)
+        cap_ent = cap_lists * max(n, 1)
+        ll = np.zeros(cap_lists, dtype=np.int32)
+        lv = np.zeros(cap_lists, dtype=np.int32)
+        off = np.zeros(cap_lists + 1, dtype=np.int64)
+        ent = np.zeros(cap_ent, dtype=np.uint32)
+        k = self.lib.orc_shadow_lists(C.c_int64(n), _p(aabb), _p(flags), C.c_int32(len(lights)), _p(lights),
+                                      _p(main_planes), C.c_int32(cap_lists), _p(ll), _p(lv), _p(off),
+                                      C.c_int64(cap_ent), _p(ent))
+        assert k >= 0
+        return ll[:k].copy(), lv[:k].copy(), off[:k + 1].copy(), ent[:off[k]].copy()
+
+    # ---- tier A object world (reference build only)
+    def world(self) -> "RefWorld":
+        assert self.has_world, "object world exists only in the reference-compiled oracle"
+        return RefWorld(self)
+
+
+class RefWorld:
+    """SimpleRenderWorld + RenderEntity + RenderLight + RenderView exactly as the reference ships them."""
+
+    def __init__(self, oracle: Oracle):
+        self.o = oracle
+        self.lib = oracle.lib
+        self.h = C.c_void_p(self.lib.oref_world_create())
+        self.n_entities = 0
+        self.n_lights = 0
+
+    def close(self):
+        if self.h:
+            self.lib.oref_world_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        self.close()
+
+    def add_entities(self, trs, local_aabb, flags=None) -> int:
+        trs = _f32(trs, (-1, 10))
+        local_aabb = _f32(local_aabb, (-1, 6))
+        flags = np.ascontiguousarray(flags, dtype=np.uint32) if flags is not None else None
+        first = self.lib.oref_world_add_entities(self.h, C.c_int64(len(trs)), _p(trs), _p(local_aabb), _p(flags))
+        self.n_entities += len(trs)
+        return first
+
+    def set_transforms(self, idx, trs):
+        idx = np.ascontiguousarray(idx, dtype=np.uint32)
+        trs = _f32(trs, (-1, 10))
+        self.lib.oref_world_set_transforms(self.h, C.c_int64(len(idx)), _p(idx), _p(trs))
+
+    def set_local_aabb(self, idx, box):
+        box = _f32(box, (6,))
+        self.lib.oref_world_set_local_aabb(self.h, C.c_uint32(idx), _p(box))
+
+    def set_flags(self, idx, flags):
+        self.lib.oref_world_set_flags(self.h, C.c_uint32(idx), C.c_uint32(flags))
+
+    def remove_entity(self, idx):
+        self.lib.oref_world_remove_entity(self.h, C.c_uint32(idx))
+
+    def bounds(self, first=0, n=None) -> np.ndarray:
+        n = self.n_entities - first if n is None else n
+        out = np.zeros((n, 6), dtype=np.float32)
+        self.lib.oref_world_get_bounds(self.h, C.c_int64(first), C.c_int64(n), _p(out))
+        return out
+
+    def matrices(self, first=0, n=None) -> np.ndarray:
+        n = self.n_entities - first if n is None else n
+        out = np.zeros((n, 16), dtype=np.float32)
+        self.lib.oref_world_get_matrices(self.h, C.c_int64(first), C.c_int64(n), _p(out))
+        return out
+
+    def add_lights(self, lights) -> int:
+        lights = np.ascontiguousarray(lights, dtype=LIGHT_DTYPE).reshape(-1)
+        first = self.lib.oref_world_add_lights(self.h, C.c_int32(len(lights)), _p(lights))
+        self.n_lights += len(lights)
+        return first
+
+    def update_light(self, idx, light):
+        light = np.ascontiguousarray(light, dtype=LIGHT_DTYPE)
+        self.lib.oref_world_update_light(self.h, C.c_uint32(idx), _p(light))
+
+    def remove_light(self, idx):
+        self.lib.oref_world_remove_light(self.h, C.c_uint32(idx))
+
+    def cull(self, view, flags=CULL_LIGHTS):
+        ents = np.empty(max(self.n_entities, 1), dtype=np.uint32)
+        lights = np.empty(max(self.n_lights, 1), dtype=np.uint32)
+        nl = C.c_int32(0)
+        ne = self.lib.oref_world_cull(self.h, _p(view), C.c_uint32(flags), _p(ents), _p(lights), C.byref(nl))
+        return ents[:ne].copy(), lights[:nl.value].copy()
+
+    def shadow_lists(self, main_view, shadow_res=512):
+        cap_lists = 6 * max(self.n_lights, 1)
+        cap_ent = cap_lists * max(self.n_entities, 1)
+        ll = np.zeros(cap_lists, dtype=np.int32)
+        lv = np.zeros(cap_lists, dtype=np.int32)
+        off = np.zeros(cap_lists + 1, dtype=np.int64)
+        ent = np.zeros(cap_ent, dtype=np.uint32)
+        k = self.lib.oref_world_shadow_lists(self.h, _p(main_view), C.c_int32(shadow_res), C.c_int32(cap_lists),
+                                             _p(ll), _p(lv), _p(off), C.c_int64(cap_ent), _p(ent))
+        assert k >= 0
+        return ll[:k].copy(), lv[:k].copy(), off[:k + 1].copy(), ent[:off[k]].copy()
+
+    def time_cull(self, view, flags=0, iters=5):
+        ms = np.zeros(iters, dtype=np.float64)
+        vis = C.c_int64(0)
+        self.lib.oref_world_time_cull(self.h, _p(view), C.c_uint32(flags), C.c_int32(iters), _p(ms), C.byref(vis))
+        return ms, vis.value
+
+
+_cache: dict[str, Oracle] = {}
+
+
+def load(kind: str = "port") -> Oracle:
+    """kind = "port" | "reference" | "best" (reference when built, else port)."""
+    if kind == "best":
+        kind = "reference" if available("reference") else "port"
+    if kind not in _cache:
+        path = PORT_SO if kind == "port" else REF_SO
+        if not os.path.exists(path):
+            if kind == "port":
+                build()
+            else:
+                raise FileNotFoundError(f"{path} is not built (needs /root/reference; run make -C oracle ref)")
+        _cache[kind] = Oracle(path)
+    return _cache[kind]

@@ -1,0 +1,148 @@
+"""The C restatement (oracle/ovis_oracle.c) must equal the reference-compiled oracle (oracle/_ref)
+value-for-value on every function of the path. Runs only where oracle/_ref is built (the container
+that has /root/reference, or a box the prebuilt .so travelled to); tests/test_golden.py pins the same
+functions against committed fixtures everywhere else."""
+import numpy as np
+import pytest
+
+from orion_b200 import scenes
+import vis_testutil as util
+from vis_testutil import same
+
+
+def test_view_planes_and_matrices(port, ref):
+    rng = np.random.default_rng(11)
+    views = util.random_views(rng, 300)
+    for v in list(views) + [scenes.default_camera(), scenes.cubes_scene()["view"]]:
+        v = np.asarray(v)
+        assert same(port.view_planes(v), ref.view_planes(v))
+        pm, pc = port.view_matrices(v)
+        rm, rc = ref.view_matrices(v)
+        assert same(pm, rm) and same(pc, rc)
+
+
+def test_world_trs_chain(port, ref):
+    rng = np.random.default_rng(12)
+    n = 5000
+    parent = np.empty(n, dtype=np.int32)
+    parent[0] = -1
+    parent[1:] = (rng.random(n - 1) * np.arange(1, n)).astype(np.int32)   # any earlier node
+    parent[1:50] = np.arange(0, 49)                                        # a 50-deep chain
+    local = util.random_trs(rng, n)
+    assert same(port.world_trs(parent, local), ref.world_trs(parent, local))
+
+
+def test_matrix_and_world_aabb(port, ref):
+    rng = np.random.default_rng(13)
+    n = 20000
+    trs = util.random_trs(rng, n)
+    boxes = util.random_boxes(rng, n)
+    trs[:16] = scenes.IDENTITY_TRS
+    e = util.edge_boxes()
+    boxes[:len(e)] = e
+    trs[16, 0] = np.nan
+    trs[17, 3] = np.inf
+    trs[18, 7:10] = 0
+    assert same(port.trs_matrix(trs), ref.trs_matrix(trs))
+    assert same(port.world_aabb(trs, boxes), ref.world_aabb(trs, boxes))
+
+
+def test_cull_flat(port, ref):
+    rng = np.random.default_rng(14)
+    boxes = np.concatenate([util.edge_boxes(), util.random_boxes(rng, 50000, extent=300.0)])
+    flags = rng.integers(0, 4, len(boxes)).astype(np.uint32)
+    for v in util.random_views(rng, 20, extent=50.0):
+        planes = ref.view_planes(np.asarray(v))
+        a = ref.cull_aabb(boxes, planes)
+        assert np.array_equal(port.cull_aabb(boxes, planes), a)
+        assert np.array_equal(port.cull_aabb(boxes, planes, threads=3), a)
+        assert np.array_equal(ref.cull_aabb(boxes, planes, threads=4), a)
+        b = ref.cull_aabb(boxes, planes, flags, 1)
+        assert np.array_equal(port.cull_aabb(boxes, planes, flags, 1), b)
+        assert np.array_equal(b, a[(flags[a] & 1) == 1])
+    # axis-aligned planes with zero normal components and boxes touching them exactly
+    planes = np.array([[1, 0, 0, -10], [-1, 0, 0, -10], [0, -1, 0, -10], [0, 1, 0, -10], [0, 0, -1, -10],
+                       [0, 0, 1, -10]], dtype=np.float32)
+    touch = np.array([[10, 0, 0, 11, 1, 1], [-11, 0, 0, -10, 1, 1], [10.000001, 0, 0, 11, 1, 1],
+                      [-12, 0, 0, -10.000001, 1, 1], [0, 0, 0, 1, 1, 1]], dtype=np.float32)
+    assert np.array_equal(port.cull_aabb(touch, planes), ref.cull_aabb(touch, planes))
+    planes[:, :3] *= -0.0   # all-zero normals with negative zero sign: p-vertex picks max, distance = -w
+    assert np.array_equal(port.cull_aabb(touch, planes), ref.cull_aabb(touch, planes))
+
+
+def test_lights(port, ref):
+    rng = np.random.default_rng(15)
+    lights = util.random_lights(rng, 400)
+    for l in lights[lights["type"] == scenes.LIGHT_SPOT]:
+        assert same(port.light_spot_aabb(np.asarray(l)), ref.light_spot_aabb(np.asarray(l)))
+    for l in lights:
+        pv, rv = port.light_shadow_views(np.asarray(l)), ref.light_shadow_views(np.asarray(l))
+        assert pv.tobytes() == rv.tobytes()
+    for v in util.random_views(rng, 10, extent=50.0):
+        planes = ref.view_planes(np.asarray(v))
+        assert np.array_equal(port.light_cull(lights, planes), ref.light_cull(lights, planes))
+
+
+def test_shadow_lists_flat(port, ref):
+    rng = np.random.default_rng(16)
+    boxes = util.random_boxes(rng, 4000, extent=60.0, hmax=3.0)
+    flags = rng.integers(0, 2, len(boxes)).astype(np.uint32)
+    lights = util.random_lights(rng, 24, extent=40.0)
+    cam = scenes.make_view((0, 0, 70), (1, 0, 0, 0), 90.0, 0.1, 300.0, 1600, 900)
+    planes = ref.view_planes(cam)
+    a, b = port.shadow_lists(boxes, flags, lights, planes), ref.shadow_lists(boxes, flags, lights, planes)
+    assert len(a[0]) > 0
+    for x, y in zip(a, b):
+        assert np.array_equal(x, y)
+
+
+def test_tier_a_world_equals_flat(port, ref):
+    """SimpleRenderWorld as shipped (std::list of RenderEntity) == the flat restated loop, including
+    removal keeping order, light culling and the prepareLights shadow lists."""
+    rng = np.random.default_rng(17)
+    n = 3000
+    trs = util.random_trs(rng, n, pos=60.0)
+    local = util.random_boxes(rng, n, extent=2.0, hmax=2.0)
+    flags = rng.integers(0, 2, n).astype(np.uint32)
+    lights = util.random_lights(rng, 16, extent=40.0)
+    w = ref.world()
+    w.add_entities(trs, local, flags)
+    w.add_lights(lights)
+    wb = w.bounds()
+    assert same(wb, port.world_aabb(trs, local))
+    assert same(w.matrices(), port.trs_matrix(trs))
+    cam = scenes.make_view((0, 0, 80), (1, 0, 0, 0), 90.0, 0.1, 300.0, 1600, 900)
+    planes = port.view_planes(cam)
+    ents, ls = w.cull(cam)
+    assert np.array_equal(ents, port.cull_aabb(wb, planes))
+    assert np.array_equal(ls, port.light_cull(lights, planes))
+    got = w.shadow_lists(cam)
+    exp = port.shadow_lists(wb, flags, lights, planes)
+    for x, y in zip(got, exp):
+        assert np.array_equal(x, y)
+    # removal preserves the order of the survivors (std::list::remove, simple_render_world.cc:65-67)
+    removed = rng.choice(n, 500, replace=False)
+    for i in removed:
+        w.remove_entity(int(i))
+    keep = np.ones(n, dtype=bool)
+    keep[removed] = False
+    ents2, _ = w.cull(cam, flags=0)
+    assert np.array_equal(ents2, ents[keep[ents]])
+    w.close()
+
+
+def test_cubes_scene_twenty_views(port, ref):
+    s = scenes.cubes_scene()
+    w = ref.world()
+    w.add_entities(s["trs"], s["local_aabb"], s["flags"])
+    w.add_lights(s["lights"])
+    ents, ls = w.cull(s["view"])
+    ll, lv, off, ent = w.shadow_lists(s["view"])
+    assert len(ll) + 1 == 20 or len(ls) < 5      # 1 + 1 + 3*6 views when every light is visible
+    wb = port.world_aabb(s["trs"], s["local_aabb"])
+    planes = port.view_planes(s["view"])
+    assert np.array_equal(ents, port.cull_aabb(wb, planes))
+    exp = port.shadow_lists(wb, s["flags"], s["lights"], planes)
+    for x, y in zip((ll, lv, off, ent), exp):
+        assert np.array_equal(x, y)
+    w.close()

@@ -1,0 +1,72 @@
+"""Shared helpers for the parity tests."""
+import numpy as np
+
+from orion_b200 import scenes
+
+
+def same(a, b) -> bool:
+    """Value-exact equality for float arrays: identical values, NaNs in identical places."""
+    a, b = np.asarray(a), np.asarray(b)
+    return a.shape == b.shape and bool(np.array_equal(a, b, equal_nan=True))
+
+
+def random_views(rng, n, extent=100.0):
+    out = np.zeros(n, dtype=scenes.VIEW_DTYPE)
+    sizes = [(1920, 1080), (1440, 900), (512, 512), (800, 600), (1000, 333)]
+    for i in range(n):
+        w, h = sizes[rng.integers(len(sizes))]
+        zn = float(rng.uniform(0.05, 2.0))
+        out[i] = scenes.make_view(rng.uniform(-extent, extent, 3), scenes.random_unit_quats(rng, 1)[0],
+                                  float(rng.uniform(20, 120)), zn, zn + float(rng.uniform(5, 2000)), w, h)
+    return out
+
+
+def random_trs(rng, n, pos=100.0):
+    t = np.empty((n, 10), dtype=np.float32)
+    t[:, 0:3] = rng.uniform(-pos, pos, (n, 3))
+    t[:, 3:7] = scenes.random_unit_quats(rng, n)
+    t[:, 7:10] = rng.uniform(-3, 3, (n, 3))          # negative scale included
+    return t
+
+
+def random_boxes(rng, n, extent=100.0, hmax=8.0):
+    c = rng.uniform(-extent, extent, (n, 3)).astype(np.float32)
+    h = rng.uniform(0, hmax, (n, 3)).astype(np.float32)
+    return np.concatenate([c - h, c + h], axis=1).astype(np.float32)
+
+
+def edge_boxes():
+    """Edge-case pack: skybox, zero-size, inverted, NaN, Inf, signed zeros."""
+    fmax = np.finfo(np.float32).max
+    inf, nan = np.float32(np.inf), np.float32(np.nan)
+    return np.array([
+        [-fmax, -fmax, -fmax, fmax, fmax, fmax],
+        [0, 0, 0, 0, 0, 0],
+        [1, 2, -30, 1, 2, -30],
+        [5, 5, -5, -5, -5, -50],
+        [nan, 0, 0, 1, 1, 1],
+        [0, 0, 0, nan, nan, nan],
+        [-inf, -inf, -inf, inf, inf, inf],
+        [inf, inf, inf, inf, inf, inf],
+        [-0.0, -0.0, -0.0, 0.0, 0.0, 0.0],
+        [-1e-30, -1e-30, -1e-30, 1e-30, 1e-30, 1e-30],
+        [1e30, 1e30, 1e30, 2e30, 2e30, 2e30],
+    ], dtype=np.float32)
+
+
+def random_lights(rng, n, extent=100.0):
+    l = np.zeros(n, dtype=scenes.LIGHT_DTYPE)
+    l["type"] = rng.integers(0, 4, n)
+    l["flags"] = rng.integers(0, 2, n)
+    l["position"] = rng.uniform(-extent, extent, (n, 3))
+    d = rng.standard_normal((n, 3)).astype(np.float32)
+    axis = rng.random(n) < 0.2                        # exact axis directions hit quatRotateBetween's special branch
+    d[axis] = np.array([[0, 0, 1], [0, 0, -1], [0, 1, 0], [1, 0, 0], [0, -1, 0]], dtype=np.float32)[rng.integers(0, 5, axis.sum())]
+    l["direction"] = d
+    l["colour"] = rng.uniform(0, 1, (n, 3))
+    black = rng.random(n) < 0.1
+    l["colour"][black] = 0
+    l["intensity"] = np.where(rng.random(n) < 0.1, 0.0, rng.uniform(0.01, 2.0, n))
+    l["range"] = rng.uniform(1, 80, n)
+    l["cutoff"] = rng.uniform(1, 45, n)
+    return l
