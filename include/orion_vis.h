@@ -1,0 +1,225 @@
+/*
+ * orion_vis.h - C ABI of the B200 scene-visibility library (liborion_vis.so).
+ *
+ * This is the drop-in boundary for the one hot path this project accelerates: Orion's per-frame
+ * scene visibility (world-transform propagation + world AABB recompute, frustum culling of render
+ * entities and lights per view, per-light shadow-caster lists). Each entry point names the reference
+ * interface it replaces; paths are relative to /root/reference/engine/runtime/ unless they start
+ * with engine/ or apps/. INTEGRATION.md shows the C++ adapter (CudaRenderWorld : RenderWorld) a
+ * maintainer drops in at graphics/src/graphics_system.cc:33-36.
+ *
+ * Rules of the ABI
+ *   - plain C types only; every function returns an OvisStatus (0 = ok) and never throws or exits;
+ *     ovis_last_error() returns a thread-local description of the last failure.
+ *   - one host thread per world (the engine is single-threaded).
+ *   - there is NO CPU fallback: without a CUDA device every call that needs one fails with
+ *     OVIS_ERR_CUDA.
+ *   - entity / node / light ids are stable uint32 handles, assigned in insertion order. Every result
+ *     list is emitted in insertion order of the ids it holds, which is the order the reference's
+ *     std::list walk produces (render/src/simple_render_world.cc:38-41,53-55,65-67).
+ *
+ * Layouts (all little-endian fp32 / uint32)
+ *   TRS    10 floats: position xyz, orientation w x y z, scale xyz       (core/include/math/transform.h:55-61)
+ *   AABB    6 floats: minimum xyz, maximum xyz                            (core/include/math/bounding_box.h:28-31)
+ *   planes 24 floats: 6 x (normal xyz, distance), Left Right Top Bottom Near Far (core/include/math/frustum.h:39-47)
+ */
+#ifndef ORION_VIS_H
+#define ORION_VIS_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct OvisWorld OvisWorld;
+
+typedef enum OvisStatus {
+    OVIS_OK = 0,
+    OVIS_ERR_INVALID = 1,     /* bad argument (null pointer, unknown id, unsupported flag mask ...) */
+    OVIS_ERR_CUDA = 2,        /* CUDA runtime error or no device */
+    OVIS_ERR_CAPACITY = 3,    /* caller-provided output buffer too small; required size is reported */
+    OVIS_ERR_NOMEM = 4
+} OvisStatus;
+
+/* RenderLight::Type, render/include/render_light.h:52-58 */
+enum { OVIS_LIGHT_AMBIENT = 0, OVIS_LIGHT_DIRECTIONAL = 1, OVIS_LIGHT_POINT = 2, OVIS_LIGHT_SPOT = 3 };
+/* RenderEntity::kCastsShadow (render/include/render_entity.h:50-53), RenderLight::kCastsShadows (render_light.h:61-64) */
+enum { OVIS_CASTS_SHADOW = 1u };
+/* RenderWorld::CullFlags::kCullLights, render/include/render_world.h:43-46 */
+enum { OVIS_CULL_LIGHTS = 1u };
+#define OVIS_NO_PARENT (-1)
+
+/* Parameters a RenderLight is configured with through its setters (render/src/render_light.cc:67-142). */
+typedef struct OvisLight {
+    int32_t  type;
+    uint32_t flags;
+    float    position[3];
+    float    direction[3];    /* normalised on use, as RenderLight::setDirection does (:78-85) */
+    float    colour[3];
+    float    intensity;
+    float    range;
+    float    cutoff;          /* degrees, spot lights, <= 45 (:104) */
+} OvisLight;                   /* 56 bytes */
+
+/* Parameters a RenderView is configured with: setTransform / perspective / setViewport
+ * (render/src/render_view.cc:51-90). aspect = (float)vp_width / (float)vp_height (:84). */
+typedef struct OvisView {
+    float   position[3];
+    float   orientation[4];   /* w x y z */
+    float   hfov_deg;
+    float   znear;
+    float   zfar;
+    int32_t vp_width;
+    int32_t vp_height;
+} OvisView;                    /* 48 bytes */
+
+const char *ovis_last_error(void);
+/* Library build description, e.g. "orion_vis sm_100a fmad=off". */
+const char *ovis_version(void);
+
+/* ------------------------------------------------------------------------------------------------
+ * World lifetime - replaces `new SimpleRenderWorld` (graphics/src/graphics_system.cc:33-36,
+ * render/include/simple_render_world.h:29-53). All device memory of the world lives on `device`.
+ * ---------------------------------------------------------------------------------------------- */
+int ovis_world_create(int device, OvisWorld **out_world);
+int ovis_world_destroy(OvisWorld *world);
+/* Pre-size device storage (optional; storage otherwise grows geometrically). */
+int ovis_world_reserve(OvisWorld *world, int64_t n_entities, int64_t n_nodes);
+/* All kernels and copies of the world are issued on this cudaStream_t (default: the legacy stream). */
+int ovis_world_set_stream(OvisWorld *world, void *cuda_stream);
+/* Sharded worlds: this world holds the contiguous id range starting at id_base
+ * of a larger scene; ids reported by the entity culls are local id + id_base, so the per-shard lists
+ * concatenated in rank order are the single-world list of simple_render_world.cc:38-41. Ids passed
+ * INTO the API stay local. Default 0. */
+int ovis_world_set_id_base(OvisWorld *world, uint32_t id_base);
+int ovis_world_counts(OvisWorld *world, int64_t *n_entities, int64_t *n_nodes, int32_t *n_lights);
+
+/* ------------------------------------------------------------------------------------------------
+ * Render entities - RenderWorld::addEntity / updateEntity / removeEntity
+ * (render/include/render_world.h:69-83; callers render/src/render_entity.cc:52-97).
+ * ---------------------------------------------------------------------------------------------- */
+/* RenderEntity::setWorld -> addEntity (render_entity.cc:52-60) for n entities; local AABBs as
+ * RenderEntity::setBoundingBox (:76-80), flags as setFlags (render_entity.h:64). Ids are
+ * first_id .. first_id + n - 1. An entity has no world bounds until it is given a transform
+ * (ovis_entity_set_transforms / ovis_node_bind_entities) or explicit bounds (ovis_entity_set_world_aabbs);
+ * until then its world AABB is its local AABB (identity transform, Transform::Transform() transform.h:64-70). */
+int ovis_entity_add(OvisWorld *world, int64_t n, const float *local_aabb, const uint32_t *flags, uint32_t *out_first_id);
+/* RenderEntity::~RenderEntity -> setWorld(nullptr) -> removeEntity (render_entity.cc:46-60;
+ * simple_render_world.cc:65-67): survivors keep their relative order. */
+int ovis_entity_remove(OvisWorld *world, int64_t n, const uint32_t *ids);
+/* RenderEntity::setBoundingBox (render_entity.cc:76-80) */
+int ovis_entity_set_local_aabbs(OvisWorld *world, int64_t n, const uint32_t *ids, const float *local_aabb);
+/* RenderEntity::setFlags (render_entity.h:64) */
+int ovis_entity_set_flags(OvisWorld *world, int64_t n, const uint32_t *ids, const uint32_t *flags);
+/* RenderEntity::setTransform with a WORLD transform (render_entity.cc:64-72; caller
+ * graphics/src/renderer.cc:62-66). World AABBs are recomputed on the device by the next
+ * ovis_update_transforms (or implicitly by the next cull). */
+int ovis_entity_set_transforms(OvisWorld *world, int64_t n, const uint32_t *ids, const float *world_trs);
+/* Static geometry: give n consecutive entities their WORLD AABBs directly (what updateWorld,
+ * render_entity.cc:90-93, would have produced), bypassing the transform stage. */
+int ovis_entity_set_world_aabbs(OvisWorld *world, uint32_t first_id, int64_t n, const float *world_aabb);
+
+/* ------------------------------------------------------------------------------------------------
+ * Transform tree - Entity local/world transforms (engine/include/entity.h:45-190,
+ * engine/src/entity.cc:309-363 setters, :382-411 transformed()).
+ * ---------------------------------------------------------------------------------------------- */
+/* Add n nodes. parent[i] is an existing node id, an id assigned earlier in this same call, or
+ * OVIS_NO_PARENT for a child of the (identity) root. Ids are first_id .. first_id + n - 1. */
+int ovis_node_add(OvisWorld *world, int64_t n, const int32_t *parent, const float *local_trs, uint32_t *out_first_id);
+/* Entity::setPosition / setOrientation / setScale, batched (entity.cc:309-363). */
+int ovis_node_set_local_trs(OvisWorld *world, int64_t n, const uint32_t *ids, const float *local_trs);
+/* Renderer component on an Entity: its RenderEntities follow the node's world transform
+ * (graphics/src/renderer.cc:62-66). */
+int ovis_node_bind_entities(OvisWorld *world, int64_t n, const uint32_t *node_ids, const uint32_t *entity_ids);
+/* Entity::transformed over everything that changed since the last call (entity.cc:382-411), then
+ * Transform::matrix + BoundingBox::transform for every affected entity (core/src/math/transform.cc:26-35,
+ * core/src/math/bounding_box.cc:27-40, render_entity.cc:90-93). Asynchronous on the world's stream. */
+int ovis_update_transforms(OvisWorld *world);
+
+/* ------------------------------------------------------------------------------------------------
+ * Lights - RenderWorld::addLight / updateLight / removeLight (render_world.h:85-95).
+ * ---------------------------------------------------------------------------------------------- */
+int ovis_light_add(OvisWorld *world, int32_t n, const OvisLight *lights, uint32_t *out_first_id);
+int ovis_light_update(OvisWorld *world, uint32_t id, const OvisLight *light);
+int ovis_light_remove(OvisWorld *world, uint32_t id);
+
+/* ------------------------------------------------------------------------------------------------
+ * Host-side view / light set-up (O(views); kept on the host so the planes are built by the same
+ * libm and the same operation order as the reference).
+ * ---------------------------------------------------------------------------------------------- */
+/* RenderView::updateMatrices + Frustum::update (render/src/render_view.cc:102-135, core/src/math/frustum.cc:27-67) */
+int ovis_view_planes(const OvisView *view, float out_planes[24]);
+/* Same, also returning view, projection, viewProjection, inverseViewProjection (4 x 16 floats,
+ * column-major) and the 8 frustum corners (frustum.cc:70-84). Either output may be NULL. */
+int ovis_view_matrices(const OvisView *view, float out_mats[64], float out_corners[24]);
+/* RenderLight::updateVolumeTransform, spot branch (render/src/render_light.cc:227-249) */
+int ovis_light_spot_aabb(const OvisLight *light, float out_aabb[6]);
+/* RenderLight::updateShadowViews (render_light.cc:258-332) with the square shadow-map viewport of
+ * render/src/deferred_render_pipeline.cc:261-265. *out_count = 0, 1 (spot) or 6 (point). */
+int ovis_light_shadow_views(const OvisLight *light, int32_t shadow_map_resolution, OvisView out_views[6], int32_t *out_count);
+
+/* ------------------------------------------------------------------------------------------------
+ * Culling - RenderWorld::cull (render/include/render_world.h:69-77; render/src/simple_render_world.cc:37-49).
+ * Pending transform updates are flushed first.
+ * ---------------------------------------------------------------------------------------------- */
+/* cull(view, results, flags) into HOST buffers. out_entities receives ids of entities whose world
+ * AABB intersects the view frustum (core/src/math/intersection.cc:42-57); when flags has
+ * OVIS_CULL_LIGHTS, out_lights receives ids of lights for which RenderLight::cull is false
+ * (render_light.cc:187-209). Counts are always written; if a capacity is too small the call returns
+ * OVIS_ERR_CAPACITY and nothing else is written for that list. out_lights may be NULL when
+ * OVIS_CULL_LIGHTS is not set. */
+int ovis_cull(OvisWorld *world, const OvisView *view, uint32_t flags,
+              uint32_t *out_entities, int64_t cap_entities, int64_t *out_n_entities,
+              uint32_t *out_lights, int32_t cap_lights, int32_t *out_n_lights);
+/* Entity cull against explicit planes; require = 0 or OVIS_CASTS_SHADOW (the castsShadow() filter of
+ * deferred_render_pipeline.cc:273 folded into the pass). HOST output. */
+int ovis_cull_planes(OvisWorld *world, const float planes[24], uint32_t require,
+                     uint32_t *out_entities, int64_t cap_entities, int64_t *out_n_entities);
+/* Same, DEVICE output, asynchronous on the world's stream: d_out_entities must hold one uint32 per
+ * live entity slot (ovis_world_counts), d_out_count is one uint32 in device memory. */
+int ovis_cull_planes_device(OvisWorld *world, const float planes[24], uint32_t require,
+                            uint32_t *d_out_entities, uint32_t *d_out_count);
+
+/* Many views in one pass over the bounds (main camera + cascades + every shadow view:
+ * deferred_render_pipeline.cc:147,259-284). planes = n_views x 24 floats, require = n_views masks (NULL = 0).
+ * Results stay on the device in CSR form and are valid until the next call on this world:
+ * *d_offsets -> n_views + 1 int64, *d_entities -> offsets[n_views] uint32 (insertion order per view).
+ * host_offsets (optional, n_views + 1) receives a synchronous copy of the offsets. */
+int ovis_cull_views_device(OvisWorld *world, int32_t n_views, const float *planes, const uint32_t *require,
+                           const int64_t **d_offsets, const uint32_t **d_entities, int64_t *host_offsets);
+
+/* DeferredRenderPipeline::prepareLights' cull+filter loop (deferred_render_pipeline.cc:207,247,257-284):
+ * for every light not culled by main_view that casts shadows (spot, point), one list per shadow view
+ * holding the ids of the castsShadow() entities intersecting it. HOST output:
+ * out_list_light[k] / out_list_view[k] name list k, out_offsets has n_lists + 1 entries.
+ * Returns OVIS_ERR_CAPACITY (with *out_n_lists / *out_n_entities = required sizes) if a buffer is too small. */
+int ovis_build_shadow_lists(OvisWorld *world, const OvisView *main_view, int32_t shadow_map_resolution,
+                            int32_t cap_lists, int32_t *out_list_light, int32_t *out_list_view,
+                            int64_t *out_offsets, int32_t *out_n_lists,
+                            int64_t cap_entities, uint32_t *out_entities, int64_t *out_n_entities);
+
+/* ------------------------------------------------------------------------------------------------
+ * Read-back for parity checks (RenderEntity::worldBoundingBox / Entity::worldTransform /
+ * RenderEntity::transform().matrix()). HOST output, synchronous.
+ * ---------------------------------------------------------------------------------------------- */
+int ovis_get_world_aabbs(OvisWorld *world, uint32_t first_entity, int64_t n, float *out_aabb);
+int ovis_get_node_world_trs(OvisWorld *world, uint32_t first_node, int64_t n, float *out_trs);
+
+/* Copy `bytes` from a device pointer this library handed out (e.g. the CSR arrays of
+ * ovis_cull_views_device) to host memory, after all work queued on the world's stream; for ABI users
+ * that bind no CUDA runtime of their own (cgo, ctypes). No counterpart in the reference (its results are
+ * host std::lists, render_world.h:49-55). */
+int ovis_read_device(OvisWorld *world, const void *d_src, int64_t bytes, void *host_dst);
+
+/* Pinned host memory for result buffers (plain malloc'd buffers work too, only slower to copy into). */
+int ovis_host_alloc(int64_t bytes, void **out_ptr);
+int ovis_host_free(void *ptr);
+
+/* Number of kernels this library has launched on behalf of `world` since creation (bench.py's gpu_launches). */
+int ovis_world_launch_count(OvisWorld *world, int64_t *out_launches);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ORION_VIS_H */

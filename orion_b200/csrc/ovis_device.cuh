@@ -1,0 +1,137 @@
+// ovis_device.cuh - device-side arithmetic shared by the kernels.
+//
+// Everything on a result path is IEEE binary32 round-to-nearest with NO contraction: the library is
+// compiled with -fmad=false and the helpers below additionally spell the operations with
+// __fmul_rn / __fadd_rn / __fsub_rn (which the compiler never fuses), in the association order of the
+// reference's GLM 0.9.8.0 scalar code. Citations are relative to /root/reference/engine/runtime/
+// ("glm/" = /root/reference/engine/3rdparty/glm/repo/glm/).
+#pragma once
+
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace ovis {
+
+__device__ __forceinline__ float mul(float a, float b) { return __fmul_rn(a, b); }
+__device__ __forceinline__ float add(float a, float b) { return __fadd_rn(a, b); }
+__device__ __forceinline__ float sub(float a, float b) { return __fsub_rn(a, b); }
+// glm/detail/func_common.inl:15-28 - ternaries (NaN and signed-zero behaviour differs from fminf/fmaxf)
+__device__ __forceinline__ float glm_min(float a, float b) { return a < b ? a : b; }
+__device__ __forceinline__ float glm_max(float a, float b) { return a > b ? a : b; }
+
+struct DVec3 {
+    float x, y, z;
+};
+struct DVec4 {
+    float x, y, z, w;
+};
+struct DQuat {
+    float w, x, y, z;
+};
+struct DTrs {
+    DVec3 p;
+    DQuat q;
+    DVec3 s;
+};
+
+__device__ __forceinline__ DVec4 scale4(DVec4 v, float s) { return { mul(v.x, s), mul(v.y, s), mul(v.z, s), mul(v.w, s) }; }
+__device__ __forceinline__ DVec4 add4(DVec4 a, DVec4 b) { return { add(a.x, b.x), add(a.y, b.y), add(a.z, b.z), add(a.w, b.w) }; }
+
+// glm/detail/func_geometric.inl:73-85
+__device__ __forceinline__ DVec3 cross3(DVec3 a, DVec3 b) {
+    return { sub(mul(a.y, b.z), mul(b.y, a.z)), sub(mul(a.z, b.x), mul(b.z, a.x)), sub(mul(a.x, b.y), mul(b.x, a.y)) };
+}
+
+// Entity::transformed, engine/src/entity.cc:394-396 (operators: glm/gtc/quaternion.inl:313-321, :256-270)
+__device__ __forceinline__ DTrs compose_trs(const DTrs &parent, const DTrs &local) {
+    DTrs w;
+    // position = (parentOrientation * (parentScale * position)) + parentPosition
+    DVec3 t = { mul(parent.s.x, local.p.x), mul(parent.s.y, local.p.y), mul(parent.s.z, local.p.z) };
+    DVec3 u = { parent.q.x, parent.q.y, parent.q.z };
+    DVec3 uv = cross3(u, t);
+    DVec3 uuv = cross3(u, uv);
+    DVec3 r = { add(t.x, mul(add(mul(uv.x, parent.q.w), uuv.x), 2.0f)),
+                add(t.y, mul(add(mul(uv.y, parent.q.w), uuv.y), 2.0f)),
+                add(t.z, mul(add(mul(uv.z, parent.q.w), uuv.z), 2.0f)) };
+    w.p = { add(r.x, parent.p.x), add(r.y, parent.p.y), add(r.z, parent.p.z) };
+    // orientation = parentOrientation * orientation (left-to-right sums)
+    const DQuat &p = parent.q, &q = local.q;
+    w.q.w = sub(sub(sub(mul(p.w, q.w), mul(p.x, q.x)), mul(p.y, q.y)), mul(p.z, q.z));
+    w.q.x = sub(add(add(mul(p.w, q.x), mul(p.x, q.w)), mul(p.y, q.z)), mul(p.z, q.y));
+    w.q.y = sub(add(add(mul(p.w, q.y), mul(p.y, q.w)), mul(p.z, q.x)), mul(p.x, q.z));
+    w.q.z = sub(add(add(mul(p.w, q.z), mul(p.z, q.w)), mul(p.x, q.y)), mul(p.y, q.x));
+    // scale = parentScale * scale
+    w.s = { mul(parent.s.x, local.s.x), mul(parent.s.y, local.s.y), mul(parent.s.z, local.s.z) };
+    return w;
+}
+
+struct DMat4 {
+    DVec4 c[4];
+};
+
+// glm/detail/type_mat4x4.inl:601-620
+__device__ __forceinline__ DMat4 mat_mul(const DMat4 &a, const DMat4 &b) {
+    DMat4 r;
+#pragma unroll
+    for (int j = 0; j < 4; j++)
+        r.c[j] = add4(add4(add4(scale4(a.c[0], b.c[j].x), scale4(a.c[1], b.c[j].y)), scale4(a.c[2], b.c[j].z)),
+                      scale4(a.c[3], b.c[j].w));
+    return r;
+}
+
+// Transform::matrix, core/src/math/transform.cc:26-35: translate(I,p) * mat4_cast(q) * scale(I,s), evaluated
+// as the full 4x4 products GLM performs (so Inf/NaN inputs poison exactly the entries they poison there;
+// for finite inputs the compiler folds the multiplications by literal 0/1 that are value-preserving).
+__device__ __forceinline__ DMat4 trs_matrix(const DTrs &t) {
+    const DVec4 i0 = { 1.0f, 0.0f, 0.0f, 0.0f }, i1 = { 0.0f, 1.0f, 0.0f, 0.0f }, i2 = { 0.0f, 0.0f, 1.0f, 0.0f },
+                i3 = { 0.0f, 0.0f, 0.0f, 1.0f };
+    DMat4 T;   // glm/gtc/matrix_transform.inl:10-16
+    T.c[0] = i0; T.c[1] = i1; T.c[2] = i2;
+    T.c[3] = add4(add4(add4(scale4(i0, t.p.x), scale4(i1, t.p.y)), scale4(i2, t.p.z)), i3);
+    DMat4 R;   // glm/gtc/quaternion.inl:593-624
+    const DQuat &q = t.q;
+    float qxx = mul(q.x, q.x), qyy = mul(q.y, q.y), qzz = mul(q.z, q.z);
+    float qxz = mul(q.x, q.z), qxy = mul(q.x, q.y), qyz = mul(q.y, q.z);
+    float qwx = mul(q.w, q.x), qwy = mul(q.w, q.y), qwz = mul(q.w, q.z);
+    R.c[0] = { sub(1.0f, mul(2.0f, add(qyy, qzz))), mul(2.0f, add(qxy, qwz)), mul(2.0f, sub(qxz, qwy)), 0.0f };
+    R.c[1] = { mul(2.0f, sub(qxy, qwz)), sub(1.0f, mul(2.0f, add(qxx, qzz))), mul(2.0f, add(qyz, qwx)), 0.0f };
+    R.c[2] = { mul(2.0f, add(qxz, qwy)), mul(2.0f, sub(qyz, qwx)), sub(1.0f, mul(2.0f, add(qxx, qyy))), 0.0f };
+    R.c[3] = i3;
+    DMat4 S;   // glm/gtc/matrix_transform.inl:78-87
+    S.c[0] = scale4(i0, t.s.x); S.c[1] = scale4(i1, t.s.y); S.c[2] = scale4(i2, t.s.z); S.c[3] = i3;
+    return mat_mul(mat_mul(T, R), S);
+}
+
+struct DAabb {
+    float mn[3], mx[3];
+};
+
+// BoundingBox::transform, core/src/math/bounding_box.cc:27-40
+__device__ __forceinline__ DAabb transform_aabb(const DAabb &b, const DMat4 &m) {
+    DAabb o;
+    const float col0[3] = { m.c[0].x, m.c[0].y, m.c[0].z }, col1[3] = { m.c[1].x, m.c[1].y, m.c[1].z };
+    const float col2[3] = { m.c[2].x, m.c[2].y, m.c[2].z }, col3[3] = { m.c[3].x, m.c[3].y, m.c[3].z };
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+        float xa = mul(col0[k], b.mn[0]), xb = mul(col0[k], b.mx[0]);
+        float ya = mul(col1[k], b.mn[1]), yb = mul(col1[k], b.mx[1]);
+        float za = mul(col2[k], b.mn[2]), zb = mul(col2[k], b.mx[2]);
+        o.mn[k] = add(add(add(glm_min(xa, xb), glm_min(ya, yb)), glm_min(za, zb)), col3[k]);
+        o.mx[k] = add(add(add(glm_max(xa, xb), glm_max(ya, yb)), glm_max(za, zb)), col3[k]);
+    }
+    return o;
+}
+
+// One plane of Math::intersect(Frustum, BoundingBox), core/src/math/intersection.cc:49-53 with
+// BoundingBox::calcPVertex (core/include/math/bounding_box.h:60-71) and Plane::distanceTo (plane.h:70-72).
+// Returns true when the box is OUTSIDE this plane (d < 0; NaN compares false => inside).
+__device__ __forceinline__ bool outside_plane(float nx, float ny, float nz, float d,
+                                              float mnx, float mny, float mnz, float mxx, float mxy, float mxz) {
+    float px = (nx >= 0.0f) ? mxx : mnx;
+    float py = (ny >= 0.0f) ? mxy : mny;
+    float pz = (nz >= 0.0f) ? mxz : mnz;
+    float dist = sub(add(add(mul(nx, px), mul(ny, py)), mul(nz, pz)), d);
+    return dist < 0.0f;
+}
+
+}  // namespace ovis

@@ -1,0 +1,80 @@
+// ovis_kernels.h - launch interface between the host world (ovis_world.cu) and the kernels.
+#pragma once
+
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace ovis {
+
+constexpr uint32_t kNone = 0xffffffffu;
+constexpr int kCullThreads = 256;                       // threads per CTA of the cull kernel
+constexpr int kCullTile = kCullThreads * 4;             // entities per tile (one float4 group per thread)
+
+// SoA storage convention: component k of item i lives at base[k * stride + i]; stride is a multiple of
+// kCullTile so every component array is 4 KiB aligned and float4-loadable.
+
+struct LevelArgs {
+    const uint32_t *list;        // node ids of this level, or nullptr when the level is the range [first, first+count)
+    int64_t first, count;
+    const int32_t *parent;       // per node, -1 = child of the identity root
+    const float *local_trs;      // 10 x nstride
+    float *world_trs;            // 10 x nstride
+    int64_t nstride;
+    const uint32_t *node_entity; // first entity bound to the node, or kNone
+    const float *local_aabb;     // 6 x estride
+    float *world_aabb;           // 6 x estride
+    int64_t estride;
+};
+
+struct CullArgs {
+    float4 planes[6];            // normal xyz, distance
+    const float *bounds;         // world AABBs, 6 x stride
+    int64_t stride;
+    int64_t n;                   // entity slots
+    int num_tiles;
+    const uint32_t *mask;        // 1 bit per slot (alive [& caster]); only read by the MASKED variant
+    uint32_t *out;               // visible slot ids, ascending
+    long long capacity;          // writable entries of out
+    const long long *d_base;     // optional: start offset inside out (CSR chaining), device memory
+    long long *d_next;           // optional: receives base + count
+    uint32_t *d_count;           // optional: receives count
+    uint64_t *status;            // num_tiles tile-status words (scratch)
+    unsigned int *ticket;        // tile ticket (scratch, zero between launches)
+    unsigned int *done;          // CTA exit counter (scratch, zero between launches)
+    uint32_t epoch;              // launch tag, 1 .. 2^30-1, never repeated without clearing status
+    uint32_t id_base;            // added to every emitted slot id (global id of a shard's first entity)
+};
+
+enum : uint32_t { kLightNever = 0, kLightAlways = 1, kLightSphere = 2, kLightBox = 3 };
+
+struct DeviceLight {
+    float4 a;                    // sphere: centre xyz + radius; box: minimum xyz
+    float4 b;                    // box: maximum xyz
+    uint32_t kind;
+    uint32_t pad[3];
+};
+
+struct LightCullArgs {
+    float4 planes[6];
+    const DeviceLight *lights;
+    int n;
+    uint32_t *out;
+    uint32_t *d_count;
+};
+
+void launch_scatter_aos(int k, const float *src, const uint32_t *ids, uint32_t first, int64_t n, float *dst,
+                        int64_t stride, cudaStream_t s);
+void launch_gather_aos(int k, const float *src, int64_t stride, uint32_t first, int64_t n, float *dst, cudaStream_t s);
+void launch_scatter_u32(const uint32_t *src, const uint32_t *ids, int64_t n, uint32_t *dst, cudaStream_t s);
+void launch_fill_u32(uint32_t *dst, int64_t n, uint32_t value, cudaStream_t s);
+void launch_identity_bounds(const uint32_t *ids, uint32_t first, int64_t n, const float *local, float *world,
+                            int64_t stride, cudaStream_t s);
+void launch_update_level(const LevelArgs &a, cudaStream_t s);
+void launch_extra_bounds(const uint32_t *entities, const uint32_t *nodes, int64_t n, const float *world_trs,
+                         int64_t nstride, const float *local, float *world, int64_t estride, cudaStream_t s);
+void launch_cull_frustum(const CullArgs &a, bool masked, int grid, cudaStream_t s);
+int cull_frustum_max_blocks_per_sm(bool masked);
+void launch_empty_result(const long long *d_base, long long *d_next, uint32_t *d_count, cudaStream_t s);
+void launch_cull_lights(const LightCullArgs &a, cudaStream_t s);
+
+}  // namespace ovis

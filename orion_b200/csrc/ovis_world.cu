@@ -1,0 +1,1103 @@
+// ovis_world.cu - the host side of liborion_vis: device-resident world store and the C ABI of
+// include/orion_vis.h. It mirrors the reference's RenderWorld contract (render/include/render_world.h:40-98):
+// the world keeps borrowed entity/light state in insertion order and answers cull() calls; here the
+// state lives in HBM as SoA arrays and every cull is one kernel launch.
+//
+// There is deliberately no CPU implementation of any stage in this file: if CUDA is unavailable every
+// entry point that needs the device returns OVIS_ERR_CUDA.
+#include "orion_vis.h"
+
+#include <algorithm>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <string>
+#include <vector>
+
+#include <cuda_runtime.h>
+
+#include "ovis_kernels.h"
+#include "ovis_math.hpp"
+
+namespace {
+
+thread_local std::string g_error;
+
+int fail(int code, const char *fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    g_error = buf;
+    return code;
+}
+
+#define OVIS_CUDA(call)                                                                                   \
+    do {                                                                                                  \
+        cudaError_t err__ = (call);                                                                       \
+        if (err__ != cudaSuccess)                                                                         \
+            return fail(OVIS_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(err__), __FILE__, __LINE__); \
+    } while (0)
+
+#define OVIS_TRY(call)                 \
+    do {                               \
+        int rc__ = (call);             \
+        if (rc__ != OVIS_OK)           \
+            return rc__;               \
+    } while (0)
+
+inline int64_t round_up(int64_t v, int64_t m) { return (v + m - 1) / m * m; }
+
+struct Level {
+    int64_t count = 0;
+    int64_t first = 0;          // smallest node id of the level
+    bool contiguous = true;     // ids are exactly [first, first + count)
+    int64_t list_offset = 0;    // into d_level_lists when not contiguous
+};
+
+}  // namespace
+
+struct OvisWorld {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    int num_sms = 0;
+    int blocks_per_sm[2] = { 0, 0 };      // cull kernel occupancy: [unmasked, masked]
+    int64_t launches = 0;
+    uint32_t id_base = 0;                 // global id of slot 0 (sharded worlds)
+
+    // ---- entities (slot == id; slots are never reused, so slot order is insertion order)
+    int64_t n_ent = 0, cap_ent = 0, n_live = 0;
+    float *d_local = nullptr;             // 6 x cap_ent
+    float *d_world = nullptr;             // 6 x cap_ent
+    uint32_t *d_alive_bits = nullptr;     // cap_ent / 32 words: slot holds a live entity
+    uint32_t *d_caster_bits = nullptr;    // alive & castsShadow
+    std::vector<uint32_t> h_alive, h_caster_raw;   // host mirrors of the bit masks (caster before masking by alive)
+    std::vector<uint32_t> h_entity_node;  // node the entity follows, or kNone
+    bool masks_dirty = false;
+    bool any_dead = false;
+
+    // ---- transform tree
+    int64_t n_nodes = 0, cap_nodes = 0;
+    int32_t *d_parent = nullptr;
+    float *d_local_trs = nullptr;         // 10 x cap_nodes
+    float *d_world_trs = nullptr;         // 10 x cap_nodes
+    uint32_t *d_node_entity = nullptr;
+    std::vector<int32_t> h_parent, h_level;
+    std::vector<uint32_t> h_node_entity;
+    std::vector<uint32_t> h_extra_entity, h_extra_node;   // 2nd.. entity on a node
+    uint32_t *d_extra_entity = nullptr, *d_extra_node = nullptr;
+    int64_t cap_extra = 0;
+    bool extra_dirty = false;
+    std::vector<Level> levels;
+    uint32_t *d_level_lists = nullptr;
+    int64_t cap_level_lists = 0;
+    bool levels_dirty = false;
+    bool transforms_dirty = false;
+
+    // ---- lights
+    std::vector<OvisLight> lights;
+    std::vector<uint8_t> light_alive;
+    ovis::DeviceLight *d_lights = nullptr;
+    uint32_t *d_light_out = nullptr;
+    int64_t cap_lights = 0;
+    bool lights_dirty = false;
+
+    // ---- cull scratch and results
+    uint64_t *d_status = nullptr;         // one word per tile
+    int64_t cap_tiles = 0;
+    unsigned int *d_ticket = nullptr;     // [0] ticket, [1] done
+    uint32_t epoch = 0;
+    uint32_t *d_result = nullptr;         // cap_ent visible ids
+    uint32_t *d_counts = nullptr;         // [0] entities, [1] lights
+    uint32_t *h_counts = nullptr;         // pinned mirror
+    uint32_t *d_csr_entities = nullptr;
+    int64_t cap_csr = 0;
+    long long *d_csr_offsets = nullptr;
+    int64_t cap_csr_views = 0;
+
+    // ---- upload staging
+    void *d_stage[2] = { nullptr, nullptr };
+    size_t stage_bytes[2] = { 0, 0 };
+};
+
+namespace {
+
+using ovis::kCullTile;
+using ovis::kNone;
+
+constexpr int64_t kUploadChunk = 1 << 23;   // items per staged upload
+
+int use_device(OvisWorld *w) {
+    OVIS_CUDA(cudaSetDevice(w->device));
+    return OVIS_OK;
+}
+
+template <typename T>
+int grow(T *&ptr, int64_t old_items, int64_t new_items, cudaStream_t s, bool zero_new = true) {
+    T *fresh = nullptr;
+    OVIS_CUDA(cudaMalloc(&fresh, sizeof(T) * (size_t)new_items));
+    if (zero_new)
+        OVIS_CUDA(cudaMemsetAsync(fresh, 0, sizeof(T) * (size_t)new_items, s));
+    if (ptr && old_items > 0)
+        OVIS_CUDA(cudaMemcpyAsync(fresh, ptr, sizeof(T) * (size_t)old_items, cudaMemcpyDeviceToDevice, s));
+    if (ptr) {
+        OVIS_CUDA(cudaStreamSynchronize(s));
+        OVIS_CUDA(cudaFree(ptr));
+    }
+    ptr = fresh;
+    return OVIS_OK;
+}
+
+// SoA block of `comps` component arrays: copy each component to its new stride.
+int grow_soa(float *&ptr, int comps, int64_t old_cap, int64_t new_cap, int64_t used, cudaStream_t s) {
+    float *fresh = nullptr;
+    OVIS_CUDA(cudaMalloc(&fresh, sizeof(float) * (size_t)(comps * new_cap)));
+    OVIS_CUDA(cudaMemsetAsync(fresh, 0, sizeof(float) * (size_t)(comps * new_cap), s));
+    if (ptr && used > 0)
+        for (int k = 0; k < comps; k++)
+            OVIS_CUDA(cudaMemcpyAsync(fresh + k * new_cap, ptr + k * old_cap, sizeof(float) * (size_t)used,
+                                      cudaMemcpyDeviceToDevice, s));
+    if (ptr) {
+        OVIS_CUDA(cudaStreamSynchronize(s));
+        OVIS_CUDA(cudaFree(ptr));
+    }
+    ptr = fresh;
+    return OVIS_OK;
+}
+
+int stage(OvisWorld *w, int which, const void *host, size_t bytes, void **out) {
+    if (w->stage_bytes[which] < bytes) {
+        if (w->d_stage[which]) {
+            OVIS_CUDA(cudaStreamSynchronize(w->stream));
+            OVIS_CUDA(cudaFree(w->d_stage[which]));
+            w->d_stage[which] = nullptr;
+            w->stage_bytes[which] = 0;
+        }
+        size_t want = std::max(bytes, (size_t)1 << 20);
+        OVIS_CUDA(cudaMalloc(&w->d_stage[which], want));
+        w->stage_bytes[which] = want;
+    }
+    OVIS_CUDA(cudaMemcpyAsync(w->d_stage[which], host, bytes, cudaMemcpyHostToDevice, w->stream));
+    *out = w->d_stage[which];
+    return OVIS_OK;
+}
+
+int reserve_entities(OvisWorld *w, int64_t want) {
+    if (want <= w->cap_ent)
+        return OVIS_OK;
+    int64_t cap = round_up(std::max<int64_t>(want, w->cap_ent + w->cap_ent / 2), kCullTile);
+    OVIS_TRY(grow_soa(w->d_local, 6, w->cap_ent, cap, w->n_ent, w->stream));
+    OVIS_TRY(grow_soa(w->d_world, 6, w->cap_ent, cap, w->n_ent, w->stream));
+    OVIS_TRY(grow(w->d_alive_bits, w->cap_ent / 32, cap / 32, w->stream));
+    OVIS_TRY(grow(w->d_caster_bits, w->cap_ent / 32, cap / 32, w->stream));
+    OVIS_TRY(grow(w->d_result, 0, cap, w->stream, false));
+    int64_t tiles = cap / kCullTile;
+    if (tiles > w->cap_tiles) {
+        OVIS_TRY(grow(w->d_status, 0, tiles, w->stream));   // zeroed: epoch 0 is never used by a launch
+        w->cap_tiles = tiles;
+        w->epoch = 0;
+    }
+    w->cap_ent = cap;
+    w->h_alive.resize((size_t)(cap / 32), 0u);
+    w->h_caster_raw.resize((size_t)(cap / 32), 0u);
+    return OVIS_OK;
+}
+
+int reserve_nodes(OvisWorld *w, int64_t want) {
+    if (want <= w->cap_nodes)
+        return OVIS_OK;
+    int64_t cap = round_up(std::max<int64_t>(want, w->cap_nodes + w->cap_nodes / 2), kCullTile);
+    OVIS_TRY(grow_soa(w->d_local_trs, 10, w->cap_nodes, cap, w->n_nodes, w->stream));
+    OVIS_TRY(grow_soa(w->d_world_trs, 10, w->cap_nodes, cap, w->n_nodes, w->stream));
+    OVIS_TRY(grow(w->d_parent, w->n_nodes, cap, w->stream));
+    OVIS_TRY(grow(w->d_node_entity, w->n_nodes, cap, w->stream));
+    w->cap_nodes = cap;
+    return OVIS_OK;
+}
+
+int upload_masks(OvisWorld *w) {
+    if (!w->masks_dirty)
+        return OVIS_OK;
+    size_t words = (size_t)(round_up(w->n_ent, 32) / 32);
+    if (words) {
+        std::vector<uint32_t> caster(words);
+        for (size_t i = 0; i < words; i++)
+            caster[i] = w->h_caster_raw[i] & w->h_alive[i];
+        OVIS_CUDA(cudaMemcpyAsync(w->d_alive_bits, w->h_alive.data(), words * 4, cudaMemcpyHostToDevice, w->stream));
+        OVIS_CUDA(cudaMemcpyAsync(w->d_caster_bits, caster.data(), words * 4, cudaMemcpyHostToDevice, w->stream));
+        OVIS_CUDA(cudaStreamSynchronize(w->stream));   // `caster` is a local
+    }
+    w->masks_dirty = false;
+    return OVIS_OK;
+}
+
+int check_entity_ids(OvisWorld *w, int64_t n, const uint32_t *ids, bool need_alive = true) {
+    if (n < 0 || (n > 0 && !ids))
+        return fail(OVIS_ERR_INVALID, "null id array");
+    for (int64_t i = 0; i < n; i++) {
+        uint32_t id = ids[i];
+        if ((int64_t)id >= w->n_ent || (need_alive && !((w->h_alive[id >> 5] >> (id & 31)) & 1u)))
+            return fail(OVIS_ERR_INVALID, "entity id %u does not name a live entity", id);
+    }
+    return OVIS_OK;
+}
+
+int add_nodes(OvisWorld *w, int64_t n, const int32_t *parent, const float *local_trs, uint32_t *out_first) {
+    if (n < 0 || (n > 0 && (!parent || !local_trs)))
+        return fail(OVIS_ERR_INVALID, "ovis_node_add: null input");
+    int64_t first = w->n_nodes;
+    if (first + n > (int64_t)0x7fffffff)
+        return fail(OVIS_ERR_INVALID, "too many nodes");
+    for (int64_t i = 0; i < n; i++)
+        if (parent[i] != OVIS_NO_PARENT && (parent[i] < 0 || (int64_t)parent[i] >= first + i))
+            return fail(OVIS_ERR_INVALID, "node %lld: parent %d is not an earlier node", (long long)(first + i), parent[i]);
+    OVIS_TRY(reserve_nodes(w, first + n));
+    w->h_parent.resize((size_t)(first + n));
+    w->h_level.resize((size_t)(first + n));
+    w->h_node_entity.resize((size_t)(first + n), kNone);
+    for (int64_t i = 0; i < n; i++) {
+        int32_t p = parent[i];
+        w->h_parent[(size_t)(first + i)] = p;
+        w->h_level[(size_t)(first + i)] = p < 0 ? 0 : w->h_level[(size_t)p] + 1;
+    }
+    for (int64_t s = 0; s < n; s += kUploadChunk) {
+        int64_t c = std::min(kUploadChunk, n - s);
+        void *d = nullptr;
+        OVIS_TRY(stage(w, 0, local_trs + 10 * s, sizeof(float) * 10 * (size_t)c, &d));
+        ovis::launch_scatter_aos(10, (const float *)d, nullptr, (uint32_t)(first + s), c, w->d_local_trs, w->cap_nodes, w->stream);
+        w->launches++;
+    }
+    OVIS_CUDA(cudaMemcpyAsync(w->d_parent + first, parent, sizeof(int32_t) * (size_t)n, cudaMemcpyHostToDevice, w->stream));
+    ovis::launch_fill_u32(w->d_node_entity + first, n, kNone, w->stream);
+    w->launches++;
+    OVIS_CUDA(cudaGetLastError());
+    w->n_nodes = first + n;
+    w->levels_dirty = true;
+    w->transforms_dirty = true;
+    if (out_first)
+        *out_first = (uint32_t)first;
+    return OVIS_OK;
+}
+
+int rebuild_levels(OvisWorld *w) {
+    if (!w->levels_dirty)
+        return OVIS_OK;
+    int32_t depth = 0;
+    for (int64_t i = 0; i < w->n_nodes; i++)
+        depth = std::max(depth, w->h_level[(size_t)i] + 1);
+    w->levels.assign((size_t)depth, Level());
+    std::vector<int64_t> last((size_t)depth, -1);
+    for (int64_t i = 0; i < w->n_nodes; i++) {
+        Level &l = w->levels[(size_t)w->h_level[(size_t)i]];
+        if (l.count == 0)
+            l.first = i;
+        l.count++;
+        last[(size_t)w->h_level[(size_t)i]] = i;
+    }
+    int64_t list_items = 0;
+    for (int32_t d = 0; d < depth; d++) {
+        Level &l = w->levels[(size_t)d];
+        l.contiguous = (last[(size_t)d] - l.first + 1 == l.count);
+        if (!l.contiguous) {
+            l.list_offset = list_items;
+            list_items += l.count;
+        }
+    }
+    if (list_items > 0) {
+        std::vector<uint32_t> lists((size_t)list_items);
+        std::vector<int64_t> cursor((size_t)depth);
+        for (int32_t d = 0; d < depth; d++)
+            cursor[(size_t)d] = w->levels[(size_t)d].list_offset;
+        for (int64_t i = 0; i < w->n_nodes; i++) {
+            int32_t d = w->h_level[(size_t)i];
+            if (!w->levels[(size_t)d].contiguous)
+                lists[(size_t)cursor[(size_t)d]++] = (uint32_t)i;
+        }
+        if (list_items > w->cap_level_lists) {
+            OVIS_TRY(grow(w->d_level_lists, 0, list_items, w->stream, false));
+            w->cap_level_lists = list_items;
+        }
+        OVIS_CUDA(cudaMemcpyAsync(w->d_level_lists, lists.data(), sizeof(uint32_t) * (size_t)list_items,
+                                  cudaMemcpyHostToDevice, w->stream));
+        OVIS_CUDA(cudaStreamSynchronize(w->stream));
+    }
+    w->levels_dirty = false;
+    return OVIS_OK;
+}
+
+int flush_transforms(OvisWorld *w) {
+    if (!w->transforms_dirty)
+        return OVIS_OK;
+    OVIS_TRY(rebuild_levels(w));
+    if (w->extra_dirty) {
+        int64_t n = (int64_t)w->h_extra_entity.size();
+        if (n > w->cap_extra) {
+            OVIS_TRY(grow(w->d_extra_entity, 0, n, w->stream, false));
+            OVIS_TRY(grow(w->d_extra_node, 0, n, w->stream, false));
+            w->cap_extra = n;
+        }
+        if (n > 0) {
+            OVIS_CUDA(cudaMemcpyAsync(w->d_extra_entity, w->h_extra_entity.data(), 4 * (size_t)n, cudaMemcpyHostToDevice, w->stream));
+            OVIS_CUDA(cudaMemcpyAsync(w->d_extra_node, w->h_extra_node.data(), 4 * (size_t)n, cudaMemcpyHostToDevice, w->stream));
+        }
+        w->extra_dirty = false;
+    }
+    for (const Level &l : w->levels) {
+        ovis::LevelArgs a;
+        a.list = l.contiguous ? nullptr : w->d_level_lists + l.list_offset;
+        a.first = l.first;
+        a.count = l.count;
+        a.parent = w->d_parent;
+        a.local_trs = w->d_local_trs;
+        a.world_trs = w->d_world_trs;
+        a.nstride = w->cap_nodes;
+        a.node_entity = w->d_node_entity;
+        a.local_aabb = w->d_local;
+        a.world_aabb = w->d_world;
+        a.estride = w->cap_ent;
+        ovis::launch_update_level(a, w->stream);
+        w->launches++;
+    }
+    if (!w->h_extra_entity.empty()) {
+        ovis::launch_extra_bounds(w->d_extra_entity, w->d_extra_node, (int64_t)w->h_extra_entity.size(), w->d_world_trs,
+                                  w->cap_nodes, w->d_local, w->d_world, w->cap_ent, w->stream);
+        w->launches++;
+    }
+    OVIS_CUDA(cudaGetLastError());
+    w->transforms_dirty = false;
+    return OVIS_OK;
+}
+
+int bind_entities(OvisWorld *w, int64_t n, const uint32_t *nodes, const uint32_t *entities) {
+    std::vector<uint32_t> first_nodes, first_entities;
+    for (int64_t i = 0; i < n; i++) {
+        uint32_t node = nodes[i], ent = entities[i];
+        if (w->h_entity_node[ent] != kNone)
+            return fail(OVIS_ERR_INVALID, "entity %u is already bound to node %u", ent, w->h_entity_node[ent]);
+        w->h_entity_node[ent] = node;
+        if (w->h_node_entity[node] == kNone) {
+            w->h_node_entity[node] = ent;
+            first_nodes.push_back(node);
+            first_entities.push_back(ent);
+        } else {
+            w->h_extra_entity.push_back(ent);
+            w->h_extra_node.push_back(node);
+            w->extra_dirty = true;
+        }
+    }
+    for (size_t s = 0; s < first_nodes.size(); s += (size_t)kUploadChunk) {
+        size_t c = std::min((size_t)kUploadChunk, first_nodes.size() - s);
+        void *dn = nullptr, *de = nullptr;
+        OVIS_TRY(stage(w, 0, first_entities.data() + s, 4 * c, &de));
+        OVIS_TRY(stage(w, 1, first_nodes.data() + s, 4 * c, &dn));
+        ovis::launch_scatter_u32((const uint32_t *)de, (const uint32_t *)dn, (int64_t)c, w->d_node_entity, w->stream);
+        w->launches++;
+        OVIS_CUDA(cudaStreamSynchronize(w->stream));   // vectors are locals
+    }
+    w->transforms_dirty = true;
+    return OVIS_OK;
+}
+
+void load_planes(float4 dst[6], const float planes[24]) {
+    for (int i = 0; i < 6; i++)
+        dst[i] = make_float4(planes[4 * i], planes[4 * i + 1], planes[4 * i + 2], planes[4 * i + 3]);
+}
+
+// Enqueue one entity cull (K3). Output goes to `out` (device) starting at *d_base (or 0).
+int enqueue_cull(OvisWorld *w, const float planes[24], uint32_t require, uint32_t *out, long long capacity,
+                 const long long *d_base, long long *d_next, uint32_t *d_count) {
+    if (require & ~(uint32_t)OVIS_CASTS_SHADOW)
+        return fail(OVIS_ERR_INVALID, "require mask 0x%x: only 0 or OVIS_CASTS_SHADOW is supported", require);
+    if (w->n_ent == 0) {
+        ovis::launch_empty_result(d_base, d_next, d_count, w->stream);
+        w->launches++;
+        return OVIS_OK;
+    }
+    OVIS_TRY(upload_masks(w));
+    if (++w->epoch >= (1u << 30)) {                     // tag space exhausted: clear and restart
+        OVIS_CUDA(cudaMemsetAsync(w->d_status, 0, sizeof(uint64_t) * (size_t)w->cap_tiles, w->stream));
+        w->epoch = 1;
+    }
+    ovis::CullArgs a;
+    load_planes(a.planes, planes);
+    a.bounds = w->d_world;
+    a.stride = w->cap_ent;
+    a.n = w->n_ent;
+    a.num_tiles = (int)((w->n_ent + kCullTile - 1) / kCullTile);
+    const bool masked = require != 0 || w->any_dead;
+    a.mask = require ? w->d_caster_bits : w->d_alive_bits;
+    a.out = out;
+    a.capacity = capacity;
+    a.d_base = d_base;
+    a.d_next = d_next;
+    a.d_count = d_count;
+    a.status = w->d_status;
+    a.ticket = w->d_ticket;
+    a.done = w->d_ticket + 1;
+    a.epoch = w->epoch;
+    a.id_base = w->id_base;
+    int grid = std::min(a.num_tiles, w->num_sms * w->blocks_per_sm[masked ? 1 : 0]);
+    ovis::launch_cull_frustum(a, masked, grid, w->stream);
+    w->launches++;
+    OVIS_CUDA(cudaGetLastError());
+    return OVIS_OK;
+}
+
+int upload_lights(OvisWorld *w) {
+    if (!w->lights_dirty)
+        return OVIS_OK;
+    int64_t n = (int64_t)w->lights.size();
+    if (n > w->cap_lights) {
+        int64_t cap = std::max<int64_t>(n, 64);
+        OVIS_TRY(grow(w->d_lights, 0, cap, w->stream, false));
+        OVIS_TRY(grow(w->d_light_out, 0, cap, w->stream, false));
+        w->cap_lights = cap;
+    }
+    std::vector<ovis::DeviceLight> dl((size_t)n);
+    for (int64_t i = 0; i < n; i++) {
+        const OvisLight &l = w->lights[(size_t)i];
+        ovis::DeviceLight &d = dl[(size_t)i];
+        std::memset(&d, 0, sizeof d);
+        if (!w->light_alive[(size_t)i] || ovis::hm::lightHasNoEffect(l)) {          // render_light.cc:189-190
+            d.kind = ovis::kLightNever;
+        } else if (l.type == OVIS_LIGHT_AMBIENT || l.type == OVIS_LIGHT_DIRECTIONAL) {
+            d.kind = ovis::kLightAlways;
+        } else if (l.type == OVIS_LIGHT_POINT) {
+            d.kind = ovis::kLightSphere;
+            d.a = make_float4(l.position[0], l.position[1], l.position[2], l.range);
+        } else if (l.type == OVIS_LIGHT_SPOT) {
+            float box[6];
+            ovis::hm::spotAabb(l, box);
+            d.kind = ovis::kLightBox;
+            d.a = make_float4(box[0], box[1], box[2], 0.0f);
+            d.b = make_float4(box[3], box[4], box[5], 0.0f);
+        } else {
+            d.kind = ovis::kLightNever;                                              // render_light.cc:206-207
+        }
+    }
+    if (n > 0) {
+        OVIS_CUDA(cudaMemcpyAsync(w->d_lights, dl.data(), sizeof(ovis::DeviceLight) * (size_t)n, cudaMemcpyHostToDevice, w->stream));
+        OVIS_CUDA(cudaStreamSynchronize(w->stream));
+    }
+    w->lights_dirty = false;
+    return OVIS_OK;
+}
+
+int enqueue_light_cull(OvisWorld *w, const float planes[24]) {
+    OVIS_TRY(upload_lights(w));
+    ovis::LightCullArgs a;
+    load_planes(a.planes, planes);
+    a.lights = w->d_lights;
+    a.n = (int)w->lights.size();
+    a.out = w->d_light_out;
+    a.d_count = w->d_counts + 1;
+    ovis::launch_cull_lights(a, w->stream);
+    w->launches++;
+    OVIS_CUDA(cudaGetLastError());
+    return OVIS_OK;
+}
+
+int cull_views_device(OvisWorld *w, int32_t n_views, const float *planes, const uint32_t *require, int64_t *host_offsets_out,
+                      std::vector<long long> &host_offsets) {
+    OVIS_TRY(flush_transforms(w));
+    if (n_views + 1 > w->cap_csr_views) {
+        int64_t cap = std::max<int64_t>(n_views + 1, 64);
+        OVIS_TRY(grow(w->d_csr_offsets, 0, cap, w->stream, false));
+        w->cap_csr_views = cap;
+    }
+    if (w->cap_csr == 0) {
+        int64_t cap = std::max<int64_t>(w->cap_ent, 1 << 20);
+        OVIS_TRY(grow(w->d_csr_entities, 0, cap, w->stream, false));
+        w->cap_csr = cap;
+    }
+    host_offsets.assign((size_t)n_views + 1, 0);
+    for (int attempt = 0; attempt < 2; attempt++) {
+        OVIS_CUDA(cudaMemsetAsync(w->d_csr_offsets, 0, sizeof(long long), w->stream));
+        for (int32_t v = 0; v < n_views; v++)
+            OVIS_TRY(enqueue_cull(w, planes + 24 * (size_t)v, require ? require[v] : 0u, w->d_csr_entities, w->cap_csr,
+                                  w->d_csr_offsets + v, w->d_csr_offsets + v + 1, nullptr));
+        OVIS_CUDA(cudaMemcpyAsync(host_offsets.data(), w->d_csr_offsets, sizeof(long long) * ((size_t)n_views + 1),
+                                  cudaMemcpyDeviceToHost, w->stream));
+        OVIS_CUDA(cudaStreamSynchronize(w->stream));
+        if (host_offsets[(size_t)n_views] <= w->cap_csr)
+            break;
+        if (attempt == 1)
+            return fail(OVIS_ERR_NOMEM, "multi-view result did not fit after regrowing");
+        int64_t cap = round_up(host_offsets[(size_t)n_views], 1 << 20);   // counts are exact even when writes were clipped
+        OVIS_TRY(grow(w->d_csr_entities, 0, cap, w->stream, false));
+        w->cap_csr = cap;
+    }
+    if (host_offsets_out)
+        for (int32_t v = 0; v <= n_views; v++)
+            host_offsets_out[v] = host_offsets[(size_t)v];
+    return OVIS_OK;
+}
+
+}  // namespace
+
+// ================================================================================================
+// C ABI
+// ================================================================================================
+
+extern "C" {
+
+const char *ovis_last_error(void) { return g_error.c_str(); }
+
+const char *ovis_version(void) { return "orion_vis 0.1 sm_100a fmad=off"; }
+
+int ovis_world_create(int device, OvisWorld **out_world) {
+    if (!out_world)
+        return fail(OVIS_ERR_INVALID, "out_world is null");
+    *out_world = nullptr;
+    int count = 0;
+    cudaError_t err = cudaGetDeviceCount(&count);
+    if (err != cudaSuccess || count == 0)
+        return fail(OVIS_ERR_CUDA, "no CUDA device available (%s); liborion_vis has no CPU path",
+                    err == cudaSuccess ? "device count is 0" : cudaGetErrorString(err));
+    if (device < 0 || device >= count)
+        return fail(OVIS_ERR_INVALID, "device %d out of range (0..%d)", device, count - 1);
+    OVIS_CUDA(cudaSetDevice(device));
+    OvisWorld *w = new (std::nothrow) OvisWorld;
+    if (!w)
+        return fail(OVIS_ERR_NOMEM, "out of host memory");
+    w->device = device;
+    cudaDeviceProp prop;
+    OVIS_CUDA(cudaGetDeviceProperties(&prop, device));
+    w->num_sms = prop.multiProcessorCount;
+    w->blocks_per_sm[0] = std::max(1, ovis::cull_frustum_max_blocks_per_sm(false));
+    w->blocks_per_sm[1] = std::max(1, ovis::cull_frustum_max_blocks_per_sm(true));
+    OVIS_CUDA(cudaMalloc(&w->d_ticket, 2 * sizeof(unsigned int)));
+    OVIS_CUDA(cudaMemset(w->d_ticket, 0, 2 * sizeof(unsigned int)));
+    OVIS_CUDA(cudaMalloc(&w->d_counts, 2 * sizeof(uint32_t)));
+    OVIS_CUDA(cudaMemset(w->d_counts, 0, 2 * sizeof(uint32_t)));
+    OVIS_CUDA(cudaMallocHost(&w->h_counts, 2 * sizeof(uint32_t)));
+    *out_world = w;
+    return OVIS_OK;
+}
+
+int ovis_world_destroy(OvisWorld *w) {
+    if (!w)
+        return OVIS_OK;
+    cudaSetDevice(w->device);
+    cudaStreamSynchronize(w->stream);
+    void *bufs[] = { w->d_local, w->d_world, w->d_alive_bits, w->d_caster_bits, w->d_parent, w->d_local_trs, w->d_world_trs,
+                     w->d_node_entity, w->d_extra_entity, w->d_extra_node, w->d_level_lists, w->d_lights, w->d_light_out,
+                     w->d_status, w->d_ticket, w->d_result, w->d_counts, w->d_csr_entities, w->d_csr_offsets,
+                     w->d_stage[0], w->d_stage[1] };
+    for (void *b : bufs)
+        if (b)
+            cudaFree(b);
+    if (w->h_counts)
+        cudaFreeHost(w->h_counts);
+    delete w;
+    return OVIS_OK;
+}
+
+int ovis_world_reserve(OvisWorld *w, int64_t n_entities, int64_t n_nodes) {
+    if (!w)
+        return fail(OVIS_ERR_INVALID, "world is null");
+    OVIS_TRY(use_device(w));
+    if (n_entities > 0)
+        OVIS_TRY(reserve_entities(w, n_entities));
+    if (n_nodes > 0)
+        OVIS_TRY(reserve_nodes(w, n_nodes));
+    return OVIS_OK;
+}
+
+int ovis_world_set_stream(OvisWorld *w, void *cuda_stream) {
+    if (!w)
+        return fail(OVIS_ERR_INVALID, "world is null");
+    OVIS_TRY(use_device(w));
+    OVIS_CUDA(cudaStreamSynchronize(w->stream));
+    w->stream = (cudaStream_t)cuda_stream;
+    return OVIS_OK;
+}
+
+int ovis_world_set_id_base(OvisWorld *w, uint32_t id_base) {
+    if (!w)
+        return fail(OVIS_ERR_INVALID, "world is null");
+    w->id_base = id_base;
+    return OVIS_OK;
+}
+
+int ovis_world_counts(OvisWorld *w, int64_t *n_entities, int64_t *n_nodes, int32_t *n_lights) {
+    if (!w)
+        return fail(OVIS_ERR_INVALID, "world is null");
+    if (n_entities) *n_entities = w->n_ent;
+    if (n_nodes) *n_nodes = w->n_nodes;
+    if (n_lights) *n_lights = (int32_t)w->lights.size();
+    return OVIS_OK;
+}
+
+int ovis_world_launch_count(OvisWorld *w, int64_t *out_launches) {
+    if (!w || !out_launches)
+        return fail(OVIS_ERR_INVALID, "null argument");
+    *out_launches = w->launches;
+    return OVIS_OK;
+}
+
+// ---- entities ----------------------------------------------------------------------------------
+
+int ovis_entity_add(OvisWorld *w, int64_t n, const float *local_aabb, const uint32_t *flags, uint32_t *out_first_id) {
+    if (!w || n < 0)
+        return fail(OVIS_ERR_INVALID, "ovis_entity_add: bad arguments");
+    OVIS_TRY(use_device(w));
+    int64_t first = w->n_ent;
+    if (first + n > (int64_t)0xfffffffe)
+        return fail(OVIS_ERR_INVALID, "too many entities");
+    OVIS_TRY(reserve_entities(w, first + n));
+    for (int64_t s = 0; s < n && local_aabb; s += kUploadChunk) {
+        int64_t c = std::min(kUploadChunk, n - s);
+        void *d = nullptr;
+        OVIS_TRY(stage(w, 0, local_aabb + 6 * s, sizeof(float) * 6 * (size_t)c, &d));
+        ovis::launch_scatter_aos(6, (const float *)d, nullptr, (uint32_t)(first + s), c, w->d_local, w->cap_ent, w->stream);
+        w->launches++;
+    }
+    // BoundingBox() is all zeros (bounding_box.h:33-36): the SoA blocks are zero-filled on allocation.
+    ovis::launch_identity_bounds(nullptr, (uint32_t)first, n, w->d_local, w->d_world, w->cap_ent, w->stream);
+    w->launches++;
+    OVIS_CUDA(cudaGetLastError());
+    w->h_entity_node.resize((size_t)(first + n), kNone);
+    for (int64_t i = 0; i < n; i++) {
+        int64_t id = first + i;
+        w->h_alive[(size_t)(id >> 5)] |= 1u << (id & 31);
+        if (flags && (flags[i] & OVIS_CASTS_SHADOW))
+            w->h_caster_raw[(size_t)(id >> 5)] |= 1u << (id & 31);
+    }
+    w->n_ent = first + n;
+    w->n_live += n;
+    w->masks_dirty = true;
+    if (out_first_id)
+        *out_first_id = (uint32_t)first;
+    return OVIS_OK;
+}
+
+int ovis_entity_remove(OvisWorld *w, int64_t n, const uint32_t *ids) {
+    if (!w)
+        return fail(OVIS_ERR_INVALID, "world is null");
+    OVIS_TRY(check_entity_ids(w, n, ids));
+    for (int64_t i = 0; i < n; i++) {
+        uint32_t id = ids[i];
+        if (!((w->h_alive[id >> 5] >> (id & 31)) & 1u))
+            continue;                                   // listed twice
+        w->h_alive[id >> 5] &= ~(1u << (id & 31));
+        w->n_live--;
+    }
+    if (n > 0) {
+        w->any_dead = true;
+        w->masks_dirty = true;
+    }
+    return OVIS_OK;
+}
+
+int ovis_entity_set_local_aabbs(OvisWorld *w, int64_t n, const uint32_t *ids, const float *local_aabb) {
+    if (!w || (n > 0 && !local_aabb))
+        return fail(OVIS_ERR_INVALID, "ovis_entity_set_local_aabbs: null input");
+    OVIS_TRY(use_device(w));
+    OVIS_TRY(check_entity_ids(w, n, ids));
+    for (int64_t s = 0; s < n; s += kUploadChunk) {
+        int64_t c = std::min(kUploadChunk, n - s);
+        void *d = nullptr, *di = nullptr;
+        OVIS_TRY(stage(w, 0, local_aabb + 6 * s, sizeof(float) * 6 * (size_t)c, &d));
+        OVIS_TRY(stage(w, 1, ids + s, sizeof(uint32_t) * (size_t)c, &di));
+        ovis::launch_scatter_aos(6, (const float *)d, (const uint32_t *)di, 0, c, w->d_local, w->cap_ent, w->stream);
+        // entities that follow no node keep the identity transform: refresh them here; the rest are
+        // refreshed by the transform pass below
+        ovis::launch_identity_bounds((const uint32_t *)di, 0, c, w->d_local, w->d_world, w->cap_ent, w->stream);
+        w->launches += 2;
+    }
+    OVIS_CUDA(cudaGetLastError());
+    for (int64_t i = 0; i < n; i++)
+        if (w->h_entity_node[ids[i]] != kNone)
+            w->transforms_dirty = true;
+    return OVIS_OK;
+}
+
+int ovis_entity_set_flags(OvisWorld *w, int64_t n, const uint32_t *ids, const uint32_t *flags) {
+    if (!w || (n > 0 && !flags))
+        return fail(OVIS_ERR_INVALID, "ovis_entity_set_flags: null input");
+    OVIS_TRY(check_entity_ids(w, n, ids));
+    for (int64_t i = 0; i < n; i++) {
+        uint32_t id = ids[i], bit = 1u << (id & 31);
+        if (flags[i] & OVIS_CASTS_SHADOW)
+            w->h_caster_raw[id >> 5] |= bit;
+        else
+            w->h_caster_raw[id >> 5] &= ~bit;
+    }
+    if (n > 0)
+        w->masks_dirty = true;
+    return OVIS_OK;
+}
+
+int ovis_entity_set_transforms(OvisWorld *w, int64_t n, const uint32_t *ids, const float *world_trs) {
+    if (!w || (n > 0 && !world_trs))
+        return fail(OVIS_ERR_INVALID, "ovis_entity_set_transforms: null input");
+    OVIS_TRY(use_device(w));
+    OVIS_TRY(check_entity_ids(w, n, ids));
+    // An entity driven directly (RenderEntity::setTransform) follows a private root-level node whose
+    // local TRS is the given world TRS; the same kernels then serve both ways of moving an entity.
+    std::vector<uint32_t> fresh_entities, node_ids((size_t)n);
+    std::vector<float> fresh_trs;
+    for (int64_t i = 0; i < n; i++) {
+        uint32_t node = w->h_entity_node[ids[i]];
+        if (node == kNone) {
+            bool dup = false;                           // same id twice in one call: the last TRS wins
+            for (size_t k = 0; k < fresh_entities.size() && !dup; k++)
+                dup = fresh_entities[k] == ids[i];
+            if (!dup)
+                fresh_entities.push_back(ids[i]);
+        } else if (w->h_parent[node] != OVIS_NO_PARENT || w->h_node_entity[node] != ids[i]) {
+            return fail(OVIS_ERR_INVALID, "entity %u follows tree node %u; move the node instead", ids[i], node);
+        }
+    }
+    if (!fresh_entities.empty()) {
+        size_t m = fresh_entities.size();
+        std::vector<int32_t> parents(m, OVIS_NO_PARENT);
+        fresh_trs.assign(10 * m, 0.0f);
+        for (size_t k = 0; k < m; k++) {
+            fresh_trs[10 * k + 3] = 1.0f;
+            fresh_trs[10 * k + 7] = fresh_trs[10 * k + 8] = fresh_trs[10 * k + 9] = 1.0f;
+        }
+        uint32_t first_node = 0;
+        OVIS_TRY(add_nodes(w, (int64_t)m, parents.data(), fresh_trs.data(), &first_node));
+        OVIS_CUDA(cudaStreamSynchronize(w->stream));
+        std::vector<uint32_t> nodes(m);
+        for (size_t k = 0; k < m; k++)
+            nodes[k] = first_node + (uint32_t)k;
+        OVIS_TRY(bind_entities(w, (int64_t)m, nodes.data(), fresh_entities.data()));
+    }
+    for (int64_t i = 0; i < n; i++)
+        node_ids[(size_t)i] = w->h_entity_node[ids[i]];
+    return ovis_node_set_local_trs(w, n, node_ids.data(), world_trs);
+}
+
+int ovis_entity_set_world_aabbs(OvisWorld *w, uint32_t first_id, int64_t n, const float *world_aabb) {
+    if (!w || n < 0 || (n > 0 && !world_aabb))
+        return fail(OVIS_ERR_INVALID, "ovis_entity_set_world_aabbs: bad arguments");
+    if ((int64_t)first_id + n > w->n_ent)
+        return fail(OVIS_ERR_INVALID, "entity range %u..%lld exceeds %lld entities", first_id, (long long)first_id + n - 1, (long long)w->n_ent);
+    OVIS_TRY(use_device(w));
+    for (int64_t s = 0; s < n; s += kUploadChunk) {
+        int64_t c = std::min(kUploadChunk, n - s);
+        void *d = nullptr;
+        OVIS_TRY(stage(w, 0, world_aabb + 6 * s, sizeof(float) * 6 * (size_t)c, &d));
+        ovis::launch_scatter_aos(6, (const float *)d, nullptr, (uint32_t)(first_id + s), c, w->d_world, w->cap_ent, w->stream);
+        w->launches++;
+    }
+    OVIS_CUDA(cudaGetLastError());
+    return OVIS_OK;
+}
+
+// ---- transform tree ----------------------------------------------------------------------------
+
+int ovis_node_add(OvisWorld *w, int64_t n, const int32_t *parent, const float *local_trs, uint32_t *out_first_id) {
+    if (!w)
+        return fail(OVIS_ERR_INVALID, "world is null");
+    OVIS_TRY(use_device(w));
+    return add_nodes(w, n, parent, local_trs, out_first_id);
+}
+
+int ovis_node_set_local_trs(OvisWorld *w, int64_t n, const uint32_t *ids, const float *local_trs) {
+    if (!w || n < 0 || (n > 0 && (!ids || !local_trs)))
+        return fail(OVIS_ERR_INVALID, "ovis_node_set_local_trs: null input");
+    OVIS_TRY(use_device(w));
+    for (int64_t i = 0; i < n; i++)
+        if ((int64_t)ids[i] >= w->n_nodes)
+            return fail(OVIS_ERR_INVALID, "node id %u out of range", ids[i]);
+    for (int64_t s = 0; s < n; s += kUploadChunk) {
+        int64_t c = std::min(kUploadChunk, n - s);
+        void *d = nullptr, *di = nullptr;
+        OVIS_TRY(stage(w, 0, local_trs + 10 * s, sizeof(float) * 10 * (size_t)c, &d));
+        OVIS_TRY(stage(w, 1, ids + s, sizeof(uint32_t) * (size_t)c, &di));
+        ovis::launch_scatter_aos(10, (const float *)d, (const uint32_t *)di, 0, c, w->d_local_trs, w->cap_nodes, w->stream);
+        w->launches++;
+    }
+    OVIS_CUDA(cudaGetLastError());
+    if (n > 0)
+        w->transforms_dirty = true;
+    return OVIS_OK;
+}
+
+int ovis_node_bind_entities(OvisWorld *w, int64_t n, const uint32_t *node_ids, const uint32_t *entity_ids) {
+    if (!w || n < 0 || (n > 0 && (!node_ids || !entity_ids)))
+        return fail(OVIS_ERR_INVALID, "ovis_node_bind_entities: null input");
+    OVIS_TRY(use_device(w));
+    OVIS_TRY(check_entity_ids(w, n, entity_ids));
+    for (int64_t i = 0; i < n; i++)
+        if ((int64_t)node_ids[i] >= w->n_nodes)
+            return fail(OVIS_ERR_INVALID, "node id %u out of range", node_ids[i]);
+    return bind_entities(w, n, node_ids, entity_ids);
+}
+
+int ovis_update_transforms(OvisWorld *w) {
+    if (!w)
+        return fail(OVIS_ERR_INVALID, "world is null");
+    OVIS_TRY(use_device(w));
+    return flush_transforms(w);
+}
+
+// ---- lights ------------------------------------------------------------------------------------
+
+int ovis_light_add(OvisWorld *w, int32_t n, const OvisLight *lights, uint32_t *out_first_id) {
+    if (!w || n < 0 || (n > 0 && !lights))
+        return fail(OVIS_ERR_INVALID, "ovis_light_add: bad arguments");
+    if (out_first_id)
+        *out_first_id = (uint32_t)w->lights.size();
+    for (int32_t i = 0; i < n; i++) {
+        if (lights[i].type == OVIS_LIGHT_SPOT && lights[i].cutoff > 45.0f)
+            return fail(OVIS_ERR_INVALID, "spot light cutoff must be <= 45 degrees");   // render_light.cc:104
+        w->lights.push_back(lights[i]);
+        w->light_alive.push_back(1);
+    }
+    w->lights_dirty = true;
+    return OVIS_OK;
+}
+
+int ovis_light_update(OvisWorld *w, uint32_t id, const OvisLight *light) {
+    if (!w || !light || id >= w->lights.size() || !w->light_alive[id])
+        return fail(OVIS_ERR_INVALID, "ovis_light_update: unknown light %u", id);
+    if (light->type == OVIS_LIGHT_SPOT && light->cutoff > 45.0f)
+        return fail(OVIS_ERR_INVALID, "spot light cutoff must be <= 45 degrees");
+    w->lights[id] = *light;
+    w->lights_dirty = true;
+    return OVIS_OK;
+}
+
+int ovis_light_remove(OvisWorld *w, uint32_t id) {
+    if (!w || id >= w->lights.size() || !w->light_alive[id])
+        return fail(OVIS_ERR_INVALID, "ovis_light_remove: unknown light %u", id);
+    w->light_alive[id] = 0;
+    w->lights_dirty = true;
+    return OVIS_OK;
+}
+
+// ---- host-side set-up --------------------------------------------------------------------------
+
+int ovis_view_planes(const OvisView *view, float out_planes[24]) {
+    if (!view || !out_planes)
+        return fail(OVIS_ERR_INVALID, "ovis_view_planes: null argument");
+    ovis::hm::viewPlanes(*view, out_planes);
+    return OVIS_OK;
+}
+
+int ovis_view_matrices(const OvisView *view, float out_mats[64], float out_corners[24]) {
+    if (!view)
+        return fail(OVIS_ERR_INVALID, "ovis_view_matrices: null view");
+    ovis::hm::ViewMatrices m = ovis::hm::viewMatrices(*view);
+    if (out_mats) {
+        std::memcpy(out_mats, &m.view, 64);
+        std::memcpy(out_mats + 16, &m.projection, 64);
+        std::memcpy(out_mats + 32, &m.viewProjection, 64);
+        std::memcpy(out_mats + 48, &m.inverseViewProjection, 64);
+    }
+    if (out_corners)
+        ovis::hm::frustumCorners(m.inverseViewProjection, out_corners);
+    return OVIS_OK;
+}
+
+int ovis_light_spot_aabb(const OvisLight *light, float out_aabb[6]) {
+    if (!light || !out_aabb)
+        return fail(OVIS_ERR_INVALID, "ovis_light_spot_aabb: null argument");
+    ovis::hm::spotAabb(*light, out_aabb);
+    return OVIS_OK;
+}
+
+int ovis_light_shadow_views(const OvisLight *light, int32_t shadow_map_resolution, OvisView out_views[6], int32_t *out_count) {
+    if (!light || !out_views || !out_count || shadow_map_resolution <= 0)
+        return fail(OVIS_ERR_INVALID, "ovis_light_shadow_views: bad argument");
+    *out_count = ovis::hm::shadowViews(*light, shadow_map_resolution, out_views);
+    return OVIS_OK;
+}
+
+// ---- culling -----------------------------------------------------------------------------------
+
+int ovis_cull_planes_device(OvisWorld *w, const float planes[24], uint32_t require, uint32_t *d_out_entities, uint32_t *d_out_count) {
+    if (!w || !planes || !d_out_entities || !d_out_count)
+        return fail(OVIS_ERR_INVALID, "ovis_cull_planes_device: null argument");
+    OVIS_TRY(use_device(w));
+    OVIS_TRY(flush_transforms(w));
+    return enqueue_cull(w, planes, require, d_out_entities, (long long)w->n_ent, nullptr, nullptr, d_out_count);
+}
+
+static int cull_to_host(OvisWorld *w, const float planes[24], uint32_t require, bool with_lights,
+                        uint32_t *out_entities, int64_t cap_entities, int64_t *out_n_entities,
+                        uint32_t *out_lights, int32_t cap_lights, int32_t *out_n_lights) {
+    OVIS_TRY(flush_transforms(w));
+    OVIS_TRY(enqueue_cull(w, planes, require, w->d_result, (long long)w->cap_ent, nullptr, nullptr, w->d_counts));
+    if (with_lights)
+        OVIS_TRY(enqueue_light_cull(w, planes));
+    OVIS_CUDA(cudaMemcpyAsync(w->h_counts, w->d_counts, 2 * sizeof(uint32_t), cudaMemcpyDeviceToHost, w->stream));
+    OVIS_CUDA(cudaStreamSynchronize(w->stream));
+    int64_t ne = w->h_counts[0];
+    int32_t nl = with_lights ? (int32_t)w->h_counts[1] : 0;
+    if (out_n_entities) *out_n_entities = ne;
+    if (out_n_lights) *out_n_lights = nl;
+    if (ne > cap_entities || (ne > 0 && !out_entities))
+        return fail(OVIS_ERR_CAPACITY, "entity result needs %lld entries, buffer holds %lld", (long long)ne, (long long)cap_entities);
+    if (nl > cap_lights || (nl > 0 && !out_lights))
+        return fail(OVIS_ERR_CAPACITY, "light result needs %d entries, buffer holds %d", nl, cap_lights);
+    if (ne > 0)
+        OVIS_CUDA(cudaMemcpyAsync(out_entities, w->d_result, sizeof(uint32_t) * (size_t)ne, cudaMemcpyDeviceToHost, w->stream));
+    if (nl > 0)
+        OVIS_CUDA(cudaMemcpyAsync(out_lights, w->d_light_out, sizeof(uint32_t) * (size_t)nl, cudaMemcpyDeviceToHost, w->stream));
+    OVIS_CUDA(cudaStreamSynchronize(w->stream));
+    return OVIS_OK;
+}
+
+int ovis_cull_planes(OvisWorld *w, const float planes[24], uint32_t require,
+                     uint32_t *out_entities, int64_t cap_entities, int64_t *out_n_entities) {
+    if (!w || !planes)
+        return fail(OVIS_ERR_INVALID, "ovis_cull_planes: null argument");
+    OVIS_TRY(use_device(w));
+    return cull_to_host(w, planes, require, false, out_entities, cap_entities, out_n_entities, nullptr, 0, nullptr);
+}
+
+int ovis_cull(OvisWorld *w, const OvisView *view, uint32_t flags,
+              uint32_t *out_entities, int64_t cap_entities, int64_t *out_n_entities,
+              uint32_t *out_lights, int32_t cap_lights, int32_t *out_n_lights) {
+    if (!w || !view)
+        return fail(OVIS_ERR_INVALID, "ovis_cull: null argument");
+    OVIS_TRY(use_device(w));
+    float planes[24];
+    ovis::hm::viewPlanes(*view, planes);
+    return cull_to_host(w, planes, 0, (flags & OVIS_CULL_LIGHTS) != 0, out_entities, cap_entities, out_n_entities,
+                        out_lights, cap_lights, out_n_lights);
+}
+
+int ovis_cull_views_device(OvisWorld *w, int32_t n_views, const float *planes, const uint32_t *require,
+                           const int64_t **d_offsets, const uint32_t **d_entities, int64_t *host_offsets) {
+    if (!w || n_views < 0 || (n_views > 0 && !planes))
+        return fail(OVIS_ERR_INVALID, "ovis_cull_views_device: bad arguments");
+    OVIS_TRY(use_device(w));
+    std::vector<long long> offsets;
+    OVIS_TRY(cull_views_device(w, n_views, planes, require, host_offsets, offsets));
+    if (d_offsets) *d_offsets = (const int64_t *)w->d_csr_offsets;
+    if (d_entities) *d_entities = w->d_csr_entities;
+    return OVIS_OK;
+}
+
+int ovis_build_shadow_lists(OvisWorld *w, const OvisView *main_view, int32_t shadow_map_resolution,
+                            int32_t cap_lists, int32_t *out_list_light, int32_t *out_list_view,
+                            int64_t *out_offsets, int32_t *out_n_lists,
+                            int64_t cap_entities, uint32_t *out_entities, int64_t *out_n_entities) {
+    if (!w || !main_view || !out_n_lists || !out_n_entities || shadow_map_resolution <= 0)
+        return fail(OVIS_ERR_INVALID, "ovis_build_shadow_lists: bad arguments");
+    OVIS_TRY(use_device(w));
+    OVIS_TRY(flush_transforms(w));
+    // 1. lights visible from the main view, in insertion order (deferred_render_pipeline.cc:147,207)
+    float main_planes[24];
+    ovis::hm::viewPlanes(*main_view, main_planes);
+    OVIS_TRY(enqueue_light_cull(w, main_planes));
+    OVIS_CUDA(cudaMemcpyAsync(w->h_counts + 1, w->d_counts + 1, sizeof(uint32_t), cudaMemcpyDeviceToHost, w->stream));
+    OVIS_CUDA(cudaStreamSynchronize(w->stream));
+    std::vector<uint32_t> visible(w->h_counts[1]);
+    if (!visible.empty()) {
+        OVIS_CUDA(cudaMemcpyAsync(visible.data(), w->d_light_out, 4 * visible.size(), cudaMemcpyDeviceToHost, w->stream));
+        OVIS_CUDA(cudaStreamSynchronize(w->stream));
+    }
+    // 2. their shadow views (render_light.cc:258-332); only spot and point lights reach the cull
+    //    (allocateShadowMap is fatal for the rest, deferred_render_pipeline.cc:291-303)
+    std::vector<float> planes;
+    std::vector<int32_t> list_light, list_view;
+    for (uint32_t id : visible) {
+        const OvisLight &l = w->lights[id];
+        OvisView views[6];
+        int count = ovis::hm::shadowViews(l, shadow_map_resolution, views);
+        for (int i = 0; i < count; i++) {
+            planes.resize(planes.size() + 24);
+            ovis::hm::viewPlanes(views[i], planes.data() + planes.size() - 24);
+            list_light.push_back((int32_t)id);
+            list_view.push_back(i);
+        }
+    }
+    int32_t n_lists = (int32_t)list_light.size();
+    // 3. one caster-filtered cull per shadow view (:270-283)
+    std::vector<uint32_t> require((size_t)n_lists, OVIS_CASTS_SHADOW);
+    std::vector<long long> offsets;
+    OVIS_TRY(cull_views_device(w, n_lists, planes.data(), require.data(), nullptr, offsets));
+    int64_t total = offsets.empty() ? 0 : offsets[(size_t)n_lists];
+    *out_n_lists = n_lists;
+    *out_n_entities = total;
+    if (n_lists > cap_lists || total > cap_entities)
+        return fail(OVIS_ERR_CAPACITY, "shadow lists need %d lists / %lld entities", n_lists, (long long)total);
+    if ((n_lists > 0 && (!out_list_light || !out_list_view)) || !out_offsets || (total > 0 && !out_entities))
+        return fail(OVIS_ERR_INVALID, "ovis_build_shadow_lists: null output");
+    for (int32_t k = 0; k < n_lists; k++) {
+        out_list_light[k] = list_light[(size_t)k];
+        out_list_view[k] = list_view[(size_t)k];
+    }
+    for (int32_t k = 0; k <= n_lists; k++)
+        out_offsets[k] = offsets.empty() ? 0 : offsets[(size_t)k];
+    if (total > 0) {
+        OVIS_CUDA(cudaMemcpyAsync(out_entities, w->d_csr_entities, 4 * (size_t)total, cudaMemcpyDeviceToHost, w->stream));
+        OVIS_CUDA(cudaStreamSynchronize(w->stream));
+    }
+    return OVIS_OK;
+}
+
+// ---- read-back ---------------------------------------------------------------------------------
+
+static int read_back(OvisWorld *w, int comps, const float *soa, int64_t stride, uint32_t first, int64_t n, float *out) {
+    for (int64_t s = 0; s < n; s += kUploadChunk) {
+        int64_t c = std::min(kUploadChunk, n - s);
+        size_t bytes = sizeof(float) * (size_t)comps * (size_t)c;
+        if (w->stage_bytes[0] < bytes) {
+            if (w->d_stage[0]) {
+                OVIS_CUDA(cudaStreamSynchronize(w->stream));
+                OVIS_CUDA(cudaFree(w->d_stage[0]));
+                w->d_stage[0] = nullptr;
+                w->stage_bytes[0] = 0;
+            }
+            OVIS_CUDA(cudaMalloc(&w->d_stage[0], bytes));
+            w->stage_bytes[0] = bytes;
+        }
+        ovis::launch_gather_aos(comps, soa, stride, (uint32_t)(first + s), c, (float *)w->d_stage[0], w->stream);
+        w->launches++;
+        OVIS_CUDA(cudaMemcpyAsync(out + comps * s, w->d_stage[0], bytes, cudaMemcpyDeviceToHost, w->stream));
+        OVIS_CUDA(cudaStreamSynchronize(w->stream));
+    }
+    return OVIS_OK;
+}
+
+int ovis_get_world_aabbs(OvisWorld *w, uint32_t first_entity, int64_t n, float *out_aabb) {
+    if (!w || n < 0 || (n > 0 && !out_aabb) || (int64_t)first_entity + n > w->n_ent)
+        return fail(OVIS_ERR_INVALID, "ovis_get_world_aabbs: bad range");
+    OVIS_TRY(use_device(w));
+    OVIS_TRY(flush_transforms(w));
+    return read_back(w, 6, w->d_world, w->cap_ent, first_entity, n, out_aabb);
+}
+
+int ovis_get_node_world_trs(OvisWorld *w, uint32_t first_node, int64_t n, float *out_trs) {
+    if (!w || n < 0 || (n > 0 && !out_trs) || (int64_t)first_node + n > w->n_nodes)
+        return fail(OVIS_ERR_INVALID, "ovis_get_node_world_trs: bad range");
+    OVIS_TRY(use_device(w));
+    OVIS_TRY(flush_transforms(w));
+    return read_back(w, 10, w->d_world_trs, w->cap_nodes, first_node, n, out_trs);
+}
+
+int ovis_read_device(OvisWorld *w, const void *d_src, int64_t bytes, void *host_dst) {
+    if (!w || bytes < 0 || (bytes > 0 && (!d_src || !host_dst)))
+        return fail(OVIS_ERR_INVALID, "ovis_read_device: bad arguments");
+    OVIS_TRY(use_device(w));
+    if (bytes > 0)
+        OVIS_CUDA(cudaMemcpyAsync(host_dst, d_src, (size_t)bytes, cudaMemcpyDeviceToHost, w->stream));
+    OVIS_CUDA(cudaStreamSynchronize(w->stream));
+    return OVIS_OK;
+}
+
+int ovis_host_alloc(int64_t bytes, void **out_ptr) {
+    if (!out_ptr || bytes < 0)
+        return fail(OVIS_ERR_INVALID, "ovis_host_alloc: bad arguments");
+    OVIS_CUDA(cudaMallocHost(out_ptr, (size_t)std::max<int64_t>(bytes, 1)));
+    return OVIS_OK;
+}
+
+int ovis_host_free(void *ptr) {
+    if (ptr)
+        OVIS_CUDA(cudaFreeHost(ptr));
+    return OVIS_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,319 @@
+"""ctypes binding of liborion_vis.so (include/orion_vis.h) - what a cgo/JNI/ctypes user of the C ABI writes.
+
+The library is the product: if it is missing, or no CUDA device is present, calls fail loudly
+(``OvisError``); there is no Python or CPU fallback anywhere in this package.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import re
+import subprocess
+
+import numpy as np
+
+from . import scenes
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+LIB_PATH = os.path.join(HERE, "liborion_vis.so")
+HEADER = os.path.join(ROOT, "include", "orion_vis.h")
+
+OVIS_OK, OVIS_ERR_INVALID, OVIS_ERR_CUDA, OVIS_ERR_CAPACITY, OVIS_ERR_NOMEM = 0, 1, 2, 3, 4
+CASTS_SHADOW = 1
+CULL_LIGHTS = 1
+NO_PARENT = -1
+
+LIGHT_DTYPE = scenes.LIGHT_DTYPE
+VIEW_DTYPE = scenes.VIEW_DTYPE
+
+
+class OvisError(RuntimeError):
+    def __init__(self, code: int, message: str):
+        super().__init__(f"liborion_vis error {code}: {message}")
+        self.code = code
+
+
+def build(verbose: bool = False) -> str:
+    """Compile the CUDA library in-tree for sm_100a (nvcc cross-compiles without a GPU)."""
+    subprocess.run(["make", "-C", os.path.join(HERE, "csrc")] + ([] if verbose else ["-s"]), check=True)
+    return LIB_PATH
+
+
+def declared_symbols() -> list[str]:
+    """Every entry point include/orion_vis.h declares."""
+    text = open(HEADER).read()
+    return sorted(set(re.findall(r"\b(ovis_[a-z0-9_]+)\s*\(", text)))
+
+
+_lib = None
+
+
+def load() -> C.CDLL:
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise OvisError(OVIS_ERR_CUDA, f"{LIB_PATH} is not built; run `make -C orion_b200/csrc` "
+                                           "(there is no CPU fallback)")
+        lib = C.CDLL(LIB_PATH)
+        lib.ovis_last_error.restype = C.c_char_p
+        lib.ovis_version.restype = C.c_char_p
+        _lib = lib
+    return _lib
+
+
+def _check(rc: int):
+    if rc != OVIS_OK:
+        raise OvisError(rc, load().ovis_last_error().decode())
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p) if a is not None else None
+
+
+def _f32(a, shape):
+    return np.ascontiguousarray(a, dtype=np.float32).reshape(shape)
+
+
+def _u32(a):
+    return np.ascontiguousarray(a, dtype=np.uint32).reshape(-1)
+
+
+# ---- host-side set-up (no device needed) -----------------------------------------------------------
+
+def view_planes(view: np.ndarray) -> np.ndarray:
+    view = np.ascontiguousarray(view, dtype=VIEW_DTYPE)
+    out = np.zeros(24, dtype=np.float32)
+    _check(load().ovis_view_planes(_p(view), _p(out)))
+    return out.reshape(6, 4)
+
+
+def view_matrices(view: np.ndarray):
+    view = np.ascontiguousarray(view, dtype=VIEW_DTYPE)
+    mats = np.zeros(64, dtype=np.float32)
+    corners = np.zeros(24, dtype=np.float32)
+    _check(load().ovis_view_matrices(_p(view), _p(mats), _p(corners)))
+    return mats.reshape(4, 16), corners.reshape(8, 3)
+
+
+def light_spot_aabb(light: np.ndarray) -> np.ndarray:
+    light = np.ascontiguousarray(light, dtype=LIGHT_DTYPE)
+    out = np.zeros(6, dtype=np.float32)
+    _check(load().ovis_light_spot_aabb(_p(light), _p(out)))
+    return out
+
+
+def light_shadow_views(light: np.ndarray, resolution: int = 512) -> np.ndarray:
+    light = np.ascontiguousarray(light, dtype=LIGHT_DTYPE)
+    out = np.zeros(6, dtype=VIEW_DTYPE)
+    n = C.c_int32(0)
+    _check(load().ovis_light_shadow_views(_p(light), C.c_int32(resolution), _p(out), C.byref(n)))
+    return out[:n.value].copy()
+
+
+class PinnedBuffer:
+    """Page-locked host memory from ovis_host_alloc, viewed as a numpy array."""
+
+    def __init__(self, count: int, dtype=np.uint32):
+        self.ptr = C.c_void_p()
+        self.dtype = np.dtype(dtype)
+        nbytes = max(int(count), 1) * self.dtype.itemsize
+        _check(load().ovis_host_alloc(C.c_int64(nbytes), C.byref(self.ptr)))
+        buf = (C.c_char * nbytes).from_address(self.ptr.value)
+        self.array = np.frombuffer(buf, dtype=self.dtype, count=max(int(count), 1))
+
+    def free(self):
+        if self.ptr:
+            self.array = None
+            load().ovis_host_free(self.ptr)
+            self.ptr = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+
+class World:
+    """Device-resident render world: the RenderWorld of engine/runtime/render/include/render_world.h:58-98."""
+
+    def __init__(self, device: int = 0):
+        self.lib = load()
+        self.h = C.c_void_p()
+        _check(self.lib.ovis_world_create(C.c_int(device), C.byref(self.h)))
+        self.device = device
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.ovis_world_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- bookkeeping
+    def reserve(self, n_entities=0, n_nodes=0):
+        _check(self.lib.ovis_world_reserve(self.h, C.c_int64(n_entities), C.c_int64(n_nodes)))
+
+    def set_stream(self, cuda_stream: int):
+        _check(self.lib.ovis_world_set_stream(self.h, C.c_void_p(cuda_stream)))
+
+    def set_id_base(self, id_base: int):
+        _check(self.lib.ovis_world_set_id_base(self.h, C.c_uint32(id_base)))
+
+    def counts(self):
+        ne, nn, nl = C.c_int64(), C.c_int64(), C.c_int32()
+        _check(self.lib.ovis_world_counts(self.h, C.byref(ne), C.byref(nn), C.byref(nl)))
+        return ne.value, nn.value, nl.value
+
+    def launch_count(self) -> int:
+        n = C.c_int64()
+        _check(self.lib.ovis_world_launch_count(self.h, C.byref(n)))
+        return n.value
+
+    # ---- entities
+    def add_entities(self, local_aabb, flags=None) -> int:
+        local_aabb = _f32(local_aabb, (-1, 6))
+        flags = _u32(flags) if flags is not None else None
+        first = C.c_uint32()
+        _check(self.lib.ovis_entity_add(self.h, C.c_int64(len(local_aabb)), _p(local_aabb), _p(flags), C.byref(first)))
+        return first.value
+
+    def remove_entities(self, ids):
+        ids = _u32(ids)
+        _check(self.lib.ovis_entity_remove(self.h, C.c_int64(len(ids)), _p(ids)))
+
+    def set_local_aabbs(self, ids, local_aabb):
+        ids = _u32(ids)
+        local_aabb = _f32(local_aabb, (-1, 6))
+        _check(self.lib.ovis_entity_set_local_aabbs(self.h, C.c_int64(len(ids)), _p(ids), _p(local_aabb)))
+
+    def set_flags(self, ids, flags):
+        ids, flags = _u32(ids), _u32(flags)
+        _check(self.lib.ovis_entity_set_flags(self.h, C.c_int64(len(ids)), _p(ids), _p(flags)))
+
+    def set_transforms(self, ids, world_trs):
+        ids = _u32(ids)
+        world_trs = _f32(world_trs, (-1, 10))
+        _check(self.lib.ovis_entity_set_transforms(self.h, C.c_int64(len(ids)), _p(ids), _p(world_trs)))
+
+    def set_world_aabbs(self, first_id, world_aabb):
+        world_aabb = _f32(world_aabb, (-1, 6))
+        _check(self.lib.ovis_entity_set_world_aabbs(self.h, C.c_uint32(first_id), C.c_int64(len(world_aabb)), _p(world_aabb)))
+
+    # ---- transform tree
+    def add_nodes(self, parent, local_trs) -> int:
+        parent = np.ascontiguousarray(parent, dtype=np.int32).reshape(-1)
+        local_trs = _f32(local_trs, (-1, 10))
+        first = C.c_uint32()
+        _check(self.lib.ovis_node_add(self.h, C.c_int64(len(parent)), _p(parent), _p(local_trs), C.byref(first)))
+        return first.value
+
+    def set_node_local_trs(self, ids, local_trs):
+        ids = _u32(ids)
+        local_trs = _f32(local_trs, (-1, 10))
+        _check(self.lib.ovis_node_set_local_trs(self.h, C.c_int64(len(ids)), _p(ids), _p(local_trs)))
+
+    def bind_entities(self, node_ids, entity_ids):
+        node_ids, entity_ids = _u32(node_ids), _u32(entity_ids)
+        _check(self.lib.ovis_node_bind_entities(self.h, C.c_int64(len(node_ids)), _p(node_ids), _p(entity_ids)))
+
+    def update_transforms(self):
+        _check(self.lib.ovis_update_transforms(self.h))
+
+    # ---- lights
+    def add_lights(self, lights) -> int:
+        lights = np.ascontiguousarray(lights, dtype=LIGHT_DTYPE).reshape(-1)
+        first = C.c_uint32()
+        _check(self.lib.ovis_light_add(self.h, C.c_int32(len(lights)), _p(lights), C.byref(first)))
+        return first.value
+
+    def update_light(self, light_id, light):
+        light = np.ascontiguousarray(light, dtype=LIGHT_DTYPE)
+        _check(self.lib.ovis_light_update(self.h, C.c_uint32(light_id), _p(light)))
+
+    def remove_light(self, light_id):
+        _check(self.lib.ovis_light_remove(self.h, C.c_uint32(light_id)))
+
+    # ---- culling
+    def cull(self, view, flags=CULL_LIGHTS, out_entities=None, out_lights=None):
+        """RenderWorld::cull(view, results, flags) -> (entity ids, light ids), host arrays."""
+        view = np.ascontiguousarray(view, dtype=VIEW_DTYPE)
+        ne_slots, _, nl_slots = self.counts()
+        ents = out_entities if out_entities is not None else np.empty(max(ne_slots, 1), dtype=np.uint32)
+        lights = out_lights if out_lights is not None else np.empty(max(nl_slots, 1), dtype=np.uint32)
+        ne, nl = C.c_int64(), C.c_int32()
+        _check(self.lib.ovis_cull(self.h, _p(view), C.c_uint32(flags), _p(ents), C.c_int64(len(ents)), C.byref(ne),
+                                  _p(lights), C.c_int32(len(lights)), C.byref(nl)))
+        return ents[:ne.value], lights[:nl.value]
+
+    def cull_planes(self, planes, require=0, out=None):
+        planes = _f32(planes, (24,))
+        ne_slots, _, _ = self.counts()
+        ents = out if out is not None else np.empty(max(ne_slots, 1), dtype=np.uint32)
+        ne = C.c_int64()
+        _check(self.lib.ovis_cull_planes(self.h, _p(planes), C.c_uint32(require), _p(ents), C.c_int64(len(ents)), C.byref(ne)))
+        return ents[:ne.value]
+
+    def cull_planes_device(self, planes, d_out_ptr: int, d_count_ptr: int, require=0):
+        """Asynchronous; results stay on the device (raw device pointers, e.g. torch tensor .data_ptr())."""
+        planes = _f32(planes, (24,))
+        _check(self.lib.ovis_cull_planes_device(self.h, _p(planes), C.c_uint32(require), C.c_void_p(d_out_ptr),
+                                                C.c_void_p(d_count_ptr)))
+
+    def cull_views_device(self, planes, require=None):
+        """Many views, CSR result on the device. Returns (host offsets, d_offsets ptr, d_entities ptr)."""
+        planes = _f32(planes, (-1, 24))
+        nv = len(planes)
+        require = _u32(require) if require is not None else None
+        d_off, d_ent = C.c_void_p(), C.c_void_p()
+        host = np.zeros(nv + 1, dtype=np.int64)
+        _check(self.lib.ovis_cull_views_device(self.h, C.c_int32(nv), _p(planes), _p(require), C.byref(d_off),
+                                               C.byref(d_ent), _p(host)))
+        return host, d_off.value, d_ent.value
+
+    def shadow_lists(self, main_view, shadow_res=512):
+        """prepareLights' per-shadow-view caster lists -> (list_light, list_view, offsets, entities)."""
+        main_view = np.ascontiguousarray(main_view, dtype=VIEW_DTYPE)
+        ne_slots, _, nl_slots = self.counts()
+        cap_lists = 6 * max(nl_slots, 1)
+        cap_ent = max(ne_slots, 1) * 2
+        while True:
+            ll = np.zeros(cap_lists, dtype=np.int32)
+            lv = np.zeros(cap_lists, dtype=np.int32)
+            off = np.zeros(cap_lists + 1, dtype=np.int64)
+            ent = np.zeros(cap_ent, dtype=np.uint32)
+            nl, ne = C.c_int32(), C.c_int64()
+            rc = self.lib.ovis_build_shadow_lists(self.h, _p(main_view), C.c_int32(shadow_res), C.c_int32(cap_lists),
+                                                  _p(ll), _p(lv), _p(off), C.byref(nl), C.c_int64(cap_ent), _p(ent),
+                                                  C.byref(ne))
+            if rc == OVIS_ERR_CAPACITY:
+                cap_lists, cap_ent = max(cap_lists, nl.value), max(cap_ent, ne.value)
+                continue
+            _check(rc)
+            k = nl.value
+            return ll[:k].copy(), lv[:k].copy(), off[:k + 1].copy(), ent[:ne.value].copy()
+
+    # ---- read-back
+    def read_device(self, d_ptr: int, count: int, dtype=np.uint32) -> np.ndarray:
+        out = np.empty(max(count, 1), dtype=dtype)
+        _check(self.lib.ovis_read_device(self.h, C.c_void_p(d_ptr), C.c_int64(count * out.itemsize), _p(out)))
+        return out[:count]
+
+    def world_aabbs(self, first=0, n=None) -> np.ndarray:
+        if n is None:
+            n = self.counts()[0] - first
+        out = np.zeros((n, 6), dtype=np.float32)
+        _check(self.lib.ovis_get_world_aabbs(self.h, C.c_uint32(first), C.c_int64(n), _p(out)))
+        return out
+
+    def node_world_trs(self, first=0, n=None) -> np.ndarray:
+        if n is None:
+            n = self.counts()[1] - first
+        out = np.zeros((n, 10), dtype=np.float32)
+        _check(self.lib.ovis_get_node_world_trs(self.h, C.c_uint32(first), C.c_int64(n), _p(out)))
+        return out

@@ -1,0 +1,266 @@
+"""GPU parity: the CUDA path, called through the C ABI, against the CPU oracle on identical inputs.
+Visible sets and lists must be identical (same ids, same order); transforms and bounds are compared
+for exact value equality (the tolerance north_star allows is 1e-5 relative; we hold 0)."""
+import numpy as np
+import pytest
+
+from orion_b200 import lib, scenes
+import vis_testutil as util
+from vis_testutil import same
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def oracle():
+    from oracle import pyoracle
+    return pyoracle.load("best")
+
+
+def _world_static(aabb, flags=None):
+    w = lib.World(0)
+    first = w.add_entities(aabb, flags)
+    w.set_world_aabbs(first, aabb)
+    return w
+
+
+@pytest.mark.parametrize("n", [0, 1, 3, 4, 5, 1023, 1024, 1025, 4097, 100_000])
+def test_single_view_sizes(oracle, n):
+    rng = np.random.default_rng(100 + n)
+    aabb = util.random_boxes(rng, n, extent=300.0)
+    flags = rng.integers(0, 2, n).astype(np.uint32)
+    w = _world_static(aabb, flags)
+    for v in util.random_views(rng, 3, extent=50.0):
+        planes = oracle.view_planes(np.asarray(v))
+        assert np.array_equal(w.cull_planes(planes), oracle.cull_aabb(aabb, planes))
+        assert np.array_equal(w.cull_planes(planes, require=1), oracle.cull_aabb(aabb, planes, flags, 1))
+        ents, _ = w.cull(np.asarray(v), flags=0)
+        assert np.array_equal(ents, oracle.cull_aabb(aabb, planes))
+    w.close()
+
+
+def test_config2_one_million_static(oracle):
+    s = scenes.config2()
+    w = _world_static(s["aabb"], s["flags"])
+    planes = oracle.view_planes(s["view"])
+    exp = oracle.cull_aabb(s["aabb"], planes, threads=8)
+    got, _ = w.cull(s["view"], flags=0)
+    assert 0.02 * len(s["aabb"]) < len(exp) < 0.3 * len(s["aabb"])
+    assert np.array_equal(got, exp)
+    # repeated launches reuse the tile-status scratch through the epoch tag: results must not change
+    for _ in range(5):
+        assert np.array_equal(w.cull_planes(planes), exp)
+    w.close()
+
+
+def test_edge_boxes_and_planes(oracle):
+    rng = np.random.default_rng(31)
+    aabb = np.concatenate([util.edge_boxes(), util.random_boxes(rng, 2000, extent=30.0)])
+    w = _world_static(aabb)
+    for v in util.random_views(rng, 10, extent=20.0):
+        planes = oracle.view_planes(np.asarray(v))
+        assert np.array_equal(w.cull_planes(planes), oracle.cull_aabb(aabb, planes))
+    axis = np.array([[1, 0, 0, -10], [-1, 0, 0, -10], [0, -1, 0, -10], [0, 1, 0, -10], [0, 0, -1, -10],
+                     [0, 0, 1, -10]], dtype=np.float32)
+    touch = np.array([[10, 0, 0, 11, 1, 1], [-11, 0, 0, -10, 1, 1], [10.000001, 0, 0, 11, 1, 1],
+                      [-12, 0, 0, -10.000001, 1, 1], [0, 0, 0, 1, 1, 1]], dtype=np.float32)
+    w2 = _world_static(touch)
+    assert np.array_equal(w2.cull_planes(axis), oracle.cull_aabb(touch, axis))
+    neg0 = axis.copy()
+    neg0[:, :3] *= -0.0
+    assert np.array_equal(w2.cull_planes(neg0), oracle.cull_aabb(touch, neg0))
+    w.close()
+    w2.close()
+
+
+def test_remove_keeps_order_and_flags_update(oracle):
+    rng = np.random.default_rng(32)
+    n = 20_000
+    aabb = util.random_boxes(rng, n, extent=200.0)
+    flags = rng.integers(0, 2, n).astype(np.uint32)
+    w = _world_static(aabb, flags)
+    v = scenes.make_view((0, 0, 250), (1, 0, 0, 0), 90.0, 0.1, 1000.0, 1600, 900)
+    planes = oracle.view_planes(v)
+    full = oracle.cull_aabb(aabb, planes)
+    removed = rng.choice(n, 3000, replace=False).astype(np.uint32)
+    w.remove_entities(removed)
+    keep = np.ones(n, dtype=bool)
+    keep[removed] = False
+    assert np.array_equal(w.cull_planes(planes), full[keep[full]])
+    flags2 = flags.copy()
+    flip = rng.choice(np.flatnonzero(keep), 2000, replace=False).astype(np.uint32)
+    flags2[flip] ^= 1
+    w.set_flags(flip, flags2[flip])
+    exp = oracle.cull_aabb(aabb, planes, flags2, 1)
+    assert np.array_equal(w.cull_planes(planes, require=1), exp[keep[exp]])
+    # entities appended later come after every earlier id
+    more = util.random_boxes(rng, 500, extent=200.0)
+    first = w.add_entities(more)
+    w.set_world_aabbs(first, more)
+    allb = np.concatenate([aabb, more])
+    keep2 = np.concatenate([keep, np.ones(500, dtype=bool)])
+    e2 = oracle.cull_aabb(allb, planes)
+    assert np.array_equal(w.cull_planes(planes), e2[keep2[e2]])
+    with pytest.raises(lib.OvisError):
+        w.remove_entities(removed[:1])      # already gone
+    w.close()
+
+
+def test_transform_tree_and_bounds(oracle):
+    rng = np.random.default_rng(33)
+    n = 30_000
+    parent = np.empty(n, dtype=np.int32)
+    parent[0] = -1
+    parent[1:] = (rng.random(n - 1) * np.arange(1, n)).astype(np.int32)      # arbitrary earlier parent: ragged levels
+    parent[1:40] = np.arange(0, 39)                                           # deep chain
+    local = util.random_trs(rng, n)
+    local[:, 7:10] = rng.uniform(0.5, 1.5, (n, 3))                            # keep magnitudes finite down the chain
+    boxes = util.random_boxes(rng, n, extent=2.0, hmax=2.0)
+    flags = rng.integers(0, 2, n).astype(np.uint32)
+    w = lib.World(0)
+    e0 = w.add_entities(boxes, flags)
+    n0 = w.add_nodes(parent, local)
+    w.bind_entities(np.arange(n0, n0 + n), np.arange(e0, e0 + n))
+    wt = oracle.world_trs(parent, local)
+    assert same(w.node_world_trs(), wt)
+    wb = oracle.world_aabb(wt, boxes)
+    assert same(w.world_aabbs(), wb)
+    v = scenes.make_view((0, 0, 150), (1, 0, 0, 0), 90.0, 0.1, 1000.0, 1600, 900)
+    planes = oracle.view_planes(v)
+    assert np.array_equal(w.cull_planes(planes), oracle.cull_aabb(wb, planes))
+    # move some nodes: everything below must follow
+    moved = rng.choice(n, 500, replace=False).astype(np.uint32)
+    local[moved] = util.random_trs(rng, 500)
+    local[moved, 7:10] = rng.uniform(0.5, 1.5, (500, 3))
+    w.set_node_local_trs(moved, local[moved])
+    wt = oracle.world_trs(parent, local)
+    wb = oracle.world_aabb(wt, boxes)
+    assert same(w.node_world_trs(), wt)
+    assert same(w.world_aabbs(), wb)
+    assert np.array_equal(w.cull_planes(planes), oracle.cull_aabb(wb, planes))
+    w.close()
+
+
+def test_two_entities_on_one_node(oracle):
+    """A MeshRenderer owns one RenderEntity per sub-mesh, all following the same Entity."""
+    rng = np.random.default_rng(38)
+    parent = np.array([-1, 0, 1], dtype=np.int32)
+    local = util.random_trs(rng, 3)
+    boxes = util.random_boxes(rng, 5, extent=2.0)
+    w = lib.World(0)
+    w.add_entities(boxes)
+    w.add_nodes(parent, local)
+    w.bind_entities([2, 2, 2, 1, 0], [0, 1, 2, 3, 4])
+    wt = oracle.world_trs(parent, local)
+    exp = oracle.world_aabb(wt[[2, 2, 2, 1, 0]], boxes)
+    assert same(w.world_aabbs(), exp)
+    w.close()
+
+
+def test_direct_transforms_and_edge_cases(oracle):
+    """RenderEntity::setTransform path incl. skybox box, negative scale, NaN / Inf transforms."""
+    rng = np.random.default_rng(34)
+    n = 5000
+    trs = util.random_trs(rng, n)
+    boxes = util.random_boxes(rng, n, extent=2.0, hmax=2.0)
+    e = util.edge_boxes()
+    boxes[:len(e)] = e
+    trs[:len(e)] = scenes.IDENTITY_TRS
+    trs[20] = scenes.IDENTITY_TRS
+    boxes[20] = e[0]
+    trs[20, 0:3] = (5, 6, 7)                 # translated skybox box -> Inf/NaN bounds
+    trs[21, 0] = np.nan
+    trs[22, 3] = np.inf
+    trs[23, 7:10] = 0
+    w = lib.World(0)
+    w.add_entities(boxes)
+    # before any transform: world box = local box under the identity transform
+    assert same(w.world_aabbs(), oracle.world_aabb(np.tile(scenes.IDENTITY_TRS, (n, 1)), boxes))
+    w.set_transforms(np.arange(n), trs)
+    wb = oracle.world_aabb(trs, boxes)
+    assert same(w.world_aabbs(), wb)
+    for v in util.random_views(rng, 5, extent=50.0):
+        planes = oracle.view_planes(np.asarray(v))
+        assert np.array_equal(w.cull_planes(planes), oracle.cull_aabb(wb, planes))
+    # second update of a subset, and a changed local box
+    sub = rng.choice(n, 700, replace=False).astype(np.uint32)
+    trs[sub] = util.random_trs(rng, 700)
+    w.set_transforms(sub, trs[sub])
+    boxes[sub[:50]] = util.random_boxes(rng, 50, extent=1.0)
+    w.set_local_aabbs(sub[:50], boxes[sub[:50]])
+    assert same(w.world_aabbs(), oracle.world_aabb(trs, boxes))
+    w.close()
+
+
+def test_lights_and_full_cull(oracle):
+    rng = np.random.default_rng(35)
+    aabb = util.random_boxes(rng, 10_000, extent=100.0)
+    lights = util.random_lights(rng, 700, extent=120.0)
+    w = _world_static(aabb)
+    w.add_lights(lights)
+    for v in util.random_views(rng, 8, extent=60.0):
+        v = np.asarray(v)
+        planes = oracle.view_planes(v)
+        ents, ls = w.cull(v)
+        assert np.array_equal(ents, oracle.cull_aabb(aabb, planes))
+        assert np.array_equal(ls, oracle.light_cull(lights, planes))
+    lights2 = lights.copy()
+    lights2[5] = util.random_lights(rng, 1)[0]
+    w.update_light(5, lights2[5])
+    w.remove_light(7)
+    v = np.asarray(util.random_views(rng, 1, extent=60.0)[0])
+    planes = oracle.view_planes(v)
+    exp = oracle.light_cull(lights2, planes)
+    _, ls = w.cull(v)
+    assert np.array_equal(ls, exp[exp != 7])
+    w.close()
+
+
+def test_shadow_lists_and_cubes_scene(oracle):
+    s = scenes.cubes_scene()
+    w = lib.World(0)
+    w.add_entities(s["local_aabb"], s["flags"])
+    w.set_transforms(np.arange(4), s["trs"])
+    w.add_lights(s["lights"])
+    wb = oracle.world_aabb(s["trs"], s["local_aabb"])
+    assert same(w.world_aabbs(), wb)
+    planes = oracle.view_planes(s["view"])
+    ents, ls = w.cull(s["view"])
+    assert np.array_equal(ents, oracle.cull_aabb(wb, planes))
+    assert np.array_equal(ls, oracle.light_cull(s["lights"], planes))
+    got = w.shadow_lists(s["view"])
+    exp = oracle.shadow_lists(wb, s["flags"], s["lights"], planes)
+    for x, y in zip(got, exp):
+        assert np.array_equal(x, y)
+    w.close()
+    rng = np.random.default_rng(36)
+    boxes = util.random_boxes(rng, 20_000, extent=60.0, hmax=3.0)
+    flags = rng.integers(0, 2, len(boxes)).astype(np.uint32)
+    lights = util.random_lights(rng, 40, extent=40.0)
+    w = _world_static(boxes, flags)
+    w.add_lights(lights)
+    cam = scenes.make_view((0, 0, 70), (1, 0, 0, 0), 90.0, 0.1, 300.0, 1600, 900)
+    got = w.shadow_lists(cam)
+    exp = oracle.shadow_lists(boxes, flags, lights, oracle.view_planes(cam))
+    assert len(exp[0]) > 6
+    for x, y in zip(got, exp):
+        assert np.array_equal(x, y)
+    w.close()
+
+
+def test_multi_view_csr(oracle):
+    rng = np.random.default_rng(37)
+    boxes = util.random_boxes(rng, 50_000, extent=200.0)
+    flags = rng.integers(0, 2, len(boxes)).astype(np.uint32)
+    w = _world_static(boxes, flags)
+    views = util.random_views(rng, 9, extent=80.0)
+    planes = np.stack([oracle.view_planes(np.asarray(v)).reshape(24) for v in views])
+    require = np.array([0, 1, 0, 1, 1, 0, 0, 1, 0], dtype=np.uint32)
+    off, d_off, d_ent = w.cull_views_device(planes, require)
+    total = int(off[-1])
+    ent = w.read_device(d_ent, total)
+    assert np.array_equal(w.read_device(d_off, len(views) + 1, np.int64), off)
+    for i in range(len(views)):
+        exp = oracle.cull_aabb(boxes, planes[i], flags, int(require[i]))
+        assert np.array_equal(ent[off[i]:off[i + 1]], exp)
+    w.close()
