@@ -1,0 +1,453 @@
+#!/usr/bin/env python
+"""bench.py - entity-view cull throughput of the B200 scene-visibility path (BASELINE.json metric).
+
+    python bench.py --gpus N --steps K --warmup W            # ours (CUDA, through the C ABI)
+    python bench.py --impl reference --gpus N --steps K --warmup W   # the reference's CPU cull, host cores
+
+Workload (config.workload): BASELINE.json configs[4] sharded by contiguous id range with a FIXED shard of
+12.5 M entities per GPU (100 M at 8 GPUs; weak scaling), entities generated like configs[1]/[4]
+(SURVEY.md section 8(d)), one camera frustum. A step = one frame's cull of the whole (sharded) entity set:
+one single-pass cull kernel per GPU and, for N > 1, one NCCL all-gather of the compacted per-shard lists.
+configs[1] itself (1 M entities, 24 MB: L2-resident and launch-latency-bound) is reported beside it under
+"also" at N = 1, cold (L2 flushed between iterations) and warm.
+
+One JSON line on stdout (rank 0). Timing: CUDA events on the launching stream, barrier + synchronize on
+both sides, max over ranks. The 300 MB shard is larger than the 126 MB L2, so every step streams from HBM.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+from orion_b200 import scenes  # noqa: E402
+
+SHARD_ENTITIES = 12_500_000
+SCENE_SEED = 4
+EXTENT = 4000.0
+METRIC = "entity-view cull tests/sec"
+UNIT = "tests/s"
+
+
+def shard_scene(shard: int, n: int):
+    """Shard `shard` of the sharded configs[4] scene: every shard has its own seed so any rank can build its part."""
+    return scenes.static_boxes(n, SCENE_SEED * 1000 + shard, EXTENT)
+
+
+def workload_name(n_gpus: int, n: int) -> str:
+    return (f"configs[4] sharded: {n / 1e6:g}M entities/GPU x {n_gpus} GPU = {n * n_gpus / 1e6:g}M entities, "
+            f"1 camera frustum (hfov 75, 16:9, far 1000), config-2 distribution in [-{EXTENT:g},{EXTENT:g}]^3")
+
+
+def host_cores() -> int:
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+# --------------------------------------------------------------------------------------------------
+# clocks
+# --------------------------------------------------------------------------------------------------
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock and clock-event reasons through NVML while the timed region runs."""
+    REASONS = {0x4: "sw_power_cap", 0x8: "hw_slowdown", 0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown",
+               0x80: "hw_power_brake_slowdown", 0x2: "applications_clocks_setting"}
+
+    def __init__(self, device_index: int, period: float = 0.01):
+        super().__init__(daemon=True)
+        self.period = period
+        self.samples = []          # (t, sm_mhz, reasons)
+        self.stop_flag = threading.Event()
+        self.ok = False
+        try:
+            import pynvml
+            import torch
+            pynvml.nvmlInit()
+            uuid = str(torch.cuda.get_device_properties(device_index).uuid)
+            if not uuid.startswith("GPU-"):
+                uuid = "GPU-" + uuid
+            try:
+                self.h = pynvml.nvmlDeviceGetHandleByUUID(uuid)
+            except Exception:
+                self.h = pynvml.nvmlDeviceGetHandleByIndex(device_index)
+            self.nv = pynvml
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+            self.ok = True
+        except Exception as e:   # NVML missing: report that instead of inventing numbers
+            self.error = repr(e)
+
+    def run(self):
+        if not self.ok:
+            return
+        nv = self.nv
+        while not self.stop_flag.is_set():
+            try:
+                mhz = nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)
+                try:
+                    reasons = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                except Exception:
+                    reasons = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                self.samples.append((time.perf_counter(), mhz, reasons))
+            except Exception:
+                pass
+            time.sleep(self.period)
+
+    def count_between(self, t0: float, t1: float) -> int:
+        return len([s for s in self.samples if t0 <= s[0] <= t1])
+
+    def summary(self, t0: float, t1: float, note: str):
+        if not self.ok:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "error": getattr(self, "error", "nvml unavailable")}
+        sel = [s for s in self.samples if t0 <= s[0] <= t1]
+        reasons = set()
+        for _, _, r in sel:
+            for bit, name in self.REASONS.items():
+                if r & bit:
+                    reasons.add(name)
+        mhz = float(np.median([s[1] for s in sel])) if sel else None
+        return {"sm_mhz": mhz, "sm_max_mhz": float(self.max_mhz), "reasons": sorted(reasons), "samples": len(sel),
+                "sampled_over": note}
+
+
+# --------------------------------------------------------------------------------------------------
+# reference arm: the reference's CPU cull on the host cores
+# --------------------------------------------------------------------------------------------------
+
+def cpu_cull_timing(oracle, aabb, planes, threads: int, steps: int, warmup: int):
+    out = None
+    for _ in range(warmup):
+        out = oracle.cull_aabb(aabb, planes, threads=threads)
+    times = []
+    for _ in range(steps):
+        t0 = time.perf_counter()
+        out = oracle.cull_aabb(aabb, planes, threads=threads)
+        times.append(time.perf_counter() - t0)
+    return np.array(times), out
+
+
+def as_shipped_timing(oracle, aabb, view, iters=5):
+    """SimpleRenderWorld::cull over std::list<RenderEntity*> exactly as shipped, 1 thread (tier A)."""
+    if not oracle.has_world:
+        return None
+    w = oracle.world()
+    n = len(aabb)
+    w.add_entities(np.tile(scenes.IDENTITY_TRS, (n, 1)), aabb, None)
+    ms, vis = w.time_cull(view, flags=0, iters=iters)
+    w.abandon()     # entity-by-entity teardown is O(n^2) in the reference
+    return {"entities": n, "ms_per_frame": float(np.median(ms)), "tests_per_s": n / (float(np.median(ms)) * 1e-3),
+            "visible": int(vis), "threads": 1}
+
+
+def run_reference(args, rank: int):
+    if rank != 0:
+        return
+    from oracle import pyoracle
+    oracle = pyoracle.load("best")
+    cores = host_cores()
+    n = args.entities_per_gpu
+    aabb, _ = shard_scene(0, n)
+    view = scenes.default_camera()
+    planes = oracle.view_planes(view)
+    times, out = cpu_cull_timing(oracle, aabb, planes, cores, args.steps, max(args.warmup, 1))
+    total = float(times.sum())
+    value = n * args.steps / total
+    shipped = as_shipped_timing(oracle, aabb[:1_000_000], view) if not args.skip_extras else None
+    sample = (f"shard 0 ({n / 1e6:g}M entities, 1 frustum) per step; the arithmetic is the reference's own "
+              f"Math::intersect compiled from its sources, driven over flat AABB arrays by {cores} host threads"
+              if oracle.name == "reference" else
+              f"shard 0 ({n / 1e6:g}M entities, 1 frustum) per step; C restatement of the reference, {cores} host threads")
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": total / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": workload_name(args.gpus, n), "entities_per_step_timed": n, "views": 1},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": oracle.name, "sample": sample,
+                         "visible": int(len(out)), "as_shipped_std_list_1thread": shipped},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# --------------------------------------------------------------------------------------------------
+# ours
+# --------------------------------------------------------------------------------------------------
+
+def time_kernel_loop(torch, stream, fn, iters: int, flush=None):
+    """Per-iteration device times (ms) of fn() with CUDA events on `stream`."""
+    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(iters)]
+    with torch.cuda.stream(stream):
+        for a, b in evs:
+            if flush is not None:
+                flush()
+            a.record(stream)
+            fn()
+            b.record(stream)
+    stream.synchronize()
+    return np.array([a.elapsed_time(b) for a, b in evs])
+
+
+def config2_extra(torch, lib, stream, scratch, peak_gbs):
+    """configs[1]: 1M static entities, 1 frustum, 1 GPU - cold (L2 flushed) and warm, kernel only + e2e."""
+    s = scenes.config2()
+    n = len(s["aabb"])
+    w = lib.World(torch.cuda.current_device())
+    w.set_stream(stream.cuda_stream)
+    first = w.add_entities(s["aabb"], s["flags"])
+    w.set_world_aabbs(first, s["aabb"])
+    planes = lib.view_planes(s["view"])
+    out = torch.zeros(n + 1, dtype=torch.int32, device="cuda")
+
+    def fn():
+        w.cull_planes_device(planes, out.data_ptr() + 4, out.data_ptr())
+
+    time_kernel_loop(torch, stream, fn, 5)
+    cold = time_kernel_loop(torch, stream, fn, 30, flush=lambda: scratch.add_(1))   # 512 MB r+w evicts the 126 MB L2
+    warm = time_kernel_loop(torch, stream, fn, 200)
+    vis = int(out[0].item())
+    pinned = lib.PinnedBuffer(n)
+    for _ in range(3):
+        w.cull(s["view"], flags=0, out_entities=pinned.array)
+    t0 = time.perf_counter()
+    reps = 50
+    for _ in range(reps):
+        w.cull(s["view"], flags=0, out_entities=pinned.array)
+    e2e_ms = (time.perf_counter() - t0) / reps * 1e3
+    w.close()
+    bytes_alg = 24 * n + 4 * vis
+
+    def pack(ms):
+        return {"ms_per_frame": ms, "tests_per_s": n / (ms * 1e-3), "achieved_gbs": bytes_alg / (ms * 1e-3) / 1e9,
+                "frac_of_hbm_peak": bytes_alg / (ms * 1e-3) / 1e9 / peak_gbs}
+
+    return {"workload": "configs[1]: synthetic 1M static entities, 1 camera frustum, 1 GPU", "entities": n, "visible": vis,
+            "cold_l2_flushed": pack(float(np.median(cold))), "warm_l2_resident": pack(float(np.median(warm))),
+            "e2e_host_api": {"ms_per_frame": e2e_ms, "tests_per_s": n / (e2e_ms * 1e-3)},
+            "note": "24 MB of bounds = 3.7 us of HBM traffic at the measured peak: this size is launch-latency bound"}
+
+
+def run_ours(args, rank: int, local_rank: int, world_size: int):
+    import torch
+    import torch.distributed as dist
+    from orion_b200 import lib
+    from orion_b200.sharded import ShardedWorld, merged_list
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device - the product path has no CPU fallback "
+                         "(use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local_rank)
+    if world_size > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak_gbs = float(peaks.get("hbm_gbs", 6650.0))
+    peak_src = "MEASURED_PEAKS.json hbm_gbs (measured)" if "hbm_gbs" in peaks else "6650 GB/s fallback (B200_PROFILING.md)"
+
+    n = args.entities_per_gpu
+    aabb, flags = shard_scene(rank, n)
+    view = scenes.default_camera()
+    planes = lib.view_planes(view)
+
+    stream = torch.cuda.Stream()
+    world = lib.World(local_rank)
+    world.reserve(n_entities=n)
+    first = world.add_entities(aabb, flags)
+    world.set_world_aabbs(first, aabb)
+    sw = ShardedWorld(world, rank, world_size, rank * n, n, stream=stream)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world_size > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- warm-up (also sizes the exchange block from the real counts)
+    blocks, counts = sw.cull(planes)
+    sw.resize(int(counts.max() * 1.25) + 1024)
+    for _ in range(max(args.warmup, 3)):
+        sw.cull_device(planes)
+    barrier()
+
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    time.sleep(0.05)
+
+    # ---- timed region: exactly K steps, device-resident inputs
+    launches0 = world.launch_count()
+    k_start = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
+    k_end = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    t_wall0 = time.perf_counter()
+    with torch.cuda.stream(stream):
+        ev0.record(stream)
+        for i in range(args.steps):
+            k_start[i].record(stream)
+            sw.cull_local(planes)
+            k_end[i].record(stream)
+            if world_size > 1:
+                blocks = sw.exchange()
+        ev1.record(stream)
+    barrier()
+    t_wall1 = time.perf_counter()
+    launches = world.launch_count() - launches0
+    elapsed_ms = ev0.elapsed_time(ev1)
+    kernel_ms = np.array([a.elapsed_time(b) for a, b in zip(k_start, k_end)])
+    t = torch.tensor([elapsed_ms], dtype=torch.float64, device="cuda")
+    if world_size > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    elapsed_ms = float(t.item())
+
+    # clocks: the timed region can be shorter than a few NVML samples; soak with the identical loop if so
+    note = "timed region"
+    if sampler.count_between(t_wall0, t_wall1) < 3:
+        t_soak = time.perf_counter()
+        while time.perf_counter() - t_soak < 1.0:
+            for _ in range(50):
+                sw.cull_local(planes)
+            stream.synchronize()
+        t_wall1 = time.perf_counter()
+        note = "timed region + 1 s of the identical untimed loop (region shorter than 3 NVML samples)"
+    clocks = sampler.summary(t_wall0, t_wall1, note)
+
+    # ---- e2e: the call a user makes, host buffers, copies inside the timed region
+    blocks, counts = sw.cull(planes)
+    total_visible = int(counts.sum())
+    pinned = lib.PinnedBuffer(max(total_visible * 2, 1024))
+    if world_size == 1:
+        def e2e_step():
+            ents, _ = world.cull(view, flags=0, out_entities=pinned.array)   # ovis_cull: view in, ids out
+            return len(ents)
+        d2h = 8 + 4 * total_visible
+    else:
+        pinned_t = torch.empty((world_size, sw.capacity + 1), dtype=torch.int32).pin_memory()
+
+        def e2e_step():
+            b, c = sw.cull(lib.view_planes(view))
+            with torch.cuda.stream(stream):
+                pinned_t.copy_(b, non_blocking=True)        # merged (segmented) list to the host
+            stream.synchronize()
+            return int(c.sum())
+        d2h = 4 * world_size * (sw.capacity + 1) + 4 * world_size
+    for _ in range(3):
+        e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    got = 0
+    for _ in range(args.steps):
+        got = e2e_step()
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    t = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
+    if world_size > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_s = float(t.item())
+    assert got == total_visible
+    sampler.stop_flag.set()
+
+    total_entities = n * world_size
+    value = total_entities * args.steps / (elapsed_ms * 1e-3)
+    local_visible = int(counts[rank])
+    alg_bytes = 24 * n + 4 * local_visible
+    k_ms = float(kernel_ms.mean())
+    achieved = alg_bytes / (k_ms * 1e-3) / 1e9
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world_size, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": elapsed_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "config": {"workload": workload_name(world_size, n), "entities_total": total_entities, "views": 1,
+                   "visible_total": total_visible,
+                   "parallelism": (f"entity shards x{world_size}, NCCL all-gather of visible lists" if world_size > 1 else "1 GPU"),
+                   "cache": "inputs larger than L2 (300 MB of bounds per GPU vs 126 MB L2); no flush needed"},
+        "cull_ms_per_frame": elapsed_ms / args.steps,
+        "roofline": {"bound": "hbm", "kernel": "ovis::cull_frustum_kernel<false>", "achieved": achieved, "peak": peak_gbs,
+                     "unit": "GB/s", "frac": achieved / peak_gbs, "traffic": None,
+                     "algorithmic_bytes_per_launch": alg_bytes, "kernel_ms_mean": k_ms, "kernel_ms_min": float(kernel_ms.min()),
+                     "peak_source": peak_src, "formula": "24 B/entity + 4 B/visible id (SURVEY.md 8(d))"},
+        "e2e": {"value": total_entities * args.steps / e2e_s, "unit": UNIT, "ms_per_step": e2e_s / args.steps * 1e3,
+                "h2d_bytes_per_step": 96, "d2h_bytes_per_step": d2h,
+                "what": "ovis_cull(view) -> visible ids in pinned host memory; the world is device-resident between frames, "
+                        "like the reference's SimpleRenderWorld is host-resident; per-frame inputs are the view (planes ride "
+                        "in the kernel parameters)"},
+        "gpu_launches": int(launches),
+        "clocks": clocks,
+    }
+
+    if rank == 0 and world_size == 1 and not args.skip_extras:
+        # parity of the benched result + CPU baseline on the same shard, same host
+        from oracle import pyoracle
+        oracle = pyoracle.load("best")
+        cores = host_cores()
+        times, exp = cpu_cull_timing(oracle, aabb, planes, cores, 5, 1)
+        got_ids = merged_list(blocks, counts)
+        line["parity"] = {"bit_exact_vs_oracle": bool(np.array_equal(got_ids, exp)), "oracle": oracle.name,
+                          "visible": int(len(exp))}
+        t1, _ = cpu_cull_timing(oracle, aabb, planes, 1, 2, 1)
+        line["cpu_baseline"] = {
+            "value": n / float(np.median(times)), "unit": UNIT, "cores": cores, "kind": oracle.name,
+            "sample": f"the whole benched shard ({n / 1e6:g}M entities, 1 frustum), 5 timed passes, flat AABB arrays, "
+                      f"{cores} host threads over contiguous index ranges",
+            "ms_per_frame": float(np.median(times)) * 1e3,
+            "one_thread_flat": {"tests_per_s": n / float(np.median(t1)), "ms_per_frame": float(np.median(t1)) * 1e3},
+            "as_shipped_std_list_1thread": as_shipped_timing(oracle, aabb[:1_000_000], view),
+        }
+        scratch = torch.zeros(128 * 1024 * 1024, dtype=torch.int32, device="cuda")
+
+        def masked():
+            sw.cull_local(planes, 1)
+
+        time_kernel_loop(torch, stream, masked, 3)
+        mk = time_kernel_loop(torch, stream, masked, 20)
+        vis_m = int(sw.block[0].item())
+        with torch.cuda.stream(stream):
+            line["also"] = {
+                "masked_cull_same_shard": {"kernel": "ovis::cull_frustum_kernel<true>", "kernel_ms_mean": float(mk.mean()),
+                                           "achieved_gbs": (24 * n + n / 8 + 4 * vis_m) / (float(mk.mean()) * 1e-3) / 1e9},
+                "config2_1M": config2_extra(torch, lib, stream, scratch, peak_gbs),
+            }
+        del scratch
+
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    world.close()
+    if world_size > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
+    ap.add_argument("--entities-per-gpu", type=int, default=SHARD_ENTITIES)
+    ap.add_argument("--skip-extras", action="store_true", help="only the headline numbers (no CPU baseline / also)")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world_size = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.impl == "reference":
+        run_reference(args, rank)
+        return
+    if world_size == 1 and args.gpus > 1:
+        raise SystemExit(f"bench.py --gpus {args.gpus}: launch with torchrun --nproc-per-node {args.gpus} (one rank per GPU)")
+    run_ours(args, rank, local_rank, world_size)
+
+
+if __name__ == "__main__":
+    main()

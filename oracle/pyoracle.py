@@ -206,6 +206,12 @@ class RefWorld:
             self.lib.oref_world_destroy(self.h)
             self.h = None
 
+    def abandon(self):
+        """Leak the world on purpose: destroying n entities one by one is O(n^2) in the reference."""
+        if self.h:
+            self.lib.oref_world_abandon(self.h)
+            self.h = None
+
     def __del__(self):
         self.close()
 

@@ -273,6 +273,14 @@ void oref_world_destroy(void *w) {
     delete rw;
 }
 
+/* Tearing a big world down entity by entity is O(n^2) in the reference (each ~RenderEntity does a
+ * std::list::remove scan, simple_render_world.cc:65-67). The baseline timer abandons its world instead. */
+void oref_world_abandon(void *w) {
+    RefWorld *rw = static_cast<RefWorld *>(w);
+    for (auto &e : rw->entities) e.release();
+    for (auto &l : rw->lights) l.release();
+}
+
 int64_t oref_world_add_entities(void *w, int64_t n, const float *t, const float *local_aabb, const uint32_t *flags) {
     RefWorld *rw = static_cast<RefWorld *>(w);
     int64_t first = (int64_t)rw->entities.size();
