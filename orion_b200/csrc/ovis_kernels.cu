@@ -195,197 +195,205 @@ void launch_extra_bounds(const uint32_t *entities, const uint32_t *nodes, int64_
 }
 
 // ------------------------------------------------------------------------------------------------
-// K3: one view over all entity slots with ORDER-PRESERVING compaction in a single pass.
+// K3: one view over all entity slots with ORDER-PRESERVING compaction, in two launches.
 //
-// Persistent CTAs take 1024-entity tiles from an atomic ticket (so a tile's predecessors are always
-// running or finished), test 4 entities per thread, rank survivors with a warp shuffle scan + a
-// block scan, and obtain the tile's global base with a decoupled look-back over 64-bit tile status
-// words {epoch, state, value}. Output order = slot order = insertion order, identical from run to
-// run (no atomics decide a position). The epoch tag makes stale words from the previous launch read as
-// "not ready", so the status array never needs clearing; the last CTA to leave resets the ticket.
+//   K3a cull_test_kernel     pure streaming, no barrier and no inter-CTA dependency: every WARP owns
+//                            "warp tiles" of 128 x GROUPS consecutive entities, tests 4 x GROUPS entities
+//                            per lane (six 128-bit loads per group, the next tile's loads issued before the
+//                            current tile's ranking), ranks survivors with shuffle scans and stores their ids
+//                            at the start of the tile's fixed slot in a staging array, plus one count per tile
+//                            and (integer atomicAdd, order-independent) one total per block of 256 tiles.
+//   K3b cull_gather_kernel   one CTA per block of 256 tiles: base = sum of the earlier block totals, exclusive
+//                            scan of its 256 counts, then moves the staged ids to their final, dense position.
+//
+// Output order = slot order = insertion order and is identical from run to run: positions come from sums
+// of counts only. An earlier single-launch version (decoupled look-back over tile status words) was limited
+// to ~2.1 TB/s by CTA-wide barrier stalls behind the look-back chain; see profiles/r01_cull_notes.md.
 // ------------------------------------------------------------------------------------------------
 
-constexpr uint32_t kStateAggregate = 1u, kStatePrefix = 2u;
+template <int GROUPS, bool MASKED>
+__global__ void __launch_bounds__(kCullThreads, 4 / GROUPS)
+cull_test_kernel(const __grid_constant__ CullArgs a) {
+    constexpr int WT = 128 * GROUPS;                       // entities per warp tile
+    const int lane = threadIdx.x & 31;
+    const int warps_total = gridDim.x * (kCullThreads / 32);
+    const int gwarp = blockIdx.x * (kCullThreads / 32) + (threadIdx.x >> 5);
+    const float4 *__restrict__ bounds = reinterpret_cast<const float4 *>(a.bounds);
+    const int64_t vstride = a.stride >> 2;                 // component stride in float4 units
 
-__device__ __forceinline__ uint64_t pack_status(uint32_t epoch, uint32_t state, uint32_t value) {
-    return ((uint64_t)((epoch << 2) | state) << 32) | value;
-}
+    // re-arm the block totals the NEXT launch will accumulate into (this launch uses the other set)
+    for (int i = blockIdx.x * kCullThreads + threadIdx.x; i < a.num_blocks; i += gridDim.x * kCullThreads)
+        a.block_totals_next[i] = 0u;
 
-__device__ __forceinline__ uint64_t load_status(const uint64_t *p) {
-    uint64_t v;
-    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-    return v;
-}
-
-__device__ __forceinline__ void store_status(uint64_t *p, uint64_t v) {
-    asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
-}
-
-// Called by all 32 lanes of warp 0. Returns the number of survivors in all earlier tiles.
-__device__ __forceinline__ uint32_t tile_exclusive_prefix(uint64_t *status, int tile, uint32_t aggregate, uint32_t epoch,
-                                                          int lane) {
-    if (tile == 0) {
-        if (lane == 0)
-            store_status(status, pack_status(epoch, kStatePrefix, aggregate));
-        return 0;
-    }
-    if (lane == 0)
-        store_status(status + tile, pack_status(epoch, kStateAggregate, aggregate));
-    uint32_t exclusive = 0;
-    int look = tile - 1;
-    while (true) {
-        int idx = look - lane;
-        uint32_t state = kStatePrefix, value = 0;      // tiles before tile 0: prefix 0
-        if (idx >= 0) {
-            uint64_t s = load_status(status + idx);
-            uint32_t hi = (uint32_t)(s >> 32);
-            state = ((hi >> 2) == epoch) ? (hi & 3u) : 0u;
-            value = (uint32_t)s;
+    float4 mnx[GROUPS], mny[GROUPS], mnz[GROUPS], mxx[GROUPS], mxy[GROUPS], mxz[GROUPS];
+    uint32_t mask_bits[GROUPS];
+    auto issue_loads = [&](int wt) {
+        if (wt >= a.num_tiles)
+            return;
+#pragma unroll
+        for (int g = 0; g < GROUPS; g++) {
+            const int64_t v = (int64_t)wt * (32 * GROUPS) + g * 32 + lane;     // float4 index: entities 4v .. 4v+3
+            mnx[g] = __ldg(bounds + 0 * vstride + v); mny[g] = __ldg(bounds + 1 * vstride + v); mnz[g] = __ldg(bounds + 2 * vstride + v);
+            mxx[g] = __ldg(bounds + 3 * vstride + v); mxy[g] = __ldg(bounds + 4 * vstride + v); mxz[g] = __ldg(bounds + 5 * vstride + v);
+            if (MASKED)
+                mask_bits[g] = __ldg(a.mask + (v >> 3));                       // the 4 bits of entity 4v sit at bit (4v & 31)
         }
-        uint32_t not_ready = __ballot_sync(0xffffffffu, state == 0u);
-        uint32_t prefixes = __ballot_sync(0xffffffffu, state == kStatePrefix);
-        // lanes [0, stop) are usable when none of them is "not ready"; stop at the first prefix (inclusive)
-        int first_prefix = prefixes ? (__ffs(prefixes) - 1) : 32;
-        int first_bad = not_ready ? (__ffs(not_ready) - 1) : 32;
-        if (first_bad < first_prefix && first_bad < 32) {
-            if (first_bad == 0)
-                continue;                                // nothing usable yet: poll again
-            // consume the ready aggregates in front of the first unready tile, then poll from there
-            uint32_t part = (lane < first_bad) ? value : 0u;
-            exclusive += __reduce_add_sync(0xffffffffu, part);
-            look -= first_bad;
-            continue;
+    };
+
+    int wt = gwarp;
+    issue_loads(wt);
+    for (; wt < a.num_tiles; wt += warps_total) {
+        uint32_t keep[GROUPS];
+#pragma unroll
+        for (int g = 0; g < GROUPS; g++) {
+            const int64_t e0 = ((int64_t)wt * (32 * GROUPS) + g * 32 + lane) << 2;   // entities e0 .. e0+3
+            uint32_t k = 0xfu;                                                // bit j: entity e0 + j still inside
+            if (MASKED)
+                k = (mask_bits[g] >> (e0 & 31)) & 0xfu;
+            if (e0 + 3 >= a.n) {                                              // ragged tail of the last tile
+                int64_t valid = a.n - e0;
+                k &= valid <= 0 ? 0u : ((1u << valid) - 1u);
+            }
+#pragma unroll
+            for (int p = 0; p < 6; p++) {                                     // Left Right Top Bottom Near Far
+                const float nx = a.planes[p].x, ny = a.planes[p].y, nz = a.planes[p].z, d = a.planes[p].w;
+                if (outside_plane(nx, ny, nz, d, mnx[g].x, mny[g].x, mnz[g].x, mxx[g].x, mxy[g].x, mxz[g].x)) k &= ~1u;
+                if (outside_plane(nx, ny, nz, d, mnx[g].y, mny[g].y, mnz[g].y, mxx[g].y, mxy[g].y, mxz[g].y)) k &= ~2u;
+                if (outside_plane(nx, ny, nz, d, mnx[g].z, mny[g].z, mnz[g].z, mxx[g].z, mxy[g].z, mxz[g].z)) k &= ~4u;
+                if (outside_plane(nx, ny, nz, d, mnx[g].w, mny[g].w, mnz[g].w, mxx[g].w, mxy[g].w, mxz[g].w)) k &= ~8u;
+            }
+            keep[g] = k;
         }
-        int take = first_prefix < 32 ? first_prefix + 1 : 32;
-        uint32_t part = (lane < take) ? value : 0u;
-        exclusive += __reduce_add_sync(0xffffffffu, part);
-        if (first_prefix < 32)
-            break;
-        look -= 32;
+        issue_loads(wt + warps_total);                                        // this tile's registers are dead now
+
+        // rank inside the warp tile: per group an inclusive shuffle scan, groups in index order
+        uint32_t base = 0;
+        uint32_t *slot = a.staging + (int64_t)wt * WT;
+#pragma unroll
+        for (int g = 0; g < GROUPS; g++) {
+            uint32_t sum = __popc(keep[g]);
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                uint32_t up = __shfl_up_sync(0xffffffffu, sum, o);
+                if (lane >= o)
+                    sum += up;
+            }
+            if (keep[g]) {
+                uint32_t rank = base + sum - __popc(keep[g]);
+                const uint32_t e0 = (uint32_t)(((int64_t)wt * (32 * GROUPS) + g * 32 + lane) << 2) + a.id_base;
+#pragma unroll
+                for (int j = 0; j < 4; j++)
+                    if (keep[g] & (1u << j))
+                        slot[rank++] = e0 + j;
+            }
+            base += __shfl_sync(0xffffffffu, sum, 31);
+        }
+        if (lane == 0) {
+            a.tile_counts[wt] = base;
+            if (base)
+                atomicAdd(a.block_totals + (wt >> 8), base);
+        }
     }
-    if (lane == 0)
-        store_status(status + tile, pack_status(epoch, kStatePrefix, exclusive + aggregate));
-    return exclusive;
 }
 
-template <bool MASKED>
-__global__ void __launch_bounds__(kCullThreads)
-cull_frustum_kernel(const __grid_constant__ CullArgs a) {
-    __shared__ uint32_t s_warp_total[kCullThreads / 32];
-    __shared__ uint32_t s_tile_base;
-    __shared__ int s_tile;
-
+__global__ void __launch_bounds__(256)
+cull_gather_kernel(const __grid_constant__ GatherArgs a) {
+    __shared__ uint32_t s_scan[256];       // exclusive scan of this block's tile counts
+    __shared__ uint32_t s_warp[8];
+    __shared__ uint32_t s_base, s_sum;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int num_tiles = a.num_tiles;
-    const float4 *__restrict__ bx0 = reinterpret_cast<const float4 *>(a.bounds);
-    const int64_t vstride = a.stride >> 2;            // stride in float4 units
+    const int block = blockIdx.x;
 
-    // output base of this view inside a CSR buffer (0 for a stand-alone list)
-    const long long out_base = a.d_base ? *a.d_base : 0ll;
-
-    while (true) {
-        if (tid == 0)
-            s_tile = (int)atomicAdd(a.ticket, 1u);
-        __syncthreads();
-        const int tile = s_tile;
-        if (tile >= num_tiles)
-            break;
-
-        const int64_t v = (int64_t)tile * kCullThreads + tid;      // float4 index: entities 4v .. 4v+3
-        const int64_t e0 = v << 2;
-        const float4 mnx = __ldg(bx0 + 0 * vstride + v), mny = __ldg(bx0 + 1 * vstride + v), mnz = __ldg(bx0 + 2 * vstride + v);
-        const float4 mxx = __ldg(bx0 + 3 * vstride + v), mxy = __ldg(bx0 + 4 * vstride + v), mxz = __ldg(bx0 + 5 * vstride + v);
-
-        uint32_t keep = 0xfu;                                        // bit j: entity e0 + j still inside
-        if (MASKED)
-            keep = (__ldg(a.mask + (e0 >> 5)) >> (e0 & 31)) & 0xfu;
-        if (e0 + 3 >= a.n) {                                         // ragged tail of the last tile
-            int valid = (int)(a.n - e0);
-            keep &= valid <= 0 ? 0u : ((1u << valid) - 1u);
-        }
-#pragma unroll
-        for (int p = 0; p < 6; p++) {                                // Left Right Top Bottom Near Far
-            const float nx = a.planes[p].x, ny = a.planes[p].y, nz = a.planes[p].z, d = a.planes[p].w;
-            if (outside_plane(nx, ny, nz, d, mnx.x, mny.x, mnz.x, mxx.x, mxy.x, mxz.x)) keep &= ~1u;
-            if (outside_plane(nx, ny, nz, d, mnx.y, mny.y, mnz.y, mxx.y, mxy.y, mxz.y)) keep &= ~2u;
-            if (outside_plane(nx, ny, nz, d, mnx.z, mny.z, mnz.z, mxx.z, mxy.z, mxz.z)) keep &= ~4u;
-            if (outside_plane(nx, ny, nz, d, mnx.w, mny.w, mnz.w, mxx.w, mxy.w, mxz.w)) keep &= ~8u;
-        }
-
-        // rank inside the warp: inclusive shuffle scan of the per-thread survivor counts
-        const uint32_t mine = __popc(keep);
-        uint32_t incl = mine;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            uint32_t up = __shfl_up_sync(0xffffffffu, incl, o);
-            if (lane >= o)
-                incl += up;
-        }
-        if (lane == 31)
-            s_warp_total[warp] = incl;
-        __syncthreads();
-
-        if (warp == 0) {
-            uint32_t wt = (lane < kCullThreads / 32) ? s_warp_total[lane] : 0u;
-            uint32_t aggregate = __reduce_add_sync(0xffffffffu, wt);
-            uint32_t excl = tile_exclusive_prefix(a.status, tile, aggregate, a.epoch, lane);
-            if (lane == 0) {
-                s_tile_base = excl;
-                if (tile == num_tiles - 1) {                         // the last tile knows the total
-                    uint32_t total = excl + aggregate;
-                    if (a.d_count) *a.d_count = total;
-                    if (a.d_next) *a.d_next = out_base + (long long)total;
-                }
-            }
-        }
-        __syncthreads();
-
-        uint32_t rank = s_tile_base + incl - mine;
-#pragma unroll
-        for (int w = 0; w < kCullThreads / 32; w++)
-            if (w < warp)
-                rank += s_warp_total[w];
-        if (keep) {
-            long long pos = out_base + (long long)rank;
-#pragma unroll
-            for (int j = 0; j < 4; j++) {
-                if (keep & (1u << j)) {
-                    if (pos < a.capacity)
-                        a.out[pos] = (uint32_t)(e0 + j) + a.id_base;
-                    pos++;
-                }
-            }
-        }
-        // No trailing barrier: s_tile is rewritten by thread 0 only after every thread has passed the two
-        // barriers above (so has read it), and s_warp_total / s_tile_base are rewritten only after the
-        // next iteration's first barrier.
-    }
-
-    // the last CTA out re-arms the ticket for the next launch
+    // base = survivors in all earlier blocks
+    uint32_t part = 0;
+    for (int i = tid; i < block; i += 256)
+        part += a.block_totals[i];
+    part = __reduce_add_sync(0xffffffffu, part);
+    if (lane == 0)
+        s_warp[warp] = part;
+    __syncthreads();
     if (tid == 0) {
-        __threadfence();
-        unsigned int done = atomicAdd(a.done, 1u);
-        if (done == gridDim.x - 1) {
-            *a.ticket = 0u;
-            *a.done = 0u;
-            __threadfence();
+        uint32_t b = 0;
+#pragma unroll
+        for (int w = 0; w < 8; w++)
+            b += s_warp[w];
+        s_base = b;
+    }
+    __syncthreads();
+
+    // exclusive scan of the block's 256 tile counts
+    const int tile = block * 256 + tid;
+    const uint32_t c = tile < a.num_tiles ? a.tile_counts[tile] : 0u;
+    uint32_t incl = c;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        uint32_t up = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o)
+            incl += up;
+    }
+    if (lane == 31)
+        s_warp[warp] = incl;
+    __syncthreads();
+    uint32_t before = 0;
+#pragma unroll
+    for (int w = 0; w < 8; w++)
+        if (w < warp)
+            before += s_warp[w];
+    s_scan[tid] = before + incl - c;
+    if (tid == 255)
+        s_sum = before + incl;
+    __syncthreads();
+
+    const uint32_t total = s_sum;
+    const long long out_base = a.d_base ? *a.d_base : 0ll;
+    const long long dst0 = out_base + (long long)s_base;
+    if (block == gridDim.x - 1 && tid == 0) {                  // the last block knows the grand total
+        uint32_t grand = s_base + total;
+        if (a.d_count) *a.d_count = grand;
+        if (a.d_next) *a.d_next = out_base + (long long)grand;
+    }
+    // position k of this block's output comes from the tile t with s_scan[t] <= k < s_scan[t+1]
+    for (uint32_t k = tid; k < total; k += 256) {
+        int lo = 0, hi = 255;
+        while (lo < hi) {                                      // last t with s_scan[t] <= k
+            int mid = (lo + hi + 1) >> 1;
+            if (s_scan[mid] <= k) lo = mid; else hi = mid - 1;
         }
+        const int64_t src = (int64_t)(block * 256 + lo) * a.tile_entities + (k - s_scan[lo]);
+        if (dst0 + k < a.capacity)
+            a.out[dst0 + k] = a.staging[src];
     }
 }
 
-void launch_cull_frustum(const CullArgs &a, bool masked, int grid, cudaStream_t s) {
-    if (masked)
-        cull_frustum_kernel<true><<<grid, kCullThreads, 0, s>>>(a);
-    else
-        cull_frustum_kernel<false><<<grid, kCullThreads, 0, s>>>(a);
+// Launch shapes selectable at run time (OVIS_CULL_VARIANT, tuning only). Variant 0 is the default.
+static const CullVariant kVariants[] = { { 2 }, { 1 }, { 4 } };
+
+int cull_num_variants() { return (int)(sizeof(kVariants) / sizeof(kVariants[0])); }
+CullVariant cull_variant(int v) { return kVariants[v]; }
+
+template <typename F>
+static void with_variant(int variant, bool masked, F &&f) {
+    switch (kVariants[variant].groups) {
+    case 1: if (masked) f(cull_test_kernel<1, true>); else f(cull_test_kernel<1, false>); break;
+    case 2: if (masked) f(cull_test_kernel<2, true>); else f(cull_test_kernel<2, false>); break;
+    case 4: if (masked) f(cull_test_kernel<4, true>); else f(cull_test_kernel<4, false>); break;
+    }
 }
 
-int cull_frustum_max_blocks_per_sm(bool masked) {
+void launch_cull_test(const CullArgs &a, bool masked, int variant, int grid, cudaStream_t s) {
+    with_variant(variant, masked, [&](auto kernel) { kernel<<<grid, kCullThreads, 0, s>>>(a); });
+}
+
+void launch_cull_gather(const GatherArgs &a, cudaStream_t s) {
+    int blocks = (a.num_tiles + 255) / 256;
+    cull_gather_kernel<<<blocks, 256, 0, s>>>(a);
+}
+
+int cull_test_max_blocks_per_sm(bool masked, int variant) {
     int blocks = 0;
-    if (masked)
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks, cull_frustum_kernel<true>, kCullThreads, 0);
-    else
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks, cull_frustum_kernel<false>, kCullThreads, 0);
+    with_variant(variant, masked, [&](auto kernel) {
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks, kernel, kCullThreads, 0);
+    });
     return blocks;
 }
 

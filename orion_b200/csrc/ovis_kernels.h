@@ -7,8 +7,13 @@
 namespace ovis {
 
 constexpr uint32_t kNone = 0xffffffffu;
-constexpr int kCullThreads = 256;                       // threads per CTA of the cull kernel
-constexpr int kCullTile = kCullThreads * 4;             // entities per tile (one float4 group per thread)
+constexpr int kCullThreads = 256;                       // threads per CTA of the cull test kernel
+constexpr int kCullTile = 1024;                         // storage padding: a multiple of every warp-tile size
+
+struct CullVariant {
+    int groups;                  // float4 groups (4 consecutive entities each) per lane
+    int tile() const { return 128 * groups; }   // entities per warp tile
+};
 
 // SoA storage convention: component k of item i lives at base[k * stride + i]; stride is a multiple of
 // kCullTile so every component array is 4 KiB aligned and float4-loadable.
@@ -26,23 +31,32 @@ struct LevelArgs {
     int64_t estride;
 };
 
-struct CullArgs {
+struct CullArgs {                 // K3a
     float4 planes[6];            // normal xyz, distance
     const float *bounds;         // world AABBs, 6 x stride
     int64_t stride;
     int64_t n;                   // entity slots
-    int num_tiles;
+    int num_tiles;               // warp tiles: ceil(n / tile of the launched variant)
+    int num_blocks;              // blocks of 256 warp tiles
     const uint32_t *mask;        // 1 bit per slot (alive [& caster]); only read by the MASKED variant
+    uint32_t *staging;           // scratch: num_tiles x tile ids, each tile's survivors at the start of its slot
+    uint32_t *tile_counts;       // scratch: survivors per warp tile
+    uint32_t *block_totals;      // scratch: survivors per block of 256 tiles (zero on entry)
+    uint32_t *block_totals_next; // scratch: the set the next launch accumulates into; zeroed here
+    uint32_t id_base;            // added to every emitted slot id (global id of a shard's first entity)
+};
+
+struct GatherArgs {               // K3b
+    const uint32_t *staging;
+    const uint32_t *tile_counts;
+    const uint32_t *block_totals;
+    int num_tiles;
+    int tile_entities;
     uint32_t *out;               // visible slot ids, ascending
     long long capacity;          // writable entries of out
     const long long *d_base;     // optional: start offset inside out (CSR chaining), device memory
     long long *d_next;           // optional: receives base + count
     uint32_t *d_count;           // optional: receives count
-    uint64_t *status;            // num_tiles tile-status words (scratch)
-    unsigned int *ticket;        // tile ticket (scratch, zero between launches)
-    unsigned int *done;          // CTA exit counter (scratch, zero between launches)
-    uint32_t epoch;              // launch tag, 1 .. 2^30-1, never repeated without clearing status
-    uint32_t id_base;            // added to every emitted slot id (global id of a shard's first entity)
 };
 
 enum : uint32_t { kLightNever = 0, kLightAlways = 1, kLightSphere = 2, kLightBox = 3 };
@@ -72,8 +86,11 @@ void launch_identity_bounds(const uint32_t *ids, uint32_t first, int64_t n, cons
 void launch_update_level(const LevelArgs &a, cudaStream_t s);
 void launch_extra_bounds(const uint32_t *entities, const uint32_t *nodes, int64_t n, const float *world_trs,
                          int64_t nstride, const float *local, float *world, int64_t estride, cudaStream_t s);
-void launch_cull_frustum(const CullArgs &a, bool masked, int grid, cudaStream_t s);
-int cull_frustum_max_blocks_per_sm(bool masked);
+int cull_num_variants();
+CullVariant cull_variant(int v);
+void launch_cull_test(const CullArgs &a, bool masked, int variant, int grid, cudaStream_t s);
+void launch_cull_gather(const GatherArgs &a, cudaStream_t s);
+int cull_test_max_blocks_per_sm(bool masked, int variant);
 void launch_empty_result(const long long *d_base, long long *d_next, uint32_t *d_count, cudaStream_t s);
 void launch_cull_lights(const LightCullArgs &a, cudaStream_t s);
 

@@ -10,6 +10,7 @@
 #include <algorithm>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 #include <string>
@@ -63,6 +64,7 @@ struct OvisWorld {
     int device = 0;
     cudaStream_t stream = nullptr;
     int num_sms = 0;
+    int variant = 0;                      // cull launch shape (ovis_kernels.cu kVariants)
     int blocks_per_sm[2] = { 0, 0 };      // cull kernel occupancy: [unmasked, masked]
     int64_t launches = 0;
     uint32_t id_base = 0;                 // global id of slot 0 (sharded worlds)
@@ -105,10 +107,11 @@ struct OvisWorld {
     bool lights_dirty = false;
 
     // ---- cull scratch and results
-    uint64_t *d_status = nullptr;         // one word per tile
-    int64_t cap_tiles = 0;
-    unsigned int *d_ticket = nullptr;     // [0] ticket, [1] done
-    uint32_t epoch = 0;
+    uint32_t *d_staging = nullptr;        // cap_ent ids: per-warp-tile survivor lists before the gather
+    uint32_t *d_tile_counts = nullptr;    // cap_ent / 128 counts
+    uint32_t *d_block_totals = nullptr;   // 2 x cap_blocks totals, used alternately (the idle set is zero)
+    int64_t cap_blocks = 0;
+    int totals_parity = 0;
     uint32_t *d_result = nullptr;         // cap_ent visible ids
     uint32_t *d_counts = nullptr;         // [0] entities, [1] lights
     uint32_t *h_counts = nullptr;         // pinned mirror
@@ -193,12 +196,12 @@ int reserve_entities(OvisWorld *w, int64_t want) {
     OVIS_TRY(grow(w->d_alive_bits, w->cap_ent / 32, cap / 32, w->stream));
     OVIS_TRY(grow(w->d_caster_bits, w->cap_ent / 32, cap / 32, w->stream));
     OVIS_TRY(grow(w->d_result, 0, cap, w->stream, false));
-    int64_t tiles = cap / kCullTile;
-    if (tiles > w->cap_tiles) {
-        OVIS_TRY(grow(w->d_status, 0, tiles, w->stream));   // zeroed: epoch 0 is never used by a launch
-        w->cap_tiles = tiles;
-        w->epoch = 0;
-    }
+    OVIS_TRY(grow(w->d_staging, 0, cap, w->stream, false));
+    OVIS_TRY(grow(w->d_tile_counts, 0, cap / 128, w->stream, false));
+    int64_t blocks = cap / 128 / 256 + 1;
+    OVIS_TRY(grow(w->d_block_totals, 0, 2 * blocks, w->stream));   // both sets start zeroed
+    w->cap_blocks = blocks;
+    w->totals_parity = 0;
     w->cap_ent = cap;
     w->h_alive.resize((size_t)(cap / 32), 0u);
     w->h_caster_raw.resize((size_t)(cap / 32), 0u);
@@ -416,31 +419,38 @@ int enqueue_cull(OvisWorld *w, const float planes[24], uint32_t require, uint32_
         return OVIS_OK;
     }
     OVIS_TRY(upload_masks(w));
-    if (++w->epoch >= (1u << 30)) {                     // tag space exhausted: clear and restart
-        OVIS_CUDA(cudaMemsetAsync(w->d_status, 0, sizeof(uint64_t) * (size_t)w->cap_tiles, w->stream));
-        w->epoch = 1;
-    }
+    const int tile = ovis::cull_variant(w->variant).tile();
+    const bool masked = require != 0 || w->any_dead;
     ovis::CullArgs a;
     load_planes(a.planes, planes);
     a.bounds = w->d_world;
     a.stride = w->cap_ent;
     a.n = w->n_ent;
-    a.num_tiles = (int)((w->n_ent + kCullTile - 1) / kCullTile);
-    const bool masked = require != 0 || w->any_dead;
+    a.num_tiles = (int)((w->n_ent + tile - 1) / tile);
+    a.num_blocks = (a.num_tiles + 255) / 256;
     a.mask = require ? w->d_caster_bits : w->d_alive_bits;
-    a.out = out;
-    a.capacity = capacity;
-    a.d_base = d_base;
-    a.d_next = d_next;
-    a.d_count = d_count;
-    a.status = w->d_status;
-    a.ticket = w->d_ticket;
-    a.done = w->d_ticket + 1;
-    a.epoch = w->epoch;
+    a.staging = w->d_staging;
+    a.tile_counts = w->d_tile_counts;
+    a.block_totals = w->d_block_totals + w->totals_parity * w->cap_blocks;
+    a.block_totals_next = w->d_block_totals + (w->totals_parity ^ 1) * w->cap_blocks;
     a.id_base = w->id_base;
-    int grid = std::min(a.num_tiles, w->num_sms * w->blocks_per_sm[masked ? 1 : 0]);
-    ovis::launch_cull_frustum(a, masked, grid, w->stream);
-    w->launches++;
+    const int warps_needed_blocks = (a.num_tiles + ovis::kCullThreads / 32 - 1) / (ovis::kCullThreads / 32);
+    int grid = std::min(warps_needed_blocks, w->num_sms * w->blocks_per_sm[masked ? 1 : 0]);
+    ovis::launch_cull_test(a, masked, w->variant, grid, w->stream);
+    ovis::GatherArgs g;
+    g.staging = w->d_staging;
+    g.tile_counts = w->d_tile_counts;
+    g.block_totals = a.block_totals;
+    g.num_tiles = a.num_tiles;
+    g.tile_entities = tile;
+    g.out = out;
+    g.capacity = capacity;
+    g.d_base = d_base;
+    g.d_next = d_next;
+    g.d_count = d_count;
+    ovis::launch_cull_gather(g, w->stream);
+    w->totals_parity ^= 1;
+    w->launches += 2;
     OVIS_CUDA(cudaGetLastError());
     return OVIS_OK;
 }
@@ -566,10 +576,13 @@ int ovis_world_create(int device, OvisWorld **out_world) {
     cudaDeviceProp prop;
     OVIS_CUDA(cudaGetDeviceProperties(&prop, device));
     w->num_sms = prop.multiProcessorCount;
-    w->blocks_per_sm[0] = std::max(1, ovis::cull_frustum_max_blocks_per_sm(false));
-    w->blocks_per_sm[1] = std::max(1, ovis::cull_frustum_max_blocks_per_sm(true));
-    OVIS_CUDA(cudaMalloc(&w->d_ticket, 2 * sizeof(unsigned int)));
-    OVIS_CUDA(cudaMemset(w->d_ticket, 0, 2 * sizeof(unsigned int)));
+    if (const char *v = getenv("OVIS_CULL_VARIANT")) {   // tuning knob, not part of the ABI
+        int k = atoi(v);
+        if (k >= 0 && k < ovis::cull_num_variants())
+            w->variant = k;
+    }
+    w->blocks_per_sm[0] = std::max(1, ovis::cull_test_max_blocks_per_sm(false, w->variant));
+    w->blocks_per_sm[1] = std::max(1, ovis::cull_test_max_blocks_per_sm(true, w->variant));
     OVIS_CUDA(cudaMalloc(&w->d_counts, 2 * sizeof(uint32_t)));
     OVIS_CUDA(cudaMemset(w->d_counts, 0, 2 * sizeof(uint32_t)));
     OVIS_CUDA(cudaMallocHost(&w->h_counts, 2 * sizeof(uint32_t)));
@@ -584,7 +597,7 @@ int ovis_world_destroy(OvisWorld *w) {
     cudaStreamSynchronize(w->stream);
     void *bufs[] = { w->d_local, w->d_world, w->d_alive_bits, w->d_caster_bits, w->d_parent, w->d_local_trs, w->d_world_trs,
                      w->d_node_entity, w->d_extra_entity, w->d_extra_node, w->d_level_lists, w->d_lights, w->d_light_out,
-                     w->d_status, w->d_ticket, w->d_result, w->d_counts, w->d_csr_entities, w->d_csr_offsets,
+                     w->d_staging, w->d_tile_counts, w->d_block_totals, w->d_result, w->d_counts, w->d_csr_entities, w->d_csr_offsets,
                      w->d_stage[0], w->d_stage[1] };
     for (void *b : bufs)
         if (b)
