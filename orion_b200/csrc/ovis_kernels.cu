@@ -202,9 +202,9 @@ void launch_extra_bounds(const uint32_t *entities, const uint32_t *nodes, int64_
 //                            per lane (six 128-bit loads per group, the next tile's loads issued before the
 //                            current tile's ranking), ranks survivors with shuffle scans and stores their ids
 //                            at the start of the tile's fixed slot in a staging array, plus one count per tile
-//                            and (integer atomicAdd, order-independent) one total per block of 256 tiles.
-//   K3b cull_gather_kernel   one CTA per block of 256 tiles: base = sum of the earlier block totals, exclusive
-//                            scan of its 256 counts, then moves the staged ids to their final, dense position.
+//                            and (integer atomicAdd, order-independent) one total per block of 64 tiles.
+//   K3b cull_gather_kernel   one CTA per block of 64 tiles: base = sum of the earlier block totals, exclusive
+//                            scan of its 64 counts, then moves the staged ids to their final, dense position.
 //
 // Output order = slot order = insertion order and is identical from run to run: positions come from sums
 // of counts only. An earlier single-launch version (decoupled look-back over tile status words) was limited
@@ -291,16 +291,16 @@ cull_test_kernel(const __grid_constant__ CullArgs a) {
         if (lane == 0) {
             a.tile_counts[wt] = base;
             if (base)
-                atomicAdd(a.block_totals + (wt >> 8), base);
+                atomicAdd(a.block_totals + wt / kGatherTiles, base);
         }
     }
 }
 
 __global__ void __launch_bounds__(256)
 cull_gather_kernel(const __grid_constant__ GatherArgs a) {
-    __shared__ uint32_t s_scan[256];       // exclusive scan of this block's tile counts
+    __shared__ uint32_t s_scan[kGatherTiles + 1];   // exclusive scan of this block's tile counts, then the block sum
     __shared__ uint32_t s_warp[8];
-    __shared__ uint32_t s_base, s_sum;
+    __shared__ uint32_t s_base;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int block = blockIdx.x;
 
@@ -311,7 +311,27 @@ cull_gather_kernel(const __grid_constant__ GatherArgs a) {
     part = __reduce_add_sync(0xffffffffu, part);
     if (lane == 0)
         s_warp[warp] = part;
+
+    // exclusive scan of the block's tile counts (kGatherTiles = 64: two warps)
+    uint32_t c = 0, incl = 0;
+    if (tid < kGatherTiles) {
+        const int tile = block * kGatherTiles + tid;
+        c = tile < a.num_tiles ? a.tile_counts[tile] : 0u;
+        incl = c;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            uint32_t up = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o)
+                incl += up;
+        }
+        if (tid == 31)
+            s_scan[kGatherTiles] = incl;                    // total of the first warp, fixed up below
+    }
     __syncthreads();
+    if (tid < kGatherTiles) {
+        const uint32_t first = s_scan[kGatherTiles];
+        s_scan[tid] = (warp ? first : 0u) + incl - c;
+    }
     if (tid == 0) {
         uint32_t b = 0;
 #pragma unroll
@@ -320,48 +340,41 @@ cull_gather_kernel(const __grid_constant__ GatherArgs a) {
         s_base = b;
     }
     __syncthreads();
-
-    // exclusive scan of the block's 256 tile counts
-    const int tile = block * 256 + tid;
-    const uint32_t c = tile < a.num_tiles ? a.tile_counts[tile] : 0u;
-    uint32_t incl = c;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        uint32_t up = __shfl_up_sync(0xffffffffu, incl, o);
-        if (lane >= o)
-            incl += up;
-    }
-    if (lane == 31)
-        s_warp[warp] = incl;
-    __syncthreads();
-    uint32_t before = 0;
-#pragma unroll
-    for (int w = 0; w < 8; w++)
-        if (w < warp)
-            before += s_warp[w];
-    s_scan[tid] = before + incl - c;
-    if (tid == 255)
-        s_sum = before + incl;
+    if (tid == kGatherTiles - 1)
+        s_scan[kGatherTiles] = s_scan[tid] + c;             // block sum
     __syncthreads();
 
-    const uint32_t total = s_sum;
+    const uint32_t total = s_scan[kGatherTiles];
     const long long out_base = a.d_base ? *a.d_base : 0ll;
     const long long dst0 = out_base + (long long)s_base;
-    if (block == gridDim.x - 1 && tid == 0) {                  // the last block knows the grand total
+    if (block == gridDim.x - 1 && tid == 0) {               // the last block knows the grand total
         uint32_t grand = s_base + total;
         if (a.d_count) *a.d_count = grand;
         if (a.d_next) *a.d_next = out_base + (long long)grand;
     }
-    // position k of this block's output comes from the tile t with s_scan[t] <= k < s_scan[t+1]
-    for (uint32_t k = tid; k < total; k += 256) {
-        int lo = 0, hi = 255;
-        while (lo < hi) {                                      // last t with s_scan[t] <= k
-            int mid = (lo + hi + 1) >> 1;
-            if (s_scan[mid] <= k) lo = mid; else hi = mid - 1;
+    // output position k of this block comes from the tile t with s_scan[t] <= k < s_scan[t+1];
+    // four independent positions per pass keep several staging loads in flight per thread
+    const int64_t tile0 = (int64_t)block * kGatherTiles;
+    for (uint32_t k0 = tid; k0 < total; k0 += 4 * 256) {
+        uint32_t val[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const uint32_t k = k0 + u * 256;
+            if (k < total) {
+                int lo = 0;
+#pragma unroll
+                for (int step = kGatherTiles / 2; step > 0; step >>= 1)      // last t with s_scan[t] <= k
+                    if (s_scan[lo + step] <= k)
+                        lo += step;
+                val[u] = a.staging[(tile0 + lo) * a.tile_entities + (k - s_scan[lo])];
+            }
         }
-        const int64_t src = (int64_t)(block * 256 + lo) * a.tile_entities + (k - s_scan[lo]);
-        if (dst0 + k < a.capacity)
-            a.out[dst0 + k] = a.staging[src];
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const uint32_t k = k0 + u * 256;
+            if (k < total && dst0 + k < a.capacity)
+                a.out[dst0 + k] = val[u];
+        }
     }
 }
 
@@ -385,7 +398,7 @@ void launch_cull_test(const CullArgs &a, bool masked, int variant, int grid, cud
 }
 
 void launch_cull_gather(const GatherArgs &a, cudaStream_t s) {
-    int blocks = (a.num_tiles + 255) / 256;
+    int blocks = (a.num_tiles + kGatherTiles - 1) / kGatherTiles;
     cull_gather_kernel<<<blocks, 256, 0, s>>>(a);
 }
 

@@ -8,6 +8,7 @@ namespace ovis {
 
 constexpr uint32_t kNone = 0xffffffffu;
 constexpr int kCullThreads = 256;                       // threads per CTA of the cull test kernel
+constexpr int kGatherTiles = 64;                        // warp tiles per block of the gather kernel
 constexpr int kCullTile = 1024;                         // storage padding: a multiple of every warp-tile size
 
 struct CullVariant {
@@ -37,11 +38,11 @@ struct CullArgs {                 // K3a
     int64_t stride;
     int64_t n;                   // entity slots
     int num_tiles;               // warp tiles: ceil(n / tile of the launched variant)
-    int num_blocks;              // blocks of 256 warp tiles
+    int num_blocks;              // blocks of kGatherTiles warp tiles
     const uint32_t *mask;        // 1 bit per slot (alive [& caster]); only read by the MASKED variant
     uint32_t *staging;           // scratch: num_tiles x tile ids, each tile's survivors at the start of its slot
     uint32_t *tile_counts;       // scratch: survivors per warp tile
-    uint32_t *block_totals;      // scratch: survivors per block of 256 tiles (zero on entry)
+    uint32_t *block_totals;      // scratch: survivors per block of kGatherTiles tiles (zero on entry)
     uint32_t *block_totals_next; // scratch: the set the next launch accumulates into; zeroed here
     uint32_t id_base;            // added to every emitted slot id (global id of a shard's first entity)
 };

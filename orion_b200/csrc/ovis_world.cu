@@ -64,8 +64,8 @@ struct OvisWorld {
     int device = 0;
     cudaStream_t stream = nullptr;
     int num_sms = 0;
-    int variant = 0;                      // cull launch shape (ovis_kernels.cu kVariants)
-    int blocks_per_sm[2] = { 0, 0 };      // cull kernel occupancy: [unmasked, masked]
+    int forced_variant = -1;              // OVIS_CULL_VARIANT (tuning); -1 = pick by size
+    int blocks_per_sm[8][2] = {};         // cull test kernel occupancy per variant: [unmasked, masked]
     int64_t launches = 0;
     uint32_t id_base = 0;                 // global id of slot 0 (sharded worlds)
 
@@ -198,7 +198,7 @@ int reserve_entities(OvisWorld *w, int64_t want) {
     OVIS_TRY(grow(w->d_result, 0, cap, w->stream, false));
     OVIS_TRY(grow(w->d_staging, 0, cap, w->stream, false));
     OVIS_TRY(grow(w->d_tile_counts, 0, cap / 128, w->stream, false));
-    int64_t blocks = cap / 128 / 256 + 1;
+    int64_t blocks = cap / 128 / ovis::kGatherTiles + 1;
     OVIS_TRY(grow(w->d_block_totals, 0, 2 * blocks, w->stream));   // both sets start zeroed
     w->cap_blocks = blocks;
     w->totals_parity = 0;
@@ -419,7 +419,9 @@ int enqueue_cull(OvisWorld *w, const float planes[24], uint32_t require, uint32_
         return OVIS_OK;
     }
     OVIS_TRY(upload_masks(w));
-    const int tile = ovis::cull_variant(w->variant).tile();
+    // small worlds are latency-bound: smaller warp tiles spread them over more warps
+    const int variant = w->forced_variant >= 0 ? w->forced_variant : (w->n_ent < (4 << 20) ? 1 : 0);
+    const int tile = ovis::cull_variant(variant).tile();
     const bool masked = require != 0 || w->any_dead;
     ovis::CullArgs a;
     load_planes(a.planes, planes);
@@ -427,7 +429,7 @@ int enqueue_cull(OvisWorld *w, const float planes[24], uint32_t require, uint32_
     a.stride = w->cap_ent;
     a.n = w->n_ent;
     a.num_tiles = (int)((w->n_ent + tile - 1) / tile);
-    a.num_blocks = (a.num_tiles + 255) / 256;
+    a.num_blocks = (a.num_tiles + ovis::kGatherTiles - 1) / ovis::kGatherTiles;
     a.mask = require ? w->d_caster_bits : w->d_alive_bits;
     a.staging = w->d_staging;
     a.tile_counts = w->d_tile_counts;
@@ -435,8 +437,8 @@ int enqueue_cull(OvisWorld *w, const float planes[24], uint32_t require, uint32_
     a.block_totals_next = w->d_block_totals + (w->totals_parity ^ 1) * w->cap_blocks;
     a.id_base = w->id_base;
     const int warps_needed_blocks = (a.num_tiles + ovis::kCullThreads / 32 - 1) / (ovis::kCullThreads / 32);
-    int grid = std::min(warps_needed_blocks, w->num_sms * w->blocks_per_sm[masked ? 1 : 0]);
-    ovis::launch_cull_test(a, masked, w->variant, grid, w->stream);
+    int grid = std::min(warps_needed_blocks, w->num_sms * w->blocks_per_sm[variant][masked ? 1 : 0]);
+    ovis::launch_cull_test(a, masked, variant, grid, w->stream);
     ovis::GatherArgs g;
     g.staging = w->d_staging;
     g.tile_counts = w->d_tile_counts;
@@ -579,10 +581,12 @@ int ovis_world_create(int device, OvisWorld **out_world) {
     if (const char *v = getenv("OVIS_CULL_VARIANT")) {   // tuning knob, not part of the ABI
         int k = atoi(v);
         if (k >= 0 && k < ovis::cull_num_variants())
-            w->variant = k;
+            w->forced_variant = k;
     }
-    w->blocks_per_sm[0] = std::max(1, ovis::cull_test_max_blocks_per_sm(false, w->variant));
-    w->blocks_per_sm[1] = std::max(1, ovis::cull_test_max_blocks_per_sm(true, w->variant));
+    for (int v = 0; v < ovis::cull_num_variants() && v < 8; v++) {
+        w->blocks_per_sm[v][0] = std::max(1, ovis::cull_test_max_blocks_per_sm(false, v));
+        w->blocks_per_sm[v][1] = std::max(1, ovis::cull_test_max_blocks_per_sm(true, v));
+    }
     OVIS_CUDA(cudaMalloc(&w->d_counts, 2 * sizeof(uint32_t)));
     OVIS_CUDA(cudaMemset(w->d_counts, 0, 2 * sizeof(uint32_t)));
     OVIS_CUDA(cudaMallocHost(&w->h_counts, 2 * sizeof(uint32_t)));
