@@ -216,6 +216,14 @@ int ovis_read_device(OvisWorld *world, const void *d_src, int64_t bytes, void *h
 int ovis_host_alloc(int64_t bytes, void **out_ptr);
 int ovis_host_free(void *ptr);
 
+/* Profiling hook (no counterpart in the reference, whose cull path has no timers - SURVEY.md section 5):
+ * while enabled, every entity cull records CUDA events on the world's stream before the test kernel,
+ * between the test and the gather kernel, and after the gather kernel. ovis_world_read_timing synchronises
+ * the stream, writes the per-cull device times (milliseconds) of the culls since the last read / enable
+ * (at most `capacity` entries) and resets the record. */
+int ovis_world_set_timing(OvisWorld *world, int enabled);
+int ovis_world_read_timing(OvisWorld *world, int32_t capacity, float *test_ms, float *gather_ms, int32_t *out_count);
+
 /* Number of kernels this library has launched on behalf of `world` since creation (bench.py's gpu_launches). */
 int ovis_world_launch_count(OvisWorld *world, int64_t *out_launches);
 

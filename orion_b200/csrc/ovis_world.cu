@@ -120,6 +120,11 @@ struct OvisWorld {
     long long *d_csr_offsets = nullptr;
     int64_t cap_csr_views = 0;
 
+    // ---- optional per-kernel timing of the entity cull (bench / profiling hook)
+    bool timing = false;
+    std::vector<cudaEvent_t> timing_events;   // triples: before test, after test, after gather
+    size_t timing_used = 0;
+
     // ---- upload staging
     void *d_stage[2] = { nullptr, nullptr };
     size_t stage_bytes[2] = { 0, 0 };
@@ -438,7 +443,21 @@ int enqueue_cull(OvisWorld *w, const float planes[24], uint32_t require, uint32_
     a.id_base = w->id_base;
     const int warps_needed_blocks = (a.num_tiles + ovis::kCullThreads / 32 - 1) / (ovis::kCullThreads / 32);
     int grid = std::min(warps_needed_blocks, w->num_sms * w->blocks_per_sm[variant][masked ? 1 : 0]);
+    cudaEvent_t *ev = nullptr;
+    if (w->timing) {
+        if (w->timing_used + 3 > w->timing_events.size()) {
+            size_t old = w->timing_events.size();
+            w->timing_events.resize(old + 3 * 256);
+            for (size_t i = old; i < w->timing_events.size(); i++)
+                OVIS_CUDA(cudaEventCreate(&w->timing_events[i]));
+        }
+        ev = &w->timing_events[w->timing_used];
+        w->timing_used += 3;
+        OVIS_CUDA(cudaEventRecord(ev[0], w->stream));
+    }
     ovis::launch_cull_test(a, masked, variant, grid, w->stream);
+    if (ev)
+        OVIS_CUDA(cudaEventRecord(ev[1], w->stream));
     ovis::GatherArgs g;
     g.staging = w->d_staging;
     g.tile_counts = w->d_tile_counts;
@@ -451,6 +470,8 @@ int enqueue_cull(OvisWorld *w, const float planes[24], uint32_t require, uint32_
     g.d_next = d_next;
     g.d_count = d_count;
     ovis::launch_cull_gather(g, w->stream);
+    if (ev)
+        OVIS_CUDA(cudaEventRecord(ev[2], w->stream));
     w->totals_parity ^= 1;
     w->launches += 2;
     OVIS_CUDA(cudaGetLastError());
@@ -608,6 +629,8 @@ int ovis_world_destroy(OvisWorld *w) {
             cudaFree(b);
     if (w->h_counts)
         cudaFreeHost(w->h_counts);
+    for (cudaEvent_t e : w->timing_events)
+        cudaEventDestroy(e);
     delete w;
     return OVIS_OK;
 }
@@ -645,6 +668,32 @@ int ovis_world_counts(OvisWorld *w, int64_t *n_entities, int64_t *n_nodes, int32
     if (n_entities) *n_entities = w->n_ent;
     if (n_nodes) *n_nodes = w->n_nodes;
     if (n_lights) *n_lights = (int32_t)w->lights.size();
+    return OVIS_OK;
+}
+
+int ovis_world_set_timing(OvisWorld *w, int enabled) {
+    if (!w)
+        return fail(OVIS_ERR_INVALID, "world is null");
+    w->timing = enabled != 0;
+    w->timing_used = 0;
+    return OVIS_OK;
+}
+
+int ovis_world_read_timing(OvisWorld *w, int32_t capacity, float *test_ms, float *gather_ms, int32_t *out_count) {
+    if (!w || !out_count || capacity < 0)
+        return fail(OVIS_ERR_INVALID, "ovis_world_read_timing: bad arguments");
+    OVIS_TRY(use_device(w));
+    OVIS_CUDA(cudaStreamSynchronize(w->stream));
+    int32_t n = (int32_t)(w->timing_used / 3);
+    *out_count = n;
+    for (int32_t i = 0; i < n && i < capacity; i++) {
+        cudaEvent_t *ev = &w->timing_events[3 * (size_t)i];
+        if (test_ms)
+            OVIS_CUDA(cudaEventElapsedTime(&test_ms[i], ev[0], ev[1]));
+        if (gather_ms)
+            OVIS_CUDA(cudaEventElapsedTime(&gather_ms[i], ev[1], ev[2]));
+    }
+    w->timing_used = 0;
     return OVIS_OK;
 }
 

@@ -170,6 +170,18 @@ class World:
         _check(self.lib.ovis_world_counts(self.h, C.byref(ne), C.byref(nn), C.byref(nl)))
         return ne.value, nn.value, nl.value
 
+    def set_timing(self, enabled: bool):
+        _check(self.lib.ovis_world_set_timing(self.h, C.c_int(1 if enabled else 0)))
+
+    def read_timing(self, capacity: int = 65536):
+        """Per-cull device times (ms) of the test and gather kernels recorded since set_timing(True)."""
+        test = np.zeros(capacity, dtype=np.float32)
+        gather = np.zeros(capacity, dtype=np.float32)
+        n = C.c_int32()
+        _check(self.lib.ovis_world_read_timing(self.h, C.c_int32(capacity), _p(test), _p(gather), C.byref(n)))
+        k = min(n.value, capacity)
+        return test[:k].copy(), gather[:k].copy()
+
     def launch_count(self) -> int:
         n = C.c_int64()
         _check(self.lib.ovis_world_launch_count(self.h, C.byref(n)))
