@@ -181,6 +181,24 @@ int ovis_cull_planes(OvisWorld *world, const float planes[24], uint32_t require,
 int ovis_cull_planes_device(OvisWorld *world, const float planes[24], uint32_t require,
                             uint32_t *d_out_entities, uint32_t *d_out_count);
 
+/* Entity cull for callers that cannot allocate GPU memory - a render thread in the middle of a frame, or an
+ * engine that forbids cudaMalloc/cudaFree after start-up because they synchronise the device, can fail under
+ * a fixed VRAM budget, and bypass its own pool. No counterpart in the reference. Same result as
+ * ovis_cull_planes_device (ids ascending, id_base added, *d_out_count = number of visible entities even if
+ * `capacity` clipped the writes), but it needs no OvisWorld and allocates nothing: the caller passes the
+ * world AABBs as device memory in the library's SoA layout (component k of entity i at
+ * d_world_aabb[k * stride + i], k = min xyz then max xyz; stride a multiple of 4 and >= n_entities rounded
+ * up to 256) and the device outputs, and the kernels' scratch is a fixed ~4.2 MB array inside the library
+ * image (present on every GPU that loads the library, until exit). Limits and rules: at most
+ * OVIS_NOALLOC_MAX_ENTITIES entities per call (more -> OVIS_ERR_CAPACITY); all calls on a GPU share that one
+ * scratch, so calls whose kernels could overlap on the GPU (different streams or threads) race - keep them on
+ * one stream or serialise them; the first call on each device resolves the scratch address and launch
+ * geometry, so make that first call before starting any stream capture. Asynchronous on `cuda_stream`. */
+#define OVIS_NOALLOC_MAX_ENTITIES 1048576
+int ovis_cull_planes_noalloc(int device, void *cuda_stream, const float *d_world_aabb, int64_t stride,
+                             int64_t n_entities, const float planes[24], uint32_t id_base,
+                             uint32_t *d_out_entities, int64_t capacity, uint32_t *d_out_count);
+
 /* Many views in one pass over the bounds (main camera + cascades + every shadow view:
  * deferred_render_pipeline.cc:147,259-284). planes = n_views x 24 floats, require = n_views masks (NULL = 0).
  * Results stay on the device in CSR form and are valid until the next call on this world:

@@ -1,0 +1,171 @@
+// ovis_noalloc.cu - ovis_cull_planes_noalloc: the single-view entity cull for callers that must not
+// allocate GPU memory.
+//
+// Who needs this: a renderer calling the cull from inside its frame loop. There, cudaMalloc / cudaFree
+// are off limits - they synchronise the whole device (a stall in the middle of a frame), they can fail
+// when the graphics API has already taken the VRAM budget, and many engines simply forbid driver
+// allocations after start-up and hand out all device memory from their own pool. Such a caller owns its
+// bounds and result buffers already; the only thing the cull needs beyond them is scratch space for the
+// per-warp-tile survivor lists and counts. Here that scratch is a fixed array that is part of the library
+// image, so the call path contains no cudaMalloc, cudaFree, or any allocating runtime/library routine.
+//
+// The price is a hard size limit (OVIS_NOALLOC_MAX_ENTITIES) and one shared scratch per GPU:
+//   - every GPU that loads liborion_vis.so carries the ~4.2 MB array until the process exits;
+//   - all calls on a GPU use the same array. It still holds the previous call's data, so each call clears
+//     the one part that has to start at zero (the block totals); the rest is overwritten before it is read;
+//   - two calls whose kernels overlap on the same GPU (different streams, or different host threads) would
+//     write the same scratch and race. Issue them on one stream, or serialise them yourself.
+#include "orion_vis.h"
+
+#include <cstdio>
+#include <mutex>
+
+#include <cuda_runtime.h>
+
+#include "ovis_kernels.h"
+
+namespace ovis {
+int report_error(int code, const char *message);
+}
+
+namespace {
+
+constexpr int64_t kMaxEntities = OVIS_NOALLOC_MAX_ENTITIES;
+constexpr int kVariant = 0;                                     // 256-entity warp tiles, as the world path uses for large sets
+constexpr int64_t kTileEntities = 256;
+constexpr int64_t kMaxTiles = kMaxEntities / kTileEntities;     // 4096
+constexpr int64_t kMaxBlocks = kMaxTiles / ovis::kGatherTiles + 1;
+
+// Scratch layout inside the array, in bytes.
+constexpr size_t kStagingBytes = sizeof(uint32_t) * kMaxEntities;                 // survivor ids, one slot per warp tile
+constexpr size_t kCountsBytes = sizeof(uint32_t) * kMaxTiles;                     // survivors per warp tile
+constexpr size_t kTotalsBytes = sizeof(uint32_t) * 2 * kMaxBlocks;                // two sets of per-block totals
+constexpr size_t kScratchBytes = kStagingBytes + kCountsBytes + ((kTotalsBytes + 255) / 256) * 256;
+
+// The scratch itself. In host code this name is only a handle for the runtime, NOT a device address: it must
+// never be handed to a kernel. The address kernels may use comes from cudaGetSymbolAddress (below).
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kScratchBytes];
+
+struct DeviceSetup {
+    bool ready = false;
+    unsigned char *scratch = nullptr;     // device address of g_noalloc_scratch on this GPU
+    int num_sms = 0;
+    int blocks_per_sm = 0;
+};
+
+constexpr int kMaxDevices = 64;
+DeviceSetup g_setup[kMaxDevices];
+std::mutex g_setup_mutex;
+
+int fail_cuda(const char *what, cudaError_t err) {
+    char buf[256];
+    snprintf(buf, sizeof buf, "ovis_cull_planes_noalloc: %s failed: %s", what, cudaGetErrorString(err));
+    return ovis::report_error(OVIS_ERR_CUDA, buf);
+}
+
+// One-time set-up for `device`, which must be the current device: resolve the scratch array's device address
+// and cache the launch geometry. None of these calls allocates.
+int setup_device(int device, DeviceSetup **out) {
+    std::lock_guard<std::mutex> lock(g_setup_mutex);
+    DeviceSetup &s = g_setup[device];
+    if (!s.ready) {
+        void *ptr = nullptr;
+        cudaError_t err = cudaGetSymbolAddress(&ptr, g_noalloc_scratch);
+        if (err != cudaSuccess)
+            return fail_cuda("cudaGetSymbolAddress(scratch)", err);
+        s.scratch = static_cast<unsigned char *>(ptr);
+        err = cudaDeviceGetAttribute(&s.num_sms, cudaDevAttrMultiProcessorCount, device);
+        if (err != cudaSuccess)
+            return fail_cuda("cudaDeviceGetAttribute", err);
+        s.blocks_per_sm = ovis::cull_test_max_blocks_per_sm(false, kVariant);
+        if (s.blocks_per_sm < 1)
+            s.blocks_per_sm = 1;
+        s.ready = true;
+    }
+    *out = &s;
+    return OVIS_OK;
+}
+
+}  // namespace
+
+extern "C" int ovis_cull_planes_noalloc(int device, void *cuda_stream, const float *d_world_aabb, int64_t stride,
+                                        int64_t n_entities, const float planes[24], uint32_t id_base,
+                                        uint32_t *d_out_entities, int64_t capacity, uint32_t *d_out_count) {
+    if (!planes || !d_out_count || n_entities < 0 || capacity < 0 || (n_entities > 0 && (!d_world_aabb || !d_out_entities)))
+        return ovis::report_error(OVIS_ERR_INVALID, "ovis_cull_planes_noalloc: null or negative argument");
+    if (n_entities > kMaxEntities) {
+        char buf[200];
+        snprintf(buf, sizeof buf, "ovis_cull_planes_noalloc: %lld entities exceed the fixed scratch (at most %lld per call); "
+                                  "use a world (ovis_cull_planes_device) for larger sets",
+                 (long long)n_entities, (long long)kMaxEntities);
+        return ovis::report_error(OVIS_ERR_CAPACITY, buf);
+    }
+    const int64_t padded = (n_entities + kTileEntities - 1) / kTileEntities * kTileEntities;
+    if (stride % 4 != 0 || stride < padded)
+        return ovis::report_error(OVIS_ERR_INVALID, "ovis_cull_planes_noalloc: stride must be a multiple of 4 and at least "
+                                                    "n_entities rounded up to 256 (whole warp tiles are loaded)");
+    if (device < 0 || device >= kMaxDevices)
+        return ovis::report_error(OVIS_ERR_INVALID, "ovis_cull_planes_noalloc: device out of range");
+    cudaError_t err = cudaSetDevice(device);
+    if (err != cudaSuccess)
+        return fail_cuda("cudaSetDevice", err);
+    DeviceSetup *setup = nullptr;
+    int rc = setup_device(device, &setup);
+    if (rc != OVIS_OK)
+        return rc;
+    cudaStream_t stream = static_cast<cudaStream_t>(cuda_stream);
+
+    if (n_entities == 0) {
+        ovis::launch_empty_result(nullptr, nullptr, d_out_count, stream);
+        err = cudaGetLastError();
+        return err == cudaSuccess ? OVIS_OK : fail_cuda("empty-result launch", err);
+    }
+
+    uint32_t *staging = reinterpret_cast<uint32_t *>(setup->scratch);
+    uint32_t *tile_counts = reinterpret_cast<uint32_t *>(setup->scratch + kStagingBytes);
+    uint32_t *totals = reinterpret_cast<uint32_t *>(setup->scratch + kStagingBytes + kCountsBytes);
+
+    ovis::CullArgs a;
+    for (int i = 0; i < 6; i++)
+        a.planes[i] = make_float4(planes[4 * i], planes[4 * i + 1], planes[4 * i + 2], planes[4 * i + 3]);
+    a.bounds = d_world_aabb;
+    a.stride = stride;
+    a.n = n_entities;
+    a.num_tiles = (int)(padded / kTileEntities);
+    a.num_blocks = (a.num_tiles + ovis::kGatherTiles - 1) / ovis::kGatherTiles;
+    a.mask = nullptr;
+    a.staging = staging;
+    a.tile_counts = tile_counts;
+    a.block_totals = totals;                       // accumulated into by this call: must start at zero
+    a.block_totals_next = totals + kMaxBlocks;     // the kernel's "re-arm the other set" write lands here, unused
+    a.id_base = id_base;
+
+    // The array keeps whatever the previous call left. Only the block totals are added to rather than
+    // overwritten, so they are the only part that has to be cleared.
+    err = cudaMemsetAsync(totals, 0, sizeof(uint32_t) * (size_t)a.num_blocks, stream);
+    if (err != cudaSuccess)
+        return fail_cuda("cudaMemsetAsync(block totals)", err);
+
+    const int warps_per_block = ovis::kCullThreads / 32;
+    int grid = (a.num_tiles + warps_per_block - 1) / warps_per_block;
+    if (grid > setup->num_sms * setup->blocks_per_sm)
+        grid = setup->num_sms * setup->blocks_per_sm;
+    ovis::launch_cull_test(a, false, kVariant, grid, stream);
+
+    ovis::GatherArgs g;
+    g.staging = staging;
+    g.tile_counts = tile_counts;
+    g.block_totals = totals;
+    g.num_tiles = a.num_tiles;
+    g.tile_entities = (int)kTileEntities;
+    g.out = d_out_entities;
+    g.capacity = capacity;
+    g.d_base = nullptr;
+    g.d_next = nullptr;
+    g.d_count = d_out_count;
+    ovis::launch_cull_gather(g, stream);
+    err = cudaGetLastError();
+    if (err != cudaSuccess)
+        return fail_cuda("kernel launch", err);
+    return OVIS_OK;
+}

@@ -570,6 +570,11 @@ int cull_views_device(OvisWorld *w, int32_t n_views, const float *planes, const 
 
 }  // namespace
 
+namespace ovis {
+// Lets the library's other .cu files report through ovis_last_error().
+int report_error(int code, const char *message) { return fail(code, "%s", message); }
+}  // namespace ovis
+
 // ================================================================================================
 // C ABI
 // ================================================================================================

@@ -111,6 +111,21 @@ def light_shadow_views(light: np.ndarray, resolution: int = 512) -> np.ndarray:
     return out[:n.value].copy()
 
 
+NOALLOC_MAX_ENTITIES = 1 << 20
+
+
+def cull_planes_noalloc(device: int, stream: int, d_world_aabb: int, stride: int, n_entities: int, planes,
+                        d_out: int, capacity: int, d_count: int, id_base: int = 0):
+    """ovis_cull_planes_noalloc: the single-view cull with library-internal fixed scratch (no allocation).
+
+    All pointers are raw device addresses owned by the caller; asynchronous on `stream`.
+    """
+    planes = _f32(planes, (24,))
+    _check(load().ovis_cull_planes_noalloc(C.c_int(device), C.c_void_p(stream), C.c_void_p(d_world_aabb),
+                                           C.c_int64(stride), C.c_int64(n_entities), _p(planes), C.c_uint32(id_base),
+                                           C.c_void_p(d_out), C.c_int64(capacity), C.c_void_p(d_count)))
+
+
 class PinnedBuffer:
     """Page-locked host memory from ovis_host_alloc, viewed as a numpy array."""
 
