@@ -119,6 +119,9 @@ int ovis_entity_set_transforms(OvisWorld *world, int64_t n, const uint32_t *ids,
 /* Static geometry: give n consecutive entities their WORLD AABBs directly (what updateWorld,
  * render_entity.cc:90-93, would have produced), bypassing the transform stage. */
 int ovis_entity_set_world_aabbs(OvisWorld *world, uint32_t first_id, int64_t n, const float *world_aabb);
+/* Same for scattered ids: what a RenderWorld::updateEntity implementation forwards when the RenderEntity has
+ * already recomputed worldBoundingBox() on the host (render_entity.cc:90-97). */
+int ovis_entity_set_world_aabbs_by_id(OvisWorld *world, int64_t n, const uint32_t *ids, const float *world_aabb);
 
 /* ------------------------------------------------------------------------------------------------
  * Transform tree - Entity local/world transforms (engine/include/entity.h:45-190,

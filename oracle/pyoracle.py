@@ -76,6 +76,8 @@ def build(reference_root: str = "/root/reference") -> None:
     subprocess.run(["make", "-s", "-C", HERE, "libovis_oracle.so"], check=True)
     if os.path.isdir(os.path.join(reference_root, "engine", "runtime")):
         subprocess.run(["make", "-s", "-C", HERE, f"REF={reference_root}", "ref"], check=True)
+        if os.path.exists(os.path.join(os.path.dirname(HERE), "orion_b200", "liborion_vis.so")):
+            subprocess.run(["make", "-s", "-C", HERE, f"REF={reference_root}", "adapter_check"], check=True)
 
 
 def available(kind: str) -> bool:

@@ -861,6 +861,23 @@ int ovis_entity_set_world_aabbs(OvisWorld *w, uint32_t first_id, int64_t n, cons
     return OVIS_OK;
 }
 
+int ovis_entity_set_world_aabbs_by_id(OvisWorld *w, int64_t n, const uint32_t *ids, const float *world_aabb) {
+    if (!w || n < 0 || (n > 0 && !world_aabb))
+        return fail(OVIS_ERR_INVALID, "ovis_entity_set_world_aabbs_by_id: bad arguments");
+    OVIS_TRY(use_device(w));
+    OVIS_TRY(check_entity_ids(w, n, ids));
+    for (int64_t s = 0; s < n; s += kUploadChunk) {
+        int64_t c = std::min(kUploadChunk, n - s);
+        void *d = nullptr, *di = nullptr;
+        OVIS_TRY(stage(w, 0, world_aabb + 6 * s, sizeof(float) * 6 * (size_t)c, &d));
+        OVIS_TRY(stage(w, 1, ids + s, sizeof(uint32_t) * (size_t)c, &di));
+        ovis::launch_scatter_aos(6, (const float *)d, (const uint32_t *)di, 0, c, w->d_world, w->cap_ent, w->stream);
+        w->launches++;
+    }
+    OVIS_CUDA(cudaGetLastError());
+    return OVIS_OK;
+}
+
 // ---- transform tree ----------------------------------------------------------------------------
 
 int ovis_node_add(OvisWorld *w, int64_t n, const int32_t *parent, const float *local_trs, uint32_t *out_first_id) {

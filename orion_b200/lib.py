@@ -232,6 +232,11 @@ class World:
         world_aabb = _f32(world_aabb, (-1, 6))
         _check(self.lib.ovis_entity_set_world_aabbs(self.h, C.c_uint32(first_id), C.c_int64(len(world_aabb)), _p(world_aabb)))
 
+    def set_world_aabbs_by_id(self, ids, world_aabb):
+        ids = _u32(ids)
+        world_aabb = _f32(world_aabb, (-1, 6))
+        _check(self.lib.ovis_entity_set_world_aabbs_by_id(self.h, C.c_int64(len(ids)), _p(ids), _p(world_aabb)))
+
     # ---- transform tree
     def add_nodes(self, parent, local_trs) -> int:
         parent = np.ascontiguousarray(parent, dtype=np.int32).reshape(-1)
