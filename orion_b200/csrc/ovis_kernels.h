@@ -60,6 +60,41 @@ struct GatherArgs {               // K3b
     uint32_t *d_count;           // optional: receives count
 };
 
+// ---- K4 multi-view ------------------------------------------------------------------------------
+constexpr int kMultiMaxViews = 1024;          // views per pass (one CTA of 1024 threads scans them)
+
+struct ViewGroupDev {
+    float px, py, pz;            // centre of the pre-filter cube (a point light's position)
+    float r;                     // half-side before inflation (the light's range); +inf = no pre-filter
+    float pmax;                  // largest |coordinate| of the centre (for the rounding margin)
+    int first_view, n_views;     // consecutive views of the pass that share this cube
+    int pad;
+};
+
+struct MultiArgs {
+    const float *bounds;         // world AABBs, 6 x stride
+    int64_t stride;
+    int64_t n;
+    int num_tiles;               // supertiles of 1024 entities
+    const uint32_t *alive_mask;  // nullptr when every slot is live
+    const uint32_t *caster_mask; // alive & castsShadow
+    const ViewGroupDev *groups;
+    int n_groups;
+    const float4 *planes;        // 6 per view
+    const uint32_t *view_require;// per view: non-zero = shadow casters only
+    int n_views;
+    uint32_t *counts;            // [num_tiles][n_views]: counts after pass A, positions after the scans
+    uint32_t *block_totals;      // [num_blocks][n_views], zero before pass A
+    const long long *csr_offsets;// [n_views + 1] start of each view's list (valid after the scans)
+    uint32_t *out;
+    long long capacity;
+    uint32_t id_base;
+};
+
+int multi_max_blocks_per_sm(int n_views);
+void launch_multi_pass(const MultiArgs &a, bool write, int grid, cudaStream_t s);
+void launch_multi_scans(const MultiArgs &a, long long *csr_offsets_of_pass, cudaStream_t s);
+
 enum : uint32_t { kLightNever = 0, kLightAlways = 1, kLightSphere = 2, kLightBox = 3 };
 
 struct DeviceLight {

@@ -12,6 +12,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <limits>
 #include <new>
 #include <string>
 #include <vector>
@@ -119,6 +120,17 @@ struct OvisWorld {
     int64_t cap_csr = 0;
     long long *d_csr_offsets = nullptr;
     int64_t cap_csr_views = 0;
+
+    // ---- multi-view (K4) scratch
+    uint32_t *d_mv_counts = nullptr;      // [supertiles][views of a pass]
+    int64_t cap_mv_counts = 0;
+    uint32_t *d_mv_totals = nullptr;      // [blocks][views of a pass]
+    int64_t cap_mv_totals = 0;
+    float *d_mv_planes = nullptr;         // 24 floats per view
+    uint32_t *d_mv_require = nullptr;
+    int64_t cap_mv_views = 0;
+    ovis::ViewGroupDev *d_mv_groups = nullptr;
+    int64_t cap_mv_groups = 0;
 
     // ---- optional per-kernel timing of the entity cull (bench / profiling hook)
     bool timing = false;
@@ -532,9 +544,12 @@ int enqueue_light_cull(OvisWorld *w, const float planes[24]) {
     return OVIS_OK;
 }
 
-int cull_views_device(OvisWorld *w, int32_t n_views, const float *planes, const uint32_t *require, int64_t *host_offsets_out,
-                      std::vector<long long> &host_offsets) {
+// K4: all views of `groups` in passes of at most kMultiMaxViews views; result in w->d_csr_* (CSR, device).
+int cull_views_grouped(OvisWorld *w, int32_t n_views, const float *planes, const uint32_t *require,
+                       const std::vector<ovis::ViewGroupDev> &groups, int64_t *host_offsets_out,
+                       std::vector<long long> &host_offsets) {
     OVIS_TRY(flush_transforms(w));
+    host_offsets.assign((size_t)n_views + 1, 0);
     if (n_views + 1 > w->cap_csr_views) {
         int64_t cap = std::max<int64_t>(n_views + 1, 64);
         OVIS_TRY(grow(w->d_csr_offsets, 0, cap, w->stream, false));
@@ -545,12 +560,105 @@ int cull_views_device(OvisWorld *w, int32_t n_views, const float *planes, const 
         OVIS_TRY(grow(w->d_csr_entities, 0, cap, w->stream, false));
         w->cap_csr = cap;
     }
-    host_offsets.assign((size_t)n_views + 1, 0);
+    OVIS_CUDA(cudaMemsetAsync(w->d_csr_offsets, 0, sizeof(long long), w->stream));
+    if (n_views == 0 || w->n_ent == 0) {
+        if (n_views > 0)
+            OVIS_CUDA(cudaMemsetAsync(w->d_csr_offsets, 0, sizeof(long long) * ((size_t)n_views + 1), w->stream));
+        OVIS_CUDA(cudaStreamSynchronize(w->stream));
+        if (host_offsets_out)
+            for (int32_t v = 0; v <= n_views; v++)
+                host_offsets_out[v] = 0;
+        return OVIS_OK;
+    }
+    OVIS_TRY(upload_masks(w));
+    bool any_require = false;
+    for (int32_t v = 0; v < n_views; v++) {
+        uint32_t r = require ? require[v] : 0u;
+        if (r & ~(uint32_t)OVIS_CASTS_SHADOW)
+            return fail(OVIS_ERR_INVALID, "require mask 0x%x: only 0 or OVIS_CASTS_SHADOW is supported", r);
+        any_require |= r != 0;
+    }
+    // split the groups into passes of at most kMultiMaxViews views (a group is never split)
+    struct Pass { size_t g0, g1; int32_t v0, v1; };
+    std::vector<Pass> passes;
+    {
+        Pass cur = { 0, 0, 0, 0 };
+        for (size_t g = 0; g < groups.size(); g++) {
+            if (groups[g].n_views > ovis::kMultiMaxViews)
+                return fail(OVIS_ERR_INVALID, "a view group holds more than %d views", ovis::kMultiMaxViews);
+            if (cur.v1 - cur.v0 + groups[g].n_views > ovis::kMultiMaxViews) {
+                passes.push_back(cur);
+                cur = { g, g, cur.v1, cur.v1 };
+            }
+            cur.g1 = g + 1;
+            cur.v1 += groups[g].n_views;
+        }
+        if (cur.g1 > cur.g0)
+            passes.push_back(cur);
+    }
+    const int num_tiles = (int)((w->n_ent + 1023) / 1024);
+    const int num_blocks = (num_tiles + ovis::kGatherTiles - 1) / ovis::kGatherTiles;
+    const int64_t pass_views = std::min<int64_t>(n_views, ovis::kMultiMaxViews);
+    if ((int64_t)num_tiles * pass_views > w->cap_mv_counts) {
+        OVIS_TRY(grow(w->d_mv_counts, 0, (int64_t)num_tiles * pass_views, w->stream, false));
+        w->cap_mv_counts = (int64_t)num_tiles * pass_views;
+    }
+    if ((int64_t)num_blocks * pass_views > w->cap_mv_totals) {
+        OVIS_TRY(grow(w->d_mv_totals, 0, (int64_t)num_blocks * pass_views, w->stream, false));
+        w->cap_mv_totals = (int64_t)num_blocks * pass_views;
+    }
+    if (n_views > w->cap_mv_views) {
+        OVIS_TRY(grow(w->d_mv_planes, 0, 24 * (int64_t)n_views, w->stream, false));
+        OVIS_TRY(grow(w->d_mv_require, 0, (int64_t)n_views, w->stream, false));
+        w->cap_mv_views = n_views;
+    }
+    if ((int64_t)groups.size() > w->cap_mv_groups) {
+        OVIS_TRY(grow(w->d_mv_groups, 0, (int64_t)groups.size(), w->stream, false));
+        w->cap_mv_groups = (int64_t)groups.size();
+    }
+    // groups are uploaded with first_view relative to their pass
+    std::vector<ovis::ViewGroupDev> rel(groups);
+    std::vector<uint32_t> req((size_t)n_views, 0u);
+    for (int32_t v = 0; v < n_views; v++)
+        req[(size_t)v] = require ? require[v] : 0u;
+    for (const Pass &p : passes)
+        for (size_t g = p.g0; g < p.g1; g++)
+            rel[g].first_view -= p.v0;
+    OVIS_CUDA(cudaMemcpyAsync(w->d_mv_planes, planes, sizeof(float) * 24 * (size_t)n_views, cudaMemcpyHostToDevice, w->stream));
+    OVIS_CUDA(cudaMemcpyAsync(w->d_mv_require, req.data(), sizeof(uint32_t) * (size_t)n_views, cudaMemcpyHostToDevice, w->stream));
+    OVIS_CUDA(cudaMemcpyAsync(w->d_mv_groups, rel.data(), sizeof(ovis::ViewGroupDev) * rel.size(), cudaMemcpyHostToDevice, w->stream));
+    OVIS_CUDA(cudaStreamSynchronize(w->stream));       // rel / req are locals
+
     for (int attempt = 0; attempt < 2; attempt++) {
         OVIS_CUDA(cudaMemsetAsync(w->d_csr_offsets, 0, sizeof(long long), w->stream));
-        for (int32_t v = 0; v < n_views; v++)
-            OVIS_TRY(enqueue_cull(w, planes + 24 * (size_t)v, require ? require[v] : 0u, w->d_csr_entities, w->cap_csr,
-                                  w->d_csr_offsets + v, w->d_csr_offsets + v + 1, nullptr));
+        for (const Pass &p : passes) {
+            ovis::MultiArgs a;
+            a.bounds = w->d_world;
+            a.stride = w->cap_ent;
+            a.n = w->n_ent;
+            a.num_tiles = num_tiles;
+            a.alive_mask = w->any_dead ? w->d_alive_bits : nullptr;
+            a.caster_mask = any_require ? w->d_caster_bits : nullptr;
+            a.groups = w->d_mv_groups + p.g0;
+            a.n_groups = (int)(p.g1 - p.g0);
+            a.planes = reinterpret_cast<const float4 *>(w->d_mv_planes) + 6 * (size_t)p.v0;
+            a.view_require = w->d_mv_require + p.v0;
+            a.n_views = p.v1 - p.v0;
+            a.counts = w->d_mv_counts;
+            a.block_totals = w->d_mv_totals;
+            a.csr_offsets = w->d_csr_offsets + p.v0;
+            a.out = w->d_csr_entities;
+            a.capacity = w->cap_csr;
+            a.id_base = w->id_base;
+            OVIS_CUDA(cudaMemsetAsync(w->d_mv_totals, 0, sizeof(uint32_t) * (size_t)num_blocks * (size_t)a.n_views, w->stream));
+            int per_sm = std::max(1, ovis::multi_max_blocks_per_sm(a.n_views));
+            int grid = std::min((num_tiles + 7) / 8, w->num_sms * per_sm);
+            ovis::launch_multi_pass(a, false, grid, w->stream);
+            ovis::launch_multi_scans(a, w->d_csr_offsets + p.v0, w->stream);
+            ovis::launch_multi_pass(a, true, grid, w->stream);
+            w->launches += 4;
+            OVIS_CUDA(cudaGetLastError());
+        }
         OVIS_CUDA(cudaMemcpyAsync(host_offsets.data(), w->d_csr_offsets, sizeof(long long) * ((size_t)n_views + 1),
                                   cudaMemcpyDeviceToHost, w->stream));
         OVIS_CUDA(cudaStreamSynchronize(w->stream));
@@ -566,6 +674,22 @@ int cull_views_device(OvisWorld *w, int32_t n_views, const float *planes, const 
         for (int32_t v = 0; v <= n_views; v++)
             host_offsets_out[v] = host_offsets[(size_t)v];
     return OVIS_OK;
+}
+
+// Views without a shared pre-filter: one group per view, infinite cube.
+int cull_views_device(OvisWorld *w, int32_t n_views, const float *planes, const uint32_t *require, int64_t *host_offsets_out,
+                      std::vector<long long> &host_offsets) {
+    std::vector<ovis::ViewGroupDev> groups((size_t)n_views);
+    for (int32_t v = 0; v < n_views; v++) {
+        ovis::ViewGroupDev &g = groups[(size_t)v];
+        g.px = g.py = g.pz = 0.0f;
+        g.r = std::numeric_limits<float>::infinity();
+        g.pmax = 0.0f;
+        g.first_view = v;
+        g.n_views = 1;
+        g.pad = 0;
+    }
+    return cull_views_grouped(w, n_views, planes, require, groups, host_offsets_out, host_offsets);
 }
 
 }  // namespace
@@ -627,7 +751,8 @@ int ovis_world_destroy(OvisWorld *w) {
     cudaStreamSynchronize(w->stream);
     void *bufs[] = { w->d_local, w->d_world, w->d_alive_bits, w->d_caster_bits, w->d_parent, w->d_local_trs, w->d_world_trs,
                      w->d_node_entity, w->d_extra_entity, w->d_extra_node, w->d_level_lists, w->d_lights, w->d_light_out,
-                     w->d_staging, w->d_tile_counts, w->d_block_totals, w->d_result, w->d_counts, w->d_csr_entities, w->d_csr_offsets,
+                     w->d_staging, w->d_tile_counts, w->d_block_totals, w->d_mv_counts, w->d_mv_totals, w->d_mv_planes,
+                     w->d_mv_require, w->d_mv_groups, w->d_result, w->d_counts, w->d_csr_entities, w->d_csr_offsets,
                      w->d_stage[0], w->d_stage[1] };
     for (void *b : bufs)
         if (b)
@@ -1089,10 +1214,23 @@ int ovis_build_shadow_lists(OvisWorld *w, const OvisView *main_view, int32_t sha
     //    (allocateShadowMap is fatal for the rest, deferred_render_pipeline.cc:291-303)
     std::vector<float> planes;
     std::vector<int32_t> list_light, list_view;
+    std::vector<ovis::ViewGroupDev> groups;
     for (uint32_t id : visible) {
         const OvisLight &l = w->lights[id];
         OvisView views[6];
         int count = ovis::hm::shadowViews(l, shadow_map_resolution, views);
+        if (count == 0)
+            continue;
+        ovis::ViewGroupDev g;
+        g.px = l.position[0]; g.py = l.position[1]; g.pz = l.position[2];
+        // A point light's six face frusta (fov 90, far = range) lie inside the cube of half-side `range` about the
+        // light; a spot light's single frustum gets no pre-filter.
+        g.r = (l.type == OVIS_LIGHT_POINT) ? l.range : std::numeric_limits<float>::infinity();
+        g.pmax = std::max(std::fabs(g.px), std::max(std::fabs(g.py), std::fabs(g.pz)));
+        g.first_view = (int)list_light.size();
+        g.n_views = count;
+        g.pad = 0;
+        groups.push_back(g);
         for (int i = 0; i < count; i++) {
             planes.resize(planes.size() + 24);
             ovis::hm::viewPlanes(views[i], planes.data() + planes.size() - 24);
@@ -1101,10 +1239,10 @@ int ovis_build_shadow_lists(OvisWorld *w, const OvisView *main_view, int32_t sha
         }
     }
     int32_t n_lists = (int32_t)list_light.size();
-    // 3. one caster-filtered cull per shadow view (:270-283)
+    // 3. one caster-filtered multi-view pass over the bounds for all shadow views (:270-283)
     std::vector<uint32_t> require((size_t)n_lists, OVIS_CASTS_SHADOW);
     std::vector<long long> offsets;
-    OVIS_TRY(cull_views_device(w, n_lists, planes.data(), require.data(), nullptr, offsets));
+    OVIS_TRY(cull_views_grouped(w, n_lists, planes.data(), require.data(), groups, nullptr, offsets));
     int64_t total = offsets.empty() ? 0 : offsets[(size_t)n_lists];
     *out_n_lists = n_lists;
     *out_n_entities = total;

@@ -264,3 +264,76 @@ def test_multi_view_csr(oracle):
         exp = oracle.cull_aabb(boxes, planes[i], flags, int(require[i]))
         assert np.array_equal(ent[off[i]:off[i + 1]], exp)
     w.close()
+
+
+def test_shadow_lists_prefilter_is_conservative(oracle):
+    """The cube pre-filter in front of the exact shadow-view tests must never drop a pair the reference keeps:
+    giant boxes (the P-vertex test accepts them far outside the cube), skybox / infinite / NaN boxes, inverted
+    boxes, boxes hugging cube faces and corners, lights at large coordinates. More than 1024 views forces
+    several passes; removed entities and non-casters must stay out."""
+    rng = np.random.default_rng(39)
+    n = 30_000
+    boxes = util.random_boxes(rng, n, extent=300.0, hmax=4.0)
+    e = util.edge_boxes()
+    boxes[:len(e)] = e
+    big = rng.choice(n, 300, replace=False)
+    boxes[big] = util.random_boxes(rng, 300, extent=300.0, hmax=500.0)          # giant boxes
+    boxes[100] = [-1e6, -1e6, -1e6, 1e6, 1e6, 1e6]
+    boxes[101] = [5, 5, 5, -5, -5, -5]                                            # inverted
+    flags = (rng.random(n) < 0.7).astype(np.uint32)
+    flags[:len(e)] = 1
+    lights = scenes.point_lights(260, 77, 280.0, 5.0, 120.0)
+    lights["flags"][::7] = 0                                                       # some cast no shadows
+    spot = util.random_lights(rng, 30, extent=250.0)
+    spot["type"] = scenes.LIGHT_SPOT
+    spot["flags"] = 1
+    spot["intensity"] = 1.0
+    spot["colour"] = 1.0
+    lights = np.concatenate([lights, spot])
+    # boxes hugging the first light's cube faces / corners from outside and inside
+    p, r = lights["position"][0], lights["range"][0]
+    k = 200
+    for sx in (-1, 1):
+        for d in (0.999, 1.0, 1.001, 1.02):
+            c = p + np.array([sx * r * d, r * d * 0.99, -r * d])
+            boxes[k] = np.concatenate([c - 0.01, c + 0.01])
+            k += 1
+    w = _world_static(boxes, flags)
+    w.add_lights(lights)
+    removed = rng.choice(np.arange(300, n), 2000, replace=False).astype(np.uint32)
+    w.remove_entities(removed)
+    cam = scenes.make_view((0, 0, 900), (1, 0, 0, 0), 90.0, 0.1, 3000.0, 1600, 900)   # sees every light
+    got = w.shadow_lists(cam)
+    keep = np.ones(n, dtype=bool)
+    keep[removed] = False
+    oflags = flags * keep                                                             # a removed entity casts nothing
+    exp = oracle.shadow_lists(boxes, oflags, lights, oracle.view_planes(cam))
+    assert len(exp[0]) > 1024                                                         # several passes
+    for x, y in zip(got, exp):
+        assert np.array_equal(x, y)
+    w.close()
+
+
+def test_multi_view_many_views_and_empty(oracle):
+    rng = np.random.default_rng(40)
+    boxes = util.random_boxes(rng, 7001, extent=150.0)
+    flags = rng.integers(0, 2, len(boxes)).astype(np.uint32)
+    w = _world_static(boxes, flags)
+    views = util.random_views(rng, 40, extent=100.0)
+    planes = np.stack([oracle.view_planes(np.asarray(v)).reshape(24) for v in views])
+    require = rng.integers(0, 2, 40).astype(np.uint32)
+    off, d_off, d_ent = w.cull_views_device(planes, require)
+    ent = w.read_device(d_ent, int(off[-1]))
+    for i in range(len(views)):
+        assert np.array_equal(ent[off[i]:off[i + 1]], oracle.cull_aabb(boxes, planes[i], flags, int(require[i])))
+    # a second call reuses every scratch buffer
+    off2, _, d_ent2 = w.cull_views_device(planes[::-1].copy(), require[::-1].copy())
+    ent2 = w.read_device(d_ent2, int(off2[-1]))
+    for i in range(len(views)):
+        j = len(views) - 1 - i
+        assert np.array_equal(ent2[off2[i]:off2[i + 1]], ent[off[j]:off[j + 1]])
+    w.close()
+    w0 = lib.World(0)
+    off0, _, _ = w0.cull_views_device(planes[:3])
+    assert np.array_equal(off0, np.zeros(4, dtype=np.int64))
+    w0.close()
