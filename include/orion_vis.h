@@ -210,6 +210,16 @@ int ovis_cull_planes_noalloc(int device, void *cuda_stream, const float *d_world
 int ovis_cull_views_device(OvisWorld *world, int32_t n_views, const float *planes, const uint32_t *require,
                            const int64_t **d_offsets, const uint32_t **d_entities, int64_t *host_offsets);
 
+/* The shadow-view culls of prepareLights (deferred_render_pipeline.cc:259-284) for an explicit set of lights,
+ * regardless of their visibility: every shadow view (RenderLight::updateShadowViews, render_light.cc:258-332; six
+ * cube faces per point light, one per spot light, none otherwise or without OVIS_CASTS_SHADOW) is culled for
+ * castsShadow() entities in one multi-view pass set. List k belongs to light out_list_light[k], view
+ * out_list_view[k]; results stay on the device in CSR form as for ovis_cull_views_device (host_offsets optional,
+ * n_lists + 1 entries). OVIS_ERR_CAPACITY (with *out_n_lists = required) if cap_lists is too small. */
+int ovis_cull_shadow_views_device(OvisWorld *world, int32_t n_lights, const uint32_t *light_ids, int32_t shadow_map_resolution,
+                                  int32_t cap_lists, int32_t *out_list_light, int32_t *out_list_view, int32_t *out_n_lists,
+                                  const int64_t **d_offsets, const uint32_t **d_entities, int64_t *host_offsets);
+
 /* DeferredRenderPipeline::prepareLights' cull+filter loop (deferred_render_pipeline.cc:207,247,257-284):
  * for every light not culled by main_view that casts shadows (spot, point), one list per shadow view
  * holding the ids of the castsShadow() entities intersecting it. HOST output:

@@ -105,11 +105,13 @@ class Oracle:
 
     # ---- views
     def view_planes(self, view: np.ndarray) -> np.ndarray:
+        view = np.ascontiguousarray(view, dtype=VIEW_DTYPE)
         out = np.zeros(24, dtype=np.float32)
         self.lib.orc_view_planes(_p(view), _p(out))
         return out.reshape(6, 4)
 
     def view_matrices(self, view: np.ndarray):
+        view = np.ascontiguousarray(view, dtype=VIEW_DTYPE)
         mats = np.zeros(64, dtype=np.float32)
         corners = np.zeros(24, dtype=np.float32)
         self.lib.orc_view_matrices(_p(view), _p(mats), _p(corners))
@@ -153,6 +155,7 @@ class Oracle:
 
     # ---- lights
     def light_spot_aabb(self, light: np.ndarray) -> np.ndarray:
+        light = np.ascontiguousarray(light, dtype=LIGHT_DTYPE)
         out = np.zeros(6, dtype=np.float32)
         self.lib.orc_light_spot_aabb(_p(light), _p(out))
         return out
@@ -165,6 +168,7 @@ class Oracle:
         return out[:c].copy()
 
     def light_shadow_views(self, light: np.ndarray) -> np.ndarray:
+        light = np.ascontiguousarray(light, dtype=LIGHT_DTYPE)
         out = np.zeros(6, dtype=VIEW_DTYPE)
         c = self.lib.orc_light_shadow_views(_p(light), _p(out))
         return out[:c].copy()

@@ -676,6 +676,42 @@ int cull_views_grouped(OvisWorld *w, int32_t n_views, const float *planes, const
     return OVIS_OK;
 }
 
+// Shadow views (render_light.cc:258-332) of the given lights, culled for shadow casters (deferred_render_pipeline.cc:
+// 270-283) with K4; only spot and point lights have any (allocateShadowMap is fatal for the rest, :291-303).
+int shadow_views_device(OvisWorld *w, const std::vector<uint32_t> &light_ids, int32_t shadow_map_resolution,
+                        std::vector<int32_t> &list_light, std::vector<int32_t> &list_view, std::vector<long long> &offsets) {
+    std::vector<float> planes;
+    std::vector<ovis::ViewGroupDev> groups;
+    list_light.clear();
+    list_view.clear();
+    for (uint32_t id : light_ids) {
+        const OvisLight &l = w->lights[id];
+        OvisView views[6];
+        int count = ovis::hm::shadowViews(l, shadow_map_resolution, views);
+        if (count == 0)
+            continue;
+        ovis::ViewGroupDev g;
+        g.px = l.position[0]; g.py = l.position[1]; g.pz = l.position[2];
+        // A point light's six face frusta (fov 90, far = range, apex at the light) only accept boxes that overlap
+        // the cube of half-side range + box extent about the light; a spot light's single frustum gets no pre-filter.
+        g.r = (l.type == OVIS_LIGHT_POINT) ? l.range : std::numeric_limits<float>::infinity();
+        g.pmax = std::max(std::fabs(g.px), std::max(std::fabs(g.py), std::fabs(g.pz)));
+        g.first_view = (int)list_light.size();
+        g.n_views = count;
+        g.pad = 0;
+        groups.push_back(g);
+        for (int i = 0; i < count; i++) {
+            planes.resize(planes.size() + 24);
+            ovis::hm::viewPlanes(views[i], planes.data() + planes.size() - 24);
+            list_light.push_back((int32_t)id);
+            list_view.push_back(i);
+        }
+    }
+    int32_t n_lists = (int32_t)list_light.size();
+    std::vector<uint32_t> require((size_t)n_lists, OVIS_CASTS_SHADOW);
+    return cull_views_grouped(w, n_lists, planes.data(), require.data(), groups, nullptr, offsets);
+}
+
 // Views without a shared pre-filter: one group per view, infinite cube.
 int cull_views_device(OvisWorld *w, int32_t n_views, const float *planes, const uint32_t *require, int64_t *host_offsets_out,
                       std::vector<long long> &host_offsets) {
@@ -1191,6 +1227,35 @@ int ovis_cull_views_device(OvisWorld *w, int32_t n_views, const float *planes, c
     return OVIS_OK;
 }
 
+int ovis_cull_shadow_views_device(OvisWorld *w, int32_t n_lights, const uint32_t *light_ids, int32_t shadow_map_resolution,
+                                  int32_t cap_lists, int32_t *out_list_light, int32_t *out_list_view, int32_t *out_n_lists,
+                                  const int64_t **d_offsets, const uint32_t **d_entities, int64_t *host_offsets) {
+    if (!w || n_lights < 0 || (n_lights > 0 && !light_ids) || !out_n_lists || shadow_map_resolution <= 0)
+        return fail(OVIS_ERR_INVALID, "ovis_cull_shadow_views_device: bad arguments");
+    OVIS_TRY(use_device(w));
+    std::vector<uint32_t> ids(light_ids, light_ids + n_lights);
+    for (uint32_t id : ids)
+        if (id >= w->lights.size() || !w->light_alive[id])
+            return fail(OVIS_ERR_INVALID, "ovis_cull_shadow_views_device: unknown light %u", id);
+    std::vector<int32_t> list_light, list_view;
+    std::vector<long long> offsets;
+    OVIS_TRY(shadow_views_device(w, ids, shadow_map_resolution, list_light, list_view, offsets));
+    int32_t n_lists = (int32_t)list_light.size();
+    *out_n_lists = n_lists;
+    if (n_lists > cap_lists)
+        return fail(OVIS_ERR_CAPACITY, "shadow views need %d list slots, %d given", n_lists, cap_lists);
+    for (int32_t k = 0; k < n_lists; k++) {
+        if (out_list_light) out_list_light[k] = list_light[(size_t)k];
+        if (out_list_view) out_list_view[k] = list_view[(size_t)k];
+    }
+    if (host_offsets)
+        for (int32_t k = 0; k <= n_lists; k++)
+            host_offsets[k] = offsets[(size_t)k];
+    if (d_offsets) *d_offsets = (const int64_t *)w->d_csr_offsets;
+    if (d_entities) *d_entities = w->d_csr_entities;
+    return OVIS_OK;
+}
+
 int ovis_build_shadow_lists(OvisWorld *w, const OvisView *main_view, int32_t shadow_map_resolution,
                             int32_t cap_lists, int32_t *out_list_light, int32_t *out_list_view,
                             int64_t *out_offsets, int32_t *out_n_lists,
@@ -1210,39 +1275,11 @@ int ovis_build_shadow_lists(OvisWorld *w, const OvisView *main_view, int32_t sha
         OVIS_CUDA(cudaMemcpyAsync(visible.data(), w->d_light_out, 4 * visible.size(), cudaMemcpyDeviceToHost, w->stream));
         OVIS_CUDA(cudaStreamSynchronize(w->stream));
     }
-    // 2. their shadow views (render_light.cc:258-332); only spot and point lights reach the cull
-    //    (allocateShadowMap is fatal for the rest, deferred_render_pipeline.cc:291-303)
-    std::vector<float> planes;
+    // 2.+3. their shadow views, culled for shadow casters in one multi-view pass set
     std::vector<int32_t> list_light, list_view;
-    std::vector<ovis::ViewGroupDev> groups;
-    for (uint32_t id : visible) {
-        const OvisLight &l = w->lights[id];
-        OvisView views[6];
-        int count = ovis::hm::shadowViews(l, shadow_map_resolution, views);
-        if (count == 0)
-            continue;
-        ovis::ViewGroupDev g;
-        g.px = l.position[0]; g.py = l.position[1]; g.pz = l.position[2];
-        // A point light's six face frusta (fov 90, far = range) lie inside the cube of half-side `range` about the
-        // light; a spot light's single frustum gets no pre-filter.
-        g.r = (l.type == OVIS_LIGHT_POINT) ? l.range : std::numeric_limits<float>::infinity();
-        g.pmax = std::max(std::fabs(g.px), std::max(std::fabs(g.py), std::fabs(g.pz)));
-        g.first_view = (int)list_light.size();
-        g.n_views = count;
-        g.pad = 0;
-        groups.push_back(g);
-        for (int i = 0; i < count; i++) {
-            planes.resize(planes.size() + 24);
-            ovis::hm::viewPlanes(views[i], planes.data() + planes.size() - 24);
-            list_light.push_back((int32_t)id);
-            list_view.push_back(i);
-        }
-    }
-    int32_t n_lists = (int32_t)list_light.size();
-    // 3. one caster-filtered multi-view pass over the bounds for all shadow views (:270-283)
-    std::vector<uint32_t> require((size_t)n_lists, OVIS_CASTS_SHADOW);
     std::vector<long long> offsets;
-    OVIS_TRY(cull_views_grouped(w, n_lists, planes.data(), require.data(), groups, nullptr, offsets));
+    OVIS_TRY(shadow_views_device(w, visible, shadow_map_resolution, list_light, list_view, offsets));
+    int32_t n_lists = (int32_t)list_light.size();
     int64_t total = offsets.empty() ? 0 : offsets[(size_t)n_lists];
     *out_n_lists = n_lists;
     *out_n_entities = total;

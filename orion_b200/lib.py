@@ -308,6 +308,21 @@ class World:
                                                C.byref(d_ent), _p(host)))
         return host, d_off.value, d_ent.value
 
+    def cull_shadow_views_device(self, light_ids, shadow_res=512):
+        """Shadow-view culls of the given lights -> (list_light, list_view, host offsets, d_offsets, d_entities)."""
+        light_ids = _u32(light_ids)
+        cap = 6 * max(len(light_ids), 1)
+        ll = np.zeros(cap, dtype=np.int32)
+        lv = np.zeros(cap, dtype=np.int32)
+        off = np.zeros(cap + 1, dtype=np.int64)
+        n = C.c_int32()
+        d_off, d_ent = C.c_void_p(), C.c_void_p()
+        _check(self.lib.ovis_cull_shadow_views_device(self.h, C.c_int32(len(light_ids)), _p(light_ids), C.c_int32(shadow_res),
+                                                      C.c_int32(cap), _p(ll), _p(lv), C.byref(n), C.byref(d_off),
+                                                      C.byref(d_ent), _p(off)))
+        k = n.value
+        return ll[:k].copy(), lv[:k].copy(), off[:k + 1].copy(), d_off.value, d_ent.value
+
     def shadow_lists(self, main_view, shadow_res=512):
         """prepareLights' per-shadow-view caster lists -> (list_light, list_view, offsets, entities)."""
         main_view = np.ascontiguousarray(main_view, dtype=VIEW_DTYPE)
