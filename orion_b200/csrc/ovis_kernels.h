@@ -64,11 +64,9 @@ struct GatherArgs {               // K3b
 constexpr int kMultiMaxViews = 1024;          // views per pass (one CTA of 1024 threads scans them)
 
 struct ViewGroupDev {
-    float px, py, pz;            // centre of the pre-filter cube (a point light's position)
-    float r;                     // half-side before inflation (the light's range); +inf = no pre-filter
-    float pmax;                  // largest |coordinate| of the centre (for the rounding margin)
+    float lo[3], hi[3];          // the group's pre-filter cube, already inflated by its rounding margin
+                                 // (centre -/+ (1.001 * range + 1e-3 * max|centre| + 0.01)); -inf/+inf = no pre-filter
     int first_view, n_views;     // consecutive views of the pass that share this cube
-    int pad;
 };
 
 struct MultiArgs {
@@ -85,13 +83,14 @@ struct MultiArgs {
     int n_views;
     uint32_t *counts;            // [num_tiles][n_views]: counts after pass A, positions after the scans
     uint32_t *block_totals;      // [num_blocks][n_views], zero before pass A
+    uint32_t *group_hits;        // [num_tiles][ceil(n_groups / 32)]: bit = group had a candidate (A writes, C reads)
     const long long *csr_offsets;// [n_views + 1] start of each view's list (valid after the scans)
     uint32_t *out;
     long long capacity;
     uint32_t id_base;
 };
 
-int multi_max_blocks_per_sm(int n_views);
+int multi_max_blocks_per_sm(int n_views, int n_groups);
 void launch_multi_pass(const MultiArgs &a, bool write, int grid, cudaStream_t s);
 void launch_multi_scans(const MultiArgs &a, long long *csr_offsets_of_pass, cudaStream_t s);
 

@@ -7,15 +7,16 @@
 // cube of half-side `range` about the light); a group without a cube has an infinite radius. Per pass (at most
 // kMultiMaxViews views):
 //
-//   A  multi_pass_kernel<false>  every warp walks "supertiles" of 1024 consecutive entities (4 x 256): loads the bounds
-//                                 once, and for every group runs the cube pre-filter (12 instructions per entity) and,
+//   A  multi_pass_kernel<false>  every warp walks "supertiles" of 1024 consecutive entities (8 x 128): loads the bounds
+//                                 once, and for every group runs the cube pre-filter (6 compares per entity) and,
 //                                 only where a candidate exists in the warp, the exact six-plane tests of its views with
 //                                 warp-uniform early-out. It counts survivors per (supertile, view): one coalesced row of
 //                                 counts per supertile plus sparse integer atomicAdds into per-(64-supertile block, view)
-//                                 totals.
+//                                 totals, and a bit per (supertile, group) that had any candidate.
 //   B1 multi_scan_blocks_kernel  per view: exclusive scan of the block totals, view totals, CSR offsets of the pass.
 //   B2 multi_scan_tiles_kernel   per block: exclusive scan over its 64 supertiles, in place (counts -> positions).
-//   C  multi_pass_kernel<true>   the same walk again, now writing each survivor id at its final position.
+//   C  multi_pass_kernel<true>   the same walk again over the groups that had candidates, now writing each survivor id
+//                                 at its final position.
 //
 // Positions are sums of counts, so every list is in slot (= insertion) order and identical from run to run. The exact
 // tests are the same instructions as K3 (ovis_device.cuh: outside_plane), so lists are bit-identical to brute force;
@@ -27,16 +28,21 @@
 
 namespace ovis {
 
-constexpr int kSuperTile = 1024;                 // entities per supertile (one warp, 4 sub-tiles of 256)
-constexpr int kSubTiles = 4;
+constexpr int kSuperTile = 1024;                 // entities per supertile (one warp, 8 sub-tiles of 128)
+constexpr int kSubTiles = 8;
 constexpr int kMultiWarps = 8;                   // warps per CTA
 
+// Shared memory per warp: n_views survivor counters + ceil(n_groups / 32) "this group had a candidate" words.
+__host__ __device__ inline int multi_words_per_warp(int n_views, int n_groups) { return n_views + (n_groups + 31) / 32; }
+
 template <bool WRITE>
-__global__ void __launch_bounds__(kMultiWarps * 32, 2)
+__global__ void __launch_bounds__(kMultiWarps * 32, 3)
 multi_pass_kernel(const __grid_constant__ MultiArgs a) {
-    extern __shared__ uint32_t s_counters[];     // kMultiWarps x n_views: survivors so far in this supertile, per view
+    extern __shared__ uint32_t s_words[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    uint32_t *counters = s_counters + warp * a.n_views;
+    const int hit_words = (a.n_groups + 31) / 32;
+    uint32_t *counters = s_words + warp * multi_words_per_warp(a.n_views, a.n_groups);   // survivors so far, per view
+    uint32_t *hits = counters + a.n_views;                                                // groups with a candidate
     const int warps_total = gridDim.x * kMultiWarps;
     const float4 *__restrict__ bounds = reinterpret_cast<const float4 *>(a.bounds);
     const int64_t vstride = a.stride >> 2;
@@ -44,127 +50,155 @@ multi_pass_kernel(const __grid_constant__ MultiArgs a) {
     for (int tile = blockIdx.x * kMultiWarps + warp; tile < a.num_tiles; tile += warps_total) {
         for (int v = lane; v < a.n_views; v += 32)
             counters[v] = 0u;
+        // pass A finds which groups have any candidate in this supertile; pass C only revisits those
+        for (int k = lane; k < hit_words; k += 32)
+            hits[k] = WRITE ? a.group_hits[(int64_t)tile * hit_words + k] : 0u;
         __syncwarp();
         const uint32_t *row = WRITE ? a.counts + (int64_t)tile * a.n_views : nullptr;   // positions after pass B2
 
         for (int sub = 0; sub < kSubTiles; sub++) {
-            // ---- load 8 entities per lane (two float4 groups), as K3 does
-            float mn[3][8], mx[3][8];
-            uint32_t alive = 0xffu, caster = 0xffu;
-            uint32_t ebase[2];
-#pragma unroll
-            for (int g = 0; g < 2; g++) {
-                const int64_t v = (int64_t)tile * (kSuperTile / 4) + sub * 64 + g * 32 + lane;    // float4 index
-                const int64_t e0 = v << 2;
-                ebase[g] = (uint32_t)e0;
-                const float4 ax = __ldg(bounds + 0 * vstride + v), ay = __ldg(bounds + 1 * vstride + v), az = __ldg(bounds + 2 * vstride + v);
-                const float4 bx = __ldg(bounds + 3 * vstride + v), by = __ldg(bounds + 4 * vstride + v), bz = __ldg(bounds + 5 * vstride + v);
-                mn[0][4 * g + 0] = ax.x; mn[0][4 * g + 1] = ax.y; mn[0][4 * g + 2] = ax.z; mn[0][4 * g + 3] = ax.w;
-                mn[1][4 * g + 0] = ay.x; mn[1][4 * g + 1] = ay.y; mn[1][4 * g + 2] = ay.z; mn[1][4 * g + 3] = ay.w;
-                mn[2][4 * g + 0] = az.x; mn[2][4 * g + 1] = az.y; mn[2][4 * g + 2] = az.z; mn[2][4 * g + 3] = az.w;
-                mx[0][4 * g + 0] = bx.x; mx[0][4 * g + 1] = bx.y; mx[0][4 * g + 2] = bx.z; mx[0][4 * g + 3] = bx.w;
-                mx[1][4 * g + 0] = by.x; mx[1][4 * g + 1] = by.y; mx[1][4 * g + 2] = by.z; mx[1][4 * g + 3] = by.w;
-                mx[2][4 * g + 0] = bz.x; mx[2][4 * g + 1] = bz.y; mx[2][4 * g + 2] = bz.z; mx[2][4 * g + 3] = bz.w;
-                uint32_t valid = 0xfu;
-                if (e0 + 3 >= a.n) {
-                    int64_t left = a.n - e0;
-                    valid = left <= 0 ? 0u : ((1u << left) - 1u);
-                }
-                uint32_t al = valid, ca = valid;
-                if (a.alive_mask)
-                    al &= (__ldg(a.alive_mask + (e0 >> 5)) >> (e0 & 31)) & 0xfu;
-                if (a.caster_mask)
-                    ca &= (__ldg(a.caster_mask + (e0 >> 5)) >> (e0 & 31)) & 0xfu;       // caster mask already implies alive
-                else
-                    ca = al;
-                alive = (alive & ~(0xfu << (4 * g))) | (al << (4 * g));
-                caster = (caster & ~(0xfu << (4 * g))) | (ca << (4 * g));
+            // ---- 4 consecutive entities per lane: six 128-bit loads
+            const int64_t v = (int64_t)tile * (kSuperTile / 4) + sub * 32 + lane;        // float4 index
+            const int64_t e0 = v << 2;
+            const float4 ax = __ldg(bounds + 0 * vstride + v), ay = __ldg(bounds + 1 * vstride + v), az = __ldg(bounds + 2 * vstride + v);
+            const float4 bx = __ldg(bounds + 3 * vstride + v), by = __ldg(bounds + 4 * vstride + v), bz = __ldg(bounds + 5 * vstride + v);
+            const float mn[3][4] = { { ax.x, ax.y, ax.z, ax.w }, { ay.x, ay.y, ay.z, ay.w }, { az.x, az.y, az.z, az.w } };
+            const float mx[3][4] = { { bx.x, bx.y, bx.z, bx.w }, { by.x, by.y, by.z, by.w }, { bz.x, bz.y, bz.z, bz.w } };
+            uint32_t alive = 0xfu;
+            if (e0 + 3 >= a.n) {
+                int64_t left = a.n - e0;
+                alive = left <= 0 ? 0u : ((1u << left) - 1u);
             }
+            uint32_t caster = alive;
+            if (a.alive_mask)
+                alive &= (__ldg(a.alive_mask + (e0 >> 5)) >> (e0 & 31)) & 0xfu;
+            if (a.caster_mask)
+                caster &= (__ldg(a.caster_mask + (e0 >> 5)) >> (e0 & 31)) & 0xfu;          // already implies alive
+            else
+                caster = alive;
             if (!__any_sync(0xffffffffu, alive))
                 continue;
 
-            // ---- per-entity terms of the pre-filter: largest extent and largest coordinate magnitude
-            float ext[8], mag[8];
+            // ---- K6 pre-filter, entity side: the box inflated by Re = 1.001 * largest extent + 1e-3 * largest
+            //      |coordinate|. A box with a NaN or non-finite side gets Re = +inf and can never be rejected.
+            float lo[3][4], hi[3][4];
+            bool lane_odd = false;
 #pragma unroll
-            for (int j = 0; j < 8; j++) {
+            for (int j = 0; j < 4; j++) {
                 const float sx = mx[0][j] - mn[0][j], sy = mx[1][j] - mn[1][j], sz = mx[2][j] - mn[2][j];
-                ext[j] = fmaxf(fmaxf(fmaxf(sx, sy), sz), 0.0f);
-                mag[j] = fmaxf(fmaxf(fmaxf(fabsf(mn[0][j]), fabsf(mx[0][j])), fmaxf(fabsf(mn[1][j]), fabsf(mx[1][j]))),
-                               fmaxf(fabsf(mn[2][j]), fabsf(mx[2][j])));
-                // fmaxf drops NaNs: a box with a NaN or non-finite side must never be filtered out
-                const bool odd = sx != sx || sy != sy || sz != sz || !(ext[j] <= 3.0e38f) || !(mag[j] <= 3.0e38f);
+                const float ext = fmaxf(fmaxf(fmaxf(sx, sy), sz), 0.0f);
+                const float mag = fmaxf(fmaxf(fmaxf(fabsf(mn[0][j]), fabsf(mx[0][j])), fmaxf(fabsf(mn[1][j]), fabsf(mx[1][j]))),
+                                        fmaxf(fabsf(mn[2][j]), fabsf(mx[2][j])));
+                float re = ext * 1.001f + mag * 1.0e-3f;
+                const bool odd = sx != sx || sy != sy || sz != sz || !(ext <= 3.0e38f) || !(mag <= 3.0e38f);   // fmaxf drops NaNs
                 if (odd)
-                    ext[j] = __int_as_float(0x7f800000);     // +inf: the cube test below can then never reject
-            }
-
-            for (int gi = 0; gi < a.n_groups; gi++) {
-                const ViewGroupDev grp = a.groups[gi];
-                // ---- K6 pre-filter: candidate iff the box overlaps the cube of half-side (range + extent + margin)
-                uint32_t cand = 0;
+                    re = __int_as_float(0x7f800000);
+                lane_odd |= odd;
 #pragma unroll
-                for (int j = 0; j < 8; j++) {
-                    const float R = (grp.r + ext[j]) * 1.001f + (grp.pmax + mag[j]) * 1.0e-3f + 1.0e-2f;
-                    const bool out = (mx[0][j] < grp.px - R) | (mn[0][j] > grp.px + R) | (mx[1][j] < grp.py - R) |
-                                     (mn[1][j] > grp.py + R) | (mx[2][j] < grp.pz - R) | (mn[2][j] > grp.pz + R);
-                    cand |= out ? 0u : (1u << j);
+                for (int c = 0; c < 3; c++) {
+                    lo[c][j] = mn[c][j] - re;
+                    hi[c][j] = mx[c][j] + re;
                 }
-                cand &= alive;
-                if (!__any_sync(0xffffffffu, cand))
-                    continue;
+            }
+            // ---- union of the warp's 128 inflated boxes: a group whose cube misses it has no candidate in this
+            //      sub-tile (scenes laid out by their hierarchy keep neighbours in space next to each other in memory)
+            float ulo[3], uhi[3];
+#pragma unroll
+            for (int c = 0; c < 3; c++) {
+                ulo[c] = fminf(fminf(lo[c][0], lo[c][1]), fminf(lo[c][2], lo[c][3]));
+                uhi[c] = fmaxf(fmaxf(hi[c][0], hi[c][1]), fmaxf(hi[c][2], hi[c][3]));
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) {
+                    ulo[c] = fminf(ulo[c], __shfl_xor_sync(0xffffffffu, ulo[c], o));
+                    uhi[c] = fmaxf(uhi[c], __shfl_xor_sync(0xffffffffu, uhi[c], o));
+                }
+            }
+            const bool warp_odd = __any_sync(0xffffffffu, lane_odd);      // fminf/fmaxf drop NaNs: then test every group
 
-                for (int vi = 0; vi < grp.n_views; vi++) {
-                    const int view = grp.first_view + vi;
-                    uint32_t keep = a.view_require[view] ? (cand & caster) : cand;
-                    const float4 *pl = a.planes + 6 * view;
-#pragma unroll 1
-                    for (int p = 0; p < 6; p++) {
-                        if (!__any_sync(0xffffffffu, keep))
-                            break;
-                        const float4 q = __ldg(pl + p);
-#pragma unroll
-                        for (int j = 0; j < 8; j++)
-                            if (outside_plane(q.x, q.y, q.z, q.w, mn[0][j], mn[1][j], mn[2][j], mx[0][j], mx[1][j], mx[2][j]))
-                                keep &= ~(1u << j);
+            for (int gw = 0; gw < hit_words; gw++) {
+                // lane-parallel: lane L tests group gw*32 + L against the union box
+                bool near = false;
+                {
+                    const int gl = gw * 32 + lane;
+                    if (gl < a.n_groups) {
+                        const ViewGroupDev gq = a.groups[gl];
+                        near = warp_odd || !((uhi[0] < gq.lo[0]) | (ulo[0] > gq.hi[0]) | (uhi[1] < gq.lo[1]) |
+                                             (ulo[1] > gq.hi[1]) | (uhi[2] < gq.lo[2]) | (ulo[2] > gq.hi[2]));
                     }
-                    if (!__any_sync(0xffffffffu, keep))
+                }
+                uint32_t todo = __ballot_sync(0xffffffffu, near);
+                if (WRITE)
+                    todo &= hits[gw];
+                uint32_t found = 0;
+                while (todo) {
+                    const int bit = __ffs(todo) - 1;
+                    todo &= todo - 1;
+                    const int gi = gw * 32 + bit;
+                    const ViewGroupDev grp = a.groups[gi];
+                    // ---- group side: candidate iff the inflated box overlaps the group's (inflated) cube
+                    uint32_t cand = 0;
+#pragma unroll
+                    for (int j = 0; j < 4; j++) {
+                        const bool out = (hi[0][j] < grp.lo[0]) | (lo[0][j] > grp.hi[0]) | (hi[1][j] < grp.lo[1]) |
+                                         (lo[1][j] > grp.hi[1]) | (hi[2][j] < grp.lo[2]) | (lo[2][j] > grp.hi[2]);
+                        cand |= out ? 0u : (1u << j);
+                    }
+                    cand &= alive;
+                    if (!__any_sync(0xffffffffu, cand))
                         continue;
-                    // ---- rank in slot order: group 0 of all lanes comes before group 1 of all lanes
-                    const uint32_t c0 = __popc(keep & 0xfu), c1 = __popc(keep >> 4);
-                    uint32_t i0 = c0, i1 = c1;
+                    found |= 1u << bit;
+
+                    for (int vi = 0; vi < grp.n_views; vi++) {
+                        const int view = grp.first_view + vi;
+                        uint32_t keep = a.view_require[view] ? (cand & caster) : cand;
+                        const float4 *pl = a.planes + 6 * view;
 #pragma unroll
-                    for (int o = 1; o < 32; o <<= 1) {
-                        uint32_t u0 = __shfl_up_sync(0xffffffffu, i0, o), u1 = __shfl_up_sync(0xffffffffu, i1, o);
-                        if (lane >= o) { i0 += u0; i1 += u1; }
+                        for (int p = 0; p < 6; p++) {
+                            if ((p == 2 || p == 4) && !__any_sync(0xffffffffu, keep))     // warp-uniform early-out
+                                break;
+                            const float4 q = __ldg(pl + p);
+#pragma unroll
+                            for (int j = 0; j < 4; j++)
+                                if (outside_plane(q.x, q.y, q.z, q.w, mn[0][j], mn[1][j], mn[2][j], mx[0][j], mx[1][j], mx[2][j]))
+                                    keep &= ~(1u << j);
+                        }
+                        if (!__any_sync(0xffffffffu, keep))
+                            continue;
+                        // ---- rank in slot order inside the sub-tile
+                        const uint32_t c = __popc(keep);
+                        uint32_t incl = c;
+#pragma unroll
+                        for (int o = 1; o < 32; o <<= 1) {
+                            uint32_t up = __shfl_up_sync(0xffffffffu, incl, o);
+                            if (lane >= o)
+                                incl += up;
+                        }
+                        const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
+                        if (WRITE) {
+                            long long pos = a.csr_offsets[view] + (long long)row[view] + counters[view] + (incl - c);
+#pragma unroll
+                            for (int j = 0; j < 4; j++)
+                                if (keep & (1u << j)) {
+                                    if (pos < a.capacity) a.out[pos] = (uint32_t)e0 + j + a.id_base;
+                                    pos++;
+                                }
+                        }
+                        __syncwarp();
+                        if (lane == 0)
+                            counters[view] += total;
+                        __syncwarp();
                     }
-                    const uint32_t t0 = __shfl_sync(0xffffffffu, i0, 31), t1 = __shfl_sync(0xffffffffu, i1, 31);
-                    if (WRITE) {
-                        const uint32_t before = counters[view];
-                        const long long base = a.csr_offsets[view] + (long long)row[view] + before;
-                        long long pos = base + (i0 - c0);
-#pragma unroll
-                        for (int j = 0; j < 4; j++)
-                            if (keep & (1u << j)) {
-                                if (pos < a.capacity) a.out[pos] = ebase[0] + j + a.id_base;
-                                pos++;
-                            }
-                        pos = base + t0 + (i1 - c1);
-#pragma unroll
-                        for (int j = 0; j < 4; j++)
-                            if (keep & (16u << j)) {
-                                if (pos < a.capacity) a.out[pos] = ebase[1] + j + a.id_base;
-                                pos++;
-                            }
-                    }
-                    __syncwarp();
+                }
+                if (!WRITE && found) {
                     if (lane == 0)
-                        counters[view] += t0 + t1;
+                        hits[gw] |= found;
                     __syncwarp();
                 }
             }
         }
 
         if (!WRITE) {
-            // one coalesced row of counts per supertile, and sparse adds into the block totals
+            // one coalesced row of counts per supertile, sparse adds into the block totals, and the group hits
             uint32_t *out_row = a.counts + (int64_t)tile * a.n_views;
             uint32_t *totals = a.block_totals + (int64_t)(tile / kGatherTiles) * a.n_views;
             __syncwarp();
@@ -174,6 +208,8 @@ multi_pass_kernel(const __grid_constant__ MultiArgs a) {
                 if (c)
                     atomicAdd(totals + v, c);
             }
+            for (int k = lane; k < hit_words; k += 32)
+                a.group_hits[(int64_t)tile * hit_words + k] = hits[k];
         }
         __syncwarp();
     }
@@ -187,11 +223,17 @@ multi_scan_blocks_kernel(uint32_t *block_totals, int num_blocks, int n_views, lo
     const int v = threadIdx.x, lane = v & 31, warp = v >> 5;
     uint32_t running = 0;
     if (v < n_views) {
-        for (int b = 0; b < num_blocks; b++) {
-            uint32_t *p = block_totals + (int64_t)b * n_views + v;
-            uint32_t c = *p;
-            *p = running;
-            running += c;
+        for (int b0 = 0; b0 < num_blocks; b0 += 8) {            // 8 independent loads in flight, then the prefix
+            uint32_t c[8];
+#pragma unroll
+            for (int k = 0; k < 8; k++)
+                c[k] = (b0 + k < num_blocks) ? block_totals[(int64_t)(b0 + k) * n_views + v] : 0u;
+#pragma unroll
+            for (int k = 0; k < 8; k++) {
+                if (b0 + k < num_blocks)
+                    block_totals[(int64_t)(b0 + k) * n_views + v] = running;
+                running += c[k];
+            }
         }
     }
     // inclusive scan of the view totals across the CTA
@@ -224,23 +266,29 @@ multi_scan_tiles_kernel(uint32_t *counts, const uint32_t *block_totals, int num_
     const int b = blockIdx.x;
     uint32_t running = block_totals[(int64_t)b * n_views + v];
     const int t1 = min(num_tiles, (b + 1) * kGatherTiles);
-    for (int t = b * kGatherTiles; t < t1; t++) {
-        uint32_t *p = counts + (int64_t)t * n_views + v;
-        uint32_t c = *p;
-        *p = running;
-        running += c;
+    for (int t0 = b * kGatherTiles; t0 < t1; t0 += 8) {
+        uint32_t c[8];
+#pragma unroll
+        for (int k = 0; k < 8; k++)
+            c[k] = (t0 + k < t1) ? counts[(int64_t)(t0 + k) * n_views + v] : 0u;
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+            if (t0 + k < t1)
+                counts[(int64_t)(t0 + k) * n_views + v] = running;
+            running += c[k];
+        }
     }
 }
 
-int multi_max_blocks_per_sm(int n_views) {
+int multi_max_blocks_per_sm(int n_views, int n_groups) {
     int blocks = 0;
-    size_t smem = sizeof(uint32_t) * kMultiWarps * (size_t)n_views;
+    size_t smem = sizeof(uint32_t) * kMultiWarps * (size_t)multi_words_per_warp(n_views, n_groups);
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks, multi_pass_kernel<false>, kMultiWarps * 32, smem);
     return blocks;
 }
 
 void launch_multi_pass(const MultiArgs &a, bool write, int grid, cudaStream_t s) {
-    size_t smem = sizeof(uint32_t) * kMultiWarps * (size_t)a.n_views;
+    size_t smem = sizeof(uint32_t) * kMultiWarps * (size_t)multi_words_per_warp(a.n_views, a.n_groups);
     if (write)
         multi_pass_kernel<true><<<grid, kMultiWarps * 32, smem, s>>>(a);
     else

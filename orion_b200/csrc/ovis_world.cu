@@ -131,6 +131,8 @@ struct OvisWorld {
     int64_t cap_mv_views = 0;
     ovis::ViewGroupDev *d_mv_groups = nullptr;
     int64_t cap_mv_groups = 0;
+    uint32_t *d_mv_hits = nullptr;        // [supertiles][group words of a pass]
+    int64_t cap_mv_hits = 0;
 
     // ---- optional per-kernel timing of the entity cull (bench / profiling hook)
     bool timing = false;
@@ -544,6 +546,32 @@ int enqueue_light_cull(OvisWorld *w, const float planes[24]) {
     return OVIS_OK;
 }
 
+// Pre-filter cube of a view group (nullptr centre = none). The entity side adds its own extent and margin in the kernel.
+ovis::ViewGroupDev make_group(const float *centre, float range, int first_view, int n_views) {
+    ovis::ViewGroupDev g;
+    const float inf = std::numeric_limits<float>::infinity();
+    for (int c = 0; c < 3; c++) {
+        g.lo[c] = -inf;
+        g.hi[c] = inf;
+    }
+    if (centre) {
+        float pmax = std::max(std::fabs(centre[0]), std::max(std::fabs(centre[1]), std::fabs(centre[2])));
+        float rg = range * 1.001f + pmax * 1.0e-3f + 1.0e-2f;
+        for (int c = 0; c < 3; c++) {
+            g.lo[c] = centre[c] - rg;
+            g.hi[c] = centre[c] + rg;
+        }
+        if (!(rg == rg) || !(pmax == pmax))            // NaN light: no filtering
+            for (int c = 0; c < 3; c++) {
+                g.lo[c] = -inf;
+                g.hi[c] = inf;
+            }
+    }
+    g.first_view = first_view;
+    g.n_views = n_views;
+    return g;
+}
+
 // K4: all views of `groups` in passes of at most kMultiMaxViews views; result in w->d_csr_* (CSR, device).
 int cull_views_grouped(OvisWorld *w, int32_t n_views, const float *planes, const uint32_t *require,
                        const std::vector<ovis::ViewGroupDev> &groups, int64_t *host_offsets_out,
@@ -607,6 +635,15 @@ int cull_views_grouped(OvisWorld *w, int32_t n_views, const float *planes, const
         OVIS_TRY(grow(w->d_mv_totals, 0, (int64_t)num_blocks * pass_views, w->stream, false));
         w->cap_mv_totals = (int64_t)num_blocks * pass_views;
     }
+    {
+        int64_t max_words = 1;
+        for (const Pass &p : passes)
+            max_words = std::max<int64_t>(max_words, (int64_t)(p.g1 - p.g0 + 31) / 32);
+        if ((int64_t)num_tiles * max_words > w->cap_mv_hits) {
+            OVIS_TRY(grow(w->d_mv_hits, 0, (int64_t)num_tiles * max_words, w->stream, false));
+            w->cap_mv_hits = (int64_t)num_tiles * max_words;
+        }
+    }
     if (n_views > w->cap_mv_views) {
         OVIS_TRY(grow(w->d_mv_planes, 0, 24 * (int64_t)n_views, w->stream, false));
         OVIS_TRY(grow(w->d_mv_require, 0, (int64_t)n_views, w->stream, false));
@@ -646,12 +683,13 @@ int cull_views_grouped(OvisWorld *w, int32_t n_views, const float *planes, const
             a.n_views = p.v1 - p.v0;
             a.counts = w->d_mv_counts;
             a.block_totals = w->d_mv_totals;
+            a.group_hits = w->d_mv_hits;
             a.csr_offsets = w->d_csr_offsets + p.v0;
             a.out = w->d_csr_entities;
             a.capacity = w->cap_csr;
             a.id_base = w->id_base;
             OVIS_CUDA(cudaMemsetAsync(w->d_mv_totals, 0, sizeof(uint32_t) * (size_t)num_blocks * (size_t)a.n_views, w->stream));
-            int per_sm = std::max(1, ovis::multi_max_blocks_per_sm(a.n_views));
+            int per_sm = std::max(1, ovis::multi_max_blocks_per_sm(a.n_views, a.n_groups));
             int grid = std::min((num_tiles + 7) / 8, w->num_sms * per_sm);
             ovis::launch_multi_pass(a, false, grid, w->stream);
             ovis::launch_multi_scans(a, w->d_csr_offsets + p.v0, w->stream);
@@ -690,16 +728,9 @@ int shadow_views_device(OvisWorld *w, const std::vector<uint32_t> &light_ids, in
         int count = ovis::hm::shadowViews(l, shadow_map_resolution, views);
         if (count == 0)
             continue;
-        ovis::ViewGroupDev g;
-        g.px = l.position[0]; g.py = l.position[1]; g.pz = l.position[2];
         // A point light's six face frusta (fov 90, far = range, apex at the light) only accept boxes that overlap
         // the cube of half-side range + box extent about the light; a spot light's single frustum gets no pre-filter.
-        g.r = (l.type == OVIS_LIGHT_POINT) ? l.range : std::numeric_limits<float>::infinity();
-        g.pmax = std::max(std::fabs(g.px), std::max(std::fabs(g.py), std::fabs(g.pz)));
-        g.first_view = (int)list_light.size();
-        g.n_views = count;
-        g.pad = 0;
-        groups.push_back(g);
+        groups.push_back(make_group(l.type == OVIS_LIGHT_POINT ? l.position : nullptr, l.range, (int)list_light.size(), count));
         for (int i = 0; i < count; i++) {
             planes.resize(planes.size() + 24);
             ovis::hm::viewPlanes(views[i], planes.data() + planes.size() - 24);
@@ -717,13 +748,7 @@ int cull_views_device(OvisWorld *w, int32_t n_views, const float *planes, const 
                       std::vector<long long> &host_offsets) {
     std::vector<ovis::ViewGroupDev> groups((size_t)n_views);
     for (int32_t v = 0; v < n_views; v++) {
-        ovis::ViewGroupDev &g = groups[(size_t)v];
-        g.px = g.py = g.pz = 0.0f;
-        g.r = std::numeric_limits<float>::infinity();
-        g.pmax = 0.0f;
-        g.first_view = v;
-        g.n_views = 1;
-        g.pad = 0;
+        groups[(size_t)v] = make_group(nullptr, 0.0f, v, 1);
     }
     return cull_views_grouped(w, n_views, planes, require, groups, host_offsets_out, host_offsets);
 }
@@ -788,7 +813,7 @@ int ovis_world_destroy(OvisWorld *w) {
     void *bufs[] = { w->d_local, w->d_world, w->d_alive_bits, w->d_caster_bits, w->d_parent, w->d_local_trs, w->d_world_trs,
                      w->d_node_entity, w->d_extra_entity, w->d_extra_node, w->d_level_lists, w->d_lights, w->d_light_out,
                      w->d_staging, w->d_tile_counts, w->d_block_totals, w->d_mv_counts, w->d_mv_totals, w->d_mv_planes,
-                     w->d_mv_require, w->d_mv_groups, w->d_result, w->d_counts, w->d_csr_entities, w->d_csr_offsets,
+                     w->d_mv_require, w->d_mv_groups, w->d_mv_hits, w->d_result, w->d_counts, w->d_csr_entities, w->d_csr_offsets,
                      w->d_stage[0], w->d_stage[1] };
     for (void *b : bufs)
         if (b)
