@@ -238,6 +238,8 @@ def config2_extra(torch, lib, stream, scratch, peak_gbs):
 
 
 def run_ours(args, rank: int, local_rank: int, world_size: int):
+    if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
+        os.environ["NCCL_DEBUG"] = "WARN"          # keep NCCL's version banner off stdout: one JSON line only
     import torch
     import torch.distributed as dist
     from orion_b200 import lib
@@ -267,7 +269,7 @@ def run_ours(args, rank: int, local_rank: int, world_size: int):
     world.reserve(n_entities=n)
     first = world.add_entities(aabb, flags)
     world.set_world_aabbs(first, aabb)
-    sw = ShardedWorld(world, rank, world_size, rank * n, n, stream=stream)
+    sw = ShardedWorld(world, rank, world_size, rank * n, n, stream=stream, exchange=args.exchange)
 
     def barrier():
         torch.cuda.synchronize()
@@ -277,7 +279,8 @@ def run_ours(args, rank: int, local_rank: int, world_size: int):
 
     # ---- warm-up (also sizes the exchange block from the real counts)
     blocks, counts = sw.cull(planes)
-    sw.resize(int(counts.max() * 1.25) + 1024)
+    if sw.exchange_mode == "nccl":
+        sw.resize(int(counts.max() * 1.25) + 1024)
     for _ in range(max(args.warmup, 3)):
         sw.cull_device(planes)
     barrier()
@@ -295,9 +298,10 @@ def run_ours(args, rank: int, local_rank: int, world_size: int):
     with torch.cuda.stream(stream):
         ev0.record(stream)
         for i in range(args.steps):
-            sw.cull_local(planes)
             if world_size > 1:
-                blocks = sw.exchange()
+                blocks = sw.cull_device(planes)        # cull + exchange (fused P2P stores, or NCCL all-gather)
+            else:
+                sw.cull_local(planes)
         ev1.record(stream)
     barrier()
     t_wall1 = time.perf_counter()
@@ -332,15 +336,19 @@ def run_ours(args, rank: int, local_rank: int, world_size: int):
             return len(ents)
         d2h = 8 + 4 * total_visible
     else:
-        pinned_t = torch.empty((world_size, sw.capacity + 1), dtype=torch.int32).pin_memory()
+        pinned_t = torch.empty(total_visible * 2 + world_size, dtype=torch.int32).pin_memory()
 
         def e2e_step():
-            b, c = sw.cull(lib.view_planes(view))
+            b, c = sw.cull(lib.view_planes(view))           # device blocks + per-rank counts on the host
             with torch.cuda.stream(stream):
-                pinned_t.copy_(b, non_blocking=True)        # merged (segmented) list to the host
+                at = 0
+                for r in range(world_size):                  # the merged list, rank order, into pinned host memory
+                    k = int(c[r])
+                    pinned_t[at:at + k].copy_(b[r, 1:1 + k], non_blocking=True)
+                    at += k
             stream.synchronize()
             return int(c.sum())
-        d2h = 4 * world_size * (sw.capacity + 1) + 4 * world_size
+        d2h = 4 * total_visible + 4 * world_size
     for _ in range(3):
         e2e_step()
     barrier()
@@ -372,7 +380,9 @@ def run_ours(args, rank: int, local_rank: int, world_size: int):
         "dtype": "f32", "data": "synthetic",
         "config": {"workload": workload_name(world_size, n), "entities_total": total_entities, "views": 1,
                    "visible_total": total_visible,
-                   "parallelism": (f"entity shards x{world_size}, NCCL all-gather of visible lists" if world_size > 1 else "1 GPU"),
+                   "parallelism": ((f"entity shards x{world_size}, exchange of visible lists: " +
+                                    ("gather kernel stores to peers over NVLink + barrier" if sw.exchange_mode == "p2p"
+                                     else "NCCL all-gather")) if world_size > 1 else "1 GPU"),
                    "cache": "inputs larger than L2 (300 MB of bounds per GPU vs 126 MB L2); no flush needed"},
         "cull_ms_per_frame": elapsed_ms / args.steps,
         "roofline": {"bound": "hbm", "kernel": "ovis::cull_test_kernel<2,false> (dominant: reads every bound once)",
@@ -441,6 +451,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
     ap.add_argument("--entities-per-gpu", type=int, default=SHARD_ENTITIES)
+    ap.add_argument("--exchange", choices=["p2p", "nccl"], default="p2p",
+                    help="multi-GPU merge of the visible lists: fused peer stores (default) or NCCL all-gather")
     ap.add_argument("--skip-extras", action="store_true", help="only the headline numbers (no CPU baseline / also)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))

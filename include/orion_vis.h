@@ -184,6 +184,14 @@ int ovis_cull_planes(OvisWorld *world, const float planes[24], uint32_t require,
 int ovis_cull_planes_device(OvisWorld *world, const float planes[24], uint32_t require,
                             uint32_t *d_out_entities, uint32_t *d_out_count);
 
+/* Sharded worlds: the same cull with the exchange fused in. The list (at most `capacity`
+ * ids, clipped beyond) and its true count are stored to n_dst destinations (1..9): destination 0 is local, the others
+ * are typically the peers' segments for this shard, i.e. peer-GPU memory mapped over NVLink (CUDA IPC / symmetric
+ * memory), written by the gather kernel itself with plain stores, so no separate all-gather of the visible lists is
+ * needed - only a barrier before the peers read. No counterpart in the reference (single process, single device). */
+int ovis_cull_planes_device_multi(OvisWorld *world, const float planes[24], uint32_t require, int64_t capacity,
+                                  int32_t n_dst, uint32_t *const *d_out_entities, uint32_t *const *d_out_count);
+
 /* Entity cull for callers that cannot allocate GPU memory - a render thread in the middle of a frame, or an
  * engine that forbids cudaMalloc/cudaFree after start-up because they synchronise the device, can fail under
  * a fixed VRAM budget, and bypass its own pool. No counterpart in the reference. Same result as

@@ -351,6 +351,8 @@ cull_gather_kernel(const __grid_constant__ GatherArgs a) {
         uint32_t grand = s_base + total;
         if (a.d_count) *a.d_count = grand;
         if (a.d_next) *a.d_next = out_base + (long long)grand;
+        for (int x = 0; x < a.n_extra; x++)
+            *a.extra_count[x] = grand;
     }
     // output position k of this block comes from the tile t with s_scan[t] <= k < s_scan[t+1];
     // four independent positions per pass keep several staging loads in flight per thread
@@ -372,8 +374,11 @@ cull_gather_kernel(const __grid_constant__ GatherArgs a) {
 #pragma unroll
         for (int u = 0; u < 4; u++) {
             const uint32_t k = k0 + u * 256;
-            if (k < total && dst0 + k < a.capacity)
+            if (k < total && dst0 + k < a.capacity) {
                 a.out[dst0 + k] = val[u];
+                for (int x = 0; x < a.n_extra; x++)            // peers' copies of this shard's segment
+                    a.extra_out[x][dst0 + k] = val[u];
+            }
         }
     }
 }

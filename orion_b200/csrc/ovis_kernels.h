@@ -8,6 +8,7 @@ namespace ovis {
 
 constexpr uint32_t kNone = 0xffffffffu;
 constexpr int kCullThreads = 256;                       // threads per CTA of the cull test kernel
+constexpr int kMaxPeers = 8;                            // extra destinations of the gather kernel (one NVSwitch box)
 constexpr int kGatherTiles = 64;                        // warp tiles per block of the gather kernel
 constexpr int kCullTile = 1024;                         // storage padding: a multiple of every warp-tile size
 
@@ -58,6 +59,11 @@ struct GatherArgs {               // K3b
     const long long *d_base;     // optional: start offset inside out (CSR chaining), device memory
     long long *d_next;           // optional: receives base + count
     uint32_t *d_count;           // optional: receives count
+    // Fused exchange of a sharded world: the same list and count are also stored to these buffers, which may be
+    // peer GPUs' memory mapped over NVLink (plain st.global to peer addresses; no CSR chaining on this path).
+    int n_extra;
+    uint32_t *extra_out[kMaxPeers];
+    uint32_t *extra_count[kMaxPeers];
 };
 
 // ---- K4 multi-view ------------------------------------------------------------------------------

@@ -163,6 +163,7 @@ extern "C" int ovis_cull_planes_noalloc(int device, void *cuda_stream, const flo
     g.d_base = nullptr;
     g.d_next = nullptr;
     g.d_count = d_out_count;
+    g.n_extra = 0;
     ovis::launch_cull_gather(g, stream);
     err = cudaGetLastError();
     if (err != cudaSuccess)

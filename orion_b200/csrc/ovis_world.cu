@@ -429,7 +429,8 @@ void load_planes(float4 dst[6], const float planes[24]) {
 
 // Enqueue one entity cull (K3). Output goes to `out` (device) starting at *d_base (or 0).
 int enqueue_cull(OvisWorld *w, const float planes[24], uint32_t require, uint32_t *out, long long capacity,
-                 const long long *d_base, long long *d_next, uint32_t *d_count) {
+                 const long long *d_base, long long *d_next, uint32_t *d_count, int n_extra = 0,
+                 uint32_t *const *extra_out = nullptr, uint32_t *const *extra_count = nullptr) {
     if (require & ~(uint32_t)OVIS_CASTS_SHADOW)
         return fail(OVIS_ERR_INVALID, "require mask 0x%x: only 0 or OVIS_CASTS_SHADOW is supported", require);
     if (w->n_ent == 0) {
@@ -483,6 +484,11 @@ int enqueue_cull(OvisWorld *w, const float planes[24], uint32_t require, uint32_
     g.d_base = d_base;
     g.d_next = d_next;
     g.d_count = d_count;
+    g.n_extra = n_extra;
+    for (int x = 0; x < n_extra; x++) {
+        g.extra_out[x] = extra_out[x];
+        g.extra_count[x] = extra_count[x];
+    }
     ovis::launch_cull_gather(g, w->stream);
     if (ev)
         OVIS_CUDA(cudaEventRecord(ev[2], w->stream));
@@ -1193,6 +1199,26 @@ int ovis_cull_planes_device(OvisWorld *w, const float planes[24], uint32_t requi
     OVIS_TRY(use_device(w));
     OVIS_TRY(flush_transforms(w));
     return enqueue_cull(w, planes, require, d_out_entities, (long long)w->n_ent, nullptr, nullptr, d_out_count);
+}
+
+int ovis_cull_planes_device_multi(OvisWorld *w, const float planes[24], uint32_t require, int64_t capacity,
+                                  int32_t n_dst, uint32_t *const *d_out_entities, uint32_t *const *d_out_count) {
+    if (!w || !planes || n_dst < 1 || n_dst > ovis::kMaxPeers + 1 || !d_out_entities || !d_out_count || capacity < 0)
+        return fail(OVIS_ERR_INVALID, "ovis_cull_planes_device_multi: bad arguments (1..%d destinations)", ovis::kMaxPeers + 1);
+    for (int32_t i = 0; i < n_dst; i++)
+        if (!d_out_entities[i] || !d_out_count[i])
+            return fail(OVIS_ERR_INVALID, "ovis_cull_planes_device_multi: destination %d is null", i);
+    OVIS_TRY(use_device(w));
+    OVIS_TRY(flush_transforms(w));
+    if (w->n_ent == 0) {
+        for (int32_t i = 0; i < n_dst; i++) {
+            ovis::launch_empty_result(nullptr, nullptr, d_out_count[i], w->stream);
+            w->launches++;
+        }
+        return OVIS_OK;
+    }
+    return enqueue_cull(w, planes, require, d_out_entities[0], capacity, nullptr, nullptr, d_out_count[0], n_dst - 1,
+                        d_out_entities + 1, d_out_count + 1);
 }
 
 static int cull_to_host(OvisWorld *w, const float planes[24], uint32_t require, bool with_lights,

@@ -297,6 +297,15 @@ class World:
         _check(self.lib.ovis_cull_planes_device(self.h, _p(planes), C.c_uint32(require), C.c_void_p(d_out_ptr),
                                                 C.c_void_p(d_count_ptr)))
 
+    def cull_planes_device_multi(self, planes, d_out_ptrs, d_count_ptrs, capacity: int, require=0):
+        """Cull with the result stored to several device buffers (local + peers' segments). Asynchronous."""
+        planes = _f32(planes, (24,))
+        n = len(d_out_ptrs)
+        outs = (C.c_void_p * n)(*d_out_ptrs)
+        counts = (C.c_void_p * n)(*d_count_ptrs)
+        _check(self.lib.ovis_cull_planes_device_multi(self.h, _p(planes), C.c_uint32(require), C.c_int64(capacity),
+                                                      C.c_int32(n), outs, counts))
+
     def cull_views_device(self, planes, require=None):
         """Many views, CSR result on the device. Returns (host offsets, d_offsets ptr, d_entities ptr)."""
         planes = _f32(planes, (-1, 24))

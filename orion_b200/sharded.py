@@ -48,11 +48,43 @@ def shard_range(n_total: int, rank: int, world_size: int) -> tuple[int, int]:
     return n_total * rank // world_size, n_total * (rank + 1) // world_size
 
 
+def open_symmetric_blocks(world_size: int, capacity: int, group=None):
+    """Two (world_size, capacity + 1) int32 buffers in NVLink-mapped symmetric memory (one per frame parity).
+
+    Returns (tensors, handles) or None when torch's symmetric memory is unavailable (then NCCL all-gather is used).
+    """
+    try:
+        import torch.distributed._symmetric_memory as symm_mem
+        group = group or dist.group.WORLD
+        try:
+            symm_mem.enable_symm_mem_for_group(group.group_name)
+        except Exception:
+            pass
+        tensors, handles = [], []
+        for _ in range(2):
+            t = symm_mem.empty((world_size, capacity + 1), dtype=torch.int32, device=torch.device("cuda", torch.cuda.current_device()))
+            h = symm_mem.rendezvous(t, group=group)
+            t.zero_()
+            tensors.append(t)
+            handles.append(h)
+        return tensors, handles
+    except Exception as e:                  # pragma: no cover - depends on the torch build / topology
+        import warnings
+        warnings.warn(f"symmetric memory unavailable ({e!r}); sharded cull falls back to NCCL all-gather")
+        return None
+
+
 class ShardedWorld:
-    """A lib.World holding one shard plus the NCCL merge of the per-shard visible lists."""
+    """A lib.World holding one shard plus the merge of the per-shard visible lists.
+
+    exchange="nccl": local cull, then one NCCL all-gather of [count | ids] blocks.
+    exchange="p2p":  the gather kernel itself stores this shard's list into every peer's segment buffer over NVLink
+                     (ovis_cull_planes_device_multi), followed by one symmetric-memory barrier; buffers alternate by
+                     frame parity so a frame's stores never land in a buffer a peer is still reading.
+    """
 
     def __init__(self, world, rank: int, world_size: int, id_base: int, n_local: int, group=None,
-                 stream: "torch.cuda.Stream | None" = None):
+                 stream: "torch.cuda.Stream | None" = None, exchange: str = "nccl", p2p_capacity: int | None = None):
         self.world = world
         self.rank, self.size, self.group = rank, world_size, group
         self.n_local = n_local
@@ -64,6 +96,23 @@ class ShardedWorld:
         self.block = torch.zeros(n_local + 1, dtype=torch.int32, device="cuda")
         self.capacity = 0
         self.resize(max(1024, n_local // 8))
+        self.exchange_mode = "nccl"
+        self.frame = 0
+        if exchange == "p2p" and world_size > 1:
+            cap = int(min(n_local, p2p_capacity or max(1024, n_local // 8)))
+            opened = open_symmetric_blocks(world_size, cap, group)
+            if opened is not None:
+                self.sym_tensors, self.sym_handles = opened
+                self.exchange_mode = "p2p"
+                self.capacity = cap
+                seg = (cap + 1) * 4
+                # destination 0 is this rank's own copy; the rest are the peers' copies of segment `rank`
+                order = [rank] + [p for p in range(world_size) if p != rank]
+                self.p2p_out, self.p2p_cnt = [], []
+                for h in self.sym_handles:
+                    ptrs = [int(h.buffer_ptrs[p]) + rank * seg for p in order]
+                    self.p2p_cnt.append(ptrs)
+                    self.p2p_out.append([q + 4 for q in ptrs])
 
     def resize(self, capacity: int):
         self.capacity = int(min(max(capacity, 1), self.n_local))
@@ -78,6 +127,14 @@ class ShardedWorld:
             return allgather_blocks(self.block[:self.capacity + 1], self.size, self.group)
 
     def cull_device(self, planes, require: int = 0) -> torch.Tensor:
+        """Enqueue one frame's cull + exchange; returns the (size, capacity + 1) blocks tensor (valid in stream order)."""
+        if self.exchange_mode == "p2p":
+            k = self.frame & 1
+            self.frame += 1
+            self.world.cull_planes_device_multi(planes, self.p2p_out[k], self.p2p_cnt[k], self.capacity, require)
+            with torch.cuda.stream(self.stream):
+                self.sym_handles[k].barrier(channel=0)
+            return self.sym_tensors[k]
         self.cull_local(planes, require)
         return self.exchange()
 
@@ -89,4 +146,7 @@ class ShardedWorld:
             counts = segment_counts(blocks)
             if counts.max(initial=0) <= self.capacity:
                 return blocks, counts
+            if self.exchange_mode == "p2p":
+                raise RuntimeError(f"visible list of {int(counts.max())} ids exceeds the symmetric segment capacity "
+                                   f"{self.capacity}; create the ShardedWorld with a larger p2p_capacity")
             self.resize(int(counts.max() * 1.25) + 1024)

@@ -1,0 +1,55 @@
+"""Two real GPUs: both exchange modes of the sharded world (NCCL all-gather, and the gather kernel storing straight into
+the peers' symmetric-memory segments over NVLink) must reproduce the single-world visible list. Skipped on boxes with
+fewer than two GPUs (the driver's -m gpu run has one); exercised with `gpurun --gpus 2`."""
+import os
+import subprocess
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+WORKER = r'''
+import os, sys, numpy as np, torch, torch.distributed as dist
+sys.path.insert(0, %r)
+from orion_b200 import lib, scenes
+from orion_b200.sharded import ShardedWorld, merged_list, shard_range
+from oracle import pyoracle
+rank, size = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+torch.cuda.set_device(rank)
+dist.init_process_group("nccl", device_id=torch.device("cuda", rank))
+oracle = pyoracle.load("best")
+n_total = 600_001
+aabb, flags = scenes.static_boxes(n_total, 9, 800.0)
+lo, hi = shard_range(n_total, rank, size)
+for mode in ("nccl", "p2p"):
+    w = lib.World(rank)
+    f = w.add_entities(aabb[lo:hi], flags[lo:hi]); w.set_world_aabbs(f, aabb[lo:hi])
+    sw = ShardedWorld(w, rank, size, lo, hi - lo, stream=torch.cuda.Stream(), exchange=mode)
+    for view, req in ((scenes.default_camera(), 0), (scenes.make_view((100, 0, 300), (1, 0, 0, 0), 60.0, 1.0, 900.0, 800, 600), 1),
+                      (scenes.default_camera(), 1)):
+        planes = lib.view_planes(view)
+        blocks, counts = sw.cull(planes, req)
+        got = merged_list(blocks, counts)
+        exp = oracle.cull_aabb(aabb, planes, flags, req, threads=4)
+        assert np.array_equal(got, exp), (mode, rank, len(got), len(exp))
+    assert mode == "nccl" or sw.exchange_mode == "p2p", "symmetric memory path did not come up"
+    dist.barrier()
+    w.close()
+if rank == 0:
+    print("MULTI_GPU_OK")
+dist.destroy_process_group()
+''' % ROOT
+
+
+@pytest.mark.gpu
+def test_two_gpu_exchange_modes(tmp_path):
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    script = tmp_path / "worker.py"
+    script.write_text(WORKER)
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+                        "--master-addr", "127.0.0.1", "--master-port", "29533", str(script)],
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and "MULTI_GPU_OK" in r.stdout, (r.stdout + r.stderr)[-4000:]
