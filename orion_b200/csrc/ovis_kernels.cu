@@ -303,6 +303,8 @@ cull_gather_kernel(const __grid_constant__ GatherArgs a) {
     __shared__ uint32_t s_base;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int block = blockIdx.x;
+    // Let the next cull's test kernel start now (if it was launched to allow that): it shares nothing with this kernel.
+    asm volatile("griddepcontrol.launch_dependents;");
 
     // base = survivors in all earlier blocks
     uint32_t part = 0;
@@ -398,8 +400,23 @@ static void with_variant(int variant, bool masked, F &&f) {
     }
 }
 
-void launch_cull_test(const CullArgs &a, bool masked, int variant, int grid, cudaStream_t s) {
-    with_variant(variant, masked, [&](auto kernel) { kernel<<<grid, kCullThreads, 0, s>>>(a); });
+// overlap_previous_gather: launch with programmatic stream serialization, so this test kernel may start while the
+// PREVIOUS cull's gather kernel (which signals its dependents at once) is still running. Only legal when the two use
+// different scratch sets; every other predecessor still completes first.
+void launch_cull_test(const CullArgs &a, bool masked, int variant, int grid, cudaStream_t s, bool overlap_previous_gather) {
+    with_variant(variant, masked, [&](auto kernel) {
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3((unsigned)grid);
+        cfg.blockDim = dim3(kCullThreads);
+        cfg.dynamicSmemBytes = 0;
+        cfg.stream = s;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = overlap_previous_gather ? 1 : 0;
+        cudaLaunchKernelEx(&cfg, kernel, a);
+    });
 }
 
 void launch_cull_gather(const GatherArgs &a, cudaStream_t s) {

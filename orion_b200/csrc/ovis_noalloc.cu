@@ -150,7 +150,8 @@ extern "C" int ovis_cull_planes_noalloc(int device, void *cuda_stream, const flo
     int grid = (a.num_tiles + warps_per_block - 1) / warps_per_block;
     if (grid > setup->num_sms * setup->blocks_per_sm)
         grid = setup->num_sms * setup->blocks_per_sm;
-    ovis::launch_cull_test(a, false, kVariant, grid, stream);
+    // one shared scratch: this call's test kernel must not overlap the previous call's gather kernel
+    ovis::launch_cull_test(a, false, kVariant, grid, stream, /*overlap_previous_gather=*/false);
 
     ovis::GatherArgs g;
     g.staging = staging;

@@ -108,11 +108,13 @@ struct OvisWorld {
     bool lights_dirty = false;
 
     // ---- cull scratch and results
-    uint32_t *d_staging = nullptr;        // cap_ent ids: per-warp-tile survivor lists before the gather
-    uint32_t *d_tile_counts = nullptr;    // cap_ent / 128 counts
-    uint32_t *d_block_totals = nullptr;   // 2 x cap_blocks totals, used alternately (the idle set is zero)
+    // Two staging/count sets and three block-total sets rotate from cull to cull, so that a cull's test kernel can
+    // run while the previous cull's gather kernel is still reading its own set.
+    uint32_t *d_staging = nullptr;        // 2 x cap_ent ids: per-warp-tile survivor lists before the gather
+    uint32_t *d_tile_counts = nullptr;    // 2 x cap_ent / 128 counts
+    uint32_t *d_block_totals = nullptr;   // 3 x cap_blocks totals (the idle sets are zero)
     int64_t cap_blocks = 0;
-    int totals_parity = 0;
+    uint64_t cull_serial = 0;             // culls launched so far (selects the scratch sets)
     uint32_t *d_result = nullptr;         // cap_ent visible ids
     uint32_t *d_counts = nullptr;         // [0] entities, [1] lights
     uint32_t *h_counts = nullptr;         // pinned mirror
@@ -215,12 +217,12 @@ int reserve_entities(OvisWorld *w, int64_t want) {
     OVIS_TRY(grow(w->d_alive_bits, w->cap_ent / 32, cap / 32, w->stream));
     OVIS_TRY(grow(w->d_caster_bits, w->cap_ent / 32, cap / 32, w->stream));
     OVIS_TRY(grow(w->d_result, 0, cap, w->stream, false));
-    OVIS_TRY(grow(w->d_staging, 0, cap, w->stream, false));
-    OVIS_TRY(grow(w->d_tile_counts, 0, cap / 128, w->stream, false));
+    OVIS_TRY(grow(w->d_staging, 0, 2 * cap, w->stream, false));
+    OVIS_TRY(grow(w->d_tile_counts, 0, 2 * (cap / 128), w->stream, false));
     int64_t blocks = cap / 128 / ovis::kGatherTiles + 1;
-    OVIS_TRY(grow(w->d_block_totals, 0, 2 * blocks, w->stream));   // both sets start zeroed
+    OVIS_TRY(grow(w->d_block_totals, 0, 3 * blocks, w->stream));   // all sets start zeroed
     w->cap_blocks = blocks;
-    w->totals_parity = 0;
+    w->cull_serial = 0;
     w->cap_ent = cap;
     w->h_alive.resize((size_t)(cap / 32), 0u);
     w->h_caster_raw.resize((size_t)(cap / 32), 0u);
@@ -451,10 +453,12 @@ int enqueue_cull(OvisWorld *w, const float planes[24], uint32_t require, uint32_
     a.num_tiles = (int)((w->n_ent + tile - 1) / tile);
     a.num_blocks = (a.num_tiles + ovis::kGatherTiles - 1) / ovis::kGatherTiles;
     a.mask = require ? w->d_caster_bits : w->d_alive_bits;
-    a.staging = w->d_staging;
-    a.tile_counts = w->d_tile_counts;
-    a.block_totals = w->d_block_totals + w->totals_parity * w->cap_blocks;
-    a.block_totals_next = w->d_block_totals + (w->totals_parity ^ 1) * w->cap_blocks;
+    const int64_t set2 = (int64_t)(w->cull_serial & 1), set3 = (int64_t)(w->cull_serial % 3);
+    a.staging = w->d_staging + set2 * w->cap_ent;
+    a.tile_counts = w->d_tile_counts + set2 * (w->cap_ent / 128);
+    a.block_totals = w->d_block_totals + set3 * w->cap_blocks;
+    // zeroed by this test kernel for the next cull; last read by the gather kernel two culls ago, which has finished
+    a.block_totals_next = w->d_block_totals + ((set3 + 1) % 3) * w->cap_blocks;
     a.id_base = w->id_base;
     const int warps_needed_blocks = (a.num_tiles + ovis::kCullThreads / 32 - 1) / (ovis::kCullThreads / 32);
     int grid = std::min(warps_needed_blocks, w->num_sms * w->blocks_per_sm[variant][masked ? 1 : 0]);
@@ -470,12 +474,12 @@ int enqueue_cull(OvisWorld *w, const float planes[24], uint32_t require, uint32_
         w->timing_used += 3;
         OVIS_CUDA(cudaEventRecord(ev[0], w->stream));
     }
-    ovis::launch_cull_test(a, masked, variant, grid, w->stream);
+    ovis::launch_cull_test(a, masked, variant, grid, w->stream, /*overlap_previous_gather=*/true);
     if (ev)
         OVIS_CUDA(cudaEventRecord(ev[1], w->stream));
     ovis::GatherArgs g;
-    g.staging = w->d_staging;
-    g.tile_counts = w->d_tile_counts;
+    g.staging = a.staging;
+    g.tile_counts = a.tile_counts;
     g.block_totals = a.block_totals;
     g.num_tiles = a.num_tiles;
     g.tile_entities = tile;
@@ -492,7 +496,7 @@ int enqueue_cull(OvisWorld *w, const float planes[24], uint32_t require, uint32_
     ovis::launch_cull_gather(g, w->stream);
     if (ev)
         OVIS_CUDA(cudaEventRecord(ev[2], w->stream));
-    w->totals_parity ^= 1;
+    w->cull_serial++;
     w->launches += 2;
     OVIS_CUDA(cudaGetLastError());
     return OVIS_OK;
