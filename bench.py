@@ -301,6 +301,8 @@ def run_ours(args, rank: int, local_rank: int, world_size: int):
                 blocks = sw.cull_device(planes)        # cull + exchange (fused P2P stores, or NCCL all-gather)
             else:
                 sw.cull_local(planes)
+        if world_size > 1 and sw.exchange_mode == "p2p":
+            stream.wait_event(sw.ready)                # the last frame's barrier (side stream) is part of the K steps
         ev1.record(stream)
     barrier()
     t_wall1 = time.perf_counter()

@@ -170,7 +170,7 @@ int ovis_light_shadow_views(const OvisLight *light, int32_t shadow_map_resolutio
  * AABB intersects the view frustum (core/src/math/intersection.cc:42-57); when flags has
  * OVIS_CULL_LIGHTS, out_lights receives ids of lights for which RenderLight::cull is false
  * (render_light.cc:187-209). Counts are always written; if a capacity is too small the call returns
- * OVIS_ERR_CAPACITY and nothing else is written for that list. out_lights may be NULL when
+ * OVIS_ERR_CAPACITY and the content of that list is unspecified. out_lights may be NULL when
  * OVIS_CULL_LIGHTS is not set. */
 int ovis_cull(OvisWorld *world, const OvisView *view, uint32_t flags,
               uint32_t *out_entities, int64_t cap_entities, int64_t *out_n_entities,

@@ -115,6 +115,7 @@ struct OvisWorld {
     uint32_t *d_block_totals = nullptr;   // 3 x cap_blocks totals (the idle sets are zero)
     int64_t cap_blocks = 0;
     uint64_t cull_serial = 0;             // culls launched so far (selects the scratch sets)
+    int64_t last_visible = 0;             // entity count of the previous host-output cull (sizes the speculative copy)
     uint32_t *d_result = nullptr;         // cap_ent visible ids
     uint32_t *d_counts = nullptr;         // [0] entities, [1] lights
     uint32_t *h_counts = nullptr;         // pinned mirror
@@ -1232,21 +1233,39 @@ static int cull_to_host(OvisWorld *w, const float planes[24], uint32_t require, 
     OVIS_TRY(enqueue_cull(w, planes, require, w->d_result, (long long)w->cap_ent, nullptr, nullptr, w->d_counts));
     if (with_lights)
         OVIS_TRY(enqueue_light_cull(w, planes));
+    // One round trip in the common case: visible sets change little from cull to cull, so the ids are copied
+    // speculatively (a little more than the previous call needed) together with the counts; only a call whose list
+    // turns out longer pays a second copy for the remainder.
+    int64_t spec_e = out_entities ? std::min<int64_t>(cap_entities, std::min<int64_t>(w->n_ent, w->last_visible + w->last_visible / 4 + 1024)) : 0;
+    int32_t spec_l = (with_lights && out_lights) ? (int32_t)std::min<int64_t>(cap_lights, (int64_t)w->lights.size()) : 0;
     OVIS_CUDA(cudaMemcpyAsync(w->h_counts, w->d_counts, 2 * sizeof(uint32_t), cudaMemcpyDeviceToHost, w->stream));
+    if (spec_e > 0)
+        OVIS_CUDA(cudaMemcpyAsync(out_entities, w->d_result, sizeof(uint32_t) * (size_t)spec_e, cudaMemcpyDeviceToHost, w->stream));
+    if (spec_l > 0)
+        OVIS_CUDA(cudaMemcpyAsync(out_lights, w->d_light_out, sizeof(uint32_t) * (size_t)spec_l, cudaMemcpyDeviceToHost, w->stream));
     OVIS_CUDA(cudaStreamSynchronize(w->stream));
     int64_t ne = w->h_counts[0];
     int32_t nl = with_lights ? (int32_t)w->h_counts[1] : 0;
+    w->last_visible = ne;
     if (out_n_entities) *out_n_entities = ne;
     if (out_n_lights) *out_n_lights = nl;
     if (ne > cap_entities || (ne > 0 && !out_entities))
         return fail(OVIS_ERR_CAPACITY, "entity result needs %lld entries, buffer holds %lld", (long long)ne, (long long)cap_entities);
     if (nl > cap_lights || (nl > 0 && !out_lights))
         return fail(OVIS_ERR_CAPACITY, "light result needs %d entries, buffer holds %d", nl, cap_lights);
-    if (ne > 0)
-        OVIS_CUDA(cudaMemcpyAsync(out_entities, w->d_result, sizeof(uint32_t) * (size_t)ne, cudaMemcpyDeviceToHost, w->stream));
-    if (nl > 0)
-        OVIS_CUDA(cudaMemcpyAsync(out_lights, w->d_light_out, sizeof(uint32_t) * (size_t)nl, cudaMemcpyDeviceToHost, w->stream));
-    OVIS_CUDA(cudaStreamSynchronize(w->stream));
+    bool again = false;
+    if (ne > spec_e) {
+        OVIS_CUDA(cudaMemcpyAsync(out_entities + spec_e, w->d_result + spec_e, sizeof(uint32_t) * (size_t)(ne - spec_e),
+                                  cudaMemcpyDeviceToHost, w->stream));
+        again = true;
+    }
+    if (nl > spec_l) {
+        OVIS_CUDA(cudaMemcpyAsync(out_lights + spec_l, w->d_light_out + spec_l, sizeof(uint32_t) * (size_t)(nl - spec_l),
+                                  cudaMemcpyDeviceToHost, w->stream));
+        again = true;
+    }
+    if (again)
+        OVIS_CUDA(cudaStreamSynchronize(w->stream));
     return OVIS_OK;
 }
 

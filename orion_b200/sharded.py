@@ -48,20 +48,19 @@ def shard_range(n_total: int, rank: int, world_size: int) -> tuple[int, int]:
     return n_total * rank // world_size, n_total * (rank + 1) // world_size
 
 
+P2P_BUFFERS = 3
+
+
 def open_symmetric_blocks(world_size: int, capacity: int, group=None):
-    """Two (world_size, capacity + 1) int32 buffers in NVLink-mapped symmetric memory (one per frame parity).
+    """Three (world_size, capacity + 1) int32 buffers in NVLink-mapped symmetric memory, used in rotation.
 
     Returns (tensors, handles) or None when torch's symmetric memory is unavailable (then NCCL all-gather is used).
     """
     try:
         import torch.distributed._symmetric_memory as symm_mem
         group = group or dist.group.WORLD
-        try:
-            symm_mem.enable_symm_mem_for_group(group.group_name)
-        except Exception:
-            pass
         tensors, handles = [], []
-        for _ in range(2):
+        for _ in range(P2P_BUFFERS):
             t = symm_mem.empty((world_size, capacity + 1), dtype=torch.int32, device=torch.device("cuda", torch.cuda.current_device()))
             h = symm_mem.rendezvous(t, group=group)
             t.zero_()
@@ -79,8 +78,11 @@ class ShardedWorld:
 
     exchange="nccl": local cull, then one NCCL all-gather of [count | ids] blocks.
     exchange="p2p":  the gather kernel itself stores this shard's list into every peer's segment buffer over NVLink
-                     (ovis_cull_planes_device_multi), followed by one symmetric-memory barrier; buffers alternate by
-                     frame parity so a frame's stores never land in a buffer a peer is still reading.
+                     (ovis_cull_planes_device_multi). The symmetric-memory barrier that makes a frame readable is
+                     enqueued on a side stream, so the cull stream goes straight on to the next frame; three buffers
+                     rotate and a frame waits for the barrier of two frames ago (long finished) before it stores into a
+                     buffer again, so stores never land in a buffer a peer may still be reading. `ready` is the event
+                     after which the returned blocks are complete.
     """
 
     def __init__(self, world, rank: int, world_size: int, id_base: int, n_local: int, group=None,
@@ -108,6 +110,8 @@ class ShardedWorld:
                 seg = (cap + 1) * 4
                 # destination 0 is this rank's own copy; the rest are the peers' copies of segment `rank`
                 order = [rank] + [p for p in range(world_size) if p != rank]
+                self.side = torch.cuda.Stream()
+                self.ready_events = [None] * P2P_BUFFERS
                 self.p2p_out, self.p2p_cnt = [], []
                 for h in self.sym_handles:
                     ptrs = [int(h.buffer_ptrs[p]) + rank * seg for p in order]
@@ -129,20 +133,40 @@ class ShardedWorld:
     def cull_device(self, planes, require: int = 0) -> torch.Tensor:
         """Enqueue one frame's cull + exchange; returns the (size, capacity + 1) blocks tensor (valid in stream order)."""
         if self.exchange_mode == "p2p":
-            k = self.frame & 1
+            k = self.frame % P2P_BUFFERS
             self.frame += 1
+            # peers have finished reading buffer k (frame - 3) once the barrier of frame - 2 has passed
+            old = self.ready_events[(k + 1) % P2P_BUFFERS]
+            if old is not None:
+                self.stream.wait_event(old)
             self.world.cull_planes_device_multi(planes, self.p2p_out[k], self.p2p_cnt[k], self.capacity, require)
-            with torch.cuda.stream(self.stream):
+            stored = torch.cuda.Event()
+            stored.record(self.stream)
+            self.side.wait_event(stored)
+            with torch.cuda.stream(self.side):
                 self.sym_handles[k].barrier(channel=0)
+                ready = torch.cuda.Event()
+                ready.record(self.side)
+            self.ready_events[k] = ready
+            self.ready = ready
             return self.sym_tensors[k]
         self.cull_local(planes, require)
-        return self.exchange()
+        blocks = self.exchange()
+        self.ready = torch.cuda.Event()
+        self.ready.record(self.stream)
+        return blocks
+
+    def wait_all(self):
+        """Block the host until every enqueued frame (cull stream and barrier stream) has finished."""
+        self.stream.synchronize()
+        if self.exchange_mode == "p2p":
+            self.side.synchronize()
 
     def cull(self, planes, require: int = 0):
         """Synchronous cull; returns (blocks on device, per-rank counts on host). Redone if a shard overflowed."""
         while True:
             blocks = self.cull_device(planes, require)
-            self.stream.synchronize()
+            self.ready.synchronize()
             counts = segment_counts(blocks)
             if counts.max(initial=0) <= self.capacity:
                 return blocks, counts
