@@ -184,6 +184,23 @@ def run_reference(args, rank: int):
 # ours
 # --------------------------------------------------------------------------------------------------
 
+def ncu_traffic_bytes():
+    """dram__bytes_read.sum + dram__bytes_write.sum of one launch of the dominant kernel, from the committed
+    `ncu --set full` summary of this same workload (profiles/r01_cull_test_kernel_ncu.csv); None if absent."""
+    path = os.path.join(ROOT, "profiles", "r01_cull_test_kernel_ncu.csv")
+    scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    try:
+        total, seen = 0.0, set()
+        for line in open(path):
+            parts = [x.strip('"') for x in line.strip().split(",")]
+            if len(parts) == 3 and parts[0] in ("dram__bytes_read.sum", "dram__bytes_write.sum") and parts[0] not in seen:
+                total += float(parts[2]) * scale[parts[1]]
+                seen.add(parts[0])
+        return total if len(seen) == 2 else None
+    except Exception:
+        return None
+
+
 def time_kernel_loop(torch, stream, fn, iters: int, flush=None):
     """Per-iteration device times (ms) of fn() with CUDA events on `stream`."""
     evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(iters)]
@@ -395,7 +412,9 @@ def run_ours(args, rank: int, local_rank: int, world_size: int):
                    "cache": "inputs larger than L2 (300 MB of bounds per GPU vs 126 MB L2); no flush needed"},
         "cull_ms_per_frame": elapsed_ms / args.steps,
         "roofline": {"bound": "hbm", "kernel": "ovis::cull_test_kernel<2,false> (dominant: reads every bound once)",
-                     "achieved": achieved, "peak": peak_gbs, "unit": "GB/s", "frac": achieved / peak_gbs, "traffic": None,
+                     "achieved": achieved, "peak": peak_gbs, "unit": "GB/s", "frac": achieved / peak_gbs,
+                     "traffic": ncu_traffic_bytes() if n == SHARD_ENTITIES else None,
+                     "traffic_source": "profiles/r01_cull_test_kernel_ncu.csv (ncu --set full, one launch, same workload)",
                      "algorithmic_bytes_per_launch": alg_bytes, "kernel_ms_mean": k_ms, "kernel_ms_min": float(test_ms.min()),
                      "gather_kernel_ms_mean": g_ms,
                      "both_kernels": {"achieved": step_achieved, "frac": step_achieved / peak_gbs,

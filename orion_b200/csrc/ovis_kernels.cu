@@ -162,8 +162,16 @@ update_level_kernel(LevelArgs a) {
     if (i >= a.count)
         return;
     int64_t node = a.list ? (int64_t)a.list[i] : a.first + i;
-    DTrs w = load_trs(a.local_trs, a.nstride, node);
     int32_t parent = a.parent[node];
+    if (a.dirty) {
+        // Entity::transformed only runs below a node that was moved (entity.cc:309-363 -> :382-411): a node is
+        // recomputed if it changed itself or its parent was recomputed (parents are in an earlier launch).
+        bool moved = a.dirty[node] != 0 || (parent >= 0 && a.dirty[parent] != 0);
+        if (!moved)
+            return;
+        a.dirty[node] = 1;
+    }
+    DTrs w = load_trs(a.local_trs, a.nstride, node);
     if (parent >= 0)
         w = compose_trs(load_trs(a.world_trs, a.nstride, parent), w);
     store_trs(a.world_trs, a.nstride, node, w);
@@ -181,17 +189,31 @@ void launch_update_level(const LevelArgs &a, cudaStream_t s) {
 // graphics/src/mesh_renderer.cc:180-187): (entity, node) pairs, run after all levels.
 __global__ void extra_bounds_kernel(const uint32_t *__restrict__ entities, const uint32_t *__restrict__ nodes, int64_t n,
                                     const float *__restrict__ world_trs, int64_t nstride, const float *__restrict__ local,
-                                    float *world, int64_t estride) {
+                                    float *world, int64_t estride, const uint8_t *__restrict__ dirty) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n)
+        return;
+    if (dirty && !dirty[nodes[i]])
         return;
     entity_bounds_from_trs(load_trs(world_trs, nstride, nodes[i]), entities[i], local, world, estride);
 }
 
 void launch_extra_bounds(const uint32_t *entities, const uint32_t *nodes, int64_t n, const float *world_trs,
-                         int64_t nstride, const float *local, float *world, int64_t estride, cudaStream_t s) {
+                         int64_t nstride, const float *local, float *world, int64_t estride, const uint8_t *dirty,
+                         cudaStream_t s) {
     if (n > 0)
-        extra_bounds_kernel<<<blocks_for(n, 256), 256, 0, s>>>(entities, nodes, n, world_trs, nstride, local, world, estride);
+        extra_bounds_kernel<<<blocks_for(n, 256), 256, 0, s>>>(entities, nodes, n, world_trs, nstride, local, world, estride, dirty);
+}
+
+__global__ void mark_dirty_kernel(const uint32_t *__restrict__ ids, int64_t n, uint8_t *dirty) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n)
+        dirty[ids[i]] = 1;
+}
+
+void launch_mark_dirty(const uint32_t *ids, int64_t n, uint8_t *dirty, cudaStream_t s) {
+    if (n > 0)
+        mark_dirty_kernel<<<blocks_for(n, 256), 256, 0, s>>>(ids, n, dirty);
 }
 
 // ------------------------------------------------------------------------------------------------

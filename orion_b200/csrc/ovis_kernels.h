@@ -27,6 +27,8 @@ struct LevelArgs {
     const float *local_trs;      // 10 x nstride
     float *world_trs;            // 10 x nstride
     int64_t nstride;
+    uint8_t *dirty;              // per node: local TRS (or a bound entity's box) changed; nullptr = recompute everything.
+                                 // The kernel sets it for every node it recomputes, so children inherit it.
     const uint32_t *node_entity; // first entity bound to the node, or kNone
     const float *local_aabb;     // 6 x estride
     float *world_aabb;           // 6 x estride
@@ -126,7 +128,9 @@ void launch_identity_bounds(const uint32_t *ids, uint32_t first, int64_t n, cons
                             int64_t stride, cudaStream_t s);
 void launch_update_level(const LevelArgs &a, cudaStream_t s);
 void launch_extra_bounds(const uint32_t *entities, const uint32_t *nodes, int64_t n, const float *world_trs,
-                         int64_t nstride, const float *local, float *world, int64_t estride, cudaStream_t s);
+                         int64_t nstride, const float *local, float *world, int64_t estride, const uint8_t *dirty,
+                         cudaStream_t s);
+void launch_mark_dirty(const uint32_t *ids, int64_t n, uint8_t *dirty, cudaStream_t s);
 int cull_num_variants();
 CullVariant cull_variant(int v);
 void launch_cull_test(const CullArgs &a, bool masked, int variant, int grid, cudaStream_t s, bool overlap_previous_gather);

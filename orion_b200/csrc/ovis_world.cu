@@ -88,6 +88,7 @@ struct OvisWorld {
     float *d_world_trs = nullptr;         // 10 x cap_nodes
     uint32_t *d_node_entity = nullptr;
     std::vector<int32_t> h_parent, h_level;
+    std::vector<uint32_t> h_subtree;      // nodes in the subtree rooted at each node (itself included)
     std::vector<uint32_t> h_node_entity;
     std::vector<uint32_t> h_extra_entity, h_extra_node;   // 2nd.. entity on a node
     uint32_t *d_extra_entity = nullptr, *d_extra_node = nullptr;
@@ -98,6 +99,9 @@ struct OvisWorld {
     int64_t cap_level_lists = 0;
     bool levels_dirty = false;
     bool transforms_dirty = false;
+    uint8_t *d_dirty = nullptr;           // per node: changed since the last update (cap_nodes bytes)
+    bool all_dirty = false;               // recompute every node (topology changed, or most nodes moved)
+    bool marks_present = false;           // d_dirty holds non-zero bytes
 
     // ---- lights
     std::vector<OvisLight> lights;
@@ -238,6 +242,7 @@ int reserve_nodes(OvisWorld *w, int64_t want) {
     OVIS_TRY(grow_soa(w->d_world_trs, 10, w->cap_nodes, cap, w->n_nodes, w->stream));
     OVIS_TRY(grow(w->d_parent, w->n_nodes, cap, w->stream));
     OVIS_TRY(grow(w->d_node_entity, w->n_nodes, cap, w->stream));
+    OVIS_TRY(grow(w->d_dirty, w->n_nodes, cap, w->stream));
     w->cap_nodes = cap;
     return OVIS_OK;
 }
@@ -282,10 +287,13 @@ int add_nodes(OvisWorld *w, int64_t n, const int32_t *parent, const float *local
     w->h_parent.resize((size_t)(first + n));
     w->h_level.resize((size_t)(first + n));
     w->h_node_entity.resize((size_t)(first + n), kNone);
+    w->h_subtree.resize((size_t)(first + n), 1u);
     for (int64_t i = 0; i < n; i++) {
         int32_t p = parent[i];
         w->h_parent[(size_t)(first + i)] = p;
         w->h_level[(size_t)(first + i)] = p < 0 ? 0 : w->h_level[(size_t)p] + 1;
+        for (int32_t a = p; a >= 0; a = w->h_parent[(size_t)a])      // O(depth): scene trees are shallow
+            w->h_subtree[(size_t)a]++;
     }
     for (int64_t s = 0; s < n; s += kUploadChunk) {
         int64_t c = std::min(kUploadChunk, n - s);
@@ -301,6 +309,7 @@ int add_nodes(OvisWorld *w, int64_t n, const int32_t *parent, const float *local
     w->n_nodes = first + n;
     w->levels_dirty = true;
     w->transforms_dirty = true;
+    w->all_dirty = true;
     if (out_first)
         *out_first = (uint32_t)first;
     return OVIS_OK;
@@ -378,6 +387,7 @@ int flush_transforms(OvisWorld *w) {
         a.local_trs = w->d_local_trs;
         a.world_trs = w->d_world_trs;
         a.nstride = w->cap_nodes;
+        a.dirty = w->all_dirty ? nullptr : w->d_dirty;
         a.node_entity = w->d_node_entity;
         a.local_aabb = w->d_local;
         a.world_aabb = w->d_world;
@@ -387,10 +397,15 @@ int flush_transforms(OvisWorld *w) {
     }
     if (!w->h_extra_entity.empty()) {
         ovis::launch_extra_bounds(w->d_extra_entity, w->d_extra_node, (int64_t)w->h_extra_entity.size(), w->d_world_trs,
-                                  w->cap_nodes, w->d_local, w->d_world, w->cap_ent, w->stream);
+                                  w->cap_nodes, w->d_local, w->d_world, w->cap_ent, w->all_dirty ? nullptr : w->d_dirty,
+                                  w->stream);
         w->launches++;
     }
     OVIS_CUDA(cudaGetLastError());
+    if (w->marks_present)
+        OVIS_CUDA(cudaMemsetAsync(w->d_dirty, 0, (size_t)w->n_nodes, w->stream));
+    w->marks_present = false;
+    w->all_dirty = false;
     w->transforms_dirty = false;
     return OVIS_OK;
 }
@@ -422,6 +437,7 @@ int bind_entities(OvisWorld *w, int64_t n, const uint32_t *nodes, const uint32_t
         OVIS_CUDA(cudaStreamSynchronize(w->stream));   // vectors are locals
     }
     w->transforms_dirty = true;
+    w->all_dirty = true;
     return OVIS_OK;
 }
 
@@ -822,7 +838,7 @@ int ovis_world_destroy(OvisWorld *w) {
     cudaSetDevice(w->device);
     cudaStreamSynchronize(w->stream);
     void *bufs[] = { w->d_local, w->d_world, w->d_alive_bits, w->d_caster_bits, w->d_parent, w->d_local_trs, w->d_world_trs,
-                     w->d_node_entity, w->d_extra_entity, w->d_extra_node, w->d_level_lists, w->d_lights, w->d_light_out,
+                     w->d_node_entity, w->d_dirty, w->d_extra_entity, w->d_extra_node, w->d_level_lists, w->d_lights, w->d_light_out,
                      w->d_staging, w->d_tile_counts, w->d_block_totals, w->d_mv_counts, w->d_mv_totals, w->d_mv_planes,
                      w->d_mv_require, w->d_mv_groups, w->d_mv_hits, w->d_result, w->d_counts, w->d_csr_entities, w->d_csr_offsets,
                      w->d_stage[0], w->d_stage[1] };
@@ -977,9 +993,21 @@ int ovis_entity_set_local_aabbs(OvisWorld *w, int64_t n, const uint32_t *ids, co
         w->launches += 2;
     }
     OVIS_CUDA(cudaGetLastError());
+    std::vector<uint32_t> nodes;
     for (int64_t i = 0; i < n; i++)
         if (w->h_entity_node[ids[i]] != kNone)
-            w->transforms_dirty = true;
+            nodes.push_back(w->h_entity_node[ids[i]]);
+    if (!nodes.empty()) {
+        w->transforms_dirty = true;
+        if (!w->all_dirty) {
+            void *dn = nullptr;
+            OVIS_TRY(stage(w, 1, nodes.data(), sizeof(uint32_t) * nodes.size(), &dn));
+            ovis::launch_mark_dirty((const uint32_t *)dn, (int64_t)nodes.size(), w->d_dirty, w->stream);
+            w->launches++;
+            w->marks_present = true;
+            OVIS_CUDA(cudaStreamSynchronize(w->stream));   // `nodes` is a local
+        }
+    }
     return OVIS_OK;
 }
 
@@ -1098,10 +1126,24 @@ int ovis_node_set_local_trs(OvisWorld *w, int64_t n, const uint32_t *ids, const 
         OVIS_TRY(stage(w, 1, ids + s, sizeof(uint32_t) * (size_t)c, &di));
         ovis::launch_scatter_aos(10, (const float *)d, (const uint32_t *)di, 0, c, w->d_local_trs, w->cap_nodes, w->stream);
         w->launches++;
+        if (!w->all_dirty) {
+            ovis::launch_mark_dirty((const uint32_t *)di, c, w->d_dirty, w->stream);
+            w->launches++;
+            w->marks_present = true;
+        }
     }
     OVIS_CUDA(cudaGetLastError());
     if (n > 0)
         w->transforms_dirty = true;
+    if (!w->all_dirty) {
+        // estimate how much of the tree sits below the moved nodes; when it is most of it, recompute everything
+        // and skip the per-node flag traffic
+        int64_t below = 0;
+        for (int64_t i = 0; i < n && below < w->n_nodes; i++)
+            below += w->h_subtree[ids[i]];
+        if (below >= w->n_nodes / 3)
+            w->all_dirty = true;
+    }
     return OVIS_OK;
 }
 

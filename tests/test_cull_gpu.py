@@ -337,3 +337,34 @@ def test_multi_view_many_views_and_empty(oracle):
     off0, _, _ = w0.cull_views_device(planes[:3])
     assert np.array_equal(off0, np.zeros(4, dtype=np.int64))
     w0.close()
+
+
+def test_partial_updates_touch_only_moved_subtrees(oracle):
+    """Only nodes below a moved node are recomputed (Entity::transformed runs from the moved entity down); the rest must
+    keep their values, including second entities on a node and a changed local box of a node-bound entity."""
+    rng = np.random.default_rng(41)
+    n = 20_000
+    parent = np.empty(n, dtype=np.int32)
+    parent[:50] = -1
+    parent[50:] = (rng.random(n - 50) * np.arange(50, n)).astype(np.int32)
+    local = util.random_trs(rng, n)
+    local[:, 7:10] = rng.uniform(0.6, 1.4, (n, 3))
+    boxes = util.random_boxes(rng, n + 300, extent=2.0, hmax=2.0)
+    w = lib.World(0)
+    w.add_entities(boxes)
+    w.add_nodes(parent, local)
+    ent_node = np.concatenate([np.arange(n), rng.integers(0, n, 300)]).astype(np.uint32)   # 300 second entities
+    w.bind_entities(ent_node, np.arange(n + 300))
+    for step in range(4):
+        moved = rng.choice(n, [1, 30, 400, 15000][step], replace=False).astype(np.uint32)   # the last one flips to "all"
+        local[moved] = util.random_trs(rng, len(moved))
+        local[moved, 7:10] = rng.uniform(0.6, 1.4, (len(moved), 3))
+        w.set_node_local_trs(moved, local[moved])
+        if step == 1:
+            changed = rng.choice(n + 300, 40, replace=False).astype(np.uint32)
+            boxes[changed] = util.random_boxes(rng, 40, extent=1.0)
+            w.set_local_aabbs(changed, boxes[changed])
+        wt = oracle.world_trs(parent, local)
+        assert same(w.node_world_trs(), wt)
+        assert same(w.world_aabbs(), oracle.world_aabb(wt[ent_node], boxes))
+    w.close()

@@ -76,6 +76,17 @@ def config3(small):
         w.update_transforms()
 
     upd_ms, _ = timed(stream, update_pre, iters=7)
+    # a frame in which only 1 % of the groups move (dirty-subtree update)
+    few = group_ids[:: 100]
+    few_moves = [m[:: 100] for m in moves]
+
+    def update_few():
+        frame[0] = frame[0] % 8 + 1
+        w.set_node_local_trs(few, few_moves[frame[0] - 1])
+        w.update_transforms()
+
+    upd_few_ms, _ = timed(stream, update_few, iters=7)
+    update_pre()                       # leave the tree in a fully known state for the parity check below
     planes = lib.view_planes(s["view"])
     out = torch.zeros(n_ent + 1, dtype=torch.int32, device="cuda")
     cull_ms, _ = timed(stream, lambda: w.cull_planes_device(planes, out.data_ptr() + 4, out.data_ptr()), iters=10)
@@ -118,7 +129,7 @@ def config3(small):
     return {
         "workload": f"configs[2]: {n_ent / 1e6:g}M dynamic entities, depth-3 hierarchy ({n_nodes} nodes), {len(s['lights'])} point lights",
         "scene_generation_s": gen_s, "world_build_s": build_s,
-        "update_ms": upd_ms, "update_bytes_per_node": 132,
+        "update_ms": upd_ms, "update_1pct_of_groups_ms": upd_few_ms, "update_bytes_per_node": 132,
         "update_achieved_gbs": 132 * n_nodes / (upd_ms * 1e-3) / 1e9,
         "main_cull_ms": cull_ms, "visible_entities": int(len(ents)), "visible_lights": int(len(ls)),
         "cull_with_lights_host_api_ms": full_cull_host_ms,
