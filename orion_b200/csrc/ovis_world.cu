@@ -292,7 +292,8 @@ int add_nodes(OvisWorld *w, int64_t n, const int32_t *parent, const float *local
         int32_t p = parent[i];
         w->h_parent[(size_t)(first + i)] = p;
         w->h_level[(size_t)(first + i)] = p < 0 ? 0 : w->h_level[(size_t)p] + 1;
-        for (int32_t a = p; a >= 0; a = w->h_parent[(size_t)a])      // O(depth): scene trees are shallow
+        int hops = 0;                                                 // an estimate is enough: stop after 64 ancestors
+        for (int32_t a = p; a >= 0 && hops < 64; a = w->h_parent[(size_t)a], hops++)
             w->h_subtree[(size_t)a]++;
     }
     for (int64_t s = 0; s < n; s += kUploadChunk) {
