@@ -10,6 +10,8 @@
 // warp covers 128 consecutive entities with fully coalesced 512 B requests per array.
 #include "ovis_kernels.h"
 
+#include <cooperative_groups.h>
+
 #include "ovis_device.cuh"
 
 namespace ovis {
@@ -234,8 +236,7 @@ void launch_mark_dirty(const uint32_t *ids, int64_t n, uint8_t *dirty, cudaStrea
 // ------------------------------------------------------------------------------------------------
 
 template <int GROUPS, bool MASKED>
-__global__ void __launch_bounds__(kCullThreads, 4 / GROUPS)
-cull_test_kernel(const __grid_constant__ CullArgs a) {
+__device__ __forceinline__ void cull_test_body(const CullArgs &a) {
     constexpr int WT = 128 * GROUPS;                       // entities per warp tile
     const int lane = threadIdx.x & 31;
     const int warps_total = gridDim.x * (kCullThreads / 32);
@@ -318,15 +319,18 @@ cull_test_kernel(const __grid_constant__ CullArgs a) {
     }
 }
 
-__global__ void __launch_bounds__(256)
-cull_gather_kernel(const __grid_constant__ GatherArgs a) {
+template <int GROUPS, bool MASKED>
+__global__ void __launch_bounds__(kCullThreads, 4 / GROUPS)
+cull_test_kernel(const __grid_constant__ CullArgs a) {
+    cull_test_body<GROUPS, MASKED>(a);
+}
+
+// Gather of one block of kGatherTiles warp tiles by one 256-thread CTA; `num_gather_blocks` = blocks in the launch.
+__device__ __forceinline__ void cull_gather_body(const GatherArgs &a, int block, int num_gather_blocks) {
     __shared__ uint32_t s_scan[kGatherTiles + 1];   // exclusive scan of this block's tile counts, then the block sum
     __shared__ uint32_t s_warp[8];
     __shared__ uint32_t s_base;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int block = blockIdx.x;
-    // Let the next cull's test kernel start now (if it was launched to allow that): it shares nothing with this kernel.
-    asm volatile("griddepcontrol.launch_dependents;");
 
     // base = survivors in all earlier blocks
     uint32_t part = 0;
@@ -371,7 +375,7 @@ cull_gather_kernel(const __grid_constant__ GatherArgs a) {
     const uint32_t total = s_scan[kGatherTiles];
     const long long out_base = a.d_base ? *a.d_base : 0ll;
     const long long dst0 = out_base + (long long)s_base;
-    if (block == gridDim.x - 1 && tid == 0) {               // the last block knows the grand total
+    if (block == num_gather_blocks - 1 && tid == 0) {       // the last block knows the grand total
         uint32_t grand = s_base + total;
         if (a.d_count) *a.d_count = grand;
         if (a.d_next) *a.d_next = out_base + (long long)grand;
@@ -407,6 +411,27 @@ cull_gather_kernel(const __grid_constant__ GatherArgs a) {
     }
 }
 
+__global__ void __launch_bounds__(256)
+cull_gather_kernel(const __grid_constant__ GatherArgs a) {
+    // Let the next cull's test kernel start now (if it was launched to allow that): it shares nothing with this kernel.
+    asm volatile("griddepcontrol.launch_dependents;");
+    cull_gather_body(a, blockIdx.x, gridDim.x);
+}
+
+// Small worlds are bound by launch and memory latency, not bandwidth: both phases in ONE cooperative launch with a grid
+// barrier in between save a kernel boundary and a launch (configs[1], 1 M entities: see profiles/r01_cull_notes.md).
+template <int GROUPS, bool MASKED>
+__global__ void __launch_bounds__(kCullThreads, 4 / GROUPS)
+cull_fused_kernel(const __grid_constant__ CullArgs a, const __grid_constant__ GatherArgs g) {
+    cull_test_body<GROUPS, MASKED>(a);
+    cooperative_groups::this_grid().sync();
+    const int num_gather_blocks = (g.num_tiles + kGatherTiles - 1) / kGatherTiles;
+    for (int b = blockIdx.x; b < num_gather_blocks; b += gridDim.x) {
+        cull_gather_body(g, b, num_gather_blocks);
+        __syncthreads();                                    // shared scan arrays are reused by the next block
+    }
+}
+
 // Launch shapes selectable at run time (OVIS_CULL_VARIANT, tuning only). Variant 0 is the default.
 static const CullVariant kVariants[] = { { 2 }, { 1 }, { 4 } };
 
@@ -439,6 +464,31 @@ void launch_cull_test(const CullArgs &a, bool masked, int variant, int grid, cud
         cfg.numAttrs = overlap_previous_gather ? 1 : 0;
         cudaLaunchKernelEx(&cfg, kernel, a);
     });
+}
+
+// Cooperative single launch of both phases; grid must not exceed the co-resident capacity (the caller sizes it so).
+cudaError_t launch_cull_fused(const CullArgs &a, const GatherArgs &g, bool masked, int variant, int grid, cudaStream_t s) {
+    cudaError_t err = cudaSuccess;
+    auto go = [&](auto kernel) {
+        void *params[2] = { (void *)&a, (void *)&g };
+        err = cudaLaunchCooperativeKernel((const void *)kernel, dim3((unsigned)grid), dim3(kCullThreads), params, 0, s);
+    };
+    switch (kVariants[variant].groups) {
+    case 1: if (masked) go(cull_fused_kernel<1, true>); else go(cull_fused_kernel<1, false>); break;
+    case 2: if (masked) go(cull_fused_kernel<2, true>); else go(cull_fused_kernel<2, false>); break;
+    default: err = cudaErrorInvalidValue; break;
+    }
+    return err;
+}
+
+int cull_fused_max_blocks_per_sm(bool masked, int variant) {
+    int blocks = 0;
+    auto q = [&](auto kernel) { cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks, kernel, kCullThreads, 0); };
+    switch (kVariants[variant].groups) {
+    case 1: if (masked) q(cull_fused_kernel<1, true>); else q(cull_fused_kernel<1, false>); break;
+    case 2: if (masked) q(cull_fused_kernel<2, true>); else q(cull_fused_kernel<2, false>); break;
+    }
+    return blocks;
 }
 
 void launch_cull_gather(const GatherArgs &a, cudaStream_t s) {

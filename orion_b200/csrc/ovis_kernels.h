@@ -135,6 +135,8 @@ int cull_num_variants();
 CullVariant cull_variant(int v);
 void launch_cull_test(const CullArgs &a, bool masked, int variant, int grid, cudaStream_t s, bool overlap_previous_gather);
 void launch_cull_gather(const GatherArgs &a, cudaStream_t s);
+int cull_fused_max_blocks_per_sm(bool masked, int variant);
+cudaError_t launch_cull_fused(const CullArgs &a, const GatherArgs &g, bool masked, int variant, int grid, cudaStream_t s);
 int cull_test_max_blocks_per_sm(bool masked, int variant);
 void launch_empty_result(const long long *d_base, long long *d_next, uint32_t *d_count, cudaStream_t s);
 void launch_cull_lights(const LightCullArgs &a, cudaStream_t s);

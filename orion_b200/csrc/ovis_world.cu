@@ -66,7 +66,9 @@ struct OvisWorld {
     cudaStream_t stream = nullptr;
     int num_sms = 0;
     int forced_variant = -1;              // OVIS_CULL_VARIANT (tuning); -1 = pick by size
+    bool fused_small = true;              // OVIS_CULL_FUSED=0 (tuning) keeps small worlds on the two-launch path
     int blocks_per_sm[8][2] = {};         // cull test kernel occupancy per variant: [unmasked, masked]
+    int fused_blocks_per_sm[8][2] = {};   // same for the fused (cooperative) kernel; 0 = not available
     int64_t launches = 0;
     uint32_t id_base = 0;                 // global id of slot 0 (sharded worlds)
 
@@ -492,9 +494,6 @@ int enqueue_cull(OvisWorld *w, const float planes[24], uint32_t require, uint32_
         w->timing_used += 3;
         OVIS_CUDA(cudaEventRecord(ev[0], w->stream));
     }
-    ovis::launch_cull_test(a, masked, variant, grid, w->stream, /*overlap_previous_gather=*/true);
-    if (ev)
-        OVIS_CUDA(cudaEventRecord(ev[1], w->stream));
     ovis::GatherArgs g;
     g.staging = a.staging;
     g.tile_counts = a.tile_counts;
@@ -511,11 +510,28 @@ int enqueue_cull(OvisWorld *w, const float planes[24], uint32_t require, uint32_
         g.extra_out[x] = extra_out[x];
         g.extra_count[x] = extra_count[x];
     }
-    ovis::launch_cull_gather(g, w->stream);
-    if (ev)
-        OVIS_CUDA(cudaEventRecord(ev[2], w->stream));
+    // Below ~half a million entities the cull is pure latency: one cooperative launch runs both phases with a grid
+    // barrier in between. Larger worlds use two launches, the second overlapped with the next cull's first.
+    const int fused_per_sm = w->fused_blocks_per_sm[variant][masked ? 1 : 0];
+    const bool fused = w->fused_small && w->n_ent < (512 << 10) && fused_per_sm > 0;
+    if (fused) {
+        grid = std::min(warps_needed_blocks, w->num_sms * fused_per_sm);      // every CTA must be co-resident
+        OVIS_CUDA(ovis::launch_cull_fused(a, g, masked, variant, grid, w->stream));
+        if (ev) {
+            OVIS_CUDA(cudaEventRecord(ev[1], w->stream));
+            OVIS_CUDA(cudaEventRecord(ev[2], w->stream));
+        }
+        w->launches += 1;
+    } else {
+        ovis::launch_cull_test(a, masked, variant, grid, w->stream, /*overlap_previous_gather=*/true);
+        if (ev)
+            OVIS_CUDA(cudaEventRecord(ev[1], w->stream));
+        ovis::launch_cull_gather(g, w->stream);
+        if (ev)
+            OVIS_CUDA(cudaEventRecord(ev[2], w->stream));
+        w->launches += 2;
+    }
     w->cull_serial++;
-    w->launches += 2;
     OVIS_CUDA(cudaGetLastError());
     return OVIS_OK;
 }
@@ -822,9 +838,13 @@ int ovis_world_create(int device, OvisWorld **out_world) {
         if (k >= 0 && k < ovis::cull_num_variants())
             w->forced_variant = k;
     }
+    if (const char *v = getenv("OVIS_CULL_FUSED"))
+        w->fused_small = atoi(v) != 0;
     for (int v = 0; v < ovis::cull_num_variants() && v < 8; v++) {
         w->blocks_per_sm[v][0] = std::max(1, ovis::cull_test_max_blocks_per_sm(false, v));
         w->blocks_per_sm[v][1] = std::max(1, ovis::cull_test_max_blocks_per_sm(true, v));
+        w->fused_blocks_per_sm[v][0] = ovis::cull_fused_max_blocks_per_sm(false, v);
+        w->fused_blocks_per_sm[v][1] = ovis::cull_fused_max_blocks_per_sm(true, v);
     }
     OVIS_CUDA(cudaMalloc(&w->d_counts, 2 * sizeof(uint32_t)));
     OVIS_CUDA(cudaMemset(w->d_counts, 0, 2 * sizeof(uint32_t)));
