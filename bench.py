@@ -362,18 +362,9 @@ def run_ours(args, rank: int, local_rank: int, world_size: int):
             return len(ents)
         d2h = 8 + 4 * total_visible
     else:
-        pinned_t = torch.empty(total_visible * 2 + world_size, dtype=torch.int32).pin_memory()
-
         def e2e_step():
-            b, c = sw.cull(lib.view_planes(view))           # device blocks + per-rank counts on the host
-            with torch.cuda.stream(stream):
-                at = 0
-                for r in range(world_size):                  # the merged list, rank order, into pinned host memory
-                    k = int(c[r])
-                    pinned_t[at:at + k].copy_(b[r, 1:1 + k], non_blocking=True)
-                    at += k
-            stream.synchronize()
-            return int(c.sum())
+            parts = sw.cull_to_host(lib.view_planes(view))   # merged (segmented) list in pinned host memory
+            return int(sum(len(p) for p in parts))
         d2h = 4 * total_visible + 4 * world_size
     for _ in range(3):
         e2e_step()

@@ -100,6 +100,8 @@ class ShardedWorld:
         self.resize(max(1024, n_local // 8))
         self.exchange_mode = "nccl"
         self.frame = 0
+        self._pinned = None
+        self._last_max = 0
         if exchange == "p2p" and world_size > 1:
             cap = int(min(n_local, p2p_capacity or max(1024, n_local // 8)))
             opened = open_symmetric_blocks(world_size, cap, group)
@@ -155,6 +157,33 @@ class ShardedWorld:
         self.ready = torch.cuda.Event()
         self.ready.record(self.stream)
         return blocks
+
+    def cull_to_host(self, planes, require: int = 0):
+        """One frame end to end: cull + exchange, then the merged list in pinned host memory with ONE strided copy
+        sized from the previous frame's counts (a frame that grew past it pays a second copy). Returns a list of
+        per-rank uint32 arrays (views of the pinned buffer, valid until the next call); rank order = list order."""
+        blocks = self.cull_device(planes, require)
+        spec = int(min(self.capacity, self._last_max + self._last_max // 4 + 256))
+        if self._pinned is None or self._pinned.shape[1] < self.capacity + 1:
+            self._pinned = torch.empty((self.size, self.capacity + 1), dtype=torch.int32).pin_memory()
+        with torch.cuda.stream(self.stream):
+            self.stream.wait_event(self.ready)
+            self._pinned[:, :spec + 1].copy_(blocks[:, :spec + 1], non_blocking=True)
+        self.stream.synchronize()
+        host = self._pinned.numpy()
+        counts = host[:, 0].astype(np.int64)
+        top = int(counts.max(initial=0))
+        if top > self.capacity:
+            if self.exchange_mode == "p2p":
+                raise RuntimeError(f"visible list of {top} ids exceeds the symmetric segment capacity {self.capacity}")
+            self.resize(int(top * 1.25) + 1024)
+            return self.cull_to_host(planes, require)
+        if top > spec:
+            with torch.cuda.stream(self.stream):
+                self._pinned[:, spec + 1:top + 1].copy_(blocks[:, spec + 1:top + 1], non_blocking=True)
+            self.stream.synchronize()
+        self._last_max = top
+        return [host[r, 1:1 + int(counts[r])].view(np.uint32) for r in range(self.size)]
 
     def wait_all(self):
         """Block the host until every enqueued frame (cull stream and barrier stream) has finished."""

@@ -33,6 +33,9 @@ for mode in ("nccl", "p2p"):
         got = merged_list(blocks, counts)
         exp = oracle.cull_aabb(aabb, planes, flags, req, threads=4)
         assert np.array_equal(got, exp), (mode, rank, len(got), len(exp))
+        for _ in range(2):                                   # host path: speculative copy, then steady state
+            parts = sw.cull_to_host(planes, req)
+            assert np.array_equal(np.concatenate(parts), exp), (mode, rank, "host")
     assert mode == "nccl" or sw.exchange_mode == "p2p", "symmetric memory path did not come up"
     dist.barrier()
     w.close()
