@@ -318,8 +318,8 @@ def run_ours(args, rank: int, local_rank: int, world_size: int):
                 blocks = sw.cull_device(planes)        # cull + exchange (fused P2P stores, or NCCL all-gather)
             else:
                 sw.cull_local(planes)
-        if world_size > 1 and sw.exchange_mode == "p2p":
-            stream.wait_event(sw.ready)                # the last frame's barrier (side stream) is part of the K steps
+        if world_size > 1:
+            sw.enqueue_ready_wait()                    # the last frame is only done when every peer's segment has landed
         ev1.record(stream)
     barrier()
     t_wall1 = time.perf_counter()
@@ -398,7 +398,7 @@ def run_ours(args, rank: int, local_rank: int, world_size: int):
         "config": {"workload": workload_name(world_size, n), "entities_total": total_entities, "views": 1,
                    "visible_total": total_visible,
                    "parallelism": ((f"entity shards x{world_size}, exchange of visible lists: " +
-                                    ("gather kernel stores to peers over NVLink + barrier" if sw.exchange_mode == "p2p"
+                                    ("gather kernel stores to peers over NVLink + ready flags, no collective" if sw.exchange_mode == "p2p"
                                      else "NCCL all-gather")) if world_size > 1 else "1 GPU"),
                    "cache": "inputs larger than L2 (300 MB of bounds per GPU vs 126 MB L2); no flush needed"},
         "cull_ms_per_frame": elapsed_ms / args.steps,

@@ -411,11 +411,62 @@ __device__ __forceinline__ void cull_gather_body(const GatherArgs &a, int block,
     }
 }
 
+__device__ __forceinline__ uint32_t load_flag_sys(const uint32_t *p) {
+    uint32_t v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+
+__device__ __forceinline__ void store_flag_sys(uint32_t *p, uint32_t v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+// Spin until flags[i] >= value for every i, at most ~2 s (a peer that never arrives must not hang the GPU).
+__device__ __forceinline__ void wait_flags_at_least(const uint32_t *flags, int n, uint32_t value, uint32_t *error_flag) {
+    const long long start = clock64();
+    for (int i = 0; i < n; i++) {
+        while ((int32_t)(load_flag_sys(flags + i) - value) < 0) {
+            if (clock64() - start > 4000000000ll) {
+                if (error_flag)
+                    *error_flag = 1u;
+                return;
+            }
+            __nanosleep(100);
+        }
+    }
+}
+
 __global__ void __launch_bounds__(256)
 cull_gather_kernel(const __grid_constant__ GatherArgs a) {
     // Let the next cull's test kernel start now (if it was launched to allow that): it shares nothing with this kernel.
     asm volatile("griddepcontrol.launch_dependents;");
+    if (a.n_wait) {                                           // peers must be done with the buffer we are about to refill
+        if (threadIdx.x == 0)
+            wait_flags_at_least(a.wait_flags, a.n_wait, a.wait_value, a.error_flag);
+        __syncthreads();
+    }
     cull_gather_body(a, blockIdx.x, gridDim.x);
+    if (a.n_signal) {                                         // the last block to finish publishes the segment
+        __syncthreads();                                      // this block's stores happen-before thread 0's fence
+        if (threadIdx.x == 0) {
+            __threadfence_system();                           // one system fence per block (cumulative over the barrier)
+            unsigned int prev = atomicAdd(a.done_counter, 1u);
+            if (prev == gridDim.x - 1) {
+                *a.done_counter = 0u;
+                __threadfence_system();
+                for (int x = 0; x < a.n_signal; x++)
+                    store_flag_sys(a.signal_flags[x], a.signal_value);
+            }
+        }
+    }
+}
+
+__global__ void wait_flags_kernel(const uint32_t *flags, int n, uint32_t value, uint32_t *error_flag) {
+    wait_flags_at_least(flags, n, value, error_flag);
+}
+
+void launch_wait_flags(const uint32_t *flags, int n, uint32_t value, uint32_t *error_flag, cudaStream_t s) {
+    wait_flags_kernel<<<1, 1, 0, s>>>(flags, n, value, error_flag);
 }
 
 // Small worlds are bound by launch and memory latency, not bandwidth: both phases in ONE cooperative launch with a grid

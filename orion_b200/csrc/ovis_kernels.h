@@ -66,6 +66,17 @@ struct GatherArgs {               // K3b
     int n_extra;
     uint32_t *extra_out[kMaxPeers];
     uint32_t *extra_count[kMaxPeers];
+    // One-way flags instead of a barrier (sharded worlds, all optional):
+    //   before storing, wait until every wait_flags[i] >= wait_value  (peers are done reading the buffer being reused);
+    //   after ALL blocks have stored, write signal_value to every signal_flags[x] (this shard's segment is complete).
+    int n_wait;
+    const uint32_t *wait_flags;
+    uint32_t wait_value;
+    int n_signal;
+    uint32_t *signal_flags[kMaxPeers + 1];
+    uint32_t signal_value;
+    unsigned int *done_counter;   // scratch, zero between launches
+    uint32_t *error_flag;         // set to 1 if a wait gave up (a peer never arrived)
 };
 
 // ---- K4 multi-view ------------------------------------------------------------------------------
@@ -135,6 +146,7 @@ int cull_num_variants();
 CullVariant cull_variant(int v);
 void launch_cull_test(const CullArgs &a, bool masked, int variant, int grid, cudaStream_t s, bool overlap_previous_gather);
 void launch_cull_gather(const GatherArgs &a, cudaStream_t s);
+void launch_wait_flags(const uint32_t *flags, int n, uint32_t value, uint32_t *error_flag, cudaStream_t s);
 int cull_fused_max_blocks_per_sm(bool masked, int variant);
 cudaError_t launch_cull_fused(const CullArgs &a, const GatherArgs &g, bool masked, int variant, int grid, cudaStream_t s);
 int cull_test_max_blocks_per_sm(bool masked, int variant);

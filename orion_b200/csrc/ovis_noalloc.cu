@@ -165,6 +165,10 @@ extern "C" int ovis_cull_planes_noalloc(int device, void *cuda_stream, const flo
     g.d_next = nullptr;
     g.d_count = d_out_count;
     g.n_extra = 0;
+    g.n_wait = 0;
+    g.n_signal = 0;
+    g.done_counter = nullptr;
+    g.error_flag = nullptr;
     ovis::launch_cull_gather(g, stream);
     err = cudaGetLastError();
     if (err != cudaSuccess)

@@ -124,6 +124,7 @@ struct OvisWorld {
     int64_t last_visible = 0;             // entity count of the previous host-output cull (sizes the speculative copy)
     uint32_t *d_result = nullptr;         // cap_ent visible ids
     uint32_t *d_counts = nullptr;         // [0] entities, [1] lights
+    unsigned int *d_exchange = nullptr;   // [0] gather done counter, [1] exchange error flag
     uint32_t *h_counts = nullptr;         // pinned mirror
     uint32_t *d_csr_entities = nullptr;
     int64_t cap_csr = 0;
@@ -450,9 +451,19 @@ void load_planes(float4 dst[6], const float planes[24]) {
 }
 
 // Enqueue one entity cull (K3). Output goes to `out` (device) starting at *d_base (or 0).
+struct FlagOpts {            // one-way ready flags of a sharded exchange (ovis_cull_planes_device_exchange)
+    int n_wait = 0;
+    const uint32_t *wait_flags = nullptr;
+    uint32_t wait_value = 0;
+    int n_signal = 0;
+    uint32_t *const *signal_flags = nullptr;
+    uint32_t signal_value = 0;
+};
+
 int enqueue_cull(OvisWorld *w, const float planes[24], uint32_t require, uint32_t *out, long long capacity,
                  const long long *d_base, long long *d_next, uint32_t *d_count, int n_extra = 0,
-                 uint32_t *const *extra_out = nullptr, uint32_t *const *extra_count = nullptr) {
+                 uint32_t *const *extra_out = nullptr, uint32_t *const *extra_count = nullptr,
+                 const FlagOpts *flags = nullptr) {
     if (require & ~(uint32_t)OVIS_CASTS_SHADOW)
         return fail(OVIS_ERR_INVALID, "require mask 0x%x: only 0 or OVIS_CASTS_SHADOW is supported", require);
     if (w->n_ent == 0) {
@@ -510,10 +521,23 @@ int enqueue_cull(OvisWorld *w, const float planes[24], uint32_t require, uint32_
         g.extra_out[x] = extra_out[x];
         g.extra_count[x] = extra_count[x];
     }
+    g.n_wait = 0;
+    g.n_signal = 0;
+    g.done_counter = w->d_exchange;
+    g.error_flag = w->d_exchange + 1;
+    if (flags) {
+        g.n_wait = flags->n_wait;
+        g.wait_flags = flags->wait_flags;
+        g.wait_value = flags->wait_value;
+        g.n_signal = flags->n_signal;
+        for (int x = 0; x < flags->n_signal; x++)
+            g.signal_flags[x] = flags->signal_flags[x];
+        g.signal_value = flags->signal_value;
+    }
     // Below ~half a million entities the cull is pure latency: one cooperative launch runs both phases with a grid
     // barrier in between. Larger worlds use two launches, the second overlapped with the next cull's first.
     const int fused_per_sm = w->fused_blocks_per_sm[variant][masked ? 1 : 0];
-    const bool fused = w->fused_small && w->n_ent < (512 << 10) && fused_per_sm > 0;
+    const bool fused = w->fused_small && w->n_ent < (512 << 10) && fused_per_sm > 0 && n_extra == 0 && !flags;
     if (fused) {
         grid = std::min(warps_needed_blocks, w->num_sms * fused_per_sm);      // every CTA must be co-resident
         OVIS_CUDA(ovis::launch_cull_fused(a, g, masked, variant, grid, w->stream));
@@ -846,6 +870,8 @@ int ovis_world_create(int device, OvisWorld **out_world) {
         w->fused_blocks_per_sm[v][0] = ovis::cull_fused_max_blocks_per_sm(false, v);
         w->fused_blocks_per_sm[v][1] = ovis::cull_fused_max_blocks_per_sm(true, v);
     }
+    OVIS_CUDA(cudaMalloc(&w->d_exchange, 2 * sizeof(unsigned int)));
+    OVIS_CUDA(cudaMemset(w->d_exchange, 0, 2 * sizeof(unsigned int)));
     OVIS_CUDA(cudaMalloc(&w->d_counts, 2 * sizeof(uint32_t)));
     OVIS_CUDA(cudaMemset(w->d_counts, 0, 2 * sizeof(uint32_t)));
     OVIS_CUDA(cudaMallocHost(&w->h_counts, 2 * sizeof(uint32_t)));
@@ -860,7 +886,7 @@ int ovis_world_destroy(OvisWorld *w) {
     cudaStreamSynchronize(w->stream);
     void *bufs[] = { w->d_local, w->d_world, w->d_alive_bits, w->d_caster_bits, w->d_parent, w->d_local_trs, w->d_world_trs,
                      w->d_node_entity, w->d_dirty, w->d_extra_entity, w->d_extra_node, w->d_level_lists, w->d_lights, w->d_light_out,
-                     w->d_staging, w->d_tile_counts, w->d_block_totals, w->d_mv_counts, w->d_mv_totals, w->d_mv_planes,
+                     w->d_staging, w->d_tile_counts, w->d_block_totals, w->d_exchange, w->d_mv_counts, w->d_mv_totals, w->d_mv_planes,
                      w->d_mv_require, w->d_mv_groups, w->d_mv_hits, w->d_result, w->d_counts, w->d_csr_entities, w->d_csr_offsets,
                      w->d_stage[0], w->d_stage[1] };
     for (void *b : bufs)
@@ -1287,6 +1313,50 @@ int ovis_cull_planes_device_multi(OvisWorld *w, const float planes[24], uint32_t
     }
     return enqueue_cull(w, planes, require, d_out_entities[0], capacity, nullptr, nullptr, d_out_count[0], n_dst - 1,
                         d_out_entities + 1, d_out_count + 1);
+}
+
+int ovis_cull_planes_device_exchange(OvisWorld *w, const float planes[24], uint32_t require, int64_t capacity,
+                                     int32_t n_dst, uint32_t *const *d_out_entities, uint32_t *const *d_out_count,
+                                     int32_t n_wait, const uint32_t *d_wait_flags, uint32_t wait_value,
+                                     int32_t n_signal, uint32_t *const *d_signal_flags, uint32_t signal_value) {
+    if (!w || !planes || n_dst < 1 || n_dst > ovis::kMaxPeers + 1 || !d_out_entities || !d_out_count || capacity < 0 ||
+        n_wait < 0 || (n_wait > 0 && !d_wait_flags) || n_signal < 0 || n_signal > ovis::kMaxPeers + 1 ||
+        (n_signal > 0 && !d_signal_flags))
+        return fail(OVIS_ERR_INVALID, "ovis_cull_planes_device_exchange: bad arguments");
+    OVIS_TRY(use_device(w));
+    OVIS_TRY(flush_transforms(w));
+    if (w->n_ent == 0)
+        return fail(OVIS_ERR_INVALID, "ovis_cull_planes_device_exchange: the shard holds no entities");
+    FlagOpts f;
+    f.n_wait = n_wait;
+    f.wait_flags = d_wait_flags;
+    f.wait_value = wait_value;
+    f.n_signal = n_signal;
+    f.signal_flags = d_signal_flags;
+    f.signal_value = signal_value;
+    return enqueue_cull(w, planes, require, d_out_entities[0], capacity, nullptr, nullptr, d_out_count[0], n_dst - 1,
+                        d_out_entities + 1, d_out_count + 1, &f);
+}
+
+int ovis_wait_flags(OvisWorld *w, const uint32_t *d_flags, int32_t n, uint32_t value) {
+    if (!w || !d_flags || n < 1)
+        return fail(OVIS_ERR_INVALID, "ovis_wait_flags: bad arguments");
+    OVIS_TRY(use_device(w));
+    ovis::launch_wait_flags(d_flags, n, value, w->d_exchange + 1, w->stream);
+    w->launches++;
+    OVIS_CUDA(cudaGetLastError());
+    return OVIS_OK;
+}
+
+int ovis_world_exchange_error(OvisWorld *w, int32_t *out_error) {
+    if (!w || !out_error)
+        return fail(OVIS_ERR_INVALID, "ovis_world_exchange_error: null argument");
+    OVIS_TRY(use_device(w));
+    unsigned int v = 0;
+    OVIS_CUDA(cudaMemcpyAsync(&v, w->d_exchange + 1, sizeof v, cudaMemcpyDeviceToHost, w->stream));
+    OVIS_CUDA(cudaStreamSynchronize(w->stream));
+    *out_error = (int32_t)v;
+    return OVIS_OK;
 }
 
 static int cull_to_host(OvisWorld *w, const float planes[24], uint32_t require, bool with_lights,

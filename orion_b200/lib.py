@@ -306,6 +306,41 @@ class World:
         _check(self.lib.ovis_cull_planes_device_multi(self.h, _p(planes), C.c_uint32(require), C.c_int64(capacity),
                                                       C.c_int32(n), outs, counts))
 
+    def cull_planes_device_exchange(self, planes, d_out_ptrs, d_count_ptrs, capacity, wait_flags_ptr, n_wait, wait_value,
+                                    signal_ptrs, signal_value, require=0):
+        """Cull + fused exchange with one-way ready flags (see ovis_cull_planes_device_exchange). Asynchronous."""
+        planes = _f32(planes, (24,))
+        n = len(d_out_ptrs)
+        outs = (C.c_void_p * n)(*d_out_ptrs)
+        counts = (C.c_void_p * n)(*d_count_ptrs)
+        sig = (C.c_void_p * len(signal_ptrs))(*signal_ptrs)
+        _check(self.lib.ovis_cull_planes_device_exchange(
+            self.h, _p(planes), C.c_uint32(require), C.c_int64(capacity), C.c_int32(n), outs, counts,
+            C.c_int32(n_wait), C.c_void_p(wait_flags_ptr), C.c_uint32(wait_value & 0xffffffff),
+            C.c_int32(len(signal_ptrs)), sig, C.c_uint32(signal_value & 0xffffffff)))
+
+    @staticmethod
+    def exchange_plan(d_out_ptrs, d_count_ptrs, signal_ptrs):
+        """Pre-built ctypes argument arrays for cull_exchange_planned (keeps per-frame host work minimal)."""
+        n = len(d_out_ptrs)
+        return ((C.c_void_p * n)(*d_out_ptrs), (C.c_void_p * n)(*d_count_ptrs), C.c_int32(n),
+                (C.c_void_p * len(signal_ptrs))(*signal_ptrs), C.c_int32(len(signal_ptrs)))
+
+    def cull_exchange_planned(self, planes_f32, plan, capacity, wait_flags_ptr, n_wait, wait_value, signal_value, require=0):
+        outs, counts, n, sig, n_sig = plan
+        _check(self.lib.ovis_cull_planes_device_exchange(
+            self.h, planes_f32.ctypes.data_as(C.c_void_p), C.c_uint32(require), C.c_int64(capacity), n, outs, counts,
+            C.c_int32(n_wait), C.c_void_p(wait_flags_ptr), C.c_uint32(wait_value & 0xffffffff), n_sig, sig,
+            C.c_uint32(signal_value & 0xffffffff)))
+
+    def wait_flags(self, d_flags_ptr, n, value):
+        _check(self.lib.ovis_wait_flags(self.h, C.c_void_p(d_flags_ptr), C.c_int32(n), C.c_uint32(value & 0xffffffff)))
+
+    def exchange_error(self) -> int:
+        e = C.c_int32()
+        _check(self.lib.ovis_world_exchange_error(self.h, C.byref(e)))
+        return e.value
+
     def cull_views_device(self, planes, require=None):
         """Many views, CSR result on the device. Returns (host offsets, d_offsets ptr, d_entities ptr)."""
         planes = _f32(planes, (-1, 24))

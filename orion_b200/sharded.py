@@ -54,11 +54,16 @@ P2P_BUFFERS = 3
 def open_symmetric_blocks(world_size: int, capacity: int, group=None):
     """Three (world_size, capacity + 1) int32 buffers in NVLink-mapped symmetric memory, used in rotation.
 
-    Returns (tensors, handles) or None when torch's symmetric memory is unavailable (then NCCL all-gather is used).
+    Also one (world_size,) int32 flag array per rank: flags[src] = last frame whose segment from rank `src` is complete
+    here. Returns (tensors, handles, flags, flag_handle), or None when torch's symmetric memory is unavailable (then NCCL
+    all-gather is used).
     """
     try:
         import torch.distributed._symmetric_memory as symm_mem
         group = group or dist.group.WORLD
+        flags = symm_mem.empty((world_size,), dtype=torch.int32, device=torch.device("cuda", torch.cuda.current_device()))
+        flag_handle = symm_mem.rendezvous(flags, group=group)
+        flags.zero_()
         tensors, handles = [], []
         for _ in range(P2P_BUFFERS):
             t = symm_mem.empty((world_size, capacity + 1), dtype=torch.int32, device=torch.device("cuda", torch.cuda.current_device()))
@@ -66,7 +71,9 @@ def open_symmetric_blocks(world_size: int, capacity: int, group=None):
             t.zero_()
             tensors.append(t)
             handles.append(h)
-        return tensors, handles
+        torch.cuda.synchronize()
+        dist.barrier(group=group)            # every rank's flags are zero before anyone signals
+        return tensors, handles, flags, flag_handle
     except Exception as e:                  # pragma: no cover - depends on the torch build / topology
         import warnings
         warnings.warn(f"symmetric memory unavailable ({e!r}); sharded cull falls back to NCCL all-gather")
@@ -77,12 +84,13 @@ class ShardedWorld:
     """A lib.World holding one shard plus the merge of the per-shard visible lists.
 
     exchange="nccl": local cull, then one NCCL all-gather of [count | ids] blocks.
-    exchange="p2p":  the gather kernel itself stores this shard's list into every peer's segment buffer over NVLink
-                     (ovis_cull_planes_device_multi). The symmetric-memory barrier that makes a frame readable is
-                     enqueued on a side stream, so the cull stream goes straight on to the next frame; three buffers
-                     rotate and a frame waits for the barrier of two frames ago (long finished) before it stores into a
-                     buffer again, so stores never land in a buffer a peer may still be reading. `ready` is the event
-                     after which the returned blocks are complete.
+    exchange="p2p":  the gather kernel itself stores this shard's list into every peer's segment buffer over NVLink and,
+                     when its last block has finished, writes the frame number into its slot of every rank's flag
+                     array (ovis_cull_planes_device_exchange). No barrier and no collective is launched: a frame is
+                     two kernels, exactly as on one GPU, so consecutive frames keep overlapping. Three segment buffers
+                     rotate; before refilling one, the gather kernel waits until every rank has signalled the frame
+                     two before the current one - which a rank only does after everything it had enqueued on the
+                     frame being overwritten. Readers enqueue `enqueue_ready_wait()` (one tiny kernel) first.
     """
 
     def __init__(self, world, rank: int, world_size: int, id_base: int, n_local: int, group=None,
@@ -106,19 +114,20 @@ class ShardedWorld:
             cap = int(min(n_local, p2p_capacity or max(1024, n_local // 8)))
             opened = open_symmetric_blocks(world_size, cap, group)
             if opened is not None:
-                self.sym_tensors, self.sym_handles = opened
+                self.sym_tensors, self.sym_handles, self.sym_flags, self.flag_handle = opened
                 self.exchange_mode = "p2p"
                 self.capacity = cap
                 seg = (cap + 1) * 4
                 # destination 0 is this rank's own copy; the rest are the peers' copies of segment `rank`
                 order = [rank] + [p for p in range(world_size) if p != rank]
-                self.side = torch.cuda.Stream()
-                self.ready_events = [None] * P2P_BUFFERS
                 self.p2p_out, self.p2p_cnt = [], []
                 for h in self.sym_handles:
                     ptrs = [int(h.buffer_ptrs[p]) + rank * seg for p in order]
                     self.p2p_cnt.append(ptrs)
                     self.p2p_out.append([q + 4 for q in ptrs])
+                self.flag_local = int(self.flag_handle.buffer_ptrs[rank])
+                self.flag_signal = [int(self.flag_handle.buffer_ptrs[p]) + rank * 4 for p in order]
+                self.plans = [world.exchange_plan(self.p2p_out[k], self.p2p_cnt[k], self.flag_signal) for k in range(P2P_BUFFERS)]
 
     def resize(self, capacity: int):
         self.capacity = int(min(max(capacity, 1), self.n_local))
@@ -135,28 +144,20 @@ class ShardedWorld:
     def cull_device(self, planes, require: int = 0) -> torch.Tensor:
         """Enqueue one frame's cull + exchange; returns the (size, capacity + 1) blocks tensor (valid in stream order)."""
         if self.exchange_mode == "p2p":
-            k = self.frame % P2P_BUFFERS
             self.frame += 1
-            # peers have finished reading buffer k (frame - 3) once the barrier of frame - 2 has passed
-            old = self.ready_events[(k + 1) % P2P_BUFFERS]
-            if old is not None:
-                self.stream.wait_event(old)
-            self.world.cull_planes_device_multi(planes, self.p2p_out[k], self.p2p_cnt[k], self.capacity, require)
-            stored = torch.cuda.Event()
-            stored.record(self.stream)
-            self.side.wait_event(stored)
-            with torch.cuda.stream(self.side):
-                self.sym_handles[k].barrier(channel=0)
-                ready = torch.cuda.Event()
-                ready.record(self.side)
-            self.ready_events[k] = ready
-            self.ready = ready
+            f = self.frame                                       # frames are numbered from 1
+            k = f % P2P_BUFFERS
+            planes = np.ascontiguousarray(planes, dtype=np.float32).reshape(24)
+            self.world.cull_exchange_planned(planes, self.plans[k], self.capacity, self.flag_local, self.size,
+                                             max(f - 2, 0), f, require)
             return self.sym_tensors[k]
         self.cull_local(planes, require)
-        blocks = self.exchange()
-        self.ready = torch.cuda.Event()
-        self.ready.record(self.stream)
-        return blocks
+        return self.exchange()
+
+    def enqueue_ready_wait(self):
+        """Make the stream wait until the latest frame's segments from every rank are complete in local memory."""
+        if self.exchange_mode == "p2p":
+            self.world.wait_flags(self.flag_local, self.size, self.frame)
 
     def cull_to_host(self, planes, require: int = 0):
         """One frame end to end: cull + exchange, then the merged list in pinned host memory with ONE strided copy
@@ -166,8 +167,8 @@ class ShardedWorld:
         spec = int(min(self.capacity, self._last_max + self._last_max // 4 + 256))
         if self._pinned is None or self._pinned.shape[1] < self.capacity + 1:
             self._pinned = torch.empty((self.size, self.capacity + 1), dtype=torch.int32).pin_memory()
+        self.enqueue_ready_wait()
         with torch.cuda.stream(self.stream):
-            self.stream.wait_event(self.ready)
             self._pinned[:, :spec + 1].copy_(blocks[:, :spec + 1], non_blocking=True)
         self.stream.synchronize()
         host = self._pinned.numpy()
@@ -187,15 +188,17 @@ class ShardedWorld:
 
     def wait_all(self):
         """Block the host until every enqueued frame (cull stream and barrier stream) has finished."""
+        self.enqueue_ready_wait()
         self.stream.synchronize()
-        if self.exchange_mode == "p2p":
-            self.side.synchronize()
 
     def cull(self, planes, require: int = 0):
         """Synchronous cull; returns (blocks on device, per-rank counts on host). Redone if a shard overflowed."""
         while True:
             blocks = self.cull_device(planes, require)
-            self.ready.synchronize()
+            self.enqueue_ready_wait()
+            self.stream.synchronize()
+            if self.exchange_mode == "p2p" and self.world.exchange_error():
+                raise RuntimeError("sharded exchange timed out waiting for a peer's ready flag")
             counts = segment_counts(blocks)
             if counts.max(initial=0) <= self.capacity:
                 return blocks, counts
