@@ -260,6 +260,60 @@ int ovis_build_shadow_lists(OvisWorld *world, const OvisView *main_view, int32_t
 int ovis_get_world_aabbs(OvisWorld *world, uint32_t first_entity, int64_t n, float *out_aabb);
 int ovis_get_node_world_trs(OvisWorld *world, uint32_t first_node, int64_t n, float *out_trs);
 
+/* ------------------------------------------------------------------------------------------------
+ * Consumers of the visible lists. The reference runs these on
+ * the CPU right after culling and hands the results to GL/Vulkan; here the lists and the uniform
+ * block stay in headless device buffers (graphics API: unavailable on this box).
+ * ---------------------------------------------------------------------------------------------- */
+/* One draw call of a draw list: DrawList::add (render/src/draw_list.cc:35-45) appends, for a given
+ * entity and pass type, one EntityDrawCall per shader pass of that type (passIndex 0, 1, ...). */
+typedef struct OvisDraw {
+    uint32_t entity;      /* entity id (global id for a sharded world) */
+    uint32_t pass_index;  /* index of the shader pass within its pass type */
+} OvisDraw;
+
+/* Shader-pass counts of an entity's material, which the reference looks up per draw through
+ * entity->shader()->numPasses(type) (draw_list.cc:41, deferred_render_pipeline.cc:322-325).
+ * Packed word: numPasses(kDeferred) | numPasses(kBasic) << 8 | numPasses(kShadowCaster) << 16
+ * (each 0..255; a new entity has 0 of everything and is never drawn). */
+#define OVIS_PASS_COUNTS(deferred, basic, shadow_caster) \
+    ((uint32_t)(deferred) | ((uint32_t)(basic) << 8) | ((uint32_t)(shadow_caster) << 16))
+int ovis_entity_set_pass_counts(OvisWorld *world, int64_t n, const uint32_t *ids, const uint32_t *pass_counts);
+
+#define OVIS_DRAWS_MAIN 0   /* prepareEntities: list 0 = deferred-pass draws, list 1 = basic-pass draws */
+#define OVIS_DRAWS_SHADOW 1 /* shadow-caster loop: list 0 = shadow-caster draws of castsShadow() entities */
+/* Expand a visible list into draw lists, in list order, on the world's stream (two small kernels).
+ *   OVIS_DRAWS_MAIN    DeferredRenderPipeline::prepareEntities (render/src/deferred_render_pipeline.cc:
+ *                      318-330): an entity whose shader has deferred passes goes to list 0 with one
+ *                      draw per deferred pass, otherwise one draw per basic pass goes to list 1
+ *                      (no pass of either type: not drawn).
+ *   OVIS_DRAWS_SHADOW  the per-shadow-view loop of prepareLights (:272-283): castsShadow() entities
+ *                      get one draw per shadow-caster pass in list 0; list 1 stays empty.
+ * d_visible/d_visible_count: a device list of entity ids and its device count, e.g. what
+ * ovis_cull_planes_device wrote, or one view's slice of ovis_cull_views_device's CSR; max_visible is
+ * an upper bound of the count known to the host (sizes the grids; < 0 = the world's entity count).
+ * Both NULL = the entity list of this world's last ovis_cull / ovis_cull_planes.
+ * Draws beyond a list's capacity are dropped, but d_draw_counts[0..1] (device; NULL = an internal
+ * pair, readable through ovis_get_draw_counts) always receive the full draw counts, so a caller can
+ * detect the overflow and retry. Never allocates after the world's arrays exist. */
+int ovis_build_draw_lists_device(OvisWorld *world, const uint32_t *d_visible, const uint32_t *d_visible_count, int64_t max_visible,
+                                 int32_t mode, OvisDraw *d_draws0, int64_t capacity0, OvisDraw *d_draws1, int64_t capacity1,
+                                 uint32_t *d_draw_counts);
+/* Host copy of the internal draw-count pair (synchronises the world's stream). */
+int ovis_get_draw_counts(OvisWorld *world, uint32_t out_counts[2]);
+
+/* EntityUniforms (render/include/render_entity.h:34-37: mat4 transform; vec3 position) of every
+ * entity of a visible list, in list order, 20 floats (80 bytes, the std140 size) per entity:
+ * [0..15] Transform::matrix() column-major, [16..18] position, [19] zero padding - what
+ * RenderEntity::setTransform (render/src/render_entity.cc:64-72) writes into each entity's uniform
+ * buffer. The reference rewrites the uniforms of every entity that moved; packing only the visible
+ * ones from the world TRS already resident on the device keeps the traffic proportional to what is
+ * drawn. Entities that were never given a transform get the identity (Transform's default).
+ * d_uniforms must be 16-byte aligned with room for `capacity` entries; entries beyond it are dropped.
+ * Pending transform updates are flushed first. List arguments as for ovis_build_draw_lists_device. */
+int ovis_pack_entity_uniforms_device(OvisWorld *world, const uint32_t *d_visible, const uint32_t *d_visible_count, int64_t max_visible,
+                                     float *d_uniforms, int64_t capacity);
+
 /* Copy `bytes` from a device pointer this library handed out (e.g. the CSR arrays of
  * ovis_cull_views_device) to host memory, after all work queued on the world's stream; for ABI users
  * that bind no CUDA runtime of their own (cgo, ctypes). No counterpart in the reference (its results are

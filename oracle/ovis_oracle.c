@@ -578,3 +578,39 @@ int32_t orc_shadow_lists(int64_t n, const float *aabb, const uint32_t *flags,
     free(visible); free(scratch);
     return lists;
 }
+
+/* ------------------------------------------------------------------ draw lists and uniforms (section 8(f)) */
+
+/* render/src/deferred_render_pipeline.cc:318-330 and :272-283 with render/src/draw_list.cc:35-45 */
+void orc_draw_lists(int64_t n_visible, const uint32_t *visible, const uint32_t *pass_counts, const uint32_t *flags,
+                    int32_t mode, uint32_t *out_draws0, uint32_t *out_draws1, int64_t out_counts[2]) {
+    int64_t c0 = 0, c1 = 0;
+    for (int64_t k = 0; k < n_visible; k++) {
+        uint32_t e = visible[k];
+        uint32_t pc = pass_counts[e];
+        uint32_t deferred = pc & 0xffu, basic = (pc >> 8) & 0xffu, caster = (pc >> 16) & 0xffu;
+        if (mode == 0) {
+            if (deferred > 0) {                                             /* :322-323 */
+                for (uint32_t i = 0; i < deferred; i++) { out_draws0[2 * c0] = e; out_draws0[2 * c0 + 1] = i; c0++; }
+            } else if (basic > 0) {                                         /* :324-325 */
+                for (uint32_t i = 0; i < basic; i++) { out_draws1[2 * c1] = e; out_draws1[2 * c1 + 1] = i; c1++; }
+            }                                                               /* else: logWarning, nothing drawn */
+        } else {
+            if ((flags[e] & ORC_CASTS_SHADOW) && caster > 0)                /* :273-277 */
+                for (uint32_t i = 0; i < caster; i++) { out_draws0[2 * c0] = e; out_draws0[2 * c0 + 1] = i; c0++; }
+        }
+    }
+    out_counts[0] = c0;
+    out_counts[1] = c1;
+}
+
+/* render/src/render_entity.cc:67-69 */
+void orc_entity_uniforms(int64_t n, const float *world_trs, float *out20) {
+    for (int64_t i = 0; i < n; i++) {
+        const float *l = world_trs + 10 * i;
+        m4 M = transform_matrix(V3(l[0], l[1], l[2]), Q(l[3], l[4], l[5], l[6]), V3(l[7], l[8], l[9]));
+        memcpy(out20 + 20 * i, &M, 64);
+        out20[20 * i + 16] = l[0]; out20[20 * i + 17] = l[1]; out20[20 * i + 18] = l[2];
+        out20[20 * i + 19] = 0.0f;
+    }
+}

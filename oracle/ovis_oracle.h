@@ -93,6 +93,20 @@ int32_t orc_shadow_lists(int64_t n, const float *aabb, const uint32_t *flags,
                          int32_t cap_lists, int32_t *out_list_light, int32_t *out_list_view,
                          int64_t *out_offsets, int64_t cap_entities, uint32_t *out_entities);
 
+/* ---- draw lists ----
+ * pass_counts[i] packs Shader::numPasses of entity i's material: bits 0-7 deferred, 8-15 basic, 16-23 shadow caster.
+ * mode 0 = DeferredRenderPipeline::prepareEntities (deferred_render_pipeline.cc:318-330): for each visible entity in
+ *          order, numPasses(deferred) draws into list 0, else numPasses(basic) draws into list 1 (DrawList::add,
+ *          draw_list.cc:35-45: one draw per pass, pass index ascending);
+ * mode 1 = the shadow-caster loop of prepareLights (:272-283): castsShadow() entities get numPasses(shadow caster)
+ *          draws into list 0.
+ * A draw is (entity id, pass index). out_draws0/1 hold 2 uint32 per draw; returns counts through out_counts[2]. */
+void orc_draw_lists(int64_t n_visible, const uint32_t *visible, const uint32_t *pass_counts, const uint32_t *flags,
+                    int32_t mode, uint32_t *out_draws0, uint32_t *out_draws1, int64_t out_counts[2]);
+/* ---- per-entity uniforms (section 8(f) row 2): EntityUniforms{mat4 transform; vec3 position} (render_entity.h:34-37),
+ * filled as RenderEntity::setTransform does (render_entity.cc:67-69). 20 floats per entity (std140: 80 bytes). */
+void orc_entity_uniforms(int64_t n, const float *world_trs, float *out20);
+
 const char *orc_name(void);   /* "port" or "reference" */
 
 #ifdef __cplusplus

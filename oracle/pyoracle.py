@@ -191,6 +191,26 @@ class Oracle:
         assert k >= 0
         return ll[:k].copy(), lv[:k].copy(), off[:k + 1].copy(), ent[:off[k]].copy()
 
+    # ---- draw lists / uniforms (section 8(f))
+    def draw_lists(self, visible, pass_counts, flags, mode=0):
+        visible = np.ascontiguousarray(visible, dtype=np.uint32)
+        pass_counts = np.ascontiguousarray(pass_counts, dtype=np.uint32)
+        flags = np.ascontiguousarray(flags, dtype=np.uint32)
+        pc = pass_counts[visible] if len(visible) else np.zeros(0, np.uint32)
+        cap = int(((pc & 0xff) + ((pc >> 8) & 0xff) + ((pc >> 16) & 0xff)).sum(dtype=np.int64)) + 1
+        d0 = np.zeros((cap, 2), dtype=np.uint32)
+        d1 = np.zeros((cap, 2), dtype=np.uint32)
+        counts = np.zeros(2, dtype=np.int64)
+        self.lib.orc_draw_lists(C.c_int64(len(visible)), _p(visible), _p(pass_counts), _p(flags), C.c_int32(mode),
+                                _p(d0), _p(d1), _p(counts))
+        return d0[:counts[0]].copy(), d1[:counts[1]].copy()
+
+    def entity_uniforms(self, world_trs) -> np.ndarray:
+        world_trs = _f32(world_trs, (-1, 10))
+        out = np.zeros((len(world_trs), 20), dtype=np.float32)
+        self.lib.orc_entity_uniforms(C.c_int64(len(world_trs)), _p(world_trs), _p(out))
+        return out
+
     # ---- tier A object world (reference build only)
     def world(self) -> "RefWorld":
         assert self.has_world, "object world exists only in the reference-compiled oracle"

@@ -459,4 +459,42 @@ int32_t orc_shadow_lists(int64_t n, const float *aabb, const uint32_t *flags,
     return lists;
 }
 
+/* RESTATED loops of prepareEntities (deferred_render_pipeline.cc:318-330) / the caster loop of prepareLights (:272-283)
+ * with DrawList::add (draw_list.cc:35-45); Shader/Material need the asset system and are replaced by their pass counts. */
+void orc_draw_lists(int64_t n_visible, const uint32_t *visible, const uint32_t *pass_counts, const uint32_t *flags,
+                    int32_t mode, uint32_t *out_draws0, uint32_t *out_draws1, int64_t out_counts[2]) {
+    std::vector<std::pair<uint32_t, uint32_t>> lists[2];
+    auto add = [&](int list, uint32_t entity, uint32_t numPasses) {
+        for (uint32_t i = 0; i < numPasses; i++)
+            lists[list].emplace_back(entity, i);
+    };
+    for (int64_t k = 0; k < n_visible; k++) {
+        uint32_t e = visible[k], pc = pass_counts[e];
+        if (mode == 0) {
+            if ((pc & 0xffu) > 0) add(0, e, pc & 0xffu);
+            else if (((pc >> 8) & 0xffu) > 0) add(1, e, (pc >> 8) & 0xffu);
+        } else if ((flags[e] & RenderEntity::kCastsShadow) && ((pc >> 16) & 0xffu) > 0) {
+            add(0, e, (pc >> 16) & 0xffu);
+        }
+    }
+    uint32_t *outs[2] = { out_draws0, out_draws1 };
+    for (int l = 0; l < 2; l++) {
+        out_counts[l] = (int64_t)lists[l].size();
+        for (size_t i = 0; i < lists[l].size(); i++) {
+            outs[l][2 * i] = lists[l][i].first;
+            outs[l][2 * i + 1] = lists[l][i].second;
+        }
+    }
+}
+
+/* EntityUniforms as RenderEntity::setTransform fills them (render_entity.cc:67-69), via the reference's Transform. */
+void orc_entity_uniforms(int64_t n, const float *world_trs, float *out20) {
+    for (int64_t i = 0; i < n; i++) {
+        Transform tr = trs(world_trs + 10 * i);
+        memcpy(out20 + 20 * i, &tr.matrix(), 64);
+        memcpy(out20 + 20 * i + 16, &tr.position(), 12);
+        out20[20 * i + 19] = 0.0f;
+    }
+}
+
 } /* extern "C" */

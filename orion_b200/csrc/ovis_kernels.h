@@ -113,6 +113,34 @@ int multi_max_blocks_per_sm(int n_views, int n_groups);
 void launch_multi_pass(const MultiArgs &a, bool write, int grid, cudaStream_t s);
 void launch_multi_scans(const MultiArgs &a, long long *csr_offsets_of_pass, cudaStream_t s);
 
+// ---- consumers of the visible lists (section 8(f)) -----------------------------------------------------------------
+struct DrawArgs {
+    const uint32_t *d_visible;       // ids (slot + id_base), list order
+    const uint32_t *d_visible_count; // device count
+    uint32_t id_base;
+    const uint32_t *pass_counts;     // per slot: numPasses deferred | basic << 8 | shadow caster << 16
+    const uint32_t *caster_mask;     // alive & castsShadow bits (mode 1)
+    int mode;                        // 0 = prepareEntities (two lists), 1 = shadow-caster list
+    uint32_t *tile_totals;           // scratch: 2 per 1024-entry tile
+    uint2 *d_draws0, *d_draws1;      // (entity id, pass index)
+    long long cap0, cap1;
+    uint32_t *d_draw_counts;         // [2]
+};
+
+struct UniformArgs {
+    const uint32_t *d_visible;
+    const uint32_t *d_visible_count;
+    uint32_t id_base;
+    const uint32_t *entity_node;     // per slot: node the entity follows, or kNone
+    const float *world_trs;          // 10 x nstride
+    int64_t nstride;
+    float *d_out;                    // 20 floats per visible entity
+    int64_t capacity;                // entries d_out can hold
+};
+
+void launch_draw_lists(const DrawArgs &a, int64_t max_visible, cudaStream_t s);
+void launch_entity_uniforms(const UniformArgs &a, int64_t max_visible, cudaStream_t s);
+
 enum : uint32_t { kLightNever = 0, kLightAlways = 1, kLightSphere = 2, kLightBox = 3 };
 
 struct DeviceLight {

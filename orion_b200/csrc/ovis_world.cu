@@ -80,6 +80,10 @@ struct OvisWorld {
     uint32_t *d_caster_bits = nullptr;    // alive & castsShadow
     std::vector<uint32_t> h_alive, h_caster_raw;   // host mirrors of the bit masks (caster before masking by alive)
     std::vector<uint32_t> h_entity_node;  // node the entity follows, or kNone
+    uint32_t *d_entity_node = nullptr;    // device copy (entity uniforms)
+    uint32_t *d_pass_counts = nullptr;    // per slot: shader passes deferred | basic << 8 | shadow caster << 16
+    uint32_t *d_draw_totals = nullptr;    // draw-list scratch: 2 per 1024 visible entries
+    uint32_t *d_draw_counts = nullptr;    // [2] draws written by the last ovis_build_draw_lists_device
     bool masks_dirty = false;
     bool any_dead = false;
 
@@ -224,6 +228,12 @@ int reserve_entities(OvisWorld *w, int64_t want) {
     OVIS_TRY(grow_soa(w->d_world, 6, w->cap_ent, cap, w->n_ent, w->stream));
     OVIS_TRY(grow(w->d_alive_bits, w->cap_ent / 32, cap / 32, w->stream));
     OVIS_TRY(grow(w->d_caster_bits, w->cap_ent / 32, cap / 32, w->stream));
+    OVIS_TRY(grow(w->d_pass_counts, w->n_ent, cap, w->stream));
+    OVIS_TRY(grow(w->d_entity_node, w->n_ent, cap, w->stream, false));
+    OVIS_CUDA(cudaMemsetAsync(w->d_entity_node + w->n_ent, 0xff, sizeof(uint32_t) * (size_t)(cap - w->n_ent), w->stream));
+    OVIS_TRY(grow(w->d_draw_totals, 0, 2 * (cap / 1024 + 1), w->stream, false));
+    if (!w->d_draw_counts)
+        OVIS_TRY(grow(w->d_draw_counts, 0, 2, w->stream));
     OVIS_TRY(grow(w->d_result, 0, cap, w->stream, false));
     OVIS_TRY(grow(w->d_staging, 0, 2 * cap, w->stream, false));
     OVIS_TRY(grow(w->d_tile_counts, 0, 2 * (cap / 128), w->stream, false));
@@ -439,6 +449,15 @@ int bind_entities(OvisWorld *w, int64_t n, const uint32_t *nodes, const uint32_t
         ovis::launch_scatter_u32((const uint32_t *)de, (const uint32_t *)dn, (int64_t)c, w->d_node_entity, w->stream);
         w->launches++;
         OVIS_CUDA(cudaStreamSynchronize(w->stream));   // vectors are locals
+    }
+    for (int64_t s = 0; s < n; s += kUploadChunk) {              // every entity, first on its node or not
+        int64_t c = std::min(kUploadChunk, n - s);
+        void *dn = nullptr, *de = nullptr;
+        OVIS_TRY(stage(w, 0, nodes + s, 4 * (size_t)c, &dn));
+        OVIS_TRY(stage(w, 1, entities + s, 4 * (size_t)c, &de));
+        ovis::launch_scatter_u32((const uint32_t *)dn, (const uint32_t *)de, c, w->d_entity_node, w->stream);
+        w->launches++;
+        OVIS_CUDA(cudaStreamSynchronize(w->stream));   // the staging buffers are reused by the next chunk
     }
     w->transforms_dirty = true;
     w->all_dirty = true;
@@ -885,7 +904,8 @@ int ovis_world_destroy(OvisWorld *w) {
     cudaSetDevice(w->device);
     cudaStreamSynchronize(w->stream);
     void *bufs[] = { w->d_local, w->d_world, w->d_alive_bits, w->d_caster_bits, w->d_parent, w->d_local_trs, w->d_world_trs,
-                     w->d_node_entity, w->d_dirty, w->d_extra_entity, w->d_extra_node, w->d_level_lists, w->d_lights, w->d_light_out,
+                     w->d_node_entity, w->d_dirty, w->d_entity_node, w->d_pass_counts, w->d_draw_totals, w->d_draw_counts,
+                     w->d_extra_entity, w->d_extra_node, w->d_level_lists, w->d_lights, w->d_light_out,
                      w->d_staging, w->d_tile_counts, w->d_block_totals, w->d_exchange, w->d_mv_counts, w->d_mv_totals, w->d_mv_planes,
                      w->d_mv_require, w->d_mv_groups, w->d_mv_hits, w->d_result, w->d_counts, w->d_csr_entities, w->d_csr_offsets,
                      w->d_stage[0], w->d_stage[1] };
@@ -1545,6 +1565,107 @@ int ovis_get_node_world_trs(OvisWorld *w, uint32_t first_node, int64_t n, float 
     OVIS_TRY(use_device(w));
     OVIS_TRY(flush_transforms(w));
     return read_back(w, 10, w->d_world_trs, w->cap_nodes, first_node, n, out_trs);
+}
+
+int ovis_entity_set_pass_counts(OvisWorld *w, int64_t n, const uint32_t *ids, const uint32_t *pass_counts) {
+    if (!w || (n > 0 && !pass_counts))
+        return fail(OVIS_ERR_INVALID, "ovis_entity_set_pass_counts: null input");
+    OVIS_TRY(use_device(w));
+    OVIS_TRY(check_entity_ids(w, n, ids));
+    for (int64_t s = 0; s < n; s += kUploadChunk) {
+        int64_t c = std::min(kUploadChunk, n - s);
+        void *dv = nullptr, *di = nullptr;
+        OVIS_TRY(stage(w, 0, pass_counts + s, 4 * (size_t)c, &dv));
+        OVIS_TRY(stage(w, 1, ids + s, 4 * (size_t)c, &di));
+        ovis::launch_scatter_u32((const uint32_t *)dv, (const uint32_t *)di, c, w->d_pass_counts, w->stream);
+        w->launches++;
+        if (s + kUploadChunk < n)
+            OVIS_CUDA(cudaStreamSynchronize(w->stream));   // the staging buffers are reused by the next chunk
+    }
+    OVIS_CUDA(cudaGetLastError());
+    return OVIS_OK;
+}
+
+int ovis_build_draw_lists_device(OvisWorld *w, const uint32_t *d_visible, const uint32_t *d_visible_count, int64_t max_visible,
+                                 int32_t mode, OvisDraw *d_draws0, int64_t capacity0, OvisDraw *d_draws1, int64_t capacity1,
+                                 uint32_t *d_draw_counts) {
+    if (!w || (mode != OVIS_DRAWS_MAIN && mode != OVIS_DRAWS_SHADOW) || capacity0 < 0 || capacity1 < 0 ||
+        (capacity0 > 0 && !d_draws0) || (capacity1 > 0 && !d_draws1))
+        return fail(OVIS_ERR_INVALID, "ovis_build_draw_lists_device: bad arguments");
+    if ((d_visible == nullptr) != (d_visible_count == nullptr))
+        return fail(OVIS_ERR_INVALID, "ovis_build_draw_lists_device: pass both the list and its count, or neither");
+    OVIS_TRY(use_device(w));
+    if (w->n_ent == 0)
+        OVIS_TRY(reserve_entities(w, 1));                       // the count words exist even for an empty world
+    if (!d_visible) {                                           // the entity list of the last ovis_cull*
+        d_visible = w->d_result;
+        d_visible_count = w->d_counts;
+        max_visible = w->n_ent;
+    }
+    if (max_visible < 0 || max_visible > w->n_ent)
+        max_visible = w->n_ent;                                 // a list of distinct entities is no longer than the world
+    OVIS_TRY(upload_masks(w));
+    ovis::DrawArgs a{};
+    a.d_visible = d_visible;
+    a.d_visible_count = d_visible_count;
+    a.id_base = w->id_base;
+    a.pass_counts = w->d_pass_counts;
+    a.caster_mask = w->d_caster_bits;
+    a.mode = mode;
+    a.tile_totals = w->d_draw_totals;
+    a.d_draws0 = reinterpret_cast<uint2 *>(d_draws0);
+    a.d_draws1 = reinterpret_cast<uint2 *>(d_draws1);
+    a.cap0 = capacity0;
+    a.cap1 = capacity1;
+    a.d_draw_counts = d_draw_counts ? d_draw_counts : w->d_draw_counts;
+    ovis::launch_draw_lists(a, max_visible, w->stream);
+    w->launches += 2;
+    OVIS_CUDA(cudaGetLastError());
+    return OVIS_OK;
+}
+
+int ovis_get_draw_counts(OvisWorld *w, uint32_t out_counts[2]) {
+    if (!w || !out_counts)
+        return fail(OVIS_ERR_INVALID, "ovis_get_draw_counts: null argument");
+    OVIS_TRY(use_device(w));
+    out_counts[0] = out_counts[1] = 0;
+    if (!w->d_draw_counts)
+        return OVIS_OK;
+    OVIS_CUDA(cudaMemcpyAsync(out_counts, w->d_draw_counts, 8, cudaMemcpyDeviceToHost, w->stream));
+    OVIS_CUDA(cudaStreamSynchronize(w->stream));
+    return OVIS_OK;
+}
+
+int ovis_pack_entity_uniforms_device(OvisWorld *w, const uint32_t *d_visible, const uint32_t *d_visible_count, int64_t max_visible,
+                                     float *d_uniforms, int64_t capacity) {
+    if (!w || capacity < 0 || (capacity > 0 && !d_uniforms) || ((uintptr_t)d_uniforms & 15u))
+        return fail(OVIS_ERR_INVALID, "ovis_pack_entity_uniforms_device: bad arguments (the output must be 16-byte aligned)");
+    if ((d_visible == nullptr) != (d_visible_count == nullptr))
+        return fail(OVIS_ERR_INVALID, "ovis_pack_entity_uniforms_device: pass both the list and its count, or neither");
+    OVIS_TRY(use_device(w));
+    if (w->n_ent == 0)
+        OVIS_TRY(reserve_entities(w, 1));
+    if (!d_visible) {
+        d_visible = w->d_result;
+        d_visible_count = w->d_counts;
+        max_visible = w->n_ent;
+    }
+    if (max_visible < 0 || max_visible > w->n_ent)
+        max_visible = w->n_ent;
+    OVIS_TRY(flush_transforms(w));
+    ovis::UniformArgs a{};
+    a.d_visible = d_visible;
+    a.d_visible_count = d_visible_count;
+    a.id_base = w->id_base;
+    a.entity_node = w->d_entity_node;
+    a.world_trs = w->d_world_trs;
+    a.nstride = w->cap_nodes;
+    a.d_out = d_uniforms;
+    a.capacity = capacity;
+    ovis::launch_entity_uniforms(a, std::min(max_visible, capacity), w->stream);
+    w->launches += std::min(max_visible, capacity) > 0 ? 1 : 0;
+    OVIS_CUDA(cudaGetLastError());
+    return OVIS_OK;
 }
 
 int ovis_read_device(OvisWorld *w, const void *d_src, int64_t bytes, void *host_dst) {

@@ -22,6 +22,7 @@ HEADER = os.path.join(ROOT, "include", "orion_vis.h")
 OVIS_OK, OVIS_ERR_INVALID, OVIS_ERR_CUDA, OVIS_ERR_CAPACITY, OVIS_ERR_NOMEM = 0, 1, 2, 3, 4
 CASTS_SHADOW = 1
 CULL_LIGHTS = 1
+DRAWS_MAIN, DRAWS_SHADOW = 0, 1
 NO_PARENT = -1
 
 LIGHT_DTYPE = scenes.LIGHT_DTYPE
@@ -388,6 +389,34 @@ class World:
             _check(rc)
             k = nl.value
             return ll[:k].copy(), lv[:k].copy(), off[:k + 1].copy(), ent[:ne.value].copy()
+
+    # ---- consumers of the visible lists
+    def set_pass_counts(self, ids, deferred, basic, shadow_caster):
+        """Shader-pass counts of the entities' materials (numPasses per pass type, each 0..255)."""
+        ids = _u32(ids)
+        packed = (_u32(deferred) & 0xff) | ((_u32(basic) & 0xff) << 8) | ((_u32(shadow_caster) & 0xff) << 16)
+        packed = np.ascontiguousarray(np.broadcast_to(packed, ids.shape), dtype=np.uint32)
+        _check(self.lib.ovis_entity_set_pass_counts(self.h, C.c_int64(len(ids)), _p(ids), _p(packed)))
+
+    def build_draw_lists_device(self, mode, d_draws0: int, cap0: int, d_draws1: int = 0, cap1: int = 0, d_visible: int = 0,
+                                d_visible_count: int = 0, max_visible: int = -1, d_draw_counts: int = 0):
+        """Asynchronous. Pointers are raw device addresses; d_visible = 0 uses the last cull's entity list."""
+        _check(self.lib.ovis_build_draw_lists_device(self.h, C.c_void_p(d_visible or None), C.c_void_p(d_visible_count or None),
+                                                     C.c_int64(max_visible), C.c_int32(mode), C.c_void_p(d_draws0 or None),
+                                                     C.c_int64(cap0), C.c_void_p(d_draws1 or None), C.c_int64(cap1),
+                                                     C.c_void_p(d_draw_counts or None)))
+
+    def draw_counts(self):
+        out = np.zeros(2, dtype=np.uint32)
+        _check(self.lib.ovis_get_draw_counts(self.h, _p(out)))
+        return int(out[0]), int(out[1])
+
+    def pack_entity_uniforms_device(self, d_uniforms: int, capacity: int, d_visible: int = 0, d_visible_count: int = 0,
+                                    max_visible: int = -1):
+        """Asynchronous. 20 floats per visible entity into d_uniforms (16-byte aligned device address)."""
+        _check(self.lib.ovis_pack_entity_uniforms_device(self.h, C.c_void_p(d_visible or None),
+                                                         C.c_void_p(d_visible_count or None), C.c_int64(max_visible),
+                                                         C.c_void_p(d_uniforms or None), C.c_int64(capacity)))
 
     # ---- read-back
     def read_device(self, d_ptr: int, count: int, dtype=np.uint32) -> np.ndarray:

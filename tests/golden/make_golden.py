@@ -82,6 +82,18 @@ def main():
     for k, x in zip(("ll", "lv", "off", "ent"), w.shadow_lists(s["view"])):
         g[f"cubes_lists_{k}"] = x
     w.close()
+    # consumers of the visible lists (section 8(f) rows 1-2): draw-list expansion and EntityUniforms packing
+    rng2 = np.random.default_rng(2027)                     # own stream: the arrays above keep their values
+    nb = len(cb)
+    deferred = np.where(rng2.random(nb) < 0.6, rng2.integers(1, 4, nb), 0)
+    basic = np.where(rng2.random(nb) < 0.8, rng2.integers(1, 3, nb), 0)
+    shadow = np.where(rng2.random(nb) < 0.7, rng2.integers(1, 3, nb), 0)
+    pc = (deferred | (basic << 8) | (shadow << 16)).astype(np.uint32)
+    g["draw_pass_counts"] = pc
+    for i in range(2):
+        g[f"draws_deferred_{i}"], g[f"draws_basic_{i}"] = ref.draw_lists(g[f"cull_all_{i}"], pc, cf, 0)
+        g[f"draws_shadow_{i}"], _ = ref.draw_lists(g[f"cull_all_{i}"], pc, cf, 1)
+    g["entity_uniforms"] = ref.entity_uniforms(g["world_trs"])
     out = os.path.join(HERE, "visibility_golden.npz")
     np.savez_compressed(out, **g)
     print(out, os.path.getsize(out), "bytes,", len(g), "arrays")

@@ -7,6 +7,7 @@ import numpy as np
 import pytest
 
 from orion_b200 import lib, scenes
+import vis_testutil as util
 from vis_testutil import same
 
 G = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "visibility_golden.npz"))
@@ -55,6 +56,15 @@ def test_port_culls_lights_and_lists(port):
         assert np.array_equal(x, y)
 
 
+def test_port_draw_lists_and_uniforms(port):
+    for i in range(2):
+        d0, d1 = port.draw_lists(G[f"cull_all_{i}"], G["draw_pass_counts"], G["cull_flags"], 0)
+        assert np.array_equal(d0, G[f"draws_deferred_{i}"]) and np.array_equal(d1, G[f"draws_basic_{i}"])
+        s0, s1 = port.draw_lists(G[f"cull_all_{i}"], G["draw_pass_counts"], G["cull_flags"], 1)
+        assert np.array_equal(s0, G[f"draws_shadow_{i}"]) and len(s1) == 0
+    assert same(port.entity_uniforms(G["world_trs"]), G["entity_uniforms"])
+
+
 def test_library_host_math_against_golden():
     for i, v in enumerate(G["views"]):
         assert same(lib.view_planes(v), G["view_planes"][i])
@@ -78,6 +88,7 @@ def test_cuda_path_against_golden():
     w.bind_entities(np.arange(n0, n0 + n), np.arange(e0, e0 + n))
     assert same(w.node_world_trs(), G["world_trs"])
     assert same(w.world_aabbs(), G["world_aabb"])
+    assert same(util.gpu_entity_uniforms(w, np.arange(n, dtype=np.uint32)), G["entity_uniforms"])
     w.close()
     w = lib.World(0)
     f = w.add_entities(G["cull_boxes"], G["cull_flags"])
@@ -87,6 +98,14 @@ def test_cuda_path_against_golden():
         ents, ls = w.cull(v)
         assert np.array_equal(ents, G[f"cull_all_{i}"]) and np.array_equal(ls, G[f"light_cull_{i}"])
         assert np.array_equal(w.cull_planes(lib.view_planes(v), require=1), G[f"cull_casters_{i}"])
+    w.set_pass_counts(np.arange(len(G["cull_boxes"])), G["draw_pass_counts"] & 0xff, (G["draw_pass_counts"] >> 8) & 0xff,
+                      G["draw_pass_counts"] >> 16)
+    for i in range(2):
+        w.cull(G["cull_views"][i])                               # draw lists straight from the cull's device result
+        d0, d1, _ = util.gpu_draw_lists(w, lib.DRAWS_MAIN)
+        assert np.array_equal(d0, G[f"draws_deferred_{i}"]) and np.array_equal(d1, G[f"draws_basic_{i}"])
+        s0, s1, _ = util.gpu_draw_lists(w, lib.DRAWS_SHADOW)
+        assert np.array_equal(s0, G[f"draws_shadow_{i}"]) and len(s1) == 0
     for x, y in zip(w.shadow_lists(G["lists_view"][0]), _lists("lists")):
         assert np.array_equal(x, y)
     w.close()

@@ -146,3 +146,24 @@ def test_cubes_scene_twenty_views(port, ref):
     for x, y in zip((ll, lv, off, ent), exp):
         assert np.array_equal(x, y)
     w.close()
+
+
+def test_draw_lists_and_entity_uniforms(port, ref):
+    """Section 8(f) rows 1-2: draw-list expansion (prepareEntities / shadow-caster loop through the reference's own
+    DrawList::add control flow) and EntityUniforms packing (Transform::matrix())."""
+    rng = np.random.default_rng(29)
+    n = 5000
+    pc = util.random_pass_counts(rng, n)
+    flags = rng.integers(0, 2, n).astype(np.uint32)
+    for m in (0, 1, 7, 2500, n):
+        visible = np.sort(rng.choice(n, m, replace=False)).astype(np.uint32)
+        for mode in (0, 1):
+            p0, p1 = port.draw_lists(visible, pc, flags, mode)
+            r0, r1 = ref.draw_lists(visible, pc, flags, mode)
+            assert np.array_equal(p0, r0) and np.array_equal(p1, r1)
+            if mode == 1:
+                assert len(p1) == 0
+    trs = util.random_trs(rng, 4000)
+    trs[:5, 7:10] = 0.0                                                     # degenerate scale
+    trs[5, 3:7] = (1, 0, 0, 0)
+    assert same(port.entity_uniforms(trs), ref.entity_uniforms(trs))

@@ -70,3 +70,52 @@ def random_lights(rng, n, extent=100.0):
     l["range"] = rng.uniform(1, 80, n)
     l["cutoff"] = rng.uniform(1, 45, n)
     return l
+
+
+def random_pass_counts(rng, n):
+    """Packed shader-pass counts (deferred | basic << 8 | shadow caster << 16); some entities have no pass of a type."""
+    deferred = np.where(rng.random(n) < 0.6, rng.integers(1, 4, n), 0)
+    basic = np.where(rng.random(n) < 0.8, rng.integers(1, 3, n), 0)
+    shadow = np.where(rng.random(n) < 0.7, rng.integers(1, 3, n), 0)
+    return (deferred | (basic << 8) | (shadow << 16)).astype(np.uint32)
+
+
+def gpu_draw_lists(world, mode, visible=None, cap=None):
+    """Run ovis_build_draw_lists_device on a host list (or, with visible=None, on the world's last cull result);
+    returns (draws0, draws1, (count0, count1)) with the lists cut to min(count, cap)."""
+    import torch
+    n_slots = world.counts()[0]
+    cap = cap if cap is not None else 8 * max(n_slots, 1)
+    d0 = torch.zeros((cap + 1, 2), dtype=torch.int32, device="cuda")
+    d1 = torch.zeros((cap + 1, 2), dtype=torch.int32, device="cuda")
+    cnt = torch.full((2,), -1, dtype=torch.int32, device="cuda")
+    if visible is None:
+        world.build_draw_lists_device(mode, d0.data_ptr(), cap, d1.data_ptr(), cap, d_draw_counts=cnt.data_ptr())
+    else:
+        vis = torch.from_numpy(np.ascontiguousarray(visible, dtype=np.uint32).view(np.int32)).cuda()
+        vcnt = torch.tensor([len(visible)], dtype=torch.int32, device="cuda")
+        world.build_draw_lists_device(mode, d0.data_ptr(), cap, d1.data_ptr(), cap, vis.data_ptr() if len(visible) else d0.data_ptr(),
+                                      vcnt.data_ptr(), len(visible), cnt.data_ptr())
+    torch.cuda.synchronize()
+    c = cnt.cpu().numpy()
+    assert not d0[cap].any() and not d1[cap].any()           # nothing written past the capacity
+    return (d0[:min(int(c[0]), cap)].cpu().numpy().view(np.uint32), d1[:min(int(c[1]), cap)].cpu().numpy().view(np.uint32),
+            (int(c[0]), int(c[1])))
+
+
+def gpu_entity_uniforms(world, visible=None, cap=None):
+    import torch
+    n_slots = world.counts()[0]
+    m = n_slots if visible is None else len(visible)
+    cap = cap if cap is not None else max(m, 1)
+    out = torch.full((cap + 1, 20), -7.0, dtype=torch.float32, device="cuda")
+    if visible is None:
+        world.pack_entity_uniforms_device(out.data_ptr(), cap)
+    else:
+        vis = torch.from_numpy(np.ascontiguousarray(visible, dtype=np.uint32).view(np.int32)).cuda()
+        vcnt = torch.tensor([len(visible)], dtype=torch.int32, device="cuda")
+        world.pack_entity_uniforms_device(out.data_ptr(), cap, vis.data_ptr() if len(visible) else out.data_ptr(), vcnt.data_ptr(),
+                                          len(visible))
+    torch.cuda.synchronize()
+    assert bool((out[cap] == -7.0).all())
+    return out[:cap].cpu().numpy()
