@@ -282,7 +282,7 @@ int ovis_entity_set_pass_counts(OvisWorld *world, int64_t n, const uint32_t *ids
 
 #define OVIS_DRAWS_MAIN 0   /* prepareEntities: list 0 = deferred-pass draws, list 1 = basic-pass draws */
 #define OVIS_DRAWS_SHADOW 1 /* shadow-caster loop: list 0 = shadow-caster draws of castsShadow() entities */
-/* Expand a visible list into draw lists, in list order, on the world's stream (two small kernels).
+/* Expand a visible list into draw lists, in list order, on the world's stream (one or two small kernels).
  *   OVIS_DRAWS_MAIN    DeferredRenderPipeline::prepareEntities (render/src/deferred_render_pipeline.cc:
  *                      318-330): an entity whose shader has deferred passes goes to list 0 with one
  *                      draw per deferred pass, otherwise one draw per basic pass goes to list 1

@@ -17,6 +17,7 @@
 namespace ovis {
 
 constexpr int kDrawTile = 1024;       // visible-list entries per CTA (256 threads x 4)
+constexpr int kDrawSingleLaunchTiles = 2;    // measured: re-counting more than ~2K entries costs more than the second launch
 
 __device__ __forceinline__ void draw_counts(const DrawArgs &a, uint32_t id, uint32_t &c0, uint32_t &c1) {
     const uint32_t slot = id - a.id_base;
@@ -82,9 +83,18 @@ draw_write_kernel(const __grid_constant__ DrawArgs a) {
         return;
     }
     uint32_t p0 = 0, p1 = 0;
-    for (int t = tid; t < (int)blockIdx.x; t += 256) {
-        p0 += a.tile_totals[2 * t];
-        p1 += a.tile_totals[2 * t + 1];
+    if (a.tile_totals) {
+        for (int t = tid; t < (int)blockIdx.x; t += 256) {
+            p0 += a.tile_totals[2 * t];
+            p1 += a.tile_totals[2 * t + 1];
+        }
+    } else {                                                 // short list, single launch: count the earlier entries here
+        for (int64_t i = tid; i < base; i += 256) {
+            uint32_t c0, c1;
+            draw_counts(a, a.d_visible[i], c0, c1);
+            p0 += c0;
+            p1 += c1;
+        }
     }
     p0 = __reduce_add_sync(0xffffffffu, p0);
     p1 = __reduce_add_sync(0xffffffffu, p1);
@@ -141,12 +151,19 @@ draw_write_kernel(const __grid_constant__ DrawArgs a) {
     }
 }
 
-void launch_draw_lists(const DrawArgs &a, int64_t max_visible, cudaStream_t s) {
+int launch_draw_lists(const DrawArgs &a, int64_t max_visible, cudaStream_t s) {
     int tiles = (int)((max_visible + kDrawTile - 1) / kDrawTile);
     if (tiles < 1)
         tiles = 1;
+    if (tiles <= kDrawSingleLaunchTiles) {                   // very short list: re-counting one tile beats a second launch
+        DrawArgs b = a;
+        b.tile_totals = nullptr;
+        draw_write_kernel<<<tiles, 256, 0, s>>>(b);
+        return 1;
+    }
     draw_count_kernel<<<tiles, 256, 0, s>>>(a);
     draw_write_kernel<<<tiles, 256, 0, s>>>(a);
+    return 2;
 }
 
 // EntityUniforms for the visible entities: 20 floats each (mat4 column-major, position, pad) = std140's 80 bytes.

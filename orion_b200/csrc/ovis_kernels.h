@@ -121,7 +121,7 @@ struct DrawArgs {
     const uint32_t *pass_counts;     // per slot: numPasses deferred | basic << 8 | shadow caster << 16
     const uint32_t *caster_mask;     // alive & castsShadow bits (mode 1)
     int mode;                        // 0 = prepareEntities (two lists), 1 = shadow-caster list
-    uint32_t *tile_totals;           // scratch: 2 per 1024-entry tile
+    uint32_t *tile_totals;           // scratch: 2 per 1024-entry tile (NULL: the write kernel counts for itself)
     uint2 *d_draws0, *d_draws1;      // (entity id, pass index)
     long long cap0, cap1;
     uint32_t *d_draw_counts;         // [2]
@@ -138,7 +138,7 @@ struct UniformArgs {
     int64_t capacity;                // entries d_out can hold
 };
 
-void launch_draw_lists(const DrawArgs &a, int64_t max_visible, cudaStream_t s);
+int launch_draw_lists(const DrawArgs &a, int64_t max_visible, cudaStream_t s);   // returns the launches made
 void launch_entity_uniforms(const UniformArgs &a, int64_t max_visible, cudaStream_t s);
 
 enum : uint32_t { kLightNever = 0, kLightAlways = 1, kLightSphere = 2, kLightBox = 3 };

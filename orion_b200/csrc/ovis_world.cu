@@ -1600,7 +1600,7 @@ int ovis_build_draw_lists_device(OvisWorld *w, const uint32_t *d_visible, const 
     if (!d_visible) {                                           // the entity list of the last ovis_cull*
         d_visible = w->d_result;
         d_visible_count = w->d_counts;
-        max_visible = w->n_ent;
+        max_visible = w->last_visible;                          // that cull returned its count to the host
     }
     if (max_visible < 0 || max_visible > w->n_ent)
         max_visible = w->n_ent;                                 // a list of distinct entities is no longer than the world
@@ -1618,8 +1618,7 @@ int ovis_build_draw_lists_device(OvisWorld *w, const uint32_t *d_visible, const 
     a.cap0 = capacity0;
     a.cap1 = capacity1;
     a.d_draw_counts = d_draw_counts ? d_draw_counts : w->d_draw_counts;
-    ovis::launch_draw_lists(a, max_visible, w->stream);
-    w->launches += 2;
+    w->launches += ovis::launch_draw_lists(a, max_visible, w->stream);
     OVIS_CUDA(cudaGetLastError());
     return OVIS_OK;
 }
@@ -1648,7 +1647,7 @@ int ovis_pack_entity_uniforms_device(OvisWorld *w, const uint32_t *d_visible, co
     if (!d_visible) {
         d_visible = w->d_result;
         d_visible_count = w->d_counts;
-        max_visible = w->n_ent;
+        max_visible = w->last_visible;                          // that cull returned its count to the host
     }
     if (max_visible < 0 || max_visible > w->n_ent)
         max_visible = w->n_ent;
