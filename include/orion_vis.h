@@ -205,6 +205,14 @@ int ovis_cull_planes_device_exchange(OvisWorld *world, const float planes[24], u
                                      int32_t n_wait, const uint32_t *d_wait_flags, uint32_t wait_value,
                                      int32_t n_signal, uint32_t *const *d_signal_flags, uint32_t signal_value);
 int ovis_wait_flags(OvisWorld *world, const uint32_t *d_flags, int32_t n, uint32_t value);
+/* The host as the reader of a sharded exchange: waits for each segment's flag (d_flags[r] >= value; NULL = no wait) and
+ * delivers the n_segments segments - [count | ids...] blocks of segment_words uint32 each, the layout the exchange
+ * writes - into host_out with the same layout, then synchronises the world's stream. With page-locked host memory
+ * (ovis_host_alloc, cudaHostAlloc) this is ONE kernel that stores each segment's count word and exactly `count` ids
+ * into host memory as soon as that segment has landed; with pageable memory it is a wait kernel and a copy of the
+ * whole buffer. Words of host_out beyond 1 + count of a segment are not written. No counterpart in the reference. */
+int ovis_read_segments_host(OvisWorld *world, const uint32_t *d_flags, uint32_t value, const uint32_t *d_segments,
+                            int64_t segment_words, int32_t n_segments, uint32_t *host_out);
 int ovis_world_exchange_error(OvisWorld *world, int32_t *out_error);
 
 /* Entity cull for callers that cannot allocate GPU memory - a render thread in the middle of a frame, or an

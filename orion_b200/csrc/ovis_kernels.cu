@@ -402,10 +402,12 @@ __device__ __forceinline__ void cull_gather_body(const GatherArgs &a, int block,
 #pragma unroll
         for (int u = 0; u < 4; u++) {
             const uint32_t k = k0 + u * 256;
-            if (k < total && dst0 + k < a.capacity) {
-                a.out[dst0 + k] = val[u];
-                for (int x = 0; x < a.n_extra; x++)            // peers' copies of this shard's segment
-                    a.extra_out[x][dst0 + k] = val[u];
+            if (k < total) {
+                if (dst0 + k < a.capacity)
+                    a.out[dst0 + k] = val[u];
+                if (dst0 + k < a.extra_capacity)
+                    for (int x = 0; x < a.n_extra; x++)        // peers' copies of this shard's segment / the host's copy
+                        a.extra_out[x][dst0 + k] = val[u];
             }
         }
     }
@@ -463,6 +465,31 @@ cull_gather_kernel(const __grid_constant__ GatherArgs a) {
 
 __global__ void wait_flags_kernel(const uint32_t *flags, int n, uint32_t value, uint32_t *error_flag) {
     wait_flags_at_least(flags, n, value, error_flag);
+}
+
+// Reader side of the sharded exchange with the host as the consumer: CTA row r waits for rank r's ready flag alone, then
+// moves that segment - its count word and exactly `count` ids - into mapped pinned host memory. One launch replaces the
+// wait kernel plus a strided device-to-host copy sized by guesswork, and a segment leaves as soon as it has landed.
+__global__ void __launch_bounds__(256)
+segments_to_host_kernel(const uint32_t *flags, uint32_t value, const uint32_t *segments, long long segment_words,
+                        uint32_t *host, uint32_t *error_flag) {
+    const int r = blockIdx.y;
+    if (flags) {
+        if (threadIdx.x == 0)
+            wait_flags_at_least(flags + r, 1, value, error_flag);
+        __syncthreads();
+    }
+    const uint32_t *seg = segments + (long long)r * segment_words;
+    uint32_t *dst = host + (long long)r * segment_words;
+    const uint32_t count = __ldcg(seg);                       // L2 is where the peers' stores land: skip L1
+    const long long words = 1 + (long long)(count < (uint32_t)(segment_words - 1) ? count : (uint32_t)(segment_words - 1));
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < words; i += (long long)gridDim.x * blockDim.x)
+        dst[i] = __ldcg(seg + i);
+}
+
+void launch_segments_to_host(const uint32_t *flags, uint32_t value, const uint32_t *segments, long long segment_words,
+                             int n_segments, uint32_t *host, uint32_t *error_flag, cudaStream_t s) {
+    segments_to_host_kernel<<<dim3(8, (unsigned)n_segments), 256, 0, s>>>(flags, value, segments, segment_words, host, error_flag);
 }
 
 void launch_wait_flags(const uint32_t *flags, int n, uint32_t value, uint32_t *error_flag, cudaStream_t s) {

@@ -63,7 +63,10 @@ struct GatherArgs {               // K3b
     uint32_t *d_count;           // optional: receives count
     // Fused exchange of a sharded world: the same list and count are also stored to these buffers, which may be
     // peer GPUs' memory mapped over NVLink (plain st.global to peer addresses; no CSR chaining on this path).
+    // The extra destinations share one capacity of their own (extra_capacity). A destination may also be pinned host
+    // memory mapped into the device's address space: the ids then reach the host without any copy after the kernel.
     int n_extra;
+    long long extra_capacity;
     uint32_t *extra_out[kMaxPeers];
     uint32_t *extra_count[kMaxPeers];
     // One-way flags instead of a barrier (sharded worlds, all optional):
@@ -174,6 +177,8 @@ int cull_num_variants();
 CullVariant cull_variant(int v);
 void launch_cull_test(const CullArgs &a, bool masked, int variant, int grid, cudaStream_t s, bool overlap_previous_gather);
 void launch_cull_gather(const GatherArgs &a, cudaStream_t s);
+void launch_segments_to_host(const uint32_t *flags, uint32_t value, const uint32_t *segments, long long segment_words,
+                             int n_segments, uint32_t *host, uint32_t *error_flag, cudaStream_t s);
 void launch_wait_flags(const uint32_t *flags, int n, uint32_t value, uint32_t *error_flag, cudaStream_t s);
 int cull_fused_max_blocks_per_sm(bool masked, int variant);
 cudaError_t launch_cull_fused(const CullArgs &a, const GatherArgs &g, bool masked, int variant, int grid, cudaStream_t s);

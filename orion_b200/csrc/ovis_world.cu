@@ -130,6 +130,8 @@ struct OvisWorld {
     uint32_t *d_counts = nullptr;         // [0] entities, [1] lights
     unsigned int *d_exchange = nullptr;   // [0] gather done counter, [1] exchange error flag
     uint32_t *h_counts = nullptr;         // pinned mirror
+    uint32_t *h_counts_dev = nullptr;     // the same words as the device addresses them (mapped pinned memory)
+    bool direct_host = true;              // OVIS_DIRECT_HOST=0 (tuning) forces the copy path
     uint32_t *d_csr_entities = nullptr;
     int64_t cap_csr = 0;
     long long *d_csr_offsets = nullptr;
@@ -482,12 +484,16 @@ struct FlagOpts {            // one-way ready flags of a sharded exchange (ovis_
 int enqueue_cull(OvisWorld *w, const float planes[24], uint32_t require, uint32_t *out, long long capacity,
                  const long long *d_base, long long *d_next, uint32_t *d_count, int n_extra = 0,
                  uint32_t *const *extra_out = nullptr, uint32_t *const *extra_count = nullptr,
-                 const FlagOpts *flags = nullptr) {
+                 const FlagOpts *flags = nullptr, long long extra_capacity = -1) {
     if (require & ~(uint32_t)OVIS_CASTS_SHADOW)
         return fail(OVIS_ERR_INVALID, "require mask 0x%x: only 0 or OVIS_CASTS_SHADOW is supported", require);
     if (w->n_ent == 0) {
         ovis::launch_empty_result(d_base, d_next, d_count, w->stream);
         w->launches++;
+        for (int x = 0; x < n_extra; x++) {
+            ovis::launch_empty_result(nullptr, nullptr, extra_count[x], w->stream);
+            w->launches++;
+        }
         return OVIS_OK;
     }
     OVIS_TRY(upload_masks(w));
@@ -536,6 +542,7 @@ int enqueue_cull(OvisWorld *w, const float planes[24], uint32_t require, uint32_
     g.d_next = d_next;
     g.d_count = d_count;
     g.n_extra = n_extra;
+    g.extra_capacity = extra_capacity >= 0 ? extra_capacity : capacity;
     for (int x = 0; x < n_extra; x++) {
         g.extra_out[x] = extra_out[x];
         g.extra_count[x] = extra_count[x];
@@ -556,7 +563,7 @@ int enqueue_cull(OvisWorld *w, const float planes[24], uint32_t require, uint32_
     // Below ~half a million entities the cull is pure latency: one cooperative launch runs both phases with a grid
     // barrier in between. Larger worlds use two launches, the second overlapped with the next cull's first.
     const int fused_per_sm = w->fused_blocks_per_sm[variant][masked ? 1 : 0];
-    const bool fused = w->fused_small && w->n_ent < (512 << 10) && fused_per_sm > 0 && n_extra == 0 && !flags;
+    const bool fused = w->fused_small && w->n_ent < (512 << 10) && fused_per_sm > 0 && !flags;
     if (fused) {
         grid = std::min(warps_needed_blocks, w->num_sms * fused_per_sm);      // every CTA must be co-resident
         OVIS_CUDA(ovis::launch_cull_fused(a, g, masked, variant, grid, w->stream));
@@ -894,6 +901,13 @@ int ovis_world_create(int device, OvisWorld **out_world) {
     OVIS_CUDA(cudaMalloc(&w->d_counts, 2 * sizeof(uint32_t)));
     OVIS_CUDA(cudaMemset(w->d_counts, 0, 2 * sizeof(uint32_t)));
     OVIS_CUDA(cudaMallocHost(&w->h_counts, 2 * sizeof(uint32_t)));
+    w->h_counts[0] = w->h_counts[1] = 0;
+    if (cudaHostGetDevicePointer((void **)&w->h_counts_dev, w->h_counts, 0) != cudaSuccess) {
+        cudaGetLastError();
+        w->h_counts_dev = nullptr;
+    }
+    if (const char *v = getenv("OVIS_DIRECT_HOST"))
+        w->direct_host = atoi(v) != 0;
     *out_world = w;
     return OVIS_OK;
 }
@@ -1368,6 +1382,30 @@ int ovis_wait_flags(OvisWorld *w, const uint32_t *d_flags, int32_t n, uint32_t v
     return OVIS_OK;
 }
 
+static uint32_t *host_alias(OvisWorld *w, const uint32_t *host);
+
+int ovis_read_segments_host(OvisWorld *w, const uint32_t *d_flags, uint32_t value, const uint32_t *d_segments,
+                            int64_t segment_words, int32_t n_segments, uint32_t *host_out) {
+    if (!w || !d_segments || !host_out || segment_words < 1 || n_segments < 1 || n_segments > 65535)
+        return fail(OVIS_ERR_INVALID, "ovis_read_segments_host: bad arguments");
+    OVIS_TRY(use_device(w));
+    uint32_t *alias = host_alias(w, host_out);
+    if (alias) {
+        ovis::launch_segments_to_host(d_flags, value, d_segments, segment_words, n_segments, alias, w->d_exchange + 1, w->stream);
+        w->launches++;
+    } else {                                                    // pageable destination: wait, then copy every segment whole
+        if (d_flags) {
+            ovis::launch_wait_flags(d_flags, n_segments, value, w->d_exchange + 1, w->stream);
+            w->launches++;
+        }
+        OVIS_CUDA(cudaMemcpyAsync(host_out, d_segments, sizeof(uint32_t) * (size_t)(segment_words * n_segments),
+                                  cudaMemcpyDeviceToHost, w->stream));
+    }
+    OVIS_CUDA(cudaGetLastError());
+    OVIS_CUDA(cudaStreamSynchronize(w->stream));
+    return OVIS_OK;
+}
+
 int ovis_world_exchange_error(OvisWorld *w, int32_t *out_error) {
     if (!w || !out_error)
         return fail(OVIS_ERR_INVALID, "ovis_world_exchange_error: null argument");
@@ -1379,19 +1417,48 @@ int ovis_world_exchange_error(OvisWorld *w, int32_t *out_error) {
     return OVIS_OK;
 }
 
+// Device alias of a caller's host buffer when the GPU can store to it directly: pinned memory from ovis_host_alloc,
+// cudaHostAlloc / cudaMallocHost or cudaHostRegister(..., mapped). NULL for pageable memory. Asked of the driver on every
+// call (well under a microsecond): a cached answer could outlive the allocation it was given for.
+static uint32_t *host_alias(OvisWorld *w, const uint32_t *host) {
+    if (!host || !w->direct_host || !w->h_counts_dev)
+        return nullptr;
+    cudaPointerAttributes attr{};
+    uint32_t *dev = nullptr;
+    if (cudaPointerGetAttributes(&attr, host) == cudaSuccess) {
+        if (attr.type == cudaMemoryTypeHost && attr.devicePointer)
+            dev = static_cast<uint32_t *>(attr.devicePointer);
+    } else {
+        cudaGetLastError();
+    }
+    return dev;
+}
+
 static int cull_to_host(OvisWorld *w, const float planes[24], uint32_t require, bool with_lights,
                         uint32_t *out_entities, int64_t cap_entities, int64_t *out_n_entities,
                         uint32_t *out_lights, int32_t cap_lights, int32_t *out_n_lights) {
     OVIS_TRY(flush_transforms(w));
-    OVIS_TRY(enqueue_cull(w, planes, require, w->d_result, (long long)w->cap_ent, nullptr, nullptr, w->d_counts));
+    // Pinned output buffer: the gather kernel stores the ids (and the count) straight into host memory as its second
+    // destination, so the frame is two kernels and one synchronise - no copy is enqueued at all.
+    uint32_t *alias = cap_entities > 0 ? host_alias(w, out_entities) : nullptr;
+    if (alias) {
+        uint32_t *extra_out[1] = { alias }, *extra_count[1] = { w->h_counts_dev };
+        OVIS_TRY(enqueue_cull(w, planes, require, w->d_result, (long long)w->cap_ent, nullptr, nullptr, w->d_counts, 1,
+                              extra_out, extra_count, nullptr, (long long)cap_entities));
+    } else {
+        OVIS_TRY(enqueue_cull(w, planes, require, w->d_result, (long long)w->cap_ent, nullptr, nullptr, w->d_counts));
+    }
     if (with_lights)
         OVIS_TRY(enqueue_light_cull(w, planes));
-    // One round trip in the common case: visible sets change little from cull to cull, so the ids are copied
-    // speculatively (a little more than the previous call needed) together with the counts; only a call whose list
-    // turns out longer pays a second copy for the remainder.
-    int64_t spec_e = out_entities ? std::min<int64_t>(cap_entities, std::min<int64_t>(w->n_ent, w->last_visible + w->last_visible / 4 + 1024)) : 0;
+    // Pageable output buffer: one round trip in the common case. Visible sets change little from cull to cull, so the
+    // ids are copied speculatively (a little more than the previous call needed) together with the counts; only a call
+    // whose list turns out longer pays a second copy for the remainder.
+    int64_t spec_e = (out_entities && !alias) ? std::min<int64_t>(cap_entities, std::min<int64_t>(w->n_ent, w->last_visible + w->last_visible / 4 + 1024)) : 0;
     int32_t spec_l = (with_lights && out_lights) ? (int32_t)std::min<int64_t>(cap_lights, (int64_t)w->lights.size()) : 0;
-    OVIS_CUDA(cudaMemcpyAsync(w->h_counts, w->d_counts, 2 * sizeof(uint32_t), cudaMemcpyDeviceToHost, w->stream));
+    if (!alias)
+        OVIS_CUDA(cudaMemcpyAsync(w->h_counts, w->d_counts, 2 * sizeof(uint32_t), cudaMemcpyDeviceToHost, w->stream));
+    else if (with_lights)
+        OVIS_CUDA(cudaMemcpyAsync(w->h_counts + 1, w->d_counts + 1, sizeof(uint32_t), cudaMemcpyDeviceToHost, w->stream));
     if (spec_e > 0)
         OVIS_CUDA(cudaMemcpyAsync(out_entities, w->d_result, sizeof(uint32_t) * (size_t)spec_e, cudaMemcpyDeviceToHost, w->stream));
     if (spec_l > 0)
@@ -1407,7 +1474,7 @@ static int cull_to_host(OvisWorld *w, const float planes[24], uint32_t require, 
     if (nl > cap_lights || (nl > 0 && !out_lights))
         return fail(OVIS_ERR_CAPACITY, "light result needs %d entries, buffer holds %d", nl, cap_lights);
     bool again = false;
-    if (ne > spec_e) {
+    if (!alias && ne > spec_e) {
         OVIS_CUDA(cudaMemcpyAsync(out_entities + spec_e, w->d_result + spec_e, sizeof(uint32_t) * (size_t)(ne - spec_e),
                                   cudaMemcpyDeviceToHost, w->stream));
         again = true;

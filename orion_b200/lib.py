@@ -284,6 +284,25 @@ class World:
                                   _p(lights), C.c_int32(len(lights)), C.byref(nl)))
         return ents[:ne.value], lights[:nl.value]
 
+    def bind_cull(self, view, out_entities: np.ndarray, flags=0, out_lights: np.ndarray | None = None):
+        """ovis_cull with its arguments marshalled once, for a frame loop: returns step() -> (n_entities, n_lights).
+        `view` (a 1-element VIEW_DTYPE array) and the output arrays are referenced, not copied: update the view in place
+        between frames and read the ids from out_entities[:n_entities]."""
+        view = np.ascontiguousarray(view, dtype=VIEW_DTYPE).reshape(1)
+        ne, nl = C.c_int64(), C.c_int32()
+        fn, h = self.lib.ovis_cull, self.h
+        args = (h, _p(view), C.c_uint32(flags), _p(out_entities), C.c_int64(len(out_entities)), C.byref(ne),
+                _p(out_lights), C.c_int32(len(out_lights) if out_lights is not None else 0), C.byref(nl))
+        keep = (view, out_entities, out_lights)
+
+        def step():
+            rc = fn(*args)
+            if rc != OVIS_OK:
+                _check(rc)
+            return ne.value, nl.value
+        step.keep = keep
+        return step
+
     def cull_planes(self, planes, require=0, out=None):
         planes = _f32(planes, (24,))
         ne_slots, _, _ = self.counts()
@@ -336,6 +355,14 @@ class World:
 
     def wait_flags(self, d_flags_ptr, n, value):
         _check(self.lib.ovis_wait_flags(self.h, C.c_void_p(d_flags_ptr), C.c_int32(n), C.c_uint32(value & 0xffffffff)))
+
+    def read_segments_host(self, d_segments_ptr: int, segment_words: int, n_segments: int, host_out: np.ndarray,
+                           d_flags_ptr: int = 0, value: int = 0):
+        """Wait for the segments' ready flags and deliver [count | ids] blocks into host_out (synchronous)."""
+        assert host_out.dtype == np.uint32 and host_out.size >= segment_words * n_segments
+        _check(self.lib.ovis_read_segments_host(self.h, C.c_void_p(d_flags_ptr or None), C.c_uint32(value),
+                                                C.c_void_p(d_segments_ptr), C.c_int64(segment_words), C.c_int32(n_segments),
+                                                _p(host_out)))
 
     def exchange_error(self) -> int:
         e = C.c_int32()

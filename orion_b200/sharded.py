@@ -160,14 +160,29 @@ class ShardedWorld:
             self.world.wait_flags(self.flag_local, self.size, self.frame)
 
     def cull_to_host(self, planes, require: int = 0):
-        """One frame end to end: cull + exchange, then the merged list in pinned host memory with ONE strided copy
-        sized from the previous frame's counts (a frame that grew past it pays a second copy). Returns a list of
-        per-rank uint32 arrays (views of the pinned buffer, valid until the next call); rank order = list order."""
+        """One frame end to end: cull + exchange, then the merged list in pinned host memory. Returns a list of per-rank
+        uint32 arrays (views of the pinned buffer, valid until the next call); rank order = list order.
+
+        p2p: two library calls - the cull with the fused exchange, and ovis_read_segments_host, whose single kernel waits
+        for each rank's ready flag and stores that segment's count and ids straight into the pinned buffer.
+        nccl: all-gather, then ONE strided copy sized from the previous frame's counts (a frame that grew past it pays
+        a second copy)."""
+        from . import lib as _lib
         blocks = self.cull_device(planes, require)
+        words = self.capacity + 1
+        if self.exchange_mode == "p2p":
+            if self._pinned is None or self._pinned.array.size < self.size * words:
+                self._pinned = _lib.PinnedBuffer(self.size * words)
+            host = self._pinned.array[:self.size * words].reshape(self.size, words)
+            self.world.read_segments_host(blocks.data_ptr(), words, self.size, self._pinned.array, self.flag_local, self.frame)
+            counts = host[:, 0].astype(np.int64)
+            top = int(counts.max(initial=0))
+            if top > self.capacity:
+                raise RuntimeError(f"visible list of {top} ids exceeds the symmetric segment capacity {self.capacity}")
+            return [host[r, 1:1 + int(counts[r])] for r in range(self.size)]
         spec = int(min(self.capacity, self._last_max + self._last_max // 4 + 256))
-        if self._pinned is None or self._pinned.shape[1] < self.capacity + 1:
-            self._pinned = torch.empty((self.size, self.capacity + 1), dtype=torch.int32).pin_memory()
-        self.enqueue_ready_wait()
+        if self._pinned is None or self._pinned.shape[1] < words:
+            self._pinned = torch.empty((self.size, words), dtype=torch.int32).pin_memory()
         with torch.cuda.stream(self.stream):
             self._pinned[:, :spec + 1].copy_(blocks[:, :spec + 1], non_blocking=True)
         self.stream.synchronize()
@@ -175,9 +190,8 @@ class ShardedWorld:
         counts = host[:, 0].astype(np.int64)
         top = int(counts.max(initial=0))
         if top > self.capacity:
-            if self.exchange_mode == "p2p":
-                raise RuntimeError(f"visible list of {top} ids exceeds the symmetric segment capacity {self.capacity}")
             self.resize(int(top * 1.25) + 1024)
+            self._pinned = None
             return self.cull_to_host(planes, require)
         if top > spec:
             with torch.cuda.stream(self.stream):

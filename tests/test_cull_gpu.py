@@ -368,3 +368,71 @@ def test_partial_updates_touch_only_moved_subtrees(oracle):
         assert same(w.node_world_trs(), wt)
         assert same(w.world_aabbs(), oracle.world_aabb(wt[ent_node], boxes))
     w.close()
+
+
+@pytest.mark.parametrize("n", [0, 3, 4097, 300_000, 1_200_000])
+def test_pinned_output_buffer_gets_the_list_without_a_copy(oracle, n):
+    """A page-locked output buffer (ovis_host_alloc) is written by the gather kernel itself; a pageable one goes through
+    the copy path. Both must hold the same list; a buffer that is too small reports the full count and is not overrun."""
+    rng = np.random.default_rng(900 + n)
+    boxes = util.random_boxes(rng, n, extent=150.0)
+    flags = rng.integers(0, 2, n).astype(np.uint32)
+    w = _world_static(boxes, flags)
+    w.add_lights(util.random_lights(rng, 40, extent=60.0))
+    pinned = lib.PinnedBuffer(n + 8)
+    for v in util.random_views(rng, 4, extent=60.0):
+        planes = lib.view_planes(v)
+        for require in (0, 1):
+            expected = oracle.cull_aabb(boxes, planes, flags, require)
+            pinned.array[:] = 0xdeadbeef
+            got = w.cull_planes(planes, require=require, out=pinned.array)
+            assert np.array_equal(got, expected)
+            assert (pinned.array[len(expected):] == 0xdeadbeef).all()
+            assert np.array_equal(w.cull_planes(planes, require=require), expected)          # pageable
+        ents, ls = w.cull(v, out_entities=pinned.array)                                      # with the light cull beside it
+        e2, l2 = w.cull(v)
+        assert np.array_equal(ents, e2) and np.array_equal(ls, l2)
+        assert np.array_equal(ents, oracle.cull_aabb(boxes, planes))
+    # too small: error + the count that is needed, nothing written past the capacity handed in
+    full = oracle.cull_aabb(boxes, lib.view_planes(scenes.make_view((0, 0, 400), (1, 0, 0, 0), 100.0, 0.1, 2000.0, 1600, 900)))
+    if len(full) > 8:
+        planes = lib.view_planes(scenes.make_view((0, 0, 400), (1, 0, 0, 0), 100.0, 0.1, 2000.0, 1600, 900))
+        pinned.array[:] = 0xdeadbeef
+        cap = len(full) // 2
+        ne = lib.C.c_int64()
+        rc = w.lib.ovis_cull_planes(w.h, lib._p(np.ascontiguousarray(planes, dtype=np.float32)), lib.C.c_uint32(0),
+                                    lib.C.c_void_p(pinned.ptr.value), lib.C.c_int64(cap), lib.C.byref(ne))
+        assert rc == lib.OVIS_ERR_CAPACITY and ne.value == len(full)
+        assert np.array_equal(pinned.array[:cap], full[:cap]) and (pinned.array[cap:] == 0xdeadbeef).all()
+        assert np.array_equal(w.cull_planes(planes, out=pinned.array), full)                 # and the next call is fine
+    w.close()
+    pinned.free()
+
+
+def test_read_segments_host_pinned_and_pageable():
+    """The reader side of the sharded exchange on one GPU: segments and flags prepared locally."""
+    import torch
+    rng = np.random.default_rng(77)
+    n_seg, words = 5, 4001
+    seg = rng.integers(0, 2**31, (n_seg, words)).astype(np.uint32)
+    counts = np.array([0, 1, 1234, 4000, 9000], dtype=np.uint32)     # the last one overflowed its segment: clipped copy
+    seg[:, 0] = counts
+    d_seg = torch.from_numpy(seg.view(np.int32)).cuda()
+    d_flags = torch.full((n_seg,), 7, dtype=torch.int32, device="cuda")
+    w = lib.World(0)
+    pinned = lib.PinnedBuffer(n_seg * words)
+    pinned.array[:] = 0xdeadbeef
+    w.read_segments_host(d_seg.data_ptr(), words, n_seg, pinned.array, d_flags.data_ptr(), 7)
+    host = pinned.array.reshape(n_seg, words)
+    for r in range(n_seg):
+        k = 1 + min(int(counts[r]), words - 1)
+        assert np.array_equal(host[r, :k], seg[r, :k])
+        assert (host[r, k:] == 0xdeadbeef).all()                      # exactly count ids are moved
+    pageable = np.zeros(n_seg * words, dtype=np.uint32)
+    w.read_segments_host(d_seg.data_ptr(), words, n_seg, pageable, d_flags.data_ptr(), 6)    # flags already past 6
+    assert np.array_equal(pageable.reshape(n_seg, words), seg)
+    w.read_segments_host(d_seg.data_ptr(), words, n_seg, pageable)                          # no flags at all
+    assert np.array_equal(pageable.reshape(n_seg, words), seg)
+    assert w.exchange_error() == 0
+    w.close()
+    pinned.free()
