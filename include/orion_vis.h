@@ -146,6 +146,10 @@ int ovis_update_transforms(OvisWorld *world);
 int ovis_light_add(OvisWorld *world, int32_t n, const OvisLight *lights, uint32_t *out_first_id);
 int ovis_light_update(OvisWorld *world, uint32_t id, const OvisLight *light);
 int ovis_light_remove(OvisWorld *world, uint32_t id);
+/* RenderLight::setAttenuation / setShadowBias (render/src/render_light.cc:130-159): the LightUniforms fields that
+ * OvisLight does not carry. A new light has its component's defaults (graphics/src/light.cc:44,63,72): bias -0.001,
+ * attenuation (1, 0.045, 0.0075) for point and (1, 0.09, 0.032) for spot lights. */
+int ovis_light_set_shading(OvisWorld *world, uint32_t light_id, const float attenuation[3], float shadow_bias_constant);
 
 /* ------------------------------------------------------------------------------------------------
  * Host-side view / light set-up (O(views); kept on the host so the planes are built by the same
@@ -161,6 +165,22 @@ int ovis_light_spot_aabb(const OvisLight *light, float out_aabb[6]);
 /* RenderLight::updateShadowViews (render_light.cc:258-332) with the square shadow-map viewport of
  * render/src/deferred_render_pipeline.cc:261-265. *out_count = 0, 1 (spot) or 6 (point). */
 int ovis_light_shadow_views(const OvisLight *light, int32_t shadow_map_resolution, OvisView out_views[6], int32_t *out_count);
+/* The uniform blocks the reference uploads per view and per light, computed on the host
+ * with the reference's operation order and libm calls (O(views), O(lights) work):
+ *   ViewUniforms  (render/include/render_view.h:28-36), 288 bytes: mat4 view, projection, viewProjection,
+ *                 inverseViewProjection; ivec2 viewportPosition, viewportSize; vec3 position; 4 bytes padding - filled
+ *                 by render_view.cc:55,79-80,113-133. viewport_pos NULL = (0, 0).
+ *   LightUniforms (render/include/render_light.h:33-47), 208 bytes, as floats: [0..2] position, [3] intensity, [4..6]
+ *                 normalised direction, [7] cosCutoff (spot), [8..10] colour, [11] range, [12..27] volumeTransform
+ *                 (point, spot: render_light.cc:219-242), [28..43] shadowSpace = bias * projection * view of the shadow
+ *                 view (shadow-casting spot: :284-290), [44] shadowZNear (shadow-casting point: :324), [45..47]
+ *                 attenuation (point, spot: :136-138), [48] shadowBiasConstant (:158), [49..51] padding - the state the
+ *                 graphics Light component leaves a RenderLight in (graphics/src/light.cc:35-45,58-74,100-108). The
+ *                 block starts zeroed (render_core/src/uniform_buffer.cc:136-137); what a type never writes stays 0.
+ *                 `range` is copied for every type (the reference copies an uninitialised member for ambient and
+ *                 directional lights, render_light.cc:336). */
+int ovis_view_uniforms(const OvisView *view, const int32_t viewport_pos[2], void *out288);
+int ovis_light_uniforms(const OvisLight *light, const float attenuation[3], float shadow_bias_constant, void *out208);
 
 /* ------------------------------------------------------------------------------------------------
  * Culling - RenderWorld::cull (render/include/render_world.h:69-77; render/src/simple_render_world.cc:37-49).
@@ -321,6 +341,15 @@ int ovis_get_draw_counts(OvisWorld *world, uint32_t out_counts[2]);
  * Pending transform updates are flushed first. List arguments as for ovis_build_draw_lists_device. */
 int ovis_pack_entity_uniforms_device(OvisWorld *world, const uint32_t *d_visible, const uint32_t *d_visible_count, int64_t max_visible,
                                      float *d_uniforms, int64_t capacity);
+/* LightUniforms blocks (208 bytes each, layout under ovis_light_uniforms) of the lights of a visible-light list, in list
+ * order, gathered on the device from a per-light table the world keeps current (one small kernel). d_visible NULL = the
+ * light list of this world's last ovis_cull with OVIS_CULL_LIGHTS. d_uniforms: 16-byte aligned, `capacity` blocks. */
+int ovis_pack_light_uniforms_device(OvisWorld *world, const uint32_t *d_visible, const uint32_t *d_visible_count, int64_t max_visible,
+                                    float *d_uniforms, int64_t capacity);
+/* ViewUniforms blocks (288 bytes each) of n_views views into device memory: host math, one asynchronous upload on the
+ * world's stream. viewport_pos: 2 ints per view, or NULL for (0, 0). */
+int ovis_pack_view_uniforms_device(OvisWorld *world, int32_t n_views, const OvisView *views, const int32_t *viewport_pos,
+                                   void *d_uniforms);
 
 /* Copy `bytes` from a device pointer this library handed out (e.g. the CSR arrays of
  * ovis_cull_views_device) to host memory, after all work queued on the world's stream; for ABI users

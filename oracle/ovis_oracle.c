@@ -614,3 +614,68 @@ void orc_entity_uniforms(int64_t n, const float *world_trs, float *out20) {
         out20[20 * i + 19] = 0.0f;
     }
 }
+
+void orc_entity_uniform_blocks(int64_t n, const float *world_trs, void *out80) {
+    orc_entity_uniforms(n, world_trs, (float *)out80);
+}
+
+void orc_uniform_sizes(int32_t out[3]) {
+    out[0] = 80; out[1] = 288; out[2] = 208;
+}
+
+/* render/src/render_view.cc:51-58 (position), :74-90 (viewport), :102-135 (matrices) */
+void orc_view_uniforms(const OrcView *view, const int32_t viewport_pos[2], void *out288) {
+    float *f = (float *)out288;
+    int32_t *i = (int32_t *)out288;
+    float planes[24];
+    m4 mv, mp, mvp, mi;
+    memset(out288, 0, 288);
+    view_compute(view, &mv, &mp, &mvp, &mi, planes, 0);
+    memcpy(f, &mv, 64); memcpy(f + 16, &mp, 64); memcpy(f + 32, &mvp, 64); memcpy(f + 48, &mi, 64);
+    i[64] = viewport_pos[0]; i[65] = viewport_pos[1];                          /* :79 */
+    i[66] = view->vp_width; i[67] = view->vp_height;                           /* :80 */
+    memcpy(f + 68, view->position, 12);                                        /* :55 */
+}
+
+/* render/src/render_light.cc setters :68-158, updateVolumeTransform :212-255, updateShadowViews :258-332 */
+void orc_light_uniforms(const OrcLight *l, const float attenuation[3], float shadow_bias, void *out208) {
+    float *f = (float *)out208;
+    memset(out208, 0, 208);
+    v3 pos = V3(l->position[0], l->position[1], l->position[2]);
+    v3 dir = light_direction(l);                                               /* :79 */
+    memcpy(f, l->position, 12);                                                /* :70 */
+    f[3] = l->intensity;                                                       /* :98 */
+    f[4] = dir.x; f[5] = dir.y; f[6] = dir.z;                                  /* :80 */
+    memcpy(f + 8, l->colour, 12);                                              /* :91 */
+    f[11] = l->range;                                                          /* :120, :336 */
+    f[48] = shadow_bias;                                                       /* :158 */
+    if (l->type == ORC_LIGHT_POINT) {
+        m4 M = transform_matrix(pos, Q(1.0f, 0.0f, 0.0f, 0.0f), V3(l->range, l->range, l->range));   /* :222-226 */
+        memcpy(f + 12, &M, 64);
+        memcpy(f + 45, attenuation, 12);                                       /* :136-138 */
+        if (l->flags & ORC_CASTS_SHADOW)
+            f[44] = 0.1f;                                                      /* :324 */
+    } else if (l->type == ORC_LIGHT_SPOT) {
+        f[7] = cosf(radians_f(l->cutoff));                                     /* :110 */
+        float radius = l->range * tanf(radians_f(l->cutoff));                  /* :235 */
+        quat orientation = quat_rotate_between(V3(0.0f, 0.0f, -1.0f), dir);    /* :239 */
+        m4 M = transform_matrix(pos, orientation, V3(radius, radius, l->range));
+        memcpy(f + 12, &M, 64);                                                /* :242 */
+        memcpy(f + 45, attenuation, 12);
+        if (l->flags & ORC_CASTS_SHADOW) {                                     /* :259-260 */
+            OrcView sv[6];
+            orc_light_shadow_views(l, sv);
+            sv[0].vp_width = sv[0].vp_height = 1;                              /* RenderView's initial aspect, render_view.cc:39 */
+            m4 mv, mp, mvp, mi;
+            float planes[24];
+            view_compute(&sv[0], &mv, &mp, &mvp, &mi, planes, 0);
+            m4 bias = m4_identity();                                           /* :284-288 */
+            bias.c[0] = V4(0.5f, 0.0f, 0.0f, 0.0f);
+            bias.c[1] = V4(0.0f, 0.5f, 0.0f, 0.0f);
+            bias.c[2] = V4(0.0f, 0.0f, 1.0f, 0.0f);
+            bias.c[3] = V4(0.5f, 0.5f, 0.0f, 1.0f);
+            m4 shadow_space = m4_mul(m4_mul(bias, mp), mv);                     /* :289-290 */
+            memcpy(f + 28, &shadow_space, 64);
+        }
+    }
+}

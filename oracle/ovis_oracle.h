@@ -106,6 +106,21 @@ void orc_draw_lists(int64_t n_visible, const uint32_t *visible, const uint32_t *
 /* ---- per-entity uniforms (section 8(f) row 2): EntityUniforms{mat4 transform; vec3 position} (render_entity.h:34-37),
  * filled as RenderEntity::setTransform does (render_entity.cc:67-69). 20 floats per entity (std140: 80 bytes). */
 void orc_entity_uniforms(int64_t n, const float *world_trs, float *out20);
+/* The same blocks read back from the uniform buffer of a RenderEntity after setTransform + getResources (the reference
+ * tier goes through UniformBuffer::flush into the headless GPU buffer; the port fills the bytes itself). 80 B each. */
+void orc_entity_uniform_blocks(int64_t n, const float *world_trs, void *out80);
+/* sizeof(EntityUniforms), sizeof(ViewUniforms), sizeof(LightUniforms): 80, 288, 208. */
+void orc_uniform_sizes(int32_t out[3]);
+/* ViewUniforms (render/include/render_view.h:28-36) of a view whose viewport starts at viewport_pos: 288 bytes =
+ * view, projection, viewProjection, inverseViewProjection (4 x mat4), ivec2 viewportPosition, ivec2 viewportSize,
+ * vec3 position, 4 bytes padding (render_view.cc:51-58,74-90,102-135). */
+void orc_view_uniforms(const OrcView *view, const int32_t viewport_pos[2], void *out288);
+/* LightUniforms (render/include/render_light.h:33-47), 208 bytes, in the state the graphics Light component leaves a
+ * RenderLight in (graphics/src/light.cc:35-45,58-74,100-108): floats [0..2] position, [3] intensity, [4..6] normalised
+ * direction, [7] cosCutoff (spot), [8..10] colour, [11] range, [12..27] volumeTransform (point, spot: render_light.cc:
+ * 219-242), [28..43] shadowSpace (shadow-casting spot: :284-290), [44] shadowZNear (shadow-casting point: :324),
+ * [45..47] attenuation (point, spot), [48] shadowBiasConstant, [49..51] padding. Fields a type never writes are 0. */
+void orc_light_uniforms(const OrcLight *light, const float attenuation[3], float shadow_bias, void *out208);
 
 const char *orc_name(void);   /* "port" or "reference" */
 

@@ -211,6 +211,32 @@ class Oracle:
         self.lib.orc_entity_uniforms(C.c_int64(len(world_trs)), _p(world_trs), _p(out))
         return out
 
+    def uniform_sizes(self):
+        out = np.zeros(3, dtype=np.int32)
+        self.lib.orc_uniform_sizes(_p(out))
+        return tuple(int(x) for x in out)
+
+    def entity_uniform_blocks(self, world_trs) -> np.ndarray:
+        """The 80-byte blocks as they sit in the entities' uniform buffers (reference tier: through RenderEntity)."""
+        world_trs = _f32(world_trs, (-1, 10))
+        out = np.zeros((len(world_trs), 20), dtype=np.float32)
+        self.lib.orc_entity_uniform_blocks(C.c_int64(len(world_trs)), _p(world_trs), _p(out))
+        return out
+
+    def view_uniforms(self, view, viewport_pos=(0, 0)) -> np.ndarray:
+        view = np.ascontiguousarray(view, dtype=VIEW_DTYPE).reshape(1)
+        pos = np.asarray(viewport_pos, dtype=np.int32)
+        out = np.zeros(288, dtype=np.uint8)
+        self.lib.orc_view_uniforms(_p(view), _p(pos), _p(out))
+        return out
+
+    def light_uniforms(self, light, attenuation=(1.0, 0.045, 0.0075), shadow_bias=-0.001) -> np.ndarray:
+        light = np.ascontiguousarray(light, dtype=LIGHT_DTYPE).reshape(1)
+        att = np.asarray(attenuation, dtype=np.float32)
+        out = np.zeros(208, dtype=np.uint8)
+        self.lib.orc_light_uniforms(_p(light), _p(att), C.c_float(shadow_bias), _p(out))
+        return out
+
     # ---- tier A object world (reference build only)
     def world(self) -> "RefWorld":
         assert self.has_world, "object world exists only in the reference-compiled oracle"

@@ -28,6 +28,8 @@
 #include "ovis_oracle.h"
 
 #include <chrono>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <memory>
 #include <thread>
@@ -495,6 +497,67 @@ void orc_entity_uniforms(int64_t n, const float *world_trs, float *out20) {
         memcpy(out20 + 20 * i + 16, &tr.position(), 12);
         out20[20 * i + 19] = 0.0f;
     }
+}
+
+/* ------------------------------------------------------------------ uniform blocks as the reference ships them */
+
+/* What UniformBuffer::flush (render_core/src/uniform_buffer.cc:147-152) wrote into the object's (headless) GPU buffer. */
+static void readUniformBlock(GPUResourceSet *set, void *out, size_t size) {
+    GPUObject *object = set->slots()[ResourceSlots::kUniforms].object.get();
+    GPUBuffer *buffer = static_cast<GPUBuffer *>(object);
+    if (buffer->size() != size) {
+        fprintf(stderr, "oracle: uniform block is %zu bytes, caller expects %zu\n", buffer->size(), size);
+        abort();
+    }
+    memcpy(out, buffer->map(0, size, 0, GPUBuffer::kWriteAccess), size);
+    buffer->unmap();
+}
+
+void orc_uniform_sizes(int32_t out[3]) {
+    out[0] = (int32_t)sizeof(EntityUniforms);
+    out[1] = (int32_t)sizeof(ViewUniforms);
+    out[2] = (int32_t)sizeof(LightUniforms);
+}
+
+/* EntityUniforms through RenderEntity::setTransform + getResources (render_entity.cc:64-72,100-103). */
+void orc_entity_uniform_blocks(int64_t n, const float *world_trs, void *out80) {
+    oref_shim_init();
+    for (int64_t i = 0; i < n; i++) {
+        TestEntity e;
+        e.setTransform(trs(world_trs + 10 * i));
+        readUniformBlock(e.getResources(), (char *)out80 + 80 * i, 80);
+    }
+}
+
+/* ViewUniforms through RenderView::setTransform/perspective/setViewport + getResources (render_view.cc:51-98). */
+void orc_view_uniforms(const OrcView *view, const int32_t viewport_pos[2], void *out288) {
+    oref_shim_init();
+    RenderView rv;
+    rv.setTransform(v3(view->position), qt(view->orientation));
+    rv.perspective(view->hfov_deg, view->znear, view->zfar);
+    rv.setViewport(IntRect(viewport_pos[0], viewport_pos[1], view->vp_width, view->vp_height));
+    readUniformBlock(rv.getResources(), out288, 288);
+}
+
+/* LightUniforms through the setters graphics/src/light.cc drives: Light::Light (:35-45: colour, intensity, flags, shadow
+ * bias), the Point/Spot constructors (:58-74: range, attenuation, cutoff), Light::transformed (:100-108: direction, then
+ * position, for EVERY light type). setRange is also called for ambient/directional lights, whose m_range the reference
+ * leaves uninitialised (it then copies it into the block, render_light.cc:336): the harness needs a defined value. */
+void orc_light_uniforms(const OrcLight *d, const float attenuation[3], float shadow_bias, void *out208) {
+    oref_shim_init();
+    RenderLight l((RenderLight::Type)d->type);
+    l.setColour(v3(d->colour));
+    l.setIntensity(d->intensity);
+    l.setFlags(d->flags);
+    l.setShadowBias(shadow_bias);
+    l.setRange(d->range);
+    if (d->type == RenderLight::kPointLight || d->type == RenderLight::kSpotLight)
+        l.setAttenuation(attenuation[0], attenuation[1], attenuation[2]);
+    if (d->type == RenderLight::kSpotLight)
+        l.setCutoff(d->cutoff);
+    l.setDirection(v3(d->direction));
+    l.setPosition(v3(d->position));
+    readUniformBlock(l.getResources(), out208, 208);
 }
 
 } /* extern "C" */

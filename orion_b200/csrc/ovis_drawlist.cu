@@ -14,6 +14,8 @@
 
 #include "ovis_device.cuh"
 
+#include <algorithm>
+
 namespace ovis {
 
 constexpr int kDrawTile = 1024;       // visible-list entries per CTA (256 threads x 4)
@@ -195,6 +197,26 @@ entity_uniforms_kernel(const __grid_constant__ UniformArgs a) {
 void launch_entity_uniforms(const UniformArgs &a, int64_t max_visible, cudaStream_t s) {
     if (max_visible > 0)
         entity_uniforms_kernel<<<(unsigned)((max_visible + 255) / 256), 256, 0, s>>>(a);
+}
+
+// LightUniforms of the visible lights, in list order: 208-byte blocks gathered from the per-light table (13 float4 each).
+__global__ void __launch_bounds__(256)
+light_uniforms_kernel(const uint32_t *visible, const uint32_t *visible_count, const float4 *table, float4 *out, int64_t capacity) {
+    const uint32_t m = *visible_count;
+    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t i = t / 13;
+    const int q = (int)(t - i * 13);
+    if (i >= m || i >= capacity)
+        return;
+    out[i * 13 + q] = table[(int64_t)visible[i] * 13 + q];
+}
+
+void launch_light_uniforms(const uint32_t *d_visible, const uint32_t *d_visible_count, const float *d_table, float *d_out,
+                           int64_t max_visible, int64_t capacity, cudaStream_t s) {
+    const int64_t threads = std::min(max_visible, capacity) * 13;
+    if (threads > 0)
+        light_uniforms_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, s>>>(
+            d_visible, d_visible_count, reinterpret_cast<const float4 *>(d_table), reinterpret_cast<float4 *>(d_out), capacity);
 }
 
 }  // namespace ovis

@@ -143,6 +143,8 @@ struct UniformArgs {
 
 int launch_draw_lists(const DrawArgs &a, int64_t max_visible, cudaStream_t s);   // returns the launches made
 void launch_entity_uniforms(const UniformArgs &a, int64_t max_visible, cudaStream_t s);
+void launch_light_uniforms(const uint32_t *d_visible, const uint32_t *d_visible_count, const float *d_table, float *d_out,
+                           int64_t max_visible, int64_t capacity, cudaStream_t s);
 
 enum : uint32_t { kLightNever = 0, kLightAlways = 1, kLightSphere = 2, kLightBox = 3 };
 

@@ -313,5 +313,62 @@ inline int shadowViews(const OvisLight &l, int resolution, OvisView out[6]) {
     return count;
 }
 
+// ViewUniforms (render/include/render_view.h:28-36), 288 bytes: 4 x mat4, ivec2 viewportPosition, ivec2 viewportSize,
+// vec3 position (+4 bytes of padding); filled by render_view.cc:55 (position), :79-80 (viewport), :113-133 (matrices).
+inline void viewUniforms(const OvisView &v, const int32_t viewportPos[2], void *out288) {
+    float *f = static_cast<float *>(out288);
+    int32_t *i = static_cast<int32_t *>(out288);
+    std::memset(out288, 0, 288);
+    ViewMatrices m = viewMatrices(v);
+    std::memcpy(f, &m.view, 64);
+    std::memcpy(f + 16, &m.projection, 64);
+    std::memcpy(f + 32, &m.viewProjection, 64);
+    std::memcpy(f + 48, &m.inverseViewProjection, 64);
+    i[64] = viewportPos[0]; i[65] = viewportPos[1];
+    i[66] = v.vp_width; i[67] = v.vp_height;
+    std::memcpy(f + 68, v.position, 12);
+}
+
+// LightUniforms (render/include/render_light.h:33-47), 208 bytes, in the state the graphics Light component leaves a
+// RenderLight in (graphics/src/light.cc:35-45,58-74,100-108). The block starts zeroed (uniform_buffer.cc:136-137) and
+// fields a light type never writes stay zero.
+inline void lightUniforms(const OvisLight &l, const float attenuation[3], float shadowBias, void *out208) {
+    float *f = static_cast<float *>(out208);
+    std::memset(out208, 0, 208);
+    Vec3 pos = { l.position[0], l.position[1], l.position[2] };
+    Vec3 dir = lightDirection(l);
+    std::memcpy(f, l.position, 12);                                                       // render_light.cc:70
+    f[3] = l.intensity;                                                                   // :98
+    f[4] = dir.x; f[5] = dir.y; f[6] = dir.z;                                             // :80
+    std::memcpy(f + 8, l.colour, 12);                                                     // :91
+    f[11] = l.range;                                                                      // :120, :336
+    f[48] = shadowBias;                                                                   // :158
+    if (l.type == OVIS_LIGHT_POINT) {
+        Mat4 volume = transformMatrix(pos, Quat{ 1.0f, 0.0f, 0.0f, 0.0f }, Vec3{ l.range, l.range, l.range });   // :222-226
+        std::memcpy(f + 12, &volume, 64);
+        std::memcpy(f + 45, attenuation, 12);                                             // :136-138
+        if (l.flags & OVIS_CASTS_SHADOW)
+            f[44] = 0.1f;                                                                 // :324
+    } else if (l.type == OVIS_LIGHT_SPOT) {
+        f[7] = cosf(radians(l.cutoff));                                                   // :110
+        float radius = l.range * tanf(radians(l.cutoff));                                 // :235
+        Quat orientation = quatRotateBetween(Vec3{ 0.0f, 0.0f, -1.0f }, dir);             // :239
+        Mat4 volume = transformMatrix(pos, orientation, Vec3{ radius, radius, l.range });
+        std::memcpy(f + 12, &volume, 64);                                                 // :242
+        std::memcpy(f + 45, attenuation, 12);
+        OvisView sv[6];
+        if (shadowViews(l, 1, sv) == 1) {                                                 // aspect 1: render_view.cc:39
+            ViewMatrices m = viewMatrices(sv[0]);
+            Mat4 bias;                                                                    // :284-288
+            bias.col[0] = { 0.5f, 0.0f, 0.0f, 0.0f };
+            bias.col[1] = { 0.0f, 0.5f, 0.0f, 0.0f };
+            bias.col[2] = { 0.0f, 0.0f, 1.0f, 0.0f };
+            bias.col[3] = { 0.5f, 0.5f, 0.0f, 1.0f };
+            Mat4 shadowSpace = bias * m.projection * m.view;                              // :289-290
+            std::memcpy(f + 28, &shadowSpace, 64);
+        }
+    }
+}
+
 }  // namespace hm
 }  // namespace ovis

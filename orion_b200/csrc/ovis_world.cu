@@ -112,6 +112,10 @@ struct OvisWorld {
     // ---- lights
     std::vector<OvisLight> lights;
     std::vector<uint8_t> light_alive;
+    struct LightShading { float attenuation[3]; float shadow_bias; };
+    std::vector<LightShading> light_shading;   // what the LightUniforms block needs beyond OvisLight
+    float *d_light_uniforms = nullptr;    // 52 floats (208 B) per light slot
+    int64_t last_visible_lights = 0;      // light count of the previous ovis_cull with OVIS_CULL_LIGHTS
     ovis::DeviceLight *d_lights = nullptr;
     uint32_t *d_light_out = nullptr;
     int64_t cap_lights = 0;
@@ -594,6 +598,7 @@ int upload_lights(OvisWorld *w) {
         int64_t cap = std::max<int64_t>(n, 64);
         OVIS_TRY(grow(w->d_lights, 0, cap, w->stream, false));
         OVIS_TRY(grow(w->d_light_out, 0, cap, w->stream, false));
+        OVIS_TRY(grow(w->d_light_uniforms, 0, 52 * cap, w->stream, false));
         w->cap_lights = cap;
     }
     std::vector<ovis::DeviceLight> dl((size_t)n);
@@ -618,8 +623,13 @@ int upload_lights(OvisWorld *w) {
             d.kind = ovis::kLightNever;                                              // render_light.cc:206-207
         }
     }
+    std::vector<float> blocks(52 * (size_t)n);
+    for (int64_t i = 0; i < n; i++)
+        ovis::hm::lightUniforms(w->lights[(size_t)i], w->light_shading[(size_t)i].attenuation, w->light_shading[(size_t)i].shadow_bias,
+                                blocks.data() + 52 * (size_t)i);
     if (n > 0) {
         OVIS_CUDA(cudaMemcpyAsync(w->d_lights, dl.data(), sizeof(ovis::DeviceLight) * (size_t)n, cudaMemcpyHostToDevice, w->stream));
+        OVIS_CUDA(cudaMemcpyAsync(w->d_light_uniforms, blocks.data(), sizeof(float) * blocks.size(), cudaMemcpyHostToDevice, w->stream));
         OVIS_CUDA(cudaStreamSynchronize(w->stream));
     }
     w->lights_dirty = false;
@@ -918,7 +928,7 @@ int ovis_world_destroy(OvisWorld *w) {
     cudaSetDevice(w->device);
     cudaStreamSynchronize(w->stream);
     void *bufs[] = { w->d_local, w->d_world, w->d_alive_bits, w->d_caster_bits, w->d_parent, w->d_local_trs, w->d_world_trs,
-                     w->d_node_entity, w->d_dirty, w->d_entity_node, w->d_pass_counts, w->d_draw_totals, w->d_draw_counts,
+                     w->d_node_entity, w->d_dirty, w->d_light_uniforms, w->d_entity_node, w->d_pass_counts, w->d_draw_totals, w->d_draw_counts,
                      w->d_extra_entity, w->d_extra_node, w->d_level_lists, w->d_lights, w->d_light_out,
                      w->d_staging, w->d_tile_counts, w->d_block_totals, w->d_exchange, w->d_mv_counts, w->d_mv_totals, w->d_mv_planes,
                      w->d_mv_require, w->d_mv_groups, w->d_mv_hits, w->d_result, w->d_counts, w->d_csr_entities, w->d_csr_offsets,
@@ -1258,6 +1268,13 @@ int ovis_light_add(OvisWorld *w, int32_t n, const OvisLight *lights, uint32_t *o
             return fail(OVIS_ERR_INVALID, "spot light cutoff must be <= 45 degrees");   // render_light.cc:104
         w->lights.push_back(lights[i]);
         w->light_alive.push_back(1);
+        // the defaults of the graphics Light components (graphics/src/light.cc:44,63,72)
+        OvisWorld::LightShading sh = { { 0.0f, 0.0f, 0.0f }, -0.001f };
+        if (lights[i].type == OVIS_LIGHT_POINT)
+            sh = { { 1.0f, 0.045f, 0.0075f }, -0.001f };
+        else if (lights[i].type == OVIS_LIGHT_SPOT)
+            sh = { { 1.0f, 0.09f, 0.032f }, -0.001f };
+        w->light_shading.push_back(sh);
     }
     w->lights_dirty = true;
     return OVIS_OK;
@@ -1269,6 +1286,15 @@ int ovis_light_update(OvisWorld *w, uint32_t id, const OvisLight *light) {
     if (light->type == OVIS_LIGHT_SPOT && light->cutoff > 45.0f)
         return fail(OVIS_ERR_INVALID, "spot light cutoff must be <= 45 degrees");
     w->lights[id] = *light;
+    w->lights_dirty = true;
+    return OVIS_OK;
+}
+
+int ovis_light_set_shading(OvisWorld *w, uint32_t id, const float attenuation[3], float shadow_bias_constant) {
+    if (!w || !attenuation || id >= w->lights.size() || !w->light_alive[id])
+        return fail(OVIS_ERR_INVALID, "ovis_light_set_shading: unknown light %u", id);
+    std::memcpy(w->light_shading[id].attenuation, attenuation, 12);
+    w->light_shading[id].shadow_bias = shadow_bias_constant;
     w->lights_dirty = true;
     return OVIS_OK;
 }
@@ -1302,6 +1328,23 @@ int ovis_view_matrices(const OvisView *view, float out_mats[64], float out_corne
     }
     if (out_corners)
         ovis::hm::frustumCorners(m.inverseViewProjection, out_corners);
+    return OVIS_OK;
+}
+
+int ovis_view_uniforms(const OvisView *view, const int32_t viewport_pos[2], void *out288) {
+    if (!view || !out288)
+        return fail(OVIS_ERR_INVALID, "ovis_view_uniforms: null argument");
+    const int32_t origin[2] = { 0, 0 };
+    ovis::hm::viewUniforms(*view, viewport_pos ? viewport_pos : origin, out288);
+    return OVIS_OK;
+}
+
+int ovis_light_uniforms(const OvisLight *light, const float attenuation[3], float shadow_bias_constant, void *out208) {
+    if (!light || !attenuation || !out208)
+        return fail(OVIS_ERR_INVALID, "ovis_light_uniforms: null argument");
+    if (light->type == OVIS_LIGHT_SPOT && light->cutoff > 45.0f)
+        return fail(OVIS_ERR_INVALID, "spot light cutoff must be <= 45 degrees");
+    ovis::hm::lightUniforms(*light, attenuation, shadow_bias_constant, out208);
     return OVIS_OK;
 }
 
@@ -1467,6 +1510,8 @@ static int cull_to_host(OvisWorld *w, const float planes[24], uint32_t require, 
     int64_t ne = w->h_counts[0];
     int32_t nl = with_lights ? (int32_t)w->h_counts[1] : 0;
     w->last_visible = ne;
+    if (with_lights)
+        w->last_visible_lights = nl;
     if (out_n_entities) *out_n_entities = ne;
     if (out_n_lights) *out_n_lights = nl;
     if (ne > cap_entities || (ne > 0 && !out_entities))
@@ -1687,6 +1732,45 @@ int ovis_build_draw_lists_device(OvisWorld *w, const uint32_t *d_visible, const 
     a.d_draw_counts = d_draw_counts ? d_draw_counts : w->d_draw_counts;
     w->launches += ovis::launch_draw_lists(a, max_visible, w->stream);
     OVIS_CUDA(cudaGetLastError());
+    return OVIS_OK;
+}
+
+int ovis_pack_light_uniforms_device(OvisWorld *w, const uint32_t *d_visible, const uint32_t *d_visible_count, int64_t max_visible,
+                                    float *d_uniforms, int64_t capacity) {
+    if (!w || capacity < 0 || (capacity > 0 && !d_uniforms) || ((uintptr_t)d_uniforms & 15u))
+        return fail(OVIS_ERR_INVALID, "ovis_pack_light_uniforms_device: bad arguments (the output must be 16-byte aligned)");
+    if ((d_visible == nullptr) != (d_visible_count == nullptr))
+        return fail(OVIS_ERR_INVALID, "ovis_pack_light_uniforms_device: pass both the list and its count, or neither");
+    OVIS_TRY(use_device(w));
+    OVIS_TRY(upload_lights(w));
+    const int64_t n_lights = (int64_t)w->lights.size();
+    if (!d_visible) {                                           // the light list of the last ovis_cull
+        d_visible = w->d_light_out;
+        d_visible_count = w->d_counts + 1;
+        max_visible = w->last_visible_lights;
+    }
+    if (max_visible < 0 || max_visible > n_lights)
+        max_visible = n_lights;
+    if (n_lights > 0 && std::min(max_visible, capacity) > 0) {
+        ovis::launch_light_uniforms(d_visible, d_visible_count, w->d_light_uniforms, d_uniforms, max_visible, capacity, w->stream);
+        w->launches++;
+    }
+    OVIS_CUDA(cudaGetLastError());
+    return OVIS_OK;
+}
+
+int ovis_pack_view_uniforms_device(OvisWorld *w, int32_t n_views, const OvisView *views, const int32_t *viewport_pos, void *d_uniforms) {
+    if (!w || n_views < 0 || (n_views > 0 && (!views || !d_uniforms)))
+        return fail(OVIS_ERR_INVALID, "ovis_pack_view_uniforms_device: bad arguments");
+    OVIS_TRY(use_device(w));
+    if (n_views == 0)
+        return OVIS_OK;
+    std::vector<uint8_t> blocks(288 * (size_t)n_views);
+    const int32_t origin[2] = { 0, 0 };
+    for (int32_t i = 0; i < n_views; i++)
+        ovis::hm::viewUniforms(views[i], viewport_pos ? viewport_pos + 2 * i : origin, blocks.data() + 288 * (size_t)i);
+    // pageable source: the runtime has taken its copy of `blocks` when this returns
+    OVIS_CUDA(cudaMemcpyAsync(d_uniforms, blocks.data(), blocks.size(), cudaMemcpyHostToDevice, w->stream));
     return OVIS_OK;
 }
 

@@ -104,6 +104,24 @@ def light_spot_aabb(light: np.ndarray) -> np.ndarray:
     return out
 
 
+def view_uniforms(view: np.ndarray, viewport_pos=(0, 0)) -> np.ndarray:
+    """ViewUniforms block (288 bytes) of a view."""
+    view = np.ascontiguousarray(view, dtype=VIEW_DTYPE).reshape(1)
+    pos = np.asarray(viewport_pos, dtype=np.int32)
+    out = np.zeros(288, dtype=np.uint8)
+    _check(load().ovis_view_uniforms(_p(view), _p(pos), _p(out)))
+    return out
+
+
+def light_uniforms(light: np.ndarray, attenuation=(1.0, 0.045, 0.0075), shadow_bias=-0.001) -> np.ndarray:
+    """LightUniforms block (208 bytes) of a light."""
+    light = np.ascontiguousarray(light, dtype=LIGHT_DTYPE).reshape(1)
+    att = np.asarray(attenuation, dtype=np.float32)
+    out = np.zeros(208, dtype=np.uint8)
+    _check(load().ovis_light_uniforms(_p(light), _p(att), C.c_float(shadow_bias), _p(out)))
+    return out
+
+
 def light_shadow_views(light: np.ndarray, resolution: int = 512) -> np.ndarray:
     light = np.ascontiguousarray(light, dtype=LIGHT_DTYPE)
     out = np.zeros(6, dtype=VIEW_DTYPE)
@@ -444,6 +462,24 @@ class World:
         _check(self.lib.ovis_pack_entity_uniforms_device(self.h, C.c_void_p(d_visible or None),
                                                          C.c_void_p(d_visible_count or None), C.c_int64(max_visible),
                                                          C.c_void_p(d_uniforms or None), C.c_int64(capacity)))
+
+    def set_light_shading(self, light_id, attenuation, shadow_bias):
+        att = np.asarray(attenuation, dtype=np.float32)
+        _check(self.lib.ovis_light_set_shading(self.h, C.c_uint32(light_id), _p(att), C.c_float(shadow_bias)))
+
+    def pack_light_uniforms_device(self, d_uniforms: int, capacity: int, d_visible: int = 0, d_visible_count: int = 0,
+                                   max_visible: int = -1):
+        """Asynchronous. 208 bytes per visible light into d_uniforms; d_visible = 0 uses the last cull's light list."""
+        _check(self.lib.ovis_pack_light_uniforms_device(self.h, C.c_void_p(d_visible or None),
+                                                        C.c_void_p(d_visible_count or None), C.c_int64(max_visible),
+                                                        C.c_void_p(d_uniforms or None), C.c_int64(capacity)))
+
+    def pack_view_uniforms_device(self, views, d_uniforms: int, viewport_pos=None):
+        """Asynchronous. 288 bytes per view into d_uniforms."""
+        views = np.ascontiguousarray(views, dtype=VIEW_DTYPE).reshape(-1)
+        pos = np.ascontiguousarray(viewport_pos, dtype=np.int32).reshape(-1) if viewport_pos is not None else None
+        assert pos is None or len(pos) == 2 * len(views)
+        _check(self.lib.ovis_pack_view_uniforms_device(self.h, C.c_int32(len(views)), _p(views), _p(pos), C.c_void_p(d_uniforms)))
 
     # ---- read-back
     def read_device(self, d_ptr: int, count: int, dtype=np.uint32) -> np.ndarray:

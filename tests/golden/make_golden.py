@@ -93,7 +93,14 @@ def main():
     for i in range(2):
         g[f"draws_deferred_{i}"], g[f"draws_basic_{i}"] = ref.draw_lists(g[f"cull_all_{i}"], pc, cf, 0)
         g[f"draws_shadow_{i}"], _ = ref.draw_lists(g[f"cull_all_{i}"], pc, cf, 1)
-    g["entity_uniforms"] = ref.entity_uniforms(g["world_trs"])
+    g["entity_uniforms"] = ref.entity_uniform_blocks(g["world_trs"])      # read back from the RenderEntity's uniform buffer
+    assert np.array_equal(g["entity_uniforms"], ref.entity_uniforms(g["world_trs"]), equal_nan=True)
+    g["view_viewport_pos"] = rng2.integers(0, 400, (len(views), 2)).astype(np.int32)
+    g["view_uniforms"] = np.stack([ref.view_uniforms(v, p) for v, p in zip(views, g["view_viewport_pos"])])
+    g["light_attenuation"] = rng2.uniform(0, 1, (len(lights), 3)).astype(np.float32)
+    g["light_shadow_bias"] = rng2.uniform(-0.01, 0, len(lights)).astype(np.float32)
+    g["light_uniforms"] = np.stack([ref.light_uniforms(l, a, float(b)) for l, a, b in
+                                    zip(lights, g["light_attenuation"], g["light_shadow_bias"])])
     out = os.path.join(HERE, "visibility_golden.npz")
     np.savez_compressed(out, **g)
     print(out, os.path.getsize(out), "bytes,", len(g), "arrays")

@@ -218,3 +218,50 @@ def test_config2_one_million_draws_and_uniforms(oracle):
     ident = oracle.entity_uniforms(np.tile(np.array([0, 0, 0, 1, 0, 0, 0, 1, 1, 1], dtype=np.float32), (1, 1)))
     assert same(u, np.repeat(ident, len(visible), axis=0))    # static geometry: Transform() of an entity never moved
     w.close()
+
+
+def test_light_and_view_uniform_blocks(oracle):
+    """LightUniforms of the visible lights (list order) gathered on the device, ViewUniforms uploaded per view."""
+    rng = np.random.default_rng(41)
+    n_lights = 700
+    lights = util.random_lights(rng, n_lights, extent=80.0)
+    w, boxes, flags, pc = _static_world(rng, 5000)
+    first = w.add_lights(lights)
+    assert first == 0
+    # default shading parameters of the Light components, then explicit ones for half of the lights
+    att = np.zeros((n_lights, 3), dtype=np.float32)
+    att[lights["type"] == scenes.LIGHT_POINT] = (1.0, 0.045, 0.0075)
+    att[lights["type"] == scenes.LIGHT_SPOT] = (1.0, 0.09, 0.032)
+    bias = np.full(n_lights, -0.001, dtype=np.float32)
+    for i in range(0, n_lights, 2):
+        att[i] = rng.uniform(0, 1, 3)
+        bias[i] = rng.uniform(-0.01, 0)
+        w.set_light_shading(i, att[i], float(bias[i]))
+
+    def expected(ids):
+        if len(ids) == 0:
+            return np.zeros((0, 208), dtype=np.uint8)
+        return np.stack([oracle.light_uniforms(lights[i], att[i], float(bias[i])) for i in ids])
+
+    for v in util.random_views(rng, 3, extent=40.0):
+        _, ls = w.cull(v)
+        assert np.array_equal(ls, oracle.light_cull(lights, lib.view_planes(v)))
+        got = util.gpu_light_uniforms(w)                                   # from the cull's device light list
+        assert got[:len(ls)].tobytes() == expected(ls).tobytes()
+        assert (got[len(ls):] == 0x55).all()
+    ids = rng.permutation(n_lights).astype(np.uint32)[:300]
+    assert util.gpu_light_uniforms(w, ids).tobytes() == expected(ids).tobytes()     # any list the caller hands in
+    assert util.gpu_light_uniforms(w, ids, cap=100).tobytes() == expected(ids[:100]).tobytes()
+    assert util.gpu_light_uniforms(w, np.empty(0, np.uint32), cap=3).shape == (3, 208)
+    # a light that changes is re-packed
+    lights[ids[0]] = util.random_lights(rng, 1, extent=80.0)[0]
+    w.update_light(int(ids[0]), lights[ids[0]])
+    assert util.gpu_light_uniforms(w, ids).tobytes() == expected(ids).tobytes()
+    # views
+    views = np.concatenate([util.random_views(rng, 50), np.asarray(scenes.default_camera()).reshape(1)])
+    pos = rng.integers(0, 2000, (len(views), 2)).astype(np.int32)
+    got = util.gpu_view_uniforms(w, views, pos)
+    want = np.stack([oracle.view_uniforms(v, p) for v, p in zip(views, pos)])
+    assert got.tobytes() == want.tobytes()
+    assert util.gpu_view_uniforms(w, views[:2]).tobytes() == np.stack([oracle.view_uniforms(v) for v in views[:2]]).tobytes()
+    w.close()

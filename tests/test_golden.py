@@ -63,9 +63,17 @@ def test_port_draw_lists_and_uniforms(port):
         s0, s1 = port.draw_lists(G[f"cull_all_{i}"], G["draw_pass_counts"], G["cull_flags"], 1)
         assert np.array_equal(s0, G[f"draws_shadow_{i}"]) and len(s1) == 0
     assert same(port.entity_uniforms(G["world_trs"]), G["entity_uniforms"])
+    for v, pos, want in zip(G["views"], G["view_viewport_pos"], G["view_uniforms"]):
+        assert port.view_uniforms(v, pos).tobytes() == want.tobytes()
+    for l, att, bias, want in zip(G["lights"], G["light_attenuation"], G["light_shadow_bias"], G["light_uniforms"]):
+        assert port.light_uniforms(l, att, float(bias)).tobytes() == want.tobytes()
 
 
 def test_library_host_math_against_golden():
+    for v, pos, want in zip(G["views"], G["view_viewport_pos"], G["view_uniforms"]):
+        assert lib.view_uniforms(v, pos).tobytes() == want.tobytes()
+    for l, att, bias, want in zip(G["lights"], G["light_attenuation"], G["light_shadow_bias"], G["light_uniforms"]):
+        assert lib.light_uniforms(l, att, float(bias)).tobytes() == want.tobytes()
     for i, v in enumerate(G["views"]):
         assert same(lib.view_planes(v), G["view_planes"][i])
         m, c = lib.view_matrices(v)
@@ -108,6 +116,13 @@ def test_cuda_path_against_golden():
         assert np.array_equal(s0, G[f"draws_shadow_{i}"]) and len(s1) == 0
     for x, y in zip(w.shadow_lists(G["lists_view"][0]), _lists("lists")):
         assert np.array_equal(x, y)
+    for i, (att, bias) in enumerate(zip(G["light_attenuation"], G["light_shadow_bias"])):
+        w.set_light_shading(i, att, float(bias))
+    _, ls = w.cull(G["cull_views"][0])
+    assert len(ls) > 5
+    assert util.gpu_light_uniforms(w)[:len(ls)].tobytes() == G["light_uniforms"][ls].tobytes()
+    got = util.gpu_view_uniforms(w, G["views"], G["view_viewport_pos"])
+    assert got.tobytes() == G["view_uniforms"].tobytes()
     w.close()
     s = scenes.cubes_scene()
     w = lib.World(0)

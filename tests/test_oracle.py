@@ -167,3 +167,21 @@ def test_draw_lists_and_entity_uniforms(port, ref):
     trs[:5, 7:10] = 0.0                                                     # degenerate scale
     trs[5, 3:7] = (1, 0, 0, 0)
     assert same(port.entity_uniforms(trs), ref.entity_uniforms(trs))
+
+
+def test_uniform_blocks_as_shipped(port, ref):
+    """Row 2 of section 8(f), pinned through the reference's own objects: the reference tier reads the 80 / 288 / 208-byte
+    blocks back from the (headless) GPU buffers that RenderEntity / RenderView / RenderLight flush into."""
+    assert ref.uniform_sizes() == port.uniform_sizes() == (80, 288, 208)
+    rng = np.random.default_rng(31)
+    trs = util.random_trs(rng, 2000)
+    blocks = ref.entity_uniform_blocks(trs)                                  # RenderEntity::setTransform + getResources
+    assert same(blocks, ref.entity_uniforms(trs)) and same(blocks, port.entity_uniform_blocks(trs))
+    for v in list(util.random_views(rng, 200)) + [scenes.default_camera(), scenes.cubes_scene()["view"]]:
+        pos = rng.integers(0, 1000, 2)
+        assert port.view_uniforms(v, pos).tobytes() == ref.view_uniforms(v, pos).tobytes()
+    lights = np.concatenate([util.random_lights(rng, 1500), scenes.cubes_scene()["lights"]])
+    for l in lights:
+        att = rng.uniform(0, 1, 3).astype(np.float32)
+        bias = float(np.float32(rng.uniform(-0.01, 0)))
+        assert port.light_uniforms(l, att, bias).tobytes() == ref.light_uniforms(l, att, bias).tobytes()

@@ -119,3 +119,31 @@ def gpu_entity_uniforms(world, visible=None, cap=None):
     torch.cuda.synchronize()
     assert bool((out[cap] == -7.0).all())
     return out[:cap].cpu().numpy()
+
+
+def gpu_light_uniforms(world, visible=None, cap=None):
+    """ovis_pack_light_uniforms_device -> (cap, 208) uint8 blocks (rows past the list are untouched 0x55 filler)."""
+    import torch
+    n_lights = world.counts()[2]
+    cap = cap if cap is not None else max(n_lights if visible is None else len(visible), 1)
+    out = torch.full((cap + 1, 208), 0x55, dtype=torch.uint8, device="cuda")
+    if visible is None:
+        world.pack_light_uniforms_device(out.data_ptr(), cap)
+    else:
+        vis = torch.from_numpy(np.ascontiguousarray(visible, dtype=np.uint32).view(np.int32)).cuda()
+        vcnt = torch.tensor([len(visible)], dtype=torch.int32, device="cuda")
+        world.pack_light_uniforms_device(out.data_ptr(), cap, vis.data_ptr() if len(visible) else out.data_ptr(), vcnt.data_ptr(),
+                                         len(visible))
+    torch.cuda.synchronize()
+    assert bool((out[cap] == 0x55).all())
+    return out[:cap].cpu().numpy()
+
+
+def gpu_view_uniforms(world, views, viewport_pos=None):
+    import torch
+    views = np.ascontiguousarray(views, dtype=scenes.VIEW_DTYPE).reshape(-1)
+    out = torch.full((len(views) + 1, 288), 0x55, dtype=torch.uint8, device="cuda")
+    world.pack_view_uniforms_device(views, out.data_ptr(), viewport_pos)
+    torch.cuda.synchronize()
+    assert bool((out[len(views)] == 0x55).all())
+    return out[:len(views)].cpu().numpy()
