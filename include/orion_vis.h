@@ -351,6 +351,53 @@ int ovis_pack_light_uniforms_device(OvisWorld *world, const uint32_t *d_visible,
 int ovis_pack_view_uniforms_device(OvisWorld *world, int32_t n_views, const OvisView *views, const int32_t *viewport_pos,
                                    void *d_uniforms);
 
+/* ------------------------------------------------------------------------------------------------
+ * Scene import: the reference's on-disk formats, read into a world.
+ * Host-side parsing; everything it creates goes through the calls above.
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct OvisSceneInfo {
+    uint32_t first_node, first_entity, first_light;   /* ids of what the import created (consecutive from these) */
+    int32_t  n_nodes;                                 /* one per Entity that is active in the world */
+    int64_t  n_entities;                              /* one per sub-mesh of every active MeshRenderer, one per Skybox */
+    int32_t  n_lights;
+    int32_t  n_cameras;
+    int32_t  shadow_map_resolution;                   /* of the first camera's DeferredRenderPipeline, 0 if none */
+} OvisSceneInfo;
+/* Load a serialised world (`.object`: the JSON array engine/src/json_serialiser.cc writes; World -> root Entity,
+ * engine/src/world.cc:56-71; Entity properties, components, children, engine/src/entity.cc:106-148) and create, in the
+ * reference's activation order (entity.cc:414-421: an entity's components, then its children, depth first; inactive
+ * entities and components are skipped as they never reach the render world):
+ *   - one transform node per Entity (local position / orientation / scale; the root keeps the identity, entity.cc:127-130);
+ *   - one render entity per sub-mesh of each MeshRenderer (graphics/src/mesh_renderer.cc:50-59,129-134; local AABB from
+ *     the .obj, see ovis_obj_submesh_aabbs) and one per Skybox (+-FLT_MAX, graphics/src/skybox.cc:46-54), bound to the
+ *     Entity's node, flags from castsShadow (graphics/src/renderer.cc:70-85);
+ *   - one light per Ambient/Directional/Point/SpotLight with the component defaults of graphics/src/light.cc:35-74, world
+ *     position and direction from the Entity's world transform at import time (light.cc:100-108; lights do not follow
+ *     later node moves - call ovis_light_update), attenuation and shadow bias via ovis_light_set_shading;
+ *   - one OvisView per Camera (graphics/src/camera.cc:46-57,71-79) with the given viewport size, returned in
+ *     out_cameras (up to cap_cameras; OVIS_ERR_CAPACITY if there are more, the world is still complete).
+ * Mesh assets "game/<path>" resolve to <game_asset_dir>/<path>.obj. Physics, controllers and post effects are ignored. */
+int ovis_scene_import(OvisWorld *world, const char *world_path, const char *game_asset_dir, int32_t vp_width,
+                      int32_t vp_height, int32_t cap_cameras, OvisView *out_cameras, OvisSceneInfo *out_info);
+/* The same in two steps, for hosts that want the parsed arrays (or have no device yet): ovis_scene_load parses into a
+ * host-side OvisScene (needs no GPU), ovis_scene_info / ovis_scene_arrays read it (node parent indices and entity->node
+ * indices are relative to the scene; light_shading = attenuation[3] + shadow bias per light; any output may be NULL; sizes
+ * from ovis_scene_info), ovis_scene_instantiate creates its content in a world, ovis_scene_free releases it. */
+typedef struct OvisScene OvisScene;
+int ovis_scene_load(const char *world_path, const char *game_asset_dir, int32_t vp_width, int32_t vp_height, OvisScene **out_scene);
+int ovis_scene_info(const OvisScene *scene, OvisSceneInfo *out_info);
+int ovis_scene_arrays(const OvisScene *scene, int32_t *out_parent, float *out_local_trs, float *out_local_aabb, uint32_t *out_flags,
+                      uint32_t *out_entity_node, OvisLight *out_lights, float *out_light_shading, OvisView *out_cameras);
+int ovis_scene_instantiate(const OvisScene *scene, OvisWorld *world, OvisSceneInfo *out_info);
+int ovis_scene_free(OvisScene *scene);
+/* Local bounding box of every sub-mesh of a Wavefront .obj file, as OBJLoader + MeshLoader::calculateBoundingBox produce
+ * them (engine/src/loaders/obj_loader.cc:94-279: a sub-mesh starts at the first face after a `usemtl` that changes the
+ * material or after any `g`; values parsed with strtof; engine/src/loaders/mesh_loader.cc:187-199: min/max over the
+ * positions the sub-mesh's faces reference). 6 floats per sub-mesh. */
+int ovis_obj_submesh_aabbs(const char *obj_path, int32_t capacity, float *out_aabb, int32_t *out_count);
+/* Read a light back: its OvisLight, attenuation[3] and shadow bias (any output may be NULL). */
+int ovis_light_get(OvisWorld *world, uint32_t light_id, OvisLight *out_light, float out_attenuation[3], float *out_shadow_bias);
+
 /* Copy `bytes` from a device pointer this library handed out (e.g. the CSR arrays of
  * ovis_cull_views_device) to host memory, after all work queued on the world's stream; for ABI users
  * that bind no CUDA runtime of their own (cgo, ctypes). No counterpart in the reference (its results are

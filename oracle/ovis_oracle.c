@@ -679,3 +679,8 @@ void orc_light_uniforms(const OrcLight *l, const float attenuation[3], float sha
         }
     }
 }
+
+void orc_quat_rotate(const float q[4], const float v[3], float out[3]) {
+    v3 r = q_rotate(Q(q[0], q[1], q[2], q[3]), V3(v[0], v[1], v[2]));
+    out[0] = r.x; out[1] = r.y; out[2] = r.z;
+}

@@ -109,6 +109,9 @@ void orc_entity_uniforms(int64_t n, const float *world_trs, float *out20);
 /* The same blocks read back from the uniform buffer of a RenderEntity after setTransform + getResources (the reference
  * tier goes through UniformBuffer::flush into the headless GPU buffer; the port fills the bytes itself). 80 B each. */
 void orc_entity_uniform_blocks(int64_t n, const float *world_trs, void *out80);
+/* glm quat (w x y z) * vec3, glm/gtc/quaternion.inl:313-321 - how a Light gets its world direction from its entity's
+ * world orientation (graphics/src/light.cc:105). */
+void orc_quat_rotate(const float q[4], const float v[3], float out[3]);
 /* sizeof(EntityUniforms), sizeof(ViewUniforms), sizeof(LightUniforms): 80, 288, 208. */
 void orc_uniform_sizes(int32_t out[3]);
 /* ViewUniforms (render/include/render_view.h:28-36) of a view whose viewport starts at viewport_pos: 288 bytes =

@@ -211,6 +211,12 @@ class Oracle:
         self.lib.orc_entity_uniforms(C.c_int64(len(world_trs)), _p(world_trs), _p(out))
         return out
 
+    def quat_rotate(self, q, v) -> np.ndarray:
+        q, v = _f32(q, (4,)), _f32(v, (3,))
+        out = np.zeros(3, dtype=np.float32)
+        self.lib.orc_quat_rotate(_p(q), _p(v), _p(out))
+        return out
+
     def uniform_sizes(self):
         out = np.zeros(3, dtype=np.int32)
         self.lib.orc_uniform_sizes(_p(out))

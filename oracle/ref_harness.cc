@@ -513,6 +513,12 @@ static void readUniformBlock(GPUResourceSet *set, void *out, size_t size) {
     buffer->unmap();
 }
 
+/* glm quat * vec3 (Light::transformed, graphics/src/light.cc:105; Light::direction :93) */
+void orc_quat_rotate(const float q[4], const float v[3], float out[3]) {
+    glm::vec3 r = qt(q) * v3(v);
+    memcpy(out, &r, 12);
+}
+
 void orc_uniform_sizes(int32_t out[3]) {
     out[0] = (int32_t)sizeof(EntityUniforms);
     out[1] = (int32_t)sizeof(ViewUniforms);

@@ -370,5 +370,35 @@ inline void lightUniforms(const OvisLight &l, const float attenuation[3], float 
     }
 }
 
+// Entity::transformed (engine/src/entity.cc:382-411): world TRS of a child from its parent's world TRS. quat * vec3 is
+// glm/gtc/quaternion.inl:313-321, quat * quat :256-270 (left-to-right sums, no renormalisation).
+struct Trs {
+    Vec3 p;
+    Quat q;
+    Vec3 s;
+};
+inline Vec3 rotate(Quat q, Vec3 v) {
+    Vec3 u = { q.x, q.y, q.z };
+    Vec3 uv = cross(u, v);
+    Vec3 uuv = cross(u, uv);
+    return v + ((uv * q.w) + uuv) * 2.0f;
+}
+inline Quat mul(Quat p, Quat q) {
+    Quat r;
+    r.w = p.w * q.w - p.x * q.x - p.y * q.y - p.z * q.z;
+    r.x = p.w * q.x + p.x * q.w + p.y * q.z - p.z * q.y;
+    r.y = p.w * q.y + p.y * q.w + p.z * q.x - p.x * q.z;
+    r.z = p.w * q.z + p.z * q.w + p.x * q.y - p.y * q.x;
+    return r;
+}
+inline Trs composeTrs(const Trs &parent, const Trs &local) {
+    Trs w;
+    Vec3 scaled = { parent.s.x * local.p.x, parent.s.y * local.p.y, parent.s.z * local.p.z };
+    w.p = rotate(parent.q, scaled) + parent.p;                                            // entity.cc:394
+    w.q = mul(parent.q, local.q);                                                         // :395
+    w.s = { parent.s.x * local.s.x, parent.s.y * local.s.y, parent.s.z * local.s.z };     // :396
+    return w;
+}
+
 }  // namespace hm
 }  // namespace ovis

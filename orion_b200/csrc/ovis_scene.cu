@@ -1,0 +1,702 @@
+// ovis_scene.cu - scene import: the reference's on-disk formats on the input side of the
+// path, read straight into a device-resident world.
+//
+//   .object world   JSON array of serialised objects (engine/src/json_serialiser.cc). World -> root Entity
+//                   (engine/src/world.cc:56-71), Entity -> properties, components, children (engine/src/entity.cc:
+//                   106-148). Only what reaches the render world is interpreted: Entity transforms and activity,
+//                   MeshRenderer / Skybox (graphics/src/renderer.cc:70-85, mesh_renderer.cc:50-59, skybox.cc:46-54),
+//                   the four Light classes (graphics/src/light.cc:35-119) and Camera (graphics/src/camera.cc:71-79).
+//   .obj mesh       per sub-mesh local bounding boxes exactly as OBJLoader + MeshLoader::calculateBoundingBox produce
+//                   them (engine/src/loaders/obj_loader.cc:94-279, mesh_loader.cc:187-199).
+//
+// Host code: parsing is a one-off, pointer-chasing job; the result is handed to the world through the same calls an
+// application would make (ovis_node_add, ovis_entity_add, ovis_node_bind_entities, ovis_light_add), so everything
+// downstream - transforms, bounds, culls - runs on the device as for any other world.
+#include "orion_vis.h"
+
+#include "ovis_math.hpp"
+
+#include <cfloat>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <map>
+#include <memory>
+#include <string>
+#include <unordered_map>
+#include <vector>
+
+namespace ovis {
+int report_error(int code, const char *message);   // ovis_world.cu: sets ovis_last_error(), returns code
+}
+
+namespace {
+
+int scene_error(int code, const char *fmt, ...) {
+    char buf[1024];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    return ovis::report_error(code, buf);
+}
+
+// ---- minimal JSON (RFC 8259 values; numbers through strtod, as rapidjson's default double path yields) -----------
+
+struct Json {
+    enum Kind { Null, Bool, Number, String, Array, Object } kind = Null;
+    bool b = false;
+    double num = 0.0;
+    std::string str;
+    std::vector<Json> items;                                    // Array
+    std::vector<std::pair<std::string, Json>> members;          // Object, in file order
+
+    const Json *get(const char *key) const {
+        for (const auto &m : members)
+            if (m.first == key)
+                return &m.second;
+        return nullptr;
+    }
+};
+
+struct JsonParser {
+    const char *p, *end;
+    std::string error;
+
+    void skip() {
+        while (p < end && (*p == ' ' || *p == '\t' || *p == '\n' || *p == '\r'))
+            p++;
+    }
+    bool fail(const char *what) {
+        if (error.empty())
+            error = what;
+        return false;
+    }
+    bool parseString(std::string &out) {
+        if (p >= end || *p != '"')
+            return fail("expected string");
+        p++;
+        while (p < end && *p != '"') {
+            if (*p == '\\') {
+                if (++p >= end)
+                    return fail("bad escape");
+                switch (*p) {
+                case 'n': out += '\n'; break;
+                case 't': out += '\t'; break;
+                case 'r': out += '\r'; break;
+                case 'b': out += '\b'; break;
+                case 'f': out += '\f'; break;
+                case 'u': {                                     // names and asset paths are ASCII; keep the low byte
+                    if (end - p < 5)
+                        return fail("bad \\u escape");
+                    char hex[5] = { p[1], p[2], p[3], p[4], 0 };
+                    out += (char)strtoul(hex, nullptr, 16);
+                    p += 4;
+                    break;
+                }
+                default: out += *p; break;                      // \" \\ \/
+                }
+                p++;
+            } else {
+                out += *p++;
+            }
+        }
+        if (p >= end)
+            return fail("unterminated string");
+        p++;
+        return true;
+    }
+    bool parse(Json &v, int depth = 0) {
+        if (depth > 64)
+            return fail("nesting too deep");
+        skip();
+        if (p >= end)
+            return fail("unexpected end of file");
+        if (*p == '{') {
+            v.kind = Json::Object;
+            p++;
+            skip();
+            if (p < end && *p == '}') { p++; return true; }
+            for (;;) {
+                skip();
+                std::string key;
+                if (!parseString(key))
+                    return false;
+                skip();
+                if (p >= end || *p != ':')
+                    return fail("expected ':'");
+                p++;
+                v.members.emplace_back(std::move(key), Json());
+                if (!parse(v.members.back().second, depth + 1))
+                    return false;
+                skip();
+                if (p < end && *p == ',') { p++; continue; }
+                if (p < end && *p == '}') { p++; return true; }
+                return fail("expected ',' or '}'");
+            }
+        }
+        if (*p == '[') {
+            v.kind = Json::Array;
+            p++;
+            skip();
+            if (p < end && *p == ']') { p++; return true; }
+            for (;;) {
+                v.items.emplace_back();
+                if (!parse(v.items.back(), depth + 1))
+                    return false;
+                skip();
+                if (p < end && *p == ',') { p++; continue; }
+                if (p < end && *p == ']') { p++; return true; }
+                return fail("expected ',' or ']'");
+            }
+        }
+        if (*p == '"') {
+            v.kind = Json::String;
+            return parseString(v.str);
+        }
+        if (end - p >= 4 && !strncmp(p, "true", 4)) { v.kind = Json::Bool; v.b = true; p += 4; return true; }
+        if (end - p >= 5 && !strncmp(p, "false", 5)) { v.kind = Json::Bool; v.b = false; p += 5; return true; }
+        if (end - p >= 4 && !strncmp(p, "null", 4)) { v.kind = Json::Null; p += 4; return true; }
+        char *stop = nullptr;
+        v.num = strtod(p, &stop);
+        if (stop == p)
+            return fail("unexpected character");
+        v.kind = Json::Number;
+        p = stop;
+        return true;
+    }
+};
+
+bool read_file(const char *path, std::string &out) {
+    FILE *f = fopen(path, "rb");
+    if (!f)
+        return false;
+    char buf[1 << 16];
+    size_t n;
+    while ((n = fread(buf, 1, sizeof buf, f)) > 0)
+        out.append(buf, n);
+    fclose(f);
+    return true;
+}
+
+// ---- OBJ sub-mesh bounding boxes --------------------------------------------------------------------------------
+
+// String::tokenize(line, tokens, delimiters) with the default trimEmpty = true (core/src/string.cc)
+void tokenize(const std::string &s, const char *delims, bool trim_empty, std::vector<std::string> &out) {
+    size_t last = 0;
+    while (last <= s.size()) {
+        size_t pos = s.find_first_of(delims, last);
+        if (pos == std::string::npos)
+            pos = s.size();
+        if (pos != last || !trim_empty)
+            out.emplace_back(s, last, pos - last);
+        last = pos + 1;
+    }
+}
+
+struct SubMeshBox {
+    float box[6];
+};
+
+// obj_loader.cc:94-152 (line dispatch), :158-181 (vertex elements), :187-278 (faces), mesh_loader.cc:187-199 (box).
+int parse_obj(const char *path, std::vector<SubMeshBox> &out, std::string &error) {
+    std::string text;
+    if (!read_file(path, text)) {
+        error = std::string("cannot read ") + path;
+        return OVIS_ERR_INVALID;
+    }
+    std::vector<ovis::hm::Vec3> positions;
+    size_t n_texcoords = 0, n_normals = 0;
+    std::string current_material = "default";
+    int current = -1;                                            // index into `out`, -1 = begin a new sub-mesh at the next face
+    size_t line_no = 0, start = 0;
+    auto bad = [&](const char *what) {
+        error = std::string(path) + ": " + std::to_string(line_no) + ": " + what;
+        return OVIS_ERR_INVALID;
+    };
+    while (start < text.size()) {
+        size_t nl = text.find('\n', start);
+        if (nl == std::string::npos)
+            nl = text.size();
+        std::string line(text, start, nl - start);
+        start = nl + 1;
+        line_no++;
+        std::vector<std::string> tok;
+        tokenize(line, " \r", true, tok);
+        if (tok.empty())
+            continue;
+        if (tok[0] == "v" || tok[0] == "vt" || tok[0] == "vn") {
+            const size_t want = tok[0] == "vt" ? 2 : 3;
+            if (tok.size() < want + 1)
+                return bad("too few values");
+            float val[3] = { 0, 0, 0 };
+            for (size_t i = 0; i < want; i++) {
+                const char *str = tok[i + 1].c_str();
+                char *stop = nullptr;
+                val[i] = strtof(str, &stop);                     // :170
+                if (stop != str + tok[i + 1].size())
+                    return bad("expected float value");
+            }
+            if (tok[0] == "v")
+                positions.push_back({ val[0], val[1], val[2] });
+            else if (tok[0] == "vt")
+                n_texcoords++;
+            else
+                n_normals++;
+        } else if (tok[0] == "f") {
+            const size_t nv = tok.size() - 1;
+            if (nv != 3 && nv != 4)
+                return bad("expected 3 or 4 vertices");
+            if (current < 0) {                                   // :188-192
+                out.push_back({ { FLT_MAX, FLT_MAX, FLT_MAX, -FLT_MAX, -FLT_MAX, -FLT_MAX } });   // mesh_loader.cc:188
+                current = (int)out.size() - 1;
+            }
+            for (size_t i = 0; i < nv; i++) {
+                std::vector<std::string> sub;
+                tokenize(tok[i + 1], "/", false, sub);
+                if (sub.size() != 3)
+                    return bad("expected v/vt/vn");
+                size_t idx[3];
+                for (int j = 0; j < 3; j++) {
+                    const char *str = sub[j].c_str();
+                    char *stop = nullptr;
+                    uint16_t value = (uint16_t)strtoul(str, &stop, 10);       // :220 (16-bit, as the reference)
+                    if (stop != str + sub[j].size())
+                        return bad("expected integer value");
+                    value -= 1;
+                    idx[j] = value;
+                }
+                // :229-248 reject an index beyond its array; the position test is strict here (the reference's `>` would
+                // let index == size read past the end of the array)
+                if (idx[0] >= positions.size())
+                    return bad("invalid position index");
+                if (idx[1] > n_texcoords)
+                    return bad("invalid texture coordinate index");
+                if (idx[2] > n_normals)
+                    return bad("invalid normal index");
+                const ovis::hm::Vec3 &p = positions[idx[0]];
+                float *b = out[(size_t)current].box;             // glm::min(minimum, position), glm::max(maximum, position)
+                b[0] = ovis::hm::glmMin(b[0], p.x); b[1] = ovis::hm::glmMin(b[1], p.y); b[2] = ovis::hm::glmMin(b[2], p.z);
+                b[3] = ovis::hm::glmMax(b[3], p.x); b[4] = ovis::hm::glmMax(b[4], p.y); b[5] = ovis::hm::glmMax(b[5], p.z);
+            }
+        } else if (tok[0] == "usemtl") {
+            if (tok.size() != 2)
+                return bad("expected single material name");
+            if (tok[1] != current_material) {                    // :123-127
+                current_material = tok[1];
+                current = -1;
+            }
+        } else if (tok[0] == "g") {
+            if (tok.size() != 2)
+                return bad("expected single group name");
+            current = -1;                                        // :139
+        }
+    }
+    return OVIS_OK;
+}
+
+}  // namespace
+
+extern "C" int ovis_obj_submesh_aabbs(const char *obj_path, int32_t capacity, float *out_aabb, int32_t *out_count) {
+    if (!obj_path || capacity < 0 || (capacity > 0 && !out_aabb) || !out_count)
+        return scene_error(OVIS_ERR_INVALID, "ovis_obj_submesh_aabbs: bad arguments");
+    std::vector<SubMeshBox> boxes;
+    std::string error;
+    int rc = parse_obj(obj_path, boxes, error);
+    if (rc != OVIS_OK)
+        return scene_error(rc, "%s", error.c_str());
+    *out_count = (int32_t)boxes.size();
+    if ((int32_t)boxes.size() > capacity)
+        return scene_error(OVIS_ERR_CAPACITY, "%s has %zu sub-meshes, buffer holds %d", obj_path, boxes.size(), capacity);
+    for (size_t i = 0; i < boxes.size(); i++)
+        std::memcpy(out_aabb + 6 * i, boxes[i].box, sizeof boxes[i].box);
+    return OVIS_OK;
+}
+
+// ---- .object world ----------------------------------------------------------------------------------------------
+
+namespace {
+
+using ovis::hm::Quat;
+using ovis::hm::Trs;
+using ovis::hm::Vec3;
+
+struct SceneObjects {
+    Json root;
+    std::unordered_map<long long, const Json *> by_id;
+};
+
+const Json *props(const Json &o) { return o.get("objectProperties"); }
+
+bool prop_bool(const Json &o, const char *name, bool fallback) {
+    const Json *p = props(o);
+    const Json *v = p ? p->get(name) : nullptr;
+    return (v && v->kind == Json::Bool) ? v->b : fallback;
+}
+
+float prop_float(const Json &o, const char *name, float fallback) {
+    const Json *p = props(o);
+    const Json *v = p ? p->get(name) : nullptr;
+    return (v && v->kind == Json::Number) ? (float)v->num : fallback;   // double -> float, as the serialiser's read<float>
+}
+
+bool prop_floats(const Json &o, const char *name, int n, float *out) {
+    const Json *p = props(o);
+    const Json *v = p ? p->get(name) : nullptr;
+    if (!v || v->kind != Json::Array || (int)v->items.size() != n)
+        return false;
+    for (int i = 0; i < n; i++)
+        out[i] = (float)v->items[(size_t)i].num;
+    return true;
+}
+
+long long ref_id(const Json *ref) {                               // {"objectID": n}; {} is a null reference
+    const Json *id = ref ? ref->get("objectID") : nullptr;
+    return (id && id->kind == Json::Number) ? (long long)id->num : -1;
+}
+
+struct Importer {
+    OvisWorld *world;                                             // unused by the walk
+    const SceneObjects &scene;
+    std::string game_dir;
+    int vp_width, vp_height;
+    std::map<std::string, std::vector<SubMeshBox>> meshes;       // parsed .obj files by asset path
+    std::string error;
+
+    // what the walk collects, in activation order (entity.cc:414-421: own components, then children, depth first)
+    std::vector<int32_t> node_parent;
+    std::vector<float> node_trs;                                  // 10 per node, local
+    std::vector<Trs> node_world;
+    std::vector<float> ent_aabb;                                  // 6 per render entity, local
+    std::vector<uint32_t> ent_flags, ent_node;
+    std::vector<OvisLight> lights;
+    std::vector<float> light_shading;                             // attenuation[3], bias per light
+    std::vector<OvisView> cameras;
+    int shadow_map_resolution = 0;
+
+    bool fail(const std::string &what) {
+        if (error.empty())
+            error = what;
+        return false;
+    }
+
+    const std::vector<SubMeshBox> *mesh(const std::string &asset) {
+        auto it = meshes.find(asset);
+        if (it != meshes.end())
+            return &it->second;
+        // asset paths are "<search path>/<file without extension>"; the game's own assets live under "game/"
+        if (asset.compare(0, 5, "game/") != 0) {
+            fail("mesh asset '" + asset + "' is outside the game asset directory");
+            return nullptr;
+        }
+        std::string path = game_dir + "/" + asset.substr(5) + ".obj";
+        std::vector<SubMeshBox> boxes;
+        std::string why;
+        if (parse_obj(path.c_str(), boxes, why) != OVIS_OK) {
+            fail(why);
+            return nullptr;
+        }
+        if (boxes.empty()) {
+            fail(path + " has no faces");
+            return nullptr;
+        }
+        return &meshes.emplace(asset, std::move(boxes)).first->second;
+    }
+
+    bool component(const Json &c, uint32_t node, const Trs &world_trs) {
+        if (!prop_bool(c, "active", false))                      // component.cc:29,104: inactive components never activate
+            return true;
+        const Json *cls = c.get("objectClass");
+        const std::string name = cls ? cls->str : "";
+        if (name == "MeshRenderer" || name == "Skybox") {
+            const uint32_t flags = prop_bool(c, "castsShadow", true) ? OVIS_CASTS_SHADOW : 0u;   // renderer.cc:32,80
+            if (name == "Skybox") {                              // skybox.cc:50-51
+                const float box[6] = { -FLT_MAX, -FLT_MAX, -FLT_MAX, FLT_MAX, FLT_MAX, FLT_MAX };
+                ent_aabb.insert(ent_aabb.end(), box, box + 6);
+                ent_flags.push_back(flags);
+                ent_node.push_back(node);
+                return true;
+            }
+            const Json *p = props(c);
+            const Json *m = p ? p->get("mesh") : nullptr;
+            const Json *asset = m ? m->get("asset") : nullptr;
+            if (!asset || asset->kind != Json::String)
+                return fail("MeshRenderer without a mesh asset");
+            const std::vector<SubMeshBox> *boxes = mesh(asset->str);
+            if (!boxes)
+                return false;
+            for (const SubMeshBox &b : *boxes) {                 // one RenderEntity per sub-mesh, mesh_renderer.cc:129-134
+                ent_aabb.insert(ent_aabb.end(), b.box, b.box + 6);
+                ent_flags.push_back(flags);
+                ent_node.push_back(node);
+            }
+            return true;
+        }
+        int type = -1;
+        if (name == "AmbientLight") type = OVIS_LIGHT_AMBIENT;
+        else if (name == "DirectionalLight") type = OVIS_LIGHT_DIRECTIONAL;
+        else if (name == "PointLight") type = OVIS_LIGHT_POINT;
+        else if (name == "SpotLight") type = OVIS_LIGHT_SPOT;
+        if (type >= 0) {
+            OvisLight l;
+            std::memset(&l, 0, sizeof l);
+            l.type = type;
+            l.flags = prop_bool(c, "castsShadows", false) ? OVIS_CASTS_SHADOW : 0u;          // light.cc:43
+            float colour[3] = { 1.0f, 1.0f, 1.0f };                                          // light.cc:39
+            prop_floats(c, "colour", 3, colour);
+            std::memcpy(l.colour, colour, sizeof colour);
+            l.intensity = prop_float(c, "intensity", 0.8f);                                  // light.cc:40
+            float att[3] = { 0.0f, 0.0f, 0.0f };
+            if (type == OVIS_LIGHT_POINT) {                                                  // light.cc:58-64
+                l.range = prop_float(c, "range", 100.0f);
+                att[0] = 1.0f; att[1] = 0.045f; att[2] = 0.0075f;
+            } else if (type == OVIS_LIGHT_SPOT) {                                            // light.cc:67-74
+                l.range = prop_float(c, "range", 50.0f);
+                att[0] = 1.0f; att[1] = 0.09f; att[2] = 0.032f;
+                l.cutoff = prop_float(c, "cutoff", 20.0f);
+                if (l.cutoff > 45.0f)
+                    return fail("spot light cutoff must be <= 45 degrees");
+            }
+            prop_floats(c, "attenuation", 3, att);
+            // Light::transformed (light.cc:100-108): absolute direction and position from the entity's world transform
+            Vec3 d = ovis::hm::rotate(world_trs.q, Vec3{ 0.0f, 0.0f, -1.0f });
+            l.direction[0] = d.x; l.direction[1] = d.y; l.direction[2] = d.z;
+            l.position[0] = world_trs.p.x; l.position[1] = world_trs.p.y; l.position[2] = world_trs.p.z;
+            lights.push_back(l);
+            light_shading.insert(light_shading.end(), att, att + 3);
+            light_shading.push_back(prop_float(c, "shadowBiasConstant", -0.001f));
+            return true;
+        }
+        if (name == "Camera") {                                                              // camera.cc:46-57,71-79
+            OvisView v;
+            std::memset(&v, 0, sizeof v);
+            v.position[0] = world_trs.p.x; v.position[1] = world_trs.p.y; v.position[2] = world_trs.p.z;
+            v.orientation[0] = world_trs.q.w; v.orientation[1] = world_trs.q.x;
+            v.orientation[2] = world_trs.q.y; v.orientation[3] = world_trs.q.z;
+            v.hfov_deg = prop_float(c, "fov", 75.0f);
+            v.znear = prop_float(c, "zNear", 0.1f);
+            v.zfar = prop_float(c, "zFar", 1000.0f);
+            v.vp_width = vp_width;
+            v.vp_height = vp_height;
+            cameras.push_back(v);
+            const Json *p = props(c);
+            const Json *pipe = scene_object(ref_id(p ? p->get("renderPipeline") : nullptr));
+            if (pipe && !shadow_map_resolution)
+                shadow_map_resolution = (int)prop_float(*pipe, "shadowMapResolution", 0.0f);
+            return true;
+        }
+        return true;                                              // physics, controllers, post effects: not on the path
+    }
+
+    const Json *scene_object(long long id) const {
+        auto it = scene.by_id.find(id);
+        return it == scene.by_id.end() ? nullptr : it->second;
+    }
+
+    // Entity::activated order; `parent_node` < 0 for the root.
+    bool entity(const Json &e, int32_t parent_node, const Trs *parent_world, int depth) {
+        if (depth > 4096)
+            return fail("entity tree too deep (cycle?)");
+        Trs local = { { 0.0f, 0.0f, 0.0f }, { 1.0f, 0.0f, 0.0f, 0.0f }, { 1.0f, 1.0f, 1.0f } };
+        if (parent_node >= 0) {                                   // the root's properties are not deserialised, entity.cc:127-130
+            if (!prop_bool(e, "active", false))
+                return true;                                      // inactive entity: nothing below it is active in the world
+            float v[4];
+            if (prop_floats(e, "position", 3, v)) local.p = { v[0], v[1], v[2] };
+            if (prop_floats(e, "orientation", 4, v)) local.q = { v[0], v[1], v[2], v[3] };
+            if (prop_floats(e, "scale", 3, v)) local.s = { v[0], v[1], v[2] };
+        }
+        const Trs world_trs = parent_world ? ovis::hm::composeTrs(*parent_world, local) : local;
+        const uint32_t node = (uint32_t)node_parent.size();
+        node_parent.push_back(parent_node);
+        const float trs[10] = { local.p.x, local.p.y, local.p.z, local.q.w, local.q.x, local.q.y, local.q.z,
+                                local.s.x, local.s.y, local.s.z };
+        node_trs.insert(node_trs.end(), trs, trs + 10);
+        node_world.push_back(world_trs);
+        if (const Json *comps = e.get("components"))
+            for (const Json &ref : comps->items) {
+                const Json *c = scene_object(ref_id(&ref));
+                if (!c)
+                    return fail("dangling component reference");
+                if (!component(*c, node, world_trs))
+                    return false;
+            }
+        if (const Json *kids = e.get("children"))
+            for (const Json &ref : kids->items) {
+                const Json *k = scene_object(ref_id(&ref));
+                if (!k)
+                    return fail("dangling child reference");
+                if (!entity(*k, (int32_t)node, &world_trs, depth + 1))
+                    return false;
+            }
+        return true;
+    }
+};
+
+}  // namespace
+
+struct OvisScene {
+    std::vector<int32_t> node_parent;
+    std::vector<float> node_trs, ent_aabb, light_shading;
+    std::vector<uint32_t> ent_flags, ent_node;
+    std::vector<OvisLight> lights;
+    std::vector<OvisView> cameras;
+    int shadow_map_resolution = 0;
+};
+
+static void fill_info(const OvisScene &sc, OvisSceneInfo *info) {
+    std::memset(info, 0, sizeof *info);
+    info->n_nodes = (int32_t)sc.node_parent.size();
+    info->n_entities = (int64_t)sc.ent_flags.size();
+    info->n_lights = (int32_t)sc.lights.size();
+    info->n_cameras = (int32_t)sc.cameras.size();
+    info->shadow_map_resolution = sc.shadow_map_resolution;
+}
+
+extern "C" {
+
+int ovis_scene_load(const char *world_path, const char *game_asset_dir, int32_t vp_width, int32_t vp_height, OvisScene **out_scene) {
+    if (!world_path || !game_asset_dir || vp_width < 1 || vp_height < 1 || !out_scene)
+        return scene_error(OVIS_ERR_INVALID, "ovis_scene_load: bad arguments");
+    *out_scene = nullptr;
+    std::string text;
+    if (!read_file(world_path, text))
+        return scene_error(OVIS_ERR_INVALID, "ovis_scene_load: cannot read %s", world_path);
+    SceneObjects scene;
+    JsonParser parser{ text.data(), text.data() + text.size(), {} };
+    if (!parser.parse(scene.root) || scene.root.kind != Json::Array)
+        return scene_error(OVIS_ERR_INVALID, "%s: not a serialised object file (%s)", world_path,
+                           parser.error.empty() ? "top level is not an array" : parser.error.c_str());
+    const Json *world_object = nullptr;
+    for (const Json &o : scene.root.items) {
+        const Json *id = o.kind == Json::Object ? o.get("objectID") : nullptr;
+        if (!id || id->kind != Json::Number)
+            return scene_error(OVIS_ERR_INVALID, "%s: object without an objectID", world_path);
+        scene.by_id[(long long)id->num] = &o;
+        const Json *cls = o.get("objectClass");
+        if (!world_object && cls && cls->str == "World")          // the primary object of a world asset
+            world_object = &o;
+    }
+    if (!world_object)
+        return scene_error(OVIS_ERR_INVALID, "%s: no World object", world_path);
+    Importer imp{ nullptr, scene, game_asset_dir, vp_width, vp_height };
+    const Json *root = imp.scene_object(ref_id(world_object->get("root")));   // world.cc:60-61
+    if (!root)
+        return scene_error(OVIS_ERR_INVALID, "%s: the World has no root entity", world_path);
+    if (!imp.entity(*root, -1, nullptr, 0))
+        return scene_error(OVIS_ERR_INVALID, "%s: %s", world_path, imp.error.c_str());
+    OvisScene *sc = new OvisScene;
+    sc->node_parent = std::move(imp.node_parent);
+    sc->node_trs = std::move(imp.node_trs);
+    sc->ent_aabb = std::move(imp.ent_aabb);
+    sc->ent_flags = std::move(imp.ent_flags);
+    sc->ent_node = std::move(imp.ent_node);
+    sc->lights = std::move(imp.lights);
+    sc->light_shading = std::move(imp.light_shading);
+    sc->cameras = std::move(imp.cameras);
+    sc->shadow_map_resolution = imp.shadow_map_resolution;
+    *out_scene = sc;
+    return OVIS_OK;
+}
+
+int ovis_scene_free(OvisScene *scene) {
+    delete scene;
+    return OVIS_OK;
+}
+
+int ovis_scene_info(const OvisScene *scene, OvisSceneInfo *out_info) {
+    if (!scene || !out_info)
+        return scene_error(OVIS_ERR_INVALID, "ovis_scene_info: null argument");
+    fill_info(*scene, out_info);
+    return OVIS_OK;
+}
+
+int ovis_scene_arrays(const OvisScene *scene, int32_t *out_parent, float *out_local_trs, float *out_local_aabb, uint32_t *out_flags,
+                      uint32_t *out_entity_node, OvisLight *out_lights, float *out_light_shading, OvisView *out_cameras) {
+    if (!scene)
+        return scene_error(OVIS_ERR_INVALID, "ovis_scene_arrays: null scene");
+    auto copy = [](void *dst, const void *src, size_t bytes) {
+        if (dst && bytes)
+            std::memcpy(dst, src, bytes);
+    };
+    copy(out_parent, scene->node_parent.data(), scene->node_parent.size() * 4);
+    copy(out_local_trs, scene->node_trs.data(), scene->node_trs.size() * 4);
+    copy(out_local_aabb, scene->ent_aabb.data(), scene->ent_aabb.size() * 4);
+    copy(out_flags, scene->ent_flags.data(), scene->ent_flags.size() * 4);
+    copy(out_entity_node, scene->ent_node.data(), scene->ent_node.size() * 4);
+    copy(out_lights, scene->lights.data(), scene->lights.size() * sizeof(OvisLight));
+    copy(out_light_shading, scene->light_shading.data(), scene->light_shading.size() * 4);
+    copy(out_cameras, scene->cameras.data(), scene->cameras.size() * sizeof(OvisView));
+    return OVIS_OK;
+}
+
+int ovis_scene_instantiate(const OvisScene *scene, OvisWorld *world, OvisSceneInfo *out_info) {
+    if (!scene || !world)
+        return scene_error(OVIS_ERR_INVALID, "ovis_scene_instantiate: null argument");
+    OvisSceneInfo info;
+    fill_info(*scene, &info);
+    int64_t have_entities = 0, have_nodes = 0;
+    int32_t have_lights = 0;
+    int rc = ovis_world_counts(world, &have_entities, &have_nodes, &have_lights);
+    if (rc != OVIS_OK)
+        return rc;
+    std::vector<int32_t> parent = scene->node_parent;             // recorded as indices into the scene: make them world ids
+    std::vector<uint32_t> ent_node = scene->ent_node;
+    if (have_nodes > 0) {
+        for (int32_t &p : parent)
+            if (p >= 0)
+                p += (int32_t)have_nodes;
+        for (uint32_t &n : ent_node)
+            n += (uint32_t)have_nodes;
+    }
+    rc = ovis_node_add(world, info.n_nodes, parent.data(), scene->node_trs.data(), &info.first_node);
+    if (rc != OVIS_OK)
+        return rc;
+    if (info.n_entities > 0) {
+        rc = ovis_entity_add(world, info.n_entities, scene->ent_aabb.data(), scene->ent_flags.data(), &info.first_entity);
+        if (rc != OVIS_OK)
+            return rc;
+        std::vector<uint32_t> ids((size_t)info.n_entities);
+        for (size_t i = 0; i < ids.size(); i++)
+            ids[i] = info.first_entity + (uint32_t)i;
+        rc = ovis_node_bind_entities(world, info.n_entities, ent_node.data(), ids.data());
+        if (rc != OVIS_OK)
+            return rc;
+    }
+    if (info.n_lights > 0) {
+        rc = ovis_light_add(world, info.n_lights, scene->lights.data(), &info.first_light);
+        if (rc != OVIS_OK)
+            return rc;
+        for (int32_t i = 0; i < info.n_lights; i++) {
+            rc = ovis_light_set_shading(world, info.first_light + (uint32_t)i, &scene->light_shading[4 * (size_t)i],
+                                        scene->light_shading[4 * (size_t)i + 3]);
+            if (rc != OVIS_OK)
+                return rc;
+        }
+    }
+    if (out_info)
+        *out_info = info;
+    return OVIS_OK;
+}
+
+int ovis_scene_import(OvisWorld *world, const char *world_path, const char *game_asset_dir, int32_t vp_width,
+                      int32_t vp_height, int32_t cap_cameras, OvisView *out_cameras, OvisSceneInfo *out_info) {
+    if (!world || cap_cameras < 0 || (cap_cameras > 0 && !out_cameras) || !out_info)
+        return scene_error(OVIS_ERR_INVALID, "ovis_scene_import: bad arguments");
+    OvisScene *scene = nullptr;
+    int rc = ovis_scene_load(world_path, game_asset_dir, vp_width, vp_height, &scene);
+    if (rc != OVIS_OK)
+        return rc;
+    std::unique_ptr<OvisScene> owner(scene);
+    rc = ovis_scene_instantiate(scene, world, out_info);
+    if (rc != OVIS_OK)
+        return rc;
+    for (int32_t i = 0; i < out_info->n_cameras && i < cap_cameras; i++)
+        out_cameras[i] = scene->cameras[(size_t)i];
+    if (out_info->n_cameras > cap_cameras)
+        return scene_error(OVIS_ERR_CAPACITY, "%s has %d cameras, buffer holds %d", world_path, out_info->n_cameras, cap_cameras);
+    return OVIS_OK;
+}
+
+}  // extern "C"

@@ -1299,6 +1299,18 @@ int ovis_light_set_shading(OvisWorld *w, uint32_t id, const float attenuation[3]
     return OVIS_OK;
 }
 
+int ovis_light_get(OvisWorld *w, uint32_t id, OvisLight *out_light, float out_attenuation[3], float *out_shadow_bias) {
+    if (!w || id >= w->lights.size() || !w->light_alive[id])
+        return fail(OVIS_ERR_INVALID, "ovis_light_get: unknown light %u", id);
+    if (out_light)
+        *out_light = w->lights[id];
+    if (out_attenuation)
+        std::memcpy(out_attenuation, w->light_shading[id].attenuation, 12);
+    if (out_shadow_bias)
+        *out_shadow_bias = w->light_shading[id].shadow_bias;
+    return OVIS_OK;
+}
+
 int ovis_light_remove(OvisWorld *w, uint32_t id) {
     if (!w || id >= w->lights.size() || !w->light_alive[id])
         return fail(OVIS_ERR_INVALID, "ovis_light_remove: unknown light %u", id);

@@ -122,6 +122,47 @@ def light_uniforms(light: np.ndarray, attenuation=(1.0, 0.045, 0.0075), shadow_b
     return out
 
 
+def obj_submesh_aabbs(path: str) -> np.ndarray:
+    """Local AABB of every sub-mesh of a Wavefront .obj (host-side parsing; no device needed)."""
+    cap = 64
+    while True:
+        out = np.zeros((cap, 6), dtype=np.float32)
+        n = C.c_int32()
+        rc = load().ovis_obj_submesh_aabbs(os.fsencode(path), C.c_int32(cap), _p(out), C.byref(n))
+        if rc == OVIS_ERR_CAPACITY:
+            cap = n.value
+            continue
+        _check(rc)
+        return out[:n.value].copy()
+
+
+class SceneInfo(C.Structure):
+    _fields_ = [("first_node", C.c_uint32), ("first_entity", C.c_uint32), ("first_light", C.c_uint32),
+                ("n_nodes", C.c_int32), ("n_entities", C.c_int64), ("n_lights", C.c_int32), ("n_cameras", C.c_int32),
+                ("shadow_map_resolution", C.c_int32)]
+
+
+def load_scene(world_path: str, game_asset_dir: str, vp_width: int, vp_height: int) -> dict:
+    """ovis_scene_load + ovis_scene_arrays: the parsed render-world content of a serialised world (host only)."""
+    lib = load()
+    h = C.c_void_p()
+    _check(lib.ovis_scene_load(os.fsencode(world_path), os.fsencode(game_asset_dir), C.c_int32(vp_width), C.c_int32(vp_height),
+                               C.byref(h)))
+    try:
+        info = SceneInfo()
+        _check(lib.ovis_scene_info(h, C.byref(info)))
+        out = {"parent": np.zeros(info.n_nodes, dtype=np.int32), "local_trs": np.zeros((info.n_nodes, 10), dtype=np.float32),
+               "local_aabb": np.zeros((info.n_entities, 6), dtype=np.float32), "flags": np.zeros(info.n_entities, dtype=np.uint32),
+               "entity_node": np.zeros(info.n_entities, dtype=np.uint32), "lights": np.zeros(info.n_lights, dtype=LIGHT_DTYPE),
+               "shading": np.zeros((info.n_lights, 4), dtype=np.float32), "cameras": np.zeros(info.n_cameras, dtype=VIEW_DTYPE),
+               "shadow_map_resolution": info.shadow_map_resolution}
+        _check(lib.ovis_scene_arrays(h, _p(out["parent"]), _p(out["local_trs"]), _p(out["local_aabb"]), _p(out["flags"]),
+                                     _p(out["entity_node"]), _p(out["lights"]), _p(out["shading"]), _p(out["cameras"])))
+        return out
+    finally:
+        lib.ovis_scene_free(h)
+
+
 def light_shadow_views(light: np.ndarray, resolution: int = 512) -> np.ndarray:
     light = np.ascontiguousarray(light, dtype=LIGHT_DTYPE)
     out = np.zeros(6, dtype=VIEW_DTYPE)
@@ -462,6 +503,22 @@ class World:
         _check(self.lib.ovis_pack_entity_uniforms_device(self.h, C.c_void_p(d_visible or None),
                                                          C.c_void_p(d_visible_count or None), C.c_int64(max_visible),
                                                          C.c_void_p(d_uniforms or None), C.c_int64(capacity)))
+
+    def import_scene(self, world_path: str, game_asset_dir: str, vp_width: int, vp_height: int, max_cameras: int = 16):
+        """ovis_scene_import -> (SceneInfo, cameras as a VIEW_DTYPE array)."""
+        info = SceneInfo()
+        cams = np.zeros(max_cameras, dtype=VIEW_DTYPE)
+        _check(self.lib.ovis_scene_import(self.h, os.fsencode(world_path), os.fsencode(game_asset_dir), C.c_int32(vp_width),
+                                          C.c_int32(vp_height), C.c_int32(max_cameras), _p(cams), C.byref(info)))
+        return info, cams[:info.n_cameras].copy()
+
+    def light(self, light_id: int):
+        """(OvisLight record, attenuation[3], shadow bias) of a light."""
+        l = np.zeros(1, dtype=LIGHT_DTYPE)
+        att = np.zeros(3, dtype=np.float32)
+        bias = C.c_float()
+        _check(self.lib.ovis_light_get(self.h, C.c_uint32(light_id), _p(l), _p(att), C.byref(bias)))
+        return l[0], att, np.float32(bias.value)
 
     def set_light_shading(self, light_id, attenuation, shadow_bias):
         att = np.asarray(attenuation, dtype=np.float32)
