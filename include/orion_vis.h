@@ -352,6 +352,41 @@ int ovis_pack_view_uniforms_device(OvisWorld *world, int32_t n_views, const Ovis
                                    void *d_uniforms);
 
 /* ------------------------------------------------------------------------------------------------
+ * Deferred light pass and colour post effects over headless device buffers:
+ * the arithmetic of the reference's shaders as CUDA kernels. The graphics API that rasterises the G-buffer
+ * and the shadow maps is unavailable on this box: the caller supplies them as plain device arrays.
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct OvisGBuffer {            /* row-major, width x height, device pointers, 16-byte aligned */
+    int32_t width, height;
+    const float *d_buffer_a;            /* 4 floats per pixel: world normal encoded n * 0.5 + 0.5 (lit_deferred_frag.glsl), a unused */
+    const float *d_buffer_b;            /* 4 floats per pixel: diffuse rgb, a unused */
+    const float *d_buffer_c;            /* 4 floats per pixel: specular rgb, shininess */
+    const float *d_depth;               /* 1 float per pixel: depth buffer value 0..1 */
+} OvisGBuffer;                          /* the reference stores these as R10G10B10A2 / fp16 / Depth32 (deferred_render_pipeline.h:51-54) */
+/* engine/shaders/deferred_light_frag.glsl:30-81 + engine/shaders/lighting.h:46-211 for every light of a visible-light
+ * list, summed per pixel in list order as the additive light passes of DeferredRenderPipeline::renderDeferredLights would
+ * (render/src/deferred_render_pipeline.cc:424-470; target cleared to (0,0,0,1), alpha = source alpha = 1): one kernel, one
+ * G-buffer read and one write per pixel whatever the number of lights. Light parameters come from the world's per-light
+ * LightUniforms table (ovis_light_uniforms), the light type selects the shader variant. d_view_uniforms: the 288-byte
+ * ViewUniforms block of the view the G-buffer was rendered from, in device memory (ovis_pack_view_uniforms_device).
+ * d_visible_lights / count / max as for ovis_pack_light_uniforms_device (NULL = the last ovis_cull's light list).
+ * d_shadow_maps: NULL (no light is shadowed: the shader variants without SHADOW), or a device array indexed by light id
+ * of device pointers to that light's shadow map - shadow_size^2 floats for a spot light, 6 x shadow_size^2 (faces +x -x
+ * +y -y +z -z) for a point light, NULL for an unshadowed light; sampled like the pipeline's sampler (bilinear, compare
+ * Less, clamp: render/src/deferred_render_pipeline.cc:250-254) with the 3x3 PCF of lighting.h. d_out_rgba: 4 floats per
+ * pixel. Asynchronous on the world's stream. */
+int ovis_shade_deferred_device(OvisWorld *world, const OvisGBuffer *gbuffer, const void *d_view_uniforms,
+                               const uint32_t *d_visible_lights, const uint32_t *d_visible_count, int64_t max_visible,
+                               const float *const *d_shadow_maps, int32_t shadow_size, float *d_out_rgba);
+enum { OVIS_POST_TONEMAP = 1u, OVIS_POST_GAMMA = 2u };
+/* engine/shaders/tonemap_effect_frag.glsl:30-71 (Uncharted 2 operator; parameters exposure, whitePoint) and / or
+ * engine/shaders/gamma_correction_effect_frag.glsl:26-31 (pow(rgb, 1 / gamma)) over n_pixels rgba float4 values; with
+ * both bits set the two effects run fused in one pass, tonemap first (the order of the cubes demo's effect chain).
+ * d_out_rgba may equal d_rgba. */
+int ovis_post_effects_device(OvisWorld *world, int64_t n_pixels, const float *d_rgba, uint32_t effects, float exposure,
+                             float white_point, float gamma, float *d_out_rgba);
+
+/* ------------------------------------------------------------------------------------------------
  * Scene import: the reference's on-disk formats, read into a world.
  * Host-side parsing; everything it creates goes through the calls above.
  * ---------------------------------------------------------------------------------------------- */

@@ -1,0 +1,216 @@
+/*
+ * oracle/glsl_harness.cc - TEST INFRASTRUCTURE. Runs the reference's own shader SOURCE on the CPU: the GLSL files under
+ * /root/reference/engine/shaders are (after the mechanical rewrite below) valid C++ against GLM, the vector library the
+ * reference vendors, so the arithmetic of the deferred light pass and the two colour post effects is the reference's
+ * text, not a restatement. Only built into oracle/_ref/liborion_ref.so, where /root/reference exists.
+ *
+ * The Makefile writes rewritten copies of lighting.h, deferred_light_frag.glsl, tonemap_effect_frag.glsl and
+ * gamma_correction_effect_frag.glsl into oracle/_ref/glsl/ (git-ignored build output; the sources are read in place):
+ *   1.25        -> 1.25f               a GLSL literal is a float, a C++ one a double
+ *   v.xyz / .rgb / .xy -> vec3(v) / vec2(v)   GLM's truncating constructors instead of swizzles
+ *   (out LightingData data) -> (LightingData &data)
+ *   the `in vec4 gl_FragCoord;` redeclaration is dropped (the built-in lives in this file)
+ * Everything else GLSL-specific is supplied here: the uniform blocks, samplers and built-ins the shaders name. What the
+ * shaders leave to fixed-function hardware - texel fetch, the shadow samplers' compare-and-filter - is NOT reference code:
+ * it calls the same definitions oracle/ovis_shading.c states (and exports for that purpose).
+ */
+#include <glm/glm.hpp>
+
+#include <cstdint>
+#include <cstring>
+
+#include "ovis_oracle.h"
+
+extern "C" {
+/* the sampler definitions shared with the C restatement (oracle/ovis_shading.c) */
+float orc_shadow_lookup_2d(const float *map, int size, float u, float v, float ref);
+float orc_shadow_lookup_cube(const float *map, int size, float x, float y, float z, float ref);
+}
+
+namespace glsl {
+
+using namespace glm;
+
+/* GLSL lets an int meet a float vector; GLM's templates do not deduce that */
+inline vec3 operator*(const vec3 &v, int s) { return v * (float)s; }
+
+struct LightBlock {                    /* render/include/render_light.h:33-47 */
+    vec3 position; float intensity;
+    vec3 direction; float cosCutoff;
+    vec3 colour; float range;
+    mat4 volumeTransform;
+    mat4 shadowSpace;
+    float shadowZNear, attenuationConstant, attenuationLinear, attenuationExp, shadowBiasConstant;
+};
+struct ViewBlock {                     /* render/include/render_view.h:28-36; the ivec2 members as the float GLSL converts them to */
+    mat4 view, projection, viewProjection, inverseViewProjection;
+    vec2 viewportPosition, viewportSize;
+    vec3 position;
+};
+
+static thread_local LightBlock light;
+static thread_local ViewBlock view;
+static thread_local vec4 gl_FragCoord;
+
+struct sampler2D { const float *data; int width, height; };
+struct sampler2DShadow { const float *map; int size; };
+struct samplerCubeShadow { const float *map; int size; };
+
+inline vec4 texelFetch(const sampler2D &s, ivec2 uv, int) {
+    const float *p = s.data + 4 * ((size_t)uv.y * s.width + uv.x);
+    return vec4(p[0], p[1], p[2], p[3]);
+}
+inline vec2 textureSize(const sampler2DShadow &s, int) { return vec2((float)s.size, (float)s.size); }
+inline vec2 textureSize(const samplerCubeShadow &s, int) { return vec2((float)s.size, (float)s.size); }
+inline vec2 textureSize(const sampler2D &s, int) { return vec2((float)s.width, (float)s.height); }
+inline float texture(const sampler2DShadow &s, vec3 p) { return s.map ? orc_shadow_lookup_2d(s.map, s.size, p.x, p.y, p.z) : 1.0f; }
+inline float texture(const samplerCubeShadow &s, vec4 p) { return s.map ? orc_shadow_lookup_cube(s.map, s.size, p.x, p.y, p.z, p.w) : 1.0f; }
+/* post effects sample the source at the pixel's own texel (nearest): gl_FragCoord.xy / size * size */
+inline vec4 texture(const sampler2D &s, vec2 uv) {
+    ivec2 t((int)(uv.x * (float)s.width), (int)(uv.y * (float)s.height));
+    return texelFetch(s, t, 0);
+}
+
+static thread_local sampler2D deferredBufferA, deferredBufferB, deferredBufferC, deferredBufferD, sourceTexture;
+static thread_local float exposure, whitePoint, gamma;
+
+#define layout(...)
+#define uniform
+#define in
+#define out
+#define main shader_main
+
+/* one namespace per shader variant (the engine compiles one per light type, with and without SHADOW) */
+namespace ambient {
+#define AMBIENT_LIGHT
+#include "_ref/glsl/deferred_light_frag.glsl"
+#undef AMBIENT_LIGHT
+#undef __LIGHTING_H
+}
+namespace directional {
+#define DIRECTIONAL_LIGHT
+#include "_ref/glsl/deferred_light_frag.glsl"
+#undef DIRECTIONAL_LIGHT
+#undef __LIGHTING_H
+}
+namespace point {
+#define POINT_LIGHT
+#include "_ref/glsl/deferred_light_frag.glsl"
+#undef __LIGHTING_H
+}
+namespace point_shadow {
+#define SHADOW
+#include "_ref/glsl/deferred_light_frag.glsl"
+#undef SHADOW
+#undef POINT_LIGHT
+#undef __LIGHTING_H
+}
+namespace spot {
+#define SPOT_LIGHT
+#include "_ref/glsl/deferred_light_frag.glsl"
+#undef __LIGHTING_H
+}
+namespace spot_shadow {
+#define SHADOW
+#include "_ref/glsl/deferred_light_frag.glsl"
+#undef SHADOW
+#undef SPOT_LIGHT
+#undef __LIGHTING_H
+}
+namespace tonemap {
+#include "_ref/glsl/tonemap_effect_frag.glsl"
+#undef __POST_EFFECT_H
+}
+namespace gamma_correction {
+#include "_ref/glsl/gamma_correction_effect_frag.glsl"
+#undef __POST_EFFECT_H
+}
+
+#undef layout
+#undef uniform
+#undef in
+#undef out
+#undef main
+
+}  // namespace glsl
+
+extern "C" {
+
+/* Same contract as orc_shade_deferred; every pixel runs the reference's main() of the variant for each light. */
+void orc_glsl_shade_deferred(int32_t width, int32_t height, const float *buffer_a, const float *buffer_b, const float *buffer_c,
+                             const float *depth, const void *view_uniforms, int32_t n_lights, const float *light_uniforms,
+                             const int32_t *light_types, const float *const *shadow_maps, int32_t shadow_size, float *out_rgba) {
+    using namespace glsl;
+    const float *vf = (const float *)view_uniforms;
+    const int32_t *vi = (const int32_t *)view_uniforms;
+    memcpy(&view.view, vf, 256);
+    view.viewportPosition = vec2((float)vi[64], (float)vi[65]);
+    view.viewportSize = vec2((float)vi[66], (float)vi[67]);
+    view.position = vec3(vf[68], vf[69], vf[70]);
+    /* the depth copy is a one-channel image: present it as the r channel of a 4-channel fetch */
+    float *depth4 = new float[(size_t)width * height * 4]();
+    for (size_t i = 0; i < (size_t)width * height; i++)
+        depth4[4 * i] = depth[i];
+    deferredBufferA = { buffer_a, width, height };
+    deferredBufferB = { buffer_b, width, height };
+    deferredBufferC = { buffer_c, width, height };
+    deferredBufferD = { depth4, width, height };
+    for (int32_t py = 0; py < height; py++)
+        for (int32_t px = 0; px < width; px++) {
+            gl_FragCoord = vec4((float)px, (float)py, 0.0f, 1.0f);     /* pixel_center_integer */
+            vec3 sum(0.0f);
+            for (int32_t l = 0; l < n_lights; l++) {
+                const float *lf = light_uniforms + 52 * (size_t)l;
+                memcpy(&light.position, lf, 12); light.intensity = lf[3];
+                memcpy(&light.direction, lf + 4, 12); light.cosCutoff = lf[7];
+                memcpy(&light.colour, lf + 8, 12); light.range = lf[11];
+                memcpy(&light.volumeTransform, lf + 12, 64);
+                memcpy(&light.shadowSpace, lf + 28, 64);
+                light.shadowZNear = lf[44]; light.attenuationConstant = lf[45]; light.attenuationLinear = lf[46];
+                light.attenuationExp = lf[47]; light.shadowBiasConstant = lf[48];
+                const float *map = shadow_maps ? shadow_maps[l] : nullptr;
+                vec4 colour;
+                switch (light_types[l]) {
+                case ORC_LIGHT_AMBIENT: ambient::shader_main(); colour = ambient::fragColour; break;
+                case ORC_LIGHT_DIRECTIONAL: directional::shader_main(); colour = directional::fragColour; break;
+                case ORC_LIGHT_POINT:
+                    if (map) { point_shadow::shadowMap = { map, shadow_size }; point_shadow::shader_main(); colour = point_shadow::fragColour; }
+                    else { point::shader_main(); colour = point::fragColour; }
+                    break;
+                default:
+                    if (map) { spot_shadow::shadowMap = { map, shadow_size }; spot_shadow::shader_main(); colour = spot_shadow::fragColour; }
+                    else { spot::shader_main(); colour = spot::fragColour; }
+                    break;
+                }
+                sum = sum + vec3(colour);                              /* additive blend, one pass per light */
+            }
+            float *o = out_rgba + 4 * ((size_t)py * width + px);
+            o[0] = sum.x; o[1] = sum.y; o[2] = sum.z; o[3] = 1.0f;
+        }
+    delete[] depth4;
+}
+
+void orc_glsl_tonemap(int64_t n_pixels, const float *rgba, float exposure_, float white_point, float *out_rgba) {
+    using namespace glsl;
+    glsl::exposure = exposure_;
+    glsl::whitePoint = white_point;
+    sourceTexture = { rgba, (int)n_pixels, 1 };
+    for (int64_t i = 0; i < n_pixels; i++) {
+        gl_FragCoord = vec4((float)i + 0.5f, 0.5f, 0.0f, 1.0f);       /* default pixel centres */
+        tonemap::shader_main();
+        memcpy(out_rgba + 4 * i, &tonemap::fragColour, 16);
+    }
+}
+
+void orc_glsl_gamma(int64_t n_pixels, const float *rgba, float gamma_, float *out_rgba) {
+    using namespace glsl;
+    glsl::gamma = gamma_;
+    sourceTexture = { rgba, (int)n_pixels, 1 };
+    for (int64_t i = 0; i < n_pixels; i++) {
+        gl_FragCoord = vec4((float)i + 0.5f, 0.5f, 0.0f, 1.0f);
+        gamma_correction::shader_main();
+        memcpy(out_rgba + 4 * i, &gamma_correction::fragColour, 16);
+    }
+}
+
+}  /* extern "C" */

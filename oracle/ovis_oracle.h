@@ -127,6 +127,20 @@ void orc_light_uniforms(const OrcLight *light, const float attenuation[3], float
 
 const char *orc_name(void);   /* "port" or "reference" */
 
+/* ---- deferred light shading and colour post effects (section 8(f) row 4) - oracle/ovis_shading.c, which states what is
+ * restated from the GLSL and what this oracle has to define itself. Buffers are row-major, width x height:
+ *   buffer_a/b/c  4 floats per pixel: encoded normal (n * 0.5 + 0.5) | diffuse rgb | specular rgb + shininess
+ *   depth         1 float per pixel (0..1)
+ *   view_uniforms the 288-byte ViewUniforms block; light_uniforms n_lights x 52 floats (LightUniforms blocks);
+ *   light_types   ORC_LIGHT_* per light (the reference compiles one shader variant per type);
+ *   shadow_maps   NULL, or per light NULL / a depth image: shadow_size^2 floats (spot) or 6 x shadow_size^2 (point).
+ * out_rgba: 4 floats per pixel - the sum of the lights' contributions in list order, alpha 1. */
+void orc_shade_deferred(int32_t width, int32_t height, const float *buffer_a, const float *buffer_b, const float *buffer_c,
+                        const float *depth, const void *view_uniforms, int32_t n_lights, const float *light_uniforms,
+                        const int32_t *light_types, const float *const *shadow_maps, int32_t shadow_size, float *out_rgba);
+void orc_tonemap(int64_t n_pixels, const float *rgba, float exposure, float white_point, float *out_rgba);
+void orc_gamma(int64_t n_pixels, const float *rgba, float gamma, float *out_rgba);
+
 #ifdef __cplusplus
 }
 #endif

@@ -243,6 +243,47 @@ class Oracle:
         self.lib.orc_light_uniforms(_p(light), _p(att), C.c_float(shadow_bias), _p(out))
         return out
 
+    # ---- deferred shading and post effects (section 8(f) row 4)
+    def shade_deferred(self, buffer_a, buffer_b, buffer_c, depth, view_uniforms, light_uniforms, light_types,
+                       shadow_maps=None, shadow_size=0, glsl=False):
+        """Sum of the lights' contributions per pixel -> (h, w, 4) float32. glsl=True runs the reference's shader source
+        compiled against GLM (reference tier only) instead of the C restatement."""
+        h, w = depth.shape
+        a, b, c = (_f32(x, (h, w, 4)) for x in (buffer_a, buffer_b, buffer_c))
+        depth = _f32(depth, (h, w))
+        vu = np.ascontiguousarray(view_uniforms, dtype=np.uint8).reshape(288)
+        lu = np.ascontiguousarray(light_uniforms).view(np.float32).reshape(-1, 52)
+        types = np.ascontiguousarray(light_types, dtype=np.int32).reshape(-1)
+        assert len(types) == len(lu)
+        maps = None
+        keep = []
+        if shadow_maps is not None:
+            maps = (C.c_void_p * len(lu))()
+            for i, m in enumerate(shadow_maps):
+                if m is not None:
+                    m = np.ascontiguousarray(m, dtype=np.float32)
+                    keep.append(m)
+                    maps[i] = m.ctypes.data
+        out = np.zeros((h, w, 4), dtype=np.float32)
+        fn = self.lib.orc_glsl_shade_deferred if glsl else self.lib.orc_shade_deferred
+        fn(C.c_int32(w), C.c_int32(h), _p(a), _p(b), _p(c), _p(depth), _p(vu), C.c_int32(len(lu)), _p(lu), _p(types), maps,
+           C.c_int32(shadow_size), _p(out))
+        return out
+
+    def tonemap(self, rgba, exposure, white_point, glsl=False):
+        rgba = _f32(rgba, (-1, 4))
+        out = np.zeros_like(rgba)
+        fn = self.lib.orc_glsl_tonemap if glsl else self.lib.orc_tonemap
+        fn(C.c_int64(len(rgba)), _p(rgba), C.c_float(exposure), C.c_float(white_point), _p(out))
+        return out
+
+    def gamma(self, rgba, gamma, glsl=False):
+        rgba = _f32(rgba, (-1, 4))
+        out = np.zeros_like(rgba)
+        fn = self.lib.orc_glsl_gamma if glsl else self.lib.orc_gamma
+        fn(C.c_int64(len(rgba)), _p(rgba), C.c_float(gamma), _p(out))
+        return out
+
     # ---- tier A object world (reference build only)
     def world(self) -> "RefWorld":
         assert self.has_world, "object world exists only in the reference-compiled oracle"

@@ -146,6 +146,25 @@ void launch_entity_uniforms(const UniformArgs &a, int64_t max_visible, cudaStrea
 void launch_light_uniforms(const uint32_t *d_visible, const uint32_t *d_visible_count, const float *d_table, float *d_out,
                            int64_t max_visible, int64_t capacity, cudaStream_t s);
 
+// ---- deferred shading over headless buffers (section 8(f) row 4) ----------------------------------------------------
+struct ShadeArgs {
+    int width, height;
+    const float *buffer_a, *buffer_b, *buffer_c;   // float4 per pixel
+    const float *depth;                            // float per pixel
+    const float *view_uniforms;                    // 72 floats (ViewUniforms block), device
+    const uint32_t *d_visible;                     // light ids, list order
+    const uint32_t *d_visible_count;
+    int64_t max_visible;
+    const float *light_table;                      // 52 floats per light slot
+    const int32_t *light_types;                    // OVIS_LIGHT_* per light slot
+    const float *const *shadow_maps;               // per light slot: depth image or NULL; NULL = no shadows at all
+    int shadow_size;
+    float *out_rgba;                               // float4 per pixel
+};
+void launch_shade_deferred(const ShadeArgs &a, cudaStream_t s);
+void launch_post_effects(int64_t n_pixels, const float *in, uint32_t effects, float exposure, float white_point, float gamma, float *out,
+                         cudaStream_t s);
+
 enum : uint32_t { kLightNever = 0, kLightAlways = 1, kLightSphere = 2, kLightBox = 3 };
 
 struct DeviceLight {

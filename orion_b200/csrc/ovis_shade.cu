@@ -1,0 +1,261 @@
+// ovis_shade.cu - the deferred light pass and the colour post effects over headless buffers.
+//
+//   shade_deferred_kernel  engine/shaders/deferred_light_frag.glsl:30-81 (G-buffer decode, position from depth) and
+//                          engine/shaders/lighting.h:46-211 (3x3 PCF shadows, Blinn-Phong, attenuation, spot cone) for
+//                          EVERY visible light of a pixel in one pass: the reference rasterises one additive pass per
+//                          light (render/src/deferred_render_pipeline.cc:424-470), re-reading the G-buffer and
+//                          read-modify-writing the HDR target each time; here a pixel's G-buffer sample is decoded once,
+//                          the lights' contributions are summed in registers in list order (the order the blend unit
+//                          would add them) and the pixel is written once.
+//   post_effects_kernel    tonemap_effect_frag.glsl:30-71 (Uncharted 2) and gamma_correction_effect_frag.glsl:26-31,
+//                          optionally fused (the reference runs them as two full-screen passes).
+//
+// Arithmetic: fp32, operations in the shader's source order, IEEE division and square root, no FMA (the library is built
+// with -fmad=false), GLM's association for mat4 * vec4 - i.e. the definition oracle/ovis_shading.c states, which is
+// bit-identical to the reference's shader source compiled against GLM. The one deviation is powf (CUDA's is accurate to
+// a few ulp, not correctly rounded): specular and gamma terms carry that, everything else is exact.
+// The light loop is uniform across a CTA (every thread shades the same light at the same time), so the per-type branches
+// of the reference's shader variants do not diverge; light blocks are staged through shared memory in chunks.
+#include "ovis_kernels.h"
+
+#include "orion_vis.h"
+
+namespace ovis {
+
+namespace {
+
+struct F3 {
+    float x, y, z;
+};
+__device__ __forceinline__ F3 f3(float x, float y, float z) { return { x, y, z }; }
+__device__ __forceinline__ F3 operator+(F3 a, F3 b) { return { a.x + b.x, a.y + b.y, a.z + b.z }; }
+__device__ __forceinline__ F3 operator-(F3 a, F3 b) { return { a.x - b.x, a.y - b.y, a.z - b.z }; }
+__device__ __forceinline__ F3 operator*(F3 a, F3 b) { return { a.x * b.x, a.y * b.y, a.z * b.z }; }
+__device__ __forceinline__ F3 operator*(F3 a, float s) { return { a.x * s, a.y * s, a.z * s }; }
+__device__ __forceinline__ float dot3(F3 a, F3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+__device__ __forceinline__ float length3(F3 a) { return sqrtf(dot3(a, a)); }
+__device__ __forceinline__ F3 normalize3(F3 a) { return a * (1.0f / length3(a)); }
+__device__ __forceinline__ float max_glsl(float a, float b) { return a > b ? a : b; }
+__device__ __forceinline__ float clamp_glsl(float x, float lo, float hi) { return fminf(fmaxf(x, lo), hi); }
+
+// (c0 v0 + c1 v1) + (c2 v2 + c3 v3), row r of a column-major mat4
+__device__ __forceinline__ float mat_row(const float *m, int r, float v0, float v1, float v2, float v3) {
+    return (m[0 + r] * v0 + m[4 + r] * v1) + (m[8 + r] * v2 + m[12 + r] * v3);
+}
+
+enum { L_POSITION = 0, L_INTENSITY = 3, L_DIRECTION = 4, L_COS_CUTOFF = 7, L_COLOUR = 8, L_RANGE = 11, L_SHADOW_SPACE = 28,
+       L_SHADOW_ZNEAR = 44, L_ATT_CONSTANT = 45, L_ATT_LINEAR = 46, L_ATT_EXP = 47, L_SHADOW_BIAS = 48, L_FLOATS = 52 };
+enum { V_INVERSE_VP = 48, V_VIEWPORT_POS = 64, V_VIEWPORT_SIZE = 66, V_POSITION = 68, V_FLOATS = 72 };
+
+// texture(sampler2DShadow, vec3(u, v, ref)): bilinear, compare Less, clamp to edge
+__device__ __forceinline__ float shadow_lookup_2d(const float *__restrict__ map, int size, float u, float v, float ref) {
+    ref = clamp_glsl(ref, 0.0f, 1.0f);
+    const float x = u * (float)size - 0.5f, y = v * (float)size - 0.5f;
+    const float fx0 = floorf(x), fy0 = floorf(y);
+    const float wx = x - fx0, wy = y - fy0;
+    int x0 = (int)fx0, y0 = (int)fy0, x1 = x0 + 1, y1 = y0 + 1;
+    x0 = min(max(x0, 0), size - 1); x1 = min(max(x1, 0), size - 1);
+    y0 = min(max(y0, 0), size - 1); y1 = min(max(y1, 0), size - 1);
+    const float c00 = ref < __ldg(map + (size_t)y0 * size + x0) ? 1.0f : 0.0f, c10 = ref < __ldg(map + (size_t)y0 * size + x1) ? 1.0f : 0.0f;
+    const float c01 = ref < __ldg(map + (size_t)y1 * size + x0) ? 1.0f : 0.0f, c11 = ref < __ldg(map + (size_t)y1 * size + x1) ? 1.0f : 0.0f;
+    const float top = c00 * (1.0f - wx) + c10 * wx, bottom = c01 * (1.0f - wx) + c11 * wx;
+    return top * (1.0f - wy) + bottom * wy;
+}
+
+// texture(samplerCubeShadow, vec4(d, ref)): GL major-axis face selection, faces +x -x +y -y +z -z
+__device__ __forceinline__ float shadow_lookup_cube(const float *__restrict__ map, int size, F3 d, float ref) {
+    const float ax = fabsf(d.x), ay = fabsf(d.y), az = fabsf(d.z);
+    float sc, tc, ma;
+    int face;
+    if (ax >= ay && ax >= az) { face = d.x >= 0.0f ? 0 : 1; ma = ax; sc = d.x >= 0.0f ? -d.z : d.z; tc = -d.y; }
+    else if (ay >= az)         { face = d.y >= 0.0f ? 2 : 3; ma = ay; sc = d.x; tc = d.y >= 0.0f ? d.z : -d.z; }
+    else                       { face = d.z >= 0.0f ? 4 : 5; ma = az; sc = d.z >= 0.0f ? d.x : -d.x; tc = -d.y; }
+    const float s = (sc / ma + 1.0f) * 0.5f, t = (tc / ma + 1.0f) * 0.5f;
+    return shadow_lookup_2d(map + (size_t)face * size * size, size, s, t, ref);
+}
+
+struct Lighting {
+    F3 normal, position, diffuse, specular;
+    float shininess;
+};
+
+// lighting.h:46-143
+__device__ __forceinline__ float calc_shadow(const Lighting &d, const float *light, int type, const float *map, int size) {
+    if (!map)
+        return 1.0f;
+    if (type == OVIS_LIGHT_SPOT) {
+        const float *m = light + L_SHADOW_SPACE;
+        const float sx = mat_row(m, 0, d.position.x, d.position.y, d.position.z, 1.0f);
+        const float sy = mat_row(m, 1, d.position.x, d.position.y, d.position.z, 1.0f);
+        const float sz = mat_row(m, 2, d.position.x, d.position.y, d.position.z, 1.0f);
+        const float sw = mat_row(m, 3, d.position.x, d.position.y, d.position.z, 1.0f);
+        const float u = sx / sw, v = sy / sw;
+        float depth = sz / sw;
+        depth += light[L_SHADOW_BIAS];
+        float shadow = 0.0f;
+        const float texel = 1.0f / (float)size;
+        for (int x = -1; x <= 1; x++)
+            for (int y = -1; y <= 1; y++)
+                shadow += shadow_lookup_2d(map, size, u + (float)x * texel, v + (float)y * texel, depth);
+        return shadow / 9.0f;
+    }
+    if (type == OVIS_LIGHT_POINT) {
+        const F3 direction = d.position - f3(light[0], light[1], light[2]);
+        const float ax = fabsf(direction.x), ay = fabsf(direction.y), az = fabsf(direction.z);
+        float local_depth;
+        F3 oa, ob;
+        if (ax >= ay && ax >= az) { local_depth = ax; oa = f3(0, 1, 0); ob = f3(0, 0, 1); }
+        else if (ay >= ax && ay >= az) { local_depth = ay; oa = f3(1, 0, 0); ob = f3(0, 0, 1); }
+        else { local_depth = az; oa = f3(1, 0, 0); ob = f3(0, 1, 0); }
+        const float far = light[L_RANGE], near = light[L_SHADOW_ZNEAR];
+        const float depth = -(far / (near - far)) - ((far * near) / (far - near) / local_depth);
+        const float texel = 1.0f / (float)size;
+        oa = (oa * texel) * 2.0f;
+        ob = (ob * texel) * 2.0f;
+        const F3 nd = normalize3(direction);
+        const float ref = depth + light[L_SHADOW_BIAS];
+        float shadow = 0.0f;
+        for (int a = -1; a <= 1; a++)
+            for (int b = -1; b <= 1; b++)
+                shadow += shadow_lookup_cube(map, size, (nd + oa * (float)a) + ob * (float)b, ref);
+        return shadow / 9.0f;
+    }
+    return 1.0f;
+}
+
+// lighting.h:149-211
+__device__ __forceinline__ F3 calc_light(const Lighting &d, const float *light, int type, F3 view_position, const float *map, int size) {
+    const F3 light_colour = f3(light[L_COLOUR], light[L_COLOUR + 1], light[L_COLOUR + 2]);
+    if (type == OVIS_LIGHT_AMBIENT)
+        return (d.diffuse * light_colour) * light[L_INTENSITY];
+    F3 direction;
+    float attenuation = 1.0f;
+    const F3 light_direction = f3(light[L_DIRECTION], light[L_DIRECTION + 1], light[L_DIRECTION + 2]);
+    if (type == OVIS_LIGHT_DIRECTIONAL) {
+        direction = light_direction;
+    } else {
+        const F3 to_fragment = d.position - f3(light[0], light[1], light[2]);
+        const float distance = length3(to_fragment);
+        direction = to_fragment * (1.0f / distance);             // normalize(): the same sqrt, computed once
+        attenuation = clamp_glsl(floorf(light[L_RANGE] / distance), 0.0f, 1.0f);
+        if (type == OVIS_LIGHT_SPOT) {
+            const float spot = max_glsl(dot3(direction, light_direction), light[L_COS_CUTOFF]);
+            attenuation *= 1.0f - ((1.0f - spot) / (1.0f - light[L_COS_CUTOFF]));
+        }
+        attenuation /= light[L_ATT_CONSTANT] + (light[L_ATT_LINEAR] * distance) + (light[L_ATT_EXP] * distance * distance);
+    }
+    attenuation *= calc_shadow(d, light, type, map, size);
+    // calcLightBlinnPhong
+    const F3 to_light = f3(-direction.x, -direction.y, -direction.z);
+    const F3 to_view = normalize3(view_position - d.position);
+    const float angle = max_glsl(dot3(d.normal, to_light), 0.0f);
+    F3 colour = (d.diffuse * light_colour) * (light[L_INTENSITY] * angle);
+    const F3 half_vector = normalize3(to_light + to_view);
+    const float specular_angle = max_glsl(dot3(d.normal, half_vector), 0.0f);
+    colour = colour + (d.specular * light_colour) * (light[L_INTENSITY] * powf(specular_angle, d.shininess));
+    return colour * attenuation;
+}
+
+constexpr int kShadeChunk = 16;    // lights staged per round: 16 x 208 B of shared memory
+
+__global__ void __launch_bounds__(256)
+shade_deferred_kernel(const __grid_constant__ ShadeArgs a) {
+    __shared__ float s_light[kShadeChunk * L_FLOATS];
+    __shared__ float s_view[V_FLOATS];
+    __shared__ int s_type[kShadeChunk];
+    __shared__ const float *s_map[kShadeChunk];
+    const int tid = threadIdx.x;
+    if (tid < V_FLOATS)
+        s_view[tid] = a.view_uniforms[tid];
+    __syncthreads();
+    const int64_t pixel = (int64_t)blockIdx.x * blockDim.x + tid;
+    const bool active = pixel < (int64_t)a.width * a.height;
+    Lighting d = {};
+    if (active) {
+        const int px = (int)(pixel % a.width), py = (int)(pixel / a.width);
+        const float4 sa = __ldg(reinterpret_cast<const float4 *>(a.buffer_a) + pixel);
+        const float4 sb = __ldg(reinterpret_cast<const float4 *>(a.buffer_b) + pixel);
+        const float4 sc = __ldg(reinterpret_cast<const float4 *>(a.buffer_c) + pixel);
+        const float depth = __ldg(a.depth + pixel);
+        d.normal = f3(sa.x * 2.0f - 1.0f, sa.y * 2.0f - 1.0f, sa.z * 2.0f - 1.0f);
+        d.diffuse = f3(sb.x, sb.y, sb.z);
+        d.specular = f3(sc.x, sc.y, sc.z);
+        d.shininess = sc.w;
+        const int *vi = reinterpret_cast<const int *>(s_view);
+        const float nx = (((float)px - (float)vi[V_VIEWPORT_POS]) / (float)vi[V_VIEWPORT_SIZE]) * 2.0f - 1.0f;
+        const float ny = (((float)py - (float)vi[V_VIEWPORT_POS + 1]) / (float)vi[V_VIEWPORT_SIZE + 1]) * 2.0f - 1.0f;
+        const float *inv = s_view + V_INVERSE_VP;
+        const float hx = mat_row(inv, 0, nx, ny, depth, 1.0f), hy = mat_row(inv, 1, nx, ny, depth, 1.0f);
+        const float hz = mat_row(inv, 2, nx, ny, depth, 1.0f), hw = mat_row(inv, 3, nx, ny, depth, 1.0f);
+        d.position = f3(hx / hw, hy / hw, hz / hw);
+    }
+    const F3 view_position = f3(s_view[V_POSITION], s_view[V_POSITION + 1], s_view[V_POSITION + 2]);
+    uint32_t m = *a.d_visible_count;
+    if ((int64_t)m > a.max_visible)
+        m = (uint32_t)a.max_visible;
+    F3 sum = f3(0.0f, 0.0f, 0.0f);
+    for (uint32_t base = 0; base < m; base += kShadeChunk) {
+        const int n = (int)min((uint32_t)kShadeChunk, m - base);
+        __syncthreads();                                          // the previous chunk has been consumed
+        for (int i = tid; i < n * L_FLOATS; i += blockDim.x) {
+            const uint32_t id = a.d_visible[base + i / L_FLOATS];
+            s_light[i] = __ldg(a.light_table + (size_t)id * L_FLOATS + i % L_FLOATS);
+        }
+        if (tid < n) {
+            const uint32_t id = a.d_visible[base + tid];
+            s_type[tid] = a.light_types[id];
+            s_map[tid] = a.shadow_maps ? a.shadow_maps[id] : nullptr;
+        }
+        __syncthreads();
+        if (active)
+            for (int l = 0; l < n; l++)
+                sum = sum + calc_light(d, s_light + l * L_FLOATS, s_type[l], view_position, s_map[l], a.shadow_size);
+    }
+    if (active)
+        reinterpret_cast<float4 *>(a.out_rgba)[pixel] = make_float4(sum.x, sum.y, sum.z, 1.0f);
+}
+
+// tonemap_effect_frag.glsl:35-44
+__device__ __forceinline__ float uncharted2(float x) {
+    const float A = 0.15f, B = 0.50f, C = 0.10f, D = 0.20f, E = 0.02f, F = 0.30f;
+    return ((x * (A * x + C * B) + D * E) / (x * (A * x + B) + D * F)) - E / F;
+}
+
+__global__ void __launch_bounds__(256)
+post_effects_kernel(int64_t n, const float4 *__restrict__ in, uint32_t effects, float exposure, float white_point, float gamma,
+                    float4 *__restrict__ out) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n)
+        return;
+    float4 c = __ldg(in + i);
+    if (effects & OVIS_POST_TONEMAP) {
+        const float white = uncharted2(white_point);
+        c.x = uncharted2((c.x * exposure) * 2.0f) / white;
+        c.y = uncharted2((c.y * exposure) * 2.0f) / white;
+        c.z = uncharted2((c.z * exposure) * 2.0f) / white;
+    }
+    if (effects & OVIS_POST_GAMMA) {
+        const float e = 1.0f / gamma;
+        c.x = powf(c.x, e);
+        c.y = powf(c.y, e);
+        c.z = powf(c.z, e);
+    }
+    out[i] = c;
+}
+
+}  // namespace
+
+void launch_shade_deferred(const ShadeArgs &a, cudaStream_t s) {
+    const int64_t pixels = (int64_t)a.width * a.height;
+    if (pixels > 0)
+        shade_deferred_kernel<<<(unsigned)((pixels + 255) / 256), 256, 0, s>>>(a);
+}
+
+void launch_post_effects(int64_t n_pixels, const float *in, uint32_t effects, float exposure, float white_point, float gamma, float *out,
+                         cudaStream_t s) {
+    if (n_pixels > 0)
+        post_effects_kernel<<<(unsigned)((n_pixels + 255) / 256), 256, 0, s>>>(
+            n_pixels, reinterpret_cast<const float4 *>(in), effects, exposure, white_point, gamma, reinterpret_cast<float4 *>(out));
+}
+
+}  // namespace ovis

@@ -115,6 +115,7 @@ struct OvisWorld {
     struct LightShading { float attenuation[3]; float shadow_bias; };
     std::vector<LightShading> light_shading;   // what the LightUniforms block needs beyond OvisLight
     float *d_light_uniforms = nullptr;    // 52 floats (208 B) per light slot
+    int32_t *d_light_types = nullptr;     // OVIS_LIGHT_* per light slot
     int64_t last_visible_lights = 0;      // light count of the previous ovis_cull with OVIS_CULL_LIGHTS
     ovis::DeviceLight *d_lights = nullptr;
     uint32_t *d_light_out = nullptr;
@@ -599,6 +600,7 @@ int upload_lights(OvisWorld *w) {
         OVIS_TRY(grow(w->d_lights, 0, cap, w->stream, false));
         OVIS_TRY(grow(w->d_light_out, 0, cap, w->stream, false));
         OVIS_TRY(grow(w->d_light_uniforms, 0, 52 * cap, w->stream, false));
+        OVIS_TRY(grow(w->d_light_types, 0, cap, w->stream, false));
         w->cap_lights = cap;
     }
     std::vector<ovis::DeviceLight> dl((size_t)n);
@@ -624,12 +626,16 @@ int upload_lights(OvisWorld *w) {
         }
     }
     std::vector<float> blocks(52 * (size_t)n);
+    std::vector<int32_t> types((size_t)n);
+    for (int64_t i = 0; i < n; i++)
+        types[(size_t)i] = w->lights[(size_t)i].type;
     for (int64_t i = 0; i < n; i++)
         ovis::hm::lightUniforms(w->lights[(size_t)i], w->light_shading[(size_t)i].attenuation, w->light_shading[(size_t)i].shadow_bias,
                                 blocks.data() + 52 * (size_t)i);
     if (n > 0) {
         OVIS_CUDA(cudaMemcpyAsync(w->d_lights, dl.data(), sizeof(ovis::DeviceLight) * (size_t)n, cudaMemcpyHostToDevice, w->stream));
         OVIS_CUDA(cudaMemcpyAsync(w->d_light_uniforms, blocks.data(), sizeof(float) * blocks.size(), cudaMemcpyHostToDevice, w->stream));
+        OVIS_CUDA(cudaMemcpyAsync(w->d_light_types, types.data(), sizeof(int32_t) * types.size(), cudaMemcpyHostToDevice, w->stream));
         OVIS_CUDA(cudaStreamSynchronize(w->stream));
     }
     w->lights_dirty = false;
@@ -928,7 +934,7 @@ int ovis_world_destroy(OvisWorld *w) {
     cudaSetDevice(w->device);
     cudaStreamSynchronize(w->stream);
     void *bufs[] = { w->d_local, w->d_world, w->d_alive_bits, w->d_caster_bits, w->d_parent, w->d_local_trs, w->d_world_trs,
-                     w->d_node_entity, w->d_dirty, w->d_light_uniforms, w->d_entity_node, w->d_pass_counts, w->d_draw_totals, w->d_draw_counts,
+                     w->d_node_entity, w->d_dirty, w->d_light_uniforms, w->d_light_types, w->d_entity_node, w->d_pass_counts, w->d_draw_totals, w->d_draw_counts,
                      w->d_extra_entity, w->d_extra_node, w->d_level_lists, w->d_lights, w->d_light_out,
                      w->d_staging, w->d_tile_counts, w->d_block_totals, w->d_exchange, w->d_mv_counts, w->d_mv_totals, w->d_mv_planes,
                      w->d_mv_require, w->d_mv_groups, w->d_mv_hits, w->d_result, w->d_counts, w->d_csr_entities, w->d_csr_offsets,
@@ -1765,6 +1771,68 @@ int ovis_pack_light_uniforms_device(OvisWorld *w, const uint32_t *d_visible, con
         max_visible = n_lights;
     if (n_lights > 0 && std::min(max_visible, capacity) > 0) {
         ovis::launch_light_uniforms(d_visible, d_visible_count, w->d_light_uniforms, d_uniforms, max_visible, capacity, w->stream);
+        w->launches++;
+    }
+    OVIS_CUDA(cudaGetLastError());
+    return OVIS_OK;
+}
+
+int ovis_shade_deferred_device(OvisWorld *w, const OvisGBuffer *g, const void *d_view_uniforms, const uint32_t *d_visible,
+                               const uint32_t *d_visible_count, int64_t max_visible, const float *const *d_shadow_maps,
+                               int32_t shadow_size, float *d_out_rgba) {
+    if (!w || !g || !d_view_uniforms || !d_out_rgba || g->width < 0 || g->height < 0)
+        return fail(OVIS_ERR_INVALID, "ovis_shade_deferred_device: null argument or negative size");
+    if ((int64_t)g->width * g->height > 0 && (!g->d_buffer_a || !g->d_buffer_b || !g->d_buffer_c || !g->d_depth))
+        return fail(OVIS_ERR_INVALID, "ovis_shade_deferred_device: incomplete G-buffer");
+    if ((((uintptr_t)g->d_buffer_a | (uintptr_t)g->d_buffer_b | (uintptr_t)g->d_buffer_c | (uintptr_t)d_out_rgba) & 15u) ||
+        ((uintptr_t)d_view_uniforms & 3u))
+        return fail(OVIS_ERR_INVALID, "ovis_shade_deferred_device: the colour buffers must be 16-byte aligned");
+    if (d_shadow_maps && shadow_size < 1)
+        return fail(OVIS_ERR_INVALID, "ovis_shade_deferred_device: shadow maps need a size");
+    if ((d_visible == nullptr) != (d_visible_count == nullptr))
+        return fail(OVIS_ERR_INVALID, "ovis_shade_deferred_device: pass both the light list and its count, or neither");
+    OVIS_TRY(use_device(w));
+    OVIS_TRY(upload_lights(w));
+    const int64_t n_lights = (int64_t)w->lights.size();
+    if (!d_visible) {
+        d_visible = w->d_light_out;
+        d_visible_count = w->d_counts + 1;
+        max_visible = w->last_visible_lights;
+    }
+    if (max_visible < 0 || max_visible > n_lights)
+        max_visible = n_lights;
+    ovis::ShadeArgs a{};
+    a.width = g->width;
+    a.height = g->height;
+    a.buffer_a = g->d_buffer_a;
+    a.buffer_b = g->d_buffer_b;
+    a.buffer_c = g->d_buffer_c;
+    a.depth = g->d_depth;
+    a.view_uniforms = static_cast<const float *>(d_view_uniforms);
+    a.d_visible = d_visible;
+    a.d_visible_count = d_visible_count;
+    a.max_visible = n_lights > 0 ? max_visible : 0;              // no lights: the count word is 0 anyway
+    a.light_table = w->d_light_uniforms;
+    a.light_types = w->d_light_types;
+    a.shadow_maps = d_shadow_maps;
+    a.shadow_size = shadow_size;
+    a.out_rgba = d_out_rgba;
+    if ((int64_t)g->width * g->height > 0) {
+        ovis::launch_shade_deferred(a, w->stream);
+        w->launches++;
+    }
+    OVIS_CUDA(cudaGetLastError());
+    return OVIS_OK;
+}
+
+int ovis_post_effects_device(OvisWorld *w, int64_t n_pixels, const float *d_rgba, uint32_t effects, float exposure, float white_point,
+                             float gamma, float *d_out_rgba) {
+    if (!w || n_pixels < 0 || (n_pixels > 0 && (!d_rgba || !d_out_rgba)) || (effects & ~(uint32_t)(OVIS_POST_TONEMAP | OVIS_POST_GAMMA)) ||
+        (((uintptr_t)d_rgba | (uintptr_t)d_out_rgba) & 15u))
+        return fail(OVIS_ERR_INVALID, "ovis_post_effects_device: bad arguments (buffers must be 16-byte aligned)");
+    OVIS_TRY(use_device(w));
+    if (n_pixels > 0) {
+        ovis::launch_post_effects(n_pixels, d_rgba, effects, exposure, white_point, gamma, d_out_rgba, w->stream);
         w->launches++;
     }
     OVIS_CUDA(cudaGetLastError());

@@ -136,6 +136,14 @@ def obj_submesh_aabbs(path: str) -> np.ndarray:
         return out[:n.value].copy()
 
 
+class GBuffer(C.Structure):
+    _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("d_buffer_a", C.c_void_p), ("d_buffer_b", C.c_void_p),
+                ("d_buffer_c", C.c_void_p), ("d_depth", C.c_void_p)]
+
+
+POST_TONEMAP, POST_GAMMA = 1, 2
+
+
 class SceneInfo(C.Structure):
     _fields_ = [("first_node", C.c_uint32), ("first_entity", C.c_uint32), ("first_light", C.c_uint32),
                 ("n_nodes", C.c_int32), ("n_entities", C.c_int64), ("n_lights", C.c_int32), ("n_cameras", C.c_int32),
@@ -537,6 +545,21 @@ class World:
         pos = np.ascontiguousarray(viewport_pos, dtype=np.int32).reshape(-1) if viewport_pos is not None else None
         assert pos is None or len(pos) == 2 * len(views)
         _check(self.lib.ovis_pack_view_uniforms_device(self.h, C.c_int32(len(views)), _p(views), _p(pos), C.c_void_p(d_uniforms)))
+
+    # ---- deferred shading over headless buffers
+    def shade_deferred_device(self, width, height, d_buffer_a, d_buffer_b, d_buffer_c, d_depth, d_view_uniforms, d_out_rgba,
+                              d_visible=0, d_visible_count=0, max_visible=-1, d_shadow_maps=0, shadow_size=0):
+        """Asynchronous. All pointers are raw device addresses; d_visible = 0 uses the last cull's light list."""
+        g = GBuffer(width, height, d_buffer_a, d_buffer_b, d_buffer_c, d_depth)
+        _check(self.lib.ovis_shade_deferred_device(self.h, C.byref(g), C.c_void_p(d_view_uniforms), C.c_void_p(d_visible or None),
+                                                   C.c_void_p(d_visible_count or None), C.c_int64(max_visible),
+                                                   C.c_void_p(d_shadow_maps or None), C.c_int32(shadow_size),
+                                                   C.c_void_p(d_out_rgba)))
+
+    def post_effects_device(self, n_pixels, d_rgba, d_out_rgba, effects, exposure=1.0, white_point=11.2, gamma=2.2):
+        _check(self.lib.ovis_post_effects_device(self.h, C.c_int64(n_pixels), C.c_void_p(d_rgba), C.c_uint32(effects),
+                                                 C.c_float(exposure), C.c_float(white_point), C.c_float(gamma),
+                                                 C.c_void_p(d_out_rgba)))
 
     # ---- read-back
     def read_device(self, d_ptr: int, count: int, dtype=np.uint32) -> np.ndarray:

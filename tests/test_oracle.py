@@ -185,3 +185,38 @@ def test_uniform_blocks_as_shipped(port, ref):
         att = rng.uniform(0, 1, 3).astype(np.float32)
         bias = float(np.float32(rng.uniform(-0.01, 0)))
         assert port.light_uniforms(l, att, bias).tobytes() == ref.light_uniforms(l, att, bias).tobytes()
+
+
+def test_shader_restatement_equals_reference_glsl(port, ref):
+    """Section 8(f) row 4: oracle/ovis_shading.c against the reference's own shader SOURCE (engine/shaders/lighting.h,
+    deferred_light_frag.glsl, tonemap_effect_frag.glsl, gamma_correction_effect_frag.glsl) compiled as C++ against GLM by
+    oracle/glsl_harness.cc. Same float operations in the same order: compared for equality."""
+    rng = np.random.default_rng(53)
+    w, h, size = 80, 45, 24
+    view = scenes.make_view((0, 2, 10), (1, 0, 0, 0), 75.0, 0.1, 500.0, w, h)
+    gbuf = util.random_gbuffer(rng, w, h)
+    vb = ref.view_uniforms(view, (2, 1))
+    lights, att, bias = util.lights_for_shading(rng, 40, view)
+    blocks = np.stack([ref.light_uniforms(l, a, float(b)) for l, a, b in zip(lights, att, bias)])
+    maps = []
+    for l in lights:
+        if l["flags"] & 1 and l["type"] == scenes.LIGHT_SPOT:
+            maps.append(rng.uniform(0.9, 1.0, (size, size)).astype(np.float32))
+        elif l["flags"] & 1 and l["type"] == scenes.LIGHT_POINT:
+            maps.append(rng.uniform(0.9, 1.0, (6, size, size)).astype(np.float32))
+        else:
+            maps.append(None)
+    for t in range(4):                                                       # one shader variant at a time, then all together
+        m = lights["type"] == t
+        assert m.sum() >= 3
+        sub = [x for x, k in zip(maps, m) if k]
+        for shadow in (None, sub):
+            glsl = ref.shade_deferred(*gbuf, vb, blocks[m], lights["type"][m], shadow, size, glsl=True)
+            assert same(ref.shade_deferred(*gbuf, vb, blocks[m], lights["type"][m], shadow, size), glsl)
+            assert same(port.shade_deferred(*gbuf, vb, blocks[m], lights["type"][m], shadow, size), glsl)
+    glsl = ref.shade_deferred(*gbuf, vb, blocks, lights["type"], maps, size, glsl=True)
+    assert same(port.shade_deferred(*gbuf, vb, blocks, lights["type"], maps, size), glsl) and np.nanmax(glsl[..., :3]) > 0.1
+    hdr = glsl.reshape(-1, 4)
+    tm = ref.tonemap(hdr, 1.5, 11.2, glsl=True)
+    assert same(port.tonemap(hdr, 1.5, 11.2), tm)
+    assert same(port.gamma(tm, 2.2), ref.gamma(tm, 2.2, glsl=True))

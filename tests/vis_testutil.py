@@ -147,3 +147,40 @@ def gpu_view_uniforms(world, views, viewport_pos=None):
     torch.cuda.synchronize()
     assert bool((out[len(views)] == 0x55).all())
     return out[:len(views)].cpu().numpy()
+
+
+def random_gbuffer(rng, width, height, sky_fraction=0.1):
+    """Headless G-buffer with every pixel independent: encoded unit normals, colours, shininess, depth in (0, 1); a
+    fraction of the pixels is left as cleared sky (depth 1, zero colour)."""
+    n = rng.standard_normal((height, width, 3)).astype(np.float32)
+    n /= np.linalg.norm(n, axis=2, keepdims=True).astype(np.float32)
+    a = np.ones((height, width, 4), dtype=np.float32)
+    a[..., :3] = (n + np.float32(1.0)) / np.float32(2.0)                 # lit_deferred_frag.glsl: (normalize(n) + 1) / 2
+    b = np.ones((height, width, 4), dtype=np.float32)
+    b[..., :3] = rng.uniform(0, 1, (height, width, 3))
+    c = np.empty((height, width, 4), dtype=np.float32)
+    c[..., :3] = rng.uniform(0, 1, (height, width, 3))
+    c[..., 3] = rng.uniform(1, 64, (height, width))
+    depth = rng.uniform(0.5, 0.9999, (height, width)).astype(np.float32)
+    sky = rng.random((height, width)) < sky_fraction
+    depth[sky] = 1.0
+    b[sky, :3] = 0
+    c[sky] = 0
+    return a, b, c, depth
+
+
+def lights_for_shading(rng, n, view, extent=30.0):
+    """Lights of all four types scattered in front of a camera (so that many pixels are in range), with shading parameters."""
+    lights = random_lights(rng, n, extent=extent)
+    lights["intensity"] = rng.uniform(0.2, 2.0, n)
+    lights["colour"] = rng.uniform(0.1, 1.0, (n, 3))
+    lights["range"] = rng.uniform(20.0, 200.0, n)
+    lights["flags"] = rng.integers(0, 2, n)
+    # a spot light pointing exactly along +-Y has a NaN shadowSpace in the reference too (quatLookAt with up = Y is
+    # degenerate, render_light.cc:270); one such light would turn every pixel into NaN and hide everything else
+    vertical = (lights["direction"][:, 0] == 0) & (lights["direction"][:, 2] == 0)
+    lights["direction"][vertical, 0] = 0.3
+    lights["direction"][vertical, 2] = 0.1
+    att = np.stack([rng.uniform(0.5, 1.0, n), rng.uniform(0.0, 0.1, n), rng.uniform(0.0, 0.01, n)], axis=1).astype(np.float32)
+    bias = rng.uniform(-0.005, 0.0, n).astype(np.float32)
+    return lights, att, bias
