@@ -156,11 +156,14 @@ struct ShadeArgs {
     const uint32_t *d_visible_count;
     int64_t max_visible;
     const float *light_table;                      // 52 floats per light slot
-    const int32_t *light_types;                    // OVIS_LIGHT_* per light slot
+    const int32_t *light_types;                    // OVIS_LIGHT_* per light slot, | kLightSkippable
     const float *const *shadow_maps;               // per light slot: depth image or NULL; NULL = no shadows at all
     int shadow_size;
     float *out_rgba;                               // float4 per pixel
 };
+// Set by the host for a point / spot light whose block is finite and bounded, with attenuation constant > 0, linear and
+// exponential terms >= 0 and (spot) cosCutoff < 1: beyond its range such a light contributes exactly +-0 to a clean pixel.
+constexpr int32_t kLightSkippable = 1 << 8;
 void launch_shade_deferred(const ShadeArgs &a, cudaStream_t s);
 void launch_post_effects(int64_t n_pixels, const float *in, uint32_t effects, float exposure, float white_point, float gamma, float *out,
                          cudaStream_t s);

@@ -123,11 +123,27 @@ __device__ __forceinline__ float calc_shadow(const Lighting &d, const float *lig
     return 1.0f;
 }
 
-// lighting.h:149-211
-__device__ __forceinline__ F3 calc_light(const Lighting &d, const float *light, int type, F3 view_position, const float *map, int size) {
+// lighting.h:149-168
+__device__ __forceinline__ F3 blinn_phong(const Lighting &d, F3 direction, const float *light, F3 view_position) {
     const F3 light_colour = f3(light[L_COLOUR], light[L_COLOUR + 1], light[L_COLOUR + 2]);
-    if (type == OVIS_LIGHT_AMBIENT)
-        return (d.diffuse * light_colour) * light[L_INTENSITY];
+    const F3 to_light = f3(-direction.x, -direction.y, -direction.z);
+    const F3 to_view = normalize3(view_position - d.position);
+    const float angle = max_glsl(dot3(d.normal, to_light), 0.0f);
+    F3 colour = (d.diffuse * light_colour) * (light[L_INTENSITY] * angle);
+    const F3 half_vector = normalize3(to_light + to_view);
+    const float specular_angle = max_glsl(dot3(d.normal, half_vector), 0.0f);
+    colour = colour + (d.specular * light_colour) * (light[L_INTENSITY] * powf(specular_angle, d.shininess));
+    return colour;
+}
+
+// lighting.h:173-211. `may_skip`: light and pixel are known to be finite and in bounds (see kLightSkippable), so that an
+// attenuation of exactly 0 means a contribution of exactly +-0 - which the caller's sum would not notice.
+__device__ __forceinline__ bool calc_light(const Lighting &d, const float *light, int type, F3 view_position, const float *map, int size,
+                                           bool may_skip, F3 &out) {
+    if (type == OVIS_LIGHT_AMBIENT) {
+        out = (d.diffuse * f3(light[L_COLOUR], light[L_COLOUR + 1], light[L_COLOUR + 2])) * light[L_INTENSITY];
+        return true;
+    }
     F3 direction;
     float attenuation = 1.0f;
     const F3 light_direction = f3(light[L_DIRECTION], light[L_DIRECTION + 1], light[L_DIRECTION + 2]);
@@ -136,8 +152,10 @@ __device__ __forceinline__ F3 calc_light(const Lighting &d, const float *light, 
     } else {
         const F3 to_fragment = d.position - f3(light[0], light[1], light[2]);
         const float distance = length3(to_fragment);
-        direction = to_fragment * (1.0f / distance);             // normalize(): the same sqrt, computed once
         attenuation = clamp_glsl(floorf(light[L_RANGE] / distance), 0.0f, 1.0f);
+        if (may_skip && attenuation == 0.0f)
+            return false;
+        direction = to_fragment * (1.0f / distance);             // normalize(): the same sqrt, computed once
         if (type == OVIS_LIGHT_SPOT) {
             const float spot = max_glsl(dot3(direction, light_direction), light[L_COS_CUTOFF]);
             attenuation *= 1.0f - ((1.0f - spot) / (1.0f - light[L_COS_CUTOFF]));
@@ -145,15 +163,8 @@ __device__ __forceinline__ F3 calc_light(const Lighting &d, const float *light, 
         attenuation /= light[L_ATT_CONSTANT] + (light[L_ATT_LINEAR] * distance) + (light[L_ATT_EXP] * distance * distance);
     }
     attenuation *= calc_shadow(d, light, type, map, size);
-    // calcLightBlinnPhong
-    const F3 to_light = f3(-direction.x, -direction.y, -direction.z);
-    const F3 to_view = normalize3(view_position - d.position);
-    const float angle = max_glsl(dot3(d.normal, to_light), 0.0f);
-    F3 colour = (d.diffuse * light_colour) * (light[L_INTENSITY] * angle);
-    const F3 half_vector = normalize3(to_light + to_view);
-    const float specular_angle = max_glsl(dot3(d.normal, half_vector), 0.0f);
-    colour = colour + (d.specular * light_colour) * (light[L_INTENSITY] * powf(specular_angle, d.shininess));
-    return colour * attenuation;
+    out = blinn_phong(d, direction, light, view_position) * attenuation;
+    return true;
 }
 
 constexpr int kShadeChunk = 16;    // lights staged per round: 16 x 208 B of shared memory
@@ -171,6 +182,7 @@ shade_deferred_kernel(const __grid_constant__ ShadeArgs a) {
     const int64_t pixel = (int64_t)blockIdx.x * blockDim.x + tid;
     const bool active = pixel < (int64_t)a.width * a.height;
     Lighting d = {};
+    bool pixel_clean = false;
     if (active) {
         const int px = (int)(pixel % a.width), py = (int)(pixel / a.width);
         const float4 sa = __ldg(reinterpret_cast<const float4 *>(a.buffer_a) + pixel);
@@ -188,6 +200,11 @@ shade_deferred_kernel(const __grid_constant__ ShadeArgs a) {
         const float hx = mat_row(inv, 0, nx, ny, depth, 1.0f), hy = mat_row(inv, 1, nx, ny, depth, 1.0f);
         const float hz = mat_row(inv, 2, nx, ny, depth, 1.0f), hw = mat_row(inv, 3, nx, ny, depth, 1.0f);
         d.position = f3(hx / hw, hy / hw, hz / hw);
+        // comparisons are false for NaN, so one chain covers "finite and within bounds"
+        pixel_clean = dot3(d.normal, d.normal) <= 1.001f && d.shininess >= 0.0f && d.shininess <= 4096.0f &&
+                      fabsf(d.diffuse.x) <= 1e6f && fabsf(d.diffuse.y) <= 1e6f && fabsf(d.diffuse.z) <= 1e6f &&
+                      fabsf(d.specular.x) <= 1e6f && fabsf(d.specular.y) <= 1e6f && fabsf(d.specular.z) <= 1e6f &&
+                      fabsf(d.position.x) <= 1e18f && fabsf(d.position.y) <= 1e18f && fabsf(d.position.z) <= 1e18f;
     }
     const F3 view_position = f3(s_view[V_POSITION], s_view[V_POSITION + 1], s_view[V_POSITION + 2]);
     uint32_t m = *a.d_visible_count;
@@ -208,8 +225,18 @@ shade_deferred_kernel(const __grid_constant__ ShadeArgs a) {
         }
         __syncthreads();
         if (active)
-            for (int l = 0; l < n; l++)
-                sum = sum + calc_light(d, s_light + l * L_FLOATS, s_type[l], view_position, s_map[l], a.shadow_size);
+            for (int l = 0; l < n; l++) {
+                const float *light = s_light + l * L_FLOATS;
+                const int type = s_type[l] & 0xff;
+                // Out of the light's range the shader multiplies a finite colour by an attenuation of exactly 0 and the
+                // blend adds +-0, which leaves the sum as it is (the sum is never -0: it starts at +0). Where every
+                // operand is known to be finite and in bounds (light checked on the host, pixel checked above), that
+                // work is skipped; a shadowed spot light is not (its projective divide can produce NaN off-range).
+                const bool may_skip = (s_type[l] & kLightSkippable) && pixel_clean && !(type == OVIS_LIGHT_SPOT && s_map[l]);
+                F3 colour;
+                if (calc_light(d, light, type, view_position, s_map[l], a.shadow_size, may_skip, colour))
+                    sum = sum + colour;
+            }
     }
     if (active)
         reinterpret_cast<float4 *>(a.out_rgba)[pixel] = make_float4(sum.x, sum.y, sum.z, 1.0f);

@@ -632,6 +632,22 @@ int upload_lights(OvisWorld *w) {
     for (int64_t i = 0; i < n; i++)
         ovis::hm::lightUniforms(w->lights[(size_t)i], w->light_shading[(size_t)i].attenuation, w->light_shading[(size_t)i].shadow_bias,
                                 blocks.data() + 52 * (size_t)i);
+    for (int64_t i = 0; i < n; i++) {                            // see kLightSkippable
+        const float *b = blocks.data() + 52 * (size_t)i;
+        const int32_t type = types[(size_t)i];
+        if (type != OVIS_LIGHT_POINT && type != OVIS_LIGHT_SPOT)
+            continue;
+        bool ok = true;
+        for (int k = 0; k < 52; k++)
+            ok = ok && std::isfinite(b[k]);
+        for (int k = 0; k < 3; k++)
+            ok = ok && std::fabs(b[k]) <= 1e18f && std::fabs(b[8 + k]) <= 1e6f;
+        ok = ok && std::fabs(b[3]) <= 1e6f && b[45] > 0.0f && b[46] >= 0.0f && b[47] >= 0.0f;
+        if (type == OVIS_LIGHT_SPOT)
+            ok = ok && b[7] < 1.0f;
+        if (ok)
+            types[(size_t)i] |= ovis::kLightSkippable;
+    }
     if (n > 0) {
         OVIS_CUDA(cudaMemcpyAsync(w->d_lights, dl.data(), sizeof(ovis::DeviceLight) * (size_t)n, cudaMemcpyHostToDevice, w->stream));
         OVIS_CUDA(cudaMemcpyAsync(w->d_light_uniforms, blocks.data(), sizeof(float) * blocks.size(), cudaMemcpyHostToDevice, w->stream));

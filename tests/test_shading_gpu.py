@@ -164,3 +164,65 @@ def test_post_effects(oracle):
     with pytest.raises(lib.OvisError):
         w.post_effects_device(n, d_in.data_ptr(), d_out.data_ptr(), 8)
     w.close()
+
+
+def test_sparse_lights_and_unclean_inputs(oracle):
+    """Most pixel-light pairs out of range (the kernel skips them where that is provably exact), plus lights and pixels
+    that must NOT take the shortcut: non-finite or out-of-bounds values, zero / negative attenuation terms."""
+    import torch
+    rng = np.random.default_rng(2024)
+    w, h, n = 150, 80, 96
+    view = scenes.make_view((0, 2, 10), scenes.quat_yaw_pitch(10.0, -5.0), 75.0, 0.1, 500.0, w, h)
+    gbuf = util.random_gbuffer(rng, w, h, linear_z=(0.1, 500.0, 1.0, 300.0))
+    a, b, c, depth = gbuf
+    a[3, 5, :3] = np.nan                       # pixels that are not "clean"
+    b[4, 6, 0] = np.inf
+    b[5, 7, 1] = 1e30
+    c[6, 8, 3] = -2.0                          # negative shininess: pow(0, -2) = inf
+    c[7, 9, 3] = 1e9
+    a[8, 10, :3] = (3.0, 3.0, 3.0)             # |normal| > 1
+    depth[9, 11] = np.nan
+    lights, att, bias = util.lights_for_shading(rng, n, view, extent=150.0)
+    lights["range"] = rng.uniform(5.0, 40.0, n)
+    att[0] = (0.0, 0.0, 0.0)                   # lights that are not "skippable"
+    att[1] = (1.0, -0.5, 0.0)
+    att[2] = (1.0, 0.0, -0.001)
+    lights["intensity"][3] = np.nan
+    lights["colour"][4] = (np.inf, 1.0, 1.0)
+    lights["intensity"][5] = 1e30
+    lights["cutoff"][6] = 0.0                  # cosCutoff = 1 for a spot light: division by zero in the cone term
+    lights["type"][6] = scenes.LIGHT_SPOT
+    lights["position"][7] = (1e30, 0.0, 0.0)
+    lights["range"][8] = -5.0
+    world = lib.World(0)
+    world.add_lights(lights)
+    for i in range(n):
+        world.set_light_shading(i, att[i], float(bias[i]))
+    blocks = np.stack([oracle.light_uniforms(l, x, float(y)) for l, x, y in zip(lights, att, bias)])
+    vb = oracle.view_uniforms(view)
+    size = 16
+    maps = [rng.uniform(0.9, 1.0, (size, size) if l["type"] == scenes.LIGHT_SPOT else (6, size, size)).astype(np.float32)
+            if (l["flags"] & 1 and l["type"] >= scenes.LIGHT_POINT) else None for l in lights]
+    clean = np.arange(9, n, dtype=np.uint32)
+    want = oracle.shade_deferred(*gbuf, vb, blocks[clean], lights["type"][clean])
+    in_range = 0
+    for i in clean[:20]:                       # the scene really is sparse: a light reaches few pixels
+        one = oracle.shade_deferred(*gbuf, vb, blocks[i:i + 1], lights["type"][i:i + 1])
+        if lights["type"][i] >= scenes.LIGHT_POINT:
+            in_range += int((one[..., :3] != 0).any(axis=2).sum())
+    assert in_range < 0.2 * 20 * w * h
+    _close(_shade(torch, world, w, h, gbuf, vb, clean), want)
+    everyone = np.arange(n, dtype=np.uint32)
+    for m, sz in ((None, 0), (maps, size)):
+        want = oracle.shade_deferred(*gbuf, vb, blocks, lights["type"], m, sz)
+        got = _shade(torch, world, w, h, gbuf, vb, everyone, m, sz)
+        assert np.array_equal(np.isnan(got), np.isnan(want))
+        _close(got, want)
+    one_by_one = [9, 0, 1, 2, 3, 4, 5, 6, 7, 8]
+    for i in one_by_one:                       # each unclean light alone, so that a NaN from another cannot mask it
+        ids = np.array([i], dtype=np.uint32)
+        want = oracle.shade_deferred(*gbuf, vb, blocks[ids], lights["type"][ids])
+        got = _shade(torch, world, w, h, gbuf, vb, ids)
+        assert np.array_equal(np.isnan(got), np.isnan(want)), i
+        _close(got, want)
+    world.close()

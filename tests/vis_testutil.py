@@ -149,7 +149,7 @@ def gpu_view_uniforms(world, views, viewport_pos=None):
     return out[:len(views)].cpu().numpy()
 
 
-def random_gbuffer(rng, width, height, sky_fraction=0.1):
+def random_gbuffer(rng, width, height, sky_fraction=0.1, linear_z=None):
     """Headless G-buffer with every pixel independent: encoded unit normals, colours, shininess, depth in (0, 1); a
     fraction of the pixels is left as cleared sky (depth 1, zero colour)."""
     n = rng.standard_normal((height, width, 3)).astype(np.float32)
@@ -162,6 +162,10 @@ def random_gbuffer(rng, width, height, sky_fraction=0.1):
     c[..., :3] = rng.uniform(0, 1, (height, width, 3))
     c[..., 3] = rng.uniform(1, 64, (height, width))
     depth = rng.uniform(0.5, 0.9999, (height, width)).astype(np.float32)
+    if linear_z is not None:                                             # (znear, zfar, lo, hi): view distance uniform in [lo, hi]
+        zn, zf, lo, hi = linear_z
+        dist = rng.uniform(lo, hi, (height, width))
+        depth = (zf / (zf - zn) * (1.0 - zn / dist)).astype(np.float32)  # perspectiveRH_ZO depth of that distance
     sky = rng.random((height, width)) < sky_fraction
     depth[sky] = 1.0
     b[sky, :3] = 0

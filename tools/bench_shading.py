@@ -104,6 +104,38 @@ def main():
         case["speedup_vs_1core"] = case["cpu_1core_ms_scaled_to_frame"] / ms
         out["cases"].append(case)
 
+    # the same frame size with lights that reach only part of the scene: view distances 1..300, 256 lights of range 5..40
+    gbuf2 = util.random_gbuffer(rng, w, h, linear_z=(0.1, 500.0, 1.0, 300.0))
+    lights2, att2, bias2 = util.lights_for_shading(rng, n_max, view, extent=150.0)
+    lights2["range"] = rng.uniform(5.0, 40.0, n_max)
+    world2 = lib.World(0)
+    world2.set_stream(stream.cuda_stream)
+    world2.add_lights(lights2)
+    for i in range(n_max):
+        world2.set_light_shading(i, att2[i], float(bias2[i]))
+    blocks2 = np.stack([oracle.light_uniforms(l, a, float(b)) for l, a, b in zip(lights2, att2, bias2)])
+    with torch.cuda.stream(stream):
+        d2 = [torch.from_numpy(x).cuda() for x in gbuf2]
+    ids = torch.arange(n_max, dtype=torch.int32, device="cuda")
+    cnt = torch.tensor([n_max], dtype=torch.int32, device="cuda")
+    torch.cuda.synchronize()
+
+    def shade_sparse():
+        world2.shade_deferred_device(w, h, d2[0].data_ptr(), d2[1].data_ptr(), d2[2].data_ptr(), d2[3].data_ptr(), d_vb.data_ptr(),
+                                     d_out.data_ptr(), ids.data_ptr(), cnt.data_ptr(), n_max)
+
+    ms = timed(stream, shade_sparse)
+    crop2 = [np.ascontiguousarray(x[:ch, :cw]) for x in gbuf2]
+    t0 = time.perf_counter()
+    want = oracle.shade_deferred(*crop2, vb, blocks2, lights2["type"])
+    cpu_ms = (time.perf_counter() - t0) * 1e3
+    got = d_out.view(h, w, 4)[:ch, :cw].cpu().numpy()
+    out["sparse_lights"] = {"lights": n_max, "light_range": "5..40", "view_distance": "1..300", "gpu_ms": ms,
+                            "ns_per_pixel_light": ms * 1e6 / (w * h * n_max), "cpu_1core_ms_scaled_to_frame": cpu_ms * (w * h) / (cw * ch),
+                            "max_rel_err_vs_oracle": rel_err(got, want),
+                            "note": "pixel-light pairs beyond the light's range are skipped where that is provably exact"}
+    world2.close()
+
     def post():
         world.post_effects_device(w * h, d_out.data_ptr(), d_post.data_ptr(), lib.POST_TONEMAP | lib.POST_GAMMA, 1.5, 11.2, 2.2)
 
