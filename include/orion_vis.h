@@ -213,13 +213,14 @@ int ovis_cull_planes_device_multi(OvisWorld *world, const float planes[24], uint
                                   int32_t n_dst, uint32_t *const *d_out_entities, uint32_t *const *d_out_count);
 
 /* The same with one-way ready flags instead of a barrier, so that nothing but the two cull kernels is enqueued per
- * frame (and back-to-back frames keep overlapping). Before storing, the gather kernel waits until each of the n_wait
- * words at d_wait_flags (local memory that the peers write) is >= wait_value - i.e. the peers have finished with the
- * buffer being refilled; after every block has stored, it writes signal_value to each of the n_signal words
- * d_signal_flags[x] (typically this shard's slot in every rank's flag array, peers' over NVLink). A reader calls
- * ovis_wait_flags (one tiny kernel on the world's stream that spins until all n words are >= value) before it touches the
- * segments. Waits give up after ~2 s and raise the world's exchange error (ovis_world_exchange_error) rather than hang.
- * Frame numbers compare modulo 2^32 (signed difference). No counterpart in the reference. */
+ * frame (and back-to-back frames keep overlapping). Before the gather kernel may store, each of the n_wait (<= 32) words
+ * at d_wait_flags (local memory that the peers write) must be >= wait_value - i.e. the peers have finished with the
+ * buffer being refilled; one warp of the test kernel checks that, hidden behind the streaming pass. After every gather
+ * block has stored, signal_value is written to each of the n_signal words d_signal_flags[x] (typically this shard's slot
+ * in every rank's flag array, peers' over NVLink). A reader calls ovis_wait_flags (one tiny kernel on the world's stream
+ * that spins until all n words are >= value) or ovis_read_segments_host before it touches the segments. Waits give up
+ * after ~2 s and raise the world's exchange error (ovis_world_exchange_error) rather than hang. Frame numbers compare
+ * modulo 2^32 (signed difference). No counterpart in the reference. */
 int ovis_cull_planes_device_exchange(OvisWorld *world, const float planes[24], uint32_t require, int64_t capacity,
                                      int32_t n_dst, uint32_t *const *d_out_entities, uint32_t *const *d_out_count,
                                      int32_t n_wait, const uint32_t *d_wait_flags, uint32_t wait_value,

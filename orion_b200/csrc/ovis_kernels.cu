@@ -235,6 +235,40 @@ void launch_mark_dirty(const uint32_t *ids, int64_t n, uint8_t *dirty, cudaStrea
 // to ~2.1 TB/s by CTA-wide barrier stalls behind the look-back chain; see profiles/r01_cull_notes.md.
 // ------------------------------------------------------------------------------------------------
 
+__device__ __forceinline__ uint32_t load_flag_sys(const uint32_t *p) {
+    uint32_t v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+
+// after a __threadfence_system(): the fence orders every earlier store before this one at system scope
+__device__ __forceinline__ void store_flag_relaxed_sys(uint32_t *p, uint32_t v) {
+    asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+// Spin until flags[i] >= value for every i, at most ~2 s (a peer that never arrives must not hang the GPU).
+__device__ __forceinline__ void wait_flags_at_least(const uint32_t *flags, int n, uint32_t value, uint32_t *error_flag) {
+    const long long start = clock64();
+    for (int i = 0; i < n; i++) {
+        while ((int32_t)(load_flag_sys(flags + i) - value) < 0) {
+            if (clock64() - start > 4000000000ll) {
+                if (error_flag)
+                    *error_flag = 1u;
+                return;
+            }
+            __nanosleep(100);
+        }
+    }
+}
+
+// The same by one whole warp, lane i polling flag i (n <= 32): the system-scope loads overlap instead of queueing up.
+__device__ __forceinline__ void wait_flags_warp(const uint32_t *flags, int n, uint32_t value, uint32_t *error_flag) {
+    const int lane = threadIdx.x & 31;
+    if (lane < n)
+        wait_flags_at_least(flags + lane, 1, value, error_flag);
+    __syncwarp();
+}
+
 template <int GROUPS, bool MASKED>
 __device__ __forceinline__ void cull_test_body(const CullArgs &a) {
     constexpr int WT = 128 * GROUPS;                       // entities per warp tile
@@ -322,6 +356,11 @@ __device__ __forceinline__ void cull_test_body(const CullArgs &a) {
 template <int GROUPS, bool MASKED>
 __global__ void __launch_bounds__(kCullThreads, 4 / GROUPS)
 cull_test_kernel(const __grid_constant__ CullArgs a) {
+    // Sharded exchange: the segment buffer this frame's gather kernel will refill must have been released by every peer.
+    // One warp of the whole grid checks that here, hidden behind the streaming pass (the gather kernel starts only after
+    // this kernel has finished), instead of every gather block paying a round of system-scope loads before its stores.
+    if (a.n_wait && blockIdx.x == 0 && threadIdx.x < 32)
+        wait_flags_warp(a.wait_flags, a.n_wait, a.wait_value, a.error_flag);
     cull_test_body<GROUPS, MASKED>(a);
 }
 
@@ -413,31 +452,6 @@ __device__ __forceinline__ void cull_gather_body(const GatherArgs &a, int block,
     }
 }
 
-__device__ __forceinline__ uint32_t load_flag_sys(const uint32_t *p) {
-    uint32_t v;
-    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-    return v;
-}
-
-__device__ __forceinline__ void store_flag_sys(uint32_t *p, uint32_t v) {
-    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
-
-// Spin until flags[i] >= value for every i, at most ~2 s (a peer that never arrives must not hang the GPU).
-__device__ __forceinline__ void wait_flags_at_least(const uint32_t *flags, int n, uint32_t value, uint32_t *error_flag) {
-    const long long start = clock64();
-    for (int i = 0; i < n; i++) {
-        while ((int32_t)(load_flag_sys(flags + i) - value) < 0) {
-            if (clock64() - start > 4000000000ll) {
-                if (error_flag)
-                    *error_flag = 1u;
-                return;
-            }
-            __nanosleep(100);
-        }
-    }
-}
-
 __global__ void __launch_bounds__(256)
 cull_gather_kernel(const __grid_constant__ GatherArgs a) {
     // Let the next cull's test kernel start now (if it was launched to allow that): it shares nothing with this kernel.
@@ -451,13 +465,20 @@ cull_gather_kernel(const __grid_constant__ GatherArgs a) {
     if (a.n_signal) {                                         // the last block to finish publishes the segment
         __syncthreads();                                      // this block's stores happen-before thread 0's fence
         if (threadIdx.x == 0) {
-            __threadfence_system();                           // one system fence per block (cumulative over the barrier)
+            // Release this block's stores (the barrier above makes them cumulative with thread 0) to the rest of the GPU;
+            // the last block's system fence below then orders every block's stores before the flags at system scope
+            // (PTX causality order is transitive across the gpu-scope and the sys-scope synchronisation). A system fence
+            // in every block was measured to cost ~4.4 us per frame: it stalls the next cull's test kernel on every SM.
+            if (a.block_fence_sys)
+                __threadfence_system();
+            else
+                __threadfence();
             unsigned int prev = atomicAdd(a.done_counter, 1u);
             if (prev == gridDim.x - 1) {
                 *a.done_counter = 0u;
                 __threadfence_system();
                 for (int x = 0; x < a.n_signal; x++)
-                    store_flag_sys(a.signal_flags[x], a.signal_value);
+                    store_flag_relaxed_sys(a.signal_flags[x], a.signal_value);
             }
         }
     }

@@ -48,6 +48,11 @@ struct CullArgs {                 // K3a
     uint32_t *block_totals;      // scratch: survivors per block of kGatherTiles tiles (zero on entry)
     uint32_t *block_totals_next; // scratch: the set the next launch accumulates into; zeroed here
     uint32_t id_base;            // added to every emitted slot id (global id of a shard's first entity)
+    // sharded exchange (optional): wait until wait_flags[i] >= wait_value for i < n_wait (<= 32) before finishing
+    int n_wait;
+    const uint32_t *wait_flags;
+    uint32_t wait_value;
+    uint32_t *error_flag;
 };
 
 struct GatherArgs {               // K3b
@@ -78,6 +83,7 @@ struct GatherArgs {               // K3b
     int n_signal;
     uint32_t *signal_flags[kMaxPeers + 1];
     uint32_t signal_value;
+    int block_fence_sys;          // OVIS_EXCHANGE_BLOCK_FENCE=sys: system-scope fence in every block (diagnostic)
     unsigned int *done_counter;   // scratch, zero between launches
     uint32_t *error_flag;         // set to 1 if a wait gave up (a peer never arrived)
 };

@@ -125,7 +125,7 @@ extern "C" int ovis_cull_planes_noalloc(int device, void *cuda_stream, const flo
     uint32_t *tile_counts = reinterpret_cast<uint32_t *>(setup->scratch + kStagingBytes);
     uint32_t *totals = reinterpret_cast<uint32_t *>(setup->scratch + kStagingBytes + kCountsBytes);
 
-    ovis::CullArgs a;
+    ovis::CullArgs a{};
     for (int i = 0; i < 6; i++)
         a.planes[i] = make_float4(planes[4 * i], planes[4 * i + 1], planes[4 * i + 2], planes[4 * i + 3]);
     a.bounds = d_world_aabb;
@@ -153,7 +153,7 @@ extern "C" int ovis_cull_planes_noalloc(int device, void *cuda_stream, const flo
     // one shared scratch: this call's test kernel must not overlap the previous call's gather kernel
     ovis::launch_cull_test(a, false, kVariant, grid, stream, /*overlap_previous_gather=*/false);
 
-    ovis::GatherArgs g;
+    ovis::GatherArgs g{};
     g.staging = staging;
     g.tile_counts = tile_counts;
     g.block_totals = totals;

@@ -137,6 +137,7 @@ struct OvisWorld {
     uint32_t *h_counts = nullptr;         // pinned mirror
     uint32_t *h_counts_dev = nullptr;     // the same words as the device addresses them (mapped pinned memory)
     bool direct_host = true;              // OVIS_DIRECT_HOST=0 (tuning) forces the copy path
+    bool block_fence_sys = false;         // OVIS_EXCHANGE_BLOCK_FENCE=sys (diagnostic): system fence in every gather block
     uint32_t *d_csr_entities = nullptr;
     int64_t cap_csr = 0;
     long long *d_csr_offsets = nullptr;
@@ -506,7 +507,7 @@ int enqueue_cull(OvisWorld *w, const float planes[24], uint32_t require, uint32_
     const int variant = w->forced_variant >= 0 ? w->forced_variant : (w->n_ent < (4 << 20) ? 1 : 0);
     const int tile = ovis::cull_variant(variant).tile();
     const bool masked = require != 0 || w->any_dead;
-    ovis::CullArgs a;
+    ovis::CullArgs a{};
     load_planes(a.planes, planes);
     a.bounds = w->d_world;
     a.stride = w->cap_ent;
@@ -521,6 +522,15 @@ int enqueue_cull(OvisWorld *w, const float planes[24], uint32_t require, uint32_
     // zeroed by this test kernel for the next cull; last read by the gather kernel two culls ago, which has finished
     a.block_totals_next = w->d_block_totals + ((set3 + 1) % 3) * w->cap_blocks;
     a.id_base = w->id_base;
+    a.n_wait = 0;
+    a.wait_flags = nullptr;
+    a.wait_value = 0;
+    a.error_flag = w->d_exchange + 1;
+    if (flags && flags->n_wait > 0) {                            // checked by the test kernel, see cull_test_kernel
+        a.n_wait = flags->n_wait;
+        a.wait_flags = flags->wait_flags;
+        a.wait_value = flags->wait_value;
+    }
     const int warps_needed_blocks = (a.num_tiles + ovis::kCullThreads / 32 - 1) / (ovis::kCullThreads / 32);
     int grid = std::min(warps_needed_blocks, w->num_sms * w->blocks_per_sm[variant][masked ? 1 : 0]);
     cudaEvent_t *ev = nullptr;
@@ -535,7 +545,7 @@ int enqueue_cull(OvisWorld *w, const float planes[24], uint32_t require, uint32_
         w->timing_used += 3;
         OVIS_CUDA(cudaEventRecord(ev[0], w->stream));
     }
-    ovis::GatherArgs g;
+    ovis::GatherArgs g{};
     g.staging = a.staging;
     g.tile_counts = a.tile_counts;
     g.block_totals = a.block_totals;
@@ -554,12 +564,11 @@ int enqueue_cull(OvisWorld *w, const float planes[24], uint32_t require, uint32_
     }
     g.n_wait = 0;
     g.n_signal = 0;
+    g.block_fence_sys = w->block_fence_sys ? 1 : 0;
     g.done_counter = w->d_exchange;
     g.error_flag = w->d_exchange + 1;
     if (flags) {
-        g.n_wait = flags->n_wait;
-        g.wait_flags = flags->wait_flags;
-        g.wait_value = flags->wait_value;
+        g.n_wait = 0;                                            // the test kernel has waited already
         g.n_signal = flags->n_signal;
         for (int x = 0; x < flags->n_signal; x++)
             g.signal_flags[x] = flags->signal_flags[x];
@@ -938,6 +947,8 @@ int ovis_world_create(int device, OvisWorld **out_world) {
         cudaGetLastError();
         w->h_counts_dev = nullptr;
     }
+    if (const char *v = getenv("OVIS_EXCHANGE_BLOCK_FENCE"))
+        w->block_fence_sys = std::strcmp(v, "sys") == 0;
     if (const char *v = getenv("OVIS_DIRECT_HOST"))
         w->direct_host = atoi(v) != 0;
     *out_world = w;
@@ -1431,7 +1442,7 @@ int ovis_cull_planes_device_exchange(OvisWorld *w, const float planes[24], uint3
                                      int32_t n_wait, const uint32_t *d_wait_flags, uint32_t wait_value,
                                      int32_t n_signal, uint32_t *const *d_signal_flags, uint32_t signal_value) {
     if (!w || !planes || n_dst < 1 || n_dst > ovis::kMaxPeers + 1 || !d_out_entities || !d_out_count || capacity < 0 ||
-        n_wait < 0 || (n_wait > 0 && !d_wait_flags) || n_signal < 0 || n_signal > ovis::kMaxPeers + 1 ||
+        n_wait < 0 || n_wait > 32 || (n_wait > 0 && !d_wait_flags) || n_signal < 0 || n_signal > ovis::kMaxPeers + 1 ||
         (n_signal > 0 && !d_signal_flags))
         return fail(OVIS_ERR_INVALID, "ovis_cull_planes_device_exchange: bad arguments");
     OVIS_TRY(use_device(w));

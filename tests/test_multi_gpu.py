@@ -37,6 +37,26 @@ for mode in ("nccl", "p2p"):
             parts = sw.cull_to_host(planes, req)
             assert np.array_equal(np.concatenate(parts), exp), (mode, rank, "host")
     assert mode == "nccl" or sw.exchange_mode == "p2p", "symmetric memory path did not come up"
+    if mode == "p2p":
+        # 300 frames back to back with the visible set changing every frame: each rank copies the segments the moment the
+        # ready flags allow it; a flag that arrives before a peer's stores would show up as a stale or torn segment
+        views = [scenes.default_camera(), scenes.make_view((100, 0, 300), (1, 0, 0, 0), 60.0, 1.0, 900.0, 800, 600),
+                 scenes.make_view((-300, 50, 0), scenes.quat_yaw_pitch(70.0, 0.0), 90.0, 0.5, 700.0, 1600, 900)]
+        planes = [lib.view_planes(v) for v in views]
+        expected = [oracle.cull_aabb(aabb, p, threads=4) for p in planes]
+        frames = 300
+        with torch.cuda.stream(sw.stream):
+            history = torch.zeros((frames, size, sw.capacity + 1), dtype=torch.int32, device="cuda")
+            for i in range(frames):
+                blocks = sw.cull_device(planes[i %% 3])
+                sw.enqueue_ready_wait()
+                history[i].copy_(blocks)
+        sw.stream.synchronize()
+        assert w.exchange_error() == 0
+        host = history.cpu()
+        for i in range(frames):
+            got = merged_list(host[i])
+            assert np.array_equal(got, expected[i %% 3]), (rank, "frame", i, len(got), len(expected[i %% 3]))
     dist.barrier()
     w.close()
 if rank == 0:
