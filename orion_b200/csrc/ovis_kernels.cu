@@ -371,6 +371,11 @@ __device__ __forceinline__ void cull_gather_body(const GatherArgs &a, int block,
     __shared__ uint32_t s_base;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
+    // A block without survivors has nothing to place (most blocks of a large world under a narrow frustum); only the last
+    // block must go on, it publishes the grand total.
+    if (block != num_gather_blocks - 1 && a.block_totals[block] == 0u)
+        return;
+
     // base = survivors in all earlier blocks
     uint32_t part = 0;
     for (int i = tid; i < block; i += 256)
