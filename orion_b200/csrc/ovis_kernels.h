@@ -110,6 +110,7 @@ struct MultiArgs {
     const uint32_t *view_require;// per view: non-zero = shadow casters only
     int n_views;
     uint32_t *counts;            // [num_tiles][n_views]: counts after pass A, positions after the scans
+    uint8_t *sub_masks;          // [num_tiles][n_views]: bit s = sub-tile s holds a survivor of the view (A writes, C reads)
     uint32_t *block_totals;      // [num_blocks][n_views], zero before pass A
     uint32_t *group_hits;        // [num_tiles][ceil(n_groups / 32)]: bit = group had a candidate (A writes, C reads)
     const long long *csr_offsets;// [n_views + 1] start of each view's list (valid after the scans)

@@ -48,8 +48,10 @@ multi_pass_kernel(const __grid_constant__ MultiArgs a) {
     const int64_t vstride = a.stride >> 2;
 
     for (int tile = blockIdx.x * kMultiWarps + warp; tile < a.num_tiles; tile += warps_total) {
+        // counters[v]: bits 0-15 survivors of view v so far in this supertile; bits 16-23 (pass A: collected, pass C:
+        // loaded) which of the 8 sub-tiles hold a survivor of view v - pass C repeats the exact tests only there
         for (int v = lane; v < a.n_views; v += 32)
-            counters[v] = 0u;
+            counters[v] = WRITE ? (uint32_t)a.sub_masks[(int64_t)tile * a.n_views + v] << 16 : 0u;
         // pass A finds which groups have any candidate in this supertile; pass C only revisits those
         for (int k = lane; k < hit_words; k += 32)
             hits[k] = WRITE ? a.group_hits[(int64_t)tile * hit_words + k] : 0u;
@@ -150,6 +152,8 @@ multi_pass_kernel(const __grid_constant__ MultiArgs a) {
 
                     for (int vi = 0; vi < grp.n_views; vi++) {
                         const int view = grp.first_view + vi;
+                        if (WRITE && !((counters[view] >> (16 + sub)) & 1u))              // pass A found nobody here
+                            continue;
                         uint32_t keep = a.view_require[view] ? (cand & caster) : cand;
                         const float4 *pl = a.planes + 6 * view;
 #pragma unroll
@@ -175,7 +179,7 @@ multi_pass_kernel(const __grid_constant__ MultiArgs a) {
                         }
                         const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
                         if (WRITE) {
-                            long long pos = a.csr_offsets[view] + (long long)row[view] + counters[view] + (incl - c);
+                            long long pos = a.csr_offsets[view] + (long long)row[view] + (counters[view] & 0xffffu) + (incl - c);
 #pragma unroll
                             for (int j = 0; j < 4; j++)
                                 if (keep & (1u << j)) {
@@ -185,7 +189,7 @@ multi_pass_kernel(const __grid_constant__ MultiArgs a) {
                         }
                         __syncwarp();
                         if (lane == 0)
-                            counters[view] += total;
+                            counters[view] += WRITE ? total : (total | (0x10000u << sub));    // each (sub, view) comes by once
                         __syncwarp();
                     }
                 }
@@ -203,8 +207,9 @@ multi_pass_kernel(const __grid_constant__ MultiArgs a) {
             uint32_t *totals = a.block_totals + (int64_t)(tile / kGatherTiles) * a.n_views;
             __syncwarp();
             for (int v = lane; v < a.n_views; v += 32) {
-                const uint32_t c = counters[v];
+                const uint32_t c = counters[v] & 0xffffu;
                 out_row[v] = c;
+                a.sub_masks[(int64_t)tile * a.n_views + v] = (uint8_t)(counters[v] >> 16);
                 if (c)
                     atomicAdd(totals + v, c);
             }

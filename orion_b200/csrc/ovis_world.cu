@@ -763,7 +763,8 @@ int cull_views_grouped(OvisWorld *w, int32_t n_views, const float *planes, const
     const int num_blocks = (num_tiles + ovis::kGatherTiles - 1) / ovis::kGatherTiles;
     const int64_t pass_views = std::min<int64_t>(n_views, ovis::kMultiMaxViews);
     if ((int64_t)num_tiles * pass_views > w->cap_mv_counts) {
-        OVIS_TRY(grow(w->d_mv_counts, 0, (int64_t)num_tiles * pass_views, w->stream, false));
+        // counts (one word) followed by the sub-tile masks (one byte) per (supertile, view)
+        OVIS_TRY(grow(w->d_mv_counts, 0, ((int64_t)num_tiles * pass_views * 5 + 3) / 4, w->stream, false));
         w->cap_mv_counts = (int64_t)num_tiles * pass_views;
     }
     if ((int64_t)num_blocks * pass_views > w->cap_mv_totals) {
@@ -804,7 +805,7 @@ int cull_views_grouped(OvisWorld *w, int32_t n_views, const float *planes, const
     for (int attempt = 0; attempt < 2; attempt++) {
         OVIS_CUDA(cudaMemsetAsync(w->d_csr_offsets, 0, sizeof(long long), w->stream));
         for (const Pass &p : passes) {
-            ovis::MultiArgs a;
+            ovis::MultiArgs a{};
             a.bounds = w->d_world;
             a.stride = w->cap_ent;
             a.n = w->n_ent;
@@ -817,6 +818,7 @@ int cull_views_grouped(OvisWorld *w, int32_t n_views, const float *planes, const
             a.view_require = w->d_mv_require + p.v0;
             a.n_views = p.v1 - p.v0;
             a.counts = w->d_mv_counts;
+            a.sub_masks = reinterpret_cast<uint8_t *>(w->d_mv_counts + w->cap_mv_counts);
             a.block_totals = w->d_mv_totals;
             a.group_hits = w->d_mv_hits;
             a.csr_offsets = w->d_csr_offsets + p.v0;
