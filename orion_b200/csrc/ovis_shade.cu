@@ -20,6 +20,8 @@
 
 #include "orion_vis.h"
 
+#include <cstdlib>
+
 namespace ovis {
 
 namespace {
@@ -124,10 +126,9 @@ __device__ __forceinline__ float calc_shadow(const Lighting &d, const float *lig
 }
 
 // lighting.h:149-168
-__device__ __forceinline__ F3 blinn_phong(const Lighting &d, F3 direction, const float *light, F3 view_position) {
+__device__ __forceinline__ F3 blinn_phong(const Lighting &d, F3 direction, const float *light, F3 to_view) {
     const F3 light_colour = f3(light[L_COLOUR], light[L_COLOUR + 1], light[L_COLOUR + 2]);
     const F3 to_light = f3(-direction.x, -direction.y, -direction.z);
-    const F3 to_view = normalize3(view_position - d.position);
     const float angle = max_glsl(dot3(d.normal, to_light), 0.0f);
     F3 colour = (d.diffuse * light_colour) * (light[L_INTENSITY] * angle);
     const F3 half_vector = normalize3(to_light + to_view);
@@ -138,7 +139,7 @@ __device__ __forceinline__ F3 blinn_phong(const Lighting &d, F3 direction, const
 
 // lighting.h:173-211. `may_skip`: light and pixel are known to be finite and in bounds (see kLightSkippable), so that an
 // attenuation of exactly 0 means a contribution of exactly +-0 - which the caller's sum would not notice.
-__device__ __forceinline__ bool calc_light(const Lighting &d, const float *light, int type, F3 view_position, const float *map, int size,
+__device__ __forceinline__ bool calc_light(const Lighting &d, const float *light, int type, F3 to_view, const float *map, int size,
                                            bool may_skip, F3 &out) {
     if (type == OVIS_LIGHT_AMBIENT) {
         out = (d.diffuse * f3(light[L_COLOUR], light[L_COLOUR + 1], light[L_COLOUR + 2])) * light[L_INTENSITY];
@@ -163,12 +164,14 @@ __device__ __forceinline__ bool calc_light(const Lighting &d, const float *light
         attenuation /= light[L_ATT_CONSTANT] + (light[L_ATT_LINEAR] * distance) + (light[L_ATT_EXP] * distance * distance);
     }
     attenuation *= calc_shadow(d, light, type, map, size);
-    out = blinn_phong(d, direction, light, view_position) * attenuation;
+    out = blinn_phong(d, direction, light, to_view) * attenuation;
     return true;
 }
 
 constexpr int kShadeChunk = 16;    // lights staged per round: 16 x 208 B of shared memory
+constexpr uint32_t kShadeTileRejectMinLights = 8;
 
+template <bool TILED>
 __global__ void __launch_bounds__(256)
 shade_deferred_kernel(const __grid_constant__ ShadeArgs a) {
     __shared__ float s_light[kShadeChunk * L_FLOATS];
@@ -179,12 +182,25 @@ shade_deferred_kernel(const __grid_constant__ ShadeArgs a) {
     if (tid < V_FLOATS)
         s_view[tid] = a.view_uniforms[tid];
     __syncthreads();
-    const int64_t pixel = (int64_t)blockIdx.x * blockDim.x + tid;
-    const bool active = pixel < (int64_t)a.width * a.height;
+    // a CTA shades a 16 x 16 pixel tile: neighbours on screen are neighbours in space, which is what makes the
+    // tile-level light rejection below (and warp-uniform out-of-range skips) effective
+    int px, py;
+    bool active;
+    if (TILED) {
+        const int tiles_x = (a.width + 15) >> 4;
+        px = (int)(blockIdx.x % tiles_x) * 16 + (tid & 15);
+        py = (int)(blockIdx.x / tiles_x) * 16 + (tid >> 4);
+        active = px < a.width && py < a.height;
+    } else {                                                  // OVIS_SHADE_LINEAR=1 (tuning): 256 consecutive pixels per CTA
+        const int64_t i = (int64_t)blockIdx.x * 256 + tid;
+        active = i < (int64_t)a.width * a.height;
+        px = (int)(i % a.width);
+        py = (int)(i / a.width);
+    }
+    const int64_t pixel = (int64_t)py * a.width + px;
     Lighting d = {};
     bool pixel_clean = false;
     if (active) {
-        const int px = (int)(pixel % a.width), py = (int)(pixel / a.width);
         const float4 sa = __ldg(reinterpret_cast<const float4 *>(a.buffer_a) + pixel);
         const float4 sb = __ldg(reinterpret_cast<const float4 *>(a.buffer_b) + pixel);
         const float4 sc = __ldg(reinterpret_cast<const float4 *>(a.buffer_c) + pixel);
@@ -206,10 +222,51 @@ shade_deferred_kernel(const __grid_constant__ ShadeArgs a) {
                       fabsf(d.specular.x) <= 1e6f && fabsf(d.specular.y) <= 1e6f && fabsf(d.specular.z) <= 1e6f &&
                       fabsf(d.position.x) <= 1e18f && fabsf(d.position.y) <= 1e18f && fabsf(d.position.z) <= 1e18f;
     }
-    const F3 view_position = f3(s_view[V_POSITION], s_view[V_POSITION + 1], s_view[V_POSITION + 2]);
+    // ---- bounds of the tile's positions; usable only if every pixel of the tile is clean
+    __shared__ float s_box[8][6];
+    __shared__ int s_tile_clean;
+    __shared__ unsigned char s_skip[kShadeChunk];
     uint32_t m = *a.d_visible_count;
     if ((int64_t)m > a.max_visible)
         m = (uint32_t)a.max_visible;
+    if (m <= kShadeTileRejectMinLights) {                     // too few lights for the bounds to pay for themselves
+        if (tid == 0)
+            s_tile_clean = 0;
+    } else {
+        const float inf = __int_as_float(0x7f800000);
+        const bool use = active && pixel_clean;
+        float lo[3] = { use ? d.position.x : inf, use ? d.position.y : inf, use ? d.position.z : inf };
+        float hi[3] = { use ? d.position.x : -inf, use ? d.position.y : -inf, use ? d.position.z : -inf };
+#pragma unroll
+        for (int c = 0; c < 3; c++)
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                lo[c] = fminf(lo[c], __shfl_xor_sync(0xffffffffu, lo[c], o));
+                hi[c] = fmaxf(hi[c], __shfl_xor_sync(0xffffffffu, hi[c], o));
+            }
+        const int all_clean = __syncthreads_and(!active || pixel_clean);
+        if ((tid & 31) == 0)
+            for (int c = 0; c < 3; c++) {
+                s_box[tid >> 5][c] = lo[c];
+                s_box[tid >> 5][3 + c] = hi[c];
+            }
+        __syncthreads();
+        if (tid < 3) {
+            float l = s_box[0][tid], h = s_box[0][3 + tid];
+            for (int wv = 1; wv < 8; wv++) {
+                l = fminf(l, s_box[wv][tid]);
+                h = fmaxf(h, s_box[wv][3 + tid]);
+            }
+            s_box[0][tid] = l;
+            s_box[0][3 + tid] = h;
+        }
+        if (tid == 0)
+            s_tile_clean = all_clean;
+        __syncthreads();
+    }
+    // normalize(view.position - data.position) does not depend on the light: the shader recomputes it per light, here it
+    // is computed once per pixel (same operations, same bits)
+    const F3 to_view = normalize3(f3(s_view[V_POSITION], s_view[V_POSITION + 1], s_view[V_POSITION + 2]) - d.position);
     F3 sum = f3(0.0f, 0.0f, 0.0f);
     for (uint32_t base = 0; base < m; base += kShadeChunk) {
         const int n = (int)min((uint32_t)kShadeChunk, m - base);
@@ -220,12 +277,29 @@ shade_deferred_kernel(const __grid_constant__ ShadeArgs a) {
         }
         if (tid < n) {
             const uint32_t id = a.d_visible[base + tid];
-            s_type[tid] = a.light_types[id];
-            s_map[tid] = a.shadow_maps ? a.shadow_maps[id] : nullptr;
+            // every load is issued before any of them is used: one memory round trip, not a chain of them
+            const float *light = a.light_table + (size_t)id * L_FLOATS;
+            const int packed_type = __ldg(a.light_types + id);
+            const float *map = a.shadow_maps ? a.shadow_maps[id] : nullptr;
+            const float r = __ldg(light + L_RANGE);
+            const float p0 = __ldg(light + 0), p1 = __ldg(light + 1), p2 = __ldg(light + 2);
+            s_type[tid] = packed_type;
+            s_map[tid] = map;
+            // Tile-level rejection: every pixel of the tile is clean, the light is skippable (see kLightSkippable) and not
+            // a shadowed spot light, and the tile's bounds are farther from the light than its range with a margin far
+            // above the rounding of the shader's own distance: then every pixel's attenuation is exactly 0.
+            const float g0 = fmaxf(fmaxf(s_box[0][0] - p0, p0 - s_box[0][3]), 0.0f);
+            const float g1 = fmaxf(fmaxf(s_box[0][1] - p1, p1 - s_box[0][4]), 0.0f);
+            const float g2 = fmaxf(fmaxf(s_box[0][2] - p2, p2 - s_box[0][5]), 0.0f);
+            const float d2 = g0 * g0 + g1 * g1 + g2 * g2;
+            const bool allowed = s_tile_clean && (packed_type & kLightSkippable) && !((packed_type & 0xff) == OVIS_LIGHT_SPOT && map);
+            s_skip[tid] = (allowed && (r < 0.0f || d2 > r * r * 1.001f)) ? 1 : 0;
         }
         __syncthreads();
         if (active)
             for (int l = 0; l < n; l++) {
+                if (s_skip[l])
+                    continue;
                 const float *light = s_light + l * L_FLOATS;
                 const int type = s_type[l] & 0xff;
                 // Out of the light's range the shader multiplies a finite colour by an attenuation of exactly 0 and the
@@ -234,7 +308,7 @@ shade_deferred_kernel(const __grid_constant__ ShadeArgs a) {
                 // work is skipped; a shadowed spot light is not (its projective divide can produce NaN off-range).
                 const bool may_skip = (s_type[l] & kLightSkippable) && pixel_clean && !(type == OVIS_LIGHT_SPOT && s_map[l]);
                 F3 colour;
-                if (calc_light(d, light, type, view_position, s_map[l], a.shadow_size, may_skip, colour))
+                if (calc_light(d, light, type, to_view, s_map[l], a.shadow_size, may_skip, colour))
                     sum = sum + colour;
             }
     }
@@ -273,9 +347,15 @@ post_effects_kernel(int64_t n, const float4 *__restrict__ in, uint32_t effects, 
 }  // namespace
 
 void launch_shade_deferred(const ShadeArgs &a, cudaStream_t s) {
+    static const bool linear = getenv("OVIS_SHADE_LINEAR") && atoi(getenv("OVIS_SHADE_LINEAR")) != 0;
+    const int64_t tiles = (int64_t)((a.width + 15) / 16) * ((a.height + 15) / 16);
     const int64_t pixels = (int64_t)a.width * a.height;
-    if (pixels > 0)
-        shade_deferred_kernel<<<(unsigned)((pixels + 255) / 256), 256, 0, s>>>(a);
+    if (pixels <= 0)
+        return;
+    if (linear)
+        shade_deferred_kernel<false><<<(unsigned)((pixels + 255) / 256), 256, 0, s>>>(a);
+    else
+        shade_deferred_kernel<true><<<(unsigned)tiles, 256, 0, s>>>(a);
 }
 
 void launch_post_effects(int64_t n_pixels, const float *in, uint32_t effects, float exposure, float white_point, float gamma, float *out,

@@ -226,3 +226,46 @@ def test_sparse_lights_and_unclean_inputs(oracle):
         assert np.array_equal(np.isnan(got), np.isnan(want)), i
         _close(got, want)
     world.close()
+
+
+def test_coherent_scene_tile_rejection(oracle):
+    """A ground plane seen in perspective with many short-range lights standing on it: most (tile, light) pairs are out of
+    range and are rejected per 16 x 16 tile. One tile carries an unclean pixel (so it must not take the shortcut), the
+    frame size is not a multiple of the tile size."""
+    import torch
+    rng = np.random.default_rng(808)
+    w, h, n = 333, 187, 160
+    view = scenes.make_view((0, 6, 40), scenes.quat_yaw_pitch(0.0, -12.0), 75.0, 0.1, 500.0, w, h)
+    gbuf = util.ground_gbuffer(rng, oracle, view, w, h)
+    gbuf[1][100, 200, 0] = np.nan                                       # unclean pixel inside tile (12, 6)
+    gbuf[2][40, 17, 3] = 1e9
+    lights, att, bias = util.lights_for_shading(rng, n, view)
+    lights["type"] = np.where(rng.random(n) < 0.5, scenes.LIGHT_POINT, scenes.LIGHT_SPOT)
+    lights["type"][:4] = (scenes.LIGHT_AMBIENT, scenes.LIGHT_DIRECTIONAL, scenes.LIGHT_POINT, scenes.LIGHT_SPOT)
+    lights["position"][:, 0] = rng.uniform(-120, 120, n)
+    lights["position"][:, 1] = rng.uniform(0.5, 5.0, n)
+    lights["position"][:, 2] = rng.uniform(-250, 35, n)
+    lights["direction"][:, 1] = -np.abs(lights["direction"][:, 1]) - 0.5   # pointing down at the ground
+    lights["range"] = rng.uniform(4.0, 25.0, n)
+    lights["range"][2] = 400.0                                          # one light that reaches everything
+    world = lib.World(0)
+    world.add_lights(lights)
+    for i in range(n):
+        world.set_light_shading(i, att[i], float(bias[i]))
+    blocks = np.stack([oracle.light_uniforms(l, x, float(y)) for l, x, y in zip(lights, att, bias)])
+    vb = oracle.view_uniforms(view)
+    ids = np.arange(n, dtype=np.uint32)
+    want = oracle.shade_deferred(*gbuf, vb, blocks, lights["type"])
+    got = _shade(torch, world, w, h, gbuf, vb, ids)
+    assert np.array_equal(np.isnan(got), np.isnan(want)) and np.isnan(want[100, 200, 0])
+    _close(got, want)
+    lit = (want[..., :3] > 0).any(axis=2)
+    assert 0.3 < lit.mean() < 1.0
+    size = 32
+    maps = [rng.uniform(0.9, 1.0, (size, size) if l["type"] == scenes.LIGHT_SPOT else (6, size, size)).astype(np.float32)
+            if l["flags"] & 1 and l["type"] >= scenes.LIGHT_POINT else None for l in lights]
+    want = oracle.shade_deferred(*gbuf, vb, blocks, lights["type"], maps, size)
+    got = _shade(torch, world, w, h, gbuf, vb, ids, maps, size)
+    assert np.array_equal(np.isnan(got), np.isnan(want))
+    _close(got, want)
+    world.close()

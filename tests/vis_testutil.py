@@ -188,3 +188,37 @@ def lights_for_shading(rng, n, view, extent=30.0):
     att = np.stack([rng.uniform(0.5, 1.0, n), rng.uniform(0.0, 0.1, n), rng.uniform(0.0, 0.01, n)], axis=1).astype(np.float32)
     bias = rng.uniform(-0.005, 0.0, n).astype(np.float32)
     return lights, att, bias
+
+
+def ground_gbuffer(rng, oracle, view, width, height):
+    """A spatially coherent headless G-buffer: what the camera sees of the ground plane y = 0 (normal +Y, mottled
+    colours), sky above the horizon. Depth is derived in float64 and stored as float32; the shader reconstructs its own
+    positions from it."""
+    mats, _ = oracle.view_matrices(view)
+    mats = np.asarray(mats, dtype=np.float64).reshape(4, 4, 4)
+    vp, inv = mats[2].T, mats[3].T                                      # stored column-major
+    px, py = np.meshgrid(np.arange(width, dtype=np.float64), np.arange(height, dtype=np.float64))
+    nx, ny = px / width * 2.0 - 1.0, py / height * 2.0 - 1.0
+
+    def unproject(z):
+        h = np.stack([nx, ny, np.full_like(nx, z), np.ones_like(nx)], axis=-1) @ inv.T
+        return h[..., :3] / h[..., 3:4]
+
+    p0, p1 = unproject(0.0), unproject(1.0)
+    dy = p1[..., 1] - p0[..., 1]
+    with np.errstate(divide="ignore", invalid="ignore"):
+        t = -p0[..., 1] / dy
+    hit = (dy < 0) & (t > 0) & (t <= 1)
+    pos = p0 + np.where(hit, t, 1.0)[..., None] * (p1 - p0)
+    clip = np.concatenate([pos, np.ones_like(pos[..., :1])], axis=-1) @ vp.T
+    depth = np.where(hit, clip[..., 2] / clip[..., 3], 1.0).astype(np.float32)
+    a = np.ones((height, width, 4), dtype=np.float32)
+    a[..., :3] = (np.array([0.0, 1.0, 0.0], dtype=np.float32) + np.float32(1.0)) / np.float32(2.0)
+    b = np.ones((height, width, 4), dtype=np.float32)
+    b[..., :3] = rng.uniform(0.3, 0.9, (height, width, 3))
+    c = np.empty((height, width, 4), dtype=np.float32)
+    c[..., :3] = rng.uniform(0.1, 0.5, (height, width, 3))
+    c[..., 3] = rng.uniform(8, 64, (height, width))
+    b[~hit, :3] = 0
+    c[~hit] = 0
+    return a, b, c, depth

@@ -136,6 +136,49 @@ def main():
                             "note": "pixel-light pairs beyond the light's range are skipped where that is provably exact"}
     world2.close()
 
+    # a spatially coherent frame: the ground plane in perspective, 256 point / spot lights of range 5..25 standing on it
+    view3 = scenes.make_view((0, 6, 40), scenes.quat_yaw_pitch(0.0, -12.0), 75.0, 0.1, 500.0, w, h)
+    gbuf3 = util.ground_gbuffer(rng, oracle, view3, w, h)
+    lights3, att3, bias3 = util.lights_for_shading(rng, n_max, view3)
+    lights3["type"] = np.where(rng.random(n_max) < 0.5, scenes.LIGHT_POINT, scenes.LIGHT_SPOT)
+    lights3["position"][:, 0] = rng.uniform(-120, 120, n_max)
+    lights3["position"][:, 1] = rng.uniform(0.5, 5.0, n_max)
+    lights3["position"][:, 2] = rng.uniform(-250, 35, n_max)
+    lights3["direction"][:, 1] = -np.abs(lights3["direction"][:, 1]) - 0.5
+    lights3["range"] = rng.uniform(5.0, 25.0, n_max)
+    world3 = lib.World(0)
+    world3.set_stream(stream.cuda_stream)
+    world3.add_lights(lights3)
+    for i in range(n_max):
+        world3.set_light_shading(i, att3[i], float(bias3[i]))
+    blocks3 = np.stack([oracle.light_uniforms(l, a, float(b)) for l, a, b in zip(lights3, att3, bias3)])
+    vb3 = oracle.view_uniforms(view3)
+    with torch.cuda.stream(stream):
+        d3 = [torch.from_numpy(x).cuda() for x in gbuf3]
+        d_vb3 = torch.from_numpy(vb3.copy()).cuda()
+    torch.cuda.synchronize()
+
+    def shade_ground():
+        world3.shade_deferred_device(w, h, d3[0].data_ptr(), d3[1].data_ptr(), d3[2].data_ptr(), d3[3].data_ptr(), d_vb3.data_ptr(),
+                                     d_out.data_ptr(), ids.data_ptr(), cnt.data_ptr(), n_max)
+
+    ms = timed(stream, shade_ground)
+    y0 = h // 2                                                          # a crop from the middle rows, where the lights are
+    crop3 = [np.ascontiguousarray(x[y0:y0 + ch, :cw]) for x in gbuf3]
+    got = d_out.view(h, w, 4)[y0:y0 + ch, :cw].cpu().numpy()
+    # the oracle derives positions from pixel coordinates: shade the crop as a frame whose viewport starts at (0, -y0)
+    vb3_crop = oracle.view_uniforms(view3, (0, -y0))
+    t0 = time.perf_counter()
+    want = oracle.shade_deferred(*crop3, vb3_crop, blocks3, lights3["type"])
+    cpu_ms = (time.perf_counter() - t0) * 1e3
+    out["ground_plane_256_lights"] = {"lights": n_max, "light_range": "5..25", "gpu_ms": ms,
+                                      "ns_per_pixel_light": ms * 1e6 / (w * h * n_max),
+                                      "cpu_1core_ms_scaled_to_frame": cpu_ms * (w * h) / (cw * ch),
+                                      "lit_fraction_of_crop": float((want[..., :3] > 0).any(axis=2).mean()),
+                                      "max_rel_err_vs_oracle": rel_err(got, want),
+                                      "note": "16x16-pixel tiles reject lights whose range ends before the tile's position bounds"}
+    world3.close()
+
     def post():
         world.post_effects_device(w * h, d_out.data_ptr(), d_post.data_ptr(), lib.POST_TONEMAP | lib.POST_GAMMA, 1.5, 11.2, 2.2)
 
