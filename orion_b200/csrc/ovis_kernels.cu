@@ -269,7 +269,7 @@ __device__ __forceinline__ void wait_flags_warp(const uint32_t *flags, int n, ui
     __syncwarp();
 }
 
-template <int GROUPS, bool MASKED>
+template <int GROUPS, bool MASKED, bool PACKED = false>
 __device__ __forceinline__ void cull_test_body(const CullArgs &a) {
     constexpr int WT = 128 * GROUPS;                       // entities per warp tile
     const int lane = threadIdx.x & 31;
@@ -314,6 +314,10 @@ __device__ __forceinline__ void cull_test_body(const CullArgs &a) {
 #pragma unroll
             for (int p = 0; p < 6; p++) {                                     // Left Right Top Bottom Near Far
                 const float nx = a.planes[p].x, ny = a.planes[p].y, nz = a.planes[p].z, d = a.planes[p].w;
+                if (PACKED) {
+                    k &= ~outside_plane4(nx, ny, nz, d, mnx[g], mny[g], mnz[g], mxx[g], mxy[g], mxz[g]);
+                    continue;
+                }
                 if (outside_plane(nx, ny, nz, d, mnx[g].x, mny[g].x, mnz[g].x, mxx[g].x, mxy[g].x, mxz[g].x)) k &= ~1u;
                 if (outside_plane(nx, ny, nz, d, mnx[g].y, mny[g].y, mnz[g].y, mxx[g].y, mxy[g].y, mxz[g].y)) k &= ~2u;
                 if (outside_plane(nx, ny, nz, d, mnx[g].z, mny[g].z, mnz[g].z, mxx[g].z, mxy[g].z, mxz[g].z)) k &= ~4u;
@@ -353,7 +357,183 @@ __device__ __forceinline__ void cull_test_body(const CullArgs &a) {
     }
 }
 
+// ---- software-pipelined form of the same pass ----------------------------------------------------------------------
+// In cull_test_body a warp has loads in flight only while it ranks the previous tile (its registers are reused), i.e. about
+// a quarter of the time; tools/read_probe.cu shows that the same bytes stream in 45 us when every warp always has loads
+// outstanding. Here a warp owns TWO register sets and requests tile t + 1 before it tests tile t.
+template <int GROUPS>
+struct TileRegs {
+    float4 mnx[GROUPS], mny[GROUPS], mnz[GROUPS], mxx[GROUPS], mxy[GROUPS], mxz[GROUPS];
+    uint32_t mask_bits[GROUPS];
+};
+
 template <int GROUPS, bool MASKED>
+__device__ __forceinline__ void tile_load(TileRegs<GROUPS> &r, const CullArgs &a, const float4 *__restrict__ bounds, int64_t vstride,
+                                          int wt, int lane) {
+    if (wt >= a.num_tiles)
+        return;
+#pragma unroll
+    for (int g = 0; g < GROUPS; g++) {
+        const int64_t v = (int64_t)wt * (32 * GROUPS) + g * 32 + lane;
+        r.mnx[g] = __ldg(bounds + 0 * vstride + v); r.mny[g] = __ldg(bounds + 1 * vstride + v); r.mnz[g] = __ldg(bounds + 2 * vstride + v);
+        r.mxx[g] = __ldg(bounds + 3 * vstride + v); r.mxy[g] = __ldg(bounds + 4 * vstride + v); r.mxz[g] = __ldg(bounds + 5 * vstride + v);
+        if (MASKED)
+            r.mask_bits[g] = __ldg(a.mask + (v >> 3));
+    }
+}
+
+template <int GROUPS, bool MASKED>
+__device__ __forceinline__ void tile_process(const TileRegs<GROUPS> &r, const CullArgs &a, int wt, int lane) {
+    constexpr int WT = 128 * GROUPS;
+    uint32_t keep[GROUPS];
+#pragma unroll
+    for (int g = 0; g < GROUPS; g++) {
+        const int64_t e0 = ((int64_t)wt * (32 * GROUPS) + g * 32 + lane) << 2;
+        uint32_t k = 0xfu;
+        if (MASKED)
+            k = (r.mask_bits[g] >> (e0 & 31)) & 0xfu;
+        if (e0 + 3 >= a.n) {
+            int64_t valid = a.n - e0;
+            k &= valid <= 0 ? 0u : ((1u << valid) - 1u);
+        }
+#pragma unroll
+        for (int p = 0; p < 6; p++) {
+            const float nx = a.planes[p].x, ny = a.planes[p].y, nz = a.planes[p].z, d = a.planes[p].w;
+            if (outside_plane(nx, ny, nz, d, r.mnx[g].x, r.mny[g].x, r.mnz[g].x, r.mxx[g].x, r.mxy[g].x, r.mxz[g].x)) k &= ~1u;
+            if (outside_plane(nx, ny, nz, d, r.mnx[g].y, r.mny[g].y, r.mnz[g].y, r.mxx[g].y, r.mxy[g].y, r.mxz[g].y)) k &= ~2u;
+            if (outside_plane(nx, ny, nz, d, r.mnx[g].z, r.mny[g].z, r.mnz[g].z, r.mxx[g].z, r.mxy[g].z, r.mxz[g].z)) k &= ~4u;
+            if (outside_plane(nx, ny, nz, d, r.mnx[g].w, r.mny[g].w, r.mnz[g].w, r.mxx[g].w, r.mxy[g].w, r.mxz[g].w)) k &= ~8u;
+        }
+        keep[g] = k;
+    }
+    uint32_t base = 0;
+    uint32_t *slot = a.staging + (int64_t)wt * WT;
+#pragma unroll
+    for (int g = 0; g < GROUPS; g++) {
+        uint32_t sum = __popc(keep[g]);
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            uint32_t up = __shfl_up_sync(0xffffffffu, sum, o);
+            if (lane >= o)
+                sum += up;
+        }
+        if (keep[g]) {
+            uint32_t rank = base + sum - __popc(keep[g]);
+            const uint32_t e0 = (uint32_t)(((int64_t)wt * (32 * GROUPS) + g * 32 + lane) << 2) + a.id_base;
+#pragma unroll
+            for (int j = 0; j < 4; j++)
+                if (keep[g] & (1u << j))
+                    slot[rank++] = e0 + j;
+        }
+        base += __shfl_sync(0xffffffffu, sum, 31);
+    }
+    if (lane == 0) {
+        a.tile_counts[wt] = base;
+        if (base)
+            atomicAdd(a.block_totals + wt / kGatherTiles, base);
+    }
+}
+
+template <int GROUPS, bool MASKED>
+__global__ void __launch_bounds__(kCullThreads, GROUPS == 1 ? 2 : 1)
+cull_test_pipelined_kernel(const __grid_constant__ CullArgs a) {
+    if (a.n_wait && blockIdx.x == 0 && threadIdx.x < 32)
+        wait_flags_warp(a.wait_flags, a.n_wait, a.wait_value, a.error_flag);
+    const int lane = threadIdx.x & 31;
+    const int warps_total = gridDim.x * (kCullThreads / 32);
+    const float4 *__restrict__ bounds = reinterpret_cast<const float4 *>(a.bounds);
+    const int64_t vstride = a.stride >> 2;
+    for (int i = blockIdx.x * kCullThreads + threadIdx.x; i < a.num_blocks; i += gridDim.x * kCullThreads)
+        a.block_totals_next[i] = 0u;
+    TileRegs<GROUPS> ra, rb;
+    int wt = blockIdx.x * (kCullThreads / 32) + (threadIdx.x >> 5);
+    tile_load<GROUPS, MASKED>(ra, a, bounds, vstride, wt, lane);
+    while (wt < a.num_tiles) {
+        tile_load<GROUPS, MASKED>(rb, a, bounds, vstride, wt + warps_total, lane);
+        tile_process<GROUPS, MASKED>(ra, a, wt, lane);
+        wt += warps_total;
+        if (wt >= a.num_tiles)
+            break;
+        tile_load<GROUPS, MASKED>(ra, a, bounds, vstride, wt + warps_total, lane);
+        tile_process<GROUPS, MASKED>(rb, a, wt, lane);
+        wt += warps_total;
+    }
+}
+
+// ---- asynchronous-copy form: the bounds stream into a per-warp shared-memory ring --------------------------------------
+// Every lane copies the 16 bytes it will itself test (cp.async, global -> shared, no registers held while in flight) STAGES
+// - 1 tiles ahead, so each warp keeps (STAGES - 1) x 3 KB outstanding all the time however long its arithmetic takes; a
+// lane only ever reads back what it copied itself, so there is no barrier and no cross-lane visibility to arrange.
+template <int STAGES>
+struct AsyncRing {
+    static constexpr int kStageBytes = 6 * 32 * 16 + 32 * 4;          // six float4 rows + one mask word per lane
+    static constexpr int kWarpBytes = STAGES * kStageBytes;
+    static constexpr int kCtaBytes = (kCullThreads / 32) * kWarpBytes;
+};
+
+__device__ __forceinline__ void cp_async_16(void *smem_dst, const void *gmem_src) {
+    const uint32_t dst = (uint32_t)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(gmem_src) : "memory");
+}
+__device__ __forceinline__ void cp_async_4(void *smem_dst, const void *gmem_src) {
+    const uint32_t dst = (uint32_t)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(gmem_src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+template <bool MASKED, int STAGES>
+__global__ void __launch_bounds__(kCullThreads, 2)
+cull_test_async_kernel(const __grid_constant__ CullArgs a) {
+    extern __shared__ __align__(16) unsigned char s_ring_bytes[];
+    if (a.n_wait && blockIdx.x == 0 && threadIdx.x < 32)
+        wait_flags_warp(a.wait_flags, a.n_wait, a.wait_value, a.error_flag);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int warps_total = gridDim.x * (kCullThreads / 32);
+    const float4 *__restrict__ bounds = reinterpret_cast<const float4 *>(a.bounds);
+    const int64_t vstride = a.stride >> 2;
+    for (int i = blockIdx.x * kCullThreads + threadIdx.x; i < a.num_blocks; i += gridDim.x * kCullThreads)
+        a.block_totals_next[i] = 0u;
+    unsigned char *ring = s_ring_bytes + warp * AsyncRing<STAGES>::kWarpBytes;
+
+    auto issue = [&](int wt, int stage) {
+        if (wt < a.num_tiles) {
+            float4 *rows = reinterpret_cast<float4 *>(ring + stage * AsyncRing<STAGES>::kStageBytes);
+            const int64_t v = (int64_t)wt * 32 + lane;                         // float4 index: entities 4v .. 4v+3
+#pragma unroll
+            for (int c = 0; c < 6; c++)
+                cp_async_16(rows + c * 32 + lane, bounds + c * vstride + v);
+            if (MASKED)
+                cp_async_4(reinterpret_cast<uint32_t *>(rows + 6 * 32) + lane, a.mask + (v >> 3));
+        }
+        cp_async_commit();                                                     // an empty group keeps the count uniform
+    };
+
+    int wt = blockIdx.x * (kCullThreads / 32) + warp;
+#pragma unroll
+    for (int st = 0; st < STAGES - 1; st++)
+        issue(wt + st * warps_total, st);
+    int stage = 0;
+    for (; wt < a.num_tiles; wt += warps_total) {
+        int ahead = stage + STAGES - 1;
+        if (ahead >= STAGES)
+            ahead -= STAGES;
+        issue(wt + (STAGES - 1) * warps_total, ahead);
+        cp_async_wait<STAGES - 1>();                                           // this lane's copies of tile wt have landed
+        const float4 *rows = reinterpret_cast<const float4 *>(ring + stage * AsyncRing<STAGES>::kStageBytes);
+        TileRegs<1> r;
+        r.mnx[0] = rows[0 * 32 + lane]; r.mny[0] = rows[1 * 32 + lane]; r.mnz[0] = rows[2 * 32 + lane];
+        r.mxx[0] = rows[3 * 32 + lane]; r.mxy[0] = rows[4 * 32 + lane]; r.mxz[0] = rows[5 * 32 + lane];
+        if (MASKED)
+            r.mask_bits[0] = reinterpret_cast<const uint32_t *>(rows + 6 * 32)[lane];
+        tile_process<1, MASKED>(r, a, wt, lane);
+        stage = stage + 1 == STAGES ? 0 : stage + 1;
+    }
+    cp_async_wait<0>();
+}
+
+template <int GROUPS, bool MASKED, bool PACKED = false>
 __global__ void __launch_bounds__(kCullThreads, 4 / GROUPS)
 cull_test_kernel(const __grid_constant__ CullArgs a) {
     // Sharded exchange: the segment buffer this frame's gather kernel will refill must have been released by every peer.
@@ -361,7 +541,7 @@ cull_test_kernel(const __grid_constant__ CullArgs a) {
     // this kernel has finished), instead of every gather block paying a round of system-scope loads before its stores.
     if (a.n_wait && blockIdx.x == 0 && threadIdx.x < 32)
         wait_flags_warp(a.wait_flags, a.n_wait, a.wait_value, a.error_flag);
-    cull_test_body<GROUPS, MASKED>(a);
+    cull_test_body<GROUPS, MASKED, PACKED>(a);
 }
 
 // Gather of one block of kGatherTiles warp tiles by one 256-thread CTA; `num_gather_blocks` = blocks in the launch.
@@ -537,13 +717,30 @@ cull_fused_kernel(const __grid_constant__ CullArgs a, const __grid_constant__ Ga
 }
 
 // Launch shapes selectable at run time (OVIS_CULL_VARIANT, tuning only). Variant 0 is the default.
-static const CullVariant kVariants[] = { { 2 }, { 1 }, { 4 } };
+static const CullVariant kVariants[] = { { 2, false, false }, { 1, false, false }, { 4, false, false }, { 1, true, false },
+                                         { 2, true, false },  { 2, false, true },  { 1, false, true },
+                                         { 1, false, false, 4 }, { 1, false, false, 3 } };
 
 int cull_num_variants() { return (int)(sizeof(kVariants) / sizeof(kVariants[0])); }
+int cull_variant_smem(int v) {
+    return kVariants[v].async_stages == 4 ? AsyncRing<4>::kCtaBytes : kVariants[v].async_stages == 3 ? AsyncRing<3>::kCtaBytes : 0;
+}
 CullVariant cull_variant(int v) { return kVariants[v]; }
 
 template <typename F>
 static void with_variant(int variant, bool masked, F &&f) {
+    if (kVariants[variant].async_stages == 4) { if (masked) f(cull_test_async_kernel<true, 4>); else f(cull_test_async_kernel<false, 4>); return; }
+    if (kVariants[variant].async_stages == 3) { if (masked) f(cull_test_async_kernel<true, 3>); else f(cull_test_async_kernel<false, 3>); return; }
+    if (kVariants[variant].pipelined) {
+        if (kVariants[variant].groups == 1) { if (masked) f(cull_test_pipelined_kernel<1, true>); else f(cull_test_pipelined_kernel<1, false>); }
+        else { if (masked) f(cull_test_pipelined_kernel<2, true>); else f(cull_test_pipelined_kernel<2, false>); }
+        return;
+    }
+    if (kVariants[variant].packed) {
+        if (kVariants[variant].groups == 1) { if (masked) f(cull_test_kernel<1, true, true>); else f(cull_test_kernel<1, false, true>); }
+        else { if (masked) f(cull_test_kernel<2, true, true>); else f(cull_test_kernel<2, false, true>); }
+        return;
+    }
     switch (kVariants[variant].groups) {
     case 1: if (masked) f(cull_test_kernel<1, true>); else f(cull_test_kernel<1, false>); break;
     case 2: if (masked) f(cull_test_kernel<2, true>); else f(cull_test_kernel<2, false>); break;
@@ -559,7 +756,9 @@ void launch_cull_test(const CullArgs &a, bool masked, int variant, int grid, cud
         cudaLaunchConfig_t cfg = {};
         cfg.gridDim = dim3((unsigned)grid);
         cfg.blockDim = dim3(kCullThreads);
-        cfg.dynamicSmemBytes = 0;
+        cfg.dynamicSmemBytes = (size_t)cull_variant_smem(variant);
+        if (cfg.dynamicSmemBytes)
+            cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cfg.dynamicSmemBytes);
         cfg.stream = s;
         cudaLaunchAttribute attr[1];
         attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
@@ -603,7 +802,10 @@ void launch_cull_gather(const GatherArgs &a, cudaStream_t s) {
 int cull_test_max_blocks_per_sm(bool masked, int variant) {
     int blocks = 0;
     with_variant(variant, masked, [&](auto kernel) {
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks, kernel, kCullThreads, 0);
+        const int smem = cull_variant_smem(variant);
+        if (smem)
+            cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks, kernel, kCullThreads, (size_t)smem);
     });
     return blocks;
 }

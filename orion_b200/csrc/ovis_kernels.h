@@ -14,6 +14,9 @@ constexpr int kCullTile = 1024;                         // storage padding: a mu
 
 struct CullVariant {
     int groups;                  // float4 groups (4 consecutive entities each) per lane
+    bool pipelined;              // two register sets per warp: tile t + 1 is requested before tile t is tested
+    bool packed;                 // sign-specialised plane code with FMUL2 products (ovis_device.cuh: outside_plane4)
+    int async_stages;            // > 0: cp.async ring of that many stages per warp in shared memory (groups must be 1)
     int tile() const { return 128 * groups; }   // entities per warp tile
 };
 
@@ -206,6 +209,7 @@ void launch_extra_bounds(const uint32_t *entities, const uint32_t *nodes, int64_
 void launch_mark_dirty(const uint32_t *ids, int64_t n, uint8_t *dirty, cudaStream_t s);
 int cull_num_variants();
 CullVariant cull_variant(int v);
+int cull_variant_smem(int v);       // dynamic shared memory per CTA of the variant's test kernel
 void launch_cull_test(const CullArgs &a, bool masked, int variant, int grid, cudaStream_t s, bool overlap_previous_gather);
 void launch_cull_gather(const GatherArgs &a, cudaStream_t s);
 void launch_segments_to_host(const uint32_t *flags, uint32_t value, const uint32_t *segments, long long segment_words,

@@ -67,8 +67,8 @@ struct OvisWorld {
     int num_sms = 0;
     int forced_variant = -1;              // OVIS_CULL_VARIANT (tuning); -1 = pick by size
     bool fused_small = true;              // OVIS_CULL_FUSED=0 (tuning) keeps small worlds on the two-launch path
-    int blocks_per_sm[8][2] = {};         // cull test kernel occupancy per variant: [unmasked, masked]
-    int fused_blocks_per_sm[8][2] = {};   // same for the fused (cooperative) kernel; 0 = not available
+    int blocks_per_sm[16][2] = {};         // cull test kernel occupancy per variant: [unmasked, masked]
+    int fused_blocks_per_sm[16][2] = {};   // same for the fused (cooperative) kernel; 0 = not available
     int64_t launches = 0;
     uint32_t id_base = 0;                 // global id of slot 0 (sharded worlds)
 
@@ -933,7 +933,7 @@ int ovis_world_create(int device, OvisWorld **out_world) {
     }
     if (const char *v = getenv("OVIS_CULL_FUSED"))
         w->fused_small = atoi(v) != 0;
-    for (int v = 0; v < ovis::cull_num_variants() && v < 8; v++) {
+    for (int v = 0; v < ovis::cull_num_variants() && v < 16; v++) {
         w->blocks_per_sm[v][0] = std::max(1, ovis::cull_test_max_blocks_per_sm(false, v));
         w->blocks_per_sm[v][1] = std::max(1, ovis::cull_test_max_blocks_per_sm(true, v));
         w->fused_blocks_per_sm[v][0] = ovis::cull_fused_max_blocks_per_sm(false, v);
