@@ -402,7 +402,7 @@ def run_ours(args, rank: int, local_rank: int, world_size: int):
                                      else "NCCL all-gather")) if world_size > 1 else "1 GPU"),
                    "cache": "inputs larger than L2 (300 MB of bounds per GPU vs 126 MB L2); no flush needed"},
         "cull_ms_per_frame": elapsed_ms / args.steps,
-        "roofline": {"bound": "hbm", "kernel": "ovis::cull_test_kernel<2,false> (dominant: reads every bound once)",
+        "roofline": {"bound": "hbm", "kernel": "ovis::cull_test_kernel<2,false,true> (dominant: reads every bound once)",
                      "achieved": achieved, "peak": peak_gbs, "unit": "GB/s", "frac": achieved / peak_gbs,
                      "traffic": ncu_traffic_bytes() if n == SHARD_ENTITIES else None,
                      "traffic_source": "profiles/r01_cull_test_kernel_ncu.csv (ncu --set full, one launch, same workload)",
@@ -449,7 +449,7 @@ def run_ours(args, rank: int, local_rank: int, world_size: int):
         vis_m = int(sw.block[0].item())
         with torch.cuda.stream(stream):
             line["also"] = {
-                "masked_cull_same_shard": {"kernel": "ovis::cull_test_kernel<2,true> + gather", "ms_mean": float(mk.mean()),
+                "masked_cull_same_shard": {"kernel": "ovis::cull_test_kernel<2,true,true> + gather", "ms_mean": float(mk.mean()),
                                            "achieved_gbs": (24 * n + n / 8 + 4 * vis_m) / (float(mk.mean()) * 1e-3) / 1e9},
                 "config2_1M": config2_extra(torch, lib, stream, scratch, peak_gbs),
             }

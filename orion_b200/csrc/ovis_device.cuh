@@ -180,4 +180,24 @@ __device__ __forceinline__ uint32_t outside_plane4(float nx, float ny, float nz,
     }
 }
 
+// Signed distances of the four P-vertices of a group to one plane (the value the reference compares with 0).
+template <bool SX, bool SY, bool SZ>
+__device__ __forceinline__ float4 plane_dist4_signed(float nx, float ny, float nz, float d, const float4 &mnx, const float4 &mny,
+                                                     const float4 &mnz, const float4 &mxx, const float4 &mxy, const float4 &mxz) {
+    const float4 &px = SX ? mxx : mnx, &py = SY ? mxy : mny, &pz = SZ ? mxz : mnz;
+    float x0, x1, x2, x3, y0, y1, y2, y3, z0, z1, z2, z3;
+    mul2(px.x, px.y, nx, x0, x1); mul2(px.z, px.w, nx, x2, x3);
+    mul2(py.x, py.y, ny, y0, y1); mul2(py.z, py.w, ny, y2, y3);
+    mul2(pz.x, pz.y, nz, z0, z1); mul2(pz.z, pz.w, nz, z2, z3);
+    return make_float4(sub(add(add(x0, y0), z0), d), sub(add(add(x1, y1), z1), d), sub(add(add(x2, y2), z2), d),
+                       sub(add(add(x3, y3), z3), d));
+}
+
+// An entity is rejected iff some plane's distance is < 0, i.e. iff the minimum over the planes is < 0 - with fminf's rule
+// that a NaN operand is ignored, which is exactly "a NaN distance rejects nothing" (d < 0 is false for NaN). Folding the
+// six compares into minima (FMNMX3 takes two new values at a time) leaves one compare per entity.
+__device__ __forceinline__ float4 min3_4(const float4 &m, const float4 &a, const float4 &b) {
+    return make_float4(fminf(fminf(m.x, a.x), b.x), fminf(fminf(m.y, a.y), b.y), fminf(fminf(m.z, a.z), b.z), fminf(fminf(m.w, a.w), b.w));
+}
+
 }  // namespace ovis

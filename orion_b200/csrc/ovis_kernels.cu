@@ -269,6 +269,55 @@ __device__ __forceinline__ void wait_flags_warp(const uint32_t *flags, int n, ui
     __syncwarp();
 }
 
+// The six plane tests of one warp tile, specialised: see outside-plane notes in ovis_device.cuh (plane_dist4_signed).
+template <int GROUPS>
+__device__ __forceinline__ void test_planes_packed(const CullArgs &a, const float4 (&mnx)[GROUPS], const float4 (&mny)[GROUPS],
+                                                   const float4 (&mnz)[GROUPS], const float4 (&mxx)[GROUPS], const float4 (&mxy)[GROUPS],
+                                                   const float4 (&mxz)[GROUPS], uint32_t (&keep)[GROUPS]) {
+    // one warp-uniform switch per plane with all GROUPS x 4 entities of the lane inside it (independent chains to
+    // overlap); distances are folded into a running minimum, two planes per FMNMX3, one compare per entity at the end
+    const float inf = __int_as_float(0x7f800000);
+    float4 lowest[GROUPS], held[GROUPS];
+#pragma unroll
+    for (int g = 0; g < GROUPS; g++)
+        lowest[g] = make_float4(inf, inf, inf, inf);
+#pragma unroll
+    for (int p = 0; p < 6; p++) {
+        const float nx = a.planes[p].x, ny = a.planes[p].y, nz = a.planes[p].z, d = a.planes[p].w;
+        const int code = (nx >= 0.0f ? 1 : 0) | (ny >= 0.0f ? 2 : 0) | (nz >= 0.0f ? 4 : 0);
+#define OVIS_PLANE_CASE(C, SX, SY, SZ)                                                                                         \
+    case C:                                                                                                                    \
+_Pragma("unroll") for (int g = 0; g < GROUPS; g++) {                                                                   \
+    const float4 dd = plane_dist4_signed<SX, SY, SZ>(nx, ny, nz, d, mnx[g], mny[g], mnz[g], mxx[g], mxy[g], mxz[g]);   \
+    if (p & 1)                                                                                                         \
+        lowest[g] = min3_4(lowest[g], held[g], dd);                                                                    \
+    else                                                                                                               \
+        held[g] = dd;                                                                                                  \
+}                                                                                                                      \
+break;
+        switch (code) {
+            OVIS_PLANE_CASE(0, false, false, false)
+            OVIS_PLANE_CASE(1, true, false, false)
+            OVIS_PLANE_CASE(2, false, true, false)
+            OVIS_PLANE_CASE(3, true, true, false)
+            OVIS_PLANE_CASE(4, false, false, true)
+            OVIS_PLANE_CASE(5, true, false, true)
+            OVIS_PLANE_CASE(6, false, true, true)
+            OVIS_PLANE_CASE(7, true, true, true)
+        }
+#undef OVIS_PLANE_CASE
+    }
+#pragma unroll
+    for (int g = 0; g < GROUPS; g++) {
+        uint32_t out = 0;
+        if (lowest[g].x < 0.0f) out |= 1u;
+        if (lowest[g].y < 0.0f) out |= 2u;
+        if (lowest[g].z < 0.0f) out |= 4u;
+        if (lowest[g].w < 0.0f) out |= 8u;
+        keep[g] &= ~out;
+    }
+}
+
 template <int GROUPS, bool MASKED, bool PACKED = false>
 __device__ __forceinline__ void cull_test_body(const CullArgs &a) {
     constexpr int WT = 128 * GROUPS;                       // entities per warp tile
@@ -314,10 +363,8 @@ __device__ __forceinline__ void cull_test_body(const CullArgs &a) {
 #pragma unroll
             for (int p = 0; p < 6; p++) {                                     // Left Right Top Bottom Near Far
                 const float nx = a.planes[p].x, ny = a.planes[p].y, nz = a.planes[p].z, d = a.planes[p].w;
-                if (PACKED) {
-                    k &= ~outside_plane4(nx, ny, nz, d, mnx[g], mny[g], mnz[g], mxx[g], mxy[g], mxz[g]);
-                    continue;
-                }
+                if (PACKED)
+                    break;                                                    // handled below, plane by plane for all groups
                 if (outside_plane(nx, ny, nz, d, mnx[g].x, mny[g].x, mnz[g].x, mxx[g].x, mxy[g].x, mxz[g].x)) k &= ~1u;
                 if (outside_plane(nx, ny, nz, d, mnx[g].y, mny[g].y, mnz[g].y, mxx[g].y, mxy[g].y, mxz[g].y)) k &= ~2u;
                 if (outside_plane(nx, ny, nz, d, mnx[g].z, mny[g].z, mnz[g].z, mxx[g].z, mxy[g].z, mxz[g].z)) k &= ~4u;
@@ -325,6 +372,8 @@ __device__ __forceinline__ void cull_test_body(const CullArgs &a) {
             }
             keep[g] = k;
         }
+        if (PACKED)
+            test_planes_packed<GROUPS>(a, mnx, mny, mnz, mxx, mxy, mxz, keep);
         issue_loads(wt + warps_total);                                        // this tile's registers are dead now
 
         // rank inside the warp tile: per group an inclusive shuffle scan, groups in index order
@@ -382,7 +431,7 @@ __device__ __forceinline__ void tile_load(TileRegs<GROUPS> &r, const CullArgs &a
     }
 }
 
-template <int GROUPS, bool MASKED>
+template <int GROUPS, bool MASKED, bool PACKED = false>
 __device__ __forceinline__ void tile_process(const TileRegs<GROUPS> &r, const CullArgs &a, int wt, int lane) {
     constexpr int WT = 128 * GROUPS;
     uint32_t keep[GROUPS];
@@ -398,6 +447,8 @@ __device__ __forceinline__ void tile_process(const TileRegs<GROUPS> &r, const Cu
         }
 #pragma unroll
         for (int p = 0; p < 6; p++) {
+            if (PACKED)
+                break;
             const float nx = a.planes[p].x, ny = a.planes[p].y, nz = a.planes[p].z, d = a.planes[p].w;
             if (outside_plane(nx, ny, nz, d, r.mnx[g].x, r.mny[g].x, r.mnz[g].x, r.mxx[g].x, r.mxy[g].x, r.mxz[g].x)) k &= ~1u;
             if (outside_plane(nx, ny, nz, d, r.mnx[g].y, r.mny[g].y, r.mnz[g].y, r.mxx[g].y, r.mxy[g].y, r.mxz[g].y)) k &= ~2u;
@@ -406,6 +457,8 @@ __device__ __forceinline__ void tile_process(const TileRegs<GROUPS> &r, const Cu
         }
         keep[g] = k;
     }
+    if (PACKED)
+        test_planes_packed<GROUPS>(a, r.mnx, r.mny, r.mnz, r.mxx, r.mxy, r.mxz, keep);
     uint32_t base = 0;
     uint32_t *slot = a.staging + (int64_t)wt * WT;
 #pragma unroll
@@ -434,7 +487,7 @@ __device__ __forceinline__ void tile_process(const TileRegs<GROUPS> &r, const Cu
     }
 }
 
-template <int GROUPS, bool MASKED>
+template <int GROUPS, bool MASKED, bool PACKED = false>
 __global__ void __launch_bounds__(kCullThreads, GROUPS == 1 ? 2 : 1)
 cull_test_pipelined_kernel(const __grid_constant__ CullArgs a) {
     if (a.n_wait && blockIdx.x == 0 && threadIdx.x < 32)
@@ -450,12 +503,12 @@ cull_test_pipelined_kernel(const __grid_constant__ CullArgs a) {
     tile_load<GROUPS, MASKED>(ra, a, bounds, vstride, wt, lane);
     while (wt < a.num_tiles) {
         tile_load<GROUPS, MASKED>(rb, a, bounds, vstride, wt + warps_total, lane);
-        tile_process<GROUPS, MASKED>(ra, a, wt, lane);
+        tile_process<GROUPS, MASKED, PACKED>(ra, a, wt, lane);
         wt += warps_total;
         if (wt >= a.num_tiles)
             break;
         tile_load<GROUPS, MASKED>(ra, a, bounds, vstride, wt + warps_total, lane);
-        tile_process<GROUPS, MASKED>(rb, a, wt, lane);
+        tile_process<GROUPS, MASKED, PACKED>(rb, a, wt, lane);
         wt += warps_total;
     }
 }
@@ -483,8 +536,8 @@ __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commi
 template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
-template <bool MASKED, int STAGES>
-__global__ void __launch_bounds__(kCullThreads, 2)
+template <bool MASKED, int STAGES, bool PACKED = false>
+__global__ void __launch_bounds__(kCullThreads, STAGES == 2 ? 4 : 2)
 cull_test_async_kernel(const __grid_constant__ CullArgs a) {
     extern __shared__ __align__(16) unsigned char s_ring_bytes[];
     if (a.n_wait && blockIdx.x == 0 && threadIdx.x < 32)
@@ -527,7 +580,7 @@ cull_test_async_kernel(const __grid_constant__ CullArgs a) {
         r.mxx[0] = rows[3 * 32 + lane]; r.mxy[0] = rows[4 * 32 + lane]; r.mxz[0] = rows[5 * 32 + lane];
         if (MASKED)
             r.mask_bits[0] = reinterpret_cast<const uint32_t *>(rows + 6 * 32)[lane];
-        tile_process<1, MASKED>(r, a, wt, lane);
+        tile_process<1, MASKED, PACKED>(r, a, wt, lane);
         stage = stage + 1 == STAGES ? 0 : stage + 1;
     }
     cp_async_wait<0>();
@@ -719,18 +772,29 @@ cull_fused_kernel(const __grid_constant__ CullArgs a, const __grid_constant__ Ga
 // Launch shapes selectable at run time (OVIS_CULL_VARIANT, tuning only). Variant 0 is the default.
 static const CullVariant kVariants[] = { { 2, false, false }, { 1, false, false }, { 4, false, false }, { 1, true, false },
                                          { 2, true, false },  { 2, false, true },  { 1, false, true },
-                                         { 1, false, false, 4 }, { 1, false, false, 3 } };
+                                         { 1, false, false, 4 }, { 1, false, false, 3 }, { 1, false, false, 2 },
+                                         { 1, true, true, 0 },   { 2, true, true, 0 },   { 1, false, true, 4 },  { 1, false, true, 2 } };
 
 int cull_num_variants() { return (int)(sizeof(kVariants) / sizeof(kVariants[0])); }
 int cull_variant_smem(int v) {
-    return kVariants[v].async_stages == 4 ? AsyncRing<4>::kCtaBytes : kVariants[v].async_stages == 3 ? AsyncRing<3>::kCtaBytes : 0;
+    const int st = kVariants[v].async_stages;
+    return st == 4 ? AsyncRing<4>::kCtaBytes : st == 3 ? AsyncRing<3>::kCtaBytes : st == 2 ? AsyncRing<2>::kCtaBytes : 0;
 }
 CullVariant cull_variant(int v) { return kVariants[v]; }
 
 template <typename F>
 static void with_variant(int variant, bool masked, F &&f) {
+    const CullVariant &cv = kVariants[variant];
+    if (cv.packed && cv.async_stages == 4) { if (masked) f(cull_test_async_kernel<true, 4, true>); else f(cull_test_async_kernel<false, 4, true>); return; }
+    if (cv.packed && cv.async_stages == 2) { if (masked) f(cull_test_async_kernel<true, 2, true>); else f(cull_test_async_kernel<false, 2, true>); return; }
+    if (cv.packed && cv.pipelined) {
+        if (cv.groups == 1) { if (masked) f(cull_test_pipelined_kernel<1, true, true>); else f(cull_test_pipelined_kernel<1, false, true>); }
+        else { if (masked) f(cull_test_pipelined_kernel<2, true, true>); else f(cull_test_pipelined_kernel<2, false, true>); }
+        return;
+    }
     if (kVariants[variant].async_stages == 4) { if (masked) f(cull_test_async_kernel<true, 4>); else f(cull_test_async_kernel<false, 4>); return; }
     if (kVariants[variant].async_stages == 3) { if (masked) f(cull_test_async_kernel<true, 3>); else f(cull_test_async_kernel<false, 3>); return; }
+    if (kVariants[variant].async_stages == 2) { if (masked) f(cull_test_async_kernel<true, 2>); else f(cull_test_async_kernel<false, 2>); return; }
     if (kVariants[variant].pipelined) {
         if (kVariants[variant].groups == 1) { if (masked) f(cull_test_pipelined_kernel<1, true>); else f(cull_test_pipelined_kernel<1, false>); }
         else { if (masked) f(cull_test_pipelined_kernel<2, true>); else f(cull_test_pipelined_kernel<2, false>); }

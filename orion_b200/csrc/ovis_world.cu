@@ -504,7 +504,8 @@ int enqueue_cull(OvisWorld *w, const float planes[24], uint32_t require, uint32_
     }
     OVIS_TRY(upload_masks(w));
     // small worlds are latency-bound: smaller warp tiles spread them over more warps
-    const int variant = w->forced_variant >= 0 ? w->forced_variant : (w->n_ent < (4 << 20) ? 1 : 0);
+    // large worlds: 256-entity tiles with the sign-specialised, FMUL2-packed plane code (variant 5; profiles/r01_cull_notes.md)
+    const int variant = w->forced_variant >= 0 ? w->forced_variant : (w->n_ent < (4 << 20) ? 1 : 5);
     const int tile = ovis::cull_variant(variant).tile();
     const bool masked = require != 0 || w->any_dead;
     ovis::CullArgs a{};
