@@ -436,3 +436,30 @@ def test_read_segments_host_pinned_and_pageable():
     assert w.exchange_error() == 0
     w.close()
     pinned.free()
+
+
+@pytest.mark.parametrize("variant", list(range(14)))
+def test_every_test_kernel_variant_is_exact(oracle, variant, monkeypatch):
+    """OVIS_CULL_VARIANT selects the launch shape / formulation of the entity test kernel (tiles of 128-512 entities, two
+    register sets, cp.async ring, sign-specialised FMUL2 plane code and their combinations). Whichever runs, the list is
+    the reference's: edge-case boxes, ragged sizes, removed entities and the castsShadow filter included."""
+    monkeypatch.setenv("OVIS_CULL_VARIANT", str(variant))
+    monkeypatch.setenv("OVIS_CULL_FUSED", "0")                 # small worlds would otherwise take the fused kernel
+    rng = np.random.default_rng(4000 + variant)
+    n = 70_001
+    boxes = np.concatenate([util.edge_boxes(), util.random_boxes(rng, n - len(util.edge_boxes()), extent=150.0)])
+    flags = rng.integers(0, 2, n).astype(np.uint32)
+    w = _world_static(boxes, flags)
+    views = list(util.random_views(rng, 3, extent=60.0)) + [scenes.make_view((0, 0, 300), (1, 0, 0, 0), 100.0, 0.1, 2000.0, 1600, 900)]
+    for v in views:
+        planes = lib.view_planes(v)
+        assert np.array_equal(w.cull_planes(planes), oracle.cull_aabb(boxes, planes))
+        assert np.array_equal(w.cull_planes(planes, require=1), oracle.cull_aabb(boxes, planes, flags, 1))
+    gone = rng.choice(n, 5000, replace=False).astype(np.uint32)
+    w.remove_entities(gone)
+    alive = np.ones(n, dtype=bool)
+    alive[gone] = False
+    planes = lib.view_planes(views[-1])
+    expected = oracle.cull_aabb(boxes, planes)
+    assert np.array_equal(w.cull_planes(planes), expected[alive[expected]])
+    w.close()
