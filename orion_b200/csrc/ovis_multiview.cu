@@ -141,9 +141,14 @@ multi_pass_kernel(const __grid_constant__ MultiArgs a) {
                     uint32_t cand = 0;
 #pragma unroll
                     for (int j = 0; j < 4; j++) {
-                        const bool out = (hi[0][j] < grp.lo[0]) | (lo[0][j] > grp.hi[0]) | (hi[1][j] < grp.lo[1]) |
-                                         (lo[1][j] > grp.hi[1]) | (hi[2][j] < grp.lo[2]) | (lo[2][j] > grp.hi[2]);
-                        cand |= out ? 0u : (1u << j);
+                        // separated along some axis <=> the largest of the six gaps is > 0. Subtractions run on the FMA
+                        // pipe and the maxima fold three at a time (FMNMX3), which leaves ONE compare on the half-rate ALU
+                        // pipe instead of six plus their combination; a NaN gap is ignored by fmaxf and an all-NaN set
+                        // compares false, so odd boxes stay candidates exactly as with the six compares.
+                        const float gap = fmaxf(fmaxf(fmaxf(grp.lo[0] - hi[0][j], lo[0][j] - grp.hi[0]),
+                                                      fmaxf(grp.lo[1] - hi[1][j], lo[1][j] - grp.hi[1])),
+                                                fmaxf(grp.lo[2] - hi[2][j], lo[2][j] - grp.hi[2]));
+                        cand |= gap > 0.0f ? 0u : (1u << j);
                     }
                     cand &= alive;
                     if (!__any_sync(0xffffffffu, cand))
