@@ -121,6 +121,7 @@ struct OvisWorld {
     uint32_t *d_light_out = nullptr;
     int64_t cap_lights = 0;
     bool lights_dirty = false;
+    int64_t lights_dirty_lo = 0, lights_dirty_hi = 0;   // light slots changed since the last upload: [lo, hi)
 
     // ---- cull scratch and results
     // Two staging/count sets and three block-total sets rotate from cull to cull, so that a cull's test kernel can
@@ -601,6 +602,19 @@ int enqueue_cull(OvisWorld *w, const float planes[24], uint32_t require, uint32_
     return OVIS_OK;
 }
 
+void mark_lights(OvisWorld *w, int64_t lo, int64_t hi) {
+    if (!w->lights_dirty) {
+        w->lights_dirty_lo = lo;
+        w->lights_dirty_hi = hi;
+    } else {
+        w->lights_dirty_lo = std::min(w->lights_dirty_lo, lo);
+        w->lights_dirty_hi = std::max(w->lights_dirty_hi, hi);
+    }
+    w->lights_dirty = true;
+}
+
+// Device copies of the lights that changed: cull record, LightUniforms block, type. Only the dirty slot range is
+// recomputed and uploaded (a light that moves every frame does not make the other 4095 pay).
 int upload_lights(OvisWorld *w) {
     if (!w->lights_dirty)
         return OVIS_OK;
@@ -612,11 +626,15 @@ int upload_lights(OvisWorld *w) {
         OVIS_TRY(grow(w->d_light_uniforms, 0, 52 * cap, w->stream, false));
         OVIS_TRY(grow(w->d_light_types, 0, cap, w->stream, false));
         w->cap_lights = cap;
+        w->lights_dirty_lo = 0;                                  // fresh buffers: everything goes up again
+        w->lights_dirty_hi = n;
     }
-    std::vector<ovis::DeviceLight> dl((size_t)n);
-    for (int64_t i = 0; i < n; i++) {
+    const int64_t lo = std::max<int64_t>(0, w->lights_dirty_lo), hi = std::min<int64_t>(n, w->lights_dirty_hi);
+    const int64_t m = std::max<int64_t>(0, hi - lo);
+    std::vector<ovis::DeviceLight> dl((size_t)m);
+    for (int64_t i = lo; i < hi; i++) {
         const OvisLight &l = w->lights[(size_t)i];
-        ovis::DeviceLight &d = dl[(size_t)i];
+        ovis::DeviceLight &d = dl[(size_t)(i - lo)];
         std::memset(&d, 0, sizeof d);
         if (!w->light_alive[(size_t)i] || ovis::hm::lightHasNoEffect(l)) {          // render_light.cc:189-190
             d.kind = ovis::kLightNever;
@@ -635,14 +653,14 @@ int upload_lights(OvisWorld *w) {
             d.kind = ovis::kLightNever;                                              // render_light.cc:206-207
         }
     }
-    std::vector<float> blocks(52 * (size_t)n);
-    std::vector<int32_t> types((size_t)n);
-    for (int64_t i = 0; i < n; i++)
-        types[(size_t)i] = w->lights[(size_t)i].type;
-    for (int64_t i = 0; i < n; i++)
+    std::vector<float> blocks(52 * (size_t)m);
+    std::vector<int32_t> types((size_t)m);
+    for (int64_t i = lo; i < hi; i++)
+        types[(size_t)(i - lo)] = w->lights[(size_t)i].type;
+    for (int64_t i = lo; i < hi; i++)
         ovis::hm::lightUniforms(w->lights[(size_t)i], w->light_shading[(size_t)i].attenuation, w->light_shading[(size_t)i].shadow_bias,
-                                blocks.data() + 52 * (size_t)i);
-    for (int64_t i = 0; i < n; i++) {                            // see kLightSkippable
+                                blocks.data() + 52 * (size_t)(i - lo));
+    for (int64_t i = 0; i < m; i++) {                            // see kLightSkippable
         const float *b = blocks.data() + 52 * (size_t)i;
         const int32_t type = types[(size_t)i];
         if (type != OVIS_LIGHT_POINT && type != OVIS_LIGHT_SPOT)
@@ -658,11 +676,12 @@ int upload_lights(OvisWorld *w) {
         if (ok)
             types[(size_t)i] |= ovis::kLightSkippable;
     }
-    if (n > 0) {
-        OVIS_CUDA(cudaMemcpyAsync(w->d_lights, dl.data(), sizeof(ovis::DeviceLight) * (size_t)n, cudaMemcpyHostToDevice, w->stream));
-        OVIS_CUDA(cudaMemcpyAsync(w->d_light_uniforms, blocks.data(), sizeof(float) * blocks.size(), cudaMemcpyHostToDevice, w->stream));
-        OVIS_CUDA(cudaMemcpyAsync(w->d_light_types, types.data(), sizeof(int32_t) * types.size(), cudaMemcpyHostToDevice, w->stream));
-        OVIS_CUDA(cudaStreamSynchronize(w->stream));
+    if (m > 0) {
+        OVIS_CUDA(cudaMemcpyAsync(w->d_lights + lo, dl.data(), sizeof(ovis::DeviceLight) * (size_t)m, cudaMemcpyHostToDevice, w->stream));
+        OVIS_CUDA(cudaMemcpyAsync(w->d_light_uniforms + 52 * lo, blocks.data(), sizeof(float) * blocks.size(), cudaMemcpyHostToDevice,
+                                  w->stream));
+        OVIS_CUDA(cudaMemcpyAsync(w->d_light_types + lo, types.data(), sizeof(int32_t) * types.size(), cudaMemcpyHostToDevice, w->stream));
+        OVIS_CUDA(cudaStreamSynchronize(w->stream));           // the vectors are locals
     }
     w->lights_dirty = false;
     return OVIS_OK;
@@ -1297,11 +1316,13 @@ int ovis_update_transforms(OvisWorld *w) {
 int ovis_light_add(OvisWorld *w, int32_t n, const OvisLight *lights, uint32_t *out_first_id) {
     if (!w || n < 0 || (n > 0 && !lights))
         return fail(OVIS_ERR_INVALID, "ovis_light_add: bad arguments");
-    if (out_first_id)
-        *out_first_id = (uint32_t)w->lights.size();
-    for (int32_t i = 0; i < n; i++) {
+    for (int32_t i = 0; i < n; i++)
         if (lights[i].type == OVIS_LIGHT_SPOT && lights[i].cutoff > 45.0f)
             return fail(OVIS_ERR_INVALID, "spot light cutoff must be <= 45 degrees");   // render_light.cc:104
+    const int64_t first = (int64_t)w->lights.size();
+    if (out_first_id)
+        *out_first_id = (uint32_t)first;
+    for (int32_t i = 0; i < n; i++) {
         w->lights.push_back(lights[i]);
         w->light_alive.push_back(1);
         // the defaults of the graphics Light components (graphics/src/light.cc:44,63,72)
@@ -1312,7 +1333,8 @@ int ovis_light_add(OvisWorld *w, int32_t n, const OvisLight *lights, uint32_t *o
             sh = { { 1.0f, 0.09f, 0.032f }, -0.001f };
         w->light_shading.push_back(sh);
     }
-    w->lights_dirty = true;
+    if (n > 0)
+        mark_lights(w, first, first + n);
     return OVIS_OK;
 }
 
@@ -1322,7 +1344,7 @@ int ovis_light_update(OvisWorld *w, uint32_t id, const OvisLight *light) {
     if (light->type == OVIS_LIGHT_SPOT && light->cutoff > 45.0f)
         return fail(OVIS_ERR_INVALID, "spot light cutoff must be <= 45 degrees");
     w->lights[id] = *light;
-    w->lights_dirty = true;
+    mark_lights(w, id, (int64_t)id + 1);
     return OVIS_OK;
 }
 
@@ -1331,7 +1353,7 @@ int ovis_light_set_shading(OvisWorld *w, uint32_t id, const float attenuation[3]
         return fail(OVIS_ERR_INVALID, "ovis_light_set_shading: unknown light %u", id);
     std::memcpy(w->light_shading[id].attenuation, attenuation, 12);
     w->light_shading[id].shadow_bias = shadow_bias_constant;
-    w->lights_dirty = true;
+    mark_lights(w, id, (int64_t)id + 1);
     return OVIS_OK;
 }
 
@@ -1351,7 +1373,7 @@ int ovis_light_remove(OvisWorld *w, uint32_t id) {
     if (!w || id >= w->lights.size() || !w->light_alive[id])
         return fail(OVIS_ERR_INVALID, "ovis_light_remove: unknown light %u", id);
     w->light_alive[id] = 0;
-    w->lights_dirty = true;
+    mark_lights(w, id, (int64_t)id + 1);
     return OVIS_OK;
 }
 

@@ -463,3 +463,56 @@ def test_every_test_kernel_variant_is_exact(oracle, variant, monkeypatch):
     expected = oracle.cull_aabb(boxes, planes)
     assert np.array_equal(w.cull_planes(planes), expected[alive[expected]])
     w.close()
+
+
+def test_light_updates_upload_only_what_changed(oracle):
+    """Lights are re-sent to the device by dirty slot range: single updates, growth past the allocated capacity, shading
+    changes and removals must all leave the device copies (cull records and LightUniforms blocks) current."""
+    rng = np.random.default_rng(61)
+    lights = util.random_lights(rng, 300, extent=80.0)
+    att = np.zeros((300, 3), dtype=np.float32)
+    att[lights["type"] == scenes.LIGHT_POINT] = (1.0, 0.045, 0.0075)
+    att[lights["type"] == scenes.LIGHT_SPOT] = (1.0, 0.09, 0.032)
+    bias = np.full(300, -0.001, dtype=np.float32)
+    w = _world_static(util.random_boxes(rng, 1000))
+    w.add_lights(lights)
+    view = scenes.make_view((0, 0, 120), (1, 0, 0, 0), 80.0, 0.1, 500.0, 1280, 720)
+    planes = lib.view_planes(view)
+    alive = np.ones(300, dtype=bool)
+
+    def check():
+        _, ls = w.cull(view)
+        want = oracle.light_cull(lights, planes)
+        assert np.array_equal(ls, want[alive[want]])
+        ids = np.flatnonzero(alive).astype(np.uint32)
+        blocks = util.gpu_light_uniforms(w, ids)
+        exp = np.stack([oracle.light_uniforms(lights[i], att[i], float(bias[i])) for i in ids])
+        assert blocks.tobytes() == exp.tobytes()
+
+    check()
+    lights[150] = util.random_lights(rng, 1, extent=80.0)[0]              # one light in the middle
+    lights[150]["type"] = scenes.LIGHT_POINT
+    att[150] = (1.0, 0.045, 0.0075)
+    w.update_light(150, lights[150])
+    w.set_light_shading(150, att[150], -0.001)
+    check()
+    more = util.random_lights(rng, 500, extent=80.0)                       # growth: new device buffers
+    more_att = np.zeros((500, 3), dtype=np.float32)
+    more_att[more["type"] == scenes.LIGHT_POINT] = (1.0, 0.045, 0.0075)
+    more_att[more["type"] == scenes.LIGHT_SPOT] = (1.0, 0.09, 0.032)
+    assert w.add_lights(more) == 300
+    lights = np.concatenate([lights, more])
+    att = np.concatenate([att, more_att])
+    bias = np.concatenate([bias, np.full(500, -0.001, dtype=np.float32)])
+    alive = np.ones(800, dtype=bool)
+    check()
+    for i in (10, 700):                                                    # two far-apart updates in one frame
+        lights[i] = util.random_lights(rng, 1, extent=80.0)[0]
+        w.update_light(i, lights[i])
+        att[i] = rng.uniform(0.1, 1.0, 3)
+        bias[i] = -0.004
+        w.set_light_shading(i, att[i], float(bias[i]))
+    w.remove_light(5)
+    alive[5] = False
+    check()
+    w.close()
