@@ -85,6 +85,7 @@ struct OvisWorld {
     uint32_t *d_draw_totals = nullptr;    // draw-list scratch: 2 per 1024 visible entries
     uint32_t *d_draw_counts = nullptr;    // [2] draws written by the last ovis_build_draw_lists_device
     bool masks_dirty = false;
+    int64_t masks_dirty_lo = 0, masks_dirty_hi = 0;     // 32-entity mask words changed since the last upload: [lo, hi)
     bool any_dead = false;
 
     // ---- transform tree
@@ -269,16 +270,32 @@ int reserve_nodes(OvisWorld *w, int64_t want) {
     return OVIS_OK;
 }
 
+void mark_masks(OvisWorld *w, int64_t first_id, int64_t last_id) {
+    const int64_t lo = first_id >> 5, hi = (last_id >> 5) + 1;
+    if (!w->masks_dirty) {
+        w->masks_dirty_lo = lo;
+        w->masks_dirty_hi = hi;
+    } else {
+        w->masks_dirty_lo = std::min(w->masks_dirty_lo, lo);
+        w->masks_dirty_hi = std::max(w->masks_dirty_hi, hi);
+    }
+    w->masks_dirty = true;
+}
+
+// Only the range of mask words that changed goes up (100 M entities are 12.5 MB per mask: a single removal must not
+// resend that).
 int upload_masks(OvisWorld *w) {
     if (!w->masks_dirty)
         return OVIS_OK;
-    size_t words = (size_t)(round_up(w->n_ent, 32) / 32);
-    if (words) {
+    const int64_t all = round_up(w->n_ent, 32) / 32;
+    const int64_t lo = std::max<int64_t>(0, w->masks_dirty_lo), hi = std::min<int64_t>(all, w->masks_dirty_hi);
+    if (hi > lo) {
+        const size_t words = (size_t)(hi - lo);
         std::vector<uint32_t> caster(words);
         for (size_t i = 0; i < words; i++)
-            caster[i] = w->h_caster_raw[i] & w->h_alive[i];
-        OVIS_CUDA(cudaMemcpyAsync(w->d_alive_bits, w->h_alive.data(), words * 4, cudaMemcpyHostToDevice, w->stream));
-        OVIS_CUDA(cudaMemcpyAsync(w->d_caster_bits, caster.data(), words * 4, cudaMemcpyHostToDevice, w->stream));
+            caster[i] = w->h_caster_raw[(size_t)lo + i] & w->h_alive[(size_t)lo + i];
+        OVIS_CUDA(cudaMemcpyAsync(w->d_alive_bits + lo, w->h_alive.data() + lo, words * 4, cudaMemcpyHostToDevice, w->stream));
+        OVIS_CUDA(cudaMemcpyAsync(w->d_caster_bits + lo, caster.data(), words * 4, cudaMemcpyHostToDevice, w->stream));
         OVIS_CUDA(cudaStreamSynchronize(w->stream));   // `caster` is a local
     }
     w->masks_dirty = false;
@@ -1098,7 +1115,8 @@ int ovis_entity_add(OvisWorld *w, int64_t n, const float *local_aabb, const uint
     }
     w->n_ent = first + n;
     w->n_live += n;
-    w->masks_dirty = true;
+    if (n > 0)
+        mark_masks(w, first, first + n - 1);
     if (out_first_id)
         *out_first_id = (uint32_t)first;
     return OVIS_OK;
@@ -1114,11 +1132,10 @@ int ovis_entity_remove(OvisWorld *w, int64_t n, const uint32_t *ids) {
             continue;                                   // listed twice
         w->h_alive[id >> 5] &= ~(1u << (id & 31));
         w->n_live--;
+        mark_masks(w, id, id);
     }
-    if (n > 0) {
+    if (n > 0)
         w->any_dead = true;
-        w->masks_dirty = true;
-    }
     return OVIS_OK;
 }
 
@@ -1167,9 +1184,8 @@ int ovis_entity_set_flags(OvisWorld *w, int64_t n, const uint32_t *ids, const ui
             w->h_caster_raw[id >> 5] |= bit;
         else
             w->h_caster_raw[id >> 5] &= ~bit;
+        mark_masks(w, id, id);
     }
-    if (n > 0)
-        w->masks_dirty = true;
     return OVIS_OK;
 }
 
