@@ -1359,6 +1359,8 @@ int ovis_light_update(OvisWorld *w, uint32_t id, const OvisLight *light) {
         return fail(OVIS_ERR_INVALID, "ovis_light_update: unknown light %u", id);
     if (light->type == OVIS_LIGHT_SPOT && light->cutoff > 45.0f)
         return fail(OVIS_ERR_INVALID, "spot light cutoff must be <= 45 degrees");
+    if (std::memcmp(&w->lights[id], light, sizeof(OvisLight)) == 0)
+        return OVIS_OK;                                          // unchanged (callers that re-describe every light per cull)
     w->lights[id] = *light;
     mark_lights(w, id, (int64_t)id + 1);
     return OVIS_OK;
