@@ -10,6 +10,8 @@
 // warp covers 128 consecutive entities with fully coalesced 512 B requests per array.
 #include "ovis_kernels.h"
 
+#include <cstdlib>
+
 #include <cooperative_groups.h>
 
 #include "ovis_device.cuh"
@@ -699,7 +701,12 @@ cull_gather_kernel(const __grid_constant__ GatherArgs a) {
             wait_flags_at_least(a.wait_flags, a.n_wait, a.wait_value, a.error_flag);
         __syncthreads();
     }
-    cull_gather_body(a, blockIdx.x, gridDim.x);
+    // a CTA takes every gridDim.x-th block of 64 tiles (blocks without survivors return at once inside the body)
+    const int num_gather_blocks = (a.num_tiles + kGatherTiles - 1) / kGatherTiles;
+    for (int b = blockIdx.x; b < num_gather_blocks; b += gridDim.x) {
+        cull_gather_body(a, b, num_gather_blocks);
+        __syncthreads();                                      // the body's shared arrays are reused by the next block
+    }
     if (a.n_signal) {                                         // the last block to finish publishes the segment
         __syncthreads();                                      // this block's stores happen-before thread 0's fence
         if (threadIdx.x == 0) {
@@ -860,6 +867,9 @@ int cull_fused_max_blocks_per_sm(bool masked, int variant) {
 
 void launch_cull_gather(const GatherArgs &a, cudaStream_t s) {
     int blocks = (a.num_tiles + kGatherTiles - 1) / kGatherTiles;
+    static const int cap = getenv("OVIS_GATHER_CTAS") ? atoi(getenv("OVIS_GATHER_CTAS")) : 0;   // tuning
+    if (cap > 0 && blocks > cap)
+        blocks = cap;
     cull_gather_kernel<<<blocks, 256, 0, s>>>(a);
 }
 
