@@ -41,12 +41,16 @@ static OvisLight describeLight(const RenderLight *light) {
 }
 
 CudaRenderWorld::CudaRenderWorld(int device) :
-    m_world (nullptr)
+    m_world                (nullptr),
+    m_entityResult         (nullptr),
+    m_entityResultCapacity (0)
 {
     OVIS_CHECK(ovis_world_create(device, &m_world));
 }
 
 CudaRenderWorld::~CudaRenderWorld() {
+    if (m_entityResult)
+        ovis_host_free(m_entityResult);
     ovis_world_destroy(m_world);
 }
 
@@ -150,12 +154,21 @@ void CudaRenderWorld::cull(RenderView &view, CullResults &outResults, uint32_t f
     v.vp_width = view.viewport().width;
     v.vp_height = view.viewport().height;
 
-    m_entityResult.resize(m_entities.size() ? m_entities.size() : 1);
+    const size_t needed = m_entities.size() ? m_entities.size() : 1;
+    if (needed > m_entityResultCapacity) {
+        if (m_entityResult)
+            OVIS_CHECK(ovis_host_free(m_entityResult));
+        m_entityResult = nullptr;
+        m_entityResultCapacity = needed + needed / 2 + 1024;
+        void *ptr = nullptr;
+        OVIS_CHECK(ovis_host_alloc(static_cast<int64_t>(m_entityResultCapacity * sizeof(uint32_t)), &ptr));
+        m_entityResult = static_cast<uint32_t *>(ptr);
+    }
     m_lightResult.resize(m_lights.size() ? m_lights.size() : 1);
     int64_t numEntities = 0;
     int32_t numLights = 0;
     OVIS_CHECK(ovis_cull(m_world, &v, (flags & kCullLights) ? OVIS_CULL_LIGHTS : 0,
-                         m_entityResult.data(), static_cast<int64_t>(m_entityResult.size()), &numEntities,
+                         m_entityResult, static_cast<int64_t>(m_entityResultCapacity), &numEntities,
                          m_lightResult.data(), static_cast<int32_t>(m_lightResult.size()), &numLights));
 
     /* Appended, never cleared, in insertion order - as simple_render_world.cc:38-47 does. */

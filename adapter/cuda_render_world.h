@@ -45,6 +45,9 @@ private:
     mutable std::vector<bool> m_isPending;
 
     /** Scratch reused between culls. */
-    mutable std::vector<uint32_t> m_entityResult, m_lightResult, m_ids;
+    mutable std::vector<uint32_t> m_lightResult, m_ids;
+    /** Visible entity ids land here: page-locked (ovis_host_alloc), so the cull's gather kernel writes them itself. */
+    mutable uint32_t *m_entityResult;
+    mutable size_t m_entityResultCapacity;
     mutable std::vector<float> m_boxes;
 };
