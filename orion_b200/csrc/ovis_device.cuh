@@ -200,4 +200,19 @@ __device__ __forceinline__ float4 min3_4(const float4 &m, const float4 &a, const
     return make_float4(fminf(fminf(m.x, a.x), b.x), fminf(fminf(m.y, a.y), b.y), fminf(fminf(m.z, a.z), b.z), fminf(fminf(m.w, a.w), b.w));
 }
 
+// plane_dist4_signed chosen by a 3-bit code (bit c = normal component c >= 0): a warp-uniform switch
+__device__ __forceinline__ float4 plane_dist4_coded(uint32_t code, float4 q, const float4 &mnx, const float4 &mny, const float4 &mnz,
+                                                    const float4 &mxx, const float4 &mxy, const float4 &mxz) {
+    switch (code & 7u) {
+    case 0: return plane_dist4_signed<false, false, false>(q.x, q.y, q.z, q.w, mnx, mny, mnz, mxx, mxy, mxz);
+    case 1: return plane_dist4_signed<true, false, false>(q.x, q.y, q.z, q.w, mnx, mny, mnz, mxx, mxy, mxz);
+    case 2: return plane_dist4_signed<false, true, false>(q.x, q.y, q.z, q.w, mnx, mny, mnz, mxx, mxy, mxz);
+    case 3: return plane_dist4_signed<true, true, false>(q.x, q.y, q.z, q.w, mnx, mny, mnz, mxx, mxy, mxz);
+    case 4: return plane_dist4_signed<false, false, true>(q.x, q.y, q.z, q.w, mnx, mny, mnz, mxx, mxy, mxz);
+    case 5: return plane_dist4_signed<true, false, true>(q.x, q.y, q.z, q.w, mnx, mny, mnz, mxx, mxy, mxz);
+    case 6: return plane_dist4_signed<false, true, true>(q.x, q.y, q.z, q.w, mnx, mny, mnz, mxx, mxy, mxz);
+    default: return plane_dist4_signed<true, true, true>(q.x, q.y, q.z, q.w, mnx, mny, mnz, mxx, mxy, mxz);
+    }
+}
+
 }  // namespace ovis

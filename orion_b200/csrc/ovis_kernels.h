@@ -111,6 +111,7 @@ struct MultiArgs {
     int n_groups;
     const float4 *planes;        // 6 per view
     const uint32_t *view_require;// per view: non-zero = shadow casters only
+    const uint32_t *view_codes;  // per view: 3 bits per plane (bit c = normal component c >= 0), plane p at bits 3p..3p+2
     int n_views;
     uint32_t *counts;            // [num_tiles][n_views]: counts after pass A, positions after the scans
     uint8_t *sub_masks;          // [num_tiles][n_views]: bit s = sub-tile s holds a survivor of the view (A writes, C reads)

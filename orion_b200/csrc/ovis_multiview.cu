@@ -161,15 +161,21 @@ multi_pass_kernel(const __grid_constant__ MultiArgs a) {
                             continue;
                         uint32_t keep = a.view_require[view] ? (cand & caster) : cand;
                         const float4 *pl = a.planes + 6 * view;
+                        const uint32_t codes = __ldg(a.view_codes + view);
+                        // Two planes at a time: the P-vertex corner is picked by a warp-uniform switch on the plane's sign
+                        // bits (no select per entity), products are packed FMUL2, and "either distance < 0" is one compare
+                        // of the smaller distance (fminf ignores a NaN operand, as a NaN distance rejects nothing). The
+                        // warp-uniform early-outs sit where they were: after the side planes and after top / bottom.
 #pragma unroll
-                        for (int p = 0; p < 6; p++) {
-                            if ((p == 2 || p == 4) && !__any_sync(0xffffffffu, keep))     // warp-uniform early-out
+                        for (int pp = 0; pp < 3; pp++) {
+                            if (pp > 0 && !__any_sync(0xffffffffu, keep))
                                 break;
-                            const float4 q = __ldg(pl + p);
-#pragma unroll
-                            for (int j = 0; j < 4; j++)
-                                if (outside_plane(q.x, q.y, q.z, q.w, mn[0][j], mn[1][j], mn[2][j], mx[0][j], mx[1][j], mx[2][j]))
-                                    keep &= ~(1u << j);
+                            const float4 d0 = plane_dist4_coded(codes >> (6 * pp), __ldg(pl + 2 * pp), ax, ay, az, bx, by, bz);
+                            const float4 d1 = plane_dist4_coded(codes >> (6 * pp + 3), __ldg(pl + 2 * pp + 1), ax, ay, az, bx, by, bz);
+                            if (fminf(d0.x, d1.x) < 0.0f) keep &= ~1u;
+                            if (fminf(d0.y, d1.y) < 0.0f) keep &= ~2u;
+                            if (fminf(d0.z, d1.z) < 0.0f) keep &= ~4u;
+                            if (fminf(d0.w, d1.w) < 0.0f) keep &= ~8u;
                         }
                         if (!__any_sync(0xffffffffu, keep))
                             continue;

@@ -152,6 +152,7 @@ struct OvisWorld {
     int64_t cap_mv_totals = 0;
     float *d_mv_planes = nullptr;         // 24 floats per view
     uint32_t *d_mv_require = nullptr;
+    uint32_t *d_mv_codes = nullptr;       // per view: P-vertex selection bits of its six planes
     int64_t cap_mv_views = 0;
     ovis::ViewGroupDev *d_mv_groups = nullptr;
     int64_t cap_mv_groups = 0;
@@ -820,6 +821,7 @@ int cull_views_grouped(OvisWorld *w, int32_t n_views, const float *planes, const
     if (n_views > w->cap_mv_views) {
         OVIS_TRY(grow(w->d_mv_planes, 0, 24 * (int64_t)n_views, w->stream, false));
         OVIS_TRY(grow(w->d_mv_require, 0, (int64_t)n_views, w->stream, false));
+        OVIS_TRY(grow(w->d_mv_codes, 0, (int64_t)n_views, w->stream, false));
         w->cap_mv_views = n_views;
     }
     if ((int64_t)groups.size() > w->cap_mv_groups) {
@@ -829,13 +831,20 @@ int cull_views_grouped(OvisWorld *w, int32_t n_views, const float *planes, const
     // groups are uploaded with first_view relative to their pass
     std::vector<ovis::ViewGroupDev> rel(groups);
     std::vector<uint32_t> req((size_t)n_views, 0u);
-    for (int32_t v = 0; v < n_views; v++)
+    std::vector<uint32_t> codes((size_t)n_views, 0u);
+    for (int32_t v = 0; v < n_views; v++) {
         req[(size_t)v] = require ? require[v] : 0u;
+        for (int p = 0; p < 6; p++)                              // calcPVertex picks max where the normal component is >= 0
+            for (int c = 0; c < 3; c++)
+                if (planes[24 * (size_t)v + 4 * p + c] >= 0.0f)
+                    codes[(size_t)v] |= 1u << (3 * p + c);
+    }
     for (const Pass &p : passes)
         for (size_t g = p.g0; g < p.g1; g++)
             rel[g].first_view -= p.v0;
     OVIS_CUDA(cudaMemcpyAsync(w->d_mv_planes, planes, sizeof(float) * 24 * (size_t)n_views, cudaMemcpyHostToDevice, w->stream));
     OVIS_CUDA(cudaMemcpyAsync(w->d_mv_require, req.data(), sizeof(uint32_t) * (size_t)n_views, cudaMemcpyHostToDevice, w->stream));
+    OVIS_CUDA(cudaMemcpyAsync(w->d_mv_codes, codes.data(), sizeof(uint32_t) * (size_t)n_views, cudaMemcpyHostToDevice, w->stream));
     OVIS_CUDA(cudaMemcpyAsync(w->d_mv_groups, rel.data(), sizeof(ovis::ViewGroupDev) * rel.size(), cudaMemcpyHostToDevice, w->stream));
     OVIS_CUDA(cudaStreamSynchronize(w->stream));       // rel / req are locals
 
@@ -853,6 +862,7 @@ int cull_views_grouped(OvisWorld *w, int32_t n_views, const float *planes, const
             a.n_groups = (int)(p.g1 - p.g0);
             a.planes = reinterpret_cast<const float4 *>(w->d_mv_planes) + 6 * (size_t)p.v0;
             a.view_require = w->d_mv_require + p.v0;
+            a.view_codes = w->d_mv_codes + p.v0;
             a.n_views = p.v1 - p.v0;
             a.counts = w->d_mv_counts;
             a.sub_masks = reinterpret_cast<uint8_t *>(w->d_mv_counts + w->cap_mv_counts);
@@ -1003,7 +1013,7 @@ int ovis_world_destroy(OvisWorld *w) {
                      w->d_node_entity, w->d_dirty, w->d_light_uniforms, w->d_light_types, w->d_entity_node, w->d_pass_counts, w->d_draw_totals, w->d_draw_counts,
                      w->d_extra_entity, w->d_extra_node, w->d_level_lists, w->d_lights, w->d_light_out,
                      w->d_staging, w->d_tile_counts, w->d_block_totals, w->d_exchange, w->d_mv_counts, w->d_mv_totals, w->d_mv_planes,
-                     w->d_mv_require, w->d_mv_groups, w->d_mv_hits, w->d_result, w->d_counts, w->d_csr_entities, w->d_csr_offsets,
+                     w->d_mv_require, w->d_mv_codes, w->d_mv_groups, w->d_mv_hits, w->d_result, w->d_counts, w->d_csr_entities, w->d_csr_offsets,
                      w->d_stage[0], w->d_stage[1] };
     for (void *b : bufs)
         if (b)
