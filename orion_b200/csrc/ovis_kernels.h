@@ -109,6 +109,7 @@ struct MultiArgs {
     const uint32_t *caster_mask; // alive & castsShadow
     const ViewGroupDev *groups;
     int n_groups;
+    int any_cube;                // 0: no group of this pass has a finite pre-filter cube (plain views): the K6 work is skipped
     const float4 *planes;        // 6 per view
     const uint32_t *view_require;// per view: non-zero = shadow casters only
     const uint32_t *view_codes;  // per view: 3 bits per plane (bit c = normal component c >= 0), plane p at bits 3p..3p+2

@@ -35,7 +35,7 @@ constexpr int kMultiWarps = 8;                   // warps per CTA
 // Shared memory per warp: n_views survivor counters + ceil(n_groups / 32) "this group had a candidate" words.
 __host__ __device__ inline int multi_words_per_warp(int n_views, int n_groups) { return n_views + (n_groups + 31) / 32; }
 
-template <bool WRITE>
+template <bool WRITE, bool CUBES>
 __global__ void __launch_bounds__(kMultiWarps * 32, 3)
 multi_pass_kernel(const __grid_constant__ MultiArgs a) {
     extern __shared__ uint32_t s_words[];
@@ -85,8 +85,11 @@ multi_pass_kernel(const __grid_constant__ MultiArgs a) {
             //      |coordinate|. A box with a NaN or non-finite side gets Re = +inf and can never be rejected.
             float lo[3][4], hi[3][4];
             bool lane_odd = false;
+            constexpr bool cubes = CUBES;                        // plain views (camera, cascades, spot lights): nothing to pre-filter
 #pragma unroll
             for (int j = 0; j < 4; j++) {
+                if (!cubes)
+                    break;
                 const float sx = mx[0][j] - mn[0][j], sy = mx[1][j] - mn[1][j], sz = mx[2][j] - mn[2][j];
                 const float ext = fmaxf(fmaxf(fmaxf(sx, sy), sz), 0.0f);
                 const float mag = fmaxf(fmaxf(fmaxf(fabsf(mn[0][j]), fabsf(mx[0][j])), fmaxf(fabsf(mn[1][j]), fabsf(mx[1][j]))),
@@ -107,6 +110,8 @@ multi_pass_kernel(const __grid_constant__ MultiArgs a) {
             float ulo[3], uhi[3];
 #pragma unroll
             for (int c = 0; c < 3; c++) {
+                if (!cubes)
+                    break;
                 ulo[c] = fminf(fminf(lo[c][0], lo[c][1]), fminf(lo[c][2], lo[c][3]));
                 uhi[c] = fmaxf(fmaxf(hi[c][0], hi[c][1]), fmaxf(hi[c][2], hi[c][3]));
 #pragma unroll
@@ -115,7 +120,7 @@ multi_pass_kernel(const __grid_constant__ MultiArgs a) {
                     uhi[c] = fmaxf(uhi[c], __shfl_xor_sync(0xffffffffu, uhi[c], o));
                 }
             }
-            const bool warp_odd = __any_sync(0xffffffffu, lane_odd);      // fminf/fmaxf drop NaNs: then test every group
+            const bool warp_odd = !cubes || __any_sync(0xffffffffu, lane_odd);   // fminf/fmaxf drop NaNs: then test every group
 
             for (int gw = 0; gw < hit_words; gw++) {
                 // lane-parallel: lane L tests group gw*32 + L against the union box
@@ -138,9 +143,11 @@ multi_pass_kernel(const __grid_constant__ MultiArgs a) {
                     const int gi = gw * 32 + bit;
                     const ViewGroupDev grp = a.groups[gi];
                     // ---- group side: candidate iff the inflated box overlaps the group's (inflated) cube
-                    uint32_t cand = 0;
+                    uint32_t cand = cubes ? 0u : 0xfu;
 #pragma unroll
                     for (int j = 0; j < 4; j++) {
+                        if (!cubes)
+                            break;
                         // separated along some axis <=> the largest of the six gaps is > 0. Subtractions run on the FMA
                         // pipe and the maxima fold three at a time (FMNMX3), which leaves ONE compare on the half-rate ALU
                         // pipe instead of six plus their combination; a NaN gap is ignored by fmaxf and an all-NaN set
@@ -299,16 +306,23 @@ multi_scan_tiles_kernel(uint32_t *counts, const uint32_t *block_totals, int num_
 int multi_max_blocks_per_sm(int n_views, int n_groups) {
     int blocks = 0;
     size_t smem = sizeof(uint32_t) * kMultiWarps * (size_t)multi_words_per_warp(n_views, n_groups);
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks, multi_pass_kernel<false>, kMultiWarps * 32, smem);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks, multi_pass_kernel<false, true>, kMultiWarps * 32, smem);
     return blocks;
 }
 
 void launch_multi_pass(const MultiArgs &a, bool write, int grid, cudaStream_t s) {
     size_t smem = sizeof(uint32_t) * kMultiWarps * (size_t)multi_words_per_warp(a.n_views, a.n_groups);
-    if (write)
-        multi_pass_kernel<true><<<grid, kMultiWarps * 32, smem, s>>>(a);
-    else
-        multi_pass_kernel<false><<<grid, kMultiWarps * 32, smem, s>>>(a);
+    if (a.any_cube) {
+        if (write)
+            multi_pass_kernel<true, true><<<grid, kMultiWarps * 32, smem, s>>>(a);
+        else
+            multi_pass_kernel<false, true><<<grid, kMultiWarps * 32, smem, s>>>(a);
+    } else {
+        if (write)
+            multi_pass_kernel<true, false><<<grid, kMultiWarps * 32, smem, s>>>(a);
+        else
+            multi_pass_kernel<false, false><<<grid, kMultiWarps * 32, smem, s>>>(a);
+    }
 }
 
 void launch_multi_scans(const MultiArgs &a, long long *csr_offsets_of_pass, cudaStream_t s) {

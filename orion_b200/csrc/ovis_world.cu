@@ -860,6 +860,10 @@ int cull_views_grouped(OvisWorld *w, int32_t n_views, const float *planes, const
             a.caster_mask = any_require ? w->d_caster_bits : nullptr;
             a.groups = w->d_mv_groups + p.g0;
             a.n_groups = (int)(p.g1 - p.g0);
+            a.any_cube = 0;
+            for (size_t g = p.g0; g < p.g1; g++)
+                if (std::isfinite(groups[g].lo[0]) || std::isfinite(groups[g].hi[0]))
+                    a.any_cube = 1;
             a.planes = reinterpret_cast<const float4 *>(w->d_mv_planes) + 6 * (size_t)p.v0;
             a.view_require = w->d_mv_require + p.v0;
             a.view_codes = w->d_mv_codes + p.v0;
