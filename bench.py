@@ -48,6 +48,15 @@ def workload_name(n_gpus: int, n: int) -> str:
             f"1 camera frustum (hfov 75, 16:9, far 1000), config-2 distribution in [-{EXTENT:g},{EXTENT:g}]^3")
 
 
+CACHE_NOTE = "inputs larger than L2 (300 MB of bounds per GPU vs 126 MB L2); no flush needed"
+
+
+def bench_config(n_gpus: int, n: int, visible_total: int) -> dict:
+    """`config` of the JSON line - the same keys and values in both arms (ours and --impl reference)."""
+    return {"workload": workload_name(n_gpus, n), "entities_total": n * n_gpus, "views": 1, "visible_total": int(visible_total),
+            "cache": CACHE_NOTE if n * 24 > 126e6 else "inputs fit L2 (sizes below the benched one are for debugging only)"}
+
+
 def host_cores() -> int:
     try:
         return len(os.sched_getaffinity(0))
@@ -150,30 +159,37 @@ def as_shipped_timing(oracle, aabb, view, iters=5):
 
 
 def run_reference(args, rank: int):
+    """The reference's CPU cull of the SAME work as our arm: every one of the N shards, every step, on this host's cores."""
     if rank != 0:
         return
     from oracle import pyoracle
     oracle = pyoracle.load("best")
     cores = host_cores()
     n = args.entities_per_gpu
-    aabb, _ = shard_scene(0, n)
+    shards = [shard_scene(r, n)[0] for r in range(args.gpus)]
     view = scenes.default_camera()
     planes = oracle.view_planes(view)
-    times, out = cpu_cull_timing(oracle, aabb, planes, cores, args.steps, max(args.warmup, 1))
-    total = float(times.sum())
-    value = n * args.steps / total
-    shipped = as_shipped_timing(oracle, aabb[:1_000_000], view) if not args.skip_extras else None
-    sample = (f"shard 0 ({n / 1e6:g}M entities, 1 frustum) per step; the arithmetic is the reference's own "
-              f"Math::intersect compiled from its sources, driven over flat AABB arrays by {cores} host threads"
-              if oracle.name == "reference" else
-              f"shard 0 ({n / 1e6:g}M entities, 1 frustum) per step; C restatement of the reference, {cores} host threads")
+    visible = 0
+    for _ in range(max(args.warmup, 1)):
+        visible = sum(len(oracle.cull_aabb(a, planes, threads=cores)) for a in shards)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        for a in shards:
+            oracle.cull_aabb(a, planes, threads=cores)
+    total = time.perf_counter() - t0
+    value = n * args.gpus * args.steps / total
+    shipped = as_shipped_timing(oracle, shards[0][:1_000_000], view) if not args.skip_extras else None
+    how = ("the arithmetic is the reference's own Math::intersect compiled from its sources, driven over flat AABB arrays"
+           if oracle.name == "reference" else "C restatement of the reference")
+    sample = (f"all {args.gpus} shard(s) of {n / 1e6:g}M entities, 1 frustum, per step ({n * args.gpus / 1e6:g}M entity-view tests); "
+              f"{how} by {cores} host threads")
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": total / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": workload_name(args.gpus, n), "entities_per_step_timed": n, "views": 1},
+        "config": bench_config(args.gpus, n, visible),
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": oracle.name, "sample": sample,
-                         "visible": int(len(out)), "as_shipped_std_list_1thread": shipped},
+                         "visible": int(visible), "as_shipped_std_list_1thread": shipped},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -395,14 +411,12 @@ def run_ours(args, rank: int, local_rank: int, world_size: int):
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world_size, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": elapsed_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
-        "config": {"workload": workload_name(world_size, n), "entities_total": total_entities, "views": 1,
-                   "visible_total": total_visible,
-                   "parallelism": ((f"entity shards x{world_size}, exchange of visible lists: " +
-                                    ("gather kernel stores to peers over NVLink + ready flags, no collective" if sw.exchange_mode == "p2p"
-                                     else "NCCL all-gather")) if world_size > 1 else "1 GPU"),
-                   "cache": "inputs larger than L2 (300 MB of bounds per GPU vs 126 MB L2); no flush needed"},
+        "config": bench_config(world_size, n, total_visible),
+        "parallelism": ((f"entity shards x{world_size}, exchange of visible lists: " +
+                         ("gather kernel stores to peers over NVLink + ready flags, no collective" if sw.exchange_mode == "p2p"
+                          else "NCCL all-gather")) if world_size > 1 else "1 GPU"),
         "cull_ms_per_frame": elapsed_ms / args.steps,
-        "roofline": {"bound": "hbm", "kernel": "ovis::cull_test_kernel<2,false,true> (dominant: reads every bound once)",
+        "roofline": {"bound": "hbm", "kernel": "ovis::cull_test_kernel<1,false,4> (dominant: reads every bound once)",
                      "achieved": achieved, "peak": peak_gbs, "unit": "GB/s", "frac": achieved / peak_gbs,
                      "traffic": ncu_traffic_bytes() if n == SHARD_ENTITIES else None,
                      "traffic_source": "profiles/r01_cull_test_kernel_ncu.csv (ncu --set full, one launch, same workload)",
@@ -421,15 +435,25 @@ def run_ours(args, rank: int, local_rank: int, world_size: int):
         "clocks": clocks,
     }
 
-    if rank == 0 and world_size == 1 and not args.skip_extras:
-        # parity of the benched result + CPU baseline on the same shard, same host
+    if rank == 0 and not args.skip_extras:
+        # parity of the benched result: the merged list of ALL shards against the CPU oracle's cull of all shards
         from oracle import pyoracle
         oracle = pyoracle.load("best")
         cores = host_cores()
-        times, exp = cpu_cull_timing(oracle, aabb, planes, cores, 5, 1)
         got_ids = merged_list(blocks, counts)
+        exp_parts, times = [], None
+        for r in range(world_size):
+            shard = aabb if r == rank else shard_scene(r, n)[0]
+            if r == 0 and world_size == 1:
+                times, e = cpu_cull_timing(oracle, shard, planes, cores, 5, 1)
+            else:
+                e = oracle.cull_aabb(shard, planes, threads=cores)
+            exp_parts.append(e.astype(np.uint64) + np.uint64(r * n))
+        exp = np.concatenate(exp_parts).astype(np.uint32)
         line["parity"] = {"bit_exact_vs_oracle": bool(np.array_equal(got_ids, exp)), "oracle": oracle.name,
-                          "visible": int(len(exp))}
+                          "visible": int(len(exp)), "shards_checked": world_size}
+    if rank == 0 and world_size == 1 and not args.skip_extras:
+        # CPU baseline on the same shard, same host
         t1, _ = cpu_cull_timing(oracle, aabb, planes, 1, 2, 1)
         line["cpu_baseline"] = {
             "value": n / float(np.median(times)), "unit": UNIT, "cores": cores, "kind": oracle.name,
@@ -449,15 +473,30 @@ def run_ours(args, rank: int, local_rank: int, world_size: int):
         vis_m = int(sw.block[0].item())
         with torch.cuda.stream(stream):
             line["also"] = {
-                "masked_cull_same_shard": {"kernel": "ovis::cull_test_kernel<2,true,true> + gather", "ms_mean": float(mk.mean()),
+                "masked_cull_same_shard": {"kernel": "masked test kernel + gather", "ms_mean": float(mk.mean()),
                                            "achieved_gbs": (24 * n + n / 8 + 4 * vis_m) / (float(mk.mean()) * 1e-3) / 1e9},
                 "config2_1M": config2_extra(torch, lib, stream, scratch, peak_gbs),
             }
         del scratch
+        # the other BASELINE.json configs, each with parity against the oracle and its own CPU baseline (tools/bench_configs.py)
+        world.close()
+        world = None
+        del sw
+        torch.cuda.empty_cache()
+        from tools import bench_configs
+        for key, fn in (("config1", bench_configs.config1),
+                        ("config3", lambda: bench_configs.config3(False, full_parity=True)),
+                        ("config4", lambda: bench_configs.config4(False, full_parity=True, brute=False)),
+                        ("dense_visible", bench_configs.dense_visible)):
+            try:
+                line["also"][key] = fn()
+            except Exception as e:            # an extra must not take the headline line with it
+                line["also"][key] = {"error": repr(e)}
 
     if rank == 0:
         emit(line)
-    world.close()
+    if world is not None:
+        world.close()
     if world_size > 1:
         dist.barrier()
         dist.destroy_process_group()

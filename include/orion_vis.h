@@ -243,7 +243,9 @@ int ovis_world_exchange_error(OvisWorld *world, int32_t *out_error);
  * `capacity` clipped the writes), but it needs no OvisWorld and allocates nothing: the caller passes the
  * world AABBs as device memory in the library's SoA layout (component k of entity i at
  * d_world_aabb[k * stride + i], k = min xyz then max xyz; stride a multiple of 4 and >= n_entities rounded
- * up to 256) and the device outputs, and the kernels' scratch is a fixed ~4.2 MB array inside the library
+ * up to 256; d_world_aabb 16-byte aligned, because the kernels read 128-bit vectors - a misaligned pointer is
+ * refused with OVIS_ERR_INVALID rather than left to fault on the device) and the device outputs, and the kernels'
+ * scratch is a fixed ~4.2 MB array inside the library
  * image (present on every GPU that loads the library, until exit). Limits and rules: at most
  * OVIS_NOALLOC_MAX_ENTITIES entities per call (more -> OVIS_ERR_CAPACITY); all calls on a GPU share that one
  * scratch, so calls whose kernels could overlap on the GPU (different streams or threads) race - keep them on

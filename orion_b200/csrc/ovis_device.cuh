@@ -215,4 +215,38 @@ __device__ __forceinline__ float4 plane_dist4_coded(uint32_t code, float4 q, con
     }
 }
 
+// ---- results of one group of 128 entities (4 per lane) ---------------------------------------------------------------
+// keep: bit j = entity 4 * lane + j of the group is visible. The 128 bits leave as four bitmap words, assembled with
+// three butterfly shuffles (lanes 8k .. 8k+7 own word k).
+__device__ __forceinline__ void store_group_bits(uint32_t *survivors, int64_t group, uint32_t keep, int lane) {
+    uint32_t v = keep << ((lane & 7) * 4);
+    v |= __shfl_xor_sync(0xffffffffu, v, 1);
+    v |= __shfl_xor_sync(0xffffffffu, v, 2);
+    v |= __shfl_xor_sync(0xffffffffu, v, 4);
+    if ((lane & 7) == 0)
+        survivors[group * 4 + (lane >> 3)] = v;
+}
+
+// bits of the lane's four entities that exist (ragged tail) and, if MASKED, are set in the alive / caster mask
+template <bool MASKED>
+__device__ __forceinline__ uint32_t candidate_bits(int64_t e0, int64_t n, uint32_t mask_word) {
+    uint32_t k = 0xfu;
+    if (MASKED)
+        k = (mask_word >> (e0 & 31)) & 0xfu;
+    if (e0 + 3 >= n) {
+        const int64_t valid = n - e0;
+        k &= valid <= 0 ? 0u : ((1u << valid) - 1u);
+    }
+    return k;
+}
+
+__device__ __forceinline__ uint32_t negative_bits(const float4 &lowest) {
+    uint32_t out = 0;
+    if (lowest.x < 0.0f) out |= 1u;
+    if (lowest.y < 0.0f) out |= 2u;
+    if (lowest.z < 0.0f) out |= 4u;
+    if (lowest.w < 0.0f) out |= 8u;
+    return out;
+}
+
 }  // namespace ovis

@@ -9,15 +9,16 @@ namespace ovis {
 constexpr uint32_t kNone = 0xffffffffu;
 constexpr int kCullThreads = 256;                       // threads per CTA of the cull test kernel
 constexpr int kMaxPeers = 8;                            // extra destinations of the gather kernel (one NVSwitch box)
-constexpr int kGatherTiles = 64;                        // warp tiles per block of the gather kernel
+constexpr int kMaskBlockEntities = 8192;                // entity slots per block of the gather kernel ...
+constexpr int kMaskBlockWords = kMaskBlockEntities / 32;   // ... = 256 words of the survivor bitmap, one per thread
+constexpr int kMaskBlockGroups = kMaskBlockEntities / 128; // ... = 64 groups of 128 entities (one warp, 4 per lane)
 constexpr int kCullTile = 1024;                         // storage padding: a multiple of every warp-tile size
 
 struct CullVariant {
-    int groups;                  // float4 groups (4 consecutive entities each) per lane
-    bool pipelined;              // two register sets per warp: tile t + 1 is requested before tile t is tested
-    bool packed;                 // sign-specialised plane code with FMUL2 products (ovis_device.cuh: outside_plane4)
-    int async_stages;            // > 0: cp.async ring of that many stages per warp in shared memory (groups must be 1)
-    int tile() const { return 128 * groups; }   // entities per warp tile
+    int groups;                  // register-fed kernel: float4 groups (4 consecutive entities each) per lane and tile
+    int ctas;                    // register-fed kernel: CTAs per SM it is compiled for
+    int ring_stages;             // > 0: the TMA ring kernel with that many stages of 1024 entities per CTA
+    int ring_sets;               // ... and that many sets of eight consumer warps taking the stages in turn
 };
 
 // SoA storage convention: component k of item i lives at base[k * stride + i]; stride is a multiple of
@@ -40,17 +41,16 @@ struct LevelArgs {
 
 struct CullArgs {                 // K3a
     float4 planes[6];            // normal xyz, distance
+    uint32_t sign_codes;         // plane_sign_codes(planes): which corner is the P-vertex, 3 bits per plane
     const float *bounds;         // world AABBs, 6 x stride
     int64_t stride;
     int64_t n;                   // entity slots
-    int num_tiles;               // warp tiles: ceil(n / tile of the launched variant)
-    int num_blocks;              // blocks of kGatherTiles warp tiles
-    const uint32_t *mask;        // 1 bit per slot (alive [& caster]); only read by the MASKED variant
-    uint32_t *staging;           // scratch: num_tiles x tile ids, each tile's survivors at the start of its slot
-    uint32_t *tile_counts;       // scratch: survivors per warp tile
-    uint32_t *block_totals;      // scratch: survivors per block of kGatherTiles tiles (zero on entry)
+    int num_groups;              // groups of 128 entities: ceil(n / 128)
+    int num_blocks;              // blocks of kMaskBlockEntities slots
+    const uint32_t *mask;        // 1 bit per slot (alive [& caster]); only read by the MASKED kernels
+    uint32_t *survivors;         // scratch: 1 bit per slot, 4 words per group; every group's words are written
+    uint32_t *block_totals;      // scratch: survivors per block (zero on entry)
     uint32_t *block_totals_next; // scratch: the set the next launch accumulates into; zeroed here
-    uint32_t id_base;            // added to every emitted slot id (global id of a shard's first entity)
     // sharded exchange (optional): wait until wait_flags[i] >= wait_value for i < n_wait (<= 32) before finishing
     int n_wait;
     const uint32_t *wait_flags;
@@ -59,11 +59,11 @@ struct CullArgs {                 // K3a
 };
 
 struct GatherArgs {               // K3b
-    const uint32_t *staging;
-    const uint32_t *tile_counts;
+    const uint32_t *survivors;
     const uint32_t *block_totals;
-    int num_tiles;
-    int tile_entities;
+    int64_t num_words;           // bitmap words: 4 x num_groups
+    int num_blocks;
+    uint32_t id_base;            // added to every emitted slot id (global id of a shard's first entity)
     uint32_t *out;               // visible slot ids, ascending
     long long capacity;          // writable entries of out
     const long long *d_base;     // optional: start offset inside out (CSR chaining), device memory
@@ -91,42 +91,75 @@ struct GatherArgs {               // K3b
     uint32_t *error_flag;         // set to 1 if a wait gave up (a peer never arrived)
 };
 
-// ---- K4 multi-view ------------------------------------------------------------------------------
-constexpr int kMultiMaxViews = 1024;          // views per pass (one CTA of 1024 threads scans them)
+// ---- K4 multi-view + K6 light binning (ovis_multiview.cu) -------------------------------------------------------
+// Views are numbered 0 .. n_views - 1 in the caller's order; every view owns a row of per-block totals and a CSR list.
+// "Plain" views (camera, cascades, spot lights: no pre-filter) go through a dense pass that leaves one survivor bit
+// per (view, entity); the six faces of a point light form a "cube group" and go through the sparse pass, which finds
+// the few (entity, light) candidate pairs through a uniform grid over the lights.
+constexpr int kMvMaxGroupViews = 6;           // views of one cube group (a point light's faces)
+constexpr int kMvMaxGroups = 4096;            // cube groups per call (12 bits of the record key)
+constexpr int kMvGridMax = 64;                // cells per axis of the light grid (bitmap rows are 64-bit words)
+constexpr int kMvPairCapacity = 8192;         // candidate pairs one block of 8192 entities may produce before falling back
 
-struct ViewGroupDev {
-    float lo[3], hi[3];          // the group's pre-filter cube, already inflated by its rounding margin
-                                 // (centre -/+ (1.001 * range + 1e-3 * max|centre| + 0.01)); -inf/+inf = no pre-filter
-    int first_view, n_views;     // consecutive views of the pass that share this cube
+struct MvGroup {                  // one cube group
+    float lo[3], hi[3];          // the pre-filter cube, already inflated by its rounding margin
+    int first_view, n_views;     // its views are consecutive
+    uint32_t cell_lo, cell_hi;   // grid cells it covers: x | y << 8 | z << 16, inclusive (host-computed)
 };
 
-struct MultiArgs {
+struct MvGrid {
+    float lo[3], hi[3];          // exact bounds of the union of the groups' cubes
+    float inv_cell[3];           // cells per unit length
+    int dim[3];                  // cells per axis (<= kMvGridMax)
+};
+
+struct MvItem {                   // one survivor of the sparse pass, placed by mv_expand_items_kernel
+    uint32_t view, rank, id;     // rank inside (view, block); id already includes id_base
+};
+
+struct MvArgs {
     const float *bounds;         // world AABBs, 6 x stride
     int64_t stride;
     int64_t n;
-    int num_tiles;               // supertiles of 1024 entities
+    int num_groups128;           // groups of 128 entities
+    int num_blocks;              // blocks of kMaskBlockEntities
     const uint32_t *alive_mask;  // nullptr when every slot is live
-    const uint32_t *caster_mask; // alive & castsShadow
-    const ViewGroupDev *groups;
-    int n_groups;
-    int any_cube;                // 0: no group of this pass has a finite pre-filter cube (plain views): the K6 work is skipped
+    const uint32_t *caster_mask; // alive & castsShadow; nullptr when no view asks for casters
     const float4 *planes;        // 6 per view
-    const uint32_t *view_require;// per view: non-zero = shadow casters only
-    const uint32_t *view_codes;  // per view: 3 bits per plane (bit c = normal component c >= 0), plane p at bits 3p..3p+2
+    const uint32_t *view_meta;   // per view: bits 0-17 P-vertex sign codes (3 per plane), bit 31 = shadow casters only
     int n_views;
-    uint32_t *counts;            // [num_tiles][n_views]: counts after pass A, positions after the scans
-    uint8_t *sub_masks;          // [num_tiles][n_views]: bit s = sub-tile s holds a survivor of the view (A writes, C reads)
-    uint32_t *block_totals;      // [num_blocks][n_views], zero before pass A
-    uint32_t *group_hits;        // [num_tiles][ceil(n_groups / 32)]: bit = group had a candidate (A writes, C reads)
-    const long long *csr_offsets;// [n_views + 1] start of each view's list (valid after the scans)
+    uint32_t *totals;            // [n_views][num_blocks + 1]: counts, then (after the scan) exclusive prefixes + the total
+    long long *csr_offsets;      // [n_views + 1]
     uint32_t *out;
     long long capacity;
     uint32_t id_base;
+    uint32_t *state;             // [0] overflow bits (kMvOverflow*), [1] scan ticket, [2] light-grid nodes used, [3] items used
+    // dense pass
+    const uint32_t *plain_views; // view ids handled by the dense pass
+    int n_plain;
+    int views_per_warp;          // plain views one warp handles for its 128 entities (small worlds split the views)
+    uint32_t *masks;             // [n_plain][num_groups128 * 4]
+    // sparse pass
+    const MvGroup *groups;
+    int n_groups;
+    MvGrid grid;
+    unsigned long long *bitmap;  // [dim z][dim y]: bit x = some cube covers the cell
+    int32_t *heads;              // per cell: first node of its group list, -1 = none
+    uint32_t *node_group;        // per node: group index
+    int32_t *node_next;
+    uint32_t node_capacity;
+    MvItem *items;
+    uint32_t item_capacity;
+    uint2 *segments;             // per block: (first item, items)
 };
+constexpr uint32_t kMvOverflowPairs = 1u, kMvOverflowItems = 2u, kMvOverflowNodes = 4u;
 
-int multi_max_blocks_per_sm(int n_views, int n_groups);
-void launch_multi_pass(const MultiArgs &a, bool write, int grid, cudaStream_t s);
-void launch_multi_scans(const MultiArgs &a, long long *csr_offsets_of_pass, cudaStream_t s);
+void launch_mv_plain_test(const MvArgs &a, int num_sms, cudaStream_t s);
+void launch_mv_bin_lights(const MvArgs &a, cudaStream_t s);
+void launch_mv_sparse(const MvArgs &a, cudaStream_t s);
+void launch_mv_scan(const MvArgs &a, cudaStream_t s);
+void launch_mv_expand_masks(const MvArgs &a, cudaStream_t s);
+void launch_mv_expand_items(const MvArgs &a, cudaStream_t s);
 
 // ---- consumers of the visible lists (section 8(f)) -----------------------------------------------------------------
 struct DrawArgs {
@@ -211,7 +244,11 @@ void launch_extra_bounds(const uint32_t *entities, const uint32_t *nodes, int64_
 void launch_mark_dirty(const uint32_t *ids, int64_t n, uint8_t *dirty, cudaStream_t s);
 int cull_num_variants();
 CullVariant cull_variant(int v);
-int cull_variant_smem(int v);       // dynamic shared memory per CTA of the variant's test kernel
+// The variant used when none is forced: small sets are latency-bound (register-fed, many small warp tiles); large sets
+// stream through the TMA ring.
+inline int cull_default_variant(int64_t n_entities) { return n_entities < (4 << 20) ? 1 : 2; }
+int cull_test_grid(int variant, int num_groups, int resident_ctas);   // CTAs to launch
+uint32_t plane_sign_codes(const float planes[24]);
 void launch_cull_test(const CullArgs &a, bool masked, int variant, int grid, cudaStream_t s, bool overlap_previous_gather);
 void launch_cull_gather(const GatherArgs &a, cudaStream_t s);
 void launch_segments_to_host(const uint32_t *flags, uint32_t value, const uint32_t *segments, long long segment_words,

@@ -1,334 +1,747 @@
-// ovis_multiview.cu - K4: many views in one pass over the bounds, with K6's conservative pre-filter.
+// ovis_multiview.cu - K4: many views over one world, K6: light -> entity candidate binning.
 //
 // Replaces the reference's "one full world cull per shadow view" (render/src/deferred_render_pipeline.cc:259-284:
-// 1 + sum of shadow views full scans per frame) and serves the main camera + cascade views the same way.
+// 1 + sum of shadow views full scans per frame) and serves the main camera + cascade views the same way. Every exact
+// test is evaluated ONCE (round 1 counted, scanned and then repeated the tests to write).
 //
-// Views come in GROUPS: the views of one group share a pre-filter ball-cube (a point light's six cube faces share the
-// cube of half-side `range` about the light); a group without a cube has an infinite radius. Per pass (at most
-// kMultiMaxViews views):
-//
-//   A  multi_pass_kernel<false>  every warp walks "supertiles" of 1024 consecutive entities (8 x 128): loads the bounds
-//                                 once, and for every group runs the cube pre-filter (6 compares per entity) and,
-//                                 only where a candidate exists in the warp, the exact six-plane tests of its views with
-//                                 warp-uniform early-out. It counts survivors per (supertile, view): one coalesced row of
-//                                 counts per supertile plus sparse integer atomicAdds into per-(64-supertile block, view)
-//                                 totals, and a bit per (supertile, group) that had any candidate.
-//   B1 multi_scan_blocks_kernel  per view: exclusive scan of the block totals, view totals, CSR offsets of the pass.
-//   B2 multi_scan_tiles_kernel   per block: exclusive scan over its 64 supertiles, in place (counts -> positions).
-//   C  multi_pass_kernel<true>   the same walk again over the groups that had candidates, now writing each survivor id
-//                                 at its final position.
+//   dense pass (views without a pre-filter: camera, cascades, spot lights)
+//     mv_plain_test_kernel    a warp takes 128 entities (4 per lane, six 128-bit loads) and a chunk of the plain views; per
+//                             view the six plane tests with K3's instructions, result = 128 survivor bits in the view's
+//                             bitmap + the count added to the view's total for that block of 8192 entities. Small worlds
+//                             split the views over more warps so that the machine fills.
+//   sparse pass (cube groups: the six faces of a point light share the cube of half-side range + extent about the light)
+//     mv_bin_lights_kernel    K6, light side: every group is linked into the cells of a uniform grid it covers (per-cell
+//                             lists built with atomics) and marks them in an occupancy bitmap.
+//     mv_sparse_kernel        one CTA per block of 8192 entities: (1) every entity looks its cells up in the occupancy
+//                             bitmap held in shared memory - nearly all leave here; (2) the rest walk their cells' lists
+//                             and append (entity, light) candidate pairs that pass the cube test to a shared-memory list
+//                             with shared-memory atomics; (3) one thread per pair runs the exact tests of the light's
+//                             faces; (4) the surviving records are sorted by (light, entity) in shared memory, which makes
+//                             everything that follows independent of the order the atomics happened in; (5) a segmented
+//                             scan ranks each survivor inside its (view, block), the block's per-view totals are stored
+//                             and the survivors leave as (view, rank, id) items.
+//   mv_scan_kernel            per view: exclusive scan of the block totals; the last CTA turns the view totals into CSR
+//                             offsets.
+//   mv_expand_masks_kernel    dense pass: (block, view) bitmap -> ids at csr_offset + block prefix + rank.
+//   mv_expand_items_kernel    sparse pass: items -> ids at csr_offset + block prefix + rank.
 //
 // Positions are sums of counts, so every list is in slot (= insertion) order and identical from run to run. The exact
-// tests are the same instructions as K3 (ovis_device.cuh: outside_plane), so lists are bit-identical to brute force;
-// the pre-filter only ever skips (entity, group) pairs that every one of the group's views would reject
-// (derivation in DESIGN.md section 4, K6).
+// tests are the same instructions as K3 (ovis_device.cuh), so lists are bit-identical to brute force; the grid and the
+// cube test only ever skip (entity, group) pairs that every one of the group's views would reject.
 #include "ovis_kernels.h"
 
 #include "ovis_device.cuh"
 
 namespace ovis {
 
-constexpr int kSuperTile = 1024;                 // entities per supertile (one warp, 8 sub-tiles of 128)
-constexpr int kSubTiles = 8;
-constexpr int kMultiWarps = 8;                   // warps per CTA
+constexpr int kMvThreads = 256;
 
-// Shared memory per warp: n_views survivor counters + ceil(n_groups / 32) "this group had a candidate" words.
-__host__ __device__ inline int multi_words_per_warp(int n_views, int n_groups) { return n_views + (n_groups + 31) / 32; }
+// ------------------------------------------------------------------------------------------------
+// dense pass
+// ------------------------------------------------------------------------------------------------
 
-template <bool WRITE, bool CUBES>
-__global__ void __launch_bounds__(kMultiWarps * 32, 3)
-multi_pass_kernel(const __grid_constant__ MultiArgs a) {
-    extern __shared__ uint32_t s_words[];
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int hit_words = (a.n_groups + 31) / 32;
-    uint32_t *counters = s_words + warp * multi_words_per_warp(a.n_views, a.n_groups);   // survivors so far, per view
-    uint32_t *hits = counters + a.n_views;                                                // groups with a candidate
-    const int warps_total = gridDim.x * kMultiWarps;
-    const float4 *__restrict__ bounds = reinterpret_cast<const float4 *>(a.bounds);
-    const int64_t vstride = a.stride >> 2;
-
-    for (int tile = blockIdx.x * kMultiWarps + warp; tile < a.num_tiles; tile += warps_total) {
-        // counters[v]: bits 0-15 survivors of view v so far in this supertile; bits 16-23 (pass A: collected, pass C:
-        // loaded) which of the 8 sub-tiles hold a survivor of view v - pass C repeats the exact tests only there
-        for (int v = lane; v < a.n_views; v += 32)
-            counters[v] = WRITE ? (uint32_t)a.sub_masks[(int64_t)tile * a.n_views + v] << 16 : 0u;
-        // pass A finds which groups have any candidate in this supertile; pass C only revisits those
-        for (int k = lane; k < hit_words; k += 32)
-            hits[k] = WRITE ? a.group_hits[(int64_t)tile * hit_words + k] : 0u;
-        __syncwarp();
-        const uint32_t *row = WRITE ? a.counts + (int64_t)tile * a.n_views : nullptr;   // positions after pass B2
-
-        for (int sub = 0; sub < kSubTiles; sub++) {
-            // ---- 4 consecutive entities per lane: six 128-bit loads
-            const int64_t v = (int64_t)tile * (kSuperTile / 4) + sub * 32 + lane;        // float4 index
-            const int64_t e0 = v << 2;
-            const float4 ax = __ldg(bounds + 0 * vstride + v), ay = __ldg(bounds + 1 * vstride + v), az = __ldg(bounds + 2 * vstride + v);
-            const float4 bx = __ldg(bounds + 3 * vstride + v), by = __ldg(bounds + 4 * vstride + v), bz = __ldg(bounds + 5 * vstride + v);
-            const float mn[3][4] = { { ax.x, ax.y, ax.z, ax.w }, { ay.x, ay.y, ay.z, ay.w }, { az.x, az.y, az.z, az.w } };
-            const float mx[3][4] = { { bx.x, bx.y, bx.z, bx.w }, { by.x, by.y, by.z, by.w }, { bz.x, bz.y, bz.z, bz.w } };
-            uint32_t alive = 0xfu;
-            if (e0 + 3 >= a.n) {
-                int64_t left = a.n - e0;
-                alive = left <= 0 ? 0u : ((1u << left) - 1u);
-            }
-            uint32_t caster = alive;
-            if (a.alive_mask)
-                alive &= (__ldg(a.alive_mask + (e0 >> 5)) >> (e0 & 31)) & 0xfu;
-            if (a.caster_mask)
-                caster &= (__ldg(a.caster_mask + (e0 >> 5)) >> (e0 & 31)) & 0xfu;          // already implies alive
-            else
-                caster = alive;
-            if (!__any_sync(0xffffffffu, alive))
-                continue;
-
-            // ---- K6 pre-filter, entity side: the box inflated by Re = 1.001 * largest extent + 1e-3 * largest
-            //      |coordinate|. A box with a NaN or non-finite side gets Re = +inf and can never be rejected.
-            float lo[3][4], hi[3][4];
-            bool lane_odd = false;
-            constexpr bool cubes = CUBES;                        // plain views (camera, cascades, spot lights): nothing to pre-filter
+// The exact tests of R plain views that share their P-vertex sign codes (a camera and its cascades; the same face of
+// every point light), for the lane's four entities. Which corner is the P-vertex is decided by ONE warp-uniform switch per
+// plane for all R views (ncu, one view at a time: the six switches per view were a third of all instructions).
+// Products are packed FMUL2, "any distance < 0" is "minimum distance < 0" (fminf ignores a NaN operand exactly as a NaN
+// distance rejects nothing): the same instructions as K3. Warp-uniform early-out after the two side planes.
+template <int R>
+__device__ __forceinline__ void test_view_run(const MvArgs &a, int pv, uint32_t codes, const float4 &ax, const float4 &ay, const float4 &az,
+                                              const float4 &bx, const float4 &by, const float4 &bz, uint32_t alive, uint32_t caster,
+                                              int64_t group, int lane) {
+    const int64_t num_words = (int64_t)a.num_groups128 * 4;
+    const int row = a.num_blocks + 1;
+    int view[R];
+    uint32_t keep[R];
+    const float4 *pl[R];
+    uint32_t any = 0;
 #pragma unroll
-            for (int j = 0; j < 4; j++) {
-                if (!cubes)
-                    break;
-                const float sx = mx[0][j] - mn[0][j], sy = mx[1][j] - mn[1][j], sz = mx[2][j] - mn[2][j];
-                const float ext = fmaxf(fmaxf(fmaxf(sx, sy), sz), 0.0f);
-                const float mag = fmaxf(fmaxf(fmaxf(fabsf(mn[0][j]), fabsf(mx[0][j])), fmaxf(fabsf(mn[1][j]), fabsf(mx[1][j]))),
-                                        fmaxf(fabsf(mn[2][j]), fabsf(mx[2][j])));
-                float re = ext * 1.001f + mag * 1.0e-3f;
-                const bool odd = sx != sx || sy != sy || sz != sz || !(ext <= 3.0e38f) || !(mag <= 3.0e38f);   // fmaxf drops NaNs
-                if (odd)
-                    re = __int_as_float(0x7f800000);
-                lane_odd |= odd;
+    for (int r = 0; r < R; r++) {
+        view[r] = (int)__ldg(a.plain_views + pv + r);
+        keep[r] = (__ldg(a.view_meta + view[r]) >> 31) ? caster : alive;
+        pl[r] = a.planes + 6 * view[r];
+        any |= keep[r];
+    }
+    const float inf = __int_as_float(0x7f800000);
+    float4 lowest[R], held[R];
 #pragma unroll
-                for (int c = 0; c < 3; c++) {
-                    lo[c][j] = mn[c][j] - re;
-                    hi[c][j] = mx[c][j] + re;
-                }
-            }
-            // ---- union of the warp's 128 inflated boxes: a group whose cube misses it has no candidate in this
-            //      sub-tile (scenes laid out by their hierarchy keep neighbours in space next to each other in memory)
-            float ulo[3], uhi[3];
+    for (int r = 0; r < R; r++)
+        lowest[r] = make_float4(inf, inf, inf, inf);
+    bool alive_somewhere = __any_sync(0xffffffffu, any != 0u);
 #pragma unroll
-            for (int c = 0; c < 3; c++) {
-                if (!cubes)
-                    break;
-                ulo[c] = fminf(fminf(lo[c][0], lo[c][1]), fminf(lo[c][2], lo[c][3]));
-                uhi[c] = fmaxf(fmaxf(hi[c][0], hi[c][1]), fmaxf(hi[c][2], hi[c][3]));
-#pragma unroll
-                for (int o = 16; o > 0; o >>= 1) {
-                    ulo[c] = fminf(ulo[c], __shfl_xor_sync(0xffffffffu, ulo[c], o));
-                    uhi[c] = fmaxf(uhi[c], __shfl_xor_sync(0xffffffffu, uhi[c], o));
-                }
-            }
-            const bool warp_odd = !cubes || __any_sync(0xffffffffu, lane_odd);   // fminf/fmaxf drop NaNs: then test every group
-
-            for (int gw = 0; gw < hit_words; gw++) {
-                // lane-parallel: lane L tests group gw*32 + L against the union box
-                bool near = false;
-                {
-                    const int gl = gw * 32 + lane;
-                    if (gl < a.n_groups) {
-                        const ViewGroupDev gq = a.groups[gl];
-                        near = warp_odd || !((uhi[0] < gq.lo[0]) | (ulo[0] > gq.hi[0]) | (uhi[1] < gq.lo[1]) |
-                                             (ulo[1] > gq.hi[1]) | (uhi[2] < gq.lo[2]) | (ulo[2] > gq.hi[2]));
-                    }
-                }
-                uint32_t todo = __ballot_sync(0xffffffffu, near);
-                if (WRITE)
-                    todo &= hits[gw];
-                uint32_t found = 0;
-                while (todo) {
-                    const int bit = __ffs(todo) - 1;
-                    todo &= todo - 1;
-                    const int gi = gw * 32 + bit;
-                    const ViewGroupDev grp = a.groups[gi];
-                    // ---- group side: candidate iff the inflated box overlaps the group's (inflated) cube
-                    uint32_t cand = cubes ? 0u : 0xfu;
-#pragma unroll
-                    for (int j = 0; j < 4; j++) {
-                        if (!cubes)
-                            break;
-                        // separated along some axis <=> the largest of the six gaps is > 0. Subtractions run on the FMA
-                        // pipe and the maxima fold three at a time (FMNMX3), which leaves ONE compare on the half-rate ALU
-                        // pipe instead of six plus their combination; a NaN gap is ignored by fmaxf and an all-NaN set
-                        // compares false, so odd boxes stay candidates exactly as with the six compares.
-                        const float gap = fmaxf(fmaxf(fmaxf(grp.lo[0] - hi[0][j], lo[0][j] - grp.hi[0]),
-                                                      fmaxf(grp.lo[1] - hi[1][j], lo[1][j] - grp.hi[1])),
-                                                fmaxf(grp.lo[2] - hi[2][j], lo[2][j] - grp.hi[2]));
-                        cand |= gap > 0.0f ? 0u : (1u << j);
-                    }
-                    cand &= alive;
-                    if (!__any_sync(0xffffffffu, cand))
-                        continue;
-                    found |= 1u << bit;
-
-                    for (int vi = 0; vi < grp.n_views; vi++) {
-                        const int view = grp.first_view + vi;
-                        if (WRITE && !((counters[view] >> (16 + sub)) & 1u))              // pass A found nobody here
-                            continue;
-                        uint32_t keep = a.view_require[view] ? (cand & caster) : cand;
-                        const float4 *pl = a.planes + 6 * view;
-                        const uint32_t codes = __ldg(a.view_codes + view);
-                        // Two planes at a time: the P-vertex corner is picked by a warp-uniform switch on the plane's sign
-                        // bits (no select per entity), products are packed FMUL2, and "either distance < 0" is one compare
-                        // of the smaller distance (fminf ignores a NaN operand, as a NaN distance rejects nothing). The
-                        // warp-uniform early-outs sit where they were: after the side planes and after top / bottom.
-#pragma unroll
-                        for (int pp = 0; pp < 3; pp++) {
-                            if (pp > 0 && !__any_sync(0xffffffffu, keep))
-                                break;
-                            const float4 d0 = plane_dist4_coded(codes >> (6 * pp), __ldg(pl + 2 * pp), ax, ay, az, bx, by, bz);
-                            const float4 d1 = plane_dist4_coded(codes >> (6 * pp + 3), __ldg(pl + 2 * pp + 1), ax, ay, az, bx, by, bz);
-                            if (fminf(d0.x, d1.x) < 0.0f) keep &= ~1u;
-                            if (fminf(d0.y, d1.y) < 0.0f) keep &= ~2u;
-                            if (fminf(d0.z, d1.z) < 0.0f) keep &= ~4u;
-                            if (fminf(d0.w, d1.w) < 0.0f) keep &= ~8u;
-                        }
-                        if (!__any_sync(0xffffffffu, keep))
-                            continue;
-                        // ---- rank in slot order inside the sub-tile
-                        const uint32_t c = __popc(keep);
-                        uint32_t incl = c;
-#pragma unroll
-                        for (int o = 1; o < 32; o <<= 1) {
-                            uint32_t up = __shfl_up_sync(0xffffffffu, incl, o);
-                            if (lane >= o)
-                                incl += up;
-                        }
-                        const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
-                        if (WRITE) {
-                            long long pos = a.csr_offsets[view] + (long long)row[view] + (counters[view] & 0xffffu) + (incl - c);
-#pragma unroll
-                            for (int j = 0; j < 4; j++)
-                                if (keep & (1u << j)) {
-                                    if (pos < a.capacity) a.out[pos] = (uint32_t)e0 + j + a.id_base;
-                                    pos++;
-                                }
-                        }
-                        __syncwarp();
-                        if (lane == 0)
-                            counters[view] += WRITE ? total : (total | (0x10000u << sub));    // each (sub, view) comes by once
-                        __syncwarp();
-                    }
-                }
-                if (!WRITE && found) {
-                    if (lane == 0)
-                        hits[gw] |= found;
-                    __syncwarp();
-                }
-            }
+    for (int p = 0; p < 6; p++) {
+        if (!alive_somewhere)
+            break;
+#define OVIS_MV_CASE(C, SX, SY, SZ)                                                                                     \
+    case C:                                                                                                             \
+_Pragma("unroll") for (int r = 0; r < R; r++) {                                                                 \
+    const float4 q = __ldg(pl[r] + p);                                                                              \
+    const float4 dd = plane_dist4_signed<SX, SY, SZ>(q.x, q.y, q.z, q.w, ax, ay, az, bx, by, bz);                   \
+    if (p & 1)                                                                                                      \
+        lowest[r] = min3_4(lowest[r], held[r], dd);                                                                 \
+    else                                                                                                            \
+        held[r] = dd;                                                                                               \
+}                                                                                                               \
+break;
+        switch ((codes >> (3 * p)) & 7u) {
+            OVIS_MV_CASE(0, false, false, false)
+            OVIS_MV_CASE(1, true, false, false)
+            OVIS_MV_CASE(2, false, true, false)
+            OVIS_MV_CASE(3, true, true, false)
+            OVIS_MV_CASE(4, false, false, true)
+            OVIS_MV_CASE(5, true, false, true)
+            OVIS_MV_CASE(6, false, true, true)
+            OVIS_MV_CASE(7, true, true, true)
         }
-
-        if (!WRITE) {
-            // one coalesced row of counts per supertile, sparse adds into the block totals, and the group hits
-            uint32_t *out_row = a.counts + (int64_t)tile * a.n_views;
-            uint32_t *totals = a.block_totals + (int64_t)(tile / kGatherTiles) * a.n_views;
-            __syncwarp();
-            for (int v = lane; v < a.n_views; v += 32) {
-                const uint32_t c = counters[v] & 0xffffu;
-                out_row[v] = c;
-                a.sub_masks[(int64_t)tile * a.n_views + v] = (uint8_t)(counters[v] >> 16);
-                if (c)
-                    atomicAdd(totals + v, c);
-            }
-            for (int k = lane; k < hit_words; k += 32)
-                a.group_hits[(int64_t)tile * hit_words + k] = hits[k];
+#undef OVIS_MV_CASE
+        if (p == 1) {                                                  // the side planes reject most tiles of a coherent scene
+            uint32_t left = 0;
+#pragma unroll
+            for (int r = 0; r < R; r++)
+                left |= keep[r] & ~negative_bits(lowest[r]);
+            alive_somewhere = __any_sync(0xffffffffu, left != 0u);
         }
-        __syncwarp();
+    }
+#pragma unroll
+    for (int r = 0; r < R; r++) {
+        const uint32_t k = alive_somewhere ? (keep[r] & ~negative_bits(lowest[r])) : 0u;
+        store_group_bits(a.masks + (int64_t)(pv + r) * num_words, group, k, lane);
+        const uint32_t total = __reduce_add_sync(0xffffffffu, __popc(k));
+        if (lane == 0 && total)
+            atomicAdd(a.totals + (int64_t)view[r] * row + group / kMaskBlockGroups, total);
     }
 }
 
-// B1: one CTA, thread per view. block_totals[b][v] becomes the number of survivors of view v in blocks < b;
-// csr_offsets[first_view + v + 1] receives the end of view v's list (csr_offsets[first_view] is the start of the pass).
-__global__ void __launch_bounds__(1024)
-multi_scan_blocks_kernel(uint32_t *block_totals, int num_blocks, int n_views, long long *csr_offsets) {
-    __shared__ long long s_warp[32];
-    const int v = threadIdx.x, lane = v & 31, warp = v >> 5;
-    uint32_t running = 0;
-    if (v < n_views) {
-        for (int b0 = 0; b0 < num_blocks; b0 += 8) {            // 8 independent loads in flight, then the prefix
-            uint32_t c[8];
-#pragma unroll
-            for (int k = 0; k < 8; k++)
-                c[k] = (b0 + k < num_blocks) ? block_totals[(int64_t)(b0 + k) * n_views + v] : 0u;
-#pragma unroll
-            for (int k = 0; k < 8; k++) {
-                if (b0 + k < num_blocks)
-                    block_totals[(int64_t)(b0 + k) * n_views + v] = running;
-                running += c[k];
+__global__ void __launch_bounds__(kMvThreads, 2)
+mv_plain_test_kernel(const __grid_constant__ MvArgs a) {
+    const int lane = threadIdx.x & 31;
+    const long long warps_total = (long long)gridDim.x * (kMvThreads / 32);
+    const long long gwarp = (long long)blockIdx.x * (kMvThreads / 32) + (threadIdx.x >> 5);
+    const float4 *__restrict__ bounds = reinterpret_cast<const float4 *>(a.bounds);
+    const int64_t vstride = a.stride >> 2;
+    const int n_chunks = (a.n_plain + a.views_per_warp - 1) / a.views_per_warp;
+    const long long items = (long long)a.num_groups128 * n_chunks;
+
+    float4 ax, ay, az, bx, by, bz;
+    auto issue_loads = [&](long long item) {
+        if (item >= items)
+            return;
+        const int64_t v = (n_chunks == 1 ? item : item % a.num_groups128) * 32 + lane;   // float4 index: entities 4v .. 4v+3
+        ax = __ldg(bounds + 0 * vstride + v); ay = __ldg(bounds + 1 * vstride + v); az = __ldg(bounds + 2 * vstride + v);
+        bx = __ldg(bounds + 3 * vstride + v); by = __ldg(bounds + 4 * vstride + v); bz = __ldg(bounds + 5 * vstride + v);
+    };
+    long long item = gwarp;
+    issue_loads(item);
+    for (; item < items; item += warps_total) {
+        const int chunk = n_chunks == 1 ? 0 : (int)(item / a.num_groups128);
+        const int64_t group = n_chunks == 1 ? item : item % a.num_groups128;
+        const int64_t e0 = (group * 32 + lane) << 2;
+        uint32_t alive = candidate_bits<false>(e0, a.n, 0u);
+        if (a.alive_mask)
+            alive &= (__ldg(a.alive_mask + (e0 >> 5)) >> (e0 & 31)) & 0xfu;
+        uint32_t caster = alive;
+        if (a.caster_mask)
+            caster &= (__ldg(a.caster_mask + (e0 >> 5)) >> (e0 & 31)) & 0xfu;
+        const int pv1 = min(a.n_plain, (chunk + 1) * a.views_per_warp);
+        // the host lists the plain views sorted by sign code: take them in runs of up to 4 equal codes
+        for (int pv = chunk * a.views_per_warp; pv < pv1;) {
+            const uint32_t codes = __ldg(a.view_meta + __ldg(a.plain_views + pv)) & 0x3ffffu;
+            int run = 1;
+            while (run < 4 && pv + run < pv1 && (__ldg(a.view_meta + __ldg(a.plain_views + pv + run)) & 0x3ffffu) == codes)
+                run++;
+            if (run == 4) {
+                test_view_run<4>(a, pv, codes, ax, ay, az, bx, by, bz, alive, caster, group, lane);
+            } else if (run >= 2) {
+                run = 2;
+                test_view_run<2>(a, pv, codes, ax, ay, az, bx, by, bz, alive, caster, group, lane);
+            } else {
+                test_view_run<1>(a, pv, codes, ax, ay, az, bx, by, bz, alive, caster, group, lane);
             }
+            pv += run;
         }
+        issue_loads(item + warps_total);
     }
-    // inclusive scan of the view totals across the CTA
-    long long incl = running;
+}
+
+// block-wide exclusive scan of one value per thread (256 threads); returns the rank, *total = the block sum
+__device__ __forceinline__ uint32_t block_exclusive_scan(uint32_t c, uint32_t *s_warp, uint32_t *total) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint32_t incl = c;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
-        long long up = __shfl_up_sync(0xffffffffu, incl, o);
+        uint32_t up = __shfl_up_sync(0xffffffffu, incl, o);
         if (lane >= o)
             incl += up;
     }
+    __syncthreads();                                       // s_warp may still be read from the previous use
     if (lane == 31)
         s_warp[warp] = incl;
     __syncthreads();
-    long long before = 0;
-    for (int w = 0; w < warp; w++)
-        before += s_warp[w];
-    const long long start = csr_offsets[0];
-    __syncthreads();
-    if (v < n_views)
-        csr_offsets[v + 1] = start + before + incl;
+    uint32_t before = 0, sum = 0;
+#pragma unroll
+    for (int k = 0; k < kMvThreads / 32; k++) {
+        if (k < warp)
+            before += s_warp[k];
+        sum += s_warp[k];
+    }
+    *total = sum;
+    return before + incl - c;
 }
 
-// B2: one CTA per block of kGatherTiles supertiles, thread per view: counts[tile][v] becomes the number of survivors
-// of view v in all earlier supertiles.
-__global__ void __launch_bounds__(1024)
-multi_scan_tiles_kernel(uint32_t *counts, const uint32_t *block_totals, int num_tiles, int n_views) {
-    const int v = threadIdx.x;
-    if (v >= n_views)
+__global__ void __launch_bounds__(kMvThreads)
+mv_expand_masks_kernel(const __grid_constant__ MvArgs a) {
+    __shared__ uint32_t s_ids[kMaskBlockEntities];
+    __shared__ uint32_t s_warp[kMvThreads / 32];
+    const int b = blockIdx.x, pv = blockIdx.y, tid = threadIdx.x;
+    const int view = (int)a.plain_views[pv];
+    const uint32_t *row = a.totals + (int64_t)view * (a.num_blocks + 1);
+    const uint32_t before = row[b], count = row[b + 1] - before;
+    if (count == 0)
         return;
+    const int64_t num_words = (int64_t)a.num_groups128 * 4;
+    const int64_t w = (int64_t)b * kMaskBlockWords + tid;
+    uint32_t word = w < num_words ? a.masks[(int64_t)pv * num_words + w] : 0u;
+    uint32_t total;
+    uint32_t rank = block_exclusive_scan(__popc(word), s_warp, &total);
+    const uint32_t id0 = (uint32_t)(w << 5) + a.id_base;
+    while (word) {
+        const int bit = __ffs(word) - 1;
+        word &= word - 1;
+        s_ids[rank++] = id0 + bit;
+    }
+    __syncthreads();
+    const long long dst0 = a.csr_offsets[view] + (long long)before;
+    for (uint32_t k = tid; k < total; k += kMvThreads)
+        if (dst0 + k < a.capacity)
+            a.out[dst0 + k] = s_ids[k];
+}
+
+// ------------------------------------------------------------------------------------------------
+// scan: totals[view][block] -> exclusive prefixes (+ the view total in the extra column), then CSR offsets
+// ------------------------------------------------------------------------------------------------
+
+__global__ void __launch_bounds__(kMvThreads)
+mv_scan_kernel(const __grid_constant__ MvArgs a) {
+    __shared__ uint32_t s_warp[kMvThreads / 32];
+    __shared__ long long s_warp64[kMvThreads / 32];
+    __shared__ bool s_last;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int nb = a.num_blocks;
+    uint32_t *row = a.totals + (int64_t)blockIdx.x * (nb + 1);
+    uint32_t carry = 0;
+    for (int b0 = 0; b0 < nb; b0 += kMvThreads) {
+        const int i = b0 + tid;
+        const uint32_t c = i < nb ? row[i] : 0u;
+        uint32_t total;
+        const uint32_t rank = block_exclusive_scan(c, s_warp, &total);
+        if (i < nb)
+            row[i] = carry + rank;
+        carry += total;
+    }
+    if (tid == 0) {
+        row[nb] = carry;
+        __threadfence();
+        s_last = atomicAdd(a.state + 1, 1u) == gridDim.x - 1;
+    }
+    __syncthreads();
+    if (!s_last)
+        return;
+    // the last CTA to finish: view totals -> CSR offsets (the pass starts where csr_offsets[0] says)
+    __threadfence();
+    long long running = a.csr_offsets[0];
+    for (int v0 = 0; v0 < a.n_views; v0 += kMvThreads) {
+        const int v = v0 + tid;
+        const long long c = v < a.n_views ? (long long)__ldcg(a.totals + (int64_t)v * (nb + 1) + nb) : 0ll;
+        long long incl = c;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            long long up = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o)
+                incl += up;
+        }
+        __syncthreads();
+        if (lane == 31)
+            s_warp64[warp] = incl;
+        __syncthreads();
+        long long before = 0, sum = 0;
+        for (int k = 0; k < kMvThreads / 32; k++) {
+            if (k < warp)
+                before += s_warp64[k];
+            sum += s_warp64[k];
+        }
+        if (v < a.n_views)
+            a.csr_offsets[v + 1] = running + before + incl;
+        running += sum;
+    }
+    if (tid == 0)
+        a.state[1] = 0u;
+}
+
+// ------------------------------------------------------------------------------------------------
+// sparse pass
+// ------------------------------------------------------------------------------------------------
+
+__global__ void __launch_bounds__(kMvThreads)
+mv_bin_lights_kernel(const __grid_constant__ MvArgs a) {
+    const int g = blockIdx.x;                                  // one CTA per group: a large light covers hundreds of cells
+    const MvGroup grp = a.groups[g];
+    const int x0 = grp.cell_lo & 255, y0 = (grp.cell_lo >> 8) & 255, z0 = (grp.cell_lo >> 16) & 255;
+    const int dx = (int)(grp.cell_hi & 255) - x0 + 1, dy = (int)((grp.cell_hi >> 8) & 255) - y0 + 1,
+              dz = (int)((grp.cell_hi >> 16) & 255) - z0 + 1;
+    const int cells = dx * dy * dz;
+    for (int i = threadIdx.x; i < cells; i += kMvThreads) {
+        const int x = x0 + i % dx, y = y0 + (i / dx) % dy, z = z0 + i / (dx * dy);
+        const uint32_t node = atomicAdd(a.state + 2, 1u);
+        if (node >= a.node_capacity) {
+            atomicOr(a.state, kMvOverflowNodes);
+            continue;
+        }
+        a.node_group[node] = (uint32_t)g;
+        a.node_next[node] = atomicExch(a.heads + ((int64_t)z * a.grid.dim[1] + y) * a.grid.dim[0] + x, (int32_t)node);
+        atomicOr(a.bitmap + z * a.grid.dim[1] + y, 1ull << x);
+    }
+}
+
+struct CellRange {
+    int x0, x1, y0, y1, z0, z1;
+};
+
+// cell index of a coordinate: the same monotone function on the host (for the groups: floor, clamp in float, convert)
+// and here (for the entities: convert with round-down and saturation, clamp as integers - the same value for every input,
+// NaN included), so two intervals that overlap in space always share a cell
+__device__ __forceinline__ int cell_of(float v, float lo, float inv, int dim) {
+    return min(max(__float2int_rd(__fmul_rn(__fsub_rn(v, lo), inv)), 0), dim - 1);
+}
+
+// K6 pre-filter, entity side: the box inflated by Re = 1.001 * largest extent + 1e-3 * largest |coordinate|.
+// Returns 0: no cube can reach it; 1: candidates are in the cells of `r`, at most 2 x 2 rows of the bitmap; 2: test every
+// group (a box with a NaN or non-finite side can never be rejected - *odd; a box that spans more rows is cheaper to test
+// against every cube). Branch-free on purpose: it runs for every entity of the world.
+__device__ __forceinline__ int entity_cells(const MvGrid &g, const float mn[3], const float mx[3], float lo[3], float hi[3],
+                                            CellRange &r, bool *odd) {
+    const float sx = mx[0] - mn[0], sy = mx[1] - mn[1], sz = mx[2] - mn[2];
+    const float ext = fmaxf(fmaxf(fmaxf(sx, sy), sz), 0.0f);
+    const float mag = fmaxf(fmaxf(fmaxf(fabsf(mn[0]), fabsf(mx[0])), fmaxf(fabsf(mn[1]), fabsf(mx[1]))),
+                            fmaxf(fabsf(mn[2]), fabsf(mx[2])));
+    *odd = !((sx == sx) & (sy == sy) & (sz == sz) & (ext <= 3.0e38f) & (mag <= 3.0e38f));     // fmaxf drops NaNs
+    const float re = ext * 1.001f + mag * 1.0e-3f;
+#pragma unroll
+    for (int c = 0; c < 3; c++) {
+        lo[c] = mn[c] - re;
+        hi[c] = mx[c] + re;
+    }
+    const bool outside = (hi[0] < g.lo[0]) | (lo[0] > g.hi[0]) | (hi[1] < g.lo[1]) | (lo[1] > g.hi[1]) | (hi[2] < g.lo[2]) | (lo[2] > g.hi[2]);
+    r.x0 = cell_of(lo[0], g.lo[0], g.inv_cell[0], g.dim[0]); r.x1 = cell_of(hi[0], g.lo[0], g.inv_cell[0], g.dim[0]);
+    r.y0 = cell_of(lo[1], g.lo[1], g.inv_cell[1], g.dim[1]); r.y1 = cell_of(hi[1], g.lo[1], g.inv_cell[1], g.dim[1]);
+    r.z0 = cell_of(lo[2], g.lo[2], g.inv_cell[2], g.dim[2]); r.z1 = cell_of(hi[2], g.lo[2], g.inv_cell[2], g.dim[2]);
+    const bool big = (r.y1 - r.y0 > 1) | (r.z1 - r.z0 > 1);
+    return *odd ? 2 : (outside ? 0 : (big ? 2 : 1));
+}
+
+__device__ __forceinline__ unsigned long long x_range_bits(int x0, int x1) {
+    return ((2ull << (x1 - x0)) - 1ull) << x0;              // x1 - x0 = 63: the shift wraps to 0 and 0 - 1 is all ones
+}
+
+// candidate iff the inflated box overlaps the group's (inflated) cube: separated along some axis <=> the largest of the
+// six gaps is > 0 (a NaN gap is ignored by fmaxf, an all-NaN set compares false: such boxes stay candidates)
+__device__ __forceinline__ bool overlaps_cube(const MvGroup &grp, const float lo[3], const float hi[3]) {
+    const float gap = fmaxf(fmaxf(fmaxf(grp.lo[0] - hi[0], lo[0] - grp.hi[0]), fmaxf(grp.lo[1] - hi[1], lo[1] - grp.hi[1])),
+                            fmaxf(grp.lo[2] - hi[2], lo[2] - grp.hi[2]));
+    return !(gap > 0.0f);
+}
+
+__device__ __forceinline__ void load_box(const MvArgs &a, int64_t e, float mn[3], float mx[3]) {
+#pragma unroll
+    for (int c = 0; c < 3; c++) {
+        mn[c] = __ldg(a.bounds + c * a.stride + e);
+        mx[c] = __ldg(a.bounds + (c + 3) * a.stride + e);
+    }
+}
+
+// record key: group (12 bits) | entity inside the block (13 bits) | face mask (6 bits); 0xffffffff = no record
+__device__ __forceinline__ void append_pair(uint32_t *s_pairs, uint32_t *s_npairs, uint32_t g, uint32_t el) {
+    const uint32_t i = atomicAdd(s_npairs, 1u);
+    if (i < (uint32_t)kMvPairCapacity)
+        s_pairs[i] = (g << 13) | el;
+}
+
+struct SegCount {                 // per-face survivor counts of a (group, block) run, 16 bits each, and the segment flag
+    uint32_t p0, p1, p2;
+    bool cut;
+};
+__device__ __forceinline__ void seg_add(SegCount &s, uint32_t fm) {
+    s.p0 += (fm & 1u) | (((fm >> 1) & 1u) << 16);
+    s.p1 += ((fm >> 2) & 1u) | (((fm >> 3) & 1u) << 16);
+    s.p2 += ((fm >> 4) & 1u) | (((fm >> 5) & 1u) << 16);
+}
+__device__ __forceinline__ uint32_t seg_get(const SegCount &s, int f) {
+    const uint32_t p = f < 2 ? s.p0 : (f < 4 ? s.p1 : s.p2);
+    return (p >> (16 * (f & 1))) & 0xffffu;
+}
+// `later` follows `earlier`: a cut in `later` discards what came before it
+__device__ __forceinline__ SegCount seg_join(const SegCount &earlier, const SegCount &later) {
+    SegCount r = later;
+    if (!later.cut) {
+        r.p0 += earlier.p0;
+        r.p1 += earlier.p1;
+        r.p2 += earlier.p2;
+    }
+    r.cut = earlier.cut || later.cut;
+    return r;
+}
+
+__global__ void __launch_bounds__(kMvThreads, 2)
+mv_sparse_kernel(const __grid_constant__ MvArgs a) {
+    extern __shared__ __align__(16) unsigned char s_mv[];
+    const int rows = a.grid.dim[1] * a.grid.dim[2];
+    unsigned long long *s_bitmap = reinterpret_cast<unsigned long long *>(s_mv);
+    uint32_t *s_pairs = reinterpret_cast<uint32_t *>(s_bitmap + rows);
+    uint32_t *s_hit = s_pairs + kMvPairCapacity;               // 256 words: bit = entity has an occupied cell
+    uint32_t *s_big = s_hit + kMaskBlockWords;                 // 256 words: bit = entity is tested against every group
+    __shared__ uint32_t s_npairs, s_nrec, s_item_base;
+    __shared__ uint32_t s_warp[kMvThreads / 32];
+    __shared__ SegCount s_seg[kMvThreads / 32];
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int b = blockIdx.x;
-    uint32_t running = block_totals[(int64_t)b * n_views + v];
-    const int t1 = min(num_tiles, (b + 1) * kGatherTiles);
-    for (int t0 = b * kGatherTiles; t0 < t1; t0 += 8) {
-        uint32_t c[8];
+    const float4 *__restrict__ bounds = reinterpret_cast<const float4 *>(a.bounds);
+    const int64_t vstride = a.stride >> 2;
+    const int64_t block_e0 = (int64_t)b * kMaskBlockEntities;
+
+    for (int i = tid; i < rows; i += kMvThreads)
+        s_bitmap[i] = a.bitmap[i];
+    if (tid == 0) {
+        s_npairs = 0;
+        s_nrec = 0;
+    }
+    __syncthreads();
+
+    // ---- (1) which entities have an occupied cell? 8 groups of 128 entities per warp
+    for (int k = 0; k < kMaskBlockGroups / (kMvThreads / 32); k++) {
+        const int gl = warp * (kMaskBlockGroups / (kMvThreads / 32)) + k;       // group inside the block
+        const int64_t group = (int64_t)b * kMaskBlockGroups + gl;
+        uint32_t hit = 0, big = 0, alive_bits = 0;
+        if (group < a.num_groups128) {
+            const int64_t v = group * 32 + lane;
+            const int64_t e0 = v << 2;
+            const float4 ax = __ldg(bounds + 0 * vstride + v), ay = __ldg(bounds + 1 * vstride + v), az = __ldg(bounds + 2 * vstride + v);
+            const float4 bx = __ldg(bounds + 3 * vstride + v), by = __ldg(bounds + 4 * vstride + v), bz = __ldg(bounds + 5 * vstride + v);
+            uint32_t alive = candidate_bits<false>(e0, a.n, 0u);
+            if (a.alive_mask)
+                alive &= (__ldg(a.alive_mask + (e0 >> 5)) >> (e0 & 31)) & 0xfu;
+            alive_bits = alive;
+            const float mnv[4][3] = { { ax.x, ay.x, az.x }, { ax.y, ay.y, az.y }, { ax.z, ay.z, az.z }, { ax.w, ay.w, az.w } };
+            const float mxv[4][3] = { { bx.x, by.x, bz.x }, { bx.y, by.y, bz.y }, { bx.z, by.z, bz.z }, { bx.w, by.w, bz.w } };
 #pragma unroll
-        for (int k = 0; k < 8; k++)
-            c[k] = (t0 + k < t1) ? counts[(int64_t)(t0 + k) * n_views + v] : 0u;
+            for (int j = 0; j < 4; j++) {
+                float lo[3], hi[3];
+                CellRange r;
+                bool odd;
+                const int kind = entity_cells(a.grid, mnv[j], mxv[j], lo, hi, r, &odd);
+                // kind 1 spans at most 2 x 2 rows: look at the four corner rows (duplicates when it spans fewer)
+                const unsigned long long rows = (s_bitmap[r.z0 * a.grid.dim[1] + r.y0] | s_bitmap[r.z0 * a.grid.dim[1] + r.y1]) |
+                                                (s_bitmap[r.z1 * a.grid.dim[1] + r.y0] | s_bitmap[r.z1 * a.grid.dim[1] + r.y1]);
+                const bool occupied = (rows & x_range_bits(r.x0, r.x1)) != 0ull;
+                big |= (kind == 2 ? 1u : 0u) << j;
+                hit |= ((kind == 1) & occupied ? 1u : 0u) << j;
+            }
+        }
+        store_group_bits(s_hit, gl, hit & alive_bits, lane);
+        store_group_bits(s_big, gl, big & alive_bits, lane);
+    }
+    __syncthreads();
+
+    // ---- (2) candidate pairs: thread t owns the 32 entities of word t
+    {
+        uint32_t word = s_hit[tid];
+        while (word) {
+            const int bit = __ffs(word) - 1;
+            word &= word - 1;
+            const uint32_t el = (uint32_t)tid * 32 + bit;
+            float mn[3], mx[3], lo[3], hi[3];
+            CellRange r;
+            bool odd;
+            load_box(a, block_e0 + el, mn, mx);
+            entity_cells(a.grid, mn, mx, lo, hi, r, &odd);
+            const unsigned long long xm = x_range_bits(r.x0, r.x1);
+            for (int z = r.z0; z <= r.z1; z++)
+                for (int y = r.y0; y <= r.y1; y++) {
+                    unsigned long long occupied = s_bitmap[z * a.grid.dim[1] + y] & xm;
+                    while (occupied) {
+                        const int x = __ffsll((long long)occupied) - 1;
+                        occupied &= occupied - 1;
+                        for (int32_t node = a.heads[((int64_t)z * a.grid.dim[1] + y) * a.grid.dim[0] + x]; node >= 0; node = a.node_next[node]) {
+                            const uint32_t g = a.node_group[node];
+                            const MvGroup grp = a.groups[g];
+                            // a group shared by several of the entity's cells is taken in the first of them only
+                            const int gx = max(r.x0, (int)(grp.cell_lo & 255)), gy = max(r.y0, (int)((grp.cell_lo >> 8) & 255)),
+                                      gz = max(r.z0, (int)((grp.cell_lo >> 16) & 255));
+                            if (x != gx || y != gy || z != gz)
+                                continue;
+                            if (overlaps_cube(grp, lo, hi))
+                                append_pair(s_pairs, &s_npairs, g, el);
+                        }
+                    }
+                }
+        }
+    }
+    // entities tested against every group: the whole CTA shares each one, a thread takes every 256th group
+    for (int w = 0; w < kMaskBlockWords; w++) {
+        uint32_t word = s_big[w];
+        while (word) {
+            const int bit = __ffs(word) - 1;
+            word &= word - 1;
+            const uint32_t el = (uint32_t)w * 32 + bit;
+            float mn[3], mx[3], lo[3], hi[3];
+            CellRange r;
+            bool odd;
+            load_box(a, block_e0 + el, mn, mx);
+            entity_cells(a.grid, mn, mx, lo, hi, r, &odd);
+            for (int g = tid; g < a.n_groups; g += kMvThreads)
+                if (odd || overlaps_cube(a.groups[g], lo, hi))
+                    append_pair(s_pairs, &s_npairs, (uint32_t)g, el);
+        }
+    }
+    __syncthreads();
+    const uint32_t npairs = s_npairs;
+    if (npairs > (uint32_t)kMvPairCapacity) {                   // too dense for this pass: the host reruns these views densely
+        if (tid == 0) {
+            atomicOr(a.state, kMvOverflowPairs);
+            a.segments[b] = make_uint2(0u, 0u);
+        }
+        return;
+    }
+    if (npairs == 0) {
+        if (tid == 0)
+            a.segments[b] = make_uint2(0u, 0u);
+        return;
+    }
+
+    // ---- (3) exact tests: one thread per pair, every face of the light (Math::intersect, intersection.cc:42-57)
+    uint32_t n_valid = 0;
+    for (uint32_t i = tid; i < npairs; i += kMvThreads) {
+        const uint32_t pair = s_pairs[i];
+        const uint32_t g = pair >> 13, el = pair & 8191u;
+        const int64_t e = block_e0 + el;
+        float mn[3], mx[3];
+        load_box(a, e, mn, mx);
+        const bool caster = a.caster_mask ? ((__ldg(a.caster_mask + (e >> 5)) >> (e & 31)) & 1u) != 0 : true;
+        const MvGroup grp = a.groups[g];
+        uint32_t fm = 0;
+        for (int f = 0; f < grp.n_views; f++) {
+            const int view = grp.first_view + f;
+            if ((__ldg(a.view_meta + view) >> 31) && !caster)
+                continue;
+            const float4 *pl = a.planes + 6 * view;
+            bool inside = true;
 #pragma unroll
-        for (int k = 0; k < 8; k++) {
-            if (t0 + k < t1)
-                counts[(int64_t)(t0 + k) * n_views + v] = running;
-            running += c[k];
+            for (int p = 0; p < 6 && inside; p++) {
+                const float4 q = __ldg(pl + p);
+                inside = !outside_plane(q.x, q.y, q.z, q.w, mn[0], mn[1], mn[2], mx[0], mx[1], mx[2]);
+            }
+            if (inside)
+                fm |= 1u << f;
+        }
+        s_pairs[i] = fm ? ((pair << 6) | fm) : 0xffffffffu;
+        n_valid += fm ? 1u : 0u;
+    }
+    n_valid = __reduce_add_sync(0xffffffffu, n_valid);
+    if (lane == 0 && n_valid)
+        atomicAdd(&s_nrec, n_valid);
+
+    // ---- (4) sort the records by (group, entity): bitonic, in shared memory
+    uint32_t n_sort = 32;
+    while (n_sort < npairs)
+        n_sort <<= 1;
+    for (uint32_t i = npairs + tid; i < n_sort; i += kMvThreads)
+        s_pairs[i] = 0xffffffffu;
+    __syncthreads();
+    const uint32_t nrec = s_nrec;
+    if (nrec == 0) {
+        if (tid == 0)
+            a.segments[b] = make_uint2(0u, 0u);
+        return;
+    }
+    for (uint32_t k = 2; k <= n_sort; k <<= 1)
+        for (uint32_t j = k >> 1; j > 0; j >>= 1) {
+            for (uint32_t i = tid; i < n_sort; i += kMvThreads) {
+                const uint32_t partner = i ^ j;
+                if (partner > i) {
+                    const uint32_t x = s_pairs[i], y = s_pairs[partner];
+                    const bool ascending = (i & k) == 0;
+                    if ((x > y) == ascending) {
+                        s_pairs[i] = y;
+                        s_pairs[partner] = x;
+                    }
+                }
+            }
+            __syncthreads();
+        }
+
+    // ---- (5) rank inside (view, block), totals, items. Thread t owns records [t * per, (t + 1) * per).
+    const uint32_t per = (nrec + kMvThreads - 1) / kMvThreads;
+    const uint32_t i0 = min(nrec, (uint32_t)tid * per), i1 = min(nrec, i0 + per);
+    SegCount mine = { 0u, 0u, 0u, false };
+    uint32_t my_items = 0;
+    {
+        uint32_t prev_g = i0 > 0 ? s_pairs[i0 - 1] >> 19 : 0xffffffffu;
+        for (uint32_t i = i0; i < i1; i++) {
+            const uint32_t key = s_pairs[i], g = key >> 19, fm = key & 63u;
+            if (g != prev_g) {
+                mine = { 0u, 0u, 0u, true };
+                prev_g = g;
+            }
+            seg_add(mine, fm);
+            my_items += __popc(fm);
+        }
+    }
+    // segmented exclusive scan of `mine` over the threads (a cut = a new group starts inside the thread's records)
+    SegCount incl = mine;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        SegCount up;
+        up.p0 = __shfl_up_sync(0xffffffffu, incl.p0, o);
+        up.p1 = __shfl_up_sync(0xffffffffu, incl.p1, o);
+        up.p2 = __shfl_up_sync(0xffffffffu, incl.p2, o);
+        up.cut = __shfl_up_sync(0xffffffffu, (int)incl.cut, o) != 0;
+        if (lane >= o)
+            incl = seg_join(up, incl);
+    }
+    SegCount carry;                                          // what precedes this thread inside its warp
+    carry.p0 = __shfl_up_sync(0xffffffffu, incl.p0, 1);
+    carry.p1 = __shfl_up_sync(0xffffffffu, incl.p1, 1);
+    carry.p2 = __shfl_up_sync(0xffffffffu, incl.p2, 1);
+    carry.cut = __shfl_up_sync(0xffffffffu, (int)incl.cut, 1) != 0;
+    if (lane == 0)
+        carry = { 0u, 0u, 0u, false };
+    if (lane == 31)
+        s_seg[warp] = incl;
+    uint32_t items_total;
+    const uint32_t item_rank = block_exclusive_scan(my_items, s_warp, &items_total);   // (contains the barriers s_seg needs)
+    {
+        SegCount before = { 0u, 0u, 0u, false };
+        for (int k = 0; k < warp; k++)
+            before = seg_join(before, s_seg[k]);
+        carry = seg_join(before, carry);
+    }
+    if (tid == 0) {
+        s_item_base = atomicAdd(a.state + 3, items_total);
+        a.segments[b] = make_uint2(s_item_base, items_total);
+    }
+    __syncthreads();
+    const uint32_t item_base = s_item_base;
+    const bool fits = (unsigned long long)item_base + items_total <= (unsigned long long)a.item_capacity;
+    if (!fits && tid == 0) {
+        atomicOr(a.state, kMvOverflowItems);
+        a.segments[b] = make_uint2(0u, 0u);
+    }
+    {
+        SegCount run = carry;
+        uint32_t prev_g = i0 > 0 ? s_pairs[i0 - 1] >> 19 : 0xffffffffu;
+        uint32_t slot = item_base + item_rank;
+        int first_view = 0;
+        const int row = a.num_blocks + 1;
+        for (uint32_t i = i0; i < i1; i++) {
+            const uint32_t key = s_pairs[i], g = key >> 19, el = (key >> 6) & 8191u;
+            uint32_t fm = key & 63u;
+            if (g != prev_g || i == i0) {
+                if (g != prev_g)
+                    run = { 0u, 0u, 0u, false };
+                prev_g = g;
+                first_view = a.groups[g].first_view;
+            }
+            const uint32_t id = (uint32_t)(block_e0 + el) + a.id_base;
+            for (uint32_t bits = fm; bits; bits &= bits - 1) {
+                const int f = __ffs(bits) - 1;
+                if (fits)
+                    a.items[slot] = { (uint32_t)(first_view + f), seg_get(run, f), id };
+                slot++;
+            }
+            seg_add(run, fm);
+            const uint32_t next_g = i + 1 < nrec ? s_pairs[i + 1] >> 19 : 0xffffffffu;
+            if (next_g != g) {                                  // the group's run ends here: its totals for this block
+#pragma unroll
+                for (int f = 0; f < kMvMaxGroupViews; f++) {
+                    const uint32_t c = seg_get(run, f);
+                    if (c)
+                        a.totals[(int64_t)(first_view + f) * row + b] = c;
+                }
+            }
         }
     }
 }
 
-int multi_max_blocks_per_sm(int n_views, int n_groups) {
-    int blocks = 0;
-    size_t smem = sizeof(uint32_t) * kMultiWarps * (size_t)multi_words_per_warp(n_views, n_groups);
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks, multi_pass_kernel<false, true>, kMultiWarps * 32, smem);
-    return blocks;
-}
-
-void launch_multi_pass(const MultiArgs &a, bool write, int grid, cudaStream_t s) {
-    size_t smem = sizeof(uint32_t) * kMultiWarps * (size_t)multi_words_per_warp(a.n_views, a.n_groups);
-    if (a.any_cube) {
-        if (write)
-            multi_pass_kernel<true, true><<<grid, kMultiWarps * 32, smem, s>>>(a);
-        else
-            multi_pass_kernel<false, true><<<grid, kMultiWarps * 32, smem, s>>>(a);
-    } else {
-        if (write)
-            multi_pass_kernel<true, false><<<grid, kMultiWarps * 32, smem, s>>>(a);
-        else
-            multi_pass_kernel<false, false><<<grid, kMultiWarps * 32, smem, s>>>(a);
+__global__ void __launch_bounds__(kMvThreads)
+mv_expand_items_kernel(const __grid_constant__ MvArgs a) {
+    const int row = a.num_blocks + 1;
+    for (int b = blockIdx.x; b < a.num_blocks; b += gridDim.x) {
+        const uint2 seg = a.segments[b];
+        for (uint32_t i = threadIdx.x; i < seg.y; i += kMvThreads) {
+            const MvItem it = a.items[seg.x + i];
+            const long long pos = a.csr_offsets[it.view] + (long long)a.totals[(int64_t)it.view * row + b] + it.rank;
+            if (pos < a.capacity)
+                a.out[pos] = it.id;
+        }
     }
 }
 
-void launch_multi_scans(const MultiArgs &a, long long *csr_offsets_of_pass, cudaStream_t s) {
-    int num_blocks = (a.num_tiles + kGatherTiles - 1) / kGatherTiles;
-    multi_scan_blocks_kernel<<<1, 1024, 0, s>>>(a.block_totals, num_blocks, a.n_views, csr_offsets_of_pass);
-    multi_scan_tiles_kernel<<<num_blocks, 1024, 0, s>>>(a.counts, a.block_totals, a.num_tiles, a.n_views);
+// ------------------------------------------------------------------------------------------------
+// launchers
+// ------------------------------------------------------------------------------------------------
+
+void launch_mv_plain_test(const MvArgs &a, int num_sms, cudaStream_t s) {
+    if (a.n_plain <= 0 || a.num_groups128 <= 0)
+        return;
+    const int n_chunks = (a.n_plain + a.views_per_warp - 1) / a.views_per_warp;
+    const long long items = (long long)a.num_groups128 * n_chunks;
+    static int per_sm = 0;
+    if (!per_sm) {
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, mv_plain_test_kernel, kMvThreads, 0);
+        if (per_sm < 1)
+            per_sm = 1;
+    }
+    long long grid = (items + kMvThreads / 32 - 1) / (kMvThreads / 32);
+    if (grid > (long long)num_sms * per_sm)
+        grid = (long long)num_sms * per_sm;
+    mv_plain_test_kernel<<<(unsigned)grid, kMvThreads, 0, s>>>(a);
+}
+
+void launch_mv_expand_masks(const MvArgs &a, cudaStream_t s) {
+    if (a.n_plain <= 0 || a.num_blocks <= 0)
+        return;
+    mv_expand_masks_kernel<<<dim3((unsigned)a.num_blocks, (unsigned)a.n_plain), kMvThreads, 0, s>>>(a);
+}
+
+void launch_mv_scan(const MvArgs &a, cudaStream_t s) {
+    if (a.n_views > 0)
+        mv_scan_kernel<<<(unsigned)a.n_views, kMvThreads, 0, s>>>(a);
+}
+
+void launch_mv_bin_lights(const MvArgs &a, cudaStream_t s) {
+    if (a.n_groups > 0)
+        mv_bin_lights_kernel<<<(unsigned)a.n_groups, kMvThreads, 0, s>>>(a);
+}
+
+static size_t mv_sparse_smem(const MvArgs &a) {
+    return sizeof(unsigned long long) * (size_t)(a.grid.dim[1] * a.grid.dim[2]) + sizeof(uint32_t) * (kMvPairCapacity + 2 * kMaskBlockWords);
+}
+
+void launch_mv_sparse(const MvArgs &a, cudaStream_t s) {
+    if (a.n_groups <= 0 || a.num_blocks <= 0)
+        return;
+    const size_t smem = mv_sparse_smem(a);
+    static size_t allowed = 0;
+    if (smem > allowed) {
+        cudaFuncSetAttribute(mv_sparse_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        allowed = smem;
+    }
+    mv_sparse_kernel<<<(unsigned)a.num_blocks, kMvThreads, smem, s>>>(a);
+}
+
+void launch_mv_expand_items(const MvArgs &a, cudaStream_t s) {
+    if (a.n_groups <= 0 || a.num_blocks <= 0)
+        return;
+    mv_expand_items_kernel<<<(unsigned)(a.num_blocks < 1184 ? a.num_blocks : 1184), kMvThreads, 0, s>>>(a);
 }
 
 }  // namespace ovis

@@ -6,11 +6,11 @@
 // when the graphics API has already taken the VRAM budget, and many engines simply forbid driver
 // allocations after start-up and hand out all device memory from their own pool. Such a caller owns its
 // bounds and result buffers already; the only thing the cull needs beyond them is scratch space for the
-// per-warp-tile survivor lists and counts. Here that scratch is a fixed array that is part of the library
+// survivor bitmap (one bit per entity) and the per-block totals. Here that scratch is a fixed array that is part of the library
 // image, so the call path contains no cudaMalloc, cudaFree, or any allocating runtime/library routine.
 //
 // The price is a hard size limit (OVIS_NOALLOC_MAX_ENTITIES) and one shared scratch per GPU:
-//   - every GPU that loads liborion_vis.so carries the ~4.2 MB array until the process exits;
+//   - every GPU that loads liborion_vis.so carries the ~130 KB array until the process exits;
 //   - all calls on a GPU use the same array. It still holds the previous call's data, so each call clears
 //     the one part that has to start at zero (the block totals); the rest is overwritten before it is read;
 //   - two calls whose kernels overlap on the same GPU (different streams, or different host threads) would
@@ -31,16 +31,13 @@ int report_error(int code, const char *message);
 namespace {
 
 constexpr int64_t kMaxEntities = OVIS_NOALLOC_MAX_ENTITIES;
-constexpr int kVariant = 0;                                     // 256-entity warp tiles, as the world path uses for large sets
-constexpr int64_t kTileEntities = 256;
-constexpr int64_t kMaxTiles = kMaxEntities / kTileEntities;     // 4096
-constexpr int64_t kMaxBlocks = kMaxTiles / ovis::kGatherTiles + 1;
+constexpr int64_t kStrideTile = 256;                            // the documented stride rule: whole 256-entity tiles
+constexpr int64_t kMaxBlocks = kMaxEntities / ovis::kMaskBlockEntities + 1;
 
-// Scratch layout inside the array, in bytes.
-constexpr size_t kStagingBytes = sizeof(uint32_t) * kMaxEntities;                 // survivor ids, one slot per warp tile
-constexpr size_t kCountsBytes = sizeof(uint32_t) * kMaxTiles;                     // survivors per warp tile
-constexpr size_t kTotalsBytes = sizeof(uint32_t) * 2 * kMaxBlocks;                // two sets of per-block totals
-constexpr size_t kScratchBytes = kStagingBytes + kCountsBytes + ((kTotalsBytes + 255) / 256) * 256;
+// Scratch layout inside the array, in bytes: the survivor bitmap (one bit per entity slot) and two sets of block totals.
+constexpr size_t kBitmapBytes = sizeof(uint32_t) * (kMaxEntities / 32);
+constexpr size_t kTotalsBytes = sizeof(uint32_t) * 2 * kMaxBlocks;
+constexpr size_t kScratchBytes = kBitmapBytes + ((kTotalsBytes + 255) / 256) * 256;
 
 // The scratch itself. In host code this name is only a handle for the runtime, NOT a device address: it must
 // never be handed to a kernel. The address kernels may use comes from cudaGetSymbolAddress (below).
@@ -50,6 +47,7 @@ struct DeviceSetup {
     bool ready = false;
     unsigned char *scratch = nullptr;     // device address of g_noalloc_scratch on this GPU
     int num_sms = 0;
+    int variant = 0;                      // what a world holding kMaxEntities or fewer would use
     int blocks_per_sm = 0;
 };
 
@@ -77,7 +75,8 @@ int setup_device(int device, DeviceSetup **out) {
         err = cudaDeviceGetAttribute(&s.num_sms, cudaDevAttrMultiProcessorCount, device);
         if (err != cudaSuccess)
             return fail_cuda("cudaDeviceGetAttribute", err);
-        s.blocks_per_sm = ovis::cull_test_max_blocks_per_sm(false, kVariant);
+        s.variant = 1;                                // register-fed, 128-entity warp tiles: what a world of this size uses
+        s.blocks_per_sm = ovis::cull_test_max_blocks_per_sm(false, s.variant);
         if (s.blocks_per_sm < 1)
             s.blocks_per_sm = 1;
         s.ready = true;
@@ -100,10 +99,16 @@ extern "C" int ovis_cull_planes_noalloc(int device, void *cuda_stream, const flo
                  (long long)n_entities, (long long)kMaxEntities);
         return ovis::report_error(OVIS_ERR_CAPACITY, buf);
     }
-    const int64_t padded = (n_entities + kTileEntities - 1) / kTileEntities * kTileEntities;
+    const int64_t padded = (n_entities + kStrideTile - 1) / kStrideTile * kStrideTile;
     if (stride % 4 != 0 || stride < padded)
         return ovis::report_error(OVIS_ERR_INVALID, "ovis_cull_planes_noalloc: stride must be a multiple of 4 and at least "
                                                     "n_entities rounded up to 256 (whole warp tiles are loaded)");
+    // The kernels read the bounds as 128-bit vectors: a pointer that is not 16-byte aligned would fault on the device and
+    // take the whole CUDA context with it, so it is refused here.
+    if (reinterpret_cast<uintptr_t>(d_world_aabb) & 15u)
+        return ovis::report_error(OVIS_ERR_INVALID, "ovis_cull_planes_noalloc: d_world_aabb must be 16-byte aligned");
+    if ((reinterpret_cast<uintptr_t>(d_out_entities) | reinterpret_cast<uintptr_t>(d_out_count)) & 3u)
+        return ovis::report_error(OVIS_ERR_INVALID, "ovis_cull_planes_noalloc: the outputs must be 4-byte aligned");
     if (device < 0 || device >= kMaxDevices)
         return ovis::report_error(OVIS_ERR_INVALID, "ovis_cull_planes_noalloc: device out of range");
     cudaError_t err = cudaSetDevice(device);
@@ -121,9 +126,8 @@ extern "C" int ovis_cull_planes_noalloc(int device, void *cuda_stream, const flo
         return err == cudaSuccess ? OVIS_OK : fail_cuda("empty-result launch", err);
     }
 
-    uint32_t *staging = reinterpret_cast<uint32_t *>(setup->scratch);
-    uint32_t *tile_counts = reinterpret_cast<uint32_t *>(setup->scratch + kStagingBytes);
-    uint32_t *totals = reinterpret_cast<uint32_t *>(setup->scratch + kStagingBytes + kCountsBytes);
+    uint32_t *survivors = reinterpret_cast<uint32_t *>(setup->scratch);
+    uint32_t *totals = reinterpret_cast<uint32_t *>(setup->scratch + kBitmapBytes);
 
     ovis::CullArgs a{};
     for (int i = 0; i < 6; i++)
@@ -131,14 +135,13 @@ extern "C" int ovis_cull_planes_noalloc(int device, void *cuda_stream, const flo
     a.bounds = d_world_aabb;
     a.stride = stride;
     a.n = n_entities;
-    a.num_tiles = (int)(padded / kTileEntities);
-    a.num_blocks = (a.num_tiles + ovis::kGatherTiles - 1) / ovis::kGatherTiles;
+    a.sign_codes = ovis::plane_sign_codes(planes);
+    a.num_groups = (int)((n_entities + 127) / 128);
+    a.num_blocks = (int)((n_entities + ovis::kMaskBlockEntities - 1) / ovis::kMaskBlockEntities);
     a.mask = nullptr;
-    a.staging = staging;
-    a.tile_counts = tile_counts;
+    a.survivors = survivors;
     a.block_totals = totals;                       // accumulated into by this call: must start at zero
     a.block_totals_next = totals + kMaxBlocks;     // the kernel's "re-arm the other set" write lands here, unused
-    a.id_base = id_base;
 
     // The array keeps whatever the previous call left. Only the block totals are added to rather than
     // overwritten, so they are the only part that has to be cleared.
@@ -146,19 +149,16 @@ extern "C" int ovis_cull_planes_noalloc(int device, void *cuda_stream, const flo
     if (err != cudaSuccess)
         return fail_cuda("cudaMemsetAsync(block totals)", err);
 
-    const int warps_per_block = ovis::kCullThreads / 32;
-    int grid = (a.num_tiles + warps_per_block - 1) / warps_per_block;
-    if (grid > setup->num_sms * setup->blocks_per_sm)
-        grid = setup->num_sms * setup->blocks_per_sm;
+    const int grid = ovis::cull_test_grid(setup->variant, a.num_groups, setup->num_sms * setup->blocks_per_sm);
     // one shared scratch: this call's test kernel must not overlap the previous call's gather kernel
-    ovis::launch_cull_test(a, false, kVariant, grid, stream, /*overlap_previous_gather=*/false);
+    ovis::launch_cull_test(a, false, setup->variant, grid, stream, /*overlap_previous_gather=*/false);
 
     ovis::GatherArgs g{};
-    g.staging = staging;
-    g.tile_counts = tile_counts;
+    g.survivors = survivors;
     g.block_totals = totals;
-    g.num_tiles = a.num_tiles;
-    g.tile_entities = (int)kTileEntities;
+    g.num_words = (int64_t)a.num_groups * 4;
+    g.num_blocks = a.num_blocks;
+    g.id_base = id_base;
     g.out = d_out_entities;
     g.capacity = capacity;
     g.d_base = nullptr;

@@ -70,6 +70,7 @@ struct OvisWorld {
     int blocks_per_sm[16][2] = {};         // cull test kernel occupancy per variant: [unmasked, masked]
     int fused_blocks_per_sm[16][2] = {};   // same for the fused (cooperative) kernel; 0 = not available
     int64_t launches = 0;
+    int64_t launches_after_gather = -1;   // value of `launches` right after the last gather kernel went out
     uint32_t id_base = 0;                 // global id of slot 0 (sharded worlds)
 
     // ---- entities (slot == id; slots are never reused, so slot order is insertion order)
@@ -125,10 +126,9 @@ struct OvisWorld {
     int64_t lights_dirty_lo = 0, lights_dirty_hi = 0;   // light slots changed since the last upload: [lo, hi)
 
     // ---- cull scratch and results
-    // Two staging/count sets and three block-total sets rotate from cull to cull, so that a cull's test kernel can
+    // Two survivor bitmaps and three block-total sets rotate from cull to cull, so that a cull's test kernel can
     // run while the previous cull's gather kernel is still reading its own set.
-    uint32_t *d_staging = nullptr;        // 2 x cap_ent ids: per-warp-tile survivor lists before the gather
-    uint32_t *d_tile_counts = nullptr;    // 2 x cap_ent / 128 counts
+    uint32_t *d_survivors = nullptr;      // 2 x cap_ent / 32 words: one bit per slot, written by the test kernel
     uint32_t *d_block_totals = nullptr;   // 3 x cap_blocks totals (the idle sets are zero)
     int64_t cap_blocks = 0;
     uint64_t cull_serial = 0;             // culls launched so far (selects the scratch sets)
@@ -145,19 +145,27 @@ struct OvisWorld {
     long long *d_csr_offsets = nullptr;
     int64_t cap_csr_views = 0;
 
-    // ---- multi-view (K4) scratch
-    uint32_t *d_mv_counts = nullptr;      // [supertiles][views of a pass]
-    int64_t cap_mv_counts = 0;
-    uint32_t *d_mv_totals = nullptr;      // [blocks][views of a pass]
+    // ---- multi-view (K4 / K6) scratch, see MvArgs
+    void *h_mv_stage = nullptr;           // pinned: planes | view meta | plain view ids | cube groups of one round
+    size_t cap_h_mv_stage = 0;
+    unsigned char *d_mv_stage = nullptr;  // the device copy
+    size_t cap_d_mv_stage = 0;
+    void *h_mv_result = nullptr;          // pinned: CSR offsets + state words read back at the end of a call
+    size_t cap_h_mv_result = 0;
+    unsigned char *d_mv_state = nullptr;  // [overflow, scan ticket, nodes used, items used | pad | occupancy bitmap]
+    int32_t *d_mv_heads = nullptr;        // per grid cell: first node of its light list
+    uint32_t *d_mv_totals = nullptr;      // [views of a round][blocks + 1]
     int64_t cap_mv_totals = 0;
-    float *d_mv_planes = nullptr;         // 24 floats per view
-    uint32_t *d_mv_require = nullptr;
-    uint32_t *d_mv_codes = nullptr;       // per view: P-vertex selection bits of its six planes
-    int64_t cap_mv_views = 0;
-    ovis::ViewGroupDev *d_mv_groups = nullptr;
-    int64_t cap_mv_groups = 0;
-    uint32_t *d_mv_hits = nullptr;        // [supertiles][group words of a pass]
-    int64_t cap_mv_hits = 0;
+    uint32_t *d_mv_masks = nullptr;       // [plain views of a round][words]
+    int64_t cap_mv_masks = 0;
+    uint32_t *d_mv_node_group = nullptr;
+    int32_t *d_mv_node_next = nullptr;
+    int64_t cap_mv_nodes = 0;
+    ovis::MvItem *d_mv_items = nullptr;
+    int64_t cap_mv_items = 0;
+    uint2 *d_mv_segments = nullptr;
+    int64_t cap_mv_segments = 0;
+    bool mv_force_dense = false;          // OVIS_MV_DENSE=1 (testing): cube groups take the dense pass too
 
     // ---- optional per-kernel timing of the entity cull (bench / profiling hook)
     bool timing = false;
@@ -175,6 +183,8 @@ using ovis::kCullTile;
 using ovis::kNone;
 
 constexpr int64_t kUploadChunk = 1 << 23;   // items per staged upload
+constexpr size_t kMvBitmapOffset = 64;      // bytes: four state words, padding, then the light grid's occupancy bitmap
+constexpr size_t kMvStateBytes = kMvBitmapOffset + sizeof(unsigned long long) * ovis::kMvGridMax * ovis::kMvGridMax;
 
 int use_device(OvisWorld *w) {
     OVIS_CUDA(cudaSetDevice(w->device));
@@ -246,9 +256,8 @@ int reserve_entities(OvisWorld *w, int64_t want) {
     if (!w->d_draw_counts)
         OVIS_TRY(grow(w->d_draw_counts, 0, 2, w->stream));
     OVIS_TRY(grow(w->d_result, 0, cap, w->stream, false));
-    OVIS_TRY(grow(w->d_staging, 0, 2 * cap, w->stream, false));
-    OVIS_TRY(grow(w->d_tile_counts, 0, 2 * (cap / 128), w->stream, false));
-    int64_t blocks = cap / 128 / ovis::kGatherTiles + 1;
+    OVIS_TRY(grow(w->d_survivors, 0, 2 * (cap / 32), w->stream, false));
+    int64_t blocks = cap / ovis::kMaskBlockEntities + 1;
     OVIS_TRY(grow(w->d_block_totals, 0, 3 * blocks, w->stream));   // all sets start zeroed
     w->cap_blocks = blocks;
     w->cull_serial = 0;
@@ -523,25 +532,24 @@ int enqueue_cull(OvisWorld *w, const float planes[24], uint32_t require, uint32_
     }
     OVIS_TRY(upload_masks(w));
     // small worlds are latency-bound: smaller warp tiles spread them over more warps
-    // large worlds: 256-entity tiles with the sign-specialised, FMUL2-packed plane code (variant 5; profiles/r01_cull_notes.md)
-    const int variant = w->forced_variant >= 0 ? w->forced_variant : (w->n_ent < (4 << 20) ? 1 : 5);
-    const int tile = ovis::cull_variant(variant).tile();
+    // large worlds: 256-entity tiles with the sign-specialised, FMUL2-packed plane code (profiles/r01_cull_notes.md)
+    const int variant = w->forced_variant >= 0 ? w->forced_variant : ovis::cull_default_variant(w->n_ent);
     const bool masked = require != 0 || w->any_dead;
     ovis::CullArgs a{};
     load_planes(a.planes, planes);
+    a.sign_codes = ovis::plane_sign_codes(planes);
     a.bounds = w->d_world;
     a.stride = w->cap_ent;
     a.n = w->n_ent;
-    a.num_tiles = (int)((w->n_ent + tile - 1) / tile);
-    a.num_blocks = (a.num_tiles + ovis::kGatherTiles - 1) / ovis::kGatherTiles;
+    a.num_groups = (int)((w->n_ent + 127) / 128);
+    a.num_blocks = (int)((w->n_ent + ovis::kMaskBlockEntities - 1) / ovis::kMaskBlockEntities);
     a.mask = require ? w->d_caster_bits : w->d_alive_bits;
     const int64_t set2 = (int64_t)(w->cull_serial & 1), set3 = (int64_t)(w->cull_serial % 3);
-    a.staging = w->d_staging + set2 * w->cap_ent;
-    a.tile_counts = w->d_tile_counts + set2 * (w->cap_ent / 128);
+    a.survivors = w->d_survivors + set2 * (w->cap_ent / 32);
     a.block_totals = w->d_block_totals + set3 * w->cap_blocks;
-    // zeroed by this test kernel for the next cull; last read by the gather kernel two culls ago, which has finished
+    // zeroed by this test kernel for the next cull; last read by the gather kernel two culls ago, which has finished:
+    // the previous test kernel ended with griddepcontrol.wait, i.e. not before that gather kernel had completed
     a.block_totals_next = w->d_block_totals + ((set3 + 1) % 3) * w->cap_blocks;
-    a.id_base = w->id_base;
     a.n_wait = 0;
     a.wait_flags = nullptr;
     a.wait_value = 0;
@@ -551,8 +559,7 @@ int enqueue_cull(OvisWorld *w, const float planes[24], uint32_t require, uint32_
         a.wait_flags = flags->wait_flags;
         a.wait_value = flags->wait_value;
     }
-    const int warps_needed_blocks = (a.num_tiles + ovis::kCullThreads / 32 - 1) / (ovis::kCullThreads / 32);
-    int grid = std::min(warps_needed_blocks, w->num_sms * w->blocks_per_sm[variant][masked ? 1 : 0]);
+    int grid = ovis::cull_test_grid(variant, a.num_groups, w->num_sms * w->blocks_per_sm[variant][masked ? 1 : 0]);
     cudaEvent_t *ev = nullptr;
     if (w->timing) {
         if (w->timing_used + 3 > w->timing_events.size()) {
@@ -566,11 +573,11 @@ int enqueue_cull(OvisWorld *w, const float planes[24], uint32_t require, uint32_
         OVIS_CUDA(cudaEventRecord(ev[0], w->stream));
     }
     ovis::GatherArgs g{};
-    g.staging = a.staging;
-    g.tile_counts = a.tile_counts;
+    g.survivors = a.survivors;
     g.block_totals = a.block_totals;
-    g.num_tiles = a.num_tiles;
-    g.tile_entities = tile;
+    g.num_words = (int64_t)a.num_groups * 4;
+    g.num_blocks = a.num_blocks;
+    g.id_base = w->id_base;
     g.out = out;
     g.capacity = capacity;
     g.d_base = d_base;
@@ -599,7 +606,7 @@ int enqueue_cull(OvisWorld *w, const float planes[24], uint32_t require, uint32_
     const int fused_per_sm = w->fused_blocks_per_sm[variant][masked ? 1 : 0];
     const bool fused = w->fused_small && w->n_ent < (512 << 10) && fused_per_sm > 0 && !flags;
     if (fused) {
-        grid = std::min(warps_needed_blocks, w->num_sms * fused_per_sm);      // every CTA must be co-resident
+        grid = ovis::cull_test_grid(variant, a.num_groups, w->num_sms * fused_per_sm);   // every CTA must be co-resident
         OVIS_CUDA(ovis::launch_cull_fused(a, g, masked, variant, grid, w->stream));
         if (ev) {
             OVIS_CUDA(cudaEventRecord(ev[1], w->stream));
@@ -607,13 +614,18 @@ int enqueue_cull(OvisWorld *w, const float planes[24], uint32_t require, uint32_
         }
         w->launches += 1;
     } else {
-        ovis::launch_cull_test(a, masked, variant, grid, w->stream, /*overlap_previous_gather=*/true);
+        // The test kernel may overlap the gather kernel in front of it only if that is really what is in front of it: any
+        // other kernel this world enqueued since (transform levels, scatters, the light cull ...) may have written what
+        // the test kernel reads, and must have completed first.
+        const bool after_own_gather = w->launches == w->launches_after_gather;
+        ovis::launch_cull_test(a, masked, variant, grid, w->stream, /*overlap_previous_gather=*/after_own_gather);
         if (ev)
             OVIS_CUDA(cudaEventRecord(ev[1], w->stream));
         ovis::launch_cull_gather(g, w->stream);
         if (ev)
             OVIS_CUDA(cudaEventRecord(ev[2], w->stream));
         w->launches += 2;
+        w->launches_after_gather = w->launches;
     }
     w->cull_serial++;
     OVIS_CUDA(cudaGetLastError());
@@ -719,52 +731,117 @@ int enqueue_light_cull(OvisWorld *w, const float planes[24]) {
     return OVIS_OK;
 }
 
+// A group of consecutive views that share a pre-filter cube (a point light's six faces), or a single plain view.
+struct HostGroup {
+    float lo[3], hi[3];          // the cube, already inflated by its rounding margin; meaningless when !cube
+    int first_view, n_views;
+    bool cube;
+};
+
 // Pre-filter cube of a view group (nullptr centre = none). The entity side adds its own extent and margin in the kernel.
-ovis::ViewGroupDev make_group(const float *centre, float range, int first_view, int n_views) {
-    ovis::ViewGroupDev g;
-    const float inf = std::numeric_limits<float>::infinity();
-    for (int c = 0; c < 3; c++) {
-        g.lo[c] = -inf;
-        g.hi[c] = inf;
-    }
+HostGroup make_group(const float *centre, float range, int first_view, int n_views) {
+    HostGroup g{};
+    g.cube = false;
     if (centre) {
         float pmax = std::max(std::fabs(centre[0]), std::max(std::fabs(centre[1]), std::fabs(centre[2])));
         float rg = range * 1.001f + pmax * 1.0e-3f + 1.0e-2f;
+        g.cube = std::isfinite(rg) && std::isfinite(pmax);                    // NaN / infinite light: no filtering
         for (int c = 0; c < 3; c++) {
             g.lo[c] = centre[c] - rg;
             g.hi[c] = centre[c] + rg;
+            g.cube = g.cube && std::isfinite(g.lo[c]) && std::isfinite(g.hi[c]);
         }
-        if (!(rg == rg) || !(pmax == pmax))            // NaN light: no filtering
-            for (int c = 0; c < 3; c++) {
-                g.lo[c] = -inf;
-                g.hi[c] = inf;
-            }
     }
     g.first_view = first_view;
     g.n_views = n_views;
     return g;
 }
 
-// K4: all views of `groups` in passes of at most kMultiMaxViews views; result in w->d_csr_* (CSR, device).
+template <typename T>
+int ensure(T *&ptr, int64_t &cap, int64_t want, cudaStream_t s) {
+    if (want <= cap)
+        return OVIS_OK;
+    int64_t fresh = std::max<int64_t>(want, cap + cap / 2);
+    OVIS_TRY(grow(ptr, 0, fresh, s, false));
+    cap = fresh;
+    return OVIS_OK;
+}
+
+int ensure_pinned(void *&ptr, size_t &cap, size_t want) {
+    if (want <= cap)
+        return OVIS_OK;
+    if (ptr)
+        OVIS_CUDA(cudaFreeHost(ptr));
+    ptr = nullptr;
+    cap = 0;
+    size_t fresh = std::max(want + want / 2, (size_t)1 << 16);
+    OVIS_CUDA(cudaMallocHost(&ptr, fresh));
+    cap = fresh;
+    return OVIS_OK;
+}
+
+// Uniform grid over the union of the cubes of groups[ids]: cell size = the larger of (largest extent / 64) and a quarter
+// of the smallest cube side, coarsened until the per-cell lists need at most `node_budget` nodes. Fills the groups' cell
+// ranges with the same monotone cell function the kernel applies to the entities (mv cell_of).
+int64_t build_light_grid(std::vector<ovis::MvGroup> &groups, ovis::MvGrid &grid, int64_t node_budget) {
+    const float inf = std::numeric_limits<float>::infinity();
+    float min_side = inf;
+    for (int c = 0; c < 3; c++) {
+        grid.lo[c] = inf;
+        grid.hi[c] = -inf;
+    }
+    for (const ovis::MvGroup &g : groups)
+        for (int c = 0; c < 3; c++) {
+            grid.lo[c] = std::min(grid.lo[c], g.lo[c]);
+            grid.hi[c] = std::max(grid.hi[c], g.hi[c]);
+            min_side = std::min(min_side, g.hi[c] - g.lo[c]);
+        }
+    float extent[3], largest = 0.0f;
+    for (int c = 0; c < 3; c++) {
+        extent[c] = grid.hi[c] - grid.lo[c];
+        largest = std::max(largest, extent[c]);
+    }
+    float cell = std::max(largest / (float)ovis::kMvGridMax, min_side * 0.25f);
+    if (!(cell > 0.0f) || !std::isfinite(cell))
+        cell = 1.0f;
+    for (;;) {
+        for (int c = 0; c < 3; c++) {
+            float cells = std::ceil(extent[c] / cell);
+            grid.dim[c] = (int)std::min(std::max(cells, 1.0f), (float)ovis::kMvGridMax);
+            grid.inv_cell[c] = 1.0f / cell;
+        }
+        int64_t nodes = 0;
+        for (ovis::MvGroup &g : groups) {
+            int lo[3], hi[3];
+            for (int c = 0; c < 3; c++) {
+                float a = std::floor((g.lo[c] - grid.lo[c]) * grid.inv_cell[c]);
+                float b = std::floor((g.hi[c] - grid.lo[c]) * grid.inv_cell[c]);
+                lo[c] = (int)std::min(std::max(a, 0.0f), (float)(grid.dim[c] - 1));
+                hi[c] = (int)std::min(std::max(b, 0.0f), (float)(grid.dim[c] - 1));
+            }
+            g.cell_lo = (uint32_t)lo[0] | ((uint32_t)lo[1] << 8) | ((uint32_t)lo[2] << 16);
+            g.cell_hi = (uint32_t)hi[0] | ((uint32_t)hi[1] << 8) | ((uint32_t)hi[2] << 16);
+            nodes += (int64_t)(hi[0] - lo[0] + 1) * (hi[1] - lo[1] + 1) * (hi[2] - lo[2] + 1);
+        }
+        if (nodes <= node_budget || (grid.dim[0] == 1 && grid.dim[1] == 1 && grid.dim[2] == 1))
+            return nodes;
+        cell *= 2.0f;
+    }
+}
+
+// K4: all views of `groups` (consecutive, covering views 0 .. n_views - 1 in order); result in w->d_csr_* (CSR, device).
+// One upload, the kernels, one read-back of the offsets and the overflow word: a single synchronisation per call. Views
+// are processed in rounds only when the scratch of one round would exceed its budget (dense bitmaps of very many views).
 int cull_views_grouped(OvisWorld *w, int32_t n_views, const float *planes, const uint32_t *require,
-                       const std::vector<ovis::ViewGroupDev> &groups, int64_t *host_offsets_out,
+                       const std::vector<HostGroup> &groups, int64_t *host_offsets_out,
                        std::vector<long long> &host_offsets) {
     OVIS_TRY(flush_transforms(w));
     host_offsets.assign((size_t)n_views + 1, 0);
-    if (n_views + 1 > w->cap_csr_views) {
-        int64_t cap = std::max<int64_t>(n_views + 1, 64);
-        OVIS_TRY(grow(w->d_csr_offsets, 0, cap, w->stream, false));
-        w->cap_csr_views = cap;
-    }
-    if (w->cap_csr == 0) {
-        int64_t cap = std::max<int64_t>(w->cap_ent, 1 << 20);
-        OVIS_TRY(grow(w->d_csr_entities, 0, cap, w->stream, false));
-        w->cap_csr = cap;
-    }
-    OVIS_CUDA(cudaMemsetAsync(w->d_csr_offsets, 0, sizeof(long long), w->stream));
+    OVIS_TRY(ensure(w->d_csr_offsets, w->cap_csr_views, std::max<int64_t>(n_views + 1, 64), w->stream));
+    if (w->cap_csr == 0)
+        OVIS_TRY(ensure(w->d_csr_entities, w->cap_csr, std::max<int64_t>(w->cap_ent, 1 << 20), w->stream));
     if (n_views == 0 || w->n_ent == 0) {
-        if (n_views > 0)
-            OVIS_CUDA(cudaMemsetAsync(w->d_csr_offsets, 0, sizeof(long long) * ((size_t)n_views + 1), w->stream));
+        OVIS_CUDA(cudaMemsetAsync(w->d_csr_offsets, 0, sizeof(long long) * ((size_t)n_views + 1), w->stream));
         OVIS_CUDA(cudaStreamSynchronize(w->stream));
         if (host_offsets_out)
             for (int32_t v = 0; v <= n_views; v++)
@@ -779,122 +856,176 @@ int cull_views_grouped(OvisWorld *w, int32_t n_views, const float *planes, const
             return fail(OVIS_ERR_INVALID, "require mask 0x%x: only 0 or OVIS_CASTS_SHADOW is supported", r);
         any_require |= r != 0;
     }
-    // split the groups into passes of at most kMultiMaxViews views (a group is never split)
-    struct Pass { size_t g0, g1; int32_t v0, v1; };
-    std::vector<Pass> passes;
-    {
-        Pass cur = { 0, 0, 0, 0 };
-        for (size_t g = 0; g < groups.size(); g++) {
-            if (groups[g].n_views > ovis::kMultiMaxViews)
-                return fail(OVIS_ERR_INVALID, "a view group holds more than %d views", ovis::kMultiMaxViews);
-            if (cur.v1 - cur.v0 + groups[g].n_views > ovis::kMultiMaxViews) {
-                passes.push_back(cur);
-                cur = { g, g, cur.v1, cur.v1 };
-            }
-            cur.g1 = g + 1;
-            cur.v1 += groups[g].n_views;
-        }
-        if (cur.g1 > cur.g0)
-            passes.push_back(cur);
+    const int num_groups128 = (int)((w->n_ent + 127) / 128);
+    const int num_blocks = (int)((w->n_ent + ovis::kMaskBlockEntities - 1) / ovis::kMaskBlockEntities);
+    const int64_t num_words = (int64_t)num_groups128 * 4;
+    const int64_t row = num_blocks + 1;
+    // scratch budgets of one round
+    const int64_t max_plain = std::max<int64_t>(1, ((int64_t)1 << 28) / num_words);          // 1 GiB of survivor bitmaps
+    const int64_t max_views = std::max<int64_t>(ovis::kMvMaxGroupViews, ((int64_t)1 << 28) / row);   // 1 GiB of block totals
+    if (!w->d_mv_state) {
+        OVIS_CUDA(cudaMalloc(&w->d_mv_state, kMvStateBytes));
+        OVIS_CUDA(cudaMemsetAsync(w->d_mv_state, 0, kMvStateBytes, w->stream));
+        OVIS_CUDA(cudaMalloc(&w->d_mv_heads, sizeof(int32_t) * ovis::kMvGridMax * ovis::kMvGridMax * ovis::kMvGridMax));
     }
-    const int num_tiles = (int)((w->n_ent + 1023) / 1024);
-    const int num_blocks = (num_tiles + ovis::kGatherTiles - 1) / ovis::kGatherTiles;
-    const int64_t pass_views = std::min<int64_t>(n_views, ovis::kMultiMaxViews);
-    if ((int64_t)num_tiles * pass_views > w->cap_mv_counts) {
-        // counts (one word) followed by the sub-tile masks (one byte) per (supertile, view)
-        OVIS_TRY(grow(w->d_mv_counts, 0, ((int64_t)num_tiles * pass_views * 5 + 3) / 4, w->stream, false));
-        w->cap_mv_counts = (int64_t)num_tiles * pass_views;
-    }
-    if ((int64_t)num_blocks * pass_views > w->cap_mv_totals) {
-        OVIS_TRY(grow(w->d_mv_totals, 0, (int64_t)num_blocks * pass_views, w->stream, false));
-        w->cap_mv_totals = (int64_t)num_blocks * pass_views;
-    }
-    {
-        int64_t max_words = 1;
-        for (const Pass &p : passes)
-            max_words = std::max<int64_t>(max_words, (int64_t)(p.g1 - p.g0 + 31) / 32);
-        if ((int64_t)num_tiles * max_words > w->cap_mv_hits) {
-            OVIS_TRY(grow(w->d_mv_hits, 0, (int64_t)num_tiles * max_words, w->stream, false));
-            w->cap_mv_hits = (int64_t)num_tiles * max_words;
-        }
-    }
-    if (n_views > w->cap_mv_views) {
-        OVIS_TRY(grow(w->d_mv_planes, 0, 24 * (int64_t)n_views, w->stream, false));
-        OVIS_TRY(grow(w->d_mv_require, 0, (int64_t)n_views, w->stream, false));
-        OVIS_TRY(grow(w->d_mv_codes, 0, (int64_t)n_views, w->stream, false));
-        w->cap_mv_views = n_views;
-    }
-    if ((int64_t)groups.size() > w->cap_mv_groups) {
-        OVIS_TRY(grow(w->d_mv_groups, 0, (int64_t)groups.size(), w->stream, false));
-        w->cap_mv_groups = (int64_t)groups.size();
-    }
-    // groups are uploaded with first_view relative to their pass
-    std::vector<ovis::ViewGroupDev> rel(groups);
-    std::vector<uint32_t> req((size_t)n_views, 0u);
-    std::vector<uint32_t> codes((size_t)n_views, 0u);
-    for (int32_t v = 0; v < n_views; v++) {
-        req[(size_t)v] = require ? require[v] : 0u;
-        for (int p = 0; p < 6; p++)                              // calcPVertex picks max where the normal component is >= 0
-            for (int c = 0; c < 3; c++)
-                if (planes[24 * (size_t)v + 4 * p + c] >= 0.0f)
-                    codes[(size_t)v] |= 1u << (3 * p + c);
-    }
-    for (const Pass &p : passes)
-        for (size_t g = p.g0; g < p.g1; g++)
-            rel[g].first_view -= p.v0;
-    OVIS_CUDA(cudaMemcpyAsync(w->d_mv_planes, planes, sizeof(float) * 24 * (size_t)n_views, cudaMemcpyHostToDevice, w->stream));
-    OVIS_CUDA(cudaMemcpyAsync(w->d_mv_require, req.data(), sizeof(uint32_t) * (size_t)n_views, cudaMemcpyHostToDevice, w->stream));
-    OVIS_CUDA(cudaMemcpyAsync(w->d_mv_codes, codes.data(), sizeof(uint32_t) * (size_t)n_views, cudaMemcpyHostToDevice, w->stream));
-    OVIS_CUDA(cudaMemcpyAsync(w->d_mv_groups, rel.data(), sizeof(ovis::ViewGroupDev) * rel.size(), cudaMemcpyHostToDevice, w->stream));
-    OVIS_CUDA(cudaStreamSynchronize(w->stream));       // rel / req are locals
+    bool force_dense = w->mv_force_dense;
 
-    for (int attempt = 0; attempt < 2; attempt++) {
+    for (int attempt = 0;; attempt++) {
+        if (attempt == 8)
+            return fail(OVIS_ERR_NOMEM, "multi-view result did not fit after regrowing");
         OVIS_CUDA(cudaMemsetAsync(w->d_csr_offsets, 0, sizeof(long long), w->stream));
-        for (const Pass &p : passes) {
-            ovis::MultiArgs a{};
+        OVIS_CUDA(cudaMemsetAsync(w->d_mv_state, 0, sizeof(uint32_t), w->stream));       // the overflow word of the call
+        size_t g0 = 0;
+        while (g0 < groups.size()) {
+            // ---- one round: groups [g0, g1), views [v0, v1)
+            const int v0 = groups[g0].first_view;
+            std::vector<uint32_t> plain;                 // view ids relative to v0
+            std::vector<ovis::MvGroup> cubes;
+            size_t g1 = g0;
+            int v1 = v0;
+            for (; g1 < groups.size(); g1++) {
+                const HostGroup &hg = groups[g1];
+                const bool sparse = hg.cube && !force_dense && hg.n_views <= ovis::kMvMaxGroupViews &&
+                                    (int64_t)cubes.size() < ovis::kMvMaxGroups;
+                if (g1 > g0 && ((v1 - v0) + hg.n_views > max_views || (!sparse && (int64_t)plain.size() + hg.n_views > max_plain)))
+                    break;
+                if (sparse) {
+                    ovis::MvGroup mg{};
+                    std::memcpy(mg.lo, hg.lo, sizeof mg.lo);
+                    std::memcpy(mg.hi, hg.hi, sizeof mg.hi);
+                    mg.first_view = hg.first_view - v0;
+                    mg.n_views = hg.n_views;
+                    cubes.push_back(mg);
+                } else {
+                    for (int k = 0; k < hg.n_views; k++)
+                        plain.push_back((uint32_t)(hg.first_view - v0 + k));
+                }
+                v1 += hg.n_views;
+            }
+            const int nv = v1 - v0;
+            ovis::MvArgs a{};
+            int64_t nodes = 0;
+            if (!cubes.empty())
+                nodes = build_light_grid(cubes, a.grid, (int64_t)1 << 24);
+            // ---- staging: planes | view meta | plain view ids | cube groups, one copy
+            const size_t off_meta = sizeof(float) * 24 * (size_t)nv;
+            const size_t off_plain = off_meta + sizeof(uint32_t) * (size_t)nv;
+            const size_t off_groups = (off_plain + sizeof(uint32_t) * plain.size() + 15) & ~(size_t)15;
+            const size_t bytes = off_groups + sizeof(ovis::MvGroup) * cubes.size();
+            OVIS_TRY(ensure_pinned(w->h_mv_stage, w->cap_h_mv_stage, bytes));
+            {
+                int64_t cap = (int64_t)w->cap_d_mv_stage;
+                OVIS_TRY(ensure(w->d_mv_stage, cap, (int64_t)bytes, w->stream));
+                w->cap_d_mv_stage = (size_t)cap;
+            }
+            unsigned char *hs = static_cast<unsigned char *>(w->h_mv_stage);
+            std::memcpy(hs, planes + 24 * (size_t)v0, sizeof(float) * 24 * (size_t)nv);
+            uint32_t *meta = reinterpret_cast<uint32_t *>(hs + off_meta);
+            for (int v = 0; v < nv; v++)
+                meta[v] = ovis::plane_sign_codes(planes + 24 * (size_t)(v0 + v)) | ((require && require[v0 + v]) ? 0x80000000u : 0u);
+            // views with equal P-vertex sign codes next to each other: the kernel tests them in runs (a view's bitmap row
+            // is its position in this list, its totals row and CSR list are found through the view id, so any order works)
+            std::stable_sort(plain.begin(), plain.end(), [&](uint32_t x, uint32_t y) { return (meta[x] & 0x3ffffu) < (meta[y] & 0x3ffffu); });
+            if (!plain.empty())
+                std::memcpy(hs + off_plain, plain.data(), sizeof(uint32_t) * plain.size());
+            if (!cubes.empty())
+                std::memcpy(hs + off_groups, cubes.data(), sizeof(ovis::MvGroup) * cubes.size());
+            OVIS_CUDA(cudaMemcpyAsync(w->d_mv_stage, hs, bytes, cudaMemcpyHostToDevice, w->stream));
+            // ---- scratch
+            OVIS_TRY(ensure(w->d_mv_totals, w->cap_mv_totals, (int64_t)nv * row, w->stream));
+            OVIS_TRY(ensure(w->d_mv_masks, w->cap_mv_masks, std::max<int64_t>(1, (int64_t)plain.size() * num_words), w->stream));
+            if (!cubes.empty()) {
+                if (nodes > w->cap_mv_nodes) {
+                    const int64_t fresh = std::max<int64_t>(nodes + nodes / 2, 1 << 16);
+                    OVIS_TRY(grow(w->d_mv_node_group, 0, fresh, w->stream, false));
+                    OVIS_TRY(grow(w->d_mv_node_next, 0, fresh, w->stream, false));
+                    w->cap_mv_nodes = fresh;
+                }
+                OVIS_TRY(ensure(w->d_mv_items, w->cap_mv_items, std::max<int64_t>((int64_t)1 << 20, w->n_ent / 8), w->stream));
+                OVIS_TRY(ensure(w->d_mv_segments, w->cap_mv_segments, num_blocks, w->stream));
+            }
+            const unsigned char *ds = static_cast<const unsigned char *>(w->d_mv_stage);
             a.bounds = w->d_world;
             a.stride = w->cap_ent;
             a.n = w->n_ent;
-            a.num_tiles = num_tiles;
+            a.num_groups128 = num_groups128;
+            a.num_blocks = num_blocks;
             a.alive_mask = w->any_dead ? w->d_alive_bits : nullptr;
             a.caster_mask = any_require ? w->d_caster_bits : nullptr;
-            a.groups = w->d_mv_groups + p.g0;
-            a.n_groups = (int)(p.g1 - p.g0);
-            a.any_cube = 0;
-            for (size_t g = p.g0; g < p.g1; g++)
-                if (std::isfinite(groups[g].lo[0]) || std::isfinite(groups[g].hi[0]))
-                    a.any_cube = 1;
-            a.planes = reinterpret_cast<const float4 *>(w->d_mv_planes) + 6 * (size_t)p.v0;
-            a.view_require = w->d_mv_require + p.v0;
-            a.view_codes = w->d_mv_codes + p.v0;
-            a.n_views = p.v1 - p.v0;
-            a.counts = w->d_mv_counts;
-            a.sub_masks = reinterpret_cast<uint8_t *>(w->d_mv_counts + w->cap_mv_counts);
-            a.block_totals = w->d_mv_totals;
-            a.group_hits = w->d_mv_hits;
-            a.csr_offsets = w->d_csr_offsets + p.v0;
+            a.planes = reinterpret_cast<const float4 *>(ds);
+            a.view_meta = reinterpret_cast<const uint32_t *>(ds + off_meta);
+            a.n_views = nv;
+            a.totals = w->d_mv_totals;
+            a.csr_offsets = w->d_csr_offsets + v0;
             a.out = w->d_csr_entities;
             a.capacity = w->cap_csr;
             a.id_base = w->id_base;
-            OVIS_CUDA(cudaMemsetAsync(w->d_mv_totals, 0, sizeof(uint32_t) * (size_t)num_blocks * (size_t)a.n_views, w->stream));
-            int per_sm = std::max(1, ovis::multi_max_blocks_per_sm(a.n_views, a.n_groups));
-            int grid = std::min((num_tiles + 7) / 8, w->num_sms * per_sm);
-            ovis::launch_multi_pass(a, false, grid, w->stream);
-            ovis::launch_multi_scans(a, w->d_csr_offsets + p.v0, w->stream);
-            ovis::launch_multi_pass(a, true, grid, w->stream);
-            w->launches += 4;
+            a.state = reinterpret_cast<uint32_t *>(w->d_mv_state);
+            a.plain_views = reinterpret_cast<const uint32_t *>(ds + off_plain);
+            a.n_plain = (int)plain.size();
+            {
+                // small worlds: split the views over more warps so that every SM has work
+                const int64_t want_warps = (int64_t)w->num_sms * 48;
+                int64_t vpw = num_groups128 >= want_warps ? (int64_t)plain.size()
+                                                          : ((int64_t)plain.size() * num_groups128 + want_warps - 1) / want_warps;
+                a.views_per_warp = (int)std::max<int64_t>(1, vpw);
+            }
+            a.masks = w->d_mv_masks;
+            a.groups = reinterpret_cast<const ovis::MvGroup *>(ds + off_groups);
+            a.n_groups = (int)cubes.size();
+            a.bitmap = reinterpret_cast<unsigned long long *>(w->d_mv_state + kMvBitmapOffset);
+            a.heads = w->d_mv_heads;
+            a.node_group = w->d_mv_node_group;
+            a.node_next = w->d_mv_node_next;
+            a.node_capacity = (uint32_t)std::min<int64_t>(w->cap_mv_nodes, 0xffffffffll);
+            a.items = w->d_mv_items;
+            a.item_capacity = (uint32_t)std::min<int64_t>(w->cap_mv_items, 0xffffffffll);
+            a.segments = w->d_mv_segments;
+            // ---- reset: per-block totals, the round's counters + occupancy bitmap, the cells' list heads
+            OVIS_CUDA(cudaMemsetAsync(w->d_mv_totals, 0, sizeof(uint32_t) * (size_t)((int64_t)nv * row), w->stream));
+            OVIS_CUDA(cudaMemsetAsync(w->d_mv_state + sizeof(uint32_t), 0, kMvStateBytes - sizeof(uint32_t), w->stream));   // all but the overflow word
+            if (!cubes.empty())
+                OVIS_CUDA(cudaMemsetAsync(w->d_mv_heads, 0xff, sizeof(int32_t) * (size_t)(a.grid.dim[0] * a.grid.dim[1] * a.grid.dim[2]), w->stream));
+            // ---- kernels
+            ovis::launch_mv_bin_lights(a, w->stream);
+            ovis::launch_mv_plain_test(a, w->num_sms, w->stream);
+            ovis::launch_mv_sparse(a, w->stream);
+            ovis::launch_mv_scan(a, w->stream);
+            ovis::launch_mv_expand_masks(a, w->stream);
+            ovis::launch_mv_expand_items(a, w->stream);
+            w->launches += 1 + (plain.empty() ? 0 : 2) + (cubes.empty() ? 0 : 3);
             OVIS_CUDA(cudaGetLastError());
+            if (g1 < groups.size())
+                OVIS_CUDA(cudaStreamSynchronize(w->stream));     // the pinned staging buffer is refilled by the next round
+            g0 = g1;
         }
-        OVIS_CUDA(cudaMemcpyAsync(host_offsets.data(), w->d_csr_offsets, sizeof(long long) * ((size_t)n_views + 1),
-                                  cudaMemcpyDeviceToHost, w->stream));
+        // ---- one read-back: offsets + the overflow word
+        OVIS_TRY(ensure_pinned(w->h_mv_result, w->cap_h_mv_result, sizeof(long long) * ((size_t)n_views + 3)));
+        long long *hr = static_cast<long long *>(w->h_mv_result);
+        OVIS_CUDA(cudaMemcpyAsync(hr, w->d_csr_offsets, sizeof(long long) * ((size_t)n_views + 1), cudaMemcpyDeviceToHost, w->stream));
+        OVIS_CUDA(cudaMemcpyAsync(hr + n_views + 1, w->d_mv_state, 4 * sizeof(uint32_t), cudaMemcpyDeviceToHost, w->stream));
         OVIS_CUDA(cudaStreamSynchronize(w->stream));
-        if (host_offsets[(size_t)n_views] <= w->cap_csr)
-            break;
-        if (attempt == 1)
-            return fail(OVIS_ERR_NOMEM, "multi-view result did not fit after regrowing");
-        int64_t cap = round_up(host_offsets[(size_t)n_views], 1 << 20);   // counts are exact even when writes were clipped
-        OVIS_TRY(grow(w->d_csr_entities, 0, cap, w->stream, false));
-        w->cap_csr = cap;
+        const uint32_t *state = reinterpret_cast<const uint32_t *>(hr + n_views + 1);
+        const uint32_t overflow = state[0];
+        if (overflow & ovis::kMvOverflowPairs) {         // some block was too dense for the sparse pass: everything densely
+            force_dense = true;
+            continue;
+        }
+        if (overflow & (ovis::kMvOverflowItems | ovis::kMvOverflowNodes)) {
+            if (overflow & ovis::kMvOverflowItems)
+                OVIS_TRY(ensure(w->d_mv_items, w->cap_mv_items, std::max<int64_t>(w->cap_mv_items * 2, (int64_t)state[3] + 1024), w->stream));
+            if (overflow & ovis::kMvOverflowNodes)
+                return fail(OVIS_ERR_CUDA, "light grid: node list overflow (internal error)");
+            continue;
+        }
+        if (hr[n_views] > w->cap_csr) {                  // counts are exact even when writes were clipped
+            OVIS_TRY(grow(w->d_csr_entities, 0, round_up(hr[n_views], 1 << 20), w->stream, false));
+            w->cap_csr = round_up(hr[n_views], 1 << 20);
+            continue;
+        }
+        for (int32_t v = 0; v <= n_views; v++)
+            host_offsets[(size_t)v] = hr[v];
+        break;
     }
     if (host_offsets_out)
         for (int32_t v = 0; v <= n_views; v++)
@@ -907,7 +1038,7 @@ int cull_views_grouped(OvisWorld *w, int32_t n_views, const float *planes, const
 int shadow_views_device(OvisWorld *w, const std::vector<uint32_t> &light_ids, int32_t shadow_map_resolution,
                         std::vector<int32_t> &list_light, std::vector<int32_t> &list_view, std::vector<long long> &offsets) {
     std::vector<float> planes;
-    std::vector<ovis::ViewGroupDev> groups;
+    std::vector<HostGroup> groups;
     list_light.clear();
     list_view.clear();
     for (uint32_t id : light_ids) {
@@ -934,7 +1065,7 @@ int shadow_views_device(OvisWorld *w, const std::vector<uint32_t> &light_ids, in
 // Views without a shared pre-filter: one group per view, infinite cube.
 int cull_views_device(OvisWorld *w, int32_t n_views, const float *planes, const uint32_t *require, int64_t *host_offsets_out,
                       std::vector<long long> &host_offsets) {
-    std::vector<ovis::ViewGroupDev> groups((size_t)n_views);
+    std::vector<HostGroup> groups((size_t)n_views);
     for (int32_t v = 0; v < n_views; v++) {
         groups[(size_t)v] = make_group(nullptr, 0.0f, v, 1);
     }
@@ -1004,6 +1135,8 @@ int ovis_world_create(int device, OvisWorld **out_world) {
         w->block_fence_sys = std::strcmp(v, "sys") == 0;
     if (const char *v = getenv("OVIS_DIRECT_HOST"))
         w->direct_host = atoi(v) != 0;
+    if (const char *v = getenv("OVIS_MV_DENSE"))
+        w->mv_force_dense = atoi(v) != 0;
     *out_world = w;
     return OVIS_OK;
 }
@@ -1016,14 +1149,18 @@ int ovis_world_destroy(OvisWorld *w) {
     void *bufs[] = { w->d_local, w->d_world, w->d_alive_bits, w->d_caster_bits, w->d_parent, w->d_local_trs, w->d_world_trs,
                      w->d_node_entity, w->d_dirty, w->d_light_uniforms, w->d_light_types, w->d_entity_node, w->d_pass_counts, w->d_draw_totals, w->d_draw_counts,
                      w->d_extra_entity, w->d_extra_node, w->d_level_lists, w->d_lights, w->d_light_out,
-                     w->d_staging, w->d_tile_counts, w->d_block_totals, w->d_exchange, w->d_mv_counts, w->d_mv_totals, w->d_mv_planes,
-                     w->d_mv_require, w->d_mv_codes, w->d_mv_groups, w->d_mv_hits, w->d_result, w->d_counts, w->d_csr_entities, w->d_csr_offsets,
+                     w->d_survivors, w->d_block_totals, w->d_exchange, w->d_mv_stage, w->d_mv_state, w->d_mv_heads, w->d_mv_totals,
+                     w->d_mv_masks, w->d_mv_node_group, w->d_mv_node_next, w->d_mv_items, w->d_mv_segments, w->d_result, w->d_counts, w->d_csr_entities, w->d_csr_offsets,
                      w->d_stage[0], w->d_stage[1] };
     for (void *b : bufs)
         if (b)
             cudaFree(b);
     if (w->h_counts)
         cudaFreeHost(w->h_counts);
+    if (w->h_mv_stage)
+        cudaFreeHost(w->h_mv_stage);
+    if (w->h_mv_result)
+        cudaFreeHost(w->h_mv_result);
     for (cudaEvent_t e : w->timing_events)
         cudaEventDestroy(e);
     delete w;
@@ -1047,6 +1184,7 @@ int ovis_world_set_stream(OvisWorld *w, void *cuda_stream) {
     OVIS_TRY(use_device(w));
     OVIS_CUDA(cudaStreamSynchronize(w->stream));
     w->stream = (cudaStream_t)cuda_stream;
+    w->launches_after_gather = -1;                 // nothing of ours is in front on the new stream
     return OVIS_OK;
 }
 

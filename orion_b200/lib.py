@@ -37,7 +37,7 @@ class OvisError(RuntimeError):
 
 def build(verbose: bool = False) -> str:
     """Compile the CUDA library in-tree for sm_100a (nvcc cross-compiles without a GPU)."""
-    subprocess.run(["make", "-C", os.path.join(HERE, "csrc")] + ([] if verbose else ["-s"]), check=True)
+    subprocess.run(["make", "-j8", "-C", os.path.join(HERE, "csrc")] + ([] if verbose else ["-s"]), check=True)
     return LIB_PATH
 
 

@@ -2,10 +2,13 @@
 
 A renderer calling from inside its frame loop cannot use cudaMalloc/cudaFree (they stall the device and
 may fail under a fixed VRAM budget), so this entry point keeps its scratch in a fixed array inside the
-library. The test drives it through the C ABI with caller-owned device buffers and requires exactly the
+library. The tests drive it through the C ABI with caller-owned device buffers and require exactly the
 list the regular world path (ovis_cull_planes_device) produces - same ids, same order, same count - on two
 calls in a row with different frusta, so that anything the first call left in the shared scratch would
-show up in the second. It also checks that the size limit is enforced with a clear error.
+show up in the second; and exactly the list the CPU oracle computes, including for the edge-case boxes,
+for two calls queued back to back on one stream with no host synchronisation in between, at the size
+limit, and when `capacity` clips the output. Sizes beyond the limit and misaligned bounds are refused
+with a clear error.
 
 This file is named to be collected last: a run that stops at the first failure has then already run every
 other test. It needs nothing from the other tests and passes on its own in a fresh process.
@@ -17,6 +20,12 @@ from orion_b200 import lib, scenes
 import vis_testutil as util
 
 pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def oracle():
+    from oracle import pyoracle
+    return pyoracle.load("best")
 
 
 def _soa_on_device(torch, aabb, stride):
@@ -71,9 +80,67 @@ def test_noalloc_cull_matches_world_cull_twice_in_a_row():
     world.close()
 
 
+def test_noalloc_cull_matches_the_oracle_back_to_back_on_one_stream(oracle):
+    """Against the CPU oracle (not another CUDA path): edge-case boxes in front, two frusta queued on one stream with
+    no host synchronisation between them (the second call reuses the scratch the first one's kernels are still
+    using, in stream order), each into its own output buffer."""
+    import torch
+    rng = np.random.default_rng(72)
+    edge = util.edge_boxes()
+    n = 200_003
+    aabb = np.concatenate([edge, util.random_boxes(rng, n - len(edge), extent=300.0)])
+    stride = (n + 255) // 256 * 256
+    d_bounds = _soa_on_device(torch, aabb, stride)
+    views = [scenes.make_view((0, 0, 350), (1, 0, 0, 0), 100.0, 0.1, 2000.0, 1600, 900),
+             scenes.make_view((-100, 20, 40), scenes.quat_yaw_pitch(-70.0, 10.0), 50.0, 0.5, 400.0, 1024, 768),
+             scenes.make_view((0, 0, 350), (1, 0, 0, 0), 100.0, 0.1, 2000.0, 1600, 900)]
+    outs = [torch.zeros(n, dtype=torch.int32, device="cuda") for _ in views]
+    counts = [torch.zeros(1, dtype=torch.int32, device="cuda") for _ in views]
+    stream = torch.cuda.Stream()
+    torch.cuda.synchronize()
+    for view, d_out, d_count in zip(views, outs, counts):                 # queued, never synchronised in between
+        lib.cull_planes_noalloc(0, stream.cuda_stream, d_bounds.data_ptr(), stride, n, lib.view_planes(view),
+                                d_out.data_ptr(), n, d_count.data_ptr())
+    stream.synchronize()
+    for view, d_out, d_count in zip(views, outs, counts):
+        expected = oracle.cull_aabb(aabb, oracle.view_planes(view))
+        count = int(d_count.item())
+        assert count == len(expected) and count > 0
+        assert np.array_equal(d_out[:count].cpu().numpy().view(np.uint32), expected)
+    assert int(counts[0].item()) != int(counts[1].item())
+
+
+def test_noalloc_cull_at_the_size_limit_and_with_a_clipped_capacity(oracle):
+    import torch
+    rng = np.random.default_rng(73)
+    n = lib.NOALLOC_MAX_ENTITIES                  # exactly the limit: every tile and block slot of the scratch is used
+    aabb = util.random_boxes(rng, n, extent=500.0)
+    d_bounds = _soa_on_device(torch, aabb, n)
+    view = scenes.make_view((0, 0, 600), (1, 0, 0, 0), 80.0, 0.1, 3000.0, 1600, 900)
+    planes = lib.view_planes(view)
+    expected = oracle.cull_aabb(aabb, oracle.view_planes(view), threads=8)
+    assert len(expected) > 10_000
+    d_out = torch.zeros(n, dtype=torch.int32, device="cuda")
+    d_count = torch.zeros(1, dtype=torch.int32, device="cuda")
+    lib.cull_planes_noalloc(0, 0, d_bounds.data_ptr(), n, n, planes, d_out.data_ptr(), n, d_count.data_ptr())
+    torch.cuda.synchronize()
+    assert int(d_count.item()) == len(expected)
+    assert np.array_equal(d_out[:len(expected)].cpu().numpy().view(np.uint32), expected)
+
+    # capacity below the visible count: the first `capacity` ids are written, nothing beyond, and the count is the true one
+    cap = 1000
+    d_small = torch.full((cap + 64,), -1, dtype=torch.int32, device="cuda")
+    lib.cull_planes_noalloc(0, 0, d_bounds.data_ptr(), n, n, planes, d_small.data_ptr(), cap, d_count.data_ptr())
+    torch.cuda.synchronize()
+    assert int(d_count.item()) == len(expected)
+    got = d_small.cpu().numpy()
+    assert np.array_equal(got[:cap].view(np.uint32), expected[:cap])
+    assert np.all(got[cap:] == -1)
+
+
 def test_noalloc_cull_rejects_what_it_cannot_hold():
     import torch
-    d = torch.zeros(6 * 256, dtype=torch.float32, device="cuda")
+    d = torch.zeros(6 * 256 + 4, dtype=torch.float32, device="cuda")
     out = torch.zeros(256, dtype=torch.int32, device="cuda")
     cnt = torch.zeros(1, dtype=torch.int32, device="cuda")
     planes = lib.view_planes(scenes.default_camera())
@@ -85,7 +152,14 @@ def test_noalloc_cull_rejects_what_it_cannot_hold():
     with pytest.raises(lib.OvisError) as e:      # stride must cover whole warp tiles
         lib.cull_planes_noalloc(0, 0, d.data_ptr(), 100, 100, planes, out.data_ptr(), 256, cnt.data_ptr())
     assert e.value.code == lib.OVIS_ERR_INVALID
+    with pytest.raises(lib.OvisError) as e:      # the bounds are read as 128-bit vectors: 4 bytes off is refused, not a fault
+        lib.cull_planes_noalloc(0, 0, d.data_ptr() + 4, 256, 100, planes, out.data_ptr(), 256, cnt.data_ptr())
+    assert e.value.code == lib.OVIS_ERR_INVALID and "aligned" in str(e.value)
     # an empty set is fine and yields an empty list
     lib.cull_planes_noalloc(0, 0, d.data_ptr(), 256, 0, planes, out.data_ptr(), 256, cnt.data_ptr())
     torch.cuda.synchronize()
     assert int(cnt.item()) == 0
+    # and the context is still healthy after the refusals
+    lib.cull_planes_noalloc(0, 0, d.data_ptr(), 256, 100, planes, out.data_ptr(), 256, cnt.data_ptr())
+    torch.cuda.synchronize()
+    assert int(cnt.item()) >= 0

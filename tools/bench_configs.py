@@ -26,6 +26,21 @@ from oracle import pyoracle  # noqa: E402
 THREADS = len(os.sched_getaffinity(0))
 
 
+def hbm_peak():
+    try:
+        return float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"])
+    except Exception:
+        return 6650.0
+
+
+def issue_peak():
+    """The no-FMA fp32 issue-rate peak measured by tools/issue_probe.cu on this pool's B200 (None if not recorded)."""
+    try:
+        return json.load(open(os.path.join(ROOT, "profiles", "r02_issue_peak.json")))
+    except Exception:
+        return None
+
+
 def timed(stream, fn, iters=5, warm=2):
     for _ in range(warm):
         fn()
@@ -39,7 +54,7 @@ def timed(stream, fn, iters=5, warm=2):
     return float(np.median([a.elapsed_time(b) for a, b in evs])), out
 
 
-def config3(small):
+def config3(small, full_parity=True):
     oracle = pyoracle.load("best")
     kw = dict(n_groups=1000, n_parts=900_000, n_lights=512) if small else {}
     t0 = time.perf_counter()
@@ -115,7 +130,7 @@ def config3(small):
     cpu_cull_s = time.perf_counter() - t0
     ok_main = bool(np.array_equal(ents, exp)) and bool(np.array_equal(ls, oracle.light_cull(s["lights"], planes)))
     ent_all = w.read_device(d_ent, int(off[-1]))
-    sample = list(range(0, len(ll), max(1, len(ll) // 24)))[:24]
+    sample = list(range(len(ll))) if full_parity else list(range(0, len(ll), max(1, len(ll) // 24)))[:24]
     ok_lists = True
     cpu_view_s = 0.0
     for k in sample:
@@ -126,6 +141,9 @@ def config3(small):
         ok_lists &= bool(np.array_equal(ent_all[off[k]:off[k + 1]], e))
     ok_lists &= all(np.array_equal(a, b) for a, b in zip(full, (ll, lv, off, ent_all)))
     w.close()
+    peak = hbm_peak()
+    frame_ms = upd_ms + cull_ms + lists_ms
+    cpu_frame_s = cpu_update_s + cpu_cull_s + cpu_view_s / max(len(sample), 1) * len(ll)
     return {
         "workload": f"configs[2]: {n_ent / 1e6:g}M dynamic entities, depth-3 hierarchy ({n_nodes} nodes), {len(s['lights'])} point lights",
         "scene_generation_s": gen_s, "world_build_s": build_s,
@@ -135,17 +153,151 @@ def config3(small):
         "cull_with_lights_host_api_ms": full_cull_host_ms,
         "shadow_views": int(len(ll)), "shadow_pairs": int(off[-1]) if len(off) else 0,
         "shadow_lists_device_ms": lists_ms, "shadow_lists_host_api_ms": lists_host_ms,
-        "frame_ms_update_cull_lists": upd_ms + cull_ms + lists_ms,
-        "tests_per_s_brute_force_equivalent": n_ent * n_views / ((upd_ms + cull_ms + lists_ms) * 1e-3),
-        "parity": {"world_trs_exact": ok_trs, "world_aabb_exact": ok_aabb, "main_view_and_lights": ok_main,
-                   "shadow_lists_sampled_and_api_consistent": bool(ok_lists), "sampled_lists": len(sample), "oracle": oracle.name},
-        "cpu": {"threads": THREADS, "update_1thread_s": cpu_update_s, "main_cull_s": cpu_cull_s,
-                "per_shadow_view_cull_s": cpu_view_s / max(len(sample), 1),
-                "frame_estimate_s": cpu_update_s + cpu_cull_s + cpu_view_s / max(len(sample), 1) * len(ll)},
+        "frame_ms_update_cull_lists": frame_ms,
+        "tests_per_s_brute_force_equivalent": n_ent * n_views / (frame_ms * 1e-3),
+        "roofline_update": {"bound": "hbm", "achieved": 132 * n_nodes / (upd_ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
+                            "frac": 132 * n_nodes / (upd_ms * 1e-3) / 1e9 / peak,
+                            "formula": "132 B per dirty node (SURVEY.md 8(d)), whole update incl. the upload of the moved groups"},
+        "parity": {"bit_exact_vs_oracle": bool(ok_trs and ok_aabb and ok_main and ok_lists),
+                   "world_trs_exact": ok_trs, "world_aabb_exact": ok_aabb, "main_view_and_lights": ok_main,
+                   "shadow_lists_exact_and_api_consistent": bool(ok_lists), "lists_checked": len(sample), "lists": int(len(ll)),
+                   "oracle": oracle.name},
+        "cpu_baseline": {"value": n_ent * n_views / cpu_frame_s, "unit": "tests/s", "cores": THREADS, "kind": oracle.name,
+                         "sample": f"one whole frame: tree update (1 thread, {cpu_update_s:.2f} s) + main cull + {len(sample)} of {len(ll)} "
+                                   f"shadow-view culls timed ({THREADS} threads), scaled to all {len(ll)}",
+                         "frame_s": cpu_frame_s, "update_1thread_s": cpu_update_s, "main_cull_s": cpu_cull_s,
+                         "per_shadow_view_cull_s": cpu_view_s / max(len(sample), 1)},
     }
 
 
-def config4(small):
+def config1():
+    """configs[0]: the apps/cubes demo scene - 4 render entities, 20 views per frame (camera + 1 spot + 3 point lights x 6).
+    Times one frame's culls three ways: the reference's own SimpleRenderWorld (tier A, as DeferredRenderPipeline drives it:
+    one cull() per view), this library called the same way (ovis_cull per view: 20 host round trips), and this library's
+    frame call (ovis_cull for the camera + one ovis_build_shadow_lists). The GPU loses here and the numbers say so."""
+    oracle = pyoracle.load("best")
+    s = scenes.cubes_scene()
+    n = len(s["local_aabb"])
+    w = lib.World(0)
+    e0 = w.add_entities(s["local_aabb"], s["flags"])
+    w.set_transforms(np.arange(e0, e0 + n, dtype=np.uint32), s["trs"])
+    w.add_lights(s["lights"])
+    ents, ls = w.cull(s["view"])
+    lists = w.shadow_lists(s["view"])
+    views = [s["view"]]
+    for k in range(len(lists[0])):
+        views.append(lib.light_shadow_views(s["lights"][lists[0][k]])[lists[1][k]])
+    n_views = len(views)
+
+    def per_view():
+        w.cull(s["view"])
+        for v in views[1:]:
+            w.cull(v, flags=0)
+
+    def per_frame():
+        w.cull(s["view"])
+        return w.shadow_lists(s["view"])
+
+    def wall(fn, reps=200):
+        for _ in range(10):
+            fn()
+        t0 = time.perf_counter()
+        for _ in range(reps):
+            fn()
+        return (time.perf_counter() - t0) / reps * 1e6
+
+    per_view_us, per_frame_us = wall(per_view), wall(per_frame)
+    out = {"workload": f"configs[0]: apps/cubes demo scene, {n} render entities x {n_views} views (1 camera + 1 spot + 3 point lights x 6 faces)",
+           "entities": n, "views": n_views,
+           "gpu_per_view_calls_us_per_frame": per_view_us, "gpu_frame_call_us_per_frame": per_frame_us,
+           "tests_per_s_gpu_frame_call": n * n_views / (per_frame_us * 1e-6),
+           "note": "launch- and round-trip-bound: 80 entity-view tests per frame; the CPU reference does them in a few microseconds"}
+    ok = None
+    if oracle.has_world:
+        rw = oracle.world()
+        rw.add_entities(s["trs"], s["local_aabb"], s["flags"])
+        rw.add_lights(s["lights"])
+        r_ents, r_ls = rw.cull(s["view"])
+        r_lists = rw.shadow_lists(s["view"])
+        ok = bool(np.array_equal(ents, r_ents) and np.array_equal(ls, r_ls) and all(np.array_equal(a, b) for a, b in zip(lists, r_lists)))
+
+        def ref_frame():
+            rw.cull(s["view"])
+            rw.shadow_lists(s["view"])
+
+        ref_us = wall(ref_frame, reps=2000)
+        rw.close()
+        out["cpu_baseline"] = {"value": n * n_views / (ref_us * 1e-6), "unit": "tests/s", "cores": 1, "kind": oracle.name,
+                               "sample": "the whole frame: SimpleRenderWorld::cull for the camera + the prepareLights loop over every "
+                                         "shadow view (tier A: the reference's own classes), through ctypes, 2000 frames",
+                               "us_per_frame": ref_us}
+        out["gpu_over_cpu_time_ratio_frame_call"] = per_frame_us / ref_us
+    out["parity"] = {"bit_exact_vs_oracle": ok, "oracle": oracle.name if ok is not None else None}
+    w.close()
+    return out
+
+
+def dense_visible(n=12_500_000):
+    """The bench shard with the camera inside a dense cloud (config-2 distribution at 1/4 of the extent): ~5 % of 12.5 M
+    entities visible, so the gather kernel and the host copy carry real traffic (the headline frustum sees 0.09 %)."""
+    oracle = pyoracle.load("best")
+    aabb, flags = scenes.static_boxes(n, 4000, 1000.0)
+    view = scenes.default_camera()
+    planes = lib.view_planes(view)
+    stream = torch.cuda.Stream()
+    w = lib.World(0)
+    w.set_stream(stream.cuda_stream)
+    w.reserve(n)
+    f = w.add_entities(aabb, flags)
+    w.set_world_aabbs(f, aabb)
+    out = torch.zeros(n + 1, dtype=torch.int32, device="cuda")
+
+    def fn():
+        w.cull_planes_device(planes, out.data_ptr() + 4, out.data_ptr())
+
+    for _ in range(5):
+        fn()
+    w.set_timing(True)
+    for _ in range(30):
+        fn()
+    test_ms, gather_ms = w.read_timing()
+    w.set_timing(False)
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record(stream)
+    for _ in range(100):
+        fn()
+    b.record(stream)
+    stream.synchronize()
+    frame_ms = a.elapsed_time(b) / 100
+    vis = int(out[0].item())
+    got = out[1:1 + vis].cpu().numpy().view(np.uint32)
+    t0 = time.perf_counter()
+    exp = oracle.cull_aabb(aabb, planes, threads=THREADS)
+    cpu_s = time.perf_counter() - t0
+    pinned = lib.PinnedBuffer(max(2 * vis, 1024))
+    frame = w.bind_cull(view, pinned.array, flags=0)
+    for _ in range(3):
+        frame()
+    t0 = time.perf_counter()
+    for _ in range(50):
+        got_n = frame()[0]
+    e2e_ms = (time.perf_counter() - t0) / 50 * 1e3
+    ok = bool(np.array_equal(got, exp)) and got_n == vis and bool(np.array_equal(pinned.array[:vis], exp))
+    w.close()
+    peak = hbm_peak()
+    alg = 24 * n + 4 * vis
+    return {"workload": f"{n / 1e6:g}M entities (config-2 distribution in [-1000,1000]^3), 1 camera frustum: {100.0 * vis / n:.1f} % visible",
+            "entities": n, "visible": vis, "test_kernel_ms": float(np.median(test_ms)), "gather_kernel_ms": float(np.median(gather_ms)),
+            "cull_ms_per_frame": frame_ms, "tests_per_s": n / (frame_ms * 1e-3),
+            "roofline": {"bound": "hbm", "achieved": alg / (frame_ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
+                         "frac": alg / (frame_ms * 1e-3) / 1e9 / peak, "formula": "24 B/entity + 4 B/visible id over the whole frame (both kernels)"},
+            "e2e_host_api": {"ms_per_frame": e2e_ms, "tests_per_s": n / (e2e_ms * 1e-3), "d2h_bytes_per_step": 8 + 4 * vis},
+            "parity": {"bit_exact_vs_oracle": ok, "oracle": oracle.name},
+            "cpu_baseline": {"value": n / cpu_s, "unit": "tests/s", "cores": THREADS, "kind": oracle.name,
+                             "sample": "one pass over the same 12.5 M entities, flat arrays", "ms_per_frame": cpu_s * 1e3}}
+
+
+def config4(small, full_parity=True, brute=True):
     oracle = pyoracle.load("best")
     s = scenes.config4(n=1_000_000 if small else 10_000_000)
     n = len(s["aabb"])
@@ -166,7 +318,7 @@ def config4(small):
     lists_ms, res = timed(stream, lambda: w.cull_shadow_views_device(light_ids), iters=5)
     ll, lv, off, d_off, d_ent = res
     ent_all = w.read_device(d_ent, int(off[-1]))
-    sample = list(range(0, len(ll), 16))
+    sample = list(range(len(ll))) if full_parity else list(range(0, len(ll), 16))
     ok_lists = True
     cpu_view_s = 0.0
     for k in sample:
@@ -175,17 +327,21 @@ def config4(small):
         e = oracle.cull_aabb(s["aabb"], oracle.view_planes(v), s["flags"], 1, threads=THREADS)
         cpu_view_s += time.perf_counter() - t0
         ok_lists &= bool(np.array_equal(ent_all[off[k]:off[k + 1]], e))
-    # brute-force comparison point on the GPU: the same 384 views without the pre-filter
-    face_planes = []
-    for l in s["lights"]:
-        for v in lib.light_shadow_views(np.asarray(l)):
-            face_planes.append(lib.view_planes(v).reshape(24))
-    face_planes = np.stack(face_planes)
-    brute_ms, (boff, _, bd_ent) = timed(stream, lambda: w.cull_views_device(face_planes, np.ones(len(face_planes), dtype=np.uint32)),
-                                        iters=3, warm=1)
-    ok_brute = bool(np.array_equal(boff, off)) and bool(np.array_equal(w.read_device(bd_ent, int(boff[-1])), ent_all))
+    # brute-force comparison point on the GPU: the same 384 views without the pre-filter (the dense pass)
+    brute_ms, ok_brute = None, None
+    if brute:
+        face_planes = []
+        for l in s["lights"]:
+            for v in lib.light_shadow_views(np.asarray(l)):
+                face_planes.append(lib.view_planes(v).reshape(24))
+        face_planes = np.stack(face_planes)
+        brute_ms, (boff, _, bd_ent) = timed(stream, lambda: w.cull_views_device(face_planes, np.ones(len(face_planes), dtype=np.uint32)),
+                                            iters=3, warm=1)
+        ok_brute = bool(np.array_equal(boff, off)) and bool(np.array_equal(w.read_device(bd_ent, int(boff[-1])), ent_all))
     n_views = len(cam_views) + len(ll)
     w.close()
+    issue = issue_peak()
+    cam_tests = n * len(cam_views)
     return {
         "workload": f"configs[3]: {n / 1e6:g}M static entities x (1 camera + 4 cascade views + {len(s['lights'])} point lights x 6 faces) = {n_views} views",
         "camera_and_cascades_ms": cam_ms, "camera_visible": [int(coff[i + 1] - coff[i]) for i in range(len(cam_views))],
@@ -193,16 +349,30 @@ def config4(small):
         "frame_ms": cam_ms + lists_ms,
         "tests_per_s_brute_force_equivalent": n * n_views / ((cam_ms + lists_ms) * 1e-3),
         "light_faces_without_prefilter_ms": brute_ms,
-        "parity": {"camera_views": bool(ok_cam), "light_faces_sampled": bool(ok_lists), "sampled_lists": len(sample),
+        "roofline_camera_and_cascades": None if not issue else {
+            "bound": "fp32 issue rate without FMA", "unit": "plane tests/s",
+            "achieved": 6 * cam_tests / (cam_ms * 1e-3), "peak": issue["cull_mix_plane_tests_per_s"],
+            "frac": 6 * cam_tests / (cam_ms * 1e-3) / issue["cull_mix_plane_tests_per_s"],
+            "peak_source": "profiles/r02_issue_peak.json (tools/issue_probe.cu: the inner loop's instruction mix, nothing else)",
+            "note": "6 plane tests per entity-view counted (no early-out credit); includes the scan and expand kernels"},
+        "parity": {"bit_exact_vs_oracle": bool(ok_cam and ok_lists and (ok_brute is not False)),
+                   "camera_views": bool(ok_cam), "light_faces_exact": bool(ok_lists), "lists_checked": len(sample), "lists": int(len(ll)),
                    "prefilter_equals_brute_force_all_384": ok_brute, "oracle": oracle.name},
-        "cpu": {"threads": THREADS, "per_view_cull_s": cpu_view_s / len(sample), "frame_estimate_s": cpu_view_s / len(sample) * n_views},
+        "cpu_baseline": {"value": n * n_views / (cpu_view_s / len(sample) * n_views), "unit": "tests/s", "cores": THREADS,
+                         "kind": oracle.name,
+                         "sample": f"{len(sample)} of the {len(ll)} light-face culls timed ({THREADS} threads, flat arrays), scaled to all {n_views} views",
+                         "per_view_cull_s": cpu_view_s / len(sample), "frame_s": cpu_view_s / len(sample) * n_views},
     }
 
 
 if __name__ == "__main__":
     small = "--small" in sys.argv
-    which = [a for a in sys.argv[1:] if a in ("3", "4")] or ["3", "4"]
+    which = [a for a in sys.argv[1:] if a in ("1", "3", "4", "dense")] or ["1", "3", "4", "dense"]
     out = {}
+    if "1" in which:
+        out["config1"] = config1()
+    if "dense" in which:
+        out["dense_visible"] = dense_visible(1_000_000 if small else 12_500_000)
     if "3" in which:
         out["config3"] = config3(small)
     if "4" in which:

@@ -44,7 +44,7 @@ for n, extent in ((1_000_000, 1000.0), (12_500_000, 4000.0), (12_500_000, 1000.0
 print(json.dumps(res))
 ''' % ROOT
 
-variants = [int(v) for v in sys.argv[1:]] or list(range(3))
+variants = [int(v) for v in sys.argv[1:]] or list(range(6))
 for v in variants:
     env = dict(os.environ, OVIS_CULL_VARIANT=str(v))
     p = subprocess.run([sys.executable, "-c", CHILD], env=env, capture_output=True, text=True)
