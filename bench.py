@@ -378,9 +378,17 @@ def run_ours(args, rank: int, local_rank: int, world_size: int):
             return cull_frame()[0]
         d2h = 8 + 4 * total_visible
     else:
+        # Host consumers of a sharded world need no GPU-to-GPU exchange: every rank's gather kernel stores its segment
+        # straight into one page-locked shared-memory block all ranks map (sharded.SharedHostSegments); a frame is one
+        # ovis_cull per rank plus a flag word per rank.
+        from orion_b200.sharded import SharedHostSegments
+        seg = SharedHostSegments(rank, world_size, max(4096, int(counts.max()) * 2), f"ovis_bench_{os.environ.get('MASTER_PORT', '0')}_{os.getppid()}")
+        e2e_frame = seg.bind(world, view)
+        e2e_parts = [None]
+
         def e2e_step():
-            parts = sw.cull_to_host(lib.view_planes(view))   # merged (segmented) list in pinned host memory
-            return int(sum(len(p) for p in parts))
+            e2e_parts[0] = e2e_frame()
+            return int(sum(len(p) for p in e2e_parts[0]))
         d2h = 4 * total_visible + 4 * world_size
     for _ in range(3):
         e2e_step()
@@ -396,6 +404,10 @@ def run_ours(args, rank: int, local_rank: int, world_size: int):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     e2e_s = float(t.item())
     assert got == total_visible
+    e2e_ids = np.concatenate([np.asarray(p) for p in e2e_parts[0]]).copy() if world_size > 1 else pinned.array[:got].copy()
+    if world_size > 1:
+        barrier()
+        seg.close()
     sampler.stop_flag.set()
 
     total_entities = n * world_size
@@ -430,7 +442,8 @@ def run_ours(args, rank: int, local_rank: int, world_size: int):
                 "h2d_bytes_per_step": 96, "d2h_bytes_per_step": d2h,
                 "what": "ovis_cull(view) -> visible ids in pinned host memory; the world is device-resident between frames, "
                         "like the reference's SimpleRenderWorld is host-resident; per-frame inputs are the view (planes ride "
-                        "in the kernel parameters)"},
+                        "in the kernel parameters)" + ("; at N > 1 every rank's kernel stores its segment into one shared "
+                        "page-locked block, a frame ends when every rank's flag shows it" if world_size > 1 else "")},
         "gpu_launches": int(launches),
         "clocks": clocks,
     }
@@ -450,8 +463,9 @@ def run_ours(args, rank: int, local_rank: int, world_size: int):
                 e = oracle.cull_aabb(shard, planes, threads=cores)
             exp_parts.append(e.astype(np.uint64) + np.uint64(r * n))
         exp = np.concatenate(exp_parts).astype(np.uint32)
-        line["parity"] = {"bit_exact_vs_oracle": bool(np.array_equal(got_ids, exp)), "oracle": oracle.name,
-                          "visible": int(len(exp)), "shards_checked": world_size}
+        line["parity"] = {"bit_exact_vs_oracle": bool(np.array_equal(got_ids, exp)) and bool(np.array_equal(e2e_ids, exp)),
+                          "device_list_exact": bool(np.array_equal(got_ids, exp)), "e2e_host_list_exact": bool(np.array_equal(e2e_ids, exp)),
+                          "oracle": oracle.name, "visible": int(len(exp)), "shards_checked": world_size}
     if rank == 0 and world_size == 1 and not args.skip_extras:
         # CPU baseline on the same shard, same host
         t1, _ = cpu_cull_timing(oracle, aabb, planes, 1, 2, 1)
@@ -493,6 +507,33 @@ def run_ours(args, rank: int, local_rank: int, world_size: int):
             except Exception as e:            # an extra must not take the headline line with it
                 line["also"][key] = {"error": repr(e)}
 
+    if world_size > 1 and not args.skip_extras:
+        # The same sharded cull driven by ONE process through the C ABI (ovis_sharded_*: a worker thread per device inside
+        # the library, all gather kernels storing into one page-locked buffer) - what a single-process engine would call.
+        # Rank 0 runs it over all N GPUs while the other ranks wait on a host-side (gloo) barrier.
+        host_group = dist.new_group(backend="gloo")
+        torch.cuda.synchronize()
+        dist.barrier(group=host_group)
+        if rank == 0:
+            try:
+                spw = lib.ShardedWorld(list(range(world_size)))
+                spw.add_entities(np.concatenate([aabb if r == 0 else shard_scene(r, n)[0] for r in range(world_size)]))
+                out1 = lib.PinnedBuffer(max(total_visible * 2, 1024))
+                step1 = spw.bind_cull(view, out1.array)
+                for _ in range(5):
+                    step1()
+                t0 = time.perf_counter()
+                for _ in range(args.steps):
+                    got1, _ = step1()
+                dt = time.perf_counter() - t0
+                line.setdefault("also", {})["single_process_sharded_world"] = {
+                    "what": "ovis_sharded_cull(view) from one host thread over all N GPUs -> merged ids in host memory",
+                    "ms_per_step": dt / args.steps * 1e3, "tests_per_s": total_entities * args.steps / dt,
+                    "list_exact": bool(np.array_equal(out1.array[:got1], exp)) if "parity" in line else None}
+                spw.close()
+            except Exception as e:
+                line.setdefault("also", {})["single_process_sharded_world"] = {"error": repr(e)}
+        dist.barrier(group=host_group)
     if rank == 0:
         emit(line)
     if world is not None:

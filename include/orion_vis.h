@@ -236,6 +236,39 @@ int ovis_read_segments_host(OvisWorld *world, const uint32_t *d_flags, uint32_t 
                             int64_t segment_words, int32_t n_segments, uint32_t *host_out);
 int ovis_world_exchange_error(OvisWorld *world, int32_t *out_error);
 
+/* ---- one world over several GPUs, one host process (SURVEY.md section 8(b) "ovis_world_create(device_ids[], n, ...)",
+ * section 8(e)) ------------------------------------------------------------------------------------------------------
+ * The reference is one process and one thread (engine/src/engine.cc:147-195): its RenderWorld replacement cannot ask
+ * for a process per GPU. An OvisShardedWorld owns one OvisWorld per listed device plus one worker thread per device, so
+ * the caller's single thread still starts all shards' culls side by side. Entities are split into contiguous id ranges
+ * [r N / G, (r + 1) N / G); shard r reports global ids, so the shards' lists read in shard order are the reference's
+ * list (insertion order, simple_render_world.cc:38-41). Listing a device twice is allowed (two shards on one GPU).
+ * ovis_sharded_shard gives the shard's ordinary world for everything else (flags, removal, lights, transform trees whose
+ * nodes live on that shard). No counterpart in the reference. */
+typedef struct OvisShardedWorld OvisShardedWorld;
+int ovis_sharded_create(const int *device_ids, int32_t n_devices, OvisShardedWorld **out_world);
+int ovis_sharded_destroy(OvisShardedWorld *world);
+int ovis_sharded_count(OvisShardedWorld *world, int32_t *out_shards, int64_t *out_entities);
+int ovis_sharded_shard(OvisShardedWorld *world, int32_t shard, OvisWorld **out_world, int64_t *out_id_base);
+/* The whole entity set at once (world-space AABBs n x 6, flags n or NULL): split, uploaded, id bases set. Once per world. */
+int ovis_sharded_add_entities(OvisShardedWorld *world, int64_t n, const float *world_aabb, const uint32_t *flags);
+/* SimpleRenderWorld::cull over all shards for a HOST consumer: every device's gather kernel stores its segment straight
+ * into one page-locked buffer all devices map (no GPU-to-GPU exchange, no copy kernel); out_entities receives the merged
+ * list, dense and in id order; out_shard_counts (optional, one per shard) the per-shard counts. OVIS_ERR_CAPACITY (with
+ * *out_n_entities = required) if cap_entities is too small. */
+int ovis_sharded_cull(OvisShardedWorld *world, const OvisView *view, uint32_t require, uint32_t *out_entities,
+                      int64_t cap_entities, int64_t *out_n_entities, int64_t *out_shard_counts);
+int ovis_sharded_cull_planes(OvisShardedWorld *world, const float planes[24], uint32_t require, uint32_t *out_entities,
+                             int64_t cap_entities, int64_t *out_n_entities, int64_t *out_shard_counts);
+/* The page-locked segments of the last ovis_sharded_cull*: shard r's [count | ids...] at segments + r * segment_words. */
+int ovis_sharded_segments(OvisShardedWorld *world, const uint32_t **out_segments, int64_t *out_segment_words);
+/* For DEVICE consumers: the local culls, then one ncclAllGather per device of fixed-size [count | ids...] blocks of
+ * 1 + capacity words (the collective north_star names; NCCL is loaded at run time). On return (*out_d_blocks)[d] is, on
+ * device d, the n_shards blocks in shard order. A count above `capacity` means that block was clipped: call again with
+ * more. Needs distinct devices (one NCCL communicator). */
+int ovis_sharded_allgather_device(OvisShardedWorld *world, const float planes[24], uint32_t require, int64_t capacity,
+                                  const uint32_t *const **out_d_blocks, int64_t *out_shard_counts);
+
 /* Entity cull for callers that cannot allocate GPU memory - a render thread in the middle of a frame, or an
  * engine that forbids cudaMalloc/cudaFree after start-up because they synchronise the device, can fail under
  * a fixed VRAM budget, and bypass its own pool. No counterpart in the reference. Same result as
@@ -445,6 +478,13 @@ int ovis_read_device(OvisWorld *world, const void *d_src, int64_t bytes, void *h
 /* Pinned host memory for result buffers (plain malloc'd buffers work too, only slower to copy into). */
 int ovis_host_alloc(int64_t bytes, void **out_ptr);
 int ovis_host_free(void *ptr);
+/* Page-locks memory the caller already owns (a shared-memory segment several processes map, an engine's own result
+ * arena) so that ovis_cull / ovis_cull_planes store into it straight from the gather kernel, as they do for
+ * ovis_host_alloc memory. Processes that each hold one shard of a world can share one result buffer this way: every
+ * rank's kernel writes its own segment, no GPU-to-GPU exchange is needed for a host consumer. No counterpart in the
+ * reference. */
+int ovis_host_register(void *ptr, int64_t bytes);
+int ovis_host_unregister(void *ptr);
 
 /* Profiling hook (no counterpart in the reference, whose cull path has no timers - SURVEY.md section 5):
  * while enabled, every entity cull records CUDA events on the world's stream before the test kernel,

@@ -2143,4 +2143,17 @@ int ovis_host_free(void *ptr) {
     return OVIS_OK;
 }
 
+int ovis_host_register(void *ptr, int64_t bytes) {
+    if (!ptr || bytes <= 0)
+        return fail(OVIS_ERR_INVALID, "ovis_host_register: bad arguments");
+    OVIS_CUDA(cudaHostRegister(ptr, (size_t)bytes, cudaHostRegisterPortable | cudaHostRegisterMapped));
+    return OVIS_OK;
+}
+
+int ovis_host_unregister(void *ptr) {
+    if (ptr)
+        OVIS_CUDA(cudaHostUnregister(ptr));
+    return OVIS_OK;
+}
+
 }  // extern "C"

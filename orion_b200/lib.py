@@ -218,6 +218,15 @@ class PinnedBuffer:
             pass
 
 
+def host_register(array: np.ndarray):
+    """Page-lock (portable, mapped) memory the caller owns, e.g. a shared-memory segment: ovis_host_register."""
+    _check(load().ovis_host_register(C.c_void_p(array.ctypes.data), C.c_int64(array.nbytes)))
+
+
+def host_unregister(array: np.ndarray):
+    _check(load().ovis_host_unregister(C.c_void_p(array.ctypes.data)))
+
+
 class World:
     """Device-resident render world: the RenderWorld of engine/runtime/render/include/render_world.h:58-98."""
 
@@ -580,3 +589,78 @@ class World:
         out = np.zeros((n, 10), dtype=np.float32)
         _check(self.lib.ovis_get_node_world_trs(self.h, C.c_uint32(first), C.c_int64(n), _p(out)))
         return out
+
+
+class ShardedWorld:
+    """ovis_sharded_*: one world over several GPUs driven by one host process (worker thread per device inside the library)."""
+
+    def __init__(self, device_ids):
+        self.lib = load()
+        ids = np.ascontiguousarray(device_ids, dtype=np.int32)
+        self.h = C.c_void_p()
+        self.n = len(ids)
+        _check(self.lib.ovis_sharded_create(_p(ids), C.c_int32(len(ids)), C.byref(self.h)))
+
+    def close(self):
+        if self.h:
+            self.lib.ovis_sharded_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def add_entities(self, world_aabb, flags=None):
+        aabb = _f32(world_aabb, (-1, 6))
+        fl = _u32(flags) if flags is not None else None
+        _check(self.lib.ovis_sharded_add_entities(self.h, C.c_int64(len(aabb)), _p(aabb), _p(fl)))
+
+    def shard(self, r: int):
+        """(raw OvisWorld handle of shard r, its id base) - for the ordinary entry points."""
+        w, base = C.c_void_p(), C.c_int64()
+        _check(self.lib.ovis_sharded_shard(self.h, C.c_int32(r), C.byref(w), C.byref(base)))
+        return w, base.value
+
+    def remove_entities(self, global_ids):
+        """Convenience for tests: route removals to the owning shards (ovis_entity_remove takes shard-local slot ids)."""
+        ids = np.sort(_u32(global_ids))
+        for r in range(self.n):
+            w, base = self.shard(r)
+            _, next_base = self.shard(r + 1) if r + 1 < self.n else (None, 1 << 62)
+            local = (ids[(ids >= base) & (ids < next_base)] - np.uint32(base)).astype(np.uint32)
+            if len(local):
+                _check(self.lib.ovis_entity_remove(w, C.c_int64(len(local)), _p(local)))
+
+    def bind_cull(self, view, out_entities: np.ndarray, require=0):
+        """Frame function: step() -> (n_entities, per-shard counts); ids land in out_entities[:n]."""
+        view = np.ascontiguousarray(view, dtype=VIEW_DTYPE).reshape(1)
+        ne = C.c_int64()
+        counts = np.zeros(self.n, dtype=np.int64)
+        fn = self.lib.ovis_sharded_cull
+        args = (self.h, _p(view), C.c_uint32(require), _p(out_entities), C.c_int64(len(out_entities)), C.byref(ne), _p(counts))
+
+        def step():
+            rc = fn(*args)
+            if rc != OVIS_OK:
+                _check(rc)
+            return ne.value, counts
+        step.keep = (view, out_entities, counts)
+        return step
+
+    def cull(self, view, require=0, capacity=None):
+        ns, total = C.c_int32(), C.c_int64()
+        _check(self.lib.ovis_sharded_count(self.h, C.byref(ns), C.byref(total)))
+        out = np.empty(max(int(capacity if capacity is not None else total.value), 1), dtype=np.uint32)
+        n, counts = self.bind_cull(view, out, require)()
+        return out[:n].copy(), counts.copy()
+
+    def allgather_device(self, planes, capacity: int, require=0):
+        """NCCL mode: returns (per-device block pointers, per-shard counts)."""
+        planes = _f32(planes, (24,))
+        blocks = C.POINTER(C.c_void_p)()
+        counts = np.zeros(self.n, dtype=np.int64)
+        _check(self.lib.ovis_sharded_allgather_device(self.h, _p(planes), C.c_uint32(require), C.c_int64(capacity),
+                                                      C.byref(blocks), _p(counts)))
+        return [blocks[d] for d in range(self.n)], counts

@@ -80,6 +80,149 @@ def open_symmetric_blocks(world_size: int, capacity: int, group=None):
         return None
 
 
+class SharedHostSegments:
+    """The merged visible list for HOST consumers of a sharded world, one process per GPU: a POSIX shared-memory block
+    every rank maps and page-locks (ovis_host_register). Rank r's gather kernel stores its ids straight into segment r of
+    that block - the same single-GPU `ovis_cull` call, no GPU-to-GPU exchange, no reader kernel, one synchronise - and
+    then publishes the frame number in its flag word; a frame is complete for a rank once every flag shows it.
+
+    Layout (uint32 words): flags[size] | pad to 64 | 2 x size x (1 + capacity) segments [count | ids...]. Two segment
+    sets alternate by frame: a rank refills set (f & 1) in frame f + 2 only after it has seen every rank finish frame
+    f + 1, i.e. after every rank has consumed frame f. A frame in which some shard's list does not fit is redone by all
+    ranks in a larger block (every rank sees the same counts, so every rank takes the same decision).
+    """
+
+    def __init__(self, rank: int, size: int, capacity: int, name: str, page_lock: bool = True):
+        self.rank, self.size, self.name = rank, size, name
+        self.page_lock = page_lock                       # False: plain shared memory (the CPU tests of the protocol)
+        self.generation = 0
+        self.frame = 0
+        self.shm = None
+        self._open(int(capacity))
+
+    def _open(self, capacity: int):
+        import time
+        from multiprocessing import shared_memory
+        from . import lib as _lib
+        self._lib = _lib
+        self.capacity = capacity
+        self.seg_words = 1 + capacity
+        words = 64 + 2 * self.size * self.seg_words
+        name = f"{self.name}_g{self.generation}"
+        if self.rank == 0:
+            self.shm = shared_memory.SharedMemory(name=name, create=True, size=4 * words)
+            self.words = np.frombuffer(self.shm.buf, dtype=np.uint32, count=words)
+            self.words[:64] = 0
+            self.words[:self.size] = self.frame          # the frames so far count as delivered in the new block
+            self.words[63] = 0x600DF00D                  # the block is initialised: the other ranks may use it
+        else:
+            t0 = time.perf_counter()
+            while True:
+                try:
+                    self.shm = shared_memory.SharedMemory(name=name, create=False)
+                    if self.shm.size >= 4 * words:
+                        self.words = np.frombuffer(self.shm.buf, dtype=np.uint32, count=words)
+                        if int(self.words[63]) == 0x600DF00D:
+                            break
+                    self.shm.close()
+                except FileNotFoundError:
+                    pass
+                if time.perf_counter() - t0 > 30.0:
+                    raise RuntimeError(f"shared result block {name} never appeared")
+                time.sleep(0.0005)
+        self.flags = self.words[:self.size]
+        self.sets = self.words[64:].reshape(2, self.size, self.seg_words)
+        if self.page_lock:
+            _lib.host_register(self.words)
+
+    def _release(self):
+        if self.shm is None:
+            return
+        try:
+            if self.page_lock:
+                self._lib.host_unregister(self.words)
+        except Exception:
+            pass
+        self.flags = self.sets = self.words = None
+        try:
+            self.shm.close()
+            if self.rank == 0:
+                self.shm.unlink()
+        except Exception:
+            pass
+        self.shm = None
+
+    def bind(self, world, view):
+        """Per-rank frame function: step() -> list of per-rank id arrays (views into the shared block, valid until the
+        call after next)."""
+        import ctypes as C
+        import time
+        lib = self._lib
+        view = np.ascontiguousarray(view, dtype=lib.VIEW_DTYPE).reshape(1)
+        fn, h = world.lib.ovis_cull, world.h
+        ne, nl = C.c_int64(), C.c_int32()
+
+        def make_culls():
+            def make(k):
+                args = (h, view.ctypes.data_as(C.c_void_p), C.c_uint32(0), self.sets[k, self.rank, 1:].ctypes.data_as(C.c_void_p),
+                        C.c_int64(self.capacity), C.byref(ne), None, C.c_int32(0), C.byref(nl))
+
+                def cull():
+                    rc = fn(*args)
+                    if rc not in (lib.OVIS_OK, lib.OVIS_ERR_CAPACITY):
+                        lib._check(rc)
+                    return ne.value
+                return cull
+            return [make(0), make(1)]
+
+        step = self.bind_producer(make_culls)
+        step.keep = (view, ne, nl)
+        return step
+
+    def bind_producer(self, make_culls):
+        """The exchange protocol around any producer: make_culls() -> [cull0, cull1], where cull_k() fills
+        self.sets[k, rank, 1:1 + capacity] and returns the TRUE number of ids (also when they did not all fit). Called
+        again after the block was regrown."""
+        import time
+        lib = self._lib
+        state = {"culls": make_culls()}
+
+        def step(timeout_s: float = 20.0):
+            while True:
+                self.frame += 1
+                f, k = self.frame, self.frame & 1
+                self.sets[k, self.rank, 0] = state["culls"][k]()   # the true count, also when it did not fit
+                self.flags[self.rank] = f                     # after the ids and the count (x86 keeps the store order)
+                t0 = None
+                while int(self.flags.min()) < f:              # every rank has delivered frame f
+                    if t0 is None:
+                        t0 = time.perf_counter()
+                    elif time.perf_counter() - t0 > timeout_s:
+                        raise RuntimeError("a rank did not deliver its segment")
+                counts = self.sets[k, :, 0].astype(np.int64)
+                if int(counts.max()) <= self.capacity:
+                    return [self.sets[k, r, 1:1 + int(counts[r])] for r in range(self.size)]
+                # some shard overflowed: every rank sees that and moves to a larger block, then the frame is redone
+                old = self.shm, self.words
+                self.generation += 1
+                self.shm = None
+                self._open(int(counts.max() * 1.25) + 1024)
+                try:
+                    if self.page_lock:
+                        lib.host_unregister(old[1])
+                    old[0].close()
+                    if self.rank == 0:
+                        old[0].unlink()
+                except Exception:
+                    pass
+                state["culls"] = make_culls()
+
+        return step
+
+    def close(self):
+        self._release()
+
+
 class ShardedWorld:
     """A lib.World holding one shard plus the merge of the per-shard visible lists.
 

@@ -57,6 +57,21 @@ for mode in ("nccl", "p2p"):
         for i in range(frames):
             got = merged_list(host[i])
             assert np.array_equal(got, expected[i %% 3]), (rank, "frame", i, len(got), len(expected[i %% 3]))
+    if mode == "p2p":
+        # host consumers: every rank's kernel stores its segment into one shared page-locked block, no exchange at all;
+        # a small first block forces the regrow path on the wide frustum
+        from orion_b200.sharded import SharedHostSegments
+        seg = SharedHostSegments(rank, size, 2000, "ovis_test2gpu_%%d" %% os.getppid())
+        cams = [np.asarray(v).reshape(1).copy() for v in views]
+        cam = cams[0].copy()
+        step = seg.bind(w, cam)
+        for i in range(30):
+            cam[:] = cams[i %% 3]                             # the view is read in place every frame
+            parts = step()
+            assert np.array_equal(np.concatenate(parts), expected[i %% 3]), (rank, "shared host frame", i)
+        assert seg.generation >= 1
+        dist.barrier()
+        seg.close()
     dist.barrier()
     w.close()
 if rank == 0:
@@ -76,3 +91,47 @@ def test_two_gpu_exchange_modes(tmp_path):
                         "--master-addr", "127.0.0.1", "--master-port", "29533", str(script)],
                        capture_output=True, text=True, timeout=600)
     assert r.returncode == 0 and "MULTI_GPU_OK" in r.stdout, (r.stdout + r.stderr)[-4000:]
+
+
+ONE_GPU_WORKER = r'''
+import os, sys, numpy as np
+sys.path.insert(0, %r)
+rank, size, name = int(sys.argv[1]), int(sys.argv[2]), sys.argv[3]
+from orion_b200 import lib, scenes
+from orion_b200.sharded import SharedHostSegments, shard_range
+from oracle import pyoracle
+oracle = pyoracle.load("best")
+n_total = 300_001
+aabb, flags = scenes.static_boxes(n_total, 9, 800.0)
+lo, hi = shard_range(n_total, rank, size)
+w = lib.World(0)                                             # every shard on device 0: the box has one GPU
+f = w.add_entities(aabb[lo:hi], flags[lo:hi]); w.set_world_aabbs(f, aabb[lo:hi]); w.set_id_base(lo)
+views = [scenes.default_camera(), scenes.make_view((100, 0, 300), (1, 0, 0, 0), 60.0, 1.0, 900.0, 800, 600),
+         scenes.make_view((-300, 50, 0), scenes.quat_yaw_pitch(70.0, 0.0), 90.0, 0.5, 700.0, 1600, 900)]
+expected = [oracle.cull_aabb(aabb, oracle.view_planes(v), threads=4) for v in views]
+seg = SharedHostSegments(rank, size, 1500, name)
+cam = np.asarray(views[0]).reshape(1).copy()
+step = seg.bind(w, cam)
+for i in range(40):
+    cam[:] = np.asarray(views[i %% 3]).reshape(1)
+    parts = step()
+    assert np.array_equal(np.concatenate(parts), expected[i %% 3]), (rank, i)
+assert seg.generation >= 1
+seg.close()
+w.close()
+print("SHARED_HOST_OK", rank)
+''' % ROOT
+
+
+@pytest.mark.gpu
+def test_shared_host_segments_three_shards_on_one_gpu(tmp_path):
+    """The host-consumer merge of a sharded world (sharded.SharedHostSegments) with three processes that each hold one
+    shard on device 0: no kernel waits for another process, so it runs on a one-GPU box. Ids, order, regrow."""
+    script = tmp_path / "worker.py"
+    script.write_text(ONE_GPU_WORKER)
+    name = "ovis_test1gpu_%d" % os.getpid()
+    procs = [subprocess.Popen([sys.executable, str(script), str(r), "3", name], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+             for r in range(3)]
+    outs = [p.communicate(timeout=600)[0] for p in procs]
+    for r, (p, out) in enumerate(zip(procs, outs)):
+        assert p.returncode == 0 and "SHARED_HOST_OK" in out, (r, out[-3000:])

@@ -68,3 +68,51 @@ def test_shard_ranges_tile_the_scene():
             edges = [sharded.shard_range(n, r, g) for r in range(g)]
             assert edges[0][0] == 0 and edges[-1][1] == n
             assert all(a[1] == b[0] for a, b in zip(edges, edges[1:]))
+
+
+def _shared_host_worker(rank, size, name, n_total, capacity, frames, out_dir):
+    """One rank of the shared-host exchange with the oracle standing in for the shard's kernel (plain shared memory: no
+    CUDA in this test). Frame f uses camera f % 3, so the visible sets change and one of them overflows the block."""
+    from oracle import pyoracle
+    oracle = pyoracle.load("port")
+    aabb, _ = scenes.static_boxes(n_total, 5, 600.0)
+    lo, hi = sharded.shard_range(n_total, rank, size)
+    cams = [scenes.default_camera(), scenes.make_view((0, 0, 900), (1, 0, 0, 0), 110.0, 0.1, 3000.0, 1600, 900),
+            scenes.make_view((100, 0, 0), scenes.quat_yaw_pitch(90.0, 0.0), 40.0, 0.1, 500.0, 800, 600)]
+    lists = [oracle.cull_aabb(aabb[lo:hi], oracle.view_planes(c)) + np.uint32(lo) for c in cams]
+    seg = sharded.SharedHostSegments(rank, size, capacity, name, page_lock=False)
+    cursor = {"f": 0}
+
+    def make_culls():
+        def make(k):
+            def cull():
+                ids = lists[cursor["f"] % 3]
+                m = min(len(ids), seg.capacity)
+                seg.sets[k, rank, 1:1 + m] = ids[:m]
+                return len(ids)
+            return cull
+        return [make(0), make(1)]
+
+    step = seg.bind_producer(make_culls)
+    for f in range(frames):
+        cursor["f"] = f
+        parts = step()
+        np.save(os.path.join(out_dir, f"r{rank}_f{f}.npy"), np.concatenate([np.asarray(p) for p in parts]))
+    np.save(os.path.join(out_dir, f"gen{rank}.npy"), np.array([seg.generation, seg.capacity]))
+    seg.close()
+
+
+def test_shared_host_segments_two_ranks_with_regrow(tmp_path, port):
+    n_total, size, frames = 40_001, 2, 7
+    name = f"ovis_test_{os.getpid()}"
+    mp.spawn(_shared_host_worker, args=(size, name, n_total, 2_000, frames, str(tmp_path)), nprocs=size, join=True)
+    aabb, _ = scenes.static_boxes(n_total, 5, 600.0)
+    cams = [scenes.default_camera(), scenes.make_view((0, 0, 900), (1, 0, 0, 0), 110.0, 0.1, 3000.0, 1600, 900),
+            scenes.make_view((100, 0, 0), scenes.quat_yaw_pitch(90.0, 0.0), 40.0, 0.1, 500.0, 800, 600)]
+    exp = [port.cull_aabb(aabb, port.view_planes(c)) for c in cams]
+    assert max(len(e) for e in exp) > 2 * 2_000                 # the wide camera does not fit the first block
+    for r in range(size):
+        for f in range(frames):
+            assert np.array_equal(np.load(tmp_path / f"r{r}_f{f}.npy"), exp[f % 3]), (r, f)
+        gen, cap = np.load(tmp_path / f"gen{r}.npy")
+        assert gen >= 1 and cap > 2_000                          # both ranks moved to the larger block
