@@ -466,6 +466,12 @@ int ovis_scene_free(OvisScene *scene);
  * material or after any `g`; values parsed with strtof; engine/src/loaders/mesh_loader.cc:187-199: min/max over the
  * positions the sub-mesh's faces reference). 6 floats per sub-mesh. */
 int ovis_obj_submesh_aabbs(const char *obj_path, int32_t capacity, float *out_aabb, int32_t *out_count);
+/* Diagnostic: the canonical text of a JSON document as the scene loader's own reader sees it (strings byte for byte,
+ * members in file order, numbers as the float the reference's JSONSerialiser reads - GetFloat() = (float)double,
+ * engine/src/json_serialiser.cc:540 - plus the integer when there is one). The test suite compares it with the same dump
+ * made through the reference's own JSON dependency (the vendored rapidjson, engine/3rdparty/rapidjson), which pins the
+ * JSON layer of ovis_scene_load. OVIS_ERR_CAPACITY (with *out_length = required) if `capacity` is too small. */
+int ovis_json_canonical(const char *text, int64_t length, char *out, int64_t capacity, int64_t *out_length);
 /* Read a light back: its OvisLight, attenuation[3] and shadow bias (any output may be NULL). */
 int ovis_light_get(OvisWorld *world, uint32_t light_id, OvisLight *out_light, float out_attenuation[3], float *out_shadow_bias);
 

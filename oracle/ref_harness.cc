@@ -461,10 +461,21 @@ int32_t orc_shadow_lists(int64_t n, const float *aabb, const uint32_t *flags,
     return lists;
 }
 
-/* RESTATED loops of prepareEntities (deferred_render_pipeline.cc:318-330) / the caster loop of prepareLights (:272-283)
- * with DrawList::add (draw_list.cc:35-45); Shader/Material need the asset system and are replaced by their pass counts. */
+/* Draw lists. Up to kDrawListObjects visible entities the draws come out of the reference's own DrawList::add
+ * (draw_list.cc compiled where it lies, real RenderEntity objects: oracle/draw_harness.cc); only the two ten-line pipeline
+ * loops that pick a list (deferred_render_pipeline.cc:318-330, :272-283) are restated there. Longer lists would mean
+ * millions of RenderEntity objects (a uniform buffer and resource set each) and take the restated loop below, which
+ * tests/test_oracle.py holds equal to the DrawList path. */
+extern "C" void oref_draw_lists(int64_t n_visible, const uint32_t *visible, const uint32_t *pass_counts, const uint32_t *flags,
+                                int32_t mode, uint32_t *out_draws0, uint32_t *out_draws1, int64_t out_counts[2]);
+static const int64_t kDrawListObjects = 200000;
+
 void orc_draw_lists(int64_t n_visible, const uint32_t *visible, const uint32_t *pass_counts, const uint32_t *flags,
                     int32_t mode, uint32_t *out_draws0, uint32_t *out_draws1, int64_t out_counts[2]) {
+    if (n_visible <= kDrawListObjects) {
+        oref_draw_lists(n_visible, visible, pass_counts, flags, mode, out_draws0, out_draws1, out_counts);
+        return;
+    }
     std::vector<std::pair<uint32_t, uint32_t>> lists[2];
     auto add = [&](int list, uint32_t entity, uint32_t numPasses) {
         for (uint32_t i = 0; i < numPasses; i++)

@@ -87,11 +87,21 @@ struct JsonParser {
                 case 'r': out += '\r'; break;
                 case 'b': out += '\b'; break;
                 case 'f': out += '\f'; break;
-                case 'u': {                                     // names and asset paths are ASCII; keep the low byte
+                case 'u': {                                     // a BMP code point, stored as UTF-8 like rapidjson does
                     if (end - p < 5)
                         return fail("bad \\u escape");
                     char hex[5] = { p[1], p[2], p[3], p[4], 0 };
-                    out += (char)strtoul(hex, nullptr, 16);
+                    const unsigned long cp = strtoul(hex, nullptr, 16);
+                    if (cp < 0x80) {
+                        out += (char)cp;
+                    } else if (cp < 0x800) {
+                        out += (char)(0xc0 | (cp >> 6));
+                        out += (char)(0x80 | (cp & 0x3f));
+                    } else {
+                        out += (char)(0xe0 | (cp >> 12));
+                        out += (char)(0x80 | ((cp >> 6) & 0x3f));
+                        out += (char)(0x80 | (cp & 0x3f));
+                    }
                     p += 4;
                     break;
                 }
@@ -297,6 +307,80 @@ int parse_obj(const char *path, std::vector<SubMeshBox> &out, std::string &error
 }
 
 }  // namespace
+
+// Canonical text of a parsed document (see ovis_json_canonical in orion_vis.h). Numbers are written as the reference
+// consumes them: GetFloat() = (float)double, plus the integer when the double is one.
+static void json_canonical(const Json &v, std::string &out) {
+    char buf[64];
+    switch (v.kind) {
+    case Json::Null: out += 'z'; break;
+    case Json::Bool: out += v.b ? 't' : 'f'; break;
+    case Json::Number: {
+        const float f = (float)v.num;
+        uint32_t bits;
+        memcpy(&bits, &f, 4);
+        snprintf(buf, sizeof buf, "#%08x", bits);
+        out += buf;
+        if (v.num == (double)(long long)v.num && v.num > -9.0e15 && v.num < 9.0e15) {
+            snprintf(buf, sizeof buf, "i%lld", (long long)v.num);
+            out += buf;
+        }
+        break;
+    }
+    case Json::String:
+        out += '"';
+        for (unsigned char c : v.str) {
+            if (c < 0x20 || c == '"' || c == '\\' || c >= 0x7f) {
+                snprintf(buf, sizeof buf, "\\x%02x", c);
+                out += buf;
+            } else {
+                out += (char)c;
+            }
+        }
+        out += '"';
+        break;
+    case Json::Array:
+        out += '[';
+        for (const Json &i : v.items) {
+            json_canonical(i, out);
+            out += ',';
+        }
+        out += ']';
+        break;
+    case Json::Object:
+        out += '{';
+        for (const auto &m : v.members) {
+            Json key;
+            key.kind = Json::String;
+            key.str = m.first;
+            json_canonical(key, out);
+            out += ':';
+            json_canonical(m.second, out);
+            out += ',';
+        }
+        out += '}';
+        break;
+    }
+}
+
+extern "C" int ovis_json_canonical(const char *text, int64_t length, char *out, int64_t capacity, int64_t *out_length) {
+    if (!text || length < 0 || !out_length || capacity < 0 || (capacity > 0 && !out))
+        return scene_error(OVIS_ERR_INVALID, "ovis_json_canonical: bad arguments");
+    JsonParser parser{ text, text + length, {} };
+    Json doc;
+    if (!parser.parse(doc))
+        return scene_error(OVIS_ERR_INVALID, "ovis_json_canonical: %s", parser.error.c_str());
+    parser.skip();
+    if (parser.p != parser.end)
+        return scene_error(OVIS_ERR_INVALID, "ovis_json_canonical: trailing characters after the document");
+    std::string s;
+    json_canonical(doc, s);
+    *out_length = (int64_t)s.size();
+    if ((int64_t)s.size() > capacity)
+        return scene_error(OVIS_ERR_CAPACITY, "ovis_json_canonical: needs %lld bytes", (long long)s.size());
+    memcpy(out, s.data(), s.size());
+    return OVIS_OK;
+}
 
 extern "C" int ovis_obj_submesh_aabbs(const char *obj_path, int32_t capacity, float *out_aabb, int32_t *out_count) {
     if (!obj_path || capacity < 0 || (capacity > 0 && !out_aabb) || !out_count)

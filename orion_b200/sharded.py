@@ -120,10 +120,14 @@ class SharedHostSegments:
             while True:
                 try:
                     self.shm = shared_memory.SharedMemory(name=name, create=False)
-                    if self.shm.size >= 4 * words:
+                    try:                                       # rank 0 owns the name; this process only maps it
+                        from multiprocessing import resource_tracker
+                        resource_tracker.unregister(self.shm._name, "shared_memory")
+                    except Exception:
+                        pass
+                    if self.shm.size >= 4 * words and int(np.frombuffer(self.shm.buf, dtype=np.uint32, count=64)[63]) == 0x600DF00D:
                         self.words = np.frombuffer(self.shm.buf, dtype=np.uint32, count=words)
-                        if int(self.words[63]) == 0x600DF00D:
-                            break
+                        break
                     self.shm.close()
                 except FileNotFoundError:
                     pass
@@ -135,7 +139,9 @@ class SharedHostSegments:
         if self.page_lock:
             _lib.host_register(self.words)
 
-    def _release(self):
+    def _release(self, unlink_after: bool = False):
+        """Unmap the block. Rank 0 owns the name: it unlinks it (the other ranks' mappings stay valid until they close;
+        on a regrow they have all seen the overflowing frame's flags, and none of them touches the old block again)."""
         if self.shm is None:
             return
         try:
@@ -144,13 +150,15 @@ class SharedHostSegments:
         except Exception:
             pass
         self.flags = self.sets = self.words = None
+        shm, self.shm = self.shm, None
         try:
-            self.shm.close()
             if self.rank == 0:
-                self.shm.unlink()
+                shm.unlink()
+            shm.close()
+        except BufferError:
+            pass                                          # a caller still holds a list of an earlier frame: left to the GC
         except Exception:
             pass
-        self.shm = None
 
     def bind(self, world, view):
         """Per-rank frame function: step() -> list of per-rank id arrays (views into the shared block, valid until the
@@ -203,18 +211,12 @@ class SharedHostSegments:
                 if int(counts.max()) <= self.capacity:
                     return [self.sets[k, r, 1:1 + int(counts[r])] for r in range(self.size)]
                 # some shard overflowed: every rank sees that and moves to a larger block, then the frame is redone
-                old = self.shm, self.words
+                need = int(counts.max() * 1.25) + 1024
+                del counts
+                state["culls"] = None                        # (they hold pointers into the old block)
+                self._release(unlink_after=True)
                 self.generation += 1
-                self.shm = None
-                self._open(int(counts.max() * 1.25) + 1024)
-                try:
-                    if self.page_lock:
-                        lib.host_unregister(old[1])
-                    old[0].close()
-                    if self.rank == 0:
-                        old[0].unlink()
-                except Exception:
-                    pass
+                self._open(need)
                 state["culls"] = make_culls()
 
         return step

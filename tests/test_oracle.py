@@ -163,6 +163,17 @@ def test_draw_lists_and_entity_uniforms(port, ref):
             assert np.array_equal(p0, r0) and np.array_equal(p1, r1)
             if mode == 1:
                 assert len(p1) == 0
+    # The reference tier builds real RenderEntity objects and calls the reference's DrawList::add up to 200 000 visible
+    # entities, and falls back to its restated loop beyond: hold both equal to the port.
+    big = 400_000
+    pc = util.random_pass_counts(rng, big)
+    flags = rng.integers(0, 2, big).astype(np.uint32)
+    for m in (150_000, 250_000):
+        visible = np.sort(rng.choice(big, m, replace=False)).astype(np.uint32)
+        for mode in (0, 1):
+            p0, p1 = port.draw_lists(visible, pc, flags, mode)
+            r0, r1 = ref.draw_lists(visible, pc, flags, mode)
+            assert np.array_equal(p0, r0) and np.array_equal(p1, r1)
     trs = util.random_trs(rng, 4000)
     trs[:5, 7:10] = 0.0                                                     # degenerate scale
     trs[5, 3:7] = (1, 0, 0, 0)

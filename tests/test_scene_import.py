@@ -129,13 +129,70 @@ def test_imported_world_on_the_device():
     w.close()
 
 
+CUBES = np.load(os.path.join(HERE, "golden", "cubes_import_golden.npz"))
+
+
+@pytest.mark.skipif(not os.path.isdir(REF_ASSETS), reason="the reference's own worlds are only present where /root/reference is")
+def test_committed_cubes_import_is_what_the_reference_files_hold():
+    """tests/golden/cubes_import_golden.npz (made by make_cubes_import.py) must still be what the loader reads from the
+    reference's files: the device test below rebuilds the worlds from it where the files are absent."""
+    for name in ("main", "shadow_test"):
+        got = lib.load_scene(os.path.join(REF_ASSETS, "worlds", name + ".object"), REF_ASSETS, 1440, 900)
+        for k in KEYS:
+            assert _equal(got[k], CUBES[f"{name}_{k}"]), (name, k)
+
+
+def _json_both(ref, text: bytes):
+    import ctypes as C
+    so = lib.load()
+    n = C.c_int64()
+    buf = C.create_string_buffer(64 + 16 * len(text))
+    rc = so.ovis_json_canonical(text, C.c_int64(len(text)), buf, C.c_int64(len(buf)), C.byref(n))
+    ours = buf.raw[:n.value] if rc == lib.OVIS_OK else None
+    ref.lib.oref_json_canonical.restype = C.c_int64
+    rbuf = C.create_string_buffer(64 + 16 * len(text))
+    m = ref.lib.oref_json_canonical(text, C.c_int64(len(text)), rbuf, C.c_int64(len(rbuf)))
+    theirs = rbuf.raw[:m] if m >= 0 else None
+    return ours, theirs
+
+
+def test_json_layer_against_the_reference_rapidjson(ref):
+    """The loader's own JSON reader against the rapidjson the reference vendors and parses its worlds with
+    (json_serialiser.cc:213-214), on the reference's worlds (where present), the committed fixture and awkward documents:
+    same structure, same strings, same member order, the same float for every number."""
+    files = [FOREST]
+    if os.path.isdir(REF_ASSETS):
+        files += [os.path.join(REF_ASSETS, "worlds", n) for n in ("main.object", "shadow_test.object")]
+    for path in files:
+        text = open(path, "rb").read()
+        ours, theirs = _json_both(ref, text)
+        assert ours is not None and ours == theirs, path
+        assert len(ours) > 100
+    docs = [b'[]', b'{}', b' [ 1 , 2.5e3 , -0.0 , 1e-7 , 0.70710677 , 123456789012 , 1E+2, 3.4028235e38, 5e-324 ] ',
+            rb'{"a": {"b": [true, false, null, {"c": "d"}]}, "a2": "x\\y\"z\/\n\t\u0041\u00e9\u20ac"}',
+            b'[0.1, 0.2, 0.30000000000000004, 16777217, 0.333333333333333314829616256247, 1.17549435e-38, 2.2250738585072014e-308]',
+            b'{"objectClass": "Entity", "objectID": 7, "objectProperties": {"position": [0.4, 7, -7], "active": true}}',
+            b'[-1, -1.5, 10, 1.0e1, 0.5E-1, 9007199254740993]']
+    for d in docs:
+        ours, theirs = _json_both(ref, d)
+        assert ours is not None and ours == theirs, d
+    for bad in (b'[1, 2', b'{"a" 1}', b'[1,]', b'{"a": tru}', b'', b'[1] x'):
+        ours, theirs = _json_both(ref, bad)
+        assert ours is None and theirs is None, bad
+
+
 @pytest.mark.gpu
-@pytest.mark.skipif(not os.path.isdir(REF_ASSETS), reason="needs /root/reference")
-def test_cubes_demo_from_its_own_file_matches_golden_cull():          # pragma: no cover - /root/reference is absent on the GPU box
+def test_cubes_demo_world_on_the_device_matches_golden_cull():
+    """The reference's own main.object, as imported here from its file (cubes_import_golden.npz), rebuilt on the device
+    through the ordinary entry points: bounds and the camera's visible sets must be the tier-A golden ones."""
     g = np.load(os.path.join(HERE, "golden", "visibility_golden.npz"))
+    c = {k: CUBES[f"main_{k}"] for k in KEYS}
     w = lib.World(0)
-    info, cams = w.import_scene(os.path.join(REF_ASSETS, "worlds", "main.object"), REF_ASSETS, 1440, 900)
+    e0 = w.add_entities(c["local_aabb"], c["flags"])
+    n0 = w.add_nodes(c["parent"], c["local_trs"])
+    w.bind_entities(c["entity_node"] + n0, np.arange(e0, e0 + len(c["flags"]), dtype=np.uint32))
+    w.add_lights(c["lights"])
     assert same(w.world_aabbs(), g["cubes_bounds"])
-    ents, ls = w.cull(cams[0])
+    ents, ls = w.cull(c["cameras"][0])
     assert np.array_equal(ents, g["cubes_entities"]) and np.array_equal(ls, g["cubes_lights"])
     w.close()
