@@ -94,6 +94,15 @@ int ovis_world_set_stream(OvisWorld *world, void *cuda_stream);
  * INTO the API stay local. Default 0. */
 int ovis_world_set_id_base(OvisWorld *world, uint32_t id_base);
 int ovis_world_counts(OvisWorld *world, int64_t *n_entities, int64_t *n_nodes, int32_t *n_lights);
+/* Live entities vs entity slots: removed entities keep their slot (ids are stable handles), so a world with spawn /
+ * despawn churn grows, and as long as one slot is dead every cull reads the alive mask. */
+int ovis_world_live_counts(OvisWorld *world, int64_t *out_live_entities, int64_t *out_entity_slots);
+/* Reclaims the dead slots: the live entities move together, IN ORDER (the list order of simple_render_world.cc:38-41 is
+ * insertion order and stays it), and get the ids 0 .. new_slots - 1. out_remap[old id] = new id, or 0xffffffff for a
+ * removed entity (cap_remap >= the old slot count; NULL with cap 0 if the caller keeps no ids). Every id held outside the
+ * library must be translated. The reference's std::list shrinks on remove (simple_render_world.cc:65-67); this is the
+ * same effect, taken when the caller decides (e.g. more than a quarter of the slots dead). O(entities) on the device. */
+int ovis_world_compact(OvisWorld *world, int64_t cap_remap, uint32_t *out_remap, int64_t *out_old_slots, int64_t *out_new_slots);
 
 /* ------------------------------------------------------------------------------------------------
  * Render entities - RenderWorld::addEntity / updateEntity / removeEntity
@@ -138,6 +147,18 @@ int ovis_node_bind_entities(OvisWorld *world, int64_t n, const uint32_t *node_id
 /* Entity::transformed over everything that changed since the last call (entity.cc:382-411), then
  * Transform::matrix + BoundingBox::transform for every affected entity (core/src/math/transform.cc:26-35,
  * core/src/math/bounding_box.cc:27-40, render_entity.cc:90-93). Asynchronous on the world's stream. */
+/* Entity::addChild / re-parenting (engine/src/entity.cc:210-236): `node` becomes a child of `new_parent` (OVIS_NO_PARENT =
+ * a root). A node may not become a descendant of itself. Everything below is recomputed at the next update. */
+int ovis_node_set_parent(OvisWorld *world, uint32_t node, int32_t new_parent);
+/* Entity::destroy (engine/src/entity.cc:58-90): the node and its whole subtree leave the tree, and every render entity
+ * bound to one of them is removed as by ovis_entity_remove (destroying an Entity destroys its components, whose
+ * RenderEntities leave the world: graphics/src/renderer.cc:87-94). Lights bound to a removed node stay where they are and
+ * follow nothing. Node ids are not reused. Cost: O(nodes) on the host. */
+int ovis_node_remove(OvisWorld *world, uint32_t node, int64_t *out_removed_nodes, int64_t *out_removed_entities);
+/* A light follows a node as graphics/src/light.cc:100-108 (Light::transformed) does: after every transform update its
+ * position is the node's world position and its direction the node's world orientation applied to (0, 0, -1).
+ * OVIS_NO_PARENT unbinds. Costs one small device-to-host copy per update while any light is bound. */
+int ovis_light_bind_node(OvisWorld *world, uint32_t light, int32_t node);
 int ovis_update_transforms(OvisWorld *world);
 
 /* ------------------------------------------------------------------------------------------------
@@ -307,6 +328,15 @@ int ovis_cull_shadow_views_device(OvisWorld *world, int32_t n_lights, const uint
                                   int32_t cap_lists, int32_t *out_list_light, int32_t *out_list_view, int32_t *out_n_lists,
                                   const int64_t **d_offsets, const uint32_t **d_entities, int64_t *host_offsets);
 
+/* The same culls with HOST output and a choice of filter, for callers that serve the reference's per-view
+ * RenderWorld::cull(shadowView, results, 0) calls from one batched pass (adapter/cuda_render_world.cc): `require` = 0 keeps
+ * every entity that intersects the view, as SimpleRenderWorld::cull does (the pipeline filters castsShadow() itself,
+ * deferred_render_pipeline.cc:272-283); OVIS_CASTS_SHADOW keeps the casters only. OVIS_ERR_CAPACITY (with *out_n_lists /
+ * *out_n_entities = required) if a buffer is too small. */
+int ovis_cull_shadow_views(OvisWorld *world, int32_t n_lights, const uint32_t *light_ids, int32_t shadow_map_resolution, uint32_t require,
+                           int32_t cap_lists, int32_t *out_list_light, int32_t *out_list_view, int64_t *out_offsets, int32_t *out_n_lists,
+                           int64_t cap_entities, uint32_t *out_entities, int64_t *out_n_entities);
+
 /* DeferredRenderPipeline::prepareLights' cull+filter loop (deferred_render_pipeline.cc:207,247,257-284):
  * for every light not culled by main_view that casts shadows (spot, point), one list per shadow view
  * holding the ids of the castsShadow() entities intersecting it. HOST output:
@@ -359,7 +389,9 @@ int ovis_entity_set_pass_counts(OvisWorld *world, int64_t n, const uint32_t *ids
  * Both NULL = the entity list of this world's last ovis_cull / ovis_cull_planes.
  * Draws beyond a list's capacity are dropped, but d_draw_counts[0..1] (device; NULL = an internal
  * pair, readable through ovis_get_draw_counts) always receive the full draw counts, so a caller can
- * detect the overflow and retry. Never allocates after the world's arrays exist. */
+ * detect the overflow and retry. If the device count turns out larger than max_visible (the bound was wrong) only the
+ * first max_visible entries, rounded up to 1024, are expanded and both counts read 0xffffffff. Never allocates after the
+ * world's arrays exist. */
 int ovis_build_draw_lists_device(OvisWorld *world, const uint32_t *d_visible, const uint32_t *d_visible_count, int64_t max_visible,
                                  int32_t mode, OvisDraw *d_draws0, int64_t capacity0, OvisDraw *d_draws1, int64_t capacity1,
                                  uint32_t *d_draw_counts);
@@ -443,8 +475,8 @@ typedef struct OvisSceneInfo {
  *     the .obj, see ovis_obj_submesh_aabbs) and one per Skybox (+-FLT_MAX, graphics/src/skybox.cc:46-54), bound to the
  *     Entity's node, flags from castsShadow (graphics/src/renderer.cc:70-85);
  *   - one light per Ambient/Directional/Point/SpotLight with the component defaults of graphics/src/light.cc:35-74, world
- *     position and direction from the Entity's world transform at import time (light.cc:100-108; lights do not follow
- *     later node moves - call ovis_light_update), attenuation and shadow bias via ovis_light_set_shading;
+ *     position and direction from the Entity's world transform (light.cc:100-108); the light is bound to the Entity's
+ *     node (ovis_light_bind_node) and follows it from then on; attenuation and shadow bias via ovis_light_set_shading;
  *   - one OvisView per Camera (graphics/src/camera.cc:46-57,71-79) with the given viewport size, returned in
  *     out_cameras (up to cap_cameras; OVIS_ERR_CAPACITY if there are more, the world is still complete).
  * Mesh assets "game/<path>" resolve to <game_asset_dir>/<path>.obj. Physics, controllers and post effects are ignored. */

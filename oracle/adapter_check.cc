@@ -17,6 +17,7 @@
 
 #include "render_core/geometry.h"
 
+#include <chrono>
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
@@ -127,6 +128,35 @@ void compareWorlds(Scene &ref, Scene &gpu, RenderView &view, const char *stage) 
            ra.lights.size(), shadowViews);
 }
 
+/* One frame as DeferredRenderPipeline drives a RenderWorld: the main cull with lights, then one cull per shadow view of
+ * every visible shadow-casting light (deferred_render_pipeline.cc:147, 257-284). Returns the entity-view tests done. */
+size_t frame(Scene &s, RenderView &view, size_t *shadowViews) {
+    RenderWorld::CullResults main;
+    s.world->cull(view, main, RenderWorld::kCullLights);
+    size_t views = 1, listed = main.entities.size();
+    for (RenderLight *l : main.lights) {
+        if (!l->castsShadows() || (l->type() != RenderLight::kPointLight && l->type() != RenderLight::kSpotLight))
+            continue;
+        for (unsigned i = 0; i < l->numShadowViews(); i++) {
+            l->shadowView(i).setViewport(IntRect(0, 0, 512, 512));
+            RenderWorld::CullResults shadow;
+            s.world->cull(l->shadowView(i), shadow, 0);
+            listed += shadow.entities.size();
+            views++;
+        }
+    }
+    *shadowViews = views - 1;
+    return listed;
+}
+
+double timeFrames(Scene &s, RenderView &view, int frames, size_t *shadowViews, size_t *listed) {
+    frame(s, view, shadowViews);                                /* warm-up */
+    const auto t0 = std::chrono::steady_clock::now();
+    for (int f = 0; f < frames; f++)
+        *listed = frame(s, view, shadowViews);
+    return std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now() - t0).count() / frames;
+}
+
 }  // namespace
 
 int main(int argc, char **argv) {
@@ -200,6 +230,28 @@ int main(int argc, char **argv) {
     }
     compareWorlds(ref, gpu, view, "after removals");
 
+    for (size_t k = 0; k < numEntities / 2; k++) {             /* heavy despawn: the adapter reclaims the slots, ids change inside */
+        size_t i = rng() % numEntities;
+        ref.entities[i].reset();
+        gpu.entities[i].reset();
+    }
+    compareWorlds(ref, gpu, view, "after heavy removals");
+    for (size_t i = 0; i < numEntities; i += 7) {              /* ... and spawning goes on afterwards */
+        if (ref.entities[i])
+            continue;
+        Transform t = randomTransform(60.0f);
+        BoundingBox box = randomBox();
+        for (Scene *s : { &ref, &gpu }) {
+            std::unique_ptr<TestEntity> e(new TestEntity);
+            e->index = i;
+            e->setBoundingBox(box);
+            e->setTransform(t);
+            e->setWorld(s->world.get());
+            s->entities[i] = std::move(e);
+        }
+    }
+    compareWorlds(ref, gpu, view, "after respawns");
+
     for (size_t i = 0; i < ref.lights.size(); i += 3) {        /* setters that do NOT notify the world */
         float range = uni(5, 80);
         glm::vec3 col = (i == 6) ? glm::vec3(0.0f) : glm::vec3(1.0f);
@@ -212,6 +264,27 @@ int main(int argc, char **argv) {
     gpu.lights[4].reset();
     view.setTransform(glm::vec3(30, 10, 70), glm::normalize(glm::quat(0.95f, 0.05f, 0.3f, 0.0f)));
     compareWorlds(ref, gpu, view, "after light changes");
+
+    /* The batched shadow-view path must have been the one that answered (and agreed, above). */
+    CudaRenderWorld *cuda = static_cast<CudaRenderWorld *>(gpu.world.get());
+    printf("shadow views served from %zu batched culls: %zu\n", cuda->shadowBatches(), cuda->shadowViewsServed());
+    if (cuda->shadowViewsServed() == 0 || cuda->shadowBatches() == 0) {
+        fprintf(stderr, "the adapter never used the batched shadow-view cull\n");
+        failures++;
+    }
+    /* Frame time through the RenderWorld interface, both worlds, same scene. */
+    {
+        size_t sv = 0, listedRef = 0, listedGpu = 0;
+        const int frames = numEntities > 200000 ? 3 : 20;
+        const double refUs = timeFrames(ref, view, frames, &sv, &listedRef);
+        const double gpuUs = timeFrames(gpu, view, frames, &sv, &listedGpu);
+        printf("FRAME_US entities=%zu shadow_views=%zu listed=%zu reference=%.1f adapter=%.1f speedup=%.2f\n", numEntities, sv, listedRef,
+               refUs, gpuUs, refUs / gpuUs);
+        if (listedRef != listedGpu) {
+            fprintf(stderr, "timed frames disagree: %zu vs %zu listed entities\n", listedRef, listedGpu);
+            failures++;
+        }
+    }
 
     /* Leak the scenes instead of tearing them down one std::list::remove at a time (O(n^2)). */
     for (Scene *s : { &ref, &gpu }) {

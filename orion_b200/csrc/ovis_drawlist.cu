@@ -39,7 +39,8 @@ __device__ __forceinline__ void draw_counts(const DrawArgs &a, uint32_t id, uint
 __global__ void __launch_bounds__(256)
 draw_count_kernel(const __grid_constant__ DrawArgs a) {
     __shared__ uint32_t s0[8], s1[8];
-    const uint32_t m = *a.d_visible_count;
+    // never beyond the host's bound that sized the grid: a longer device list is cut there (and reported: see draw_write_kernel)
+    const uint32_t m = min(*a.d_visible_count, (uint32_t)min((long long)gridDim.x * kDrawTile, (long long)0xffffffffll));
     const int64_t base = (int64_t)blockIdx.x * kDrawTile;
     if (base >= m)
         return;
@@ -74,7 +75,8 @@ draw_write_kernel(const __grid_constant__ DrawArgs a) {
     __shared__ uint32_t s_w0[8], s_w1[8];
     __shared__ uint32_t s_base[2];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const uint32_t m = *a.d_visible_count;
+    // never beyond the host's bound that sized the grid: a longer device list is cut there (and reported: see draw_write_kernel)
+    const uint32_t m = min(*a.d_visible_count, (uint32_t)min((long long)gridDim.x * kDrawTile, (long long)0xffffffffll));
     const int64_t base = (int64_t)blockIdx.x * kDrawTile;
     const int tiles = (int)((m + kDrawTile - 1) / kDrawTile);
     if (base >= m) {
@@ -148,8 +150,11 @@ draw_write_kernel(const __grid_constant__ DrawArgs a) {
             if (pos1 < a.cap1) a.d_draws1[pos1] = make_uint2(ids[k], p);
     }
     if ((int)blockIdx.x == tiles - 1 && tid == 0) {          // the last tile knows the totals
-        a.d_draw_counts[0] = s_base[0] + tile0;
-        a.d_draw_counts[1] = s_base[1] + tile1;
+        // a visible list longer than the caller's bound cannot be expanded completely: say so instead of reporting the
+        // draws of its first part as if they were all (0xffffffff in both counts = "max_visible was too small")
+        const bool cut = *a.d_visible_count > m;
+        a.d_draw_counts[0] = cut ? 0xffffffffu : s_base[0] + tile0;
+        a.d_draw_counts[1] = cut ? 0xffffffffu : s_base[1] + tile1;
     }
 }
 

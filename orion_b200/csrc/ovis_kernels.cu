@@ -57,6 +57,50 @@ __global__ void fill_u32_kernel(uint32_t *dst, int64_t n, uint32_t value) {
 
 static inline unsigned blocks_for(int64_t n, int threads) { return (unsigned)((n + threads - 1) / threads); }
 
+// Stable compaction of per-entity arrays: item i of the new array is item ids[i] of the old one (ids ascending).
+template <int K>
+__global__ void compact_soa_kernel(const float *__restrict__ src, const uint32_t *__restrict__ ids, int64_t n, int64_t stride, float *dst) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n)
+        return;
+    const int64_t from = ids[i];
+#pragma unroll
+    for (int k = 0; k < K; k++)
+        dst[k * stride + i] = src[k * stride + from];
+}
+
+__global__ void compact_u32_kernel(const uint32_t *__restrict__ src, const uint32_t *__restrict__ ids, int64_t n, uint32_t *dst) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n)
+        dst[i] = src[ids[i]];
+}
+
+void launch_compact_soa6(const float *src, const uint32_t *ids, int64_t n, int64_t stride, float *dst, cudaStream_t s) {
+    if (n > 0)
+        compact_soa_kernel<6><<<blocks_for(n, 256), 256, 0, s>>>(src, ids, n, stride, dst);
+}
+
+void launch_compact_u32(const uint32_t *src, const uint32_t *ids, int64_t n, uint32_t *dst, cudaStream_t s) {
+    if (n > 0)
+        compact_u32_kernel<<<blocks_for(n, 256), 256, 0, s>>>(src, ids, n, dst);
+}
+
+// world TRS of a list of nodes, AoS (10 floats each): what lights bound to nodes read back after an update
+__global__ void gather_trs_kernel(const float *__restrict__ src, int64_t stride, const uint32_t *__restrict__ ids, int64_t n, float *dst) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n)
+        return;
+    const int64_t node = ids[i];
+#pragma unroll
+    for (int k = 0; k < 10; k++)
+        dst[i * 10 + k] = src[k * stride + node];
+}
+
+void launch_gather_trs(const float *src, int64_t stride, const uint32_t *ids, int64_t n, float *dst, cudaStream_t s) {
+    if (n > 0)
+        gather_trs_kernel<<<blocks_for(n, 256), 256, 0, s>>>(src, stride, ids, n, dst);
+}
+
 void launch_scatter_aos(int k, const float *src, const uint32_t *ids, uint32_t first, int64_t n, float *dst,
                         int64_t stride, cudaStream_t s) {
     if (n <= 0)

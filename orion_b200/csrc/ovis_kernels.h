@@ -233,6 +233,9 @@ struct LightCullArgs {
 void launch_scatter_aos(int k, const float *src, const uint32_t *ids, uint32_t first, int64_t n, float *dst,
                         int64_t stride, cudaStream_t s);
 void launch_gather_aos(int k, const float *src, int64_t stride, uint32_t first, int64_t n, float *dst, cudaStream_t s);
+void launch_compact_soa6(const float *src, const uint32_t *ids, int64_t n, int64_t stride, float *dst, cudaStream_t s);
+void launch_compact_u32(const uint32_t *src, const uint32_t *ids, int64_t n, uint32_t *dst, cudaStream_t s);
+void launch_gather_trs(const float *src, int64_t stride, const uint32_t *ids, int64_t n, float *dst, cudaStream_t s);
 void launch_scatter_u32(const uint32_t *src, const uint32_t *ids, int64_t n, uint32_t *dst, cudaStream_t s);
 void launch_fill_u32(uint32_t *dst, int64_t n, uint32_t value, cudaStream_t s);
 void launch_identity_bounds(const uint32_t *ids, uint32_t first, int64_t n, const float *local, float *world,

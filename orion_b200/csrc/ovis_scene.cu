@@ -456,6 +456,7 @@ struct Importer {
     std::vector<uint32_t> ent_flags, ent_node;
     std::vector<OvisLight> lights;
     std::vector<float> light_shading;                             // attenuation[3], bias per light
+    std::vector<uint32_t> light_node;                             // the Entity (node) each light component sits on
     std::vector<OvisView> cameras;
     int shadow_map_resolution = 0;
 
@@ -550,6 +551,7 @@ struct Importer {
             lights.push_back(l);
             light_shading.insert(light_shading.end(), att, att + 3);
             light_shading.push_back(prop_float(c, "shadowBiasConstant", -0.001f));
+            light_node.push_back(node);
             return true;
         }
         if (name == "Camera") {                                                              // camera.cc:46-57,71-79
@@ -623,7 +625,7 @@ struct Importer {
 struct OvisScene {
     std::vector<int32_t> node_parent;
     std::vector<float> node_trs, ent_aabb, light_shading;
-    std::vector<uint32_t> ent_flags, ent_node;
+    std::vector<uint32_t> ent_flags, ent_node, light_node;
     std::vector<OvisLight> lights;
     std::vector<OvisView> cameras;
     int shadow_map_resolution = 0;
@@ -678,6 +680,7 @@ int ovis_scene_load(const char *world_path, const char *game_asset_dir, int32_t 
     sc->ent_node = std::move(imp.ent_node);
     sc->lights = std::move(imp.lights);
     sc->light_shading = std::move(imp.light_shading);
+    sc->light_node = std::move(imp.light_node);
     sc->cameras = std::move(imp.cameras);
     sc->shadow_map_resolution = imp.shadow_map_resolution;
     *out_scene = sc;
@@ -755,6 +758,10 @@ int ovis_scene_instantiate(const OvisScene *scene, OvisWorld *world, OvisSceneIn
         for (int32_t i = 0; i < info.n_lights; i++) {
             rc = ovis_light_set_shading(world, info.first_light + (uint32_t)i, &scene->light_shading[4 * (size_t)i],
                                         scene->light_shading[4 * (size_t)i + 3]);
+            if (rc != OVIS_OK)
+                return rc;
+            // Light::transformed (graphics/src/light.cc:100-108): the light goes where its Entity goes
+            rc = ovis_light_bind_node(world, info.first_light + (uint32_t)i, (int32_t)(info.first_node + scene->light_node[(size_t)i]));
             if (rc != OVIS_OK)
                 return rc;
         }

@@ -96,6 +96,10 @@ struct OvisWorld {
     float *d_world_trs = nullptr;         // 10 x cap_nodes
     uint32_t *d_node_entity = nullptr;
     std::vector<int32_t> h_parent, h_level;
+    std::vector<uint8_t> h_node_dead;     // empty until the first ovis_node_remove; a dead node is in no level
+    std::vector<int32_t> light_node;      // per light: the node it follows (ovis_light_bind_node), or OVIS_NO_PARENT
+    int64_t n_bound_lights = 0;
+    bool light_bindings_dirty = false;
     std::vector<uint32_t> h_subtree;      // nodes in the subtree rooted at each node (itself included)
     std::vector<uint32_t> h_node_entity;
     std::vector<uint32_t> h_extra_entity, h_extra_node;   // 2nd.. entity on a node
@@ -241,24 +245,81 @@ int stage(OvisWorld *w, int which, const void *host, size_t bytes, void **out) {
     return OVIS_OK;
 }
 
+// A set of buffers that grow together: every new block is allocated (and filled from the old one) first; only when all of
+// them exist are the old ones released and the pointers swapped, so an out-of-memory half way leaves the world as it was.
+struct GrowSet {
+    struct Item { void **slot; void *fresh; };
+    std::vector<Item> items;
+    cudaStream_t stream;
+    bool failed = false;
+
+    explicit GrowSet(cudaStream_t s) : stream(s) {}
+    template <typename T>
+    void add(T *&ptr, int64_t old_items, int64_t new_items, bool zero_new = true, int fill_byte_new = 0) {
+        if (failed)
+            return;
+        T *fresh = nullptr;
+        if (cudaMalloc(&fresh, sizeof(T) * (size_t)new_items) != cudaSuccess) {
+            cudaGetLastError();
+            failed = true;
+            return;
+        }
+        items.push_back({ reinterpret_cast<void **>(&ptr), fresh });
+        if (zero_new || fill_byte_new)
+            cudaMemsetAsync(fresh, fill_byte_new, sizeof(T) * (size_t)new_items, stream);
+        if (ptr && old_items > 0)
+            cudaMemcpyAsync(fresh, ptr, sizeof(T) * (size_t)old_items, cudaMemcpyDeviceToDevice, stream);
+    }
+    void add_soa(float *&ptr, int comps, int64_t old_cap, int64_t new_cap, int64_t used) {
+        if (failed)
+            return;
+        float *fresh = nullptr;
+        if (cudaMalloc(&fresh, sizeof(float) * (size_t)(comps * new_cap)) != cudaSuccess) {
+            cudaGetLastError();
+            failed = true;
+            return;
+        }
+        items.push_back({ reinterpret_cast<void **>(&ptr), fresh });
+        cudaMemsetAsync(fresh, 0, sizeof(float) * (size_t)(comps * new_cap), stream);
+        if (ptr && used > 0)
+            for (int k = 0; k < comps; k++)
+                cudaMemcpyAsync(fresh + k * new_cap, ptr + k * old_cap, sizeof(float) * (size_t)used, cudaMemcpyDeviceToDevice, stream);
+    }
+    int commit() {
+        cudaError_t err = cudaStreamSynchronize(stream);
+        if (failed || err != cudaSuccess) {
+            for (Item &i : items)
+                cudaFree(i.fresh);
+            return fail(OVIS_ERR_NOMEM, "out of device memory while growing the world (nothing was changed)");
+        }
+        for (Item &i : items) {
+            if (*i.slot)
+                cudaFree(*i.slot);
+            *i.slot = i.fresh;
+        }
+        return OVIS_OK;
+    }
+};
+
 int reserve_entities(OvisWorld *w, int64_t want) {
     if (want <= w->cap_ent)
         return OVIS_OK;
-    int64_t cap = round_up(std::max<int64_t>(want, w->cap_ent + w->cap_ent / 2), kCullTile);
-    OVIS_TRY(grow_soa(w->d_local, 6, w->cap_ent, cap, w->n_ent, w->stream));
-    OVIS_TRY(grow_soa(w->d_world, 6, w->cap_ent, cap, w->n_ent, w->stream));
-    OVIS_TRY(grow(w->d_alive_bits, w->cap_ent / 32, cap / 32, w->stream));
-    OVIS_TRY(grow(w->d_caster_bits, w->cap_ent / 32, cap / 32, w->stream));
-    OVIS_TRY(grow(w->d_pass_counts, w->n_ent, cap, w->stream));
-    OVIS_TRY(grow(w->d_entity_node, w->n_ent, cap, w->stream, false));
-    OVIS_CUDA(cudaMemsetAsync(w->d_entity_node + w->n_ent, 0xff, sizeof(uint32_t) * (size_t)(cap - w->n_ent), w->stream));
-    OVIS_TRY(grow(w->d_draw_totals, 0, 2 * (cap / 1024 + 1), w->stream, false));
+    const int64_t cap = round_up(std::max<int64_t>(want, w->cap_ent + w->cap_ent / 2), kCullTile);
+    const int64_t blocks = cap / ovis::kMaskBlockEntities + 1;
+    GrowSet g(w->stream);
+    g.add_soa(w->d_local, 6, w->cap_ent, cap, w->n_ent);
+    g.add_soa(w->d_world, 6, w->cap_ent, cap, w->n_ent);
+    g.add(w->d_alive_bits, w->cap_ent / 32, cap / 32);
+    g.add(w->d_caster_bits, w->cap_ent / 32, cap / 32);
+    g.add(w->d_pass_counts, w->n_ent, cap);
+    g.add(w->d_entity_node, w->n_ent, cap, false, 0xff);           // kNone everywhere, then the old values
+    g.add(w->d_draw_totals, 0, 2 * (cap / 1024 + 1), false);
     if (!w->d_draw_counts)
-        OVIS_TRY(grow(w->d_draw_counts, 0, 2, w->stream));
-    OVIS_TRY(grow(w->d_result, 0, cap, w->stream, false));
-    OVIS_TRY(grow(w->d_survivors, 0, 2 * (cap / 32), w->stream, false));
-    int64_t blocks = cap / ovis::kMaskBlockEntities + 1;
-    OVIS_TRY(grow(w->d_block_totals, 0, 3 * blocks, w->stream));   // all sets start zeroed
+        g.add(w->d_draw_counts, 0, 2);
+    g.add(w->d_result, 0, cap, false);
+    g.add(w->d_survivors, 0, 2 * (cap / 32), false);
+    g.add(w->d_block_totals, 0, 3 * blocks);                         // all sets start zeroed
+    OVIS_TRY(g.commit());
     w->cap_blocks = blocks;
     w->cull_serial = 0;
     w->cap_ent = cap;
@@ -337,6 +398,8 @@ int add_nodes(OvisWorld *w, int64_t n, const int32_t *parent, const float *local
     w->h_level.resize((size_t)(first + n));
     w->h_node_entity.resize((size_t)(first + n), kNone);
     w->h_subtree.resize((size_t)(first + n), 1u);
+    if (!w->h_node_dead.empty())
+        w->h_node_dead.resize((size_t)(first + n), 0);
     for (int64_t i = 0; i < n; i++) {
         int32_t p = parent[i];
         w->h_parent[(size_t)(first + i)] = p;
@@ -368,12 +431,16 @@ int add_nodes(OvisWorld *w, int64_t n, const int32_t *parent, const float *local
 int rebuild_levels(OvisWorld *w) {
     if (!w->levels_dirty)
         return OVIS_OK;
+    auto dead = [&](int64_t i) { return !w->h_node_dead.empty() && w->h_node_dead[(size_t)i] != 0; };
     int32_t depth = 0;
     for (int64_t i = 0; i < w->n_nodes; i++)
-        depth = std::max(depth, w->h_level[(size_t)i] + 1);
+        if (!dead(i))
+            depth = std::max(depth, w->h_level[(size_t)i] + 1);
     w->levels.assign((size_t)depth, Level());
     std::vector<int64_t> last((size_t)depth, -1);
     for (int64_t i = 0; i < w->n_nodes; i++) {
+        if (dead(i))
+            continue;
         Level &l = w->levels[(size_t)w->h_level[(size_t)i]];
         if (l.count == 0)
             l.first = i;
@@ -395,6 +462,8 @@ int rebuild_levels(OvisWorld *w) {
         for (int32_t d = 0; d < depth; d++)
             cursor[(size_t)d] = w->levels[(size_t)d].list_offset;
         for (int64_t i = 0; i < w->n_nodes; i++) {
+            if (dead(i))
+                continue;
             int32_t d = w->h_level[(size_t)i];
             if (!w->levels[(size_t)d].contiguous)
                 lists[(size_t)cursor[(size_t)d]++] = (uint32_t)i;
@@ -411,9 +480,60 @@ int rebuild_levels(OvisWorld *w) {
     return OVIS_OK;
 }
 
+void mark_lights(OvisWorld *w, int64_t lo, int64_t hi);
+
+// Lights bound to nodes (ovis_light_bind_node) take their position and direction from the node's world transform, as
+// Light::transformed does (graphics/src/light.cc:100-108): position = worldPosition, direction = worldOrientation *
+// (0, 0, -1). Lights are host-side state (their planes, cone boxes and uniform blocks are host math), so the bound
+// nodes' world TRS comes back in one small copy after the tree update.
+int follow_nodes(OvisWorld *w) {
+    w->light_bindings_dirty = false;
+    if (w->n_bound_lights == 0)
+        return OVIS_OK;
+    std::vector<uint32_t> nodes, lights;
+    for (size_t i = 0; i < w->light_node.size(); i++)
+        if (w->light_node[i] >= 0 && w->light_alive[i]) {
+            nodes.push_back((uint32_t)w->light_node[i]);
+            lights.push_back((uint32_t)i);
+        }
+    if (nodes.empty())
+        return OVIS_OK;
+    const size_t n = nodes.size();
+    void *d_ids = nullptr;
+    OVIS_TRY(stage(w, 1, nodes.data(), sizeof(uint32_t) * n, &d_ids));
+    if (w->stage_bytes[0] < sizeof(float) * 10 * n) {
+        if (w->d_stage[0]) {
+            OVIS_CUDA(cudaStreamSynchronize(w->stream));
+            OVIS_CUDA(cudaFree(w->d_stage[0]));
+            w->d_stage[0] = nullptr;
+            w->stage_bytes[0] = 0;
+        }
+        size_t want = std::max(sizeof(float) * 10 * n, (size_t)1 << 20);
+        OVIS_CUDA(cudaMalloc(&w->d_stage[0], want));
+        w->stage_bytes[0] = want;
+    }
+    ovis::launch_gather_trs(w->d_world_trs, w->cap_nodes, (const uint32_t *)d_ids, (int64_t)n, (float *)w->d_stage[0], w->stream);
+    w->launches++;
+    std::vector<float> trs(10 * n);
+    OVIS_CUDA(cudaMemcpyAsync(trs.data(), w->d_stage[0], sizeof(float) * 10 * n, cudaMemcpyDeviceToHost, w->stream));
+    OVIS_CUDA(cudaStreamSynchronize(w->stream));
+    for (size_t k = 0; k < n; k++) {
+        const float *t = trs.data() + 10 * k;
+        OvisLight &l = w->lights[lights[k]];
+        const ovis::hm::Vec3 d = ovis::hm::rotate(ovis::hm::Quat{ t[3], t[4], t[5], t[6] }, ovis::hm::Vec3{ 0.0f, 0.0f, -1.0f });
+        const float pos[3] = { t[0], t[1], t[2] }, dir[3] = { d.x, d.y, d.z };
+        if (std::memcmp(l.position, pos, sizeof pos) != 0 || std::memcmp(l.direction, dir, sizeof dir) != 0) {
+            std::memcpy(l.position, pos, sizeof pos);
+            std::memcpy(l.direction, dir, sizeof dir);
+            mark_lights(w, lights[k], (int64_t)lights[k] + 1);
+        }
+    }
+    return OVIS_OK;
+}
+
 int flush_transforms(OvisWorld *w) {
     if (!w->transforms_dirty)
-        return OVIS_OK;
+        return w->light_bindings_dirty ? follow_nodes(w) : OVIS_OK;
     OVIS_TRY(rebuild_levels(w));
     if (w->extra_dirty) {
         int64_t n = (int64_t)w->h_extra_entity.size();
@@ -457,7 +577,7 @@ int flush_transforms(OvisWorld *w) {
     w->marks_present = false;
     w->all_dirty = false;
     w->transforms_dirty = false;
-    return OVIS_OK;
+    return follow_nodes(w);
 }
 
 int bind_entities(OvisWorld *w, int64_t n, const uint32_t *nodes, const uint32_t *entities) {
@@ -1036,7 +1156,8 @@ int cull_views_grouped(OvisWorld *w, int32_t n_views, const float *planes, const
 // Shadow views (render_light.cc:258-332) of the given lights, culled for shadow casters (deferred_render_pipeline.cc:
 // 270-283) with K4; only spot and point lights have any (allocateShadowMap is fatal for the rest, :291-303).
 int shadow_views_device(OvisWorld *w, const std::vector<uint32_t> &light_ids, int32_t shadow_map_resolution,
-                        std::vector<int32_t> &list_light, std::vector<int32_t> &list_view, std::vector<long long> &offsets) {
+                        std::vector<int32_t> &list_light, std::vector<int32_t> &list_view, std::vector<long long> &offsets,
+                        uint32_t require_mask = OVIS_CASTS_SHADOW) {
     std::vector<float> planes;
     std::vector<HostGroup> groups;
     list_light.clear();
@@ -1058,7 +1179,7 @@ int shadow_views_device(OvisWorld *w, const std::vector<uint32_t> &light_ids, in
         }
     }
     int32_t n_lists = (int32_t)list_light.size();
-    std::vector<uint32_t> require((size_t)n_lists, OVIS_CASTS_SHADOW);
+    std::vector<uint32_t> require((size_t)n_lists, require_mask);
     return cull_views_grouped(w, n_lists, planes.data(), require.data(), groups, nullptr, offsets);
 }
 
@@ -1479,6 +1600,206 @@ int ovis_update_transforms(OvisWorld *w) {
     return flush_transforms(w);
 }
 
+int ovis_node_set_parent(OvisWorld *w, uint32_t node, int32_t new_parent) {
+    if (!w || (int64_t)node >= w->n_nodes || (new_parent != OVIS_NO_PARENT && (new_parent < 0 || (int64_t)new_parent >= w->n_nodes)))
+        return fail(OVIS_ERR_INVALID, "ovis_node_set_parent: unknown node");
+    auto dead = [&](int64_t i) { return !w->h_node_dead.empty() && w->h_node_dead[(size_t)i] != 0; };
+    if (dead(node) || (new_parent >= 0 && dead(new_parent)))
+        return fail(OVIS_ERR_INVALID, "ovis_node_set_parent: the node was removed");
+    for (int32_t a = new_parent; a >= 0; a = w->h_parent[(size_t)a])     // Entity::addChild cannot create a cycle either
+        if ((uint32_t)a == node)
+            return fail(OVIS_ERR_INVALID, "ovis_node_set_parent: node %u is an ancestor of node %d", node, new_parent);
+    OVIS_TRY(use_device(w));
+    // the subtree-size estimates (they only steer the all-or-dirty choice of an update): move this subtree's share
+    const uint32_t moved = w->h_subtree[node];
+    int hops = 0;
+    for (int32_t a = w->h_parent[node]; a >= 0 && hops < 64; a = w->h_parent[(size_t)a], hops++)
+        w->h_subtree[(size_t)a] -= std::min(w->h_subtree[(size_t)a] - 1u, moved);
+    hops = 0;
+    for (int32_t a = new_parent; a >= 0 && hops < 64; a = w->h_parent[(size_t)a], hops++)
+        w->h_subtree[(size_t)a] += moved;
+    w->h_parent[node] = new_parent;
+    OVIS_CUDA(cudaMemcpyAsync(w->d_parent + node, &w->h_parent[node], sizeof(int32_t), cudaMemcpyHostToDevice, w->stream));
+    OVIS_CUDA(cudaStreamSynchronize(w->stream));
+    // levels of every node again: after re-parenting a parent may have a larger id than its child, so walk up with a memo
+    std::vector<int32_t> &level = w->h_level;
+    std::fill(level.begin(), level.end(), -1);
+    std::vector<int32_t> path;
+    for (int64_t i = 0; i < w->n_nodes; i++) {
+        int32_t a = (int32_t)i;
+        path.clear();
+        while (a >= 0 && level[(size_t)a] < 0) {
+            path.push_back(a);
+            a = w->h_parent[(size_t)a];
+        }
+        int32_t l = a >= 0 ? level[(size_t)a] : -1;
+        for (size_t k = path.size(); k-- > 0;)
+            level[(size_t)path[k]] = ++l;
+    }
+    w->levels_dirty = true;
+    w->transforms_dirty = true;
+    w->all_dirty = true;
+    return OVIS_OK;
+}
+
+int ovis_node_remove(OvisWorld *w, uint32_t node, int64_t *out_removed_nodes, int64_t *out_removed_entities) {
+    if (!w || (int64_t)node >= w->n_nodes)
+        return fail(OVIS_ERR_INVALID, "ovis_node_remove: unknown node");
+    if (w->h_node_dead.empty())
+        w->h_node_dead.assign((size_t)w->n_nodes, 0);
+    w->h_node_dead.resize((size_t)w->n_nodes, 0);
+    if (w->h_node_dead[node])
+        return fail(OVIS_ERR_INVALID, "ovis_node_remove: node %u was removed already", node);
+    // Entity::destroy (engine/src/entity.cc:58-90) takes the whole subtree and every component with it
+    w->h_node_dead[node] = 1;
+    int64_t removed = 1;
+    for (bool again = true; again;) {                       // to a fixed point: two passes when parents precede their children
+        again = false;
+        for (int64_t i = 0; i < w->n_nodes; i++) {
+            const int32_t p = w->h_parent[(size_t)i];
+            if (!w->h_node_dead[(size_t)i] && p >= 0 && w->h_node_dead[(size_t)p]) {
+                w->h_node_dead[(size_t)i] = 1;
+                removed++;
+                again = true;
+            }
+        }
+    }
+    std::vector<uint32_t> gone;
+    for (int64_t e = 0; e < w->n_ent; e++) {
+        const uint32_t n = w->h_entity_node[(size_t)e];
+        if (n != kNone && w->h_node_dead[n] && ((w->h_alive[(size_t)e >> 5] >> (e & 31)) & 1u))
+            gone.push_back((uint32_t)e);
+    }
+    if (!gone.empty())
+        OVIS_TRY(ovis_entity_remove(w, (int64_t)gone.size(), gone.data()));
+    for (size_t l = 0; l < w->light_node.size(); l++)
+        if (w->light_node[l] >= 0 && w->h_node_dead[(size_t)w->light_node[l]]) {
+            w->light_node[l] = OVIS_NO_PARENT;                // the light stays where the node left it
+            w->n_bound_lights--;
+        }
+    w->levels_dirty = true;
+    w->transforms_dirty = true;
+    if (out_removed_nodes) *out_removed_nodes = removed;
+    if (out_removed_entities) *out_removed_entities = (int64_t)gone.size();
+    return OVIS_OK;
+}
+
+int ovis_world_live_counts(OvisWorld *w, int64_t *out_live_entities, int64_t *out_entity_slots) {
+    if (!w)
+        return fail(OVIS_ERR_INVALID, "world is null");
+    if (out_live_entities) *out_live_entities = w->n_live;
+    if (out_entity_slots) *out_entity_slots = w->n_ent;
+    return OVIS_OK;
+}
+
+int ovis_world_compact(OvisWorld *w, int64_t cap_remap, uint32_t *out_remap, int64_t *out_old_slots, int64_t *out_new_slots) {
+    if (!w || cap_remap < 0 || (cap_remap > 0 && !out_remap))
+        return fail(OVIS_ERR_INVALID, "ovis_world_compact: bad arguments");
+    const int64_t n_old = w->n_ent;
+    if (out_old_slots) *out_old_slots = n_old;
+    if (out_remap && cap_remap < n_old)
+        return fail(OVIS_ERR_CAPACITY, "ovis_world_compact: the remap needs %lld entries", (long long)n_old);
+    OVIS_TRY(use_device(w));
+    OVIS_TRY(flush_transforms(w));
+    std::vector<uint32_t> keep;                              // old ids of the live entities, ascending: order is preserved
+    keep.reserve((size_t)w->n_live);
+    for (int64_t e = 0; e < n_old; e++)
+        if ((w->h_alive[(size_t)e >> 5] >> (e & 31)) & 1u)
+            keep.push_back((uint32_t)e);
+    const int64_t n_new = (int64_t)keep.size();
+    if (out_new_slots) *out_new_slots = n_new;
+    if (out_remap) {
+        std::fill(out_remap, out_remap + n_old, kNone);
+        for (int64_t i = 0; i < n_new; i++)
+            out_remap[keep[(size_t)i]] = (uint32_t)i;
+    }
+    if (n_new == n_old) {
+        w->any_dead = false;
+        return OVIS_OK;
+    }
+    // ---- device: fresh arrays of the same capacity, filled by stable gathers, swapped in together
+    float *local = nullptr, *world = nullptr;
+    uint32_t *passes = nullptr, *ent_node = nullptr, *d_keep = nullptr;
+    const size_t soa = sizeof(float) * 6 * (size_t)w->cap_ent;
+    auto release = [&]() { cudaFree(local); cudaFree(world); cudaFree(passes); cudaFree(ent_node); cudaFree(d_keep); };
+    if (cudaMalloc(&local, soa) != cudaSuccess || cudaMalloc(&world, soa) != cudaSuccess ||
+        cudaMalloc(&passes, sizeof(uint32_t) * (size_t)w->cap_ent) != cudaSuccess ||
+        cudaMalloc(&ent_node, sizeof(uint32_t) * (size_t)w->cap_ent) != cudaSuccess ||
+        cudaMalloc(&d_keep, sizeof(uint32_t) * (size_t)std::max<int64_t>(n_new, 1)) != cudaSuccess) {
+        cudaGetLastError();
+        release();
+        return fail(OVIS_ERR_NOMEM, "ovis_world_compact: out of device memory (nothing was changed)");
+    }
+    OVIS_CUDA(cudaMemsetAsync(local, 0, soa, w->stream));
+    OVIS_CUDA(cudaMemsetAsync(world, 0, soa, w->stream));
+    OVIS_CUDA(cudaMemsetAsync(passes, 0, sizeof(uint32_t) * (size_t)w->cap_ent, w->stream));
+    OVIS_CUDA(cudaMemsetAsync(ent_node, 0xff, sizeof(uint32_t) * (size_t)w->cap_ent, w->stream));
+    OVIS_CUDA(cudaMemcpyAsync(d_keep, keep.data(), sizeof(uint32_t) * (size_t)n_new, cudaMemcpyHostToDevice, w->stream));
+    ovis::launch_compact_soa6(w->d_local, d_keep, n_new, w->cap_ent, local, w->stream);
+    ovis::launch_compact_soa6(w->d_world, d_keep, n_new, w->cap_ent, world, w->stream);
+    ovis::launch_compact_u32(w->d_pass_counts, d_keep, n_new, passes, w->stream);
+    ovis::launch_compact_u32(w->d_entity_node, d_keep, n_new, ent_node, w->stream);
+    w->launches += 4;
+    OVIS_CUDA(cudaGetLastError());
+    OVIS_CUDA(cudaStreamSynchronize(w->stream));
+    cudaFree(w->d_local); cudaFree(w->d_world); cudaFree(w->d_pass_counts); cudaFree(w->d_entity_node); cudaFree(d_keep);
+    w->d_local = local; w->d_world = world; w->d_pass_counts = passes; w->d_entity_node = ent_node;
+    // ---- host mirrors
+    std::vector<uint32_t> node_of((size_t)n_new), caster((size_t)(w->cap_ent / 32), 0u);
+    for (int64_t i = 0; i < n_new; i++) {
+        const uint32_t e = keep[(size_t)i];
+        node_of[(size_t)i] = w->h_entity_node[e];
+        if ((w->h_caster_raw[e >> 5] >> (e & 31)) & 1u)
+            caster[(size_t)i >> 5] |= 1u << (i & 31);
+    }
+    w->h_entity_node = node_of;
+    w->h_caster_raw = caster;
+    std::fill(w->h_alive.begin(), w->h_alive.end(), 0u);
+    for (int64_t i = 0; i < n_new; i++)
+        w->h_alive[(size_t)i >> 5] |= 1u << (i & 31);
+    w->n_ent = n_new;
+    w->n_live = n_new;
+    w->any_dead = false;
+    mark_masks(w, 0, std::max<int64_t>(n_old, 1) - 1);
+    // ---- which entity a node carries: first bound entity per node in id order, the rest as (entity, node) pairs
+    if (w->n_nodes > 0) {
+        std::fill(w->h_node_entity.begin(), w->h_node_entity.end(), kNone);
+        w->h_extra_entity.clear();
+        w->h_extra_node.clear();
+        for (int64_t i = 0; i < n_new; i++) {
+            const uint32_t n = w->h_entity_node[(size_t)i];
+            if (n == kNone)
+                continue;
+            if (w->h_node_entity[n] == kNone) {
+                w->h_node_entity[n] = (uint32_t)i;
+            } else {
+                w->h_extra_entity.push_back((uint32_t)i);
+                w->h_extra_node.push_back(n);
+            }
+        }
+        OVIS_CUDA(cudaMemcpyAsync(w->d_node_entity, w->h_node_entity.data(), sizeof(uint32_t) * (size_t)w->n_nodes, cudaMemcpyHostToDevice, w->stream));
+        OVIS_CUDA(cudaStreamSynchronize(w->stream));
+        w->extra_dirty = true;
+    }
+    w->last_visible = 0;                                     // the device result list holds old ids
+    return OVIS_OK;
+}
+
+int ovis_light_bind_node(OvisWorld *w, uint32_t light, int32_t node) {
+    if (!w || light >= w->lights.size() || !w->light_alive[light])
+        return fail(OVIS_ERR_INVALID, "ovis_light_bind_node: unknown light %u", light);
+    if (node != OVIS_NO_PARENT && (node < 0 || (int64_t)node >= w->n_nodes || (!w->h_node_dead.empty() && w->h_node_dead[(size_t)node])))
+        return fail(OVIS_ERR_INVALID, "ovis_light_bind_node: unknown node %d", node);
+    w->light_node.resize(w->lights.size(), OVIS_NO_PARENT);
+    if (w->light_node[light] >= 0)
+        w->n_bound_lights--;
+    w->light_node[light] = node;
+    if (node >= 0)
+        w->n_bound_lights++;
+    w->light_bindings_dirty = true;
+    return OVIS_OK;
+}
+
 // ---- lights ------------------------------------------------------------------------------------
 
 int ovis_light_add(OvisWorld *w, int32_t n, const OvisLight *lights, uint32_t *out_first_id) {
@@ -1543,6 +1864,10 @@ int ovis_light_remove(OvisWorld *w, uint32_t id) {
     if (!w || id >= w->lights.size() || !w->light_alive[id])
         return fail(OVIS_ERR_INVALID, "ovis_light_remove: unknown light %u", id);
     w->light_alive[id] = 0;
+    if (id < w->light_node.size() && w->light_node[id] >= 0) {
+        w->light_node[id] = OVIS_NO_PARENT;
+        w->n_bound_lights--;
+    }
     mark_lights(w, id, (int64_t)id + 1);
     return OVIS_OK;
 }
@@ -1835,6 +2160,41 @@ int ovis_cull_shadow_views_device(OvisWorld *w, int32_t n_lights, const uint32_t
     return OVIS_OK;
 }
 
+int ovis_cull_shadow_views(OvisWorld *w, int32_t n_lights, const uint32_t *light_ids, int32_t shadow_map_resolution, uint32_t require,
+                           int32_t cap_lists, int32_t *out_list_light, int32_t *out_list_view, int64_t *out_offsets, int32_t *out_n_lists,
+                           int64_t cap_entities, uint32_t *out_entities, int64_t *out_n_entities) {
+    if (!w || n_lights < 0 || (n_lights > 0 && !light_ids) || !out_n_lists || !out_n_entities || shadow_map_resolution <= 0 ||
+        (require & ~(uint32_t)OVIS_CASTS_SHADOW))
+        return fail(OVIS_ERR_INVALID, "ovis_cull_shadow_views: bad arguments");
+    OVIS_TRY(use_device(w));
+    std::vector<uint32_t> ids(light_ids, light_ids + n_lights);
+    for (uint32_t id : ids)
+        if (id >= w->lights.size() || !w->light_alive[id])
+            return fail(OVIS_ERR_INVALID, "ovis_cull_shadow_views: unknown light %u", id);
+    std::vector<int32_t> list_light, list_view;
+    std::vector<long long> offsets;
+    OVIS_TRY(shadow_views_device(w, ids, shadow_map_resolution, list_light, list_view, offsets, require));
+    const int32_t n_lists = (int32_t)list_light.size();
+    const int64_t total = offsets.empty() ? 0 : offsets[(size_t)n_lists];
+    *out_n_lists = n_lists;
+    *out_n_entities = total;
+    if (n_lists > cap_lists || total > cap_entities)
+        return fail(OVIS_ERR_CAPACITY, "shadow views need %d lists / %lld entities", n_lists, (long long)total);
+    if ((n_lists > 0 && (!out_list_light || !out_list_view)) || !out_offsets || (total > 0 && !out_entities))
+        return fail(OVIS_ERR_INVALID, "ovis_cull_shadow_views: null output");
+    for (int32_t k = 0; k < n_lists; k++) {
+        out_list_light[k] = list_light[(size_t)k];
+        out_list_view[k] = list_view[(size_t)k];
+    }
+    for (int32_t k = 0; k <= n_lists; k++)
+        out_offsets[k] = offsets.empty() ? 0 : offsets[(size_t)k];
+    if (total > 0) {
+        OVIS_CUDA(cudaMemcpyAsync(out_entities, w->d_csr_entities, 4 * (size_t)total, cudaMemcpyDeviceToHost, w->stream));
+        OVIS_CUDA(cudaStreamSynchronize(w->stream));
+    }
+    return OVIS_OK;
+}
+
 int ovis_build_shadow_lists(OvisWorld *w, const OvisView *main_view, int32_t shadow_map_resolution,
                             int32_t cap_lists, int32_t *out_list_light, int32_t *out_list_view,
                             int64_t *out_offsets, int32_t *out_n_lists,
@@ -1849,6 +2209,7 @@ int ovis_build_shadow_lists(OvisWorld *w, const OvisView *main_view, int32_t sha
     OVIS_TRY(enqueue_light_cull(w, main_planes));
     OVIS_CUDA(cudaMemcpyAsync(w->h_counts + 1, w->d_counts + 1, sizeof(uint32_t), cudaMemcpyDeviceToHost, w->stream));
     OVIS_CUDA(cudaStreamSynchronize(w->stream));
+    w->last_visible_lights = w->h_counts[1];          // the device light list is now this view's (pack / shade read it)
     std::vector<uint32_t> visible(w->h_counts[1]);
     if (!visible.empty()) {
         OVIS_CUDA(cudaMemcpyAsync(visible.data(), w->d_light_out, 4 * visible.size(), cudaMemcpyDeviceToHost, w->stream));

@@ -664,3 +664,36 @@ class ShardedWorld:
         _check(self.lib.ovis_sharded_allgather_device(self.h, _p(planes), C.c_uint32(require), C.c_int64(capacity),
                                                       C.byref(blocks), _p(counts)))
         return [blocks[d] for d in range(self.n)], counts
+
+
+def _world_extra_methods():
+    def compact(self):
+        """ovis_world_compact -> remap (old id -> new id, 0xffffffff = removed)."""
+        live, slots = C.c_int64(), C.c_int64()
+        _check(self.lib.ovis_world_live_counts(self.h, C.byref(live), C.byref(slots)))
+        remap = np.empty(max(slots.value, 1), dtype=np.uint32)
+        old, new = C.c_int64(), C.c_int64()
+        _check(self.lib.ovis_world_compact(self.h, C.c_int64(len(remap)), _p(remap), C.byref(old), C.byref(new)))
+        return remap[:old.value], new.value
+
+    def live_counts(self):
+        live, slots = C.c_int64(), C.c_int64()
+        _check(self.lib.ovis_world_live_counts(self.h, C.byref(live), C.byref(slots)))
+        return live.value, slots.value
+
+    def set_node_parent(self, node: int, parent: int):
+        _check(self.lib.ovis_node_set_parent(self.h, C.c_uint32(node), C.c_int32(parent)))
+
+    def remove_node(self, node: int):
+        a, b = C.c_int64(), C.c_int64()
+        _check(self.lib.ovis_node_remove(self.h, C.c_uint32(node), C.byref(a), C.byref(b)))
+        return a.value, b.value
+
+    def bind_light_to_node(self, light: int, node: int):
+        _check(self.lib.ovis_light_bind_node(self.h, C.c_uint32(light), C.c_int32(node)))
+
+    for f in (compact, live_counts, set_node_parent, remove_node, bind_light_to_node):
+        setattr(World, f.__name__, f)
+
+
+_world_extra_methods()

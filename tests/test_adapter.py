@@ -42,4 +42,4 @@ def test_cuda_render_world_equals_simple_render_world():
     r = subprocess.run([CHECK, "30000"], capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, (r.stdout + r.stderr)[-3000:]
     assert "ADAPTER OK" in r.stdout
-    assert r.stdout.count("compared") == 5
+    assert r.stdout.count("compared") == 7

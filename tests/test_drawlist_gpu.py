@@ -265,3 +265,36 @@ def test_light_and_view_uniform_blocks(oracle):
     assert got.tobytes() == want.tobytes()
     assert util.gpu_view_uniforms(w, views[:2]).tobytes() == np.stack([oracle.view_uniforms(v) for v in views[:2]]).tobytes()
     w.close()
+
+
+def test_draw_lists_with_an_undersized_bound_say_so(oracle):
+    """max_visible sizes the grids; when the device count is larger than the caller promised the lists cannot be
+    complete, and the counts must say that (0xffffffff) instead of passing the first part off as the whole."""
+    import torch
+    rng = np.random.default_rng(77)
+    n = 20_000
+    boxes = util.random_boxes(rng, n, extent=50.0)
+    w = lib.World(0)
+    first = w.add_entities(boxes, np.ones(n, dtype=np.uint32))
+    w.set_world_aabbs(first, boxes)
+    pc = util.random_pass_counts(rng, n)
+    w.set_pass_counts(np.arange(n, dtype=np.uint32), pc & 0xff, (pc >> 8) & 0xff, (pc >> 16) & 0xff)
+    visible = np.arange(0, n, 2, dtype=np.uint32)                          # 10 000 entries
+    vis = torch.from_numpy(visible.view(np.int32)).cuda()
+    vcnt = torch.tensor([len(visible)], dtype=torch.int32, device="cuda")
+    cap = 8 * n
+    d0 = torch.zeros((cap, 2), dtype=torch.int32, device="cuda")
+    d1 = torch.zeros((cap, 2), dtype=torch.int32, device="cuda")
+    cnt = torch.zeros(2, dtype=torch.int32, device="cuda")
+    for bound, complete in ((len(visible), True), (3000, False), (500, False)):
+        w.build_draw_lists_device(lib.DRAWS_MAIN, d0.data_ptr(), cap, d1.data_ptr(), cap, vis.data_ptr(), vcnt.data_ptr(), bound,
+                                  cnt.data_ptr())
+        torch.cuda.synchronize()
+        c = cnt.cpu().numpy().view(np.uint32)
+        if complete:
+            e0, e1 = oracle.draw_lists(visible, pc, np.ones(n, dtype=np.uint32), 0)
+            assert (int(c[0]), int(c[1])) == (len(e0), len(e1))
+            assert np.array_equal(d0[:len(e0)].cpu().numpy().view(np.uint32), e0)
+        else:
+            assert int(c[0]) == 0xffffffff and int(c[1]) == 0xffffffff
+    w.close()
