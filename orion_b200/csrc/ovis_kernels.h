@@ -228,6 +228,8 @@ struct LightCullArgs {
     int n;
     uint32_t *out;
     uint32_t *d_count;
+    uint32_t *bits;              // scratch: one ballot word per 32 light slots (8 per CTA)
+    uint32_t *counter;           // scratch: CTAs finished, zero between launches
 };
 
 void launch_scatter_aos(int k, const float *src, const uint32_t *ids, uint32_t first, int64_t n, float *dst,

@@ -118,6 +118,11 @@ struct OvisWorld {
     // ---- lights
     std::vector<OvisLight> lights;
     std::vector<uint8_t> light_alive;
+    // Shadow views and their planes are host math with libm calls (render_light.cc:258-332, render_view.cc:102-135,
+    // frustum.cc:27-67): ~150 ns per view. They only change when the light does, so they are kept per light
+    // (4096 lights x 6 faces every frame would otherwise be 4 ms of host time in front of a 1 ms GPU pass).
+    struct LightViews { int resolution = 0, count = 0; float planes[6 * 24]; };
+    std::vector<LightViews> light_views;
     struct LightShading { float attenuation[3]; float shadow_bias; };
     std::vector<LightShading> light_shading;   // what the LightUniforms block needs beyond OvisLight
     float *d_light_uniforms = nullptr;    // 52 floats (208 B) per light slot
@@ -125,6 +130,7 @@ struct OvisWorld {
     int64_t last_visible_lights = 0;      // light count of the previous ovis_cull with OVIS_CULL_LIGHTS
     ovis::DeviceLight *d_lights = nullptr;
     uint32_t *d_light_out = nullptr;
+    uint32_t *d_light_bits = nullptr;     // K5 scratch: visibility bits per 32 lights, and the finished-CTA counter behind them
     int64_t cap_lights = 0;
     bool lights_dirty = false;
     int64_t lights_dirty_lo = 0, lights_dirty_hi = 0;   // light slots changed since the last upload: [lo, hi)
@@ -170,6 +176,16 @@ struct OvisWorld {
     uint2 *d_mv_segments = nullptr;
     int64_t cap_mv_segments = 0;
     bool mv_force_dense = false;          // OVIS_MV_DENSE=1 (testing): cube groups take the dense pass too
+    bool mv_force_sparse = false;         // OVIS_MV_DENSE=0 (testing): ... and never by the size rule
+    // Host outputs of a multi-view call ride in the same round trip as the offsets: the lists change little from frame to
+    // frame, so a little more than the previous total is copied speculatively; only a frame that grew pays a second copy.
+    uint32_t *mv_spec_out = nullptr;
+    int64_t mv_spec_cap = 0, mv_spec_copied = 0, mv_last_total = 0;
+    // The light list of the last host-output cull with lights: ovis_build_shadow_lists of the same view reuses it instead
+    // of culling the lights again and waiting for them (the pipeline culls the main view first: deferred_render_pipeline.cc:147).
+    std::vector<uint32_t> h_visible_lights;
+    float h_light_cull_planes[24] = {};
+    bool light_cull_valid = false;
 
     // ---- optional per-kernel timing of the entity cull (bench / profiling hook)
     bool timing = false;
@@ -187,6 +203,7 @@ using ovis::kCullTile;
 using ovis::kNone;
 
 constexpr int64_t kUploadChunk = 1 << 23;   // items per staged upload
+constexpr int64_t kMvDenseBelowTests = 100000000;   // entity-view tests below which cube groups take the dense pass
 constexpr size_t kMvBitmapOffset = 64;      // bytes: four state words, padding, then the light grid's occupancy bitmap
 constexpr size_t kMvStateBytes = kMvBitmapOffset + sizeof(unsigned long long) * ovis::kMvGridMax * ovis::kMvGridMax;
 
@@ -753,6 +770,9 @@ int enqueue_cull(OvisWorld *w, const float planes[24], uint32_t require, uint32_
 }
 
 void mark_lights(OvisWorld *w, int64_t lo, int64_t hi) {
+    w->light_cull_valid = false;
+    for (int64_t i = std::max<int64_t>(lo, 0); i < hi && i < (int64_t)w->light_views.size(); i++)
+        w->light_views[(size_t)i].resolution = 0;             // the cached shadow views of these lights are stale
     if (!w->lights_dirty) {
         w->lights_dirty_lo = lo;
         w->lights_dirty_hi = hi;
@@ -773,6 +793,7 @@ int upload_lights(OvisWorld *w) {
         int64_t cap = std::max<int64_t>(n, 64);
         OVIS_TRY(grow(w->d_lights, 0, cap, w->stream, false));
         OVIS_TRY(grow(w->d_light_out, 0, cap, w->stream, false));
+        OVIS_TRY(grow(w->d_light_bits, 0, cap / 32 + 16, w->stream));          // ballot words + (last word) the finished-CTA counter
         OVIS_TRY(grow(w->d_light_uniforms, 0, 52 * cap, w->stream, false));
         OVIS_TRY(grow(w->d_light_types, 0, cap, w->stream, false));
         w->cap_lights = cap;
@@ -845,6 +866,8 @@ int enqueue_light_cull(OvisWorld *w, const float planes[24]) {
     a.n = (int)w->lights.size();
     a.out = w->d_light_out;
     a.d_count = w->d_counts + 1;
+    a.bits = w->d_light_bits;
+    a.counter = w->d_light_bits ? w->d_light_bits + (w->cap_lights / 32 + 15) : nullptr;
     ovis::launch_cull_lights(a, w->stream);
     w->launches++;
     OVIS_CUDA(cudaGetLastError());
@@ -989,6 +1012,15 @@ int cull_views_grouped(OvisWorld *w, int32_t n_views, const float *planes, const
         OVIS_CUDA(cudaMalloc(&w->d_mv_heads, sizeof(int32_t) * ovis::kMvGridMax * ovis::kMvGridMax * ovis::kMvGridMax));
     }
     bool force_dense = w->mv_force_dense;
+    // The light grid pays when there are many (entity, view) pairs to avoid. A small world is tested against every view
+    // faster than its entities can be looked up in the grid (20 000 entities x 72 faces: 18 us densely, and only three
+    // blocks of 8192 entities for the sparse pass to spread over the GPU).
+    int64_t cube_views = 0;
+    for (const HostGroup &hg : groups)
+        if (hg.cube)
+            cube_views += hg.n_views;
+    if (!w->mv_force_sparse && (int64_t)w->n_ent * cube_views <= kMvDenseBelowTests)
+        force_dense = true;
 
     for (int attempt = 0;; attempt++) {
         if (attempt == 8)
@@ -1124,6 +1156,12 @@ int cull_views_grouped(OvisWorld *w, int32_t n_views, const float *planes, const
         long long *hr = static_cast<long long *>(w->h_mv_result);
         OVIS_CUDA(cudaMemcpyAsync(hr, w->d_csr_offsets, sizeof(long long) * ((size_t)n_views + 1), cudaMemcpyDeviceToHost, w->stream));
         OVIS_CUDA(cudaMemcpyAsync(hr + n_views + 1, w->d_mv_state, 4 * sizeof(uint32_t), cudaMemcpyDeviceToHost, w->stream));
+        w->mv_spec_copied = 0;
+        if (w->mv_spec_out && w->mv_spec_cap > 0) {
+            const int64_t guess = std::min(std::min(w->mv_spec_cap, w->cap_csr), w->mv_last_total + w->mv_last_total / 4 + 1024);
+            OVIS_CUDA(cudaMemcpyAsync(w->mv_spec_out, w->d_csr_entities, sizeof(uint32_t) * (size_t)guess, cudaMemcpyDeviceToHost, w->stream));
+            w->mv_spec_copied = guess;
+        }
         OVIS_CUDA(cudaStreamSynchronize(w->stream));
         const uint32_t *state = reinterpret_cast<const uint32_t *>(hr + n_views + 1);
         const uint32_t overflow = state[0];
@@ -1145,11 +1183,24 @@ int cull_views_grouped(OvisWorld *w, int32_t n_views, const float *planes, const
         }
         for (int32_t v = 0; v <= n_views; v++)
             host_offsets[(size_t)v] = hr[v];
+        w->mv_last_total = hr[n_views];
         break;
     }
     if (host_offsets_out)
         for (int32_t v = 0; v <= n_views; v++)
             host_offsets_out[v] = host_offsets[(size_t)v];
+    return OVIS_OK;
+}
+
+// The CSR entities of the last cull_views_grouped into a host buffer: whatever the speculative copy did not cover.
+int finish_host_entities(OvisWorld *w, uint32_t *out_entities, int64_t total) {
+    const int64_t have = w->mv_spec_out == out_entities ? std::min(w->mv_spec_copied, total) : 0;
+    w->mv_spec_out = nullptr;
+    if (total > have) {
+        OVIS_CUDA(cudaMemcpyAsync(out_entities + have, w->d_csr_entities + have, sizeof(uint32_t) * (size_t)(total - have),
+                                  cudaMemcpyDeviceToHost, w->stream));
+        OVIS_CUDA(cudaStreamSynchronize(w->stream));
+    }
     return OVIS_OK;
 }
 
@@ -1162,18 +1213,25 @@ int shadow_views_device(OvisWorld *w, const std::vector<uint32_t> &light_ids, in
     std::vector<HostGroup> groups;
     list_light.clear();
     list_view.clear();
+    w->light_views.resize(w->lights.size());
+    planes.reserve(light_ids.size() * 6 * 24);
     for (uint32_t id : light_ids) {
         const OvisLight &l = w->lights[id];
-        OvisView views[6];
-        int count = ovis::hm::shadowViews(l, shadow_map_resolution, views);
-        if (count == 0)
+        OvisWorld::LightViews &lv = w->light_views[id];
+        if (lv.resolution != shadow_map_resolution) {
+            OvisView views[6];
+            lv.count = ovis::hm::shadowViews(l, shadow_map_resolution, views);
+            for (int i = 0; i < lv.count; i++)
+                ovis::hm::viewPlanes(views[i], lv.planes + 24 * i);
+            lv.resolution = shadow_map_resolution;
+        }
+        if (lv.count == 0)
             continue;
         // A point light's six face frusta (fov 90, far = range, apex at the light) only accept boxes that overlap
         // the cube of half-side range + box extent about the light; a spot light's single frustum gets no pre-filter.
-        groups.push_back(make_group(l.type == OVIS_LIGHT_POINT ? l.position : nullptr, l.range, (int)list_light.size(), count));
-        for (int i = 0; i < count; i++) {
-            planes.resize(planes.size() + 24);
-            ovis::hm::viewPlanes(views[i], planes.data() + planes.size() - 24);
+        groups.push_back(make_group(l.type == OVIS_LIGHT_POINT ? l.position : nullptr, l.range, (int)list_light.size(), lv.count));
+        planes.insert(planes.end(), lv.planes, lv.planes + 24 * lv.count);
+        for (int i = 0; i < lv.count; i++) {
             list_light.push_back((int32_t)id);
             list_view.push_back(i);
         }
@@ -1256,8 +1314,10 @@ int ovis_world_create(int device, OvisWorld **out_world) {
         w->block_fence_sys = std::strcmp(v, "sys") == 0;
     if (const char *v = getenv("OVIS_DIRECT_HOST"))
         w->direct_host = atoi(v) != 0;
-    if (const char *v = getenv("OVIS_MV_DENSE"))
+    if (const char *v = getenv("OVIS_MV_DENSE")) {
         w->mv_force_dense = atoi(v) != 0;
+        w->mv_force_sparse = atoi(v) == 0;
+    }
     *out_world = w;
     return OVIS_OK;
 }
@@ -1269,7 +1329,7 @@ int ovis_world_destroy(OvisWorld *w) {
     cudaStreamSynchronize(w->stream);
     void *bufs[] = { w->d_local, w->d_world, w->d_alive_bits, w->d_caster_bits, w->d_parent, w->d_local_trs, w->d_world_trs,
                      w->d_node_entity, w->d_dirty, w->d_light_uniforms, w->d_light_types, w->d_entity_node, w->d_pass_counts, w->d_draw_totals, w->d_draw_counts,
-                     w->d_extra_entity, w->d_extra_node, w->d_level_lists, w->d_lights, w->d_light_out,
+                     w->d_extra_entity, w->d_extra_node, w->d_level_lists, w->d_lights, w->d_light_out, w->d_light_bits,
                      w->d_survivors, w->d_block_totals, w->d_exchange, w->d_mv_stage, w->d_mv_state, w->d_mv_heads, w->d_mv_totals,
                      w->d_mv_masks, w->d_mv_node_group, w->d_mv_node_next, w->d_mv_items, w->d_mv_segments, w->d_result, w->d_counts, w->d_csr_entities, w->d_csr_offsets,
                      w->d_stage[0], w->d_stage[1] };
@@ -2077,6 +2137,7 @@ static int cull_to_host(OvisWorld *w, const float planes[24], uint32_t require, 
     w->last_visible = ne;
     if (with_lights)
         w->last_visible_lights = nl;
+    w->light_cull_valid = false;
     if (out_n_entities) *out_n_entities = ne;
     if (out_n_lights) *out_n_lights = nl;
     if (ne > cap_entities || (ne > 0 && !out_entities))
@@ -2096,6 +2157,11 @@ static int cull_to_host(OvisWorld *w, const float planes[24], uint32_t require, 
     }
     if (again)
         OVIS_CUDA(cudaStreamSynchronize(w->stream));
+    if (with_lights && out_lights) {                       // kept for ovis_build_shadow_lists of the same view
+        w->h_visible_lights.assign(out_lights, out_lights + nl);
+        std::memcpy(w->h_light_cull_planes, planes, sizeof w->h_light_cull_planes);
+        w->light_cull_valid = true;
+    }
     return OVIS_OK;
 }
 
@@ -2173,7 +2239,15 @@ int ovis_cull_shadow_views(OvisWorld *w, int32_t n_lights, const uint32_t *light
             return fail(OVIS_ERR_INVALID, "ovis_cull_shadow_views: unknown light %u", id);
     std::vector<int32_t> list_light, list_view;
     std::vector<long long> offsets;
-    OVIS_TRY(shadow_views_device(w, ids, shadow_map_resolution, list_light, list_view, offsets, require));
+    w->mv_spec_out = out_entities;
+    w->mv_spec_cap = out_entities ? cap_entities : 0;
+    {
+        const int rc = shadow_views_device(w, ids, shadow_map_resolution, list_light, list_view, offsets, require);
+        if (rc != OVIS_OK) {
+            w->mv_spec_out = nullptr;
+            return rc;
+        }
+    }
     const int32_t n_lists = (int32_t)list_light.size();
     const int64_t total = offsets.empty() ? 0 : offsets[(size_t)n_lists];
     *out_n_lists = n_lists;
@@ -2188,11 +2262,7 @@ int ovis_cull_shadow_views(OvisWorld *w, int32_t n_lights, const uint32_t *light
     }
     for (int32_t k = 0; k <= n_lists; k++)
         out_offsets[k] = offsets.empty() ? 0 : offsets[(size_t)k];
-    if (total > 0) {
-        OVIS_CUDA(cudaMemcpyAsync(out_entities, w->d_csr_entities, 4 * (size_t)total, cudaMemcpyDeviceToHost, w->stream));
-        OVIS_CUDA(cudaStreamSynchronize(w->stream));
-    }
-    return OVIS_OK;
+    return finish_host_entities(w, out_entities, total);
 }
 
 int ovis_build_shadow_lists(OvisWorld *w, const OvisView *main_view, int32_t shadow_map_resolution,
@@ -2206,19 +2276,35 @@ int ovis_build_shadow_lists(OvisWorld *w, const OvisView *main_view, int32_t sha
     // 1. lights visible from the main view, in insertion order (deferred_render_pipeline.cc:147,207)
     float main_planes[24];
     ovis::hm::viewPlanes(*main_view, main_planes);
-    OVIS_TRY(enqueue_light_cull(w, main_planes));
-    OVIS_CUDA(cudaMemcpyAsync(w->h_counts + 1, w->d_counts + 1, sizeof(uint32_t), cudaMemcpyDeviceToHost, w->stream));
-    OVIS_CUDA(cudaStreamSynchronize(w->stream));
-    w->last_visible_lights = w->h_counts[1];          // the device light list is now this view's (pack / shade read it)
-    std::vector<uint32_t> visible(w->h_counts[1]);
-    if (!visible.empty()) {
-        OVIS_CUDA(cudaMemcpyAsync(visible.data(), w->d_light_out, 4 * visible.size(), cudaMemcpyDeviceToHost, w->stream));
+    std::vector<uint32_t> visible;
+    if (w->light_cull_valid && !w->lights_dirty && std::memcmp(main_planes, w->h_light_cull_planes, sizeof main_planes) == 0) {
+        visible = w->h_visible_lights;                  // this frame's ovis_cull(main_view, OVIS_CULL_LIGHTS) found them already
+    } else {
+        OVIS_TRY(enqueue_light_cull(w, main_planes));
+        OVIS_CUDA(cudaMemcpyAsync(w->h_counts + 1, w->d_counts + 1, sizeof(uint32_t), cudaMemcpyDeviceToHost, w->stream));
         OVIS_CUDA(cudaStreamSynchronize(w->stream));
+        w->last_visible_lights = w->h_counts[1];      // the device light list is now this view's (pack / shade read it)
+        visible.resize(w->h_counts[1]);
+        if (!visible.empty()) {
+            OVIS_CUDA(cudaMemcpyAsync(visible.data(), w->d_light_out, 4 * visible.size(), cudaMemcpyDeviceToHost, w->stream));
+            OVIS_CUDA(cudaStreamSynchronize(w->stream));
+        }
+        w->h_visible_lights = visible;
+        std::memcpy(w->h_light_cull_planes, main_planes, sizeof main_planes);
+        w->light_cull_valid = true;
     }
     // 2.+3. their shadow views, culled for shadow casters in one multi-view pass set
     std::vector<int32_t> list_light, list_view;
     std::vector<long long> offsets;
-    OVIS_TRY(shadow_views_device(w, visible, shadow_map_resolution, list_light, list_view, offsets));
+    w->mv_spec_out = out_entities;
+    w->mv_spec_cap = out_entities ? cap_entities : 0;
+    {
+        const int rc = shadow_views_device(w, visible, shadow_map_resolution, list_light, list_view, offsets);
+        if (rc != OVIS_OK) {
+            w->mv_spec_out = nullptr;
+            return rc;
+        }
+    }
     int32_t n_lists = (int32_t)list_light.size();
     int64_t total = offsets.empty() ? 0 : offsets[(size_t)n_lists];
     *out_n_lists = n_lists;
@@ -2233,11 +2319,7 @@ int ovis_build_shadow_lists(OvisWorld *w, const OvisView *main_view, int32_t sha
     }
     for (int32_t k = 0; k <= n_lists; k++)
         out_offsets[k] = offsets.empty() ? 0 : offsets[(size_t)k];
-    if (total > 0) {
-        OVIS_CUDA(cudaMemcpyAsync(out_entities, w->d_csr_entities, 4 * (size_t)total, cudaMemcpyDeviceToHost, w->stream));
-        OVIS_CUDA(cudaStreamSynchronize(w->stream));
-    }
-    return OVIS_OK;
+    return finish_host_entities(w, out_entities, total);
 }
 
 // ---- read-back ---------------------------------------------------------------------------------

@@ -266,11 +266,13 @@ def test_multi_view_csr(oracle):
     w.close()
 
 
-def test_shadow_lists_prefilter_is_conservative(oracle):
-    """The cube pre-filter in front of the exact shadow-view tests must never drop a pair the reference keeps:
+def test_shadow_lists_prefilter_is_conservative(oracle, monkeypatch):
+    """(OVIS_MV_DENSE=0: a world this small would otherwise skip the pre-filter and test every view densely.)
+    The cube pre-filter in front of the exact shadow-view tests must never drop a pair the reference keeps:
     giant boxes (the P-vertex test accepts them far outside the cube), skybox / infinite / NaN boxes, inverted
     boxes, boxes hugging cube faces and corners, lights at large coordinates. More than 1024 views forces
     several passes; removed entities and non-casters must stay out."""
+    monkeypatch.setenv("OVIS_MV_DENSE", "0")
     rng = np.random.default_rng(39)
     n = 30_000
     boxes = util.random_boxes(rng, n, extent=300.0, hmax=4.0)

@@ -85,9 +85,11 @@ def test_sparse_and_dense_passes_give_the_reference_lists(oracle, monkeypatch):
     assert np.array_equal(results[0][0], results[1][0]) and np.array_equal(results[0][1], results[1][1])
 
 
-def test_sparse_pass_hands_over_when_a_block_is_too_crowded(oracle):
+def test_sparse_pass_hands_over_when_a_block_is_too_crowded(oracle, monkeypatch):
     """64 lights whose cubes all contain all 20 000 entities: 64 candidate pairs per entity, far beyond what a block's
-    shared-memory pair list holds. The call must notice, rerun those views through the dense pass and still be exact."""
+    shared-memory pair list holds. The call must notice, rerun those views through the dense pass and still be exact.
+    (OVIS_MV_DENSE=0 keeps the size rule from sending so small a world to the dense pass at once.)"""
+    monkeypatch.setenv("OVIS_MV_DENSE", "0")
     rng = np.random.default_rng(502)
     n = 20_000
     boxes = util.random_boxes(rng, n, extent=20.0, hmax=1.0)
@@ -109,6 +111,26 @@ def test_sparse_pass_hands_over_when_a_block_is_too_crowded(oracle):
     for k, exp in enumerate(_expected_lists(oracle, boxes, flags, far, range(8))):
         assert np.array_equal(ent[off[k]:off[k + 1]], exp), k
     w.close()
+
+
+def test_small_worlds_take_the_dense_pass_and_agree(oracle, monkeypatch):
+    """Below ~1e8 entity-view tests the cube groups are tested densely (cheaper than the grid); same lists either way."""
+    rng = np.random.default_rng(504)
+    boxes, flags, lights = _scene(rng, 20_000, 12, 2, 60.0, 10.0, 40.0)
+    ids = np.arange(len(lights), dtype=np.uint32)
+    got = []
+    for mode in (None, "0"):
+        if mode is not None:
+            monkeypatch.setenv("OVIS_MV_DENSE", mode)
+        w = _world_static(boxes, flags)
+        w.add_lights(lights)
+        got.append(_shadow_lists(w, ids))
+        w.close()
+    for a, b in zip(got[0], got[1]):
+        assert np.array_equal(a, b)
+    ll, lv, off, ent = got[0]
+    for k, exp in enumerate(_expected_lists(oracle, boxes, flags, lights, ids)):
+        assert np.array_equal(ent[off[k]:off[k + 1]], exp), k
 
 
 def test_many_lights_small_world_and_mixed_plain_views(oracle):

@@ -1,0 +1,27 @@
+#!/usr/bin/env python
+"""configs[2]'s world with all 4096 point lights as shadow casters, one multi-view call (for ncu -k regex:mv_sparse)."""
+import os
+import sys
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from orion_b200 import lib, scenes  # noqa: E402
+
+s = scenes.config3()
+n_ent, n_nodes = s["n_entities"], s["n_nodes"]
+w = lib.World(0)
+w.reserve(n_ent, n_nodes)
+e0 = w.add_entities(s["local_aabb"], s["flags"])
+w.add_nodes(s["parent"], s["local_trs"])
+w.bind_entities(s["entity_node"], np.arange(e0, e0 + n_ent, dtype=np.uint32))
+w.add_lights(s["lights"])
+w.update_transforms()
+ids = np.arange(len(s["lights"]), dtype=np.uint32)
+for _ in range(2):
+    ll, lv, off, _, _ = w.cull_shadow_views_device(ids)
+torch.cuda.synchronize()
+print("lists", len(ll), "pairs", int(off[-1]))
+w.close()
