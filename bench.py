@@ -202,8 +202,8 @@ def run_reference(args, rank: int):
 
 def ncu_traffic_bytes():
     """dram__bytes_read.sum + dram__bytes_write.sum of one launch of the dominant kernel, from the committed
-    `ncu --set full` summary of this same workload (profiles/r01_cull_test_kernel_ncu.csv); None if absent."""
-    path = os.path.join(ROOT, "profiles", "r01_cull_test_kernel_ncu.csv")
+    `ncu --set full` summary of this same workload (profiles/r02_cull_test_kernel_ncu.csv); None if absent."""
+    path = os.path.join(ROOT, "profiles", "r02_cull_test_kernel_ncu.csv")
     scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
     try:
         total, seen = 0.0, set()
@@ -431,7 +431,7 @@ def run_ours(args, rank: int, local_rank: int, world_size: int):
         "roofline": {"bound": "hbm", "kernel": "ovis::cull_test_kernel<1,false,4> (dominant: reads every bound once)",
                      "achieved": achieved, "peak": peak_gbs, "unit": "GB/s", "frac": achieved / peak_gbs,
                      "traffic": ncu_traffic_bytes() if n == SHARD_ENTITIES else None,
-                     "traffic_source": "profiles/r01_cull_test_kernel_ncu.csv (ncu --set full, one launch, same workload)",
+                     "traffic_source": "profiles/r02_cull_test_kernel_ncu.csv (ncu --set full, one launch, same workload)",
                      "algorithmic_bytes_per_launch": alg_bytes, "kernel_ms_mean": k_ms, "kernel_ms_min": float(test_ms.min()),
                      "gather_kernel_ms_mean": g_ms,
                      "both_kernels": {"achieved": step_achieved, "frac": step_achieved / peak_gbs,

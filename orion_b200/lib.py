@@ -697,3 +697,30 @@ def _world_extra_methods():
 
 
 _world_extra_methods()
+
+
+def _world_shadow_views_host():
+    def cull_shadow_views(self, light_ids, require=CASTS_SHADOW, shadow_res=512):
+        """ovis_cull_shadow_views: (list_light, list_view, offsets, entities) on the host; require = 0 keeps every entity."""
+        light_ids = _u32(light_ids)
+        cap_lists = 6 * max(len(light_ids), 1)
+        cap_ent = 1 << 16
+        while True:
+            ll = np.zeros(cap_lists, dtype=np.int32)
+            lv = np.zeros(cap_lists, dtype=np.int32)
+            off = np.zeros(cap_lists + 1, dtype=np.int64)
+            ent = np.zeros(cap_ent, dtype=np.uint32)
+            nl, ne = C.c_int32(), C.c_int64()
+            rc = self.lib.ovis_cull_shadow_views(self.h, C.c_int32(len(light_ids)), _p(light_ids), C.c_int32(shadow_res),
+                                                 C.c_uint32(require), C.c_int32(cap_lists), _p(ll), _p(lv), _p(off), C.byref(nl),
+                                                 C.c_int64(cap_ent), _p(ent), C.byref(ne))
+            if rc == OVIS_ERR_CAPACITY:
+                cap_lists, cap_ent = max(cap_lists, nl.value), max(cap_ent, ne.value)
+                continue
+            _check(rc)
+            return ll[:nl.value], lv[:nl.value], off[:nl.value + 1], ent[:ne.value]
+
+    World.cull_shadow_views = cull_shadow_views
+
+
+_world_shadow_views_host()

@@ -163,6 +163,27 @@ def test_many_lights_small_world_and_mixed_plain_views(oracle):
     w.close()
 
 
+def test_shadow_views_host_output_with_and_without_the_caster_filter(oracle):
+    """ovis_cull_shadow_views: the batched pass the adapter serves RenderWorld::cull(shadowView, results, 0) from - with
+    require = 0 every intersecting entity is listed (SimpleRenderWorld's answer; the pipeline filters castsShadow() itself),
+    with OVIS_CASTS_SHADOW the casters only. Several calls in a row: the speculative copy of the ids must never cut a list."""
+    rng = np.random.default_rng(505)
+    boxes, flags, lights = _scene(rng, 400_000, 20, 4, 300.0, 20.0, 120.0)
+    w = _world_static(boxes, flags)
+    w.add_lights(lights)
+    for ids in (np.arange(24, dtype=np.uint32), np.array([3, 21], dtype=np.uint32), np.arange(24, dtype=np.uint32)):
+        for require in (0, 1):
+            ll, lv, off, ent = w.cull_shadow_views(ids, require)
+            k = 0
+            for i in ids:
+                for v in oracle.light_shadow_views(lights[i]):
+                    exp = oracle.cull_aabb(boxes, oracle.view_planes(v), flags if require else None, require, threads=8)
+                    assert np.array_equal(ent[off[k]:off[k + 1]], exp), (int(i), require, k)
+                    k += 1
+            assert k == len(ll) and int(off[-1]) == len(ent)
+    w.close()
+
+
 def _bench_configs():
     if ROOT not in sys.path:
         sys.path.insert(0, ROOT)
