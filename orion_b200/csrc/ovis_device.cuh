@@ -148,6 +148,43 @@ __device__ __forceinline__ void mul2(float a0, float a1, float n, float &r0, flo
     asm("mov.b64 {%0, %1}, %2;" : "=f"(r0), "=f"(r1) : "l"(d));
 }
 
+// Packed pairs kept packed: two floats in one 64-bit register pair. Only operations whose inputs are not products may be
+// packed adds / subtracts (see above: ptxas would contract mul.f32x2 -> add.f32x2 into FFMA2); "sum - d" qualifies.
+__device__ __forceinline__ unsigned long long pack2(float lo, float hi) {
+    unsigned long long r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ void unpack2(unsigned long long v, float &lo, float &hi) {
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ unsigned long long mul2p(unsigned long long a, unsigned long long b) {
+    unsigned long long d;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+__device__ __forceinline__ unsigned long long sub2p(unsigned long long a, unsigned long long b) {
+    unsigned long long d;
+    asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+
+// Signed distances of four P-vertices (already selected and packed: x01 = {p0.x, p1.x}, x23 = {p2.x, p3.x}, ...) to a plane
+// given with every component doubled: qa = (nx, nx, ny, ny), qb = (nz, nz, d, d). ((x + y) + z) - d as the reference sums.
+__device__ __forceinline__ float4 plane_dist4_packed(const float4 &qa, const float4 &qb, unsigned long long x01, unsigned long long x23,
+                                                     unsigned long long y01, unsigned long long y23, unsigned long long z01,
+                                                     unsigned long long z23) {
+    const unsigned long long nx = pack2(qa.x, qa.y), ny = pack2(qa.z, qa.w), nz = pack2(qb.x, qb.y), dd = pack2(qb.z, qb.w);
+    float x0, x1, x2, x3, y0, y1, y2, y3, z0, z1, z2, z3;
+    unpack2(mul2p(x01, nx), x0, x1); unpack2(mul2p(x23, nx), x2, x3);
+    unpack2(mul2p(y01, ny), y0, y1); unpack2(mul2p(y23, ny), y2, y3);
+    unpack2(mul2p(z01, nz), z0, z1); unpack2(mul2p(z23, nz), z2, z3);
+    float4 r;
+    unpack2(sub2p(pack2(add(add(x0, y0), z0), add(add(x1, y1), z1)), dd), r.x, r.y);
+    unpack2(sub2p(pack2(add(add(x2, y2), z2), add(add(x3, y3), z3)), dd), r.z, r.w);
+    return r;
+}
+
 template <bool SX, bool SY, bool SZ>
 __device__ __forceinline__ uint32_t outside_plane4_signed(float nx, float ny, float nz, float d, const float4 &mnx, const float4 &mny,
                                                           const float4 &mnz, const float4 &mxx, const float4 &mxy, const float4 &mxz) {

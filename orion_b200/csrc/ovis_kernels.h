@@ -133,9 +133,12 @@ struct MvArgs {
     uint32_t *out;
     long long capacity;
     uint32_t id_base;
-    uint32_t *state;             // [0] overflow bits (kMvOverflow*), [1] scan ticket, [2] light-grid nodes used, [3] items used
+    uint32_t *state;             // [0] overflow bits (kMvOverflow*), [1] scan ticket, [2] light-grid nodes used, [3] items used,
+                                 // [4] most records any block wanted (when kMvOverflowHits)
     // dense pass
     const uint32_t *plain_views; // view ids handled by the dense pass
+    const uint2 *plain_meta;     // per plain view: x = sign codes | equal codes from here on (1..4) << 18 | casters only << 31, y = view id
+    const float4 *plain_planes;  // per plain view 12: plane p = (nx, nx, ny, ny), (nz, nz, d, d)
     int n_plain;
     int views_per_warp;          // plain views one warp handles for its 128 entities (small worlds split the views)
     uint32_t *masks;             // [n_plain][num_groups128 * 4]
@@ -151,12 +154,27 @@ struct MvArgs {
     MvItem *items;
     uint32_t item_capacity;
     uint2 *segments;             // per block: (first item, items)
+    int hit_capacity;            // records per block the lists hold (the host enlarges them when a block had more)
+    float4 *hit_records;         // per block of 8192 entities hit_capacity records of two: (min xyz, max x), (max yz, tag, -);
+                                 // tag = index inside the block | tested against every group << 31 (mv_classify_kernel -> mv_sparse_kernel)
+    uint32_t *block_work;        // per block: records appended (may exceed the capacity: overflow), zeroed per call
+    long long *host_offsets;     // page-locked host copy of csr_offsets (this round's slice) and of state[0..7], written by
+    uint32_t *host_state;        // the scan kernel's last CTA; nullptr = none
 };
-constexpr uint32_t kMvOverflowPairs = 1u, kMvOverflowItems = 2u, kMvOverflowNodes = 4u;
+struct MvResetArgs {              // up to four arrays filled with a word (sizes in 16-byte units, pointers 16-byte aligned)
+    void *ptr[4];
+    int64_t quads[4];
+    uint32_t value[4];
+    uint32_t *state;             // first_round: state[0] = 0 and csr_offsets[0] = 0 as well
+    long long *csr_offsets;
+    int first_round;
+};
+void launch_mv_reset(const MvResetArgs &r, int num_sms, cudaStream_t s);
+constexpr uint32_t kMvOverflowPairs = 1u, kMvOverflowItems = 2u, kMvOverflowNodes = 4u, kMvOverflowHits = 8u;
 
 void launch_mv_plain_test(const MvArgs &a, int num_sms, cudaStream_t s);
 void launch_mv_bin_lights(const MvArgs &a, cudaStream_t s);
-void launch_mv_sparse(const MvArgs &a, cudaStream_t s);
+void launch_mv_sparse(const MvArgs &a, int num_sms, cudaStream_t s);
 void launch_mv_scan(const MvArgs &a, cudaStream_t s);
 void launch_mv_expand_masks(const MvArgs &a, cudaStream_t s);
 void launch_mv_expand_items(const MvArgs &a, cudaStream_t s);

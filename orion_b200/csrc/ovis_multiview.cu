@@ -12,8 +12,9 @@
 //   sparse pass (cube groups: the six faces of a point light share the cube of half-side range + extent about the light)
 //     mv_bin_lights_kernel    K6, light side: every group is linked into the cells of a uniform grid it covers (per-cell
 //                             lists built with atomics) and marks them in an occupancy bitmap.
-//     mv_sparse_kernel        one CTA per block of 8192 entities: (1) every entity looks its cells up in the occupancy
-//                             bitmap held in shared memory - nearly all leave here; (2) the rest walk their cells' lists
+//     mv_classify_kernel      streaming: (1) every entity looks its cells up in the occupancy bitmap held in shared memory
+//                             and leaves one bit - nearly all leave with 0
+//     mv_sparse_kernel        one CTA per block of 8192 entities with bits set: (2) those entities walk their cells' lists
 //                             and append (entity, light) candidate pairs that pass the cube test to a shared-memory list
 //                             with shared-memory atomics; (3) one thread per pair runs the exact tests of the light's
 //                             faces; (4) the surviving records are sorted by (light, entity) in shared memory, which makes
@@ -36,30 +37,57 @@ namespace ovis {
 
 constexpr int kMvThreads = 256;
 
+// The kernels of one round are a chain of short launches. Each is launched with programmatic stream serialization and
+// starts with these two instructions: "my dependents may be scheduled" and "wait until everything before me in the stream
+// has completed and is visible". The dependency stays complete (every kernel waits before it touches memory or returns,
+// so "kernel N finished" still implies "kernels before N finished"); what overlaps is the launch latency and the scheduling
+// of the next grid's CTAs with the tail of this one. Without the launch attribute both instructions do nothing.
+__device__ __forceinline__ void chain_enter() {
+    asm volatile("griddepcontrol.launch_dependents;");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+
+template <typename Kernel>
+static void launch_chained(Kernel kernel, dim3 grid, size_t smem, cudaStream_t s, const MvArgs &a) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = dim3(kMvThreads);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = s;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    cudaLaunchKernelEx(&cfg, kernel, a);
+}
+
 // ------------------------------------------------------------------------------------------------
 // dense pass
 // ------------------------------------------------------------------------------------------------
 
 // The exact tests of R plain views that share their P-vertex sign codes (a camera and its cascades; the same face of
-// every point light), for the lane's four entities. Which corner is the P-vertex is decided by ONE warp-uniform switch per
-// plane for all R views (ncu, one view at a time: the six switches per view were a third of all instructions).
-// Products are packed FMUL2, "any distance < 0" is "minimum distance < 0" (fminf ignores a NaN operand exactly as a NaN
-// distance rejects nothing): the same instructions as K3. Warp-uniform early-out after the two side planes.
+// every point light), for the lane's four entities. Which corner is the P-vertex is decided per plane by three selects on
+// the (warp-uniform) code bits, shared by the R views: no branches, so the six planes of all R views are one basic block
+// the scheduler can interleave (round 2's first version switched over the 8 codes per plane: 140 KB of code, a third of the
+// issue slots spent on branches and compares, ncu in profiles/r02_k4_config4_v2_plain_runs_sparse_ncu.csv).
+// Products are packed FMUL2, "sum - d" is a packed subtract, "any distance < 0" is "minimum distance < 0" (fminf ignores a
+// NaN operand exactly as a NaN distance rejects nothing). Planes come with doubled components (plain_planes), so a packed
+// operand is a register pair as loaded. Warp-uniform early-out after the two side planes.
 template <int R>
 __device__ __forceinline__ void test_view_run(const MvArgs &a, int pv, uint32_t codes, const float4 &ax, const float4 &ay, const float4 &az,
                                               const float4 &bx, const float4 &by, const float4 &bz, uint32_t alive, uint32_t caster,
                                               int64_t group, int lane) {
     const int64_t num_words = (int64_t)a.num_groups128 * 4;
     const int row = a.num_blocks + 1;
-    int view[R];
-    uint32_t keep[R];
-    const float4 *pl[R];
+    const float4 *__restrict__ pl = a.plain_planes + (int64_t)pv * 12;
+    uint32_t view[R], keep[R];
     uint32_t any = 0;
 #pragma unroll
     for (int r = 0; r < R; r++) {
-        view[r] = (int)__ldg(a.plain_views + pv + r);
-        keep[r] = (__ldg(a.view_meta + view[r]) >> 31) ? caster : alive;
-        pl[r] = a.planes + 6 * view[r];
+        const uint2 m = __ldg(a.plain_meta + pv + r);
+        view[r] = m.y;
+        keep[r] = (m.x >> 31) ? caster : alive;
         any |= keep[r];
     }
     const float inf = __int_as_float(0x7f800000);
@@ -68,52 +96,55 @@ __device__ __forceinline__ void test_view_run(const MvArgs &a, int pv, uint32_t 
     for (int r = 0; r < R; r++)
         lowest[r] = make_float4(inf, inf, inf, inf);
     bool alive_somewhere = __any_sync(0xffffffffu, any != 0u);
+    if (alive_somewhere) {
 #pragma unroll
-    for (int p = 0; p < 6; p++) {
-        if (!alive_somewhere)
-            break;
-#define OVIS_MV_CASE(C, SX, SY, SZ)                                                                                     \
-    case C:                                                                                                             \
-_Pragma("unroll") for (int r = 0; r < R; r++) {                                                                 \
-    const float4 q = __ldg(pl[r] + p);                                                                              \
-    const float4 dd = plane_dist4_signed<SX, SY, SZ>(q.x, q.y, q.z, q.w, ax, ay, az, bx, by, bz);                   \
-    if (p & 1)                                                                                                      \
-        lowest[r] = min3_4(lowest[r], held[r], dd);                                                                 \
-    else                                                                                                            \
-        held[r] = dd;                                                                                               \
-}                                                                                                               \
-break;
-        switch ((codes >> (3 * p)) & 7u) {
-            OVIS_MV_CASE(0, false, false, false)
-            OVIS_MV_CASE(1, true, false, false)
-            OVIS_MV_CASE(2, false, true, false)
-            OVIS_MV_CASE(3, true, true, false)
-            OVIS_MV_CASE(4, false, false, true)
-            OVIS_MV_CASE(5, true, false, true)
-            OVIS_MV_CASE(6, false, true, true)
-            OVIS_MV_CASE(7, true, true, true)
-        }
-#undef OVIS_MV_CASE
-        if (p == 1) {                                                  // the side planes reject most tiles of a coherent scene
-            uint32_t left = 0;
+        for (int p = 0; p < 6; p++) {
+            const bool sx = (codes >> (3 * p)) & 1u, sy = (codes >> (3 * p + 1)) & 1u, sz = (codes >> (3 * p + 2)) & 1u;
+            const float4 px = sx ? bx : ax, py = sy ? by : ay, pz = sz ? bz : az;
+            const unsigned long long x01 = pack2(px.x, px.y), x23 = pack2(px.z, px.w), y01 = pack2(py.x, py.y), y23 = pack2(py.z, py.w),
+                                     z01 = pack2(pz.x, pz.y), z23 = pack2(pz.z, pz.w);
 #pragma unroll
-            for (int r = 0; r < R; r++)
-                left |= keep[r] & ~negative_bits(lowest[r]);
-            alive_somewhere = __any_sync(0xffffffffu, left != 0u);
+            for (int r = 0; r < R; r++) {
+                const float4 dd = plane_dist4_packed(__ldg(pl + 12 * r + 2 * p), __ldg(pl + 12 * r + 2 * p + 1), x01, x23, y01, y23, z01, z23);
+                if (p & 1)
+                    lowest[r] = min3_4(lowest[r], held[r], dd);
+                else
+                    held[r] = dd;
+            }
+            if (p == 1) {                                              // the side planes reject most tiles of a coherent scene
+                uint32_t left = 0;
+#pragma unroll
+                for (int r = 0; r < R; r++)
+                    left |= keep[r] & ~negative_bits(lowest[r]);
+                alive_somewhere = __any_sync(0xffffffffu, left != 0u);
+                if (!alive_somewhere)
+                    break;
+            }
         }
     }
+    // Results: per view four ballots (ballot j = entity 4 * lane + j of every lane), stored as they are - the dense pass's
+    // bitmaps are "j-major" inside a group of 128 (word 4 * group + j, bit = lane), which mv_expand_masks_kernel undoes.
+    // Nothing here waits on a shuffle, and the R views' instructions are independent of one another.
 #pragma unroll
     for (int r = 0; r < R; r++) {
-        const uint32_t k = alive_somewhere ? (keep[r] & ~negative_bits(lowest[r])) : 0u;
-        store_group_bits(a.masks + (int64_t)(pv + r) * num_words, group, k, lane);
-        const uint32_t total = __reduce_add_sync(0xffffffffu, __popc(k));
-        if (lane == 0 && total)
-            atomicAdd(a.totals + (int64_t)view[r] * row + group / kMaskBlockGroups, total);
+        const uint32_t k = alive_somewhere ? keep[r] : 0u;
+        uint4 b;
+        b.x = __ballot_sync(0xffffffffu, (k & 1u) && !(lowest[r].x < 0.0f));
+        b.y = __ballot_sync(0xffffffffu, (k & 2u) && !(lowest[r].y < 0.0f));
+        b.z = __ballot_sync(0xffffffffu, (k & 4u) && !(lowest[r].z < 0.0f));
+        b.w = __ballot_sync(0xffffffffu, (k & 8u) && !(lowest[r].w < 0.0f));
+        const uint32_t total = __popc(b.x) + __popc(b.y) + __popc(b.z) + __popc(b.w);
+        if (lane == 0) {
+            *reinterpret_cast<uint4 *>(a.masks + (int64_t)(pv + r) * num_words + group * 4) = b;
+            if (total)
+                atomicAdd(a.totals + (int64_t)view[r] * row + group / kMaskBlockGroups, total);
+        }
     }
 }
 
 __global__ void __launch_bounds__(kMvThreads, 2)
 mv_plain_test_kernel(const __grid_constant__ MvArgs a) {
+    chain_enter();
     const int lane = threadIdx.x & 31;
     const long long warps_total = (long long)gridDim.x * (kMvThreads / 32);
     const long long gwarp = (long long)blockIdx.x * (kMvThreads / 32) + (threadIdx.x >> 5);
@@ -143,18 +174,19 @@ mv_plain_test_kernel(const __grid_constant__ MvArgs a) {
         if (a.caster_mask)
             caster &= (__ldg(a.caster_mask + (e0 >> 5)) >> (e0 & 31)) & 0xfu;
         const int pv1 = min(a.n_plain, (chunk + 1) * a.views_per_warp);
-        // the host lists the plain views sorted by sign code: take them in runs of up to 4 equal codes
+        // the host lists the plain views sorted by sign code and says how many equal codes follow: runs of 4, 2 or 1
         for (int pv = chunk * a.views_per_warp; pv < pv1;) {
-            const uint32_t codes = __ldg(a.view_meta + __ldg(a.plain_views + pv)) & 0x3ffffu;
-            int run = 1;
-            while (run < 4 && pv + run < pv1 && (__ldg(a.view_meta + __ldg(a.plain_views + pv + run)) & 0x3ffffu) == codes)
-                run++;
-            if (run == 4) {
+            const uint32_t m = __ldg(&a.plain_meta[pv].x);
+            const uint32_t codes = m & 0x3ffffu;
+            int run = min((int)((m >> 18) & 7u), pv1 - pv);
+            if (run >= 4) {
+                run = 4;
                 test_view_run<4>(a, pv, codes, ax, ay, az, bx, by, bz, alive, caster, group, lane);
             } else if (run >= 2) {
                 run = 2;
                 test_view_run<2>(a, pv, codes, ax, ay, az, bx, by, bz, alive, caster, group, lane);
             } else {
+                run = 1;
                 test_view_run<1>(a, pv, codes, ax, ay, az, bx, by, bz, alive, caster, group, lane);
             }
             pv += run;
@@ -190,6 +222,7 @@ __device__ __forceinline__ uint32_t block_exclusive_scan(uint32_t c, uint32_t *s
 
 __global__ void __launch_bounds__(kMvThreads)
 mv_expand_masks_kernel(const __grid_constant__ MvArgs a) {
+    chain_enter();
     __shared__ uint32_t s_ids[kMaskBlockEntities];
     __shared__ uint32_t s_warp[kMvThreads / 32];
     const int b = blockIdx.x, pv = blockIdx.y, tid = threadIdx.x;
@@ -199,8 +232,21 @@ mv_expand_masks_kernel(const __grid_constant__ MvArgs a) {
     if (count == 0)
         return;
     const int64_t num_words = (int64_t)a.num_groups128 * 4;
+    // thread tid owns entities 32 * tid .. + 31 of the block: byte (tid & 3) of each of its group's four ballot words,
+    // bit l of ballot j -> bit 4 * l + j (mv_plain_test_kernel stores ballots, not entity-ordered words)
     const int64_t w = (int64_t)b * kMaskBlockWords + tid;
-    uint32_t word = w < num_words ? a.masks[(int64_t)pv * num_words + w] : 0u;
+    uint32_t word = 0u;
+    if (w < num_words) {
+        const uint4 q = __ldg(reinterpret_cast<const uint4 *>(a.masks + (int64_t)pv * num_words + (w & ~(int64_t)3)));
+        const int sh = (tid & 3) * 8;
+        auto spread = [](uint32_t x) {                     // bit l of a byte -> bit 4 * l
+            x = (x | (x << 12)) & 0x000f000fu;
+            x = (x | (x << 6)) & 0x03030303u;
+            return (x | (x << 3)) & 0x11111111u;
+        };
+        word = spread((q.x >> sh) & 0xffu) | (spread((q.y >> sh) & 0xffu) << 1) | (spread((q.z >> sh) & 0xffu) << 2) |
+               (spread((q.w >> sh) & 0xffu) << 3);
+    }
     uint32_t total;
     uint32_t rank = block_exclusive_scan(__popc(word), s_warp, &total);
     const uint32_t id0 = (uint32_t)(w << 5) + a.id_base;
@@ -217,11 +263,47 @@ mv_expand_masks_kernel(const __grid_constant__ MvArgs a) {
 }
 
 // ------------------------------------------------------------------------------------------------
+// reset: everything a round's kernels accumulate into, in one launch (it was a memset per array: each one a submission on
+// the critical path of a call that is otherwise five short kernels)
+// ------------------------------------------------------------------------------------------------
+
+__global__ void __launch_bounds__(kMvThreads)
+mv_reset_kernel(const MvResetArgs r) {
+    const int64_t t0 = (int64_t)blockIdx.x * kMvThreads + threadIdx.x, step = (int64_t)gridDim.x * kMvThreads;
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        uint4 *p = reinterpret_cast<uint4 *>(r.ptr[k]);
+        const uint32_t v = r.value[k];
+        const uint4 fill = make_uint4(v, v, v, v);
+        for (int64_t i = t0; i < r.quads[k]; i += step)
+            p[i] = fill;
+    }
+    if (t0 == 0) {
+        r.state[1] = r.state[2] = r.state[3] = 0u;           // (the first 16 bytes are not among the arrays: word 0 outlives a round)
+        if (r.first_round) {
+            r.state[0] = 0u;
+            r.csr_offsets[0] = 0ll;
+        }
+    }
+}
+
+void launch_mv_reset(const MvResetArgs &r, int num_sms, cudaStream_t s) {
+    int64_t most = 1;
+    for (int k = 0; k < 4; k++)
+        most = most > r.quads[k] ? most : r.quads[k];
+    int64_t grid = (most + kMvThreads - 1) / kMvThreads;
+    if (grid > (int64_t)num_sms * 4)
+        grid = (int64_t)num_sms * 4;
+    mv_reset_kernel<<<(unsigned)grid, kMvThreads, 0, s>>>(r);
+}
+
+// ------------------------------------------------------------------------------------------------
 // scan: totals[view][block] -> exclusive prefixes (+ the view total in the extra column), then CSR offsets
 // ------------------------------------------------------------------------------------------------
 
 __global__ void __launch_bounds__(kMvThreads)
 mv_scan_kernel(const __grid_constant__ MvArgs a) {
+    chain_enter();
     __shared__ uint32_t s_warp[kMvThreads / 32];
     __shared__ long long s_warp64[kMvThreads / 32];
     __shared__ bool s_last;
@@ -269,9 +351,17 @@ mv_scan_kernel(const __grid_constant__ MvArgs a) {
                 before += s_warp64[k];
             sum += s_warp64[k];
         }
-        if (v < a.n_views)
+        if (v < a.n_views) {
             a.csr_offsets[v + 1] = running + before + incl;
+            if (a.host_offsets)                                 // page-locked host memory: the call's read-back without a copy
+                a.host_offsets[v + 1] = running + before + incl;
+        }
         running += sum;
+    }
+    if (a.host_offsets && tid < 8) {
+        if (tid == 0)
+            a.host_offsets[0] = a.csr_offsets[0];
+        a.host_state[tid] = tid == 1 ? 0u : __ldcg(a.state + tid);
     }
     if (tid == 0)
         a.state[1] = 0u;
@@ -283,6 +373,7 @@ mv_scan_kernel(const __grid_constant__ MvArgs a) {
 
 __global__ void __launch_bounds__(kMvThreads)
 mv_bin_lights_kernel(const __grid_constant__ MvArgs a) {
+    chain_enter();
     const int g = blockIdx.x;                                  // one CTA per group: a large light covers hundreds of cells
     const MvGroup grp = a.groups[g];
     const int x0 = grp.cell_lo & 255, y0 = (grp.cell_lo >> 8) & 255, z0 = (grp.cell_lo >> 16) & 255;
@@ -390,117 +481,172 @@ __device__ __forceinline__ SegCount seg_join(const SegCount &earlier, const SegC
     return r;
 }
 
-__global__ void __launch_bounds__(kMvThreads, 2)
-mv_sparse_kernel(const __grid_constant__ MvArgs a) {
+// K6, entity side, streaming half: every entity of the world is classified against the occupancy bitmap - bit in `hit`:
+// one of its cells is occupied, its candidates are found through the cells' lists; bit in `big`: it is tested against every
+// group. One pass over the bounds at memory speed (the walk of K3: a warp takes 128 entities, 4 per lane, six 128-bit loads),
+// nothing else happens here, so the loads never wait for the pair work of mv_sparse_kernel (round 2's first version did both
+// in one CTA per block and streamed at 1.8 TB/s: profiles/r02_k4_config4_v2_plain_runs_sparse_ncu.csv).
+__global__ void __launch_bounds__(kMvThreads, 4)
+mv_classify_kernel(const __grid_constant__ MvArgs a) {
+    chain_enter();
     extern __shared__ __align__(16) unsigned char s_mv[];
-    const int rows = a.grid.dim[1] * a.grid.dim[2];
     unsigned long long *s_bitmap = reinterpret_cast<unsigned long long *>(s_mv);
-    uint32_t *s_pairs = reinterpret_cast<uint32_t *>(s_bitmap + rows);
-    uint32_t *s_hit = s_pairs + kMvPairCapacity;               // 256 words: bit = entity has an occupied cell
-    uint32_t *s_big = s_hit + kMaskBlockWords;                 // 256 words: bit = entity is tested against every group
-    __shared__ uint32_t s_npairs, s_nrec, s_item_base;
+    const int rows = a.grid.dim[1] * a.grid.dim[2];
+    for (int i = threadIdx.x; i < rows; i += kMvThreads)
+        s_bitmap[i] = a.bitmap[i];
+    __syncthreads();
+    const int lane = threadIdx.x & 31;
+    const long long warps_total = (long long)gridDim.x * (kMvThreads / 32);
+    const float4 *__restrict__ bounds = reinterpret_cast<const float4 *>(a.bounds);
+    const int64_t vstride = a.stride >> 2;
+    const int dim_y = a.grid.dim[1];
+    for (long long group = (long long)blockIdx.x * (kMvThreads / 32) + (threadIdx.x >> 5); group < a.num_groups128; group += warps_total) {
+        const int64_t v = group * 32 + lane;
+        const int64_t e0 = v << 2;
+        const float4 ax = __ldg(bounds + 0 * vstride + v), ay = __ldg(bounds + 1 * vstride + v), az = __ldg(bounds + 2 * vstride + v);
+        const float4 bx = __ldg(bounds + 3 * vstride + v), by = __ldg(bounds + 4 * vstride + v), bz = __ldg(bounds + 5 * vstride + v);
+        uint32_t alive = candidate_bits<false>(e0, a.n, 0u);
+        if (a.alive_mask)
+            alive &= (__ldg(a.alive_mask + (e0 >> 5)) >> (e0 & 31)) & 0xfu;
+        const float mnv[4][3] = { { ax.x, ay.x, az.x }, { ax.y, ay.y, az.y }, { ax.z, ay.z, az.z }, { ax.w, ay.w, az.w } };
+        const float mxv[4][3] = { { bx.x, by.x, bz.x }, { bx.y, by.y, bz.y }, { bx.z, by.z, bz.z }, { bx.w, by.w, bz.w } };
+        uint32_t hit = 0, big = 0;
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            float lo[3], hi[3];
+            CellRange r;
+            bool odd;
+            const int kind = entity_cells(a.grid, mnv[j], mxv[j], lo, hi, r, &odd);
+            // kind 1 spans at most 2 x 2 rows: look at the four corner rows (duplicates when it spans fewer)
+            const unsigned long long seen = (s_bitmap[r.z0 * dim_y + r.y0] | s_bitmap[r.z0 * dim_y + r.y1]) |
+                                            (s_bitmap[r.z1 * dim_y + r.y0] | s_bitmap[r.z1 * dim_y + r.y1]);
+            const bool occupied = (seen & x_range_bits(r.x0, r.x1)) != 0ull;
+            big |= (kind == 2 ? 1u : 0u) << j;
+            hit |= ((kind == 1) & occupied ? 1u : 0u) << j;
+        }
+        // the classified entities leave as records (box + index inside the block) appended to their block's list: what
+        // mv_sparse_kernel needs of them arrives there in one coalesced read (reading the boxes back out of the SoA arrays
+        // cost it six sectors per entity, as much traffic as this whole pass). Order inside a list is whatever the atomics
+        // give; the records are sorted further down the line.
+        const uint32_t mine = (hit | big) & alive;
+        if (__any_sync(0xffffffffu, mine != 0u)) {
+            const uint32_t count = __popc(mine);
+            uint32_t incl = count;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t up = __shfl_up_sync(0xffffffffu, incl, o);
+                if (lane >= o)
+                    incl += up;
+            }
+            const int b = (int)(group / kMaskBlockGroups);
+            uint32_t base = 0;
+            if (lane == 31)
+                base = atomicAdd(a.block_work + b, incl);
+            base = __shfl_sync(0xffffffffu, base, 31) + incl - count;
+            float4 *__restrict__ list = a.hit_records + (int64_t)b * (2 * a.hit_capacity);
+            const uint32_t el0 = (uint32_t)(e0 & (kMaskBlockEntities - 1));
+#pragma unroll
+            for (int j = 0; j < 4; j++)
+                if ((mine >> j) & 1u) {
+                    if (base < (uint32_t)a.hit_capacity) {
+                        const uint32_t tag = (el0 + j) | (((big >> j) & 1u) << 31);
+                        list[2 * base] = make_float4(mnv[j][0], mnv[j][1], mnv[j][2], mxv[j][0]);
+                        list[2 * base + 1] = make_float4(mxv[j][1], mxv[j][2], __uint_as_float(tag), 0.0f);
+                    }
+                    base++;
+                }
+        }
+    }
+}
+
+// K6, entity side, pair half: one CTA per block of 8192 entities that has classified entities.
+__global__ void __launch_bounds__(kMvThreads, 4)
+mv_sparse_kernel(const __grid_constant__ MvArgs a) {
+    chain_enter();
+    __shared__ uint32_t s_pairs[kMvPairCapacity];
+    __shared__ uint32_t s_big[64];                             // records tested against every group (rare: huge or odd boxes)
+    __shared__ uint32_t s_npairs, s_nrec, s_item_base, s_nbig;
     __shared__ uint32_t s_warp[kMvThreads / 32];
     __shared__ SegCount s_seg[kMvThreads / 32];
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int b = blockIdx.x;
-    const float4 *__restrict__ bounds = reinterpret_cast<const float4 *>(a.bounds);
-    const int64_t vstride = a.stride >> 2;
     const int64_t block_e0 = (int64_t)b * kMaskBlockEntities;
-
-    for (int i = tid; i < rows; i += kMvThreads)
-        s_bitmap[i] = a.bitmap[i];
+    const uint32_t n_hits = a.block_work[b];
+    if (n_hits == 0u || n_hits > (uint32_t)a.hit_capacity) {
+        if (tid == 0) {
+            if (n_hits) {                                      // the block's list was too short: the host enlarges the lists and reruns
+                atomicOr(a.state, kMvOverflowHits);
+                atomicMax(a.state + 4, n_hits);
+            }
+            a.segments[b] = make_uint2(0u, 0u);
+        }
+        return;
+    }
     if (tid == 0) {
         s_npairs = 0;
         s_nrec = 0;
+        s_nbig = 0;
     }
     __syncthreads();
+    const unsigned long long *__restrict__ bitmap = a.bitmap;
+    const float4 *__restrict__ list = a.hit_records + (int64_t)b * (2 * a.hit_capacity);
 
-    // ---- (1) which entities have an occupied cell? 8 groups of 128 entities per warp
-    for (int k = 0; k < kMaskBlockGroups / (kMvThreads / 32); k++) {
-        const int gl = warp * (kMaskBlockGroups / (kMvThreads / 32)) + k;       // group inside the block
-        const int64_t group = (int64_t)b * kMaskBlockGroups + gl;
-        uint32_t hit = 0, big = 0, alive_bits = 0;
-        if (group < a.num_groups128) {
-            const int64_t v = group * 32 + lane;
-            const int64_t e0 = v << 2;
-            const float4 ax = __ldg(bounds + 0 * vstride + v), ay = __ldg(bounds + 1 * vstride + v), az = __ldg(bounds + 2 * vstride + v);
-            const float4 bx = __ldg(bounds + 3 * vstride + v), by = __ldg(bounds + 4 * vstride + v), bz = __ldg(bounds + 5 * vstride + v);
-            uint32_t alive = candidate_bits<false>(e0, a.n, 0u);
-            if (a.alive_mask)
-                alive &= (__ldg(a.alive_mask + (e0 >> 5)) >> (e0 & 31)) & 0xfu;
-            alive_bits = alive;
-            const float mnv[4][3] = { { ax.x, ay.x, az.x }, { ax.y, ay.y, az.y }, { ax.z, ay.z, az.z }, { ax.w, ay.w, az.w } };
-            const float mxv[4][3] = { { bx.x, by.x, bz.x }, { bx.y, by.y, bz.y }, { bx.z, by.z, bz.z }, { bx.w, by.w, bz.w } };
-#pragma unroll
-            for (int j = 0; j < 4; j++) {
-                float lo[3], hi[3];
-                CellRange r;
-                bool odd;
-                const int kind = entity_cells(a.grid, mnv[j], mxv[j], lo, hi, r, &odd);
-                // kind 1 spans at most 2 x 2 rows: look at the four corner rows (duplicates when it spans fewer)
-                const unsigned long long rows = (s_bitmap[r.z0 * a.grid.dim[1] + r.y0] | s_bitmap[r.z0 * a.grid.dim[1] + r.y1]) |
-                                                (s_bitmap[r.z1 * a.grid.dim[1] + r.y0] | s_bitmap[r.z1 * a.grid.dim[1] + r.y1]);
-                const bool occupied = (rows & x_range_bits(r.x0, r.x1)) != 0ull;
-                big |= (kind == 2 ? 1u : 0u) << j;
-                hit |= ((kind == 1) & occupied ? 1u : 0u) << j;
+    // ---- (2) candidate pairs: a thread takes every 256th record of the block
+    for (uint32_t h = tid; h < n_hits; h += kMvThreads) {
+        const float4 r0 = __ldg(list + 2 * h), r1 = __ldg(list + 2 * h + 1);
+        const float mn[3] = { r0.x, r0.y, r0.z }, mx[3] = { r0.w, r1.x, r1.y };
+        const uint32_t tag = __float_as_uint(r1.z), el = tag & (kMaskBlockEntities - 1);
+        float lo[3], hi[3];
+        CellRange r;
+        bool odd;
+        entity_cells(a.grid, mn, mx, lo, hi, r, &odd);
+        if (tag >> 31) {
+            const uint32_t slot = atomicAdd(&s_nbig, 1u);
+            if (slot < 64u) {
+                s_big[slot] = h;
+            } else {                                           // (more than 64 such boxes in one block: this thread alone)
+                for (int g = 0; g < a.n_groups; g++)
+                    if (odd || overlaps_cube(a.groups[g], lo, hi))
+                        append_pair(s_pairs, &s_npairs, (uint32_t)g, el);
             }
+            continue;
         }
-        store_group_bits(s_hit, gl, hit & alive_bits, lane);
-        store_group_bits(s_big, gl, big & alive_bits, lane);
-    }
-    __syncthreads();
-
-    // ---- (2) candidate pairs: thread t owns the 32 entities of word t
-    {
-        uint32_t word = s_hit[tid];
-        while (word) {
-            const int bit = __ffs(word) - 1;
-            word &= word - 1;
-            const uint32_t el = (uint32_t)tid * 32 + bit;
-            float mn[3], mx[3], lo[3], hi[3];
-            CellRange r;
-            bool odd;
-            load_box(a, block_e0 + el, mn, mx);
-            entity_cells(a.grid, mn, mx, lo, hi, r, &odd);
-            const unsigned long long xm = x_range_bits(r.x0, r.x1);
-            for (int z = r.z0; z <= r.z1; z++)
-                for (int y = r.y0; y <= r.y1; y++) {
-                    unsigned long long occupied = s_bitmap[z * a.grid.dim[1] + y] & xm;
-                    while (occupied) {
-                        const int x = __ffsll((long long)occupied) - 1;
-                        occupied &= occupied - 1;
-                        for (int32_t node = a.heads[((int64_t)z * a.grid.dim[1] + y) * a.grid.dim[0] + x]; node >= 0; node = a.node_next[node]) {
-                            const uint32_t g = a.node_group[node];
-                            const MvGroup grp = a.groups[g];
-                            // a group shared by several of the entity's cells is taken in the first of them only
-                            const int gx = max(r.x0, (int)(grp.cell_lo & 255)), gy = max(r.y0, (int)((grp.cell_lo >> 8) & 255)),
-                                      gz = max(r.z0, (int)((grp.cell_lo >> 16) & 255));
-                            if (x != gx || y != gy || z != gz)
-                                continue;
-                            if (overlaps_cube(grp, lo, hi))
-                                append_pair(s_pairs, &s_npairs, g, el);
-                        }
+        const unsigned long long xm = x_range_bits(r.x0, r.x1);
+        for (int z = r.z0; z <= r.z1; z++)
+            for (int y = r.y0; y <= r.y1; y++) {
+                unsigned long long occupied = __ldg(bitmap + z * a.grid.dim[1] + y) & xm;
+                while (occupied) {
+                    const int x = __ffsll((long long)occupied) - 1;
+                    occupied &= occupied - 1;
+                    for (int32_t node = a.heads[((int64_t)z * a.grid.dim[1] + y) * a.grid.dim[0] + x]; node >= 0; node = a.node_next[node]) {
+                        const uint32_t g = a.node_group[node];
+                        const MvGroup grp = a.groups[g];
+                        // a group shared by several of the entity's cells is taken in the first of them only
+                        const int gx = max(r.x0, (int)(grp.cell_lo & 255)), gy = max(r.y0, (int)((grp.cell_lo >> 8) & 255)),
+                                  gz = max(r.z0, (int)((grp.cell_lo >> 16) & 255));
+                        if (x != gx || y != gy || z != gz)
+                            continue;
+                        if (overlaps_cube(grp, lo, hi))
+                            append_pair(s_pairs, &s_npairs, g, el);
                     }
                 }
-        }
+            }
     }
-    // entities tested against every group: the whole CTA shares each one, a thread takes every 256th group
-    for (int w = 0; w < kMaskBlockWords; w++) {
-        uint32_t word = s_big[w];
-        while (word) {
-            const int bit = __ffs(word) - 1;
-            word &= word - 1;
-            const uint32_t el = (uint32_t)w * 32 + bit;
-            float mn[3], mx[3], lo[3], hi[3];
-            CellRange r;
-            bool odd;
-            load_box(a, block_e0 + el, mn, mx);
-            entity_cells(a.grid, mn, mx, lo, hi, r, &odd);
-            for (int g = tid; g < a.n_groups; g += kMvThreads)
-                if (odd || overlaps_cube(a.groups[g], lo, hi))
-                    append_pair(s_pairs, &s_npairs, (uint32_t)g, el);
-        }
+    __syncthreads();
+    // records tested against every group: the whole CTA shares each one, a thread takes every 256th group
+    for (uint32_t k = 0, nbig = min(s_nbig, 64u); k < nbig; k++) {
+        const uint32_t h = s_big[k];
+        const float4 r0 = __ldg(list + 2 * h), r1 = __ldg(list + 2 * h + 1);
+        const float mn[3] = { r0.x, r0.y, r0.z }, mx[3] = { r0.w, r1.x, r1.y };
+        const uint32_t el = __float_as_uint(r1.z) & (kMaskBlockEntities - 1);
+        float lo[3], hi[3];
+        CellRange r;
+        bool odd;
+        entity_cells(a.grid, mn, mx, lo, hi, r, &odd);
+        for (int g = tid; g < a.n_groups; g += kMvThreads)
+            if (odd || overlaps_cube(a.groups[g], lo, hi))
+                append_pair(s_pairs, &s_npairs, (uint32_t)g, el);
     }
     __syncthreads();
     const uint32_t npairs = s_npairs;
@@ -673,6 +819,7 @@ mv_sparse_kernel(const __grid_constant__ MvArgs a) {
 
 __global__ void __launch_bounds__(kMvThreads)
 mv_expand_items_kernel(const __grid_constant__ MvArgs a) {
+    chain_enter();
     const int row = a.num_blocks + 1;
     for (int b = blockIdx.x; b < a.num_blocks; b += gridDim.x) {
         const uint2 seg = a.segments[b];
@@ -703,45 +850,40 @@ void launch_mv_plain_test(const MvArgs &a, int num_sms, cudaStream_t s) {
     long long grid = (items + kMvThreads / 32 - 1) / (kMvThreads / 32);
     if (grid > (long long)num_sms * per_sm)
         grid = (long long)num_sms * per_sm;
-    mv_plain_test_kernel<<<(unsigned)grid, kMvThreads, 0, s>>>(a);
+    launch_chained(mv_plain_test_kernel, dim3((unsigned)grid), 0, s, a);
 }
 
 void launch_mv_expand_masks(const MvArgs &a, cudaStream_t s) {
     if (a.n_plain <= 0 || a.num_blocks <= 0)
         return;
-    mv_expand_masks_kernel<<<dim3((unsigned)a.num_blocks, (unsigned)a.n_plain), kMvThreads, 0, s>>>(a);
+    launch_chained(mv_expand_masks_kernel, dim3((unsigned)a.num_blocks, (unsigned)a.n_plain), 0, s, a);
 }
 
 void launch_mv_scan(const MvArgs &a, cudaStream_t s) {
     if (a.n_views > 0)
-        mv_scan_kernel<<<(unsigned)a.n_views, kMvThreads, 0, s>>>(a);
+        launch_chained(mv_scan_kernel, dim3((unsigned)a.n_views), 0, s, a);
 }
 
 void launch_mv_bin_lights(const MvArgs &a, cudaStream_t s) {
     if (a.n_groups > 0)
-        mv_bin_lights_kernel<<<(unsigned)a.n_groups, kMvThreads, 0, s>>>(a);
+        launch_chained(mv_bin_lights_kernel, dim3((unsigned)a.n_groups), 0, s, a);
 }
 
-static size_t mv_sparse_smem(const MvArgs &a) {
-    return sizeof(unsigned long long) * (size_t)(a.grid.dim[1] * a.grid.dim[2]) + sizeof(uint32_t) * (kMvPairCapacity + 2 * kMaskBlockWords);
-}
-
-void launch_mv_sparse(const MvArgs &a, cudaStream_t s) {
+void launch_mv_sparse(const MvArgs &a, int num_sms, cudaStream_t s) {
     if (a.n_groups <= 0 || a.num_blocks <= 0)
         return;
-    const size_t smem = mv_sparse_smem(a);
-    static size_t allowed = 0;
-    if (smem > allowed) {
-        cudaFuncSetAttribute(mv_sparse_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        allowed = smem;
-    }
-    mv_sparse_kernel<<<(unsigned)a.num_blocks, kMvThreads, smem, s>>>(a);
+    const size_t smem = sizeof(unsigned long long) * (size_t)(a.grid.dim[1] * a.grid.dim[2]);     // <= 32 KB
+    long long grid = ((long long)a.num_groups128 + kMvThreads / 32 - 1) / (kMvThreads / 32);
+    if (grid > (long long)num_sms * 4)
+        grid = (long long)num_sms * 4;
+    launch_chained(mv_classify_kernel, dim3((unsigned)grid), smem, s, a);
+    launch_chained(mv_sparse_kernel, dim3((unsigned)a.num_blocks), 0, s, a);
 }
 
 void launch_mv_expand_items(const MvArgs &a, cudaStream_t s) {
     if (a.n_groups <= 0 || a.num_blocks <= 0)
         return;
-    mv_expand_items_kernel<<<(unsigned)(a.num_blocks < 1184 ? a.num_blocks : 1184), kMvThreads, 0, s>>>(a);
+    launch_chained(mv_expand_items_kernel, dim3((unsigned)(a.num_blocks < 1184 ? a.num_blocks : 1184)), 0, s, a);
 }
 
 }  // namespace ovis

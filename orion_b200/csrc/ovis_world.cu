@@ -168,6 +168,11 @@ struct OvisWorld {
     int64_t cap_mv_totals = 0;
     uint32_t *d_mv_masks = nullptr;       // [plain views of a round][words]
     int64_t cap_mv_masks = 0;
+    float4 *d_mv_hits = nullptr;          // sparse pass: per block of 8192 entities the records of those near a light
+    int64_t cap_mv_hits = 0;
+    int mv_hit_cap = 1024;                // records per block (grown on demand, at most one per entity of the block)
+    uint32_t *d_mv_work = nullptr;        // ... and how many
+    int64_t cap_mv_work = 0;
     uint32_t *d_mv_node_group = nullptr;
     int32_t *d_mv_node_next = nullptr;
     int64_t cap_mv_nodes = 0;
@@ -1025,8 +1030,8 @@ int cull_views_grouped(OvisWorld *w, int32_t n_views, const float *planes, const
     for (int attempt = 0;; attempt++) {
         if (attempt == 8)
             return fail(OVIS_ERR_NOMEM, "multi-view result did not fit after regrowing");
-        OVIS_CUDA(cudaMemsetAsync(w->d_csr_offsets, 0, sizeof(long long), w->stream));
-        OVIS_CUDA(cudaMemsetAsync(w->d_mv_state, 0, sizeof(uint32_t), w->stream));       // the overflow word of the call
+        OVIS_TRY(ensure_pinned(w->h_mv_result, w->cap_h_mv_result, sizeof(long long) * ((size_t)n_views + 5)));
+        long long *hr = static_cast<long long *>(w->h_mv_result);
         size_t g0 = 0;
         while (g0 < groups.size()) {
             // ---- one round: groups [g0, g1), views [v0, v1)
@@ -1063,7 +1068,9 @@ int cull_views_grouped(OvisWorld *w, int32_t n_views, const float *planes, const
             const size_t off_meta = sizeof(float) * 24 * (size_t)nv;
             const size_t off_plain = off_meta + sizeof(uint32_t) * (size_t)nv;
             const size_t off_groups = (off_plain + sizeof(uint32_t) * plain.size() + 15) & ~(size_t)15;
-            const size_t bytes = off_groups + sizeof(ovis::MvGroup) * cubes.size();
+            const size_t off_pmeta = (off_groups + sizeof(ovis::MvGroup) * cubes.size() + 15) & ~(size_t)15;
+            const size_t off_pplanes = (off_pmeta + sizeof(uint2) * plain.size() + 15) & ~(size_t)15;
+            const size_t bytes = off_pplanes + sizeof(float) * 48 * plain.size();
             OVIS_TRY(ensure_pinned(w->h_mv_stage, w->cap_h_mv_stage, bytes));
             {
                 int64_t cap = (int64_t)w->cap_d_mv_stage;
@@ -1082,9 +1089,27 @@ int cull_views_grouped(OvisWorld *w, int32_t n_views, const float *planes, const
                 std::memcpy(hs + off_plain, plain.data(), sizeof(uint32_t) * plain.size());
             if (!cubes.empty())
                 std::memcpy(hs + off_groups, cubes.data(), sizeof(ovis::MvGroup) * cubes.size());
+            {
+                // what the dense kernel reads per plain view, in list order: codes + how many equal codes follow, and
+                // the planes with every component doubled (operands of the packed multiplies as loaded)
+                uint32_t *pm = reinterpret_cast<uint32_t *>(hs + off_pmeta);
+                float *pp = reinterpret_cast<float *>(hs + off_pplanes);
+                const size_t np = plain.size();
+                for (size_t k = np; k-- > 0;) {
+                    const uint32_t m = meta[plain[k]];
+                    uint32_t run = 1;
+                    if (k + 1 < np && (meta[plain[k + 1]] & 0x3ffffu) == (m & 0x3ffffu))
+                        run = std::min<uint32_t>(4u, ((pm[2 * (k + 1)] >> 18) & 7u) + 1u);
+                    pm[2 * k] = (m & 0x8003ffffu) | (run << 18);
+                    pm[2 * k + 1] = plain[k];
+                    const float *src = planes + 24 * (size_t)(v0 + plain[k]);
+                    for (int c = 0; c < 24; c++)
+                        pp[48 * k + 2 * c] = pp[48 * k + 2 * c + 1] = src[c];
+                }
+            }
             OVIS_CUDA(cudaMemcpyAsync(w->d_mv_stage, hs, bytes, cudaMemcpyHostToDevice, w->stream));
             // ---- scratch
-            OVIS_TRY(ensure(w->d_mv_totals, w->cap_mv_totals, (int64_t)nv * row, w->stream));
+            OVIS_TRY(ensure(w->d_mv_totals, w->cap_mv_totals, round_up((int64_t)nv * row, 4), w->stream));
             OVIS_TRY(ensure(w->d_mv_masks, w->cap_mv_masks, std::max<int64_t>(1, (int64_t)plain.size() * num_words), w->stream));
             if (!cubes.empty()) {
                 if (nodes > w->cap_mv_nodes) {
@@ -1095,6 +1120,8 @@ int cull_views_grouped(OvisWorld *w, int32_t n_views, const float *planes, const
                 }
                 OVIS_TRY(ensure(w->d_mv_items, w->cap_mv_items, std::max<int64_t>((int64_t)1 << 20, w->n_ent / 8), w->stream));
                 OVIS_TRY(ensure(w->d_mv_segments, w->cap_mv_segments, num_blocks, w->stream));
+                OVIS_TRY(ensure(w->d_mv_hits, w->cap_mv_hits, (int64_t)num_blocks * 2 * w->mv_hit_cap, w->stream));
+                OVIS_TRY(ensure(w->d_mv_work, w->cap_mv_work, round_up(num_blocks, 4), w->stream));
             }
             const unsigned char *ds = static_cast<const unsigned char *>(w->d_mv_stage);
             a.bounds = w->d_world;
@@ -1115,6 +1142,8 @@ int cull_views_grouped(OvisWorld *w, int32_t n_views, const float *planes, const
             a.state = reinterpret_cast<uint32_t *>(w->d_mv_state);
             a.plain_views = reinterpret_cast<const uint32_t *>(ds + off_plain);
             a.n_plain = (int)plain.size();
+            a.plain_meta = reinterpret_cast<const uint2 *>(ds + off_pmeta);
+            a.plain_planes = reinterpret_cast<const float4 *>(ds + off_pplanes);
             {
                 // small worlds: split the views over more warps so that every SM has work
                 const int64_t want_warps = (int64_t)w->num_sms * 48;
@@ -1133,29 +1162,48 @@ int cull_views_grouped(OvisWorld *w, int32_t n_views, const float *planes, const
             a.items = w->d_mv_items;
             a.item_capacity = (uint32_t)std::min<int64_t>(w->cap_mv_items, 0xffffffffll);
             a.segments = w->d_mv_segments;
-            // ---- reset: per-block totals, the round's counters + occupancy bitmap, the cells' list heads
-            OVIS_CUDA(cudaMemsetAsync(w->d_mv_totals, 0, sizeof(uint32_t) * (size_t)((int64_t)nv * row), w->stream));
-            OVIS_CUDA(cudaMemsetAsync(w->d_mv_state + sizeof(uint32_t), 0, kMvStateBytes - sizeof(uint32_t), w->stream));   // all but the overflow word
-            if (!cubes.empty())
-                OVIS_CUDA(cudaMemsetAsync(w->d_mv_heads, 0xff, sizeof(int32_t) * (size_t)(a.grid.dim[0] * a.grid.dim[1] * a.grid.dim[2]), w->stream));
+            if (!cubes.empty()) {
+                a.hit_records = w->d_mv_hits;
+                a.hit_capacity = w->mv_hit_cap;
+                a.block_work = w->d_mv_work;
+            }
+            a.host_offsets = hr + v0;
+            a.host_state = reinterpret_cast<uint32_t *>(hr + n_views + 1);
+            {
+                // ---- reset: per-block totals, the round's counters + occupancy bitmap, the cells' list heads, the blocks'
+                // record counts - one launch
+                ovis::MvResetArgs r{};
+                r.ptr[0] = w->d_mv_totals;
+                r.quads[0] = round_up((int64_t)nv * row, 4) / 4;
+                r.ptr[1] = w->d_mv_state + 16;
+                r.quads[1] = (int64_t)(kMvStateBytes - 16) / 16;
+                if (!cubes.empty()) {
+                    r.ptr[2] = w->d_mv_heads;
+                    r.quads[2] = round_up((int64_t)a.grid.dim[0] * a.grid.dim[1] * a.grid.dim[2], 4) / 4;
+                    r.value[2] = 0xffffffffu;
+                    r.ptr[3] = w->d_mv_work;
+                    r.quads[3] = round_up(num_blocks, 4) / 4;
+                }
+                r.state = reinterpret_cast<uint32_t *>(w->d_mv_state);
+                r.csr_offsets = w->d_csr_offsets;
+                r.first_round = g0 == 0 ? 1 : 0;
+                ovis::launch_mv_reset(r, w->num_sms, w->stream);
+            }
             // ---- kernels
             ovis::launch_mv_bin_lights(a, w->stream);
             ovis::launch_mv_plain_test(a, w->num_sms, w->stream);
-            ovis::launch_mv_sparse(a, w->stream);
+            ovis::launch_mv_sparse(a, w->num_sms, w->stream);
             ovis::launch_mv_scan(a, w->stream);
             ovis::launch_mv_expand_masks(a, w->stream);
             ovis::launch_mv_expand_items(a, w->stream);
-            w->launches += 1 + (plain.empty() ? 0 : 2) + (cubes.empty() ? 0 : 3);
+            w->launches += 2 + (plain.empty() ? 0 : 2) + (cubes.empty() ? 0 : 4);
             OVIS_CUDA(cudaGetLastError());
             if (g1 < groups.size())
                 OVIS_CUDA(cudaStreamSynchronize(w->stream));     // the pinned staging buffer is refilled by the next round
             g0 = g1;
         }
-        // ---- one read-back: offsets + the overflow word
-        OVIS_TRY(ensure_pinned(w->h_mv_result, w->cap_h_mv_result, sizeof(long long) * ((size_t)n_views + 3)));
-        long long *hr = static_cast<long long *>(w->h_mv_result);
-        OVIS_CUDA(cudaMemcpyAsync(hr, w->d_csr_offsets, sizeof(long long) * ((size_t)n_views + 1), cudaMemcpyDeviceToHost, w->stream));
-        OVIS_CUDA(cudaMemcpyAsync(hr + n_views + 1, w->d_mv_state, 4 * sizeof(uint32_t), cudaMemcpyDeviceToHost, w->stream));
+        // ---- read-back: the scan kernel of every round has stored its offsets and the state words in page-locked host
+        // memory (hr), nothing is copied
         w->mv_spec_copied = 0;
         if (w->mv_spec_out && w->mv_spec_cap > 0) {
             const int64_t guess = std::min(std::min(w->mv_spec_cap, w->cap_csr), w->mv_last_total + w->mv_last_total / 4 + 1024);
@@ -1167,6 +1215,11 @@ int cull_views_grouped(OvisWorld *w, int32_t n_views, const float *planes, const
         const uint32_t overflow = state[0];
         if (overflow & ovis::kMvOverflowPairs) {         // some block was too dense for the sparse pass: everything densely
             force_dense = true;
+            continue;
+        }
+        if (overflow & ovis::kMvOverflowHits) {          // more entities near lights in some block than its list holds
+            const int64_t want = (int64_t)state[4] + state[4] / 4;
+            w->mv_hit_cap = (int)std::min<int64_t>(ovis::kMaskBlockEntities, std::max<int64_t>(2 * (int64_t)w->mv_hit_cap, (want + 255) / 256 * 256));
             continue;
         }
         if (overflow & (ovis::kMvOverflowItems | ovis::kMvOverflowNodes)) {
@@ -1331,7 +1384,7 @@ int ovis_world_destroy(OvisWorld *w) {
                      w->d_node_entity, w->d_dirty, w->d_light_uniforms, w->d_light_types, w->d_entity_node, w->d_pass_counts, w->d_draw_totals, w->d_draw_counts,
                      w->d_extra_entity, w->d_extra_node, w->d_level_lists, w->d_lights, w->d_light_out, w->d_light_bits,
                      w->d_survivors, w->d_block_totals, w->d_exchange, w->d_mv_stage, w->d_mv_state, w->d_mv_heads, w->d_mv_totals,
-                     w->d_mv_masks, w->d_mv_node_group, w->d_mv_node_next, w->d_mv_items, w->d_mv_segments, w->d_result, w->d_counts, w->d_csr_entities, w->d_csr_offsets,
+                     w->d_mv_masks, w->d_mv_hits, w->d_mv_work, w->d_mv_node_group, w->d_mv_node_next, w->d_mv_items, w->d_mv_segments, w->d_result, w->d_counts, w->d_csr_entities, w->d_csr_offsets,
                      w->d_stage[0], w->d_stage[1] };
     for (void *b : bufs)
         if (b)
