@@ -110,6 +110,7 @@ struct MvGroup {                  // one cube group
 struct MvGrid {
     float lo[3], hi[3];          // exact bounds of the union of the groups' cubes
     float inv_cell[3];           // cells per unit length
+    float bias[3];               // -lo * inv_cell: cell of v = floor(fma(v, inv_cell, bias)), the same expression on host and device
     int dim[3];                  // cells per axis (<= kMvGridMax)
 };
 
@@ -148,8 +149,8 @@ struct MvArgs {
     MvGrid grid;
     unsigned long long *bitmap;  // [dim z][dim y]: bit x = some cube covers the cell
     int32_t *heads;              // per cell: first node of its group list, -1 = none
-    uint32_t *node_group;        // per node: group index
-    int32_t *node_next;
+    uint4 *nodes;                // per node two: (group | first cell x << 12 | y << 18 | z << 24, next node, cube lo x, lo y),
+                                 // (lo z, hi x, hi y, hi z): all a cell's visitor needs of the group, in one sector
     uint32_t node_capacity;
     MvItem *items;
     uint32_t item_capacity;

@@ -36,6 +36,7 @@
 namespace ovis {
 
 constexpr int kMvThreads = 256;
+constexpr int kMvRankSortBelow = 320;    // candidate pairs of a block up to which they are sorted by counting (<= kMvPairCapacity / 2)
 
 // The kernels of one round are a chain of short launches. Each is launched with programmatic stream serialization and
 // starts with these two instructions: "my dependents may be scheduled" and "wait until everything before me in the stream
@@ -387,8 +388,11 @@ mv_bin_lights_kernel(const __grid_constant__ MvArgs a) {
             atomicOr(a.state, kMvOverflowNodes);
             continue;
         }
-        a.node_group[node] = (uint32_t)g;
-        a.node_next[node] = atomicExch(a.heads + ((int64_t)z * a.grid.dim[1] + y) * a.grid.dim[0] + x, (int32_t)node);
+        const int32_t next = atomicExch(a.heads + ((int64_t)z * a.grid.dim[1] + y) * a.grid.dim[0] + x, (int32_t)node);
+        a.nodes[2 * node] = make_uint4((uint32_t)g | ((uint32_t)x0 << 12) | ((uint32_t)y0 << 18) | ((uint32_t)z0 << 24), (uint32_t)next,
+                                       __float_as_uint(grp.lo[0]), __float_as_uint(grp.lo[1]));
+        a.nodes[2 * node + 1] = make_uint4(__float_as_uint(grp.lo[2]), __float_as_uint(grp.hi[0]), __float_as_uint(grp.hi[1]),
+                                           __float_as_uint(grp.hi[2]));
         atomicOr(a.bitmap + z * a.grid.dim[1] + y, 1ull << x);
     }
 }
@@ -397,19 +401,18 @@ struct CellRange {
     int x0, x1, y0, y1, z0, z1;
 };
 
-// cell index of a coordinate: the same monotone function on the host (for the groups: floor, clamp in float, convert)
-// and here (for the entities: convert with round-down and saturation, clamp as integers - the same value for every input,
-// NaN included), so two intervals that overlap in space always share a cell
-__device__ __forceinline__ int cell_of(float v, float lo, float inv, int dim) {
-    return min(max(__float2int_rd(__fmul_rn(__fsub_rn(v, lo), inv)), 0), dim - 1);
+// cell index of a coordinate: the same monotone function on the host (for the groups: fmaf, floor, clamp in float, convert)
+// and here (for the entities: fma, convert to unsigned with round-down and saturation - negatives and NaN give 0 -, clamp),
+// so two intervals that overlap in space always share a cell
+__device__ __forceinline__ int cell_of(float v, float inv, float bias, int dim) {
+    return (int)min(__float2uint_rd(__fmaf_rn(v, inv, bias)), (uint32_t)(dim - 1));
 }
 
 // K6 pre-filter, entity side: the box inflated by Re = 1.001 * largest extent + 1e-3 * largest |coordinate|.
 // Returns 0: no cube can reach it; 1: candidates are in the cells of `r`, at most 2 x 2 rows of the bitmap; 2: test every
 // group (a box with a NaN or non-finite side can never be rejected - *odd; a box that spans more rows is cheaper to test
 // against every cube). Branch-free on purpose: it runs for every entity of the world.
-__device__ __forceinline__ int entity_cells(const MvGrid &g, const float mn[3], const float mx[3], float lo[3], float hi[3],
-                                            CellRange &r, bool *odd) {
+__device__ __forceinline__ void inflate_box(const float mn[3], const float mx[3], float lo[3], float hi[3], bool *odd) {
     const float sx = mx[0] - mn[0], sy = mx[1] - mn[1], sz = mx[2] - mn[2];
     const float ext = fmaxf(fmaxf(fmaxf(sx, sy), sz), 0.0f);
     const float mag = fmaxf(fmaxf(fmaxf(fabsf(mn[0]), fabsf(mx[0])), fmaxf(fabsf(mn[1]), fabsf(mx[1]))),
@@ -421,10 +424,15 @@ __device__ __forceinline__ int entity_cells(const MvGrid &g, const float mn[3], 
         lo[c] = mn[c] - re;
         hi[c] = mx[c] + re;
     }
+}
+
+__device__ __forceinline__ int entity_cells(const MvGrid &g, const float mn[3], const float mx[3], float lo[3], float hi[3],
+                                            CellRange &r, bool *odd) {
+    inflate_box(mn, mx, lo, hi, odd);
     const bool outside = (hi[0] < g.lo[0]) | (lo[0] > g.hi[0]) | (hi[1] < g.lo[1]) | (lo[1] > g.hi[1]) | (hi[2] < g.lo[2]) | (lo[2] > g.hi[2]);
-    r.x0 = cell_of(lo[0], g.lo[0], g.inv_cell[0], g.dim[0]); r.x1 = cell_of(hi[0], g.lo[0], g.inv_cell[0], g.dim[0]);
-    r.y0 = cell_of(lo[1], g.lo[1], g.inv_cell[1], g.dim[1]); r.y1 = cell_of(hi[1], g.lo[1], g.inv_cell[1], g.dim[1]);
-    r.z0 = cell_of(lo[2], g.lo[2], g.inv_cell[2], g.dim[2]); r.z1 = cell_of(hi[2], g.lo[2], g.inv_cell[2], g.dim[2]);
+    r.x0 = cell_of(lo[0], g.inv_cell[0], g.bias[0], g.dim[0]); r.x1 = cell_of(hi[0], g.inv_cell[0], g.bias[0], g.dim[0]);
+    r.y0 = cell_of(lo[1], g.inv_cell[1], g.bias[1], g.dim[1]); r.y1 = cell_of(hi[1], g.inv_cell[1], g.bias[1], g.dim[1]);
+    r.z0 = cell_of(lo[2], g.inv_cell[2], g.bias[2], g.dim[2]); r.z1 = cell_of(hi[2], g.inv_cell[2], g.bias[2], g.dim[2]);
     const bool big = (r.y1 - r.y0 > 1) | (r.z1 - r.z0 > 1);
     return *odd ? 2 : (outside ? 0 : (big ? 2 : 1));
 }
@@ -435,10 +443,13 @@ __device__ __forceinline__ unsigned long long x_range_bits(int x0, int x1) {
 
 // candidate iff the inflated box overlaps the group's (inflated) cube: separated along some axis <=> the largest of the
 // six gaps is > 0 (a NaN gap is ignored by fmaxf, an all-NaN set compares false: such boxes stay candidates)
-__device__ __forceinline__ bool overlaps_cube(const MvGroup &grp, const float lo[3], const float hi[3]) {
-    const float gap = fmaxf(fmaxf(fmaxf(grp.lo[0] - hi[0], lo[0] - grp.hi[0]), fmaxf(grp.lo[1] - hi[1], lo[1] - grp.hi[1])),
-                            fmaxf(grp.lo[2] - hi[2], lo[2] - grp.hi[2]));
+__device__ __forceinline__ bool overlaps_cube(const float glo[3], const float ghi[3], const float lo[3], const float hi[3]) {
+    const float gap = fmaxf(fmaxf(fmaxf(glo[0] - hi[0], lo[0] - ghi[0]), fmaxf(glo[1] - hi[1], lo[1] - ghi[1])),
+                            fmaxf(glo[2] - hi[2], lo[2] - ghi[2]));
     return !(gap > 0.0f);
+}
+__device__ __forceinline__ bool overlaps_cube(const MvGroup &grp, const float lo[3], const float hi[3]) {
+    return overlaps_cube(grp.lo, grp.hi, lo, hi);
 }
 
 __device__ __forceinline__ void load_box(const MvArgs &a, int64_t e, float mn[3], float mx[3]) {
@@ -520,14 +531,15 @@ mv_classify_kernel(const __grid_constant__ MvArgs a) {
             // kind 1 spans at most 2 x 2 rows: look at the four corner rows (duplicates when it spans fewer)
             const unsigned long long seen = (s_bitmap[r.z0 * dim_y + r.y0] | s_bitmap[r.z0 * dim_y + r.y1]) |
                                             (s_bitmap[r.z1 * dim_y + r.y0] | s_bitmap[r.z1 * dim_y + r.y1]);
-            const bool occupied = (seen & x_range_bits(r.x0, r.x1)) != 0ull;
+            const bool occupied = ((seen >> r.x0) << (63 - (r.x1 - r.x0))) != 0ull;       // any of bits x0 .. x1
             big |= (kind == 2 ? 1u : 0u) << j;
             hit |= ((kind == 1) & occupied ? 1u : 0u) << j;
         }
         // the classified entities leave as records (box + index inside the block) appended to their block's list: what
         // mv_sparse_kernel needs of them arrives there in one coalesced read (reading the boxes back out of the SoA arrays
-        // cost it six sectors per entity, as much traffic as this whole pass). Order inside a list is whatever the atomics
-        // give; the records are sorted further down the line.
+        // cost it six sectors per entity, as much traffic as this whole pass). One atomic per group of 128 reserves the slots
+        // (one per entity-of-the-lane round was tried: four dependent round trips per group, the pass went from 77 to 93 us).
+        // Order inside a list is whatever the atomics give; the records are sorted further down the line.
         const uint32_t mine = (hit | big) & alive;
         if (__any_sync(0xffffffffu, mine != 0u)) {
             const uint32_t count = __popc(mine);
@@ -560,10 +572,10 @@ mv_classify_kernel(const __grid_constant__ MvArgs a) {
 }
 
 // K6, entity side, pair half: one CTA per block of 8192 entities that has classified entities.
-__global__ void __launch_bounds__(kMvThreads, 4)
+__global__ void __launch_bounds__(kMvThreads, 6)
 mv_sparse_kernel(const __grid_constant__ MvArgs a) {
     chain_enter();
-    __shared__ uint32_t s_pairs[kMvPairCapacity];
+    __shared__ __align__(16) uint32_t s_pairs[kMvPairCapacity];
     __shared__ uint32_t s_big[64];                             // records tested against every group (rare: huge or odd boxes)
     __shared__ uint32_t s_npairs, s_nrec, s_item_base, s_nbig;
     __shared__ uint32_t s_warp[kMvThreads / 32];
@@ -593,10 +605,19 @@ mv_sparse_kernel(const __grid_constant__ MvArgs a) {
     const float4 *__restrict__ list = a.hit_records + (int64_t)b * (2 * a.hit_capacity);
 
     // ---- (2) candidate pairs: a thread takes every 256th record of the block
+    float4 n0 = make_float4(0.f, 0.f, 0.f, 0.f), n1 = n0;       // the next record is requested before this one's lists are walked
+    if ((uint32_t)tid < n_hits) {
+        n0 = __ldg(list + 2 * tid);
+        n1 = __ldg(list + 2 * tid + 1);
+    }
     for (uint32_t h = tid; h < n_hits; h += kMvThreads) {
-        const float4 r0 = __ldg(list + 2 * h), r1 = __ldg(list + 2 * h + 1);
+        const float4 r0 = n0, r1 = n1;
+        if (h + kMvThreads < n_hits) {
+            n0 = __ldg(list + 2 * (h + kMvThreads));
+            n1 = __ldg(list + 2 * (h + kMvThreads) + 1);
+        }
         const float mn[3] = { r0.x, r0.y, r0.z }, mx[3] = { r0.w, r1.x, r1.y };
-        const uint32_t tag = __float_as_uint(r1.z), el = tag & (kMaskBlockEntities - 1);
+        const uint32_t tag = __float_as_uint(r1.z);
         float lo[3], hi[3];
         CellRange r;
         bool odd;
@@ -608,7 +629,7 @@ mv_sparse_kernel(const __grid_constant__ MvArgs a) {
             } else {                                           // (more than 64 such boxes in one block: this thread alone)
                 for (int g = 0; g < a.n_groups; g++)
                     if (odd || overlaps_cube(a.groups[g], lo, hi))
-                        append_pair(s_pairs, &s_npairs, (uint32_t)g, el);
+                        append_pair(s_pairs, &s_npairs, (uint32_t)g, h);
             }
             continue;
         }
@@ -619,16 +640,18 @@ mv_sparse_kernel(const __grid_constant__ MvArgs a) {
                 while (occupied) {
                     const int x = __ffsll((long long)occupied) - 1;
                     occupied &= occupied - 1;
-                    for (int32_t node = a.heads[((int64_t)z * a.grid.dim[1] + y) * a.grid.dim[0] + x]; node >= 0; node = a.node_next[node]) {
-                        const uint32_t g = a.node_group[node];
-                        const MvGroup grp = a.groups[g];
+                    for (int32_t node = a.heads[((int64_t)z * a.grid.dim[1] + y) * a.grid.dim[0] + x]; node >= 0;) {
+                        const uint4 q0 = __ldg(a.nodes + 2 * node), q1 = __ldg(a.nodes + 2 * node + 1);
+                        node = (int32_t)q0.y;
                         // a group shared by several of the entity's cells is taken in the first of them only
-                        const int gx = max(r.x0, (int)(grp.cell_lo & 255)), gy = max(r.y0, (int)((grp.cell_lo >> 8) & 255)),
-                                  gz = max(r.z0, (int)((grp.cell_lo >> 16) & 255));
+                        const int gx = max(r.x0, (int)((q0.x >> 12) & 63u)), gy = max(r.y0, (int)((q0.x >> 18) & 63u)),
+                                  gz = max(r.z0, (int)((q0.x >> 24) & 63u));
                         if (x != gx || y != gy || z != gz)
                             continue;
-                        if (overlaps_cube(grp, lo, hi))
-                            append_pair(s_pairs, &s_npairs, g, el);
+                        const float glo[3] = { __uint_as_float(q0.z), __uint_as_float(q0.w), __uint_as_float(q1.x) };
+                        const float ghi[3] = { __uint_as_float(q1.y), __uint_as_float(q1.z), __uint_as_float(q1.w) };
+                        if (overlaps_cube(glo, ghi, lo, hi))
+                            append_pair(s_pairs, &s_npairs, q0.x & 4095u, h);
                     }
                 }
             }
@@ -639,14 +662,13 @@ mv_sparse_kernel(const __grid_constant__ MvArgs a) {
         const uint32_t h = s_big[k];
         const float4 r0 = __ldg(list + 2 * h), r1 = __ldg(list + 2 * h + 1);
         const float mn[3] = { r0.x, r0.y, r0.z }, mx[3] = { r0.w, r1.x, r1.y };
-        const uint32_t el = __float_as_uint(r1.z) & (kMaskBlockEntities - 1);
         float lo[3], hi[3];
         CellRange r;
         bool odd;
         entity_cells(a.grid, mn, mx, lo, hi, r, &odd);
         for (int g = tid; g < a.n_groups; g += kMvThreads)
             if (odd || overlaps_cube(a.groups[g], lo, hi))
-                append_pair(s_pairs, &s_npairs, (uint32_t)g, el);
+                append_pair(s_pairs, &s_npairs, (uint32_t)g, h);
     }
     __syncthreads();
     const uint32_t npairs = s_npairs;
@@ -667,10 +689,11 @@ mv_sparse_kernel(const __grid_constant__ MvArgs a) {
     uint32_t n_valid = 0;
     for (uint32_t i = tid; i < npairs; i += kMvThreads) {
         const uint32_t pair = s_pairs[i];
-        const uint32_t g = pair >> 13, el = pair & 8191u;
+        const uint32_t g = pair >> 13, h = pair & 8191u;       // (group, record): the box comes from the record, one sector
+        const float4 r0 = __ldg(list + 2 * h), r1 = __ldg(list + 2 * h + 1);
+        const float mn[3] = { r0.x, r0.y, r0.z }, mx[3] = { r0.w, r1.x, r1.y };
+        const uint32_t el = __float_as_uint(r1.z) & (kMaskBlockEntities - 1);
         const int64_t e = block_e0 + el;
-        float mn[3], mx[3];
-        load_box(a, e, mn, mx);
         const bool caster = a.caster_mask ? ((__ldg(a.caster_mask + (e >> 5)) >> (e & 31)) & 1u) != 0 : true;
         const MvGroup grp = a.groups[g];
         uint32_t fm = 0;
@@ -688,19 +711,16 @@ mv_sparse_kernel(const __grid_constant__ MvArgs a) {
             if (inside)
                 fm |= 1u << f;
         }
-        s_pairs[i] = fm ? ((pair << 6) | fm) : 0xffffffffu;
+        s_pairs[i] = fm ? ((((g << 13) | el) << 6) | fm) : 0xffffffffu;
         n_valid += fm ? 1u : 0u;
     }
     n_valid = __reduce_add_sync(0xffffffffu, n_valid);
     if (lane == 0 && n_valid)
         atomicAdd(&s_nrec, n_valid);
 
-    // ---- (4) sort the records by (group, entity): bitonic, in shared memory
-    uint32_t n_sort = 32;
-    while (n_sort < npairs)
-        n_sort <<= 1;
-    for (uint32_t i = npairs + tid; i < n_sort; i += kMvThreads)
-        s_pairs[i] = 0xffffffffu;
+    // ---- (4) sort the surviving records by (group, entity), in shared memory. A few hundred pairs (the usual block) are
+    // ranked by counting: every thread counts the keys below its own - one barrier instead of the 36 of a bitonic network
+    // over 256 keys (ncu: those barriers were a sixth of the kernel). Keys are unique (a pair is appended once).
     __syncthreads();
     const uint32_t nrec = s_nrec;
     if (nrec == 0) {
@@ -708,21 +728,49 @@ mv_sparse_kernel(const __grid_constant__ MvArgs a) {
             a.segments[b] = make_uint2(0u, 0u);
         return;
     }
-    for (uint32_t k = 2; k <= n_sort; k <<= 1)
-        for (uint32_t j = k >> 1; j > 0; j >>= 1) {
-            for (uint32_t i = tid; i < n_sort; i += kMvThreads) {
-                const uint32_t partner = i ^ j;
-                if (partner > i) {
-                    const uint32_t x = s_pairs[i], y = s_pairs[partner];
-                    const bool ascending = (i & k) == 0;
-                    if ((x > y) == ascending) {
-                        s_pairs[i] = y;
-                        s_pairs[partner] = x;
+    const uint32_t *s_rec = s_pairs;
+    if (npairs <= (uint32_t)kMvRankSortBelow) {
+        uint32_t *s_out = s_pairs + kMvPairCapacity / 2;
+        const uint32_t padded = (npairs + 3u) & ~3u;
+        for (uint32_t i = npairs + tid; i < padded; i += kMvThreads)
+            s_pairs[i] = 0xffffffffu;
+        __syncthreads();
+        for (uint32_t i = tid; i < npairs; i += kMvThreads) {
+            const uint32_t key = s_pairs[i];
+            if (key == 0xffffffffu)
+                continue;
+            uint32_t rank = 0;
+            for (uint32_t j = 0; j < padded; j += 4) {
+                const uint4 q = *reinterpret_cast<const uint4 *>(s_pairs + j);
+                rank += (q.x < key ? 1u : 0u) + (q.y < key ? 1u : 0u) + (q.z < key ? 1u : 0u) + (q.w < key ? 1u : 0u);
+            }
+            s_out[rank] = key;
+        }
+        __syncthreads();
+        s_rec = s_out;
+    } else {
+        uint32_t n_sort = 32;
+        while (n_sort < npairs)
+            n_sort <<= 1;
+        for (uint32_t i = npairs + tid; i < n_sort; i += kMvThreads)
+            s_pairs[i] = 0xffffffffu;
+        __syncthreads();
+        for (uint32_t k = 2; k <= n_sort; k <<= 1)
+            for (uint32_t j = k >> 1; j > 0; j >>= 1) {
+                for (uint32_t i = tid; i < n_sort; i += kMvThreads) {
+                    const uint32_t partner = i ^ j;
+                    if (partner > i) {
+                        const uint32_t x = s_pairs[i], y = s_pairs[partner];
+                        const bool ascending = (i & k) == 0;
+                        if ((x > y) == ascending) {
+                            s_pairs[i] = y;
+                            s_pairs[partner] = x;
+                        }
                     }
                 }
+                __syncthreads();
             }
-            __syncthreads();
-        }
+    }
 
     // ---- (5) rank inside (view, block), totals, items. Thread t owns records [t * per, (t + 1) * per).
     const uint32_t per = (nrec + kMvThreads - 1) / kMvThreads;
@@ -730,9 +778,9 @@ mv_sparse_kernel(const __grid_constant__ MvArgs a) {
     SegCount mine = { 0u, 0u, 0u, false };
     uint32_t my_items = 0;
     {
-        uint32_t prev_g = i0 > 0 ? s_pairs[i0 - 1] >> 19 : 0xffffffffu;
+        uint32_t prev_g = i0 > 0 ? s_rec[i0 - 1] >> 19 : 0xffffffffu;
         for (uint32_t i = i0; i < i1; i++) {
-            const uint32_t key = s_pairs[i], g = key >> 19, fm = key & 63u;
+            const uint32_t key = s_rec[i], g = key >> 19, fm = key & 63u;
             if (g != prev_g) {
                 mine = { 0u, 0u, 0u, true };
                 prev_g = g;
@@ -783,12 +831,12 @@ mv_sparse_kernel(const __grid_constant__ MvArgs a) {
     }
     {
         SegCount run = carry;
-        uint32_t prev_g = i0 > 0 ? s_pairs[i0 - 1] >> 19 : 0xffffffffu;
+        uint32_t prev_g = i0 > 0 ? s_rec[i0 - 1] >> 19 : 0xffffffffu;
         uint32_t slot = item_base + item_rank;
         int first_view = 0;
         const int row = a.num_blocks + 1;
         for (uint32_t i = i0; i < i1; i++) {
-            const uint32_t key = s_pairs[i], g = key >> 19, el = (key >> 6) & 8191u;
+            const uint32_t key = s_rec[i], g = key >> 19, el = (key >> 6) & 8191u;
             uint32_t fm = key & 63u;
             if (g != prev_g || i == i0) {
                 if (g != prev_g)
@@ -804,7 +852,7 @@ mv_sparse_kernel(const __grid_constant__ MvArgs a) {
                 slot++;
             }
             seg_add(run, fm);
-            const uint32_t next_g = i + 1 < nrec ? s_pairs[i + 1] >> 19 : 0xffffffffu;
+            const uint32_t next_g = i + 1 < nrec ? s_rec[i + 1] >> 19 : 0xffffffffu;
             if (next_g != g) {                                  // the group's run ends here: its totals for this block
 #pragma unroll
                 for (int f = 0; f < kMvMaxGroupViews; f++) {

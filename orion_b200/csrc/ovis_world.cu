@@ -173,8 +173,7 @@ struct OvisWorld {
     int mv_hit_cap = 1024;                // records per block (grown on demand, at most one per entity of the block)
     uint32_t *d_mv_work = nullptr;        // ... and how many
     int64_t cap_mv_work = 0;
-    uint32_t *d_mv_node_group = nullptr;
-    int32_t *d_mv_node_next = nullptr;
+    uint4 *d_mv_nodes = nullptr;          // light grid: two per node (ovis_kernels.h, MvArgs::nodes)
     int64_t cap_mv_nodes = 0;
     ovis::MvItem *d_mv_items = nullptr;
     int64_t cap_mv_items = 0;
@@ -957,13 +956,14 @@ int64_t build_light_grid(std::vector<ovis::MvGroup> &groups, ovis::MvGrid &grid,
             float cells = std::ceil(extent[c] / cell);
             grid.dim[c] = (int)std::min(std::max(cells, 1.0f), (float)ovis::kMvGridMax);
             grid.inv_cell[c] = 1.0f / cell;
+            grid.bias[c] = -(grid.lo[c] * grid.inv_cell[c]);
         }
         int64_t nodes = 0;
         for (ovis::MvGroup &g : groups) {
             int lo[3], hi[3];
             for (int c = 0; c < 3; c++) {
-                float a = std::floor((g.lo[c] - grid.lo[c]) * grid.inv_cell[c]);
-                float b = std::floor((g.hi[c] - grid.lo[c]) * grid.inv_cell[c]);
+                float a = std::floor(std::fmaf(g.lo[c], grid.inv_cell[c], grid.bias[c]));
+                float b = std::floor(std::fmaf(g.hi[c], grid.inv_cell[c], grid.bias[c]));
                 lo[c] = (int)std::min(std::max(a, 0.0f), (float)(grid.dim[c] - 1));
                 hi[c] = (int)std::min(std::max(b, 0.0f), (float)(grid.dim[c] - 1));
             }
@@ -1114,8 +1114,7 @@ int cull_views_grouped(OvisWorld *w, int32_t n_views, const float *planes, const
             if (!cubes.empty()) {
                 if (nodes > w->cap_mv_nodes) {
                     const int64_t fresh = std::max<int64_t>(nodes + nodes / 2, 1 << 16);
-                    OVIS_TRY(grow(w->d_mv_node_group, 0, fresh, w->stream, false));
-                    OVIS_TRY(grow(w->d_mv_node_next, 0, fresh, w->stream, false));
+                    OVIS_TRY(grow(w->d_mv_nodes, 0, 2 * fresh, w->stream, false));
                     w->cap_mv_nodes = fresh;
                 }
                 OVIS_TRY(ensure(w->d_mv_items, w->cap_mv_items, std::max<int64_t>((int64_t)1 << 20, w->n_ent / 8), w->stream));
@@ -1156,8 +1155,7 @@ int cull_views_grouped(OvisWorld *w, int32_t n_views, const float *planes, const
             a.n_groups = (int)cubes.size();
             a.bitmap = reinterpret_cast<unsigned long long *>(w->d_mv_state + kMvBitmapOffset);
             a.heads = w->d_mv_heads;
-            a.node_group = w->d_mv_node_group;
-            a.node_next = w->d_mv_node_next;
+            a.nodes = w->d_mv_nodes;
             a.node_capacity = (uint32_t)std::min<int64_t>(w->cap_mv_nodes, 0xffffffffll);
             a.items = w->d_mv_items;
             a.item_capacity = (uint32_t)std::min<int64_t>(w->cap_mv_items, 0xffffffffll);
@@ -1384,7 +1382,7 @@ int ovis_world_destroy(OvisWorld *w) {
                      w->d_node_entity, w->d_dirty, w->d_light_uniforms, w->d_light_types, w->d_entity_node, w->d_pass_counts, w->d_draw_totals, w->d_draw_counts,
                      w->d_extra_entity, w->d_extra_node, w->d_level_lists, w->d_lights, w->d_light_out, w->d_light_bits,
                      w->d_survivors, w->d_block_totals, w->d_exchange, w->d_mv_stage, w->d_mv_state, w->d_mv_heads, w->d_mv_totals,
-                     w->d_mv_masks, w->d_mv_hits, w->d_mv_work, w->d_mv_node_group, w->d_mv_node_next, w->d_mv_items, w->d_mv_segments, w->d_result, w->d_counts, w->d_csr_entities, w->d_csr_offsets,
+                     w->d_mv_masks, w->d_mv_hits, w->d_mv_work, w->d_mv_nodes, w->d_mv_items, w->d_mv_segments, w->d_result, w->d_counts, w->d_csr_entities, w->d_csr_offsets,
                      w->d_stage[0], w->d_stage[1] };
     for (void *b : bufs)
         if (b)
