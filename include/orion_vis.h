@@ -281,6 +281,17 @@ int ovis_sharded_cull(OvisShardedWorld *world, const OvisView *view, uint32_t re
                       int64_t cap_entities, int64_t *out_n_entities, int64_t *out_shard_counts);
 int ovis_sharded_cull_planes(OvisShardedWorld *world, const float planes[24], uint32_t require, uint32_t *out_entities,
                              int64_t cap_entities, int64_t *out_n_entities, int64_t *out_shard_counts);
+/* Lights are replicated: every shard's world receives the same lights under the same ids (render_world.h:69-72). */
+int ovis_sharded_add_lights(OvisShardedWorld *world, int32_t n, const OvisLight *lights, uint32_t *out_first_id);
+/* ovis_cull_views / ovis_build_shadow_lists over all shards (BASELINE configs[4]: "then 5 views"): every shard runs the
+ * many-view pass on its entities into its own page-locked CSR, the caller's thread splices list v of shard 0, 1, ... one
+ * after the other - per view that is the single-world list, ids global and ascending. Same arguments, outputs and
+ * OVIS_ERR_CAPACITY behaviour as the single-world calls. */
+int ovis_sharded_cull_views(OvisShardedWorld *world, int32_t n_views, const float *planes, const uint32_t *require,
+                            int64_t *out_offsets, int64_t cap_entities, uint32_t *out_entities, int64_t *out_n_entities);
+int ovis_sharded_build_shadow_lists(OvisShardedWorld *world, const OvisView *main_view, int32_t shadow_map_resolution,
+                                    int32_t cap_lists, int32_t *out_list_light, int32_t *out_list_view, int64_t *out_offsets,
+                                    int32_t *out_n_lists, int64_t cap_entities, uint32_t *out_entities, int64_t *out_n_entities);
 /* The page-locked segments of the last ovis_sharded_cull*: shard r's [count | ids...] at segments + r * segment_words. */
 int ovis_sharded_segments(OvisShardedWorld *world, const uint32_t **out_segments, int64_t *out_segment_words);
 /* For DEVICE consumers: the local culls, then one ncclAllGather per device of fixed-size [count | ids...] blocks of
@@ -317,6 +328,11 @@ int ovis_cull_planes_noalloc(int device, void *cuda_stream, const float *d_world
  * host_offsets (optional, n_views + 1) receives a synchronous copy of the offsets. */
 int ovis_cull_views_device(OvisWorld *world, int32_t n_views, const float *planes, const uint32_t *require,
                            const int64_t **d_offsets, const uint32_t **d_entities, int64_t *host_offsets);
+
+/* The same pass with HOST output: out_offsets receives n_views + 1 entries, out_entities the lists back to back.
+ * OVIS_ERR_CAPACITY (with *out_n_entities = required) if cap_entities is too small. */
+int ovis_cull_views(OvisWorld *world, int32_t n_views, const float *planes, const uint32_t *require, int64_t *out_offsets,
+                    int64_t cap_entities, uint32_t *out_entities, int64_t *out_n_entities);
 
 /* The shadow-view culls of prepareLights (deferred_render_pipeline.cc:259-284) for an explicit set of lights,
  * regardless of their visibility: every shadow view (RenderLight::updateShadowViews, render_light.cc:258-332; six

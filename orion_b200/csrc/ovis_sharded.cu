@@ -77,7 +77,14 @@ struct Worker {
     int rc = OVIS_OK;
     std::string error;
     int64_t count = 0;
+    // many-view jobs: this shard's CSR (page-locked entity buffer, grown by the worker itself)
+    std::vector<int64_t> offsets;
+    std::vector<int32_t> list_light, list_view;
+    int32_t n_lists = 0;
+    uint32_t *h_entities = nullptr;
+    int64_t cap_entities = 0;
 };
+enum JobKind { kJobCull = 0, kJobViews = 1, kJobShadowLists = 2 };
 
 }  // namespace
 
@@ -94,6 +101,13 @@ struct OvisShardedWorld {
     // the job: one cull of every shard into the shared host segments
     float planes[24];
     uint32_t require = 0;
+    int kind = kJobCull;
+    // ... or one many-view pass of every shard into its worker's CSR
+    int32_t n_views = 0;
+    const float *view_planes = nullptr;
+    const uint32_t *view_require = nullptr;
+    OvisView main_view;
+    int32_t shadow_res = 0;
     uint32_t *h_segments = nullptr;                 // portable pinned: n x (1 + seg_capacity) words
     int64_t seg_capacity = 0;
     // device consumers (NCCL)
@@ -105,6 +119,46 @@ struct OvisShardedWorld {
 };
 
 namespace {
+
+// One many-view pass of shard r into the worker's own buffers; a result that outgrows them is repeated once with more room.
+void many_views_job(OvisShardedWorld *sw, int r) {
+    Worker &me = sw->workers[r];
+    for (int attempt = 0; attempt < 3; attempt++) {
+        int64_t total = 0;
+        if (sw->kind == kJobViews) {
+            me.offsets.assign((size_t)sw->n_views + 1, 0);
+            me.n_lists = sw->n_views;
+            me.rc = ovis_cull_views(sw->shards[r], sw->n_views, sw->view_planes, sw->view_require, me.offsets.data(), me.cap_entities,
+                                    me.h_entities, &total);
+        } else {
+            int32_t n_lights = 0;
+            ovis_world_counts(sw->shards[r], nullptr, nullptr, &n_lights);
+            const size_t cap_lists = 6 * (size_t)std::max(n_lights, 1);
+            me.list_light.resize(cap_lists);
+            me.list_view.resize(cap_lists);
+            me.offsets.assign(cap_lists + 1, 0);
+            me.rc = ovis_build_shadow_lists(sw->shards[r], &sw->main_view, sw->shadow_res, (int32_t)cap_lists, me.list_light.data(),
+                                            me.list_view.data(), me.offsets.data(), &me.n_lists, me.cap_entities, me.h_entities, &total);
+        }
+        me.count = total;
+        if (me.rc != OVIS_ERR_CAPACITY || total <= me.cap_entities)
+            break;
+        if (me.h_entities)
+            ovis_host_free(me.h_entities);
+        me.h_entities = nullptr;
+        me.cap_entities = 0;
+        void *p = nullptr;
+        const int64_t want = total + total / 4 + 4096;
+        if (ovis_host_alloc((int64_t)sizeof(uint32_t) * want, &p) != OVIS_OK) {
+            me.rc = OVIS_ERR_NOMEM;
+            break;
+        }
+        me.h_entities = static_cast<uint32_t *>(p);
+        me.cap_entities = want;
+    }
+    if (me.rc != OVIS_OK)
+        me.error = ovis_last_error();
+}
 
 void worker_loop(OvisShardedWorld *sw, int r) {
     cudaSetDevice(sw->devices[r]);
@@ -126,13 +180,17 @@ void worker_loop(OvisShardedWorld *sw, int r) {
         }
         if (sw->quit.load(std::memory_order_relaxed))
             return;
-        uint32_t *seg = sw->h_segments + (int64_t)r * (1 + sw->seg_capacity);
-        int64_t count = 0;
-        me.rc = ovis_cull_planes(sw->shards[r], sw->planes, sw->require, seg + 1, sw->seg_capacity, &count);
-        if (me.rc != OVIS_OK)
-            me.error = ovis_last_error();
-        me.count = count;
-        seg[0] = (uint32_t)count;
+        if (sw->kind == kJobCull) {
+            uint32_t *seg = sw->h_segments + (int64_t)r * (1 + sw->seg_capacity);
+            int64_t count = 0;
+            me.rc = ovis_cull_planes(sw->shards[r], sw->planes, sw->require, seg + 1, sw->seg_capacity, &count);
+            if (me.rc != OVIS_OK)
+                me.error = ovis_last_error();
+            me.count = count;
+            seg[0] = (uint32_t)count;
+        } else {
+            many_views_job(sw, r);
+        }
         seen = posted;
         me.finished.store(posted, std::memory_order_release);
     }
@@ -231,6 +289,9 @@ int ovis_sharded_destroy(OvisShardedWorld *sw) {
     }
     if (sw->h_segments)
         cudaFreeHost(sw->h_segments);
+    for (Worker &w : sw->workers)
+        if (w.h_entities)
+            ovis_host_free(w.h_entities);
     delete sw;
     return OVIS_OK;
 }
@@ -328,6 +389,100 @@ int ovis_sharded_cull(OvisShardedWorld *sw, const OvisView *view, uint32_t requi
     if (rc != OVIS_OK)
         return rc;
     return ovis_sharded_cull_planes(sw, planes, require, out_entities, cap_entities, out_n_entities, out_shard_counts);
+}
+
+int ovis_sharded_add_lights(OvisShardedWorld *sw, int32_t n, const OvisLight *lights, uint32_t *out_first_id) {
+    if (!sw || n < 0 || (n > 0 && !lights))
+        return fail(OVIS_ERR_INVALID, "ovis_sharded_add_lights: bad arguments");
+    uint32_t first0 = 0;
+    for (int r = 0; r < sw->n; r++) {
+        uint32_t first = 0;
+        int rc = ovis_light_add(sw->shards[r], n, lights, &first);
+        if (rc != OVIS_OK)
+            return rc;
+        if (r == 0)
+            first0 = first;
+        else if (first != first0)
+            return fail(OVIS_ERR_INVALID, "ovis_sharded_add_lights: the shards' light ids have diverged (lights were added to a shard directly)");
+    }
+    if (out_first_id)
+        *out_first_id = first0;
+    return OVIS_OK;
+}
+
+// list v of the merged result = list v of shard 0, 1, ... one after the other (contiguous shards, global ascending ids)
+static int splice_lists(OvisShardedWorld *sw, const char *who, int32_t n_lists, int64_t *out_offsets, int64_t cap_entities,
+                        uint32_t *out_entities, int64_t *out_n_entities) {
+    int64_t total = 0;
+    for (const Worker &w : sw->workers)
+        total += w.count;
+    *out_n_entities = total;
+    if (total > cap_entities)
+        return fail(OVIS_ERR_CAPACITY, std::string(who) + ": the lists need " + std::to_string(total) + " entries, buffer holds " + std::to_string(cap_entities));
+    int64_t at = 0;
+    for (int32_t v = 0; v < n_lists; v++) {
+        out_offsets[v] = at;
+        for (const Worker &w : sw->workers) {
+            const int64_t lo = w.offsets[(size_t)v], hi = w.offsets[(size_t)v + 1];
+            if (hi > lo)
+                std::memcpy(out_entities + at, w.h_entities + lo, sizeof(uint32_t) * (size_t)(hi - lo));
+            at += hi - lo;
+        }
+    }
+    out_offsets[n_lists] = at;
+    return OVIS_OK;
+}
+
+int ovis_sharded_cull_views(OvisShardedWorld *sw, int32_t n_views, const float *planes, const uint32_t *require,
+                            int64_t *out_offsets, int64_t cap_entities, uint32_t *out_entities, int64_t *out_n_entities) {
+    if (!sw || n_views < 0 || (n_views > 0 && !planes) || !out_offsets || !out_n_entities || cap_entities < 0 ||
+        (cap_entities > 0 && !out_entities))
+        return fail(OVIS_ERR_INVALID, "ovis_sharded_cull_views: bad arguments");
+    sw->kind = kJobViews;
+    sw->n_views = n_views;
+    sw->view_planes = planes;
+    sw->view_require = require;
+    int rc = run_frame(sw);
+    sw->kind = kJobCull;
+    if (rc != OVIS_OK)
+        return rc;
+    return splice_lists(sw, "ovis_sharded_cull_views", n_views, out_offsets, cap_entities, out_entities, out_n_entities);
+}
+
+int ovis_sharded_build_shadow_lists(OvisShardedWorld *sw, const OvisView *main_view, int32_t shadow_map_resolution,
+                                    int32_t cap_lists, int32_t *out_list_light, int32_t *out_list_view, int64_t *out_offsets,
+                                    int32_t *out_n_lists, int64_t cap_entities, uint32_t *out_entities, int64_t *out_n_entities) {
+    if (!sw || !main_view || !out_n_lists || !out_n_entities || shadow_map_resolution <= 0 || cap_entities < 0 ||
+        (cap_entities > 0 && !out_entities))
+        return fail(OVIS_ERR_INVALID, "ovis_sharded_build_shadow_lists: bad arguments");
+    sw->kind = kJobShadowLists;
+    sw->main_view = *main_view;
+    sw->shadow_res = shadow_map_resolution;
+    int rc = run_frame(sw);
+    sw->kind = kJobCull;
+    if (rc != OVIS_OK)
+        return rc;
+    // the lights are replicated, so every shard names the same lists in the same order
+    const Worker &w0 = sw->workers[0];
+    for (const Worker &w : sw->workers)
+        if (w.n_lists != w0.n_lists || !std::equal(w.list_light.begin(), w.list_light.begin() + w.n_lists, w0.list_light.begin()) ||
+            !std::equal(w.list_view.begin(), w.list_view.begin() + w.n_lists, w0.list_view.begin()))
+            return fail(OVIS_ERR_INVALID, "ovis_sharded_build_shadow_lists: the shards disagree on the lights (they must hold the same lights: "
+                                          "ovis_sharded_add_lights)");
+    *out_n_lists = w0.n_lists;
+    int64_t total = 0;
+    for (const Worker &w : sw->workers)
+        total += w.count;
+    *out_n_entities = total;
+    if (w0.n_lists > cap_lists)
+        return fail(OVIS_ERR_CAPACITY, "ovis_sharded_build_shadow_lists: " + std::to_string(w0.n_lists) + " lists, room for " + std::to_string(cap_lists));
+    if (!out_offsets || (w0.n_lists > 0 && (!out_list_light || !out_list_view)))
+        return fail(OVIS_ERR_INVALID, "ovis_sharded_build_shadow_lists: null output");
+    for (int32_t k = 0; k < w0.n_lists; k++) {
+        out_list_light[k] = w0.list_light[(size_t)k];
+        out_list_view[k] = w0.list_view[(size_t)k];
+    }
+    return splice_lists(sw, "ovis_sharded_build_shadow_lists", w0.n_lists, out_offsets, cap_entities, out_entities, out_n_entities);
 }
 
 int ovis_sharded_segments(OvisShardedWorld *sw, const uint32_t **out_segments, int64_t *out_segment_words) {

@@ -2248,6 +2248,31 @@ int ovis_cull_views_device(OvisWorld *w, int32_t n_views, const float *planes, c
     return OVIS_OK;
 }
 
+int ovis_cull_views(OvisWorld *w, int32_t n_views, const float *planes, const uint32_t *require, int64_t *out_offsets,
+                    int64_t cap_entities, uint32_t *out_entities, int64_t *out_n_entities) {
+    if (!w || n_views < 0 || (n_views > 0 && !planes) || !out_offsets || !out_n_entities || cap_entities < 0 ||
+        (cap_entities > 0 && !out_entities))
+        return fail(OVIS_ERR_INVALID, "ovis_cull_views: bad arguments");
+    OVIS_TRY(use_device(w));
+    std::vector<long long> offsets;
+    w->mv_spec_out = out_entities;
+    w->mv_spec_cap = out_entities ? cap_entities : 0;
+    {
+        const int rc = cull_views_device(w, n_views, planes, require, out_offsets, offsets);
+        if (rc != OVIS_OK) {
+            w->mv_spec_out = nullptr;
+            return rc;
+        }
+    }
+    const int64_t total = offsets.empty() ? 0 : offsets[(size_t)n_views];
+    *out_n_entities = total;
+    if (total > cap_entities) {
+        w->mv_spec_out = nullptr;
+        return fail(OVIS_ERR_CAPACITY, "ovis_cull_views: the lists need %lld entries, buffer holds %lld", (long long)total, (long long)cap_entities);
+    }
+    return finish_host_entities(w, out_entities, total);
+}
+
 int ovis_cull_shadow_views_device(OvisWorld *w, int32_t n_lights, const uint32_t *light_ids, int32_t shadow_map_resolution,
                                   int32_t cap_lists, int32_t *out_list_light, int32_t *out_list_view, int32_t *out_n_lists,
                                   const int64_t **d_offsets, const uint32_t **d_entities, int64_t *host_offsets) {

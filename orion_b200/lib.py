@@ -379,6 +379,29 @@ class World:
         step.keep = keep
         return step
 
+    def bind_shadow_lists(self, main_view, cap_entities: int, shadow_res=512):
+        """ovis_build_shadow_lists with its arguments marshalled once: step() -> (n_lists, n_entities); the lists are in
+        step.list_light / list_view / offsets / entities (referenced arrays, valid until the next step)."""
+        main_view = np.ascontiguousarray(main_view, dtype=VIEW_DTYPE).reshape(1)
+        _, _, nl_slots = self.counts()
+        cap_lists = 6 * max(nl_slots, 1)
+        ll, lv = np.zeros(cap_lists, dtype=np.int32), np.zeros(cap_lists, dtype=np.int32)
+        off = np.zeros(cap_lists + 1, dtype=np.int64)
+        ent = np.zeros(max(int(cap_entities), 1), dtype=np.uint32)
+        nl, ne = C.c_int32(), C.c_int64()
+        fn = self.lib.ovis_build_shadow_lists
+        args = (self.h, _p(main_view), C.c_int32(shadow_res), C.c_int32(cap_lists), _p(ll), _p(lv), _p(off), C.byref(nl),
+                C.c_int64(len(ent)), _p(ent), C.byref(ne))
+
+        def step():
+            rc = fn(*args)
+            if rc != OVIS_OK:
+                _check(rc)
+            return nl.value, ne.value
+        step.keep = (main_view,)
+        step.list_light, step.list_view, step.offsets, step.entities = ll, lv, off, ent
+        return step
+
     def cull_planes(self, planes, require=0, out=None):
         planes = _f32(planes, (24,))
         ne_slots, _, _ = self.counts()
@@ -655,6 +678,48 @@ class ShardedWorld:
         out = np.empty(max(int(capacity if capacity is not None else total.value), 1), dtype=np.uint32)
         n, counts = self.bind_cull(view, out, require)()
         return out[:n].copy(), counts.copy()
+
+    def add_lights(self, lights) -> int:
+        lights = np.ascontiguousarray(lights, dtype=LIGHT_DTYPE).reshape(-1)
+        first = C.c_uint32()
+        _check(self.lib.ovis_sharded_add_lights(self.h, C.c_int32(len(lights)), _p(lights), C.byref(first)))
+        return first.value
+
+    def cull_views(self, planes, require=None, capacity=1 << 16):
+        """ovis_sharded_cull_views -> (offsets, entities): list v = entities[offsets[v]:offsets[v + 1]], global ids."""
+        planes = _f32(planes, (-1, 24))
+        nv = len(planes)
+        req = _u32(require) if require is not None else None
+        off = np.zeros(nv + 1, dtype=np.int64)
+        while True:
+            ent = np.empty(max(int(capacity), 1), dtype=np.uint32)
+            ne = C.c_int64()
+            rc = self.lib.ovis_sharded_cull_views(self.h, C.c_int32(nv), _p(planes), _p(req), _p(off), C.c_int64(len(ent)), _p(ent),
+                                                  C.byref(ne))
+            if rc == OVIS_ERR_CAPACITY and ne.value > len(ent):
+                capacity = ne.value
+                continue
+            _check(rc)
+            return off, ent[:ne.value]
+
+    def shadow_lists(self, main_view, n_lights: int, shadow_res=512, capacity=1 << 16):
+        """ovis_sharded_build_shadow_lists -> (list_light, list_view, offsets, entities)."""
+        main_view = np.ascontiguousarray(main_view, dtype=VIEW_DTYPE).reshape(1)
+        cap_lists = 6 * max(int(n_lights), 1)
+        ll = np.zeros(cap_lists, dtype=np.int32)
+        lv = np.zeros(cap_lists, dtype=np.int32)
+        off = np.zeros(cap_lists + 1, dtype=np.int64)
+        while True:
+            ent = np.empty(max(int(capacity), 1), dtype=np.uint32)
+            nl, ne = C.c_int32(), C.c_int64()
+            rc = self.lib.ovis_sharded_build_shadow_lists(self.h, _p(main_view), C.c_int32(shadow_res), C.c_int32(cap_lists), _p(ll), _p(lv),
+                                                          _p(off), C.byref(nl), C.c_int64(len(ent)), _p(ent), C.byref(ne))
+            if rc == OVIS_ERR_CAPACITY and ne.value > len(ent):
+                capacity = ne.value
+                continue
+            _check(rc)
+            k = nl.value
+            return ll[:k].copy(), lv[:k].copy(), off[:k + 1].copy(), ent[:ne.value]
 
     def allgather_device(self, planes, capacity: int, require=0):
         """NCCL mode: returns (per-device block pointers, per-shard counts)."""

@@ -83,3 +83,42 @@ def test_sharded_world_nccl_allgather_for_device_consumers(oracle):
         merged = np.concatenate([seg[r, 1:1 + int(seg[r, 0])] for r in range(g)])
         assert np.array_equal(merged, exp), d
     sw.close()
+
+
+@pytest.mark.parametrize("n_shards", [1, 3])
+def test_sharded_many_views_and_shadow_lists(oracle, n_shards, monkeypatch):
+    """BASELINE configs[4] "then 5 views", and the per-light shadow-caster lists, over a sharded world: every merged list
+    must be the single-world (= reference) list. The sparse pass is forced so that both many-view passes run per shard."""
+    monkeypatch.setenv("OVIS_MV_DENSE", "0")
+    rng = np.random.default_rng(720 + n_shards)
+    n = 300_007
+    boxes = np.concatenate([util.edge_boxes(), util.random_boxes(rng, n - len(util.edge_boxes()), extent=300.0, hmax=3.0)])
+    flags = (rng.random(n) < 0.7).astype(np.uint32)
+    lights = scenes.point_lights(10, 5, 250.0, 20.0, 90.0)
+    spot = util.random_lights(rng, 3, extent=200.0)
+    spot["type"] = scenes.LIGHT_SPOT
+    spot["flags"] = 1
+    lights = np.concatenate([lights, spot])
+    sw = lib.ShardedWorld(_devices(n_shards))
+    sw.add_entities(boxes, flags)
+    assert sw.add_lights(lights) == 0
+    cam = scenes.make_view((0, 0, 350), (1, 0, 0, 0), 100.0, 0.1, 2000.0, 1600, 900)
+    views = [cam,
+             scenes.make_view((-100, 20, 40), scenes.quat_yaw_pitch(-70.0, 10.0), 50.0, 0.5, 400.0, 1024, 768),
+             scenes.make_view((50, -30, 10), scenes.quat_yaw_pitch(120.0, -20.0), 70.0, 0.5, 300.0, 1024, 1024),
+             scenes.make_view((0, 200, 0), scenes.quat_yaw_pitch(0.0, -89.0), 60.0, 1.0, 500.0, 2048, 2048),
+             scenes.make_view((10, 10, 10), scenes.quat_yaw_pitch(45.0, 45.0), 30.0, 0.1, 50.0, 512, 512)]
+    planes = np.stack([oracle.view_planes(v) for v in views])
+    require = np.array([0, 1, 0, 1, 0], dtype=np.uint32)
+    for _ in range(2):                                          # the second call finds the workers' buffers already grown
+        off, ent = sw.cull_views(planes, require, capacity=16)
+        assert len(off) == 6 and off[0] == 0 and off[-1] == len(ent)
+        for v in range(5):
+            exp = oracle.cull_aabb(boxes, planes[v], flags, int(require[v]), threads=8)
+            assert np.array_equal(ent[off[v]:off[v + 1]], exp), v
+    ll, lv, off, ent = sw.shadow_lists(cam, len(lights), capacity=16)
+    e_ll, e_lv, e_off, e_ent = oracle.shadow_lists(boxes, flags, lights, oracle.view_planes(cam))
+    assert np.array_equal(ll, e_ll) and np.array_equal(lv, e_lv)
+    assert np.array_equal(off, e_off) and np.array_equal(ent, e_ent)
+    assert len(ll) > 6 and len(ent) > 0
+    sw.close()

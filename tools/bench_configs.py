@@ -220,9 +220,15 @@ def config1():
         for v in views[1:]:
             w.cull(v, flags=0)
 
+    # the frame as a C++ caller makes it: both calls with their arguments marshalled once (the convenience wrappers above
+    # allocate their result arrays per call, which at this size costs more than the library does)
+    out_e, out_l = np.zeros(max(n, 1), dtype=np.uint32), np.zeros(max(len(s["lights"]), 1), dtype=np.uint32)
+    frame_cull = w.bind_cull(s["view"], out_e, flags=lib.CULL_LIGHTS, out_lights=out_l)
+    frame_lists = w.bind_shadow_lists(s["view"], cap_entities=n * 6 * max(len(s["lights"]), 1))
+
     def per_frame():
-        w.cull(s["view"])
-        return w.shadow_lists(s["view"])
+        frame_cull()
+        return frame_lists()
 
     def wall(fn, reps=200):
         for _ in range(10):
