@@ -110,8 +110,10 @@ struct MvGroup {                  // one cube group
 struct MvGrid {
     float lo[3], hi[3];          // exact bounds of the union of the groups' cubes
     float inv_cell[3];           // cells per unit length
-    float bias[3];               // -lo * inv_cell: cell of v = floor(fma(v, inv_cell, bias)), the same expression on host and device
-    int dim[3];                  // cells per axis (<= kMvGridMax)
+    float bias[3];               // cell of v = floor(fma(v, inv_cell, bias)), the same expression on host and device; lo maps to
+                                 // 1.5: cell 0 and cell dim - 1 are a border no cube reaches, where everything outside lands
+    float re_bias;               // 1.002e-3 x the largest |coordinate| of the grid's bounds (entity inflation, see inflate_box)
+    int dim[3];                  // cells per axis, border included (<= kMvGridMax)
 };
 
 struct MvItem {                   // one survivor of the sparse pass, placed by mv_expand_items_kernel

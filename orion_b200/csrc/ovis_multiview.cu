@@ -408,17 +408,17 @@ __device__ __forceinline__ int cell_of(float v, float inv, float bias, int dim) 
     return (int)min(__float2uint_rd(__fmaf_rn(v, inv, bias)), (uint32_t)(dim - 1));
 }
 
-// K6 pre-filter, entity side: the box inflated by Re = 1.001 * largest extent + 1e-3 * largest |coordinate|.
-// Returns 0: no cube can reach it; 1: candidates are in the cells of `r`, at most 2 x 2 rows of the bitmap; 2: test every
-// group (a box with a NaN or non-finite side can never be rejected - *odd; a box that spans more rows is cheaper to test
-// against every cube). Branch-free on purpose: it runs for every entity of the world.
-__device__ __forceinline__ void inflate_box(const float mn[3], const float mx[3], float lo[3], float hi[3], bool *odd) {
+// K6 pre-filter, entity side: the box inflated by Re = 1.004 * largest extent + 1.002e-3 * G, G = the largest |coordinate|
+// of the grid's bounds. (A box that some face of some cube group accepts overlaps that group's cube, which lies inside the
+// grid's bounds, so none of its coordinates exceeds G + 2 * extent in size: Re is at least the 1.001 * extent + 1e-3 * largest
+// |coordinate| the conservativeness argument asks for - DESIGN.md, K6 - without looking at the coordinates.)
+// odd: a NaN or infinite side (the sum of the sides is then NaN or infinite; so is that of a finite box wider than 1e38,
+// which is merely treated with the same caution).
+__device__ __forceinline__ void inflate_box(const MvGrid &g, const float mn[3], const float mx[3], float lo[3], float hi[3], bool *odd) {
     const float sx = mx[0] - mn[0], sy = mx[1] - mn[1], sz = mx[2] - mn[2];
     const float ext = fmaxf(fmaxf(fmaxf(sx, sy), sz), 0.0f);
-    const float mag = fmaxf(fmaxf(fmaxf(fabsf(mn[0]), fabsf(mx[0])), fmaxf(fabsf(mn[1]), fabsf(mx[1]))),
-                            fmaxf(fabsf(mn[2]), fabsf(mx[2])));
-    *odd = !((sx == sx) & (sy == sy) & (sz == sz) & (ext <= 3.0e38f) & (mag <= 3.0e38f));     // fmaxf drops NaNs
-    const float re = ext * 1.001f + mag * 1.0e-3f;
+    *odd = !(fabsf((sx + sy) + sz) <= 3.0e38f);
+    const float re = __fmaf_rn(ext, 1.004f, g.re_bias);
 #pragma unroll
     for (int c = 0; c < 3; c++) {
         lo[c] = mn[c] - re;
@@ -426,15 +426,17 @@ __device__ __forceinline__ void inflate_box(const float mn[3], const float mx[3]
     }
 }
 
+// Returns 1: candidates are in the cells of `r`, at most 2 x 2 rows of the bitmap (a box outside the grid's bounds lands in
+// the border cells, which are never occupied); 2: test every group (an odd box can never be rejected; a box that spans more
+// rows is cheaper to test against every cube). Branch-free on purpose: it runs for every entity of the world.
 __device__ __forceinline__ int entity_cells(const MvGrid &g, const float mn[3], const float mx[3], float lo[3], float hi[3],
                                             CellRange &r, bool *odd) {
-    inflate_box(mn, mx, lo, hi, odd);
-    const bool outside = (hi[0] < g.lo[0]) | (lo[0] > g.hi[0]) | (hi[1] < g.lo[1]) | (lo[1] > g.hi[1]) | (hi[2] < g.lo[2]) | (lo[2] > g.hi[2]);
+    inflate_box(g, mn, mx, lo, hi, odd);
     r.x0 = cell_of(lo[0], g.inv_cell[0], g.bias[0], g.dim[0]); r.x1 = cell_of(hi[0], g.inv_cell[0], g.bias[0], g.dim[0]);
     r.y0 = cell_of(lo[1], g.inv_cell[1], g.bias[1], g.dim[1]); r.y1 = cell_of(hi[1], g.inv_cell[1], g.bias[1], g.dim[1]);
     r.z0 = cell_of(lo[2], g.inv_cell[2], g.bias[2], g.dim[2]); r.z1 = cell_of(hi[2], g.inv_cell[2], g.bias[2], g.dim[2]);
     const bool big = (r.y1 - r.y0 > 1) | (r.z1 - r.z0 > 1);
-    return *odd ? 2 : (outside ? 0 : (big ? 2 : 1));
+    return (*odd | big) ? 2 : 1;
 }
 
 __device__ __forceinline__ unsigned long long x_range_bits(int x0, int x1) {

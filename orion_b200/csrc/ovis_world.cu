@@ -948,15 +948,26 @@ int64_t build_light_grid(std::vector<ovis::MvGroup> &groups, ovis::MvGrid &grid,
         extent[c] = grid.hi[c] - grid.lo[c];
         largest = std::max(largest, extent[c]);
     }
-    float cell = std::max(largest / (float)ovis::kMvGridMax, min_side * 0.25f);
+    // Three of the kMvGridMax cells per axis are border: the grid's lower bound maps to 1.5, so the cubes occupy cells
+    // 1 .. dim - 2 whatever the rounding, and an entity outside the bounds clamps into cell 0 or dim - 1, which no cube marks:
+    // the kernel needs no "outside the grid" test.
+    const int usable = ovis::kMvGridMax - 3;
+    float cell = std::max(largest / (float)usable, min_side * 0.25f);
     if (!(cell > 0.0f) || !std::isfinite(cell))
         cell = 1.0f;
+    float reach = 0.0f;
+    for (int c = 0; c < 3; c++)
+        reach = std::max(reach, std::max(std::fabs(grid.lo[c]), std::fabs(grid.hi[c])));
+    grid.re_bias = reach * 1.002e-3f;
     for (;;) {
+        bool single = true;
         for (int c = 0; c < 3; c++) {
             float cells = std::ceil(extent[c] / cell);
-            grid.dim[c] = (int)std::min(std::max(cells, 1.0f), (float)ovis::kMvGridMax);
+            const int inner = (int)std::min(std::max(cells, 1.0f), (float)usable);
+            single = single && inner == 1;
+            grid.dim[c] = inner + 3;
             grid.inv_cell[c] = 1.0f / cell;
-            grid.bias[c] = -(grid.lo[c] * grid.inv_cell[c]);
+            grid.bias[c] = 1.5f - grid.lo[c] * grid.inv_cell[c];
         }
         int64_t nodes = 0;
         for (ovis::MvGroup &g : groups) {
@@ -971,7 +982,7 @@ int64_t build_light_grid(std::vector<ovis::MvGroup> &groups, ovis::MvGrid &grid,
             g.cell_hi = (uint32_t)hi[0] | ((uint32_t)hi[1] << 8) | ((uint32_t)hi[2] << 16);
             nodes += (int64_t)(hi[0] - lo[0] + 1) * (hi[1] - lo[1] + 1) * (hi[2] - lo[2] + 1);
         }
-        if (nodes <= node_budget || (grid.dim[0] == 1 && grid.dim[1] == 1 && grid.dim[2] == 1))
+        if (nodes <= node_budget || single)
             return nodes;
         cell *= 2.0f;
     }
