@@ -181,6 +181,7 @@ struct OvisWorld {
     int64_t cap_mv_segments = 0;
     bool mv_force_dense = false;          // OVIS_MV_DENSE=1 (testing): cube groups take the dense pass too
     bool mv_force_sparse = false;         // OVIS_MV_DENSE=0 (testing): ... and never by the size rule
+    int mv_round_views = 0;               // OVIS_MV_ROUND_VIEWS (testing): upper bound on the views of one round, 0 = by memory
     // Host outputs of a multi-view call ride in the same round trip as the offsets: the lists change little from frame to
     // frame, so a little more than the previous total is copied speculatively; only a frame that grew pays a second copy.
     uint32_t *mv_spec_out = nullptr;
@@ -1021,7 +1022,9 @@ int cull_views_grouped(OvisWorld *w, int32_t n_views, const float *planes, const
     const int64_t row = num_blocks + 1;
     // scratch budgets of one round
     const int64_t max_plain = std::max<int64_t>(1, ((int64_t)1 << 28) / num_words);          // 1 GiB of survivor bitmaps
-    const int64_t max_views = std::max<int64_t>(ovis::kMvMaxGroupViews, ((int64_t)1 << 28) / row);   // 1 GiB of block totals
+    int64_t max_views = std::max<int64_t>(ovis::kMvMaxGroupViews, ((int64_t)1 << 28) / row);   // 1 GiB of block totals
+    if (w->mv_round_views > 0)
+        max_views = std::min<int64_t>(max_views, w->mv_round_views);
     if (!w->d_mv_state) {
         OVIS_CUDA(cudaMalloc(&w->d_mv_state, kMvStateBytes));
         OVIS_CUDA(cudaMemsetAsync(w->d_mv_state, 0, kMvStateBytes, w->stream));
@@ -1380,6 +1383,8 @@ int ovis_world_create(int device, OvisWorld **out_world) {
         w->mv_force_dense = atoi(v) != 0;
         w->mv_force_sparse = atoi(v) == 0;
     }
+    if (const char *v = getenv("OVIS_MV_ROUND_VIEWS"))          // (testing) views per round, as if the scratch budget were that small
+        w->mv_round_views = std::max(atoi(v), ovis::kMvMaxGroupViews);
     *out_world = w;
     return OVIS_OK;
 }

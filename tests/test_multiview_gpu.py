@@ -184,6 +184,26 @@ def test_shadow_views_host_output_with_and_without_the_caster_filter(oracle):
     w.close()
 
 
+@pytest.mark.parametrize("dense", ["0", "1"])
+def test_calls_split_into_rounds_give_the_same_lists(oracle, monkeypatch, dense):
+    """A call whose scratch would not fit is processed in rounds of views (here forced: 8 views per round). Offsets continue
+    from round to round, the overflow word outlives a round, and every round's offsets reach the host."""
+    monkeypatch.setenv("OVIS_MV_ROUND_VIEWS", "8")
+    monkeypatch.setenv("OVIS_MV_DENSE", dense)
+    rng = np.random.default_rng(506)
+    boxes, flags, lights = _scene(rng, 120_000, 9, 5, 250.0, 20.0, 100.0)
+    w = _world_static(boxes, flags)
+    w.add_lights(lights)
+    ids = np.arange(len(lights), dtype=np.uint32)
+    for _ in range(2):
+        ll, lv, off, ent = _shadow_lists(w, ids)
+        exp = _expected_lists(oracle, boxes, flags, lights, ids)
+        assert len(ll) == len(exp) == 9 * 6 + 5
+        for k, e in enumerate(exp):
+            assert np.array_equal(ent[off[k]:off[k + 1]], e), k
+    w.close()
+
+
 def _bench_configs():
     if ROOT not in sys.path:
         sys.path.insert(0, ROOT)
