@@ -171,6 +171,9 @@ struct MvResetArgs {              // up to four arrays filled with a word (sizes
     uint32_t *state;             // first_round: state[0] = 0 and csr_offsets[0] = 0 as well
     long long *csr_offsets;
     int first_round;
+    const uint4 *copy_src;       // the round's staging (planes, view records, groups) in page-locked host memory -> copy_dst on
+    uint4 *copy_dst;             // the device: fetched by this kernel, which saves the call a cudaMemcpyAsync on its critical path
+    int64_t copy_quads;
 };
 void launch_mv_reset(const MvResetArgs &r, int num_sms, cudaStream_t s);
 constexpr uint32_t kMvOverflowPairs = 1u, kMvOverflowItems = 2u, kMvOverflowNodes = 4u, kMvOverflowHits = 8u;

@@ -279,6 +279,8 @@ mv_reset_kernel(const MvResetArgs r) {
         for (int64_t i = t0; i < r.quads[k]; i += step)
             p[i] = fill;
     }
+    for (int64_t i = t0; i < r.copy_quads; i += step)
+        r.copy_dst[i] = r.copy_src[i];
     if (t0 == 0) {
         r.state[1] = r.state[2] = r.state[3] = 0u;           // (the first 16 bytes are not among the arrays: word 0 outlives a round)
         if (r.first_round) {
@@ -289,7 +291,7 @@ mv_reset_kernel(const MvResetArgs r) {
 }
 
 void launch_mv_reset(const MvResetArgs &r, int num_sms, cudaStream_t s) {
-    int64_t most = 1;
+    int64_t most = r.copy_quads > 1 ? r.copy_quads : 1;
     for (int k = 0; k < 4; k++)
         most = most > r.quads[k] ? most : r.quads[k];
     int64_t grid = (most + kMvThreads - 1) / kMvThreads;

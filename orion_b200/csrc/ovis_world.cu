@@ -8,6 +8,7 @@
 #include "orion_vis.h"
 
 #include <algorithm>
+#include <chrono>
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
@@ -51,6 +52,27 @@ int fail(int code, const char *fmt, ...) {
     } while (0)
 
 inline int64_t round_up(int64_t v, int64_t m) { return (v + m - 1) / m * m; }
+
+// OVIS_MV_TRACE=1: host-side time stamps of a many-view call on stderr (where the microseconds between "kernels" and the
+// sum of the kernel times go)
+struct MvTrace {
+    bool on;
+    std::chrono::steady_clock::time_point t0, last;
+    MvTrace() {
+        static const bool enabled = getenv("OVIS_MV_TRACE") && atoi(getenv("OVIS_MV_TRACE")) != 0;
+        on = enabled;
+        if (on)
+            t0 = last = std::chrono::steady_clock::now();
+    }
+    void mark(const char *what) {
+        if (!on)
+            return;
+        const auto now = std::chrono::steady_clock::now();
+        fprintf(stderr, "[mv] %-22s +%7.1f us  (%7.1f)\n", what, std::chrono::duration<double, std::micro>(now - last).count(),
+                std::chrono::duration<double, std::micro>(now - t0).count());
+        last = now;
+    }
+};
 
 struct Level {
     int64_t count = 0;
@@ -995,6 +1017,7 @@ int64_t build_light_grid(std::vector<ovis::MvGroup> &groups, ovis::MvGrid &grid,
 int cull_views_grouped(OvisWorld *w, int32_t n_views, const float *planes, const uint32_t *require,
                        const std::vector<HostGroup> &groups, int64_t *host_offsets_out,
                        std::vector<long long> &host_offsets) {
+    MvTrace trace;
     OVIS_TRY(flush_transforms(w));
     host_offsets.assign((size_t)n_views + 1, 0);
     OVIS_TRY(ensure(w->d_csr_offsets, w->cap_csr_views, std::max<int64_t>(n_views + 1, 64), w->stream));
@@ -1085,10 +1108,10 @@ int cull_views_grouped(OvisWorld *w, int32_t n_views, const float *planes, const
             const size_t off_pmeta = (off_groups + sizeof(ovis::MvGroup) * cubes.size() + 15) & ~(size_t)15;
             const size_t off_pplanes = (off_pmeta + sizeof(uint2) * plain.size() + 15) & ~(size_t)15;
             const size_t bytes = off_pplanes + sizeof(float) * 48 * plain.size();
-            OVIS_TRY(ensure_pinned(w->h_mv_stage, w->cap_h_mv_stage, bytes));
+            OVIS_TRY(ensure_pinned(w->h_mv_stage, w->cap_h_mv_stage, bytes + 16));
             {
                 int64_t cap = (int64_t)w->cap_d_mv_stage;
-                OVIS_TRY(ensure(w->d_mv_stage, cap, (int64_t)bytes, w->stream));
+                OVIS_TRY(ensure(w->d_mv_stage, cap, (int64_t)bytes + 16, w->stream));
                 w->cap_d_mv_stage = (size_t)cap;
             }
             unsigned char *hs = static_cast<unsigned char *>(w->h_mv_stage);
@@ -1121,7 +1144,7 @@ int cull_views_grouped(OvisWorld *w, int32_t n_views, const float *planes, const
                         pp[48 * k + 2 * c] = pp[48 * k + 2 * c + 1] = src[c];
                 }
             }
-            OVIS_CUDA(cudaMemcpyAsync(w->d_mv_stage, hs, bytes, cudaMemcpyHostToDevice, w->stream));
+            trace.mark("groups, grid, staging");
             // ---- scratch
             OVIS_TRY(ensure(w->d_mv_totals, w->cap_mv_totals, round_up((int64_t)nv * row, 4), w->stream));
             OVIS_TRY(ensure(w->d_mv_masks, w->cap_mv_masks, std::max<int64_t>(1, (int64_t)plain.size() * num_words), w->stream));
@@ -1199,6 +1222,11 @@ int cull_views_grouped(OvisWorld *w, int32_t n_views, const float *planes, const
                 r.state = reinterpret_cast<uint32_t *>(w->d_mv_state);
                 r.csr_offsets = w->d_csr_offsets;
                 r.first_round = g0 == 0 ? 1 : 0;
+                // the staging goes up inside this launch (a cudaMemcpyAsync of these few KB cost the call 5-20 us of host time
+                // before the first kernel could be queued)
+                r.copy_src = reinterpret_cast<const uint4 *>(hs);
+                r.copy_dst = reinterpret_cast<uint4 *>(w->d_mv_stage);
+                r.copy_quads = (int64_t)((bytes + 15) / 16);
                 ovis::launch_mv_reset(r, w->num_sms, w->stream);
             }
             // ---- kernels
@@ -1210,6 +1238,7 @@ int cull_views_grouped(OvisWorld *w, int32_t n_views, const float *planes, const
             ovis::launch_mv_expand_items(a, w->stream);
             w->launches += 2 + (plain.empty() ? 0 : 2) + (cubes.empty() ? 0 : 4);
             OVIS_CUDA(cudaGetLastError());
+            trace.mark("kernels queued");
             if (g1 < groups.size())
                 OVIS_CUDA(cudaStreamSynchronize(w->stream));     // the pinned staging buffer is refilled by the next round
             g0 = g1;
@@ -1223,6 +1252,7 @@ int cull_views_grouped(OvisWorld *w, int32_t n_views, const float *planes, const
             w->mv_spec_copied = guess;
         }
         OVIS_CUDA(cudaStreamSynchronize(w->stream));
+        trace.mark("synchronised");
         const uint32_t *state = reinterpret_cast<const uint32_t *>(hr + n_views + 1);
         const uint32_t overflow = state[0];
         if (overflow & ovis::kMvOverflowPairs) {         // some block was too dense for the sparse pass: everything densely

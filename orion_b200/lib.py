@@ -479,6 +479,47 @@ class World:
                                                C.byref(d_ent), _p(host)))
         return host, d_off.value, d_ent.value
 
+    def bind_cull_views_device(self, planes, require=None):
+        """ovis_cull_views_device with its arguments marshalled once: step() -> None; step.offsets (host, n_views + 1),
+        step.d_offsets / step.d_entities after the first step."""
+        planes = _f32(planes, (-1, 24))
+        nv = len(planes)
+        require = _u32(require) if require is not None else None
+        d_off, d_ent = C.c_void_p(), C.c_void_p()
+        host = np.zeros(nv + 1, dtype=np.int64)
+        fn = self.lib.ovis_cull_views_device
+        args = (self.h, C.c_int32(nv), _p(planes), _p(require), C.byref(d_off), C.byref(d_ent), _p(host))
+
+        def step():
+            rc = fn(*args)
+            if rc != OVIS_OK:
+                _check(rc)
+        step.keep = (planes, require)
+        step.offsets, step.d_offsets, step.d_entities = host, d_off, d_ent
+        return step
+
+    def bind_cull_shadow_views_device(self, light_ids, shadow_res=512):
+        """ovis_cull_shadow_views_device with its arguments marshalled once: step() -> number of lists; step.list_light /
+        list_view / offsets are referenced host arrays, step.d_offsets / step.d_entities the device CSR."""
+        light_ids = _u32(light_ids)
+        cap = 6 * max(len(light_ids), 1)
+        ll, lv = np.zeros(cap, dtype=np.int32), np.zeros(cap, dtype=np.int32)
+        off = np.zeros(cap + 1, dtype=np.int64)
+        n = C.c_int32()
+        d_off, d_ent = C.c_void_p(), C.c_void_p()
+        fn = self.lib.ovis_cull_shadow_views_device
+        args = (self.h, C.c_int32(len(light_ids)), _p(light_ids), C.c_int32(shadow_res), C.c_int32(cap), _p(ll), _p(lv), C.byref(n),
+                C.byref(d_off), C.byref(d_ent), _p(off))
+
+        def step():
+            rc = fn(*args)
+            if rc != OVIS_OK:
+                _check(rc)
+            return n.value
+        step.keep = (light_ids,)
+        step.list_light, step.list_view, step.offsets, step.d_offsets, step.d_entities = ll, lv, off, d_off, d_ent
+        return step
+
     def cull_shadow_views_device(self, light_ids, shadow_res=512):
         """Shadow-view culls of the given lights -> (list_light, list_view, host offsets, d_offsets, d_entities)."""
         light_ids = _u32(light_ids)

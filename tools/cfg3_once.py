@@ -20,6 +20,11 @@ w.add_nodes(s["parent"], s["local_trs"])
 w.bind_entities(s["entity_node"], np.arange(e0, e0 + n_ent, dtype=np.uint32))
 w.add_lights(s["lights"])
 w.update_transforms()
+g0, g1 = s["group_range"]
+group_ids = np.arange(g0, g1, dtype=np.uint32)
+for f in range(1, 4):                                    # three frames of moved groups: the dirty-subtree update
+    w.set_node_local_trs(group_ids, scenes.move_groups(s, f))
+    w.update_transforms()
 ents, ls = w.cull(s["view"])
 shadow_ids = ls[(s["lights"]["flags"][ls] & 1) == 1]
 for _ in range(3):
