@@ -428,6 +428,16 @@ __device__ __forceinline__ void inflate_box(const MvGrid &g, const float mn[3], 
     }
 }
 
+// Cheap first look: can the (inflated) box touch the grid's bounds at all, or is it odd? Everything else would land in the
+// border cells and leave with nothing.
+__device__ __forceinline__ bool box_near_grid(const MvGrid &g, const float mn[3], const float mx[3]) {
+    float lo[3], hi[3];
+    bool odd;
+    inflate_box(g, mn, mx, lo, hi, &odd);
+    const bool outside = (hi[0] < g.lo[0]) | (lo[0] > g.hi[0]) | (hi[1] < g.lo[1]) | (lo[1] > g.hi[1]) | (hi[2] < g.lo[2]) | (lo[2] > g.hi[2]);
+    return odd | !outside;
+}
+
 // Returns 1: candidates are in the cells of `r`, at most 2 x 2 rows of the bitmap (a box outside the grid's bounds lands in
 // the border cells, which are never occupied); 2: test every group (an odd box can never be rejected; a box that spans more
 // rows is cheaper to test against every cube). Branch-free on purpose: it runs for every entity of the world.
@@ -506,6 +516,8 @@ mv_classify_kernel(const __grid_constant__ MvArgs a) {
     chain_enter();
     extern __shared__ __align__(16) unsigned char s_mv[];
     unsigned long long *s_bitmap = reinterpret_cast<unsigned long long *>(s_mv);
+    __shared__ float s_cbox[kMvThreads / 32][6][32];           // per warp: the boxes handed out one per lane (see below)
+    __shared__ uint32_t s_cel[kMvThreads / 32][32];
     const int rows = a.grid.dim[1] * a.grid.dim[2];
     for (int i = threadIdx.x; i < rows; i += kMvThreads)
         s_bitmap[i] = a.bitmap[i];
@@ -515,6 +527,7 @@ mv_classify_kernel(const __grid_constant__ MvArgs a) {
     const float4 *__restrict__ bounds = reinterpret_cast<const float4 *>(a.bounds);
     const int64_t vstride = a.stride >> 2;
     const int dim_y = a.grid.dim[1];
+    int straight_left = 0;
     for (long long group = (long long)blockIdx.x * (kMvThreads / 32) + (threadIdx.x >> 5); group < a.num_groups128; group += warps_total) {
         const int64_t v = group * 32 + lane;
         const int64_t e0 = v << 2;
@@ -525,6 +538,83 @@ mv_classify_kernel(const __grid_constant__ MvArgs a) {
             alive &= (__ldg(a.alive_mask + (e0 >> 5)) >> (e0 & 31)) & 0xfu;
         const float mnv[4][3] = { { ax.x, ay.x, az.x }, { ax.y, ay.y, az.y }, { ax.z, ay.z, az.z }, { ax.w, ay.w, az.w } };
         const float mxv[4][3] = { { bx.x, by.x, bz.x }, { bx.y, by.y, bz.y }, { bx.z, by.z, bz.z }, { bx.w, by.w, bz.w } };
+        // When the lights sit in a corner of the world (a camera's visible lights) most entities cannot touch the grid's
+        // bounds. A cheap test finds those that can; if the warp's 128 hold at most 32 of them they are handed out one per
+        // lane through shared memory and the cell work below runs once instead of four times.
+        // (Where the grid spans the world that first look is wasted: a warp that found more than 32 skips it for its next
+        // seven groups.)
+        const int b = (int)(group / kMaskBlockGroups);
+        float4 *__restrict__ list = a.hit_records + (int64_t)b * (2 * a.hit_capacity);
+        const uint32_t el0 = (uint32_t)(e0 & (kMaskBlockEntities - 1));
+        uint32_t near = 0, n0 = 0, n1 = 0, n2 = 0, n3 = 0, total_near = 128u;
+        if (straight_left > 0) {
+            straight_left--;
+        } else {
+#pragma unroll
+            for (int j = 0; j < 4; j++)
+                near |= (box_near_grid(a.grid, mnv[j], mxv[j]) ? 1u : 0u) << j;
+            near &= alive;
+            n0 = __ballot_sync(0xffffffffu, near & 1u); n1 = __ballot_sync(0xffffffffu, near & 2u);
+            n2 = __ballot_sync(0xffffffffu, near & 4u); n3 = __ballot_sync(0xffffffffu, near & 8u);
+            total_near = __popc(n0) + __popc(n1) + __popc(n2) + __popc(n3);
+            if (total_near == 0u)
+                continue;
+            if (total_near > 32u)
+                straight_left = 7;
+        }
+        if (total_near <= 32u) {
+            const int warp = threadIdx.x >> 5;
+            const uint32_t lt = (1u << lane) - 1u;
+            const uint32_t ballots[4] = { n0, n1, n2, n3 };
+            uint32_t first = 0;
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                if ((near >> j) & 1u) {
+                    const uint32_t slot = first + __popc(ballots[j] & lt);
+#pragma unroll
+                    for (int c = 0; c < 3; c++) {
+                        s_cbox[warp][c][slot] = mnv[j][c];
+                        s_cbox[warp][c + 3][slot] = mxv[j][c];
+                    }
+                    s_cel[warp][slot] = el0 + j;
+                }
+                first += __popc(ballots[j]);
+            }
+            __syncwarp();
+            bool mine = false, is_big = false;
+            float mn[3] = { 0.f, 0.f, 0.f }, mx[3] = { 0.f, 0.f, 0.f };
+            uint32_t el = 0;
+            if ((uint32_t)lane < total_near) {
+#pragma unroll
+                for (int c = 0; c < 3; c++) {
+                    mn[c] = s_cbox[warp][c][lane];
+                    mx[c] = s_cbox[warp][c + 3][lane];
+                }
+                el = s_cel[warp][lane];
+                float lo[3], hi[3];
+                CellRange r;
+                bool odd;
+                const int kind = entity_cells(a.grid, mn, mx, lo, hi, r, &odd);
+                const unsigned long long seen = (s_bitmap[r.z0 * dim_y + r.y0] | s_bitmap[r.z0 * dim_y + r.y1]) |
+                                                (s_bitmap[r.z1 * dim_y + r.y0] | s_bitmap[r.z1 * dim_y + r.y1]);
+                const bool occupied = ((seen >> r.x0) << (63 - (r.x1 - r.x0))) != 0ull;
+                is_big = kind == 2;
+                mine = is_big | ((kind == 1) & occupied);
+            }
+            const uint32_t who = __ballot_sync(0xffffffffu, mine);
+            if (who) {
+                uint32_t base = 0;
+                if (lane == 0)
+                    base = atomicAdd(a.block_work + b, (uint32_t)__popc(who));
+                base = __shfl_sync(0xffffffffu, base, 0) + __popc(who & lt);
+                if (mine && base < (uint32_t)a.hit_capacity) {
+                    list[2 * base] = make_float4(mn[0], mn[1], mn[2], mx[0]);
+                    list[2 * base + 1] = make_float4(mx[1], mx[2], __uint_as_float(el | ((is_big ? 1u : 0u) << 31)), 0.0f);
+                }
+            }
+            __syncwarp();                                        // the warp's slots are rewritten by its next group
+            continue;
+        }
         uint32_t hit = 0, big = 0;
 #pragma unroll
         for (int j = 0; j < 4; j++) {
@@ -554,13 +644,10 @@ mv_classify_kernel(const __grid_constant__ MvArgs a) {
                 if (lane >= o)
                     incl += up;
             }
-            const int b = (int)(group / kMaskBlockGroups);
             uint32_t base = 0;
             if (lane == 31)
                 base = atomicAdd(a.block_work + b, incl);
             base = __shfl_sync(0xffffffffu, base, 31) + incl - count;
-            float4 *__restrict__ list = a.hit_records + (int64_t)b * (2 * a.hit_capacity);
-            const uint32_t el0 = (uint32_t)(e0 & (kMaskBlockEntities - 1));
 #pragma unroll
             for (int j = 0; j < 4; j++)
                 if ((mine >> j) & 1u) {
