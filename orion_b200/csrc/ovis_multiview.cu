@@ -36,6 +36,9 @@
 namespace ovis {
 
 constexpr int kMvThreads = 256;
+constexpr int kSpThreads = 256;           // mv_sparse_kernel (128-thread CTAs, eleven per SM - one wave for a 10 M-entity world - were
+                                          // measured slower on every workload: 0.130 -> 0.161 ms for configs[2]'s shadow lists)
+constexpr int kMvBigSlots = 512;          // records per block that are tested against every group a warp each
 constexpr int kMvRankSortBelow = 320;    // candidate pairs of a block up to which they are sorted by counting (<= kMvPairCapacity / 2)
 
 // The kernels of one round are a chain of short launches. Each is launched with programmatic stream serialization and
@@ -49,10 +52,10 @@ __device__ __forceinline__ void chain_enter() {
 }
 
 template <typename Kernel>
-static void launch_chained(Kernel kernel, dim3 grid, size_t smem, cudaStream_t s, const MvArgs &a) {
+static void launch_chained(Kernel kernel, dim3 grid, size_t smem, cudaStream_t s, const MvArgs &a, int threads = kMvThreads) {
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = grid;
-    cfg.blockDim = dim3(kMvThreads);
+    cfg.blockDim = dim3((unsigned)threads);
     cfg.dynamicSmemBytes = smem;
     cfg.stream = s;
     cudaLaunchAttribute attr[1];
@@ -197,6 +200,7 @@ mv_plain_test_kernel(const __grid_constant__ MvArgs a) {
 }
 
 // block-wide exclusive scan of one value per thread (256 threads); returns the rank, *total = the block sum
+template <int THREADS = kMvThreads>
 __device__ __forceinline__ uint32_t block_exclusive_scan(uint32_t c, uint32_t *s_warp, uint32_t *total) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     uint32_t incl = c;
@@ -212,7 +216,7 @@ __device__ __forceinline__ uint32_t block_exclusive_scan(uint32_t c, uint32_t *s
     __syncthreads();
     uint32_t before = 0, sum = 0;
 #pragma unroll
-    for (int k = 0; k < kMvThreads / 32; k++) {
+    for (int k = 0; k < THREADS / 32; k++) {
         if (k < warp)
             before += s_warp[k];
         sum += s_warp[k];
@@ -474,11 +478,11 @@ __device__ __forceinline__ void load_box(const MvArgs &a, int64_t e, float mn[3]
     }
 }
 
-// record key: group (12 bits) | entity inside the block (13 bits) | face mask (6 bits); 0xffffffff = no record
+// record key: group (12 bits) | entity inside the block - at first: record index - (13 bits) | face mask (6 bits); 0xffffffff = no record
 __device__ __forceinline__ void append_pair(uint32_t *s_pairs, uint32_t *s_npairs, uint32_t g, uint32_t el) {
     const uint32_t i = atomicAdd(s_npairs, 1u);
     if (i < (uint32_t)kMvPairCapacity)
-        s_pairs[i] = (g << 13) | el;
+        s_pairs[i] = ((g << 13) | el) << 6;                    // the low six bits collect the faces that accept the box
 }
 
 struct SegCount {                 // per-face survivor counts of a (group, block) run, 16 bits each, and the segment flag
@@ -663,14 +667,14 @@ mv_classify_kernel(const __grid_constant__ MvArgs a) {
 }
 
 // K6, entity side, pair half: one CTA per block of 8192 entities that has classified entities.
-__global__ void __launch_bounds__(kMvThreads, 6)
+__global__ void __launch_bounds__(kSpThreads, 6)
 mv_sparse_kernel(const __grid_constant__ MvArgs a) {
     chain_enter();
     __shared__ __align__(16) uint32_t s_pairs[kMvPairCapacity];
-    __shared__ uint32_t s_big[64];                             // records tested against every group (rare: huge or odd boxes)
+    __shared__ uint32_t s_big[kMvBigSlots];                    // records tested against every group (huge or odd boxes)
     __shared__ uint32_t s_npairs, s_nrec, s_item_base, s_nbig;
-    __shared__ uint32_t s_warp[kMvThreads / 32];
-    __shared__ SegCount s_seg[kMvThreads / 32];
+    __shared__ uint32_t s_warp[kSpThreads / 32];
+    __shared__ SegCount s_seg[kSpThreads / 32];
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int b = blockIdx.x;
@@ -701,11 +705,11 @@ mv_sparse_kernel(const __grid_constant__ MvArgs a) {
         n0 = __ldg(list + 2 * tid);
         n1 = __ldg(list + 2 * tid + 1);
     }
-    for (uint32_t h = tid; h < n_hits; h += kMvThreads) {
+    for (uint32_t h = tid; h < n_hits; h += kSpThreads) {
         const float4 r0 = n0, r1 = n1;
-        if (h + kMvThreads < n_hits) {
-            n0 = __ldg(list + 2 * (h + kMvThreads));
-            n1 = __ldg(list + 2 * (h + kMvThreads) + 1);
+        if (h + kSpThreads < n_hits) {
+            n0 = __ldg(list + 2 * (h + kSpThreads));
+            n1 = __ldg(list + 2 * (h + kSpThreads) + 1);
         }
         const float mn[3] = { r0.x, r0.y, r0.z }, mx[3] = { r0.w, r1.x, r1.y };
         const uint32_t tag = __float_as_uint(r1.z);
@@ -715,9 +719,9 @@ mv_sparse_kernel(const __grid_constant__ MvArgs a) {
         entity_cells(a.grid, mn, mx, lo, hi, r, &odd);
         if (tag >> 31) {
             const uint32_t slot = atomicAdd(&s_nbig, 1u);
-            if (slot < 64u) {
+            if (slot < (uint32_t)kMvBigSlots) {
                 s_big[slot] = h;
-            } else {                                           // (more than 64 such boxes in one block: this thread alone)
+            } else {                                           // (more such boxes in one block than slots: this thread alone)
                 for (int g = 0; g < a.n_groups; g++)
                     if (odd || overlaps_cube(a.groups[g], lo, hi))
                         append_pair(s_pairs, &s_npairs, (uint32_t)g, h);
@@ -748,16 +752,16 @@ mv_sparse_kernel(const __grid_constant__ MvArgs a) {
             }
     }
     __syncthreads();
-    // records tested against every group: the whole CTA shares each one, a thread takes every 256th group
-    for (uint32_t k = 0, nbig = min(s_nbig, 64u); k < nbig; k++) {
+    // records tested against every group: a warp takes a record, its lanes every 32nd group (the whole CTA on one record at
+    // a time, as at first, spends eight warps on the 37 groups of a camera's visible lights: 9 M instructions for configs[2])
+    for (uint32_t k = warp, nbig = min(s_nbig, (uint32_t)kMvBigSlots); k < nbig; k += kSpThreads / 32) {
         const uint32_t h = s_big[k];
         const float4 r0 = __ldg(list + 2 * h), r1 = __ldg(list + 2 * h + 1);
         const float mn[3] = { r0.x, r0.y, r0.z }, mx[3] = { r0.w, r1.x, r1.y };
         float lo[3], hi[3];
-        CellRange r;
         bool odd;
-        entity_cells(a.grid, mn, mx, lo, hi, r, &odd);
-        for (int g = tid; g < a.n_groups; g += kMvThreads)
+        inflate_box(a.grid, mn, mx, lo, hi, &odd);
+        for (int g = lane; g < a.n_groups; g += 32)
             if (odd || overlaps_cube(a.groups[g], lo, hi))
                 append_pair(s_pairs, &s_npairs, (uint32_t)g, h);
     }
@@ -776,34 +780,47 @@ mv_sparse_kernel(const __grid_constant__ MvArgs a) {
         return;
     }
 
-    // ---- (3) exact tests: one thread per pair, every face of the light (Math::intersect, intersection.cc:42-57)
-    uint32_t n_valid = 0;
-    for (uint32_t i = tid; i < npairs; i += kMvThreads) {
+    // ---- (3) exact tests (Math::intersect, intersection.cc:42-57): one thread per (pair, face), the six planes of the face
+    // requested together - a thread per pair walking its faces plane by plane was up to 36 dependent trips to L2, the
+    // longest chain of a block with few pairs. A face that accepts the box sets its bit in the pair's word.
+    for (uint32_t t = tid; t < npairs * (uint32_t)kMvMaxGroupViews; t += kSpThreads) {
+        const uint32_t i = t / (uint32_t)kMvMaxGroupViews, f = t - i * (uint32_t)kMvMaxGroupViews;
         const uint32_t pair = s_pairs[i];
-        const uint32_t g = pair >> 13, h = pair & 8191u;       // (group, record): the box comes from the record, one sector
+        const uint32_t g = pair >> 19, h = (pair >> 6) & 8191u;   // (group, record): the box comes from the record, one sector
+        const int2 views = __ldg(reinterpret_cast<const int2 *>(&a.groups[g].first_view));     // (first_view, n_views)
+        if ((int)f >= views.y)
+            continue;
+        const int view = views.x + (int)f;
         const float4 r0 = __ldg(list + 2 * h), r1 = __ldg(list + 2 * h + 1);
-        const float mn[3] = { r0.x, r0.y, r0.z }, mx[3] = { r0.w, r1.x, r1.y };
-        const uint32_t el = __float_as_uint(r1.z) & (kMaskBlockEntities - 1);
-        const int64_t e = block_e0 + el;
-        const bool caster = a.caster_mask ? ((__ldg(a.caster_mask + (e >> 5)) >> (e & 31)) & 1u) != 0 : true;
-        const MvGroup grp = a.groups[g];
-        uint32_t fm = 0;
-        for (int f = 0; f < grp.n_views; f++) {
-            const int view = grp.first_view + f;
-            if ((__ldg(a.view_meta + view) >> 31) && !caster)
+        const float4 *pl = a.planes + 6 * view;
+        const float4 q0 = __ldg(pl), q1 = __ldg(pl + 1), q2 = __ldg(pl + 2), q3 = __ldg(pl + 3), q4 = __ldg(pl + 4), q5 = __ldg(pl + 5);
+        if (__ldg(a.view_meta + view) >> 31) {                  // shadow casters only
+            const int64_t e = block_e0 + (__float_as_uint(r1.z) & (kMaskBlockEntities - 1));
+            if (a.caster_mask && ((__ldg(a.caster_mask + (e >> 5)) >> (e & 31)) & 1u) == 0u)
                 continue;
-            const float4 *pl = a.planes + 6 * view;
-            bool inside = true;
-#pragma unroll
-            for (int p = 0; p < 6 && inside; p++) {
-                const float4 q = __ldg(pl + p);
-                inside = !outside_plane(q.x, q.y, q.z, q.w, mn[0], mn[1], mn[2], mx[0], mx[1], mx[2]);
-            }
-            if (inside)
-                fm |= 1u << f;
         }
-        s_pairs[i] = fm ? ((((g << 13) | el) << 6) | fm) : 0xffffffffu;
-        n_valid += fm ? 1u : 0u;
+        const float mn[3] = { r0.x, r0.y, r0.z }, mx[3] = { r0.w, r1.x, r1.y };
+        const bool outside = outside_plane(q0.x, q0.y, q0.z, q0.w, mn[0], mn[1], mn[2], mx[0], mx[1], mx[2]) |
+                             outside_plane(q1.x, q1.y, q1.z, q1.w, mn[0], mn[1], mn[2], mx[0], mx[1], mx[2]) |
+                             outside_plane(q2.x, q2.y, q2.z, q2.w, mn[0], mn[1], mn[2], mx[0], mx[1], mx[2]) |
+                             outside_plane(q3.x, q3.y, q3.z, q3.w, mn[0], mn[1], mn[2], mx[0], mx[1], mx[2]) |
+                             outside_plane(q4.x, q4.y, q4.z, q4.w, mn[0], mn[1], mn[2], mx[0], mx[1], mx[2]) |
+                             outside_plane(q5.x, q5.y, q5.z, q5.w, mn[0], mn[1], mn[2], mx[0], mx[1], mx[2]);
+        if (!outside)
+            atomicOr(&s_pairs[i], 1u << f);
+    }
+    __syncthreads();
+    // the pairs some face accepted become records (group, entity, faces), the others are dropped
+    uint32_t n_valid = 0;
+    for (uint32_t i = tid; i < npairs; i += kSpThreads) {
+        const uint32_t pair = s_pairs[i], fm = pair & 63u;
+        uint32_t key = 0xffffffffu;
+        if (fm) {
+            const uint32_t el = __float_as_uint(__ldg(&list[2 * ((pair >> 6) & 8191u) + 1].z)) & (kMaskBlockEntities - 1);
+            key = ((((pair >> 19) << 13) | el) << 6) | fm;
+            n_valid++;
+        }
+        s_pairs[i] = key;
     }
     n_valid = __reduce_add_sync(0xffffffffu, n_valid);
     if (lane == 0 && n_valid)
@@ -823,10 +840,10 @@ mv_sparse_kernel(const __grid_constant__ MvArgs a) {
     if (npairs <= (uint32_t)kMvRankSortBelow) {
         uint32_t *s_out = s_pairs + kMvPairCapacity / 2;
         const uint32_t padded = (npairs + 3u) & ~3u;
-        for (uint32_t i = npairs + tid; i < padded; i += kMvThreads)
+        for (uint32_t i = npairs + tid; i < padded; i += kSpThreads)
             s_pairs[i] = 0xffffffffu;
         __syncthreads();
-        for (uint32_t i = tid; i < npairs; i += kMvThreads) {
+        for (uint32_t i = tid; i < npairs; i += kSpThreads) {
             const uint32_t key = s_pairs[i];
             if (key == 0xffffffffu)
                 continue;
@@ -843,12 +860,12 @@ mv_sparse_kernel(const __grid_constant__ MvArgs a) {
         uint32_t n_sort = 32;
         while (n_sort < npairs)
             n_sort <<= 1;
-        for (uint32_t i = npairs + tid; i < n_sort; i += kMvThreads)
+        for (uint32_t i = npairs + tid; i < n_sort; i += kSpThreads)
             s_pairs[i] = 0xffffffffu;
         __syncthreads();
         for (uint32_t k = 2; k <= n_sort; k <<= 1)
             for (uint32_t j = k >> 1; j > 0; j >>= 1) {
-                for (uint32_t i = tid; i < n_sort; i += kMvThreads) {
+                for (uint32_t i = tid; i < n_sort; i += kSpThreads) {
                     const uint32_t partner = i ^ j;
                     if (partner > i) {
                         const uint32_t x = s_pairs[i], y = s_pairs[partner];
@@ -864,7 +881,7 @@ mv_sparse_kernel(const __grid_constant__ MvArgs a) {
     }
 
     // ---- (5) rank inside (view, block), totals, items. Thread t owns records [t * per, (t + 1) * per).
-    const uint32_t per = (nrec + kMvThreads - 1) / kMvThreads;
+    const uint32_t per = (nrec + kSpThreads - 1) / kSpThreads;
     const uint32_t i0 = min(nrec, (uint32_t)tid * per), i1 = min(nrec, i0 + per);
     SegCount mine = { 0u, 0u, 0u, false };
     uint32_t my_items = 0;
@@ -902,7 +919,7 @@ mv_sparse_kernel(const __grid_constant__ MvArgs a) {
     if (lane == 31)
         s_seg[warp] = incl;
     uint32_t items_total;
-    const uint32_t item_rank = block_exclusive_scan(my_items, s_warp, &items_total);   // (contains the barriers s_seg needs)
+    const uint32_t item_rank = block_exclusive_scan<kSpThreads>(my_items, s_warp, &items_total);   // (contains the barriers s_seg needs)
     {
         SegCount before = { 0u, 0u, 0u, false };
         for (int k = 0; k < warp; k++)
@@ -1016,7 +1033,7 @@ void launch_mv_sparse(const MvArgs &a, int num_sms, cudaStream_t s) {
     if (grid > (long long)num_sms * 4)
         grid = (long long)num_sms * 4;
     launch_chained(mv_classify_kernel, dim3((unsigned)grid), smem, s, a);
-    launch_chained(mv_sparse_kernel, dim3((unsigned)a.num_blocks), 0, s, a);
+    launch_chained(mv_sparse_kernel, dim3((unsigned)a.num_blocks), 0, s, a, kSpThreads);
 }
 
 void launch_mv_expand_items(const MvArgs &a, cudaStream_t s) {
