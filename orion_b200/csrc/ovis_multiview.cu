@@ -36,6 +36,7 @@
 namespace ovis {
 
 constexpr int kMvThreads = 256;
+constexpr int kPlainThreads = 256, kPlainCtas = 2;   // mv_plain_test_kernel: 128 registers, 16 warps per SM (128 x 5 at 96 registers with a little spilling: 5 % slower)
 constexpr int kSpThreads = 256;           // mv_sparse_kernel (128-thread CTAs, eleven per SM - one wave for a 10 M-entity world - were
                                           // measured slower on every workload: 0.130 -> 0.161 ms for configs[2]'s shadow lists)
 constexpr int kMvBigSlots = 512;          // records per block that are tested against every group a warp each
@@ -146,12 +147,12 @@ __device__ __forceinline__ void test_view_run(const MvArgs &a, int pv, uint32_t 
     }
 }
 
-__global__ void __launch_bounds__(kMvThreads, 2)
+__global__ void __launch_bounds__(kPlainThreads, kPlainCtas)
 mv_plain_test_kernel(const __grid_constant__ MvArgs a) {
     chain_enter();
     const int lane = threadIdx.x & 31;
-    const long long warps_total = (long long)gridDim.x * (kMvThreads / 32);
-    const long long gwarp = (long long)blockIdx.x * (kMvThreads / 32) + (threadIdx.x >> 5);
+    const long long warps_total = (long long)gridDim.x * (kPlainThreads / 32);
+    const long long gwarp = (long long)blockIdx.x * (kPlainThreads / 32) + (threadIdx.x >> 5);
     const float4 *__restrict__ bounds = reinterpret_cast<const float4 *>(a.bounds);
     const int64_t vstride = a.stride >> 2;
     const int n_chunks = (a.n_plain + a.views_per_warp - 1) / a.views_per_warp;
@@ -999,14 +1000,14 @@ void launch_mv_plain_test(const MvArgs &a, int num_sms, cudaStream_t s) {
     const long long items = (long long)a.num_groups128 * n_chunks;
     static int per_sm = 0;
     if (!per_sm) {
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, mv_plain_test_kernel, kMvThreads, 0);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, mv_plain_test_kernel, kPlainThreads, 0);
         if (per_sm < 1)
             per_sm = 1;
     }
-    long long grid = (items + kMvThreads / 32 - 1) / (kMvThreads / 32);
+    long long grid = (items + kPlainThreads / 32 - 1) / (kPlainThreads / 32);
     if (grid > (long long)num_sms * per_sm)
         grid = (long long)num_sms * per_sm;
-    launch_chained(mv_plain_test_kernel, dim3((unsigned)grid), 0, s, a);
+    launch_chained(mv_plain_test_kernel, dim3((unsigned)grid), 0, s, a, kPlainThreads);
 }
 
 void launch_mv_expand_masks(const MvArgs &a, cudaStream_t s) {
