@@ -428,7 +428,7 @@ def run_ours(args, rank: int, local_rank: int, world_size: int):
                          ("gather kernel stores to peers over NVLink + ready flags, no collective" if sw.exchange_mode == "p2p"
                           else "NCCL all-gather")) if world_size > 1 else "1 GPU"),
         "cull_ms_per_frame": elapsed_ms / args.steps,
-        "roofline": {"bound": "hbm", "kernel": "ovis::cull_test_kernel<1,false,4> (dominant: reads every bound once)",
+        "roofline": {"bound": "hbm", "kernel": "ovis::cull_test_kernel<1,false,5> (dominant: reads every bound once)",
                      "achieved": achieved, "peak": peak_gbs, "unit": "GB/s", "frac": achieved / peak_gbs,
                      "traffic": ncu_traffic_bytes() if n == SHARD_ENTITIES else None,
                      "traffic_source": "profiles/r02_cull_test_kernel_ncu.csv (ncu --set full, one launch, same workload)",

@@ -379,15 +379,17 @@ class World:
         step.keep = keep
         return step
 
-    def bind_shadow_lists(self, main_view, cap_entities: int, shadow_res=512):
+    def bind_shadow_lists(self, main_view, cap_entities: int, shadow_res=512, pinned=False):
         """ovis_build_shadow_lists with its arguments marshalled once: step() -> (n_lists, n_entities); the lists are in
-        step.list_light / list_view / offsets / entities (referenced arrays, valid until the next step)."""
+        step.list_light / list_view / offsets / entities (referenced arrays, valid until the next step). pinned: the entity
+        buffer is page-locked (the copy of the ids is then asynchronous)."""
         main_view = np.ascontiguousarray(main_view, dtype=VIEW_DTYPE).reshape(1)
         _, _, nl_slots = self.counts()
         cap_lists = 6 * max(nl_slots, 1)
         ll, lv = np.zeros(cap_lists, dtype=np.int32), np.zeros(cap_lists, dtype=np.int32)
         off = np.zeros(cap_lists + 1, dtype=np.int64)
-        ent = np.zeros(max(int(cap_entities), 1), dtype=np.uint32)
+        hold = PinnedBuffer(max(int(cap_entities), 1)) if pinned else None
+        ent = hold.array if pinned else np.zeros(max(int(cap_entities), 1), dtype=np.uint32)
         nl, ne = C.c_int32(), C.c_int64()
         fn = self.lib.ovis_build_shadow_lists
         args = (self.h, _p(main_view), C.c_int32(shadow_res), C.c_int32(cap_lists), _p(ll), _p(lv), _p(off), C.byref(nl),
@@ -398,7 +400,7 @@ class World:
             if rc != OVIS_OK:
                 _check(rc)
             return nl.value, ne.value
-        step.keep = (main_view,)
+        step.keep = (main_view, hold)
         step.list_light, step.list_view, step.offsets, step.entities = ll, lv, off, ent
         return step
 

@@ -133,7 +133,7 @@ def config3(small, full_parity=True):
     lists_ms, _ = timed(stream, w.bind_cull_shadow_views_device(shadow_ids), iters=9)
     ll, lv, off, d_off, d_ent = w.cull_shadow_views_device(shadow_ids)
     full = w.shadow_lists(s["view"])
-    frame_lists = w.bind_shadow_lists(s["view"], cap_entities=max(4 * len(full[3]), 1 << 16))
+    frame_lists = w.bind_shadow_lists(s["view"], cap_entities=max(4 * len(full[3]), 1 << 16), pinned=True)
     frame_lists()
     t0 = time.perf_counter()
     for _ in range(9):
@@ -225,9 +225,9 @@ def config1():
 
     # the frame as a C++ caller makes it: both calls with their arguments marshalled once (the convenience wrappers above
     # allocate their result arrays per call, which at this size costs more than the library does)
-    out_e, out_l = np.zeros(max(n, 1), dtype=np.uint32), np.zeros(max(len(s["lights"]), 1), dtype=np.uint32)
-    frame_cull = w.bind_cull(s["view"], out_e, flags=lib.CULL_LIGHTS, out_lights=out_l)
-    frame_lists = w.bind_shadow_lists(s["view"], cap_entities=n * 6 * max(len(s["lights"]), 1))
+    pin_e, out_l = lib.PinnedBuffer(max(n, 1)), np.zeros(max(len(s["lights"]), 1), dtype=np.uint32)
+    frame_cull = w.bind_cull(s["view"], pin_e.array, flags=lib.CULL_LIGHTS, out_lights=out_l)
+    frame_lists = w.bind_shadow_lists(s["view"], cap_entities=n * 6 * max(len(s["lights"]), 1), pinned=True)
 
     def per_frame():
         frame_cull()
