@@ -88,11 +88,14 @@ int ovis_world_destroy(OvisWorld *world);
 int ovis_world_reserve(OvisWorld *world, int64_t n_entities, int64_t n_nodes);
 /* All kernels and copies of the world are issued on this cudaStream_t (default: the legacy stream). */
 int ovis_world_set_stream(OvisWorld *world, void *cuda_stream);
+/* The stream the world's work is ordered on and the device it lives on (either output may be NULL). */
+int ovis_world_get_stream(OvisWorld *world, void **out_cuda_stream, int32_t *out_device);
 /* Sharded worlds: this world holds the contiguous id range starting at id_base
  * of a larger scene; ids reported by the entity culls are local id + id_base, so the per-shard lists
  * concatenated in rank order are the single-world list of simple_render_world.cc:38-41. Ids passed
  * INTO the API stay local. Default 0. */
 int ovis_world_set_id_base(OvisWorld *world, uint32_t id_base);
+int ovis_world_get_id_base(OvisWorld *world, uint32_t *out_id_base);
 int ovis_world_counts(OvisWorld *world, int64_t *n_entities, int64_t *n_nodes, int32_t *n_lights);
 /* Live entities vs entity slots: removed entities keep their slot (ids are stable handles), so a world with spawn /
  * despawn churn grows, and as long as one slot is dead every cull reads the alive mask. */
@@ -437,8 +440,8 @@ int ovis_pack_view_uniforms_device(OvisWorld *world, int32_t n_views, const Ovis
 
 /* ------------------------------------------------------------------------------------------------
  * Deferred light pass and colour post effects over headless device buffers:
- * the arithmetic of the reference's shaders as CUDA kernels. The graphics API that rasterises the G-buffer
- * and the shadow maps is unavailable on this box: the caller supplies them as plain device arrays.
+ * the arithmetic of the reference's shaders as CUDA kernels. The G-buffer and the shadow maps are plain device
+ * arrays: filled by the headless rasteriser below (ovis_raster_*), or by the caller.
  * ---------------------------------------------------------------------------------------------- */
 typedef struct OvisGBuffer {            /* row-major, width x height, device pointers, 16-byte aligned */
     int32_t width, height;
@@ -469,6 +472,52 @@ enum { OVIS_POST_TONEMAP = 1u, OVIS_POST_GAMMA = 2u };
  * d_out_rgba may equal d_rgba. */
 int ovis_post_effects_device(OvisWorld *world, int64_t n_pixels, const float *d_rgba, uint32_t effects, float exposure,
                              float white_point, float gamma, float *d_out_rgba);
+
+/* ------------------------------------------------------------------------------------------------
+ * Headless rasteriser: what fills the G-buffer and the shadow maps the light pass above reads, as CUDA kernels -
+ * DeferredRenderPipeline::renderDeferredGBuffer and ::renderShadowMaps (render/src/deferred_render_pipeline.cc:384-412,
+ * 335-370) drawing the entities of a visible list with engine/shaders/lit_vtx.glsl + lit_deferred_frag.glsl, resp.
+ * shadow_vtx.glsl + shadow_frag.glsl, under the reference's default pipeline state (gpu/include/state.h:105-145: depth
+ * test LessOrEqual with depth write, back faces culled, counter-clockwise = front; clear depth 1, colours 0). Pixel
+ * centres at +0.5, row 0 = the bottom row (GL window coordinates, as ovis_shade_deferred_device reads them), top-left
+ * rule, perspective-correct interpolation, near / far clip per pixel. Flat material parameters only: the shader variants
+ * without TEXTURED and NORMALMAP. An OvisRaster belongs to one world and is driven from the same host thread; its work is
+ * ordered on the world's stream.
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct OvisRaster OvisRaster;
+enum { OVIS_MATERIAL_SPECULAR = 1u };   /* the SPECULAR shader keyword (lit_deferred_frag.glsl:68-73) */
+typedef struct OvisMaterial {
+    float    diffuse[3];                /* diffuseColour */
+    float    specular[3];               /* specularColour */
+    float    shininess;
+    uint32_t flags;
+} OvisMaterial;                         /* 32 bytes */
+typedef struct OvisGBufferTarget {      /* the writable form of OvisGBuffer: row-major, 16-byte aligned device pointers */
+    int32_t width, height;
+    float *d_buffer_a, *d_buffer_b, *d_buffer_c;   /* 4 floats per pixel each */
+    float *d_depth;                     /* 1 float per pixel */
+} OvisGBufferTarget;
+int ovis_raster_create(OvisWorld *world, OvisRaster **out_raster);
+int ovis_raster_destroy(OvisRaster *raster);
+/* A triangle mesh (Mesh / SubMesh vertex data as the OBJ loader builds it, engine/src/loaders/obj_loader.cc): positions and
+ * normals 3 floats per vertex, texcoords 2 per vertex or NULL, indices 3 per triangle into this mesh's vertices. */
+int ovis_raster_add_mesh(OvisRaster *raster, int64_t n_vertices, const float *positions, const float *normals,
+                         const float *texcoords, int64_t n_indices, const uint32_t *indices, uint32_t *out_mesh);
+int ovis_raster_add_material(OvisRaster *raster, const OvisMaterial *material, uint32_t *out_material);
+/* RenderEntity(subMesh, material) (graphics/src/mesh_renderer.cc:180-187): what entity ids[i] is drawn with. */
+int ovis_raster_bind_entities(OvisRaster *raster, int64_t n, const uint32_t *entity_ids, const uint32_t *mesh_ids,
+                              const uint32_t *material_ids);
+/* The G-buffer pass for the entities of a visible list (device ids + device count, e.g. from ovis_cull_planes_device),
+ * drawn in list order from `view` (its viewport must equal the target's size). Entities without a bound mesh are skipped.
+ * Synchronises the world's stream (it sizes its scratch from the list). */
+int ovis_raster_gbuffer_device(OvisRaster *raster, const OvisView *view, const uint32_t *d_visible, const uint32_t *d_visible_count,
+                               int64_t max_visible, const OvisGBufferTarget *target);
+/* The shadow-map passes: view k draws the entities d_entities[host_offsets[k] .. host_offsets[k + 1]) (the CSR result of
+ * ovis_cull_shadow_views_device, shadow casters only) depth-only into d_maps[k]: shadow_size x shadow_size floats, cleared
+ * to 1. d_maps is a HOST array of n_views device pointers (a point light's six faces are six consecutive views: point
+ * d_maps[k + f] at map + f * shadow_size^2 to build the layout ovis_shade_deferred_device reads). */
+int ovis_raster_shadow_maps_device(OvisRaster *raster, int32_t n_views, const OvisView *views, const int64_t *host_offsets,
+                                   const uint32_t *d_entities, int32_t shadow_size, float *const *d_maps);
 
 /* ------------------------------------------------------------------------------------------------
  * Scene import: the reference's on-disk formats, read into a world.
@@ -514,6 +563,13 @@ int ovis_scene_free(OvisScene *scene);
  * material or after any `g`; values parsed with strtof; engine/src/loaders/mesh_loader.cc:187-199: min/max over the
  * positions the sub-mesh's faces reference). 6 floats per sub-mesh. */
 int ovis_obj_submesh_aabbs(const char *obj_path, int32_t capacity, float *out_aabb, int32_t *out_count);
+/* The vertex data of the same file as OBJLoader builds it (obj_loader.cc:245-276): one vertex per distinct v/vt/vn triple
+ * in order of first use, shared by all sub-meshes; a quad becomes the triangles (0, 1, 2), (2, 3, 0). positions / normals
+ * 3 floats per vertex, texcoords 2; sub-mesh k owns indices [out_first_index[k], out_first_index[k + 1]) (cap_submeshes + 1
+ * entries). The sizes are always returned; OVIS_ERR_CAPACITY if a buffer is too small. Feeds ovis_raster_add_mesh. */
+int ovis_obj_mesh(const char *obj_path, int64_t cap_vertices, float *out_positions, float *out_normals, float *out_texcoords,
+                  int64_t cap_indices, uint32_t *out_indices, int32_t cap_submeshes, int64_t *out_first_index,
+                  int64_t *out_n_vertices, int64_t *out_n_indices, int32_t *out_n_submeshes);
 /* Diagnostic: the canonical text of a JSON document as the scene loader's own reader sees it (strings byte for byte,
  * members in file order, numbers as the float the reference's JSONSerialiser reads - GetFloat() = (float)double,
  * engine/src/json_serialiser.cc:540 - plus the integer when there is one). The test suite compares it with the same dump

@@ -243,6 +243,25 @@ class Oracle:
         self.lib.orc_light_uniforms(_p(light), _p(att), C.c_float(shadow_bias), _p(out))
         return out
 
+    # ---- headless rasteriser (ovis_raster.c)
+    def raster(self, matrix, mesh, material, vertices, indices, vp, width, height, depth_only=False):
+        """G-buffer pass (or a depth-only pass) over instances drawn in order -> (a, b, c, depth), rows bottom-up."""
+        matrix = _f32(matrix, (-1, 16))
+        n = len(matrix)
+        mesh = np.ascontiguousarray(mesh, dtype=np.int64).reshape(n, 3)
+        material = _f32(material, (n, 8))
+        vertices = _f32(vertices, (-1, 8))
+        indices = np.ascontiguousarray(indices, dtype=np.uint32)
+        vp = _f32(vp, (16,))
+        depth = np.zeros((height, width), dtype=np.float32)
+        if depth_only:
+            a = b = c = None
+        else:
+            a, b, c = (np.zeros((height, width, 4), dtype=np.float32) for _ in range(3))
+        self.lib.orc_raster(C.c_int64(n), _p(matrix), _p(mesh), _p(material), _p(vertices), _p(indices), _p(vp), C.c_int32(width),
+                            C.c_int32(height), _p(a), _p(b), _p(c), _p(depth))
+        return a, b, c, depth
+
     # ---- deferred shading and post effects (section 8(f) row 4)
     def shade_deferred(self, buffer_a, buffer_b, buffer_c, depth, view_uniforms, light_uniforms, light_types,
                        shadow_maps=None, shadow_size=0, glsl=False):

@@ -21,6 +21,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <array>
 #include <map>
 #include <memory>
 #include <string>
@@ -209,14 +210,24 @@ struct SubMeshBox {
     float box[6];
 };
 
+// The vertex data OBJLoader builds next to the boxes (obj_loader.cc:245-276): one vertex per distinct v/vt/vn triple in
+// order of first use, shared by all sub-meshes of the file; a quad becomes the triangles (0, 1, 2), (2, 3, 0).
+struct ObjGeometry {
+    std::vector<float> positions, normals, texcoords;           // 3, 3, 2 per vertex
+    std::vector<uint32_t> indices;
+    std::vector<int64_t> first_index;                           // per sub-mesh; the last entry is indices.size()
+};
+
 // obj_loader.cc:94-152 (line dispatch), :158-181 (vertex elements), :187-278 (faces), mesh_loader.cc:187-199 (box).
-int parse_obj(const char *path, std::vector<SubMeshBox> &out, std::string &error) {
+int parse_obj(const char *path, std::vector<SubMeshBox> &out, std::string &error, ObjGeometry *geo = nullptr) {
     std::string text;
     if (!read_file(path, text)) {
         error = std::string("cannot read ") + path;
         return OVIS_ERR_INVALID;
     }
-    std::vector<ovis::hm::Vec3> positions;
+    std::vector<ovis::hm::Vec3> positions, normals;
+    std::vector<float> texcoords;
+    std::map<std::array<uint32_t, 3>, uint32_t> vertex_of;      // (position, texcoord, normal) -> vertex (obj_loader.cc:245)
     size_t n_texcoords = 0, n_normals = 0;
     std::string current_material = "default";
     int current = -1;                                            // index into `out`, -1 = begin a new sub-mesh at the next face
@@ -250,10 +261,14 @@ int parse_obj(const char *path, std::vector<SubMeshBox> &out, std::string &error
             }
             if (tok[0] == "v")
                 positions.push_back({ val[0], val[1], val[2] });
-            else if (tok[0] == "vt")
+            else if (tok[0] == "vt") {
                 n_texcoords++;
-            else
+                texcoords.push_back(val[0]);
+                texcoords.push_back(val[1]);
+            } else {
                 n_normals++;
+                normals.push_back({ val[0], val[1], val[2] });
+            }
         } else if (tok[0] == "f") {
             const size_t nv = tok.size() - 1;
             if (nv != 3 && nv != 4)
@@ -261,7 +276,10 @@ int parse_obj(const char *path, std::vector<SubMeshBox> &out, std::string &error
             if (current < 0) {                                   // :188-192
                 out.push_back({ { FLT_MAX, FLT_MAX, FLT_MAX, -FLT_MAX, -FLT_MAX, -FLT_MAX } });   // mesh_loader.cc:188
                 current = (int)out.size() - 1;
+                if (geo)
+                    geo->first_index.push_back((int64_t)geo->indices.size());
             }
+            uint32_t face[4] = { 0, 0, 0, 0 };
             for (size_t i = 0; i < nv; i++) {
                 std::vector<std::string> sub;
                 tokenize(tok[i + 1], "/", false, sub);
@@ -289,6 +307,24 @@ int parse_obj(const char *path, std::vector<SubMeshBox> &out, std::string &error
                 float *b = out[(size_t)current].box;             // glm::min(minimum, position), glm::max(maximum, position)
                 b[0] = ovis::hm::glmMin(b[0], p.x); b[1] = ovis::hm::glmMin(b[1], p.y); b[2] = ovis::hm::glmMin(b[2], p.z);
                 b[3] = ovis::hm::glmMax(b[3], p.x); b[4] = ovis::hm::glmMax(b[4], p.y); b[5] = ovis::hm::glmMax(b[5], p.z);
+                if (geo) {
+                    if (idx[1] >= n_texcoords || idx[2] >= n_normals)
+                        return bad("vertex refers to a texture coordinate or normal that was not declared");
+                    auto ins = vertex_of.emplace(std::array<uint32_t, 3>{ (uint32_t)idx[0], (uint32_t)idx[1], (uint32_t)idx[2] },
+                                                 (uint32_t)(geo->positions.size() / 3));
+                    if (ins.second) {
+                        geo->positions.insert(geo->positions.end(), { p.x, p.y, p.z });
+                        const ovis::hm::Vec3 &nv3 = normals[idx[2]];
+                        geo->normals.insert(geo->normals.end(), { nv3.x, nv3.y, nv3.z });
+                        geo->texcoords.insert(geo->texcoords.end(), { texcoords[2 * idx[1]], texcoords[2 * idx[1] + 1] });
+                    }
+                    face[i] = ins.first->second;
+                }
+            }
+            if (geo) {                                           // :268-276
+                geo->indices.insert(geo->indices.end(), { face[0], face[1], face[2] });
+                if (nv == 4)
+                    geo->indices.insert(geo->indices.end(), { face[2], face[3], face[0] });
             }
         } else if (tok[0] == "usemtl") {
             if (tok.size() != 2)
@@ -303,10 +339,40 @@ int parse_obj(const char *path, std::vector<SubMeshBox> &out, std::string &error
             current = -1;                                        // :139
         }
     }
+    if (geo)
+        geo->first_index.push_back((int64_t)geo->indices.size());
     return OVIS_OK;
 }
 
 }  // namespace
+
+extern "C" int ovis_obj_mesh(const char *obj_path, int64_t cap_vertices, float *out_positions, float *out_normals, float *out_texcoords,
+                             int64_t cap_indices, uint32_t *out_indices, int32_t cap_submeshes, int64_t *out_first_index,
+                             int64_t *out_n_vertices, int64_t *out_n_indices, int32_t *out_n_submeshes) {
+    if (!obj_path || cap_vertices < 0 || cap_indices < 0 || cap_submeshes < 0 || !out_n_vertices || !out_n_indices || !out_n_submeshes)
+        return scene_error(OVIS_ERR_INVALID, "ovis_obj_mesh: bad arguments");
+    std::vector<SubMeshBox> boxes;
+    ObjGeometry geo;
+    std::string error;
+    int rc = parse_obj(obj_path, boxes, error, &geo);
+    if (rc != OVIS_OK)
+        return scene_error(rc, "%s", error.c_str());
+    const int64_t nv = (int64_t)geo.positions.size() / 3, ni = (int64_t)geo.indices.size();
+    *out_n_vertices = nv;
+    *out_n_indices = ni;
+    *out_n_submeshes = (int32_t)boxes.size();
+    if (nv > cap_vertices || ni > cap_indices || (int64_t)boxes.size() > cap_submeshes)
+        return scene_error(OVIS_ERR_CAPACITY, "%s: %lld vertices, %lld indices, %zu sub-meshes", obj_path, (long long)nv, (long long)ni, boxes.size());
+    if ((nv > 0 && (!out_positions || !out_normals || !out_texcoords)) || (ni > 0 && !out_indices) || !out_first_index)
+        return scene_error(OVIS_ERR_INVALID, "ovis_obj_mesh: null output");
+    memcpy(out_positions, geo.positions.data(), sizeof(float) * geo.positions.size());
+    memcpy(out_normals, geo.normals.data(), sizeof(float) * geo.normals.size());
+    memcpy(out_texcoords, geo.texcoords.data(), sizeof(float) * geo.texcoords.size());
+    memcpy(out_indices, geo.indices.data(), sizeof(uint32_t) * geo.indices.size());
+    for (size_t i = 0; i < geo.first_index.size(); i++)
+        out_first_index[i] = geo.first_index[i];
+    return OVIS_OK;
+}
 
 // Canonical text of a parsed document (see ovis_json_canonical in orion_vis.h). Numbers are written as the reference
 // consumes them: GetFloat() = (float)double, plus the integer when the double is one.

@@ -1466,6 +1466,21 @@ int ovis_world_set_stream(OvisWorld *w, void *cuda_stream) {
     return OVIS_OK;
 }
 
+int ovis_world_get_stream(OvisWorld *w, void **out_cuda_stream, int32_t *out_device) {
+    if (!w)
+        return fail(OVIS_ERR_INVALID, "world is null");
+    if (out_cuda_stream) *out_cuda_stream = (void *)w->stream;
+    if (out_device) *out_device = w->device;
+    return OVIS_OK;
+}
+
+int ovis_world_get_id_base(OvisWorld *w, uint32_t *out_id_base) {
+    if (!w || !out_id_base)
+        return fail(OVIS_ERR_INVALID, "ovis_world_get_id_base: null argument");
+    *out_id_base = w->id_base;
+    return OVIS_OK;
+}
+
 int ovis_world_set_id_base(OvisWorld *w, uint32_t id_base) {
     if (!w)
         return fail(OVIS_ERR_INVALID, "world is null");

@@ -832,3 +832,88 @@ def _world_shadow_views_host():
 
 
 _world_shadow_views_host()
+
+
+MATERIAL_DTYPE = np.dtype([("diffuse", np.float32, 3), ("specular", np.float32, 3), ("shininess", np.float32), ("flags", np.uint32)])
+MATERIAL_SPECULAR = 1
+
+
+class _GBufferTarget(C.Structure):
+    _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("a", C.c_void_p), ("b", C.c_void_p), ("c", C.c_void_p),
+                ("depth", C.c_void_p)]
+
+
+class Raster:
+    """ovis_raster_*: the headless rasteriser of one world (G-buffer pass and shadow-map passes as CUDA kernels)."""
+
+    def __init__(self, world: "World"):
+        self.lib = world.lib
+        self.world = world
+        self.h = C.c_void_p()
+        _check(self.lib.ovis_raster_create(world.h, C.byref(self.h)))
+
+    def close(self):
+        if self.h:
+            self.lib.ovis_raster_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def add_mesh(self, positions, normals, indices, texcoords=None) -> int:
+        positions, normals = _f32(positions, (-1, 3)), _f32(normals, (-1, 3))
+        indices = _u32(indices)
+        tc = _f32(texcoords, (-1, 2)) if texcoords is not None else None
+        out = C.c_uint32()
+        _check(self.lib.ovis_raster_add_mesh(self.h, C.c_int64(len(positions)), _p(positions), _p(normals), _p(tc),
+                                             C.c_int64(len(indices)), _p(indices), C.byref(out)))
+        return out.value
+
+    def add_material(self, diffuse, specular=(0.0, 0.0, 0.0), shininess=0.0, flags=0) -> int:
+        m = np.zeros(1, dtype=MATERIAL_DTYPE)
+        m["diffuse"], m["specular"], m["shininess"], m["flags"] = diffuse, specular, shininess, flags
+        out = C.c_uint32()
+        _check(self.lib.ovis_raster_add_material(self.h, _p(m), C.byref(out)))
+        return out.value
+
+    def bind_entities(self, entity_ids, mesh_ids, material_ids):
+        e, me, ma = _u32(entity_ids), _u32(mesh_ids), _u32(material_ids)
+        me = np.ascontiguousarray(np.broadcast_to(me, e.shape), dtype=np.uint32)
+        ma = np.ascontiguousarray(np.broadcast_to(ma, e.shape), dtype=np.uint32)
+        _check(self.lib.ovis_raster_bind_entities(self.h, C.c_int64(len(e)), _p(e), _p(me), _p(ma)))
+
+    def gbuffer(self, view, d_visible: int, d_count: int, width: int, height: int, d_a: int, d_b: int, d_c: int, d_depth: int,
+                max_visible=-1):
+        """The G-buffer pass for a device list (raw device pointers, e.g. torch tensors' data_ptr())."""
+        view = np.ascontiguousarray(view, dtype=VIEW_DTYPE).reshape(1)
+        t = _GBufferTarget(width, height, d_a, d_b, d_c, d_depth)
+        _check(self.lib.ovis_raster_gbuffer_device(self.h, _p(view), C.c_void_p(d_visible), C.c_void_p(d_count), C.c_int64(max_visible),
+                                                   C.byref(t)))
+
+    def shadow_maps(self, views, host_offsets, d_entities: int, shadow_size: int, d_maps):
+        views = np.ascontiguousarray(views, dtype=VIEW_DTYPE).reshape(-1)
+        off = np.ascontiguousarray(host_offsets, dtype=np.int64)
+        maps = (C.c_void_p * len(views))(*[int(p) for p in d_maps])
+        _check(self.lib.ovis_raster_shadow_maps_device(self.h, C.c_int32(len(views)), _p(views), _p(off), C.c_void_p(d_entities),
+                                                       C.c_int32(shadow_size), maps))
+
+
+def obj_mesh(path: str):
+    """ovis_obj_mesh: (positions [n, 3], normals [n, 3], texcoords [n, 2], indices, first_index per sub-mesh + end)."""
+    L = load()
+    nv, ni, ns = C.c_int64(), C.c_int64(), C.c_int32()
+    rc = L.ovis_obj_mesh(path.encode(), C.c_int64(0), None, None, None, C.c_int64(0), None, C.c_int32(0), None, C.byref(nv), C.byref(ni),
+                         C.byref(ns))
+    if rc not in (OVIS_OK, OVIS_ERR_CAPACITY):
+        _check(rc)
+    pos = np.zeros((nv.value, 3), dtype=np.float32)
+    nrm = np.zeros((nv.value, 3), dtype=np.float32)
+    tc = np.zeros((nv.value, 2), dtype=np.float32)
+    idx = np.zeros(ni.value, dtype=np.uint32)
+    first = np.zeros(ns.value + 1, dtype=np.int64)
+    _check(L.ovis_obj_mesh(path.encode(), C.c_int64(nv.value), _p(pos), _p(nrm), _p(tc), C.c_int64(ni.value), _p(idx), C.c_int32(ns.value),
+                           _p(first), C.byref(nv), C.byref(ni), C.byref(ns)))
+    return pos, nrm, tc, idx, first

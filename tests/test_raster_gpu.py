@@ -1,0 +1,183 @@
+"""The headless rasteriser (ovis_raster_*: G-buffer pass and shadow-map passes as CUDA kernels) against its CPU
+restatement (oracle/ovis_raster.c): every pixel of every buffer must be the same value - the two evaluate the same IEEE
+operations in the same order. The instance matrices on the oracle side come from the oracle's own EntityUniforms
+(Transform::matrix), the view-projection from its own view matrices."""
+import numpy as np
+import pytest
+
+from orion_b200 import lib, scenes
+import vis_testutil as util
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def oracle():
+    from oracle import pyoracle
+    return pyoracle.load("best")
+
+
+def cube_mesh():
+    """Unit cube, 24 vertices (a normal per face), 12 triangles, counter-clockwise seen from outside."""
+    faces = [((1, 0, 0), (0, 1, 0), (0, 0, 1)), ((-1, 0, 0), (0, 0, 1), (0, 1, 0)), ((0, 1, 0), (0, 0, 1), (1, 0, 0)),
+             ((0, -1, 0), (1, 0, 0), (0, 0, 1)), ((0, 0, 1), (1, 0, 0), (0, 1, 0)), ((0, 0, -1), (0, 1, 0), (1, 0, 0))]
+    pos, nrm, idx = [], [], []
+    for n, u, v in faces:
+        n, u, v = np.array(n, np.float32), np.array(u, np.float32), np.array(v, np.float32)
+        base = len(pos)
+        for su, sv in ((-1, -1), (1, -1), (1, 1), (-1, 1)):
+            pos.append(0.5 * (n + su * u + sv * v))
+            nrm.append(n)
+        idx += [base, base + 1, base + 2, base, base + 2, base + 3]
+    return np.array(pos, np.float32), np.array(nrm, np.float32), np.array(idx, np.uint32)
+
+
+def quad_mesh():
+    """A quad in the xz plane facing +y (the cubes demo's floor)."""
+    pos = np.array([[-0.5, 0, -0.5], [-0.5, 0, 0.5], [0.5, 0, 0.5], [0.5, 0, -0.5]], np.float32)
+    nrm = np.tile(np.array([[0, 1, 0]], np.float32), (4, 1))
+    return pos, nrm, np.array([0, 1, 2, 0, 2, 3], np.uint32)
+
+
+class Scene:
+    def __init__(self, rng, n_cubes, spread, with_floor=True):
+        self.meshes = [cube_mesh(), quad_mesh()]
+        self.materials = np.zeros(3, dtype=lib.MATERIAL_DTYPE)
+        self.materials[0] = ((0.8, 0.2, 0.1), (0.5, 0.5, 0.5), 16.0, lib.MATERIAL_SPECULAR)
+        self.materials[1] = ((0.1, 0.6, 0.3), (0.0, 0.0, 0.0), 0.0, 0)
+        self.materials[2] = ((0.4, 0.4, 0.9), (0.25, 0.5, 1.0), 64.0, lib.MATERIAL_SPECULAR)
+        n = n_cubes + (1 if with_floor else 0)
+        trs = np.zeros((n, 10), dtype=np.float32)
+        trs[:, 0:3] = rng.uniform(-spread, spread, (n, 3))
+        trs[:, 3:7] = scenes.random_unit_quats(rng, n)
+        trs[:, 7:10] = rng.uniform(0.5, 3.0, (n, 3))
+        self.mesh_of = np.zeros(n, dtype=np.uint32)
+        self.material_of = rng.integers(0, 3, n).astype(np.uint32)
+        if with_floor:
+            trs[-1] = (0, -spread, 0, 1, 0, 0, 0, 8 * spread, 1, 8 * spread)
+            self.mesh_of[-1] = 1
+            self.material_of[-1] = 1
+        self.trs = trs
+        self.local_aabb = np.tile(np.array([[-0.5, -0.5, -0.5, 0.5, 0.5, 0.5]], np.float32), (n, 1))
+        if with_floor:
+            self.local_aabb[-1] = (-0.5, 0, -0.5, 0.5, 0, 0.5)
+        self.flags = np.ones(n, dtype=np.uint32)
+        # the oracle's flat arrays
+        self.vertices = np.concatenate([np.concatenate([p, nr, np.zeros((len(p), 2), np.float32)], axis=1) for p, nr, _ in self.meshes])
+        self.indices = np.concatenate([i for _, _, i in self.meshes])
+        first_v = np.cumsum([0] + [len(p) for p, _, _ in self.meshes])
+        first_i = np.cumsum([0] + [len(i) for _, _, i in self.meshes])
+        self.mesh_ref = np.array([[first_v[m], first_i[m], len(self.meshes[m][2]) // 3] for m in range(len(self.meshes))], dtype=np.int64)
+
+    def build(self):
+        w = lib.World(0)
+        e0 = w.add_entities(self.local_aabb, self.flags)
+        ids = np.arange(e0, e0 + len(self.trs), dtype=np.uint32)
+        w.set_transforms(ids, self.trs)
+        r = lib.Raster(w)
+        mesh_ids = [r.add_mesh(p, n, i) for p, n, i in self.meshes]
+        mat_ids = [r.add_material(m["diffuse"], m["specular"], float(m["shininess"]), int(m["flags"])) for m in self.materials]
+        assert mesh_ids == [0, 1] and mat_ids == [0, 1, 2]
+        r.bind_entities(ids, self.mesh_of, self.material_of)
+        return w, r
+
+    def oracle_inputs(self, oracle, entity_ids):
+        uniforms = oracle.entity_uniforms(self.trs[entity_ids])
+        mats = np.zeros((len(entity_ids), 8), dtype=np.float32)
+        m = self.materials[self.material_of[entity_ids]]
+        mats[:, 0:3], mats[:, 3:6], mats[:, 6], mats[:, 7] = m["diffuse"], m["specular"], m["shininess"], m["flags"]
+        return uniforms[:, :16], self.mesh_ref[self.mesh_of[entity_ids]], mats
+
+
+def _same(a, b):
+    return np.array_equal(a.view(np.uint32), b.view(np.uint32))
+
+
+@pytest.mark.parametrize("case", ["outside_looking_in", "camera_among_the_cubes"])
+def test_gbuffer_pass_equals_the_restatement(oracle, case):
+    import torch
+    rng = np.random.default_rng(900 if case == "outside_looking_in" else 901)
+    sc = Scene(rng, 40, 6.0)
+    w, r = sc.build()
+    width, height = 200, 120
+    if case == "outside_looking_in":
+        view = scenes.make_view((0, 2, 22), (1, 0, 0, 0), 70.0, 0.1, 200.0, width, height)
+    else:                                   # cubes cross the near plane and surround the camera: no clipping anywhere
+        view = scenes.make_view((0.5, 0.2, 0.3), scenes.quat_yaw_pitch(30.0, -10.0), 95.0, 0.3, 60.0, width, height)
+    planes = lib.view_planes(view)
+    d_vis = torch.zeros(len(sc.trs) + 1, dtype=torch.int32, device="cuda")
+    w.cull_planes_device(planes, d_vis.data_ptr() + 4, d_vis.data_ptr())
+    a, b, c = (torch.full((height, width, 4), -1.0, dtype=torch.float32, device="cuda") for _ in range(3))
+    depth = torch.full((height, width), -1.0, dtype=torch.float32, device="cuda")
+    for _ in range(2):                      # the second call reuses every scratch buffer
+        r.gbuffer(view, d_vis.data_ptr() + 4, d_vis.data_ptr(), width, height, a.data_ptr(), b.data_ptr(), c.data_ptr(), depth.data_ptr())
+    torch.cuda.synchronize()
+    vis = d_vis.cpu().numpy().view(np.uint32)
+    ids = vis[1:1 + vis[0]]
+    assert len(ids) > 10
+    matrix, mesh, material = sc.oracle_inputs(oracle, ids)
+    vp = oracle.view_matrices(view)[0][2]
+    ea, eb, ec, ed = oracle.raster(matrix, mesh, material, sc.vertices, sc.indices, vp, width, height)
+    covered = ed < 1.0
+    assert 0.2 < covered.mean() < 1.0       # the picture is neither empty nor trivial
+    assert _same(depth.cpu().numpy(), ed)
+    assert _same(a.cpu().numpy(), ea) and _same(b.cpu().numpy(), eb) and _same(c.cpu().numpy(), ec)
+    # normals decode to unit vectors wherever something was drawn; the cleared pixels hold the clear values
+    n = ea[covered][:, :3] * 2.0 - 1.0
+    assert np.allclose(np.linalg.norm(n, axis=1), 1.0, atol=1e-5)
+    assert np.all(ea[~covered] == 0.0) and np.all(ed[~covered] == 1.0)
+    r.close()
+    w.close()
+
+
+def test_shadow_map_passes_equal_the_restatement(oracle):
+    import torch
+    rng = np.random.default_rng(902)
+    sc = Scene(rng, 60, 8.0)
+    sc.flags[::3] = 0                        # a third of the entities cast no shadow: not in the lists, not in the maps
+    w, r = sc.build()
+    lights = np.zeros(2, dtype=scenes.LIGHT_DTYPE)
+    lights[0] = scenes.make_light(scenes.LIGHT_POINT, position=(1, 1, -2), range=40.0, flags=1)
+    lights[1] = scenes.make_light(scenes.LIGHT_SPOT, position=(0, 14, 3), direction=(0.1, -1, -0.2), range=50.0, cutoff=35.0, flags=1)
+    w.add_lights(lights)
+    size = 96
+    ll, lv, off, d_off, d_ent = w.cull_shadow_views_device(np.arange(2, dtype=np.uint32), shadow_res=size)
+    assert len(ll) == 7
+    views = np.stack([lib.light_shadow_views(lights[ll[k]], size)[lv[k]] for k in range(len(ll))])
+    maps = torch.full((len(ll), size, size), -1.0, dtype=torch.float32, device="cuda")
+    r.shadow_maps(views, off, d_ent, size, [maps[k].data_ptr() for k in range(len(ll))])
+    torch.cuda.synchronize()
+    ent = w.read_device(d_ent, int(off[-1]))
+    got = maps.cpu().numpy()
+    drawn = 0
+    for k in range(len(ll)):
+        ids = ent[off[k]:off[k + 1]]
+        assert np.all(sc.flags[ids] == 1)
+        matrix, mesh, material = sc.oracle_inputs(oracle, ids)
+        vp = oracle.view_matrices(views[k])[0][2]
+        _, _, _, ed = oracle.raster(matrix, mesh, material, sc.vertices, sc.indices, vp, size, size, depth_only=True)
+        assert _same(got[k], ed), k
+        drawn += int((ed < 1.0).sum())
+    assert drawn > 2000
+    r.close()
+    w.close()
+
+
+def test_raster_argument_checks():
+    w = lib.World(0)
+    w.add_entities(np.array([[-1, -1, -1, 1, 1, 1]], np.float32))
+    r = lib.Raster(w)
+    p, n, i = cube_mesh()
+    with pytest.raises(lib.OvisError):
+        r.add_mesh(p, n, np.array([0, 1, 99], np.uint32))          # index out of range
+    with pytest.raises(lib.OvisError):
+        r.add_mesh(p, n, i[:5])                                      # not a multiple of three
+    m = r.add_mesh(p, n, i)
+    with pytest.raises(lib.OvisError):
+        r.bind_entities([0], [m], [0])                               # no material yet
+    mat = r.add_material((1, 1, 1))
+    with pytest.raises(lib.OvisError):
+        r.bind_entities([5], [m], [mat])                             # unknown entity
+    r.bind_entities([0], [m], [mat])
+    r.close()
+    w.close()
