@@ -557,6 +557,9 @@ int ovis_scene_info(const OvisScene *scene, OvisSceneInfo *out_info);
 int ovis_scene_arrays(const OvisScene *scene, int32_t *out_parent, float *out_local_trs, float *out_local_aabb, uint32_t *out_flags,
                       uint32_t *out_entity_node, OvisLight *out_lights, float *out_light_shading, OvisView *out_cameras);
 int ovis_scene_instantiate(const OvisScene *scene, OvisWorld *world, OvisSceneInfo *out_info);
+/* What render entity `entity` (0-based, in the scene's order) draws: the .obj file of its MeshRenderer's mesh asset and the
+ * sub-mesh index (mesh_renderer.cc:129-134); an empty path and -1 for a Skybox. Feeds ovis_obj_mesh / ovis_raster_add_mesh. */
+int ovis_scene_entity_mesh(const OvisScene *scene, int64_t entity, char *out_obj_path, int32_t capacity, int32_t *out_submesh);
 int ovis_scene_free(OvisScene *scene);
 /* Local bounding box of every sub-mesh of a Wavefront .obj file, as OBJLoader + MeshLoader::calculateBoundingBox produce
  * them (engine/src/loaders/obj_loader.cc:94-279: a sub-mesh starts at the first face after a `usemtl` that changes the

@@ -520,6 +520,8 @@ struct Importer {
     std::vector<Trs> node_world;
     std::vector<float> ent_aabb;                                  // 6 per render entity, local
     std::vector<uint32_t> ent_flags, ent_node;
+    std::vector<std::string> ent_asset;                           // per render entity: the mesh asset ("" for a skybox)
+    std::vector<int32_t> ent_submesh;                             // ... and the sub-mesh index (-1 for a skybox)
     std::vector<OvisLight> lights;
     std::vector<float> light_shading;                             // attenuation[3], bias per light
     std::vector<uint32_t> light_node;                             // the Entity (node) each light component sits on
@@ -567,6 +569,8 @@ struct Importer {
                 ent_aabb.insert(ent_aabb.end(), box, box + 6);
                 ent_flags.push_back(flags);
                 ent_node.push_back(node);
+                ent_asset.emplace_back();
+                ent_submesh.push_back(-1);
                 return true;
             }
             const Json *p = props(c);
@@ -581,6 +585,8 @@ struct Importer {
                 ent_aabb.insert(ent_aabb.end(), b.box, b.box + 6);
                 ent_flags.push_back(flags);
                 ent_node.push_back(node);
+                ent_asset.push_back(asset->str);
+                ent_submesh.push_back((int32_t)(&b - boxes->data()));
             }
             return true;
         }
@@ -689,6 +695,9 @@ struct Importer {
 }  // namespace
 
 struct OvisScene {
+    std::vector<std::string> ent_asset;
+    std::vector<int32_t> ent_submesh;
+    std::string game_dir;
     std::vector<int32_t> node_parent;
     std::vector<float> node_trs, ent_aabb, light_shading;
     std::vector<uint32_t> ent_flags, ent_node, light_node;
@@ -744,6 +753,9 @@ int ovis_scene_load(const char *world_path, const char *game_asset_dir, int32_t 
     sc->ent_aabb = std::move(imp.ent_aabb);
     sc->ent_flags = std::move(imp.ent_flags);
     sc->ent_node = std::move(imp.ent_node);
+    sc->ent_asset = std::move(imp.ent_asset);
+    sc->ent_submesh = std::move(imp.ent_submesh);
+    sc->game_dir = imp.game_dir;
     sc->lights = std::move(imp.lights);
     sc->light_shading = std::move(imp.light_shading);
     sc->light_node = std::move(imp.light_node);
@@ -755,6 +767,18 @@ int ovis_scene_load(const char *world_path, const char *game_asset_dir, int32_t 
 
 int ovis_scene_free(OvisScene *scene) {
     delete scene;
+    return OVIS_OK;
+}
+
+int ovis_scene_entity_mesh(const OvisScene *scene, int64_t entity, char *out_obj_path, int32_t capacity, int32_t *out_submesh) {
+    if (!scene || entity < 0 || entity >= (int64_t)scene->ent_asset.size() || capacity < 0 || (capacity > 0 && !out_obj_path) || !out_submesh)
+        return scene_error(OVIS_ERR_INVALID, "ovis_scene_entity_mesh: bad arguments");
+    const std::string &asset = scene->ent_asset[(size_t)entity];
+    *out_submesh = scene->ent_submesh[(size_t)entity];
+    const std::string path = asset.empty() ? std::string() : scene->game_dir + "/" + asset.substr(5) + ".obj";
+    if ((int64_t)path.size() + 1 > capacity)
+        return scene_error(OVIS_ERR_CAPACITY, "ovis_scene_entity_mesh: the path needs %zu bytes", path.size() + 1);
+    std::memcpy(out_obj_path, path.c_str(), path.size() + 1);
     return OVIS_OK;
 }
 

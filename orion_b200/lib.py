@@ -166,6 +166,13 @@ def load_scene(world_path: str, game_asset_dir: str, vp_width: int, vp_height: i
                "shadow_map_resolution": info.shadow_map_resolution}
         _check(lib.ovis_scene_arrays(h, _p(out["parent"]), _p(out["local_trs"]), _p(out["local_aabb"]), _p(out["flags"]),
                                      _p(out["entity_node"]), _p(out["lights"]), _p(out["shading"]), _p(out["cameras"])))
+        meshes = []                                  # per render entity: (.obj path or "", sub-mesh index or -1)
+        buf = C.create_string_buffer(4096)
+        sub = C.c_int32()
+        for e in range(info.n_entities):
+            _check(lib.ovis_scene_entity_mesh(h, C.c_int64(e), buf, C.c_int32(len(buf)), C.byref(sub)))
+            meshes.append((buf.value.decode(), sub.value))
+        out["entity_mesh"] = meshes
         return out
     finally:
         lib.ovis_scene_free(h)

@@ -163,6 +163,60 @@ def test_shadow_map_passes_equal_the_restatement(oracle):
     w.close()
 
 
+def test_whole_frame_against_the_restatements(oracle):
+    """tools/render_frame.py's built-in scene, every stage of the frame held against its CPU restatement: visible lists ->
+    shadow maps and G-buffer (bit for bit) -> light pass with shadows (the tolerance of the shading test: CUDA powf) ->
+    tonemap + gamma."""
+    import os
+    import sys
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tools"))
+    import render_frame
+    st = {}
+    width, height = 160, 90
+    render_frame.render(width=width, height=height, keep_state=st, shadow_size=64)
+    d = render_frame.builtin_scene.description
+    pos, nrm, idx = d["mesh"]
+    vertices = np.concatenate([pos, nrm, np.zeros((len(pos), 2), np.float32)], axis=1)
+    mat_table = np.array([list(m[0]) + list(m[1]) + [m[2], float(m[3])] for m in d["materials"]], dtype=np.float32)
+
+    def inputs(ids):
+        return (oracle.entity_uniforms(d["trs"][ids])[:, :16], np.tile(np.array([[0, 0, len(idx) // 3]], np.int64), (len(ids), 1)),
+                mat_table[d["material_of"][ids]])
+
+    view = st["view"]
+    mats = oracle.view_matrices(view)[0]
+    # the visible list and the G-buffer
+    boxes = st["world"].world_aabbs()
+    assert np.array_equal(st["visible_entities"], oracle.cull_aabb(boxes, oracle.view_planes(view)))
+    ea, eb, ec, ed = oracle.raster(*inputs(st["visible_entities"]), vertices, idx, mats[2], width, height)
+    assert _same(st["depth"], ed) and _same(st["a"], ea) and _same(st["b"], eb) and _same(st["c"], ec)
+    assert (ed < 1.0).mean() > 0.5
+    # the shadow maps of the visible shadow-casting lights
+    ll, lv, off, ent = st["shadow_lists"]
+    size = st["shadow_size"]
+    assert len(ll) == 13                                          # one spot + two point lights
+    for k in range(len(ll)):
+        sv = lib.light_shadow_views(st["lights"][ll[k]], size)[lv[k]]
+        _, _, _, em = oracle.raster(*inputs(ent[off[k]:off[k + 1]]), vertices, idx, oracle.view_matrices(sv)[0][2], size, size, depth_only=True)
+        assert _same(st["shadow_maps"][int(ll[k])][lv[k]], em), k
+    # the light pass over the G-buffer and the maps, then the post effects
+    w = st["world"]
+    vis = st["visible_lights"]
+    lu = np.stack([oracle.light_uniforms(w.light(int(i))[0], w.light(int(i))[1], float(w.light(int(i))[2])) for i in vis])
+    types = np.array([st["lights"][int(i)]["type"] for i in vis], dtype=np.int32)
+    maps = [st["shadow_maps"].get(int(i)) for i in vis]
+    exp = oracle.shade_deferred(ea, eb, ec, ed, oracle.view_uniforms(view), lu, types, maps, size)
+    err = np.abs(st["hdr"] - exp) / np.maximum(np.abs(exp), 1e-3)
+    assert err.max() <= 1e-5, err.max()
+    lit = exp[..., :3].sum(axis=2)
+    assert (lit > 0.05).mean() > 0.3
+    no_shadows = oracle.shade_deferred(ea, eb, ec, ed, oracle.view_uniforms(view), lu, types, None, 0)
+    assert (no_shadows[..., :3].sum(axis=2) > lit + 1e-3).mean() > 0.02       # the shadow maps do darken part of the picture
+    ldr = oracle.gamma(oracle.tonemap(exp.reshape(-1, 4), 1.0, 11.2), 2.2).reshape(height, width, 4)
+    assert np.allclose(st["ldr"], ldr, rtol=1e-4, atol=1e-5)
+    w.close()
+
+
 def test_raster_argument_checks():
     w = lib.World(0)
     w.add_entities(np.array([[-1, -1, -1, 1, 1, 1]], np.float32))
