@@ -126,6 +126,31 @@ namespace gamma_correction {
 #undef __POST_EFFECT_H
 }
 
+/* ---- the shaders the rasteriser runs (oracle/ovis_raster.c restates them): lit_vtx.glsl, lit_deferred_frag.glsl without
+ * TEXTURED / NORMALMAP, shadow_vtx.glsl. The uniform blocks and material parameters are injected by the engine's shader
+ * compiler, here by hand; `X.rgb = e;` was rewritten to set_rgb(X, e) (a swizzle on the left of an assignment). */
+struct EntityBlock { mat4 transform; vec3 position; };          /* render/include/render_entity.h:34-37 */
+static thread_local EntityBlock entity;
+static thread_local vec4 gl_Position;
+static thread_local vec3 diffuseColour, specularColour;
+static thread_local float shininess;
+inline void set_rgb(vec4 &dst, const vec3 &v) { dst.x = v.x; dst.y = v.y; dst.z = v.z; }
+
+namespace lit_vtx {
+#include "_ref/glsl/lit_vtx.glsl"
+}
+namespace shadow_vtx {
+#include "_ref/glsl/shadow_vtx.glsl"
+}
+namespace lit_frag {
+#include "_ref/glsl/lit_deferred_frag.glsl"
+}
+namespace lit_frag_specular {
+#define SPECULAR
+#include "_ref/glsl/lit_deferred_frag.glsl"
+#undef SPECULAR
+}
+
 #undef layout
 #undef uniform
 #undef in
@@ -188,6 +213,48 @@ void orc_glsl_shade_deferred(int32_t width, int32_t height, const float *buffer_
             o[0] = sum.x; o[1] = sum.y; o[2] = sum.z; o[3] = 1.0f;
         }
     delete[] depth4;
+}
+
+/* lit_vtx.glsl's main() for one vertex: clip position and world-space normal (the two outputs the rasteriser consumes) */
+void orc_glsl_lit_vertex(const float *transform, const float *view_projection, const float *position, const float *normal,
+                         float *out_clip, float *out_normal) {
+    using namespace glsl;
+    memcpy(&entity.transform, transform, 64);
+    memcpy(&view.viewProjection, view_projection, 64);
+    lit_vtx::attribPosition = vec3(position[0], position[1], position[2]);
+    lit_vtx::attribNormal = vec3(normal[0], normal[1], normal[2]);
+    lit_vtx::attribTexcoord = vec2(0.0f);
+    lit_vtx::shader_main();
+    out_clip[0] = gl_Position.x; out_clip[1] = gl_Position.y; out_clip[2] = gl_Position.z; out_clip[3] = gl_Position.w;
+    out_normal[0] = lit_vtx::vtxNormal.x; out_normal[1] = lit_vtx::vtxNormal.y; out_normal[2] = lit_vtx::vtxNormal.z;
+}
+
+void orc_glsl_shadow_vertex(const float *transform, const float *view_projection, const float *position, float *out_clip) {
+    using namespace glsl;
+    memcpy(&entity.transform, transform, 64);
+    memcpy(&view.viewProjection, view_projection, 64);
+    shadow_vtx::attribPosition = vec3(position[0], position[1], position[2]);
+    shadow_vtx::shader_main();
+    out_clip[0] = gl_Position.x; out_clip[1] = gl_Position.y; out_clip[2] = gl_Position.z; out_clip[3] = gl_Position.w;
+}
+
+/* lit_deferred_frag.glsl's main() for one fragment; material = diffuse rgb, specular rgb, shininess, SPECULAR keyword (0 / 1) */
+void orc_glsl_lit_fragment(const float *normal, const float *material, float *out_a, float *out_b, float *out_c) {
+    using namespace glsl;
+    diffuseColour = vec3(material[0], material[1], material[2]);
+    specularColour = vec3(material[3], material[4], material[5]);
+    shininess = material[6];
+    vec4 a, b, c;
+    if (material[7] != 0.0f) {
+        lit_frag_specular::vtxNormal = vec3(normal[0], normal[1], normal[2]);
+        lit_frag_specular::shader_main();
+        a = lit_frag_specular::deferredBufferA; b = lit_frag_specular::deferredBufferB; c = lit_frag_specular::deferredBufferC;
+    } else {
+        lit_frag::vtxNormal = vec3(normal[0], normal[1], normal[2]);
+        lit_frag::shader_main();
+        a = lit_frag::deferredBufferA; b = lit_frag::deferredBufferB; c = lit_frag::deferredBufferC;
+    }
+    memcpy(out_a, &a, 16); memcpy(out_b, &b, 16); memcpy(out_c, &c, 16);
 }
 
 void orc_glsl_tonemap(int64_t n_pixels, const float *rgba, float exposure_, float white_point, float *out_rgba) {

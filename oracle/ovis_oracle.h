@@ -144,6 +144,9 @@ void orc_gamma(int64_t n_pixels, const float *rgba, float gamma, float *out_rgba
 #ifdef __cplusplus
 }
 #endif
+void orc_raster_vertex(const float *transform, const float *view_projection, const float *position, const float *normal,
+                       float *out_clip, float *out_normal);
+void orc_raster_fragment(const float *normal, const float *material, float *out_a, float *out_b, float *out_c);
 /* ovis_raster.c: the G-buffer pass / a shadow-map pass over the given instances (see the file's header) */
 void orc_raster(int64_t n_instances, const float *matrix, const int64_t *mesh, const float *material, const float *vertices,
                 const uint32_t *indices, const float *vp, int32_t width, int32_t height, float *out_a, float *out_b, float *out_c,

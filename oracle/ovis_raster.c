@@ -45,6 +45,27 @@ static void mat4_vec4(const float *M, float x, float y, float z, float w, float 
         out[r] = (M[r] * x + M[4 + r] * y) + (M[8 + r] * z + M[12 + r] * w);
 }
 
+/* the two shader stages on their own, for comparison with the reference's shader source (oracle/glsl_harness.cc) */
+void orc_raster_vertex(const float *transform, const float *view_projection, const float *position, const float *normal,
+                       float *out_clip, float *out_normal) {
+    float mvp[16], nrm[4];
+    mat4_mul(view_projection, transform, mvp);
+    mat4_vec4(mvp, position[0], position[1], position[2], 1.0f, out_clip);
+    mat4_vec4(transform, normal[0], normal[1], normal[2], 0.0f, nrm);
+    out_normal[0] = nrm[0]; out_normal[1] = nrm[1]; out_normal[2] = nrm[2];
+}
+
+void orc_raster_fragment(const float *n, const float *mat, float *a, float *b, float *c) {
+    const float inv = 1.0f / sqrtf((n[0] * n[0] + n[1] * n[1]) + n[2] * n[2]);
+    a[0] = (n[0] * inv + 1.0f) / 2.0f; a[1] = (n[1] * inv + 1.0f) / 2.0f; a[2] = (n[2] * inv + 1.0f) / 2.0f; a[3] = 1.0f;
+    b[0] = mat[0]; b[1] = mat[1]; b[2] = mat[2]; b[3] = 1.0f;
+    if (mat[7] != 0.0f) {
+        c[0] = mat[3]; c[1] = mat[4]; c[2] = mat[5]; c[3] = mat[6];
+    } else {
+        c[0] = c[1] = c[2] = 0.0f; c[3] = 1.0f;
+    }
+}
+
 typedef struct {
     float a[3], b[3], c[3], z[3], w[3], n[9];
     int draw, x0, x1, y0, y1;
@@ -56,7 +77,7 @@ static void setup(const float *mvp, const float *model, const float *v0, const f
     const float half_w = 0.5f * (float)width, half_h = 0.5f * (float)height;
     for (int i = 0; i < 3; i++) {
         float clip[4], nrm[4];
-        mat4_vec4(mvp, vtx[i][0], vtx[i][1], vtx[i][2], 1.0f, clip);
+        mat4_vec4(mvp, vtx[i][0], vtx[i][1], vtx[i][2], 1.0f, clip);            /* = orc_raster_vertex with the product hoisted */
         mat4_vec4(model, vtx[i][3], vtx[i][4], vtx[i][5], 0.0f, nrm);
         X[i] = (clip[0] + clip[3]) * half_w;
         Y[i] = (clip[1] + clip[3]) * half_h;
@@ -134,18 +155,7 @@ void orc_raster(int64_t n_instances, const float *matrix, const int64_t *mesh, c
                     float n[3];
                     for (int c = 0; c < 3; c++)
                         n[c] = (b0 * t.n[c] + b1 * t.n[3 + c]) + b2 * t.n[6 + c];
-                    const float inv = 1.0f / sqrtf((n[0] * n[0] + n[1] * n[1]) + n[2] * n[2]);
-                    out_a[4 * p] = (n[0] * inv + 1.0f) / 2.0f;
-                    out_a[4 * p + 1] = (n[1] * inv + 1.0f) / 2.0f;
-                    out_a[4 * p + 2] = (n[2] * inv + 1.0f) / 2.0f;
-                    out_a[4 * p + 3] = 1.0f;
-                    out_b[4 * p] = mat[0]; out_b[4 * p + 1] = mat[1]; out_b[4 * p + 2] = mat[2]; out_b[4 * p + 3] = 1.0f;
-                    if (mat[7] != 0.0f) {
-                        out_c[4 * p] = mat[3]; out_c[4 * p + 1] = mat[4]; out_c[4 * p + 2] = mat[5]; out_c[4 * p + 3] = mat[6];
-                    } else {
-                        out_c[4 * p] = out_c[4 * p + 1] = out_c[4 * p + 2] = 0.0f;
-                        out_c[4 * p + 3] = 1.0f;
-                    }
+                    orc_raster_fragment(n, mat, out_a + 4 * p, out_b + 4 * p, out_c + 4 * p);
                 }
         }
     }

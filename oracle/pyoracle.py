@@ -262,6 +262,27 @@ class Oracle:
                             C.c_int32(height), _p(a), _p(b), _p(c), _p(depth))
         return a, b, c, depth
 
+    def raster_vertex(self, transform, view_projection, position, normal, glsl=False, shadow=False):
+        """lit_vtx.glsl / shadow_vtx.glsl for one vertex -> (clip[4], world normal[3]); glsl=True runs the reference's shader
+        source compiled against GLM (reference tier only)."""
+        t, vp = _f32(transform, (16,)), _f32(view_projection, (16,))
+        pos, nrm = _f32(position, (3,)), _f32(normal, (3,))
+        clip, out_n = np.zeros(4, dtype=np.float32), np.zeros(3, dtype=np.float32)
+        if glsl and shadow:
+            self.lib.orc_glsl_shadow_vertex(_p(t), _p(vp), _p(pos), _p(clip))
+        elif glsl:
+            self.lib.orc_glsl_lit_vertex(_p(t), _p(vp), _p(pos), _p(nrm), _p(clip), _p(out_n))
+        else:
+            self.lib.orc_raster_vertex(_p(t), _p(vp), _p(pos), _p(nrm), _p(clip), _p(out_n))
+        return clip, out_n
+
+    def raster_fragment(self, normal, material, glsl=False):
+        """lit_deferred_frag.glsl (no TEXTURED / NORMALMAP) for one fragment -> (bufferA, bufferB, bufferC)."""
+        n, m = _f32(normal, (3,)), _f32(material, (8,))
+        a, b, c = (np.zeros(4, dtype=np.float32) for _ in range(3))
+        (self.lib.orc_glsl_lit_fragment if glsl else self.lib.orc_raster_fragment)(_p(n), _p(m), _p(a), _p(b), _p(c))
+        return a, b, c
+
     # ---- deferred shading and post effects (section 8(f) row 4)
     def shade_deferred(self, buffer_a, buffer_b, buffer_c, depth, view_uniforms, light_uniforms, light_types,
                        shadow_maps=None, shadow_size=0, glsl=False):

@@ -231,3 +231,31 @@ def test_shader_restatement_equals_reference_glsl(port, ref):
     tm = ref.tonemap(hdr, 1.5, 11.2, glsl=True)
     assert same(port.tonemap(hdr, 1.5, 11.2), tm)
     assert same(port.gamma(tm, 2.2), ref.gamma(tm, 2.2, glsl=True))
+
+
+def test_raster_shader_stages_equal_reference_glsl(port, ref):
+    """The shader arithmetic inside the rasteriser's restatement (oracle/ovis_raster.c: vertex transform, world normal,
+    G-buffer encode) against the reference's own shader SOURCE - engine/shaders/lit_vtx.glsl, shadow_vtx.glsl and
+    lit_deferred_frag.glsl (the variants without TEXTURED / NORMALMAP, with and without SPECULAR) compiled as C++ against
+    GLM by oracle/glsl_harness.cc. Same float operations in the same order: compared for equality."""
+    rng = np.random.default_rng(54)
+    trs = util.random_trs(rng, 200, pos=50.0)
+    transforms = ref.entity_uniforms(trs)[:, :16]
+    for k in range(200):
+        view = scenes.make_view(rng.uniform(-30, 30, 3), scenes.random_unit_quats(rng, 1)[0], float(rng.uniform(30, 120)), 0.1,
+                                float(rng.uniform(50, 500)), 640, 360)
+        vp = ref.view_matrices(view)[0][2]
+        pos = rng.uniform(-3, 3, 3).astype(np.float32)
+        nrm = rng.standard_normal(3).astype(np.float32)
+        g_clip, g_n = ref.raster_vertex(transforms[k], vp, pos, nrm, glsl=True)
+        s_clip, _ = ref.raster_vertex(transforms[k], vp, pos, nrm, glsl=True, shadow=True)
+        for o in (port, ref):
+            clip, n = o.raster_vertex(transforms[k], vp, pos, nrm)
+            assert same(clip, g_clip) and same(n, g_n) and same(clip, s_clip)
+        for flags in (0.0, 1.0):
+            mat = np.concatenate([rng.uniform(0, 1, 6), [rng.uniform(1, 128), flags]]).astype(np.float32)
+            normal = g_n if k % 7 else np.zeros(3, np.float32)          # a degenerate normal: NaN in both
+            ga, gb, gc = ref.raster_fragment(normal, mat, glsl=True)
+            for o in (port, ref):
+                a, b, c = o.raster_fragment(normal, mat)
+                assert same(a, ga) and same(b, gb) and same(c, gc)
