@@ -78,13 +78,17 @@ struct RsMeshRef {
     int pad;
 };
 
-struct RsTriangle {                             // 128 bytes: what fill and resolve need of a set-up triangle
+struct RsTriangle {                             // 80 bytes: what fill and resolve need of a set-up triangle
     float a[3], b[3], c[3];                     // edge functions E_i(x, y) = a_i x + b_i y + c_i, oriented so that inside is >= 0
     float z[3], w[3];                           // clip-space z and w of the vertices
-    float n[9];                                 // world-space normals (vec3(transform * vec4(normal, 0)))
     unsigned int instance;                      // index into the call's instance list
     unsigned int view;
-    float pad[6];
+    unsigned short x0, y0, x1, y1;              // pixel bounding box, inclusive, clamped to the target
+    unsigned int pad;
+};
+struct RsNormals {                              // G-buffer passes only: world-space normals of the three vertices
+    float n[9];                                 // vec3(transform * vec4(normal, 0))
+    float pad[3];
 };
 
 struct RsItem {
@@ -106,6 +110,7 @@ struct RsArgs {
     const unsigned int *indices;
     long long *first_triangle;                  // [n_instances + 1]: scan of the instances' triangle counts
     RsTriangle *triangles;
+    RsNormals *normals;                         // nullptr for depth-only calls
     long long triangle_capacity;
     RsItem *items;
     unsigned int item_capacity;
@@ -225,6 +230,7 @@ raster_setup_kernel(const RsArgs a) {
             continue;
         }
         RsTriangle tri;
+        RsNormals nrms;
         float X[3], Y[3];
 #pragma unroll
         for (int i = 0; i < 3; i++) {
@@ -236,7 +242,7 @@ raster_setup_kernel(const RsArgs a) {
             Y[i] = mul(add(clip[1], clip[3]), half_h);
             tri.z[i] = clip[2];
             tri.w[i] = clip[3];
-            tri.n[3 * i] = nrm[0]; tri.n[3 * i + 1] = nrm[1]; tri.n[3 * i + 2] = nrm[2];
+            nrms.n[3 * i] = nrm[0]; nrms.n[3 * i + 1] = nrm[1]; nrms.n[3 * i + 2] = nrm[2];
         }
         // edge functions: rows of the adjugate of [X; Y; w] (2-D homogeneous rasterisation)
 #pragma unroll
@@ -268,12 +274,13 @@ raster_setup_kernel(const RsArgs a) {
                 y1 = min(y1, (int)ceilf(hy - 0.5f));
             }
         }
-        if (!draw || x1 < x0 || y1 < y0) {
-            tri.view = 0xffffffffu;                            // (never referenced by an item)
-            a.triangles[id] = tri;
-            continue;
-        }
+        if (!draw || x1 < x0 || y1 < y0)
+            continue;                                          // (its record is never referenced: not written)
+        tri.x0 = (unsigned short)x0; tri.y0 = (unsigned short)y0; tri.x1 = (unsigned short)x1; tri.y1 = (unsigned short)y1;
+        tri.pad = 0u;
         a.triangles[id] = tri;
+        if (a.normals)
+            a.normals[id] = nrms;
         const int tx0 = x0 / kTile, tx1 = x1 / kTile, ty0 = y0 / kTile, ty1 = y1 / kTile;
         const unsigned int n_items = (unsigned int)((tx1 - tx0 + 1) * (ty1 - ty0 + 1));
         const unsigned int at = atomicAdd(a.counters, n_items);
@@ -316,19 +323,16 @@ raster_fill_kernel(const RsArgs a) {
     const unsigned int warps = gridDim.x * (kRasterThreads / 32);
     for (unsigned int i = blockIdx.x * (kRasterThreads / 32) + (threadIdx.x >> 5); i < n_items; i += warps) {
         const RsItem it = a.items[i];
-        const RsTriangle &t = a.triangles[it.triangle];
-        RsTriangle tri;                                         // (the fields the sample needs)
-#pragma unroll
-        for (int k = 0; k < 3; k++) {
-            tri.a[k] = t.a[k]; tri.b[k] = t.b[k]; tri.c[k] = t.c[k]; tri.z[k] = t.z[k]; tri.w[k] = t.w[k];
-        }
-        const RsView &view = a.views[t.view];
-        const int px = it.tx * kTile + (lane & 15);
-#pragma unroll
-        for (int r = 0; r < 8; r++) {
-            const int py = it.ty * kTile + (lane >> 4) + 2 * r;
-            if (px >= view.width || py >= view.height)
-                continue;
+        const RsTriangle tri = a.triangles[it.triangle];
+        const RsView &view = a.views[tri.view];
+        // the part of the tile inside the triangle's bounding box, walked 32 pixels at a time (a tessellated mesh's triangles
+        // cover a handful of pixels: testing all 256 of the tile for each was 385 instructions per item)
+        const int rx0 = max((int)tri.x0, it.tx * kTile), rx1 = min((int)tri.x1, it.tx * kTile + kTile - 1);
+        const int ry0 = max((int)tri.y0, it.ty * kTile), ry1 = min((int)tri.y1, it.ty * kTile + kTile - 1);
+        const int rw = rx1 - rx0 + 1, count = rw * (ry1 - ry0 + 1);
+        for (int p = lane; p < count; p += 32) {
+            const int row = p / rw;
+            const int px = rx0 + (p - row * rw), py = ry0 + row;
             const RsSample s = sample_pixel(tri, px, py);
             if (!s.covered)
                 continue;
@@ -344,6 +348,7 @@ raster_fill_kernel(const RsArgs a) {
 struct RsResolveArgs {
     const unsigned long long *vis;
     const RsTriangle *triangles;
+    const RsNormals *normals;
     const unsigned int *instance_entity;
     const unsigned int *entity_material;
     const OvisMaterial *materials;
@@ -366,6 +371,7 @@ raster_resolve_kernel(const RsResolveArgs a) {
         return;
     }
     const RsTriangle t = a.triangles[~(unsigned int)key];
+    const RsNormals tn = a.normals[~(unsigned int)key];
     const int px = (int)(p % a.width), py = (int)(p / a.width);
     const RsSample s = sample_pixel(t, px, py);
     const float sum = add(add(s.e[0], s.e[1]), s.e[2]);
@@ -373,7 +379,7 @@ raster_resolve_kernel(const RsResolveArgs a) {
     float n[3];
 #pragma unroll
     for (int c = 0; c < 3; c++)
-        n[c] = add(add(mul(b0, t.n[c]), mul(b1, t.n[3 + c])), mul(b2, t.n[6 + c]));
+        n[c] = add(add(mul(b0, tn.n[c]), mul(b1, tn.n[3 + c])), mul(b2, tn.n[6 + c]));
     // normalize(normal): v * inversesqrt(dot(v, v)) (GLM func_geometric.inl:95-104, func_exponential.inl: 1 / sqrt)
     const float inv = __fdiv_rn(1.0f, __fsqrt_rn(add(add(mul(n[0], n[0]), mul(n[1], n[1])), mul(n[2], n[2]))));
     const OvisMaterial m = a.materials[a.entity_material[a.instance_entity[t.instance] - a.id_base]];
@@ -418,6 +424,8 @@ struct OvisRaster {
     int64_t cap_first = 0;
     RsTriangle *d_triangles = nullptr;
     int64_t cap_triangles = 0;
+    RsNormals *d_normals = nullptr;
+    int64_t cap_normals = 0;
     RsItem *d_items = nullptr;
     int64_t cap_items = 0;
     unsigned int *d_counters = nullptr;             // [0] items, [1] overflow, [2] instance count of the call
@@ -506,12 +514,16 @@ int draw(OvisRaster *r, std::vector<RsView> &h_views, int64_t n_instances, const
     if (total_triangles > 0xfffffffell)
         return fail(OVIS_ERR_CAPACITY, "ovis_raster: more than 2^32 triangles in one call");
     RS_TRY(ensure_device(r->d_triangles, r->cap_triangles, total_triangles, 0, s));
+    const bool shaded = h_views[0].vis != nullptr;
+    if (shaded)
+        RS_TRY(ensure_device(r->d_normals, r->cap_normals, total_triangles, 0, s));
     if (r->cap_items == 0)
         RS_TRY(ensure_device(r->d_items, r->cap_items, (int64_t)1 << 20, 0, s));
     int sms = 0;
     RS_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, r->device));
     for (int attempt = 0; attempt < 6; attempt++) {
         a.triangles = r->d_triangles;
+        a.normals = shaded ? r->d_normals : nullptr;
         a.triangle_capacity = r->cap_triangles;
         a.items = r->d_items;
         a.item_capacity = (unsigned int)std::min<int64_t>(r->cap_items, 0xffffffffll);
@@ -565,7 +577,7 @@ int ovis_raster_destroy(OvisRaster *r) {
     cudaSetDevice(r->device);
     cudaDeviceSynchronize();
     void *bufs[] = { r->d_vertices, r->d_indices, r->d_meshes, r->d_materials, r->d_entity_mesh, r->d_entity_material, r->d_views,
-                     r->d_uniforms, r->d_first_triangle, r->d_triangles, r->d_items, r->d_counters, r->d_vis };
+                     r->d_uniforms, r->d_first_triangle, r->d_triangles, r->d_normals, r->d_items, r->d_counters, r->d_vis };
     for (void *b : bufs)
         if (b)
             cudaFree(b);
@@ -700,6 +712,7 @@ int ovis_raster_gbuffer_device(OvisRaster *r, const OvisView *view, const uint32
     RsResolveArgs ra{};
     ra.vis = r->d_vis;
     ra.triangles = r->d_triangles;
+    ra.normals = r->d_normals;
     ra.instance_entity = d_visible;
     ra.entity_material = r->d_entity_material;
     ra.materials = r->d_materials;
