@@ -299,6 +299,7 @@ struct RsSample {
     bool covered;
 };
 
+template <bool EARLY_OUT>
 __device__ __forceinline__ RsSample sample_pixel(const RsTriangle &t, int px, int py) {
     RsSample s;
     const float fx = (float)px + 0.5f, fy = (float)py + 0.5f;
@@ -308,6 +309,11 @@ __device__ __forceinline__ RsSample sample_pixel(const RsTriangle &t, int px, in
         s.e[i] = add(add(mul(t.a[i], fx), mul(t.b[i], fy)), t.c[i]);
         // a centre exactly on an edge belongs to the triangle whose edge is a "top" or "left" one
         inside = inside && (s.e[i] > 0.0f || (s.e[i] == 0.0f && (t.a[i] > 0.0f || (t.a[i] == 0.0f && t.b[i] > 0.0f))));
+    }
+    if (EARLY_OUT && !inside) {                                 // (the fill kernel: most centres of a bounding box are outside)
+        s.depth = 2.0f;
+        s.covered = false;
+        return s;
     }
     const float zn = add(add(mul(s.e[0], t.z[0]), mul(s.e[1], t.z[1])), mul(s.e[2], t.z[2]));
     const float wn = add(add(mul(s.e[0], t.w[0]), mul(s.e[1], t.w[1])), mul(s.e[2], t.w[2]));
@@ -330,10 +336,11 @@ raster_fill_kernel(const RsArgs a) {
         const int rx0 = max((int)tri.x0, it.tx * kTile), rx1 = min((int)tri.x1, it.tx * kTile + kTile - 1);
         const int ry0 = max((int)tri.y0, it.ty * kTile), ry1 = min((int)tri.y1, it.ty * kTile + kTile - 1);
         const int rw = rx1 - rx0 + 1, count = rw * (ry1 - ry0 + 1);
+        const unsigned int inv_rw = 65536u / (unsigned int)rw + 1u;      // p / rw for p < 256, rw <= 16: (p * inv_rw) >> 16
         for (int p = lane; p < count; p += 32) {
-            const int row = p / rw;
+            const int row = (int)(((unsigned int)p * inv_rw) >> 16);
             const int px = rx0 + (p - row * rw), py = ry0 + row;
-            const RsSample s = sample_pixel(tri, px, py);
+            const RsSample s = sample_pixel<true>(tri, px, py);
             if (!s.covered)
                 continue;
             const long long at = (long long)py * view.width + px;
@@ -373,7 +380,7 @@ raster_resolve_kernel(const RsResolveArgs a) {
     const RsTriangle t = a.triangles[~(unsigned int)key];
     const RsNormals tn = a.normals[~(unsigned int)key];
     const int px = (int)(p % a.width), py = (int)(p / a.width);
-    const RsSample s = sample_pixel(t, px, py);
+    const RsSample s = sample_pixel<false>(t, px, py);
     const float sum = add(add(s.e[0], s.e[1]), s.e[2]);
     const float b0 = __fdiv_rn(s.e[0], sum), b1 = __fdiv_rn(s.e[1], sum), b2 = __fdiv_rn(s.e[2], sum);
     float n[3];
