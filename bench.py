@@ -497,8 +497,9 @@ def run_ours(args, rank: int, local_rank: int, world_size: int):
         world = None
         del sw
         torch.cuda.empty_cache()
-        from tools import bench_configs
-        for key, fn in (("config1", bench_configs.config1),
+        from tools import bench_configs, bench_raster
+        for key, fn in (("headless_rasteriser", lambda: bench_raster.run(2000, 8)),      # G-buffer + shadow-map passes (ovis_raster.cu)
+                        ("config1", bench_configs.config1),
                         ("config3", lambda: bench_configs.config3(False, full_parity=True)),
                         ("config4", lambda: bench_configs.config4(False, full_parity=True, brute=False)),
                         ("dense_visible", bench_configs.dense_visible)):

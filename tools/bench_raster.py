@@ -35,9 +35,7 @@ def cube_mesh(k):
     return np.array(pos, np.float32), np.array(nrm, np.float32), np.array(idx, np.uint32)
 
 
-def main():
-    n = int(sys.argv[1]) if len(sys.argv) > 1 else 2000
-    k = int(sys.argv[2]) if len(sys.argv) > 2 else 8
+def run(n=2000, k=8):
     width, height, shadow = 1920, 1080, 1024
     rng = np.random.default_rng(11)
     trs = np.zeros((n, 10), dtype=np.float32)
@@ -92,10 +90,10 @@ def main():
            "shadow_instances": int(off[-1]), "shadow_triangles": int(off[-1]) * tris, "shadow_maps_ms": s_ms,
            "shadow_mtriangles_per_s": int(off[-1]) * tris / (s_ms * 1e-3) / 1e6,
            "note": "wall clock per call, synchronous (each call sizes its scratch from device counts: three round trips)"}
-    print(json.dumps(out))
     r.close()
     w.close()
+    return out
 
 
 if __name__ == "__main__":
-    main()
+    print(json.dumps(run(int(sys.argv[1]) if len(sys.argv) > 1 else 2000, int(sys.argv[2]) if len(sys.argv) > 2 else 8)))
