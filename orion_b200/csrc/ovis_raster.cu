@@ -447,6 +447,14 @@ __global__ void fill_words_kernel(unsigned int *dst, long long n, unsigned int v
         dst[i] = value;
 }
 
+// later entries win when an entity is named twice in one call only by accident of scheduling: callers name each once
+__global__ void bind_scatter_kernel(const unsigned int *stage, long long n, unsigned int *entity_mesh, unsigned int *entity_material) {
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        entity_mesh[stage[i]] = stage[n + i];
+        entity_material[stage[i]] = stage[2 * n + i];
+    }
+}
+
 int fill_words(unsigned int *dst, int64_t n, unsigned int value, cudaStream_t s) {
     if (n <= 0)
         return OVIS_OK;
@@ -668,19 +676,25 @@ int ovis_raster_bind_entities(OvisRaster *r, int64_t n, const uint32_t *entity_i
         r->d_entity_material = mat;
         r->n_bound = n_entities;
     }
-    // few bindings per call in practice (a level's entities once): one small copy each; batches of equal meshes would
-    // deserve a scatter kernel
-    std::vector<uint32_t> h_mesh((size_t)r->n_bound), h_mat((size_t)r->n_bound);
-    RS_CUDA(cudaMemcpyAsync(h_mesh.data(), r->d_entity_mesh, sizeof(uint32_t) * h_mesh.size(), cudaMemcpyDeviceToHost, r->stream));
-    RS_CUDA(cudaMemcpyAsync(h_mat.data(), r->d_entity_material, sizeof(uint32_t) * h_mat.size(), cudaMemcpyDeviceToHost, r->stream));
-    RS_CUDA(cudaStreamSynchronize(r->stream));
+    if (n == 0)
+        return OVIS_OK;
+    // ids, meshes and materials go up in one staging block; a small kernel scatters them into the two tables
+    uint32_t *d_stage = nullptr;
+    RS_CUDA(cudaMalloc(&d_stage, sizeof(uint32_t) * 3 * (size_t)n));
+    std::vector<uint32_t> h_stage(3 * (size_t)n);
     for (int64_t i = 0; i < n; i++) {
-        h_mesh[entity_ids[i] - r->id_base] = mesh_ids[i];
-        h_mat[entity_ids[i] - r->id_base] = material_ids[i];
+        h_stage[(size_t)i] = entity_ids[i] - r->id_base;
+        h_stage[(size_t)(n + i)] = mesh_ids[i];
+        h_stage[(size_t)(2 * n + i)] = material_ids[i];
     }
-    RS_CUDA(cudaMemcpyAsync(r->d_entity_mesh, h_mesh.data(), sizeof(uint32_t) * h_mesh.size(), cudaMemcpyHostToDevice, r->stream));
-    RS_CUDA(cudaMemcpyAsync(r->d_entity_material, h_mat.data(), sizeof(uint32_t) * h_mat.size(), cudaMemcpyHostToDevice, r->stream));
-    RS_CUDA(cudaStreamSynchronize(r->stream));
+    cudaError_t err = cudaMemcpyAsync(d_stage, h_stage.data(), sizeof(uint32_t) * h_stage.size(), cudaMemcpyHostToDevice, r->stream);
+    if (err == cudaSuccess) {
+        bind_scatter_kernel<<<(unsigned)std::min<int64_t>((n + 255) / 256, 65535), 256, 0, r->stream>>>(d_stage, (long long)n, r->d_entity_mesh, r->d_entity_material);
+        err = cudaStreamSynchronize(r->stream);
+    }
+    cudaFree(d_stage);
+    if (err != cudaSuccess)
+        return fail(OVIS_ERR_CUDA, std::string("ovis_raster_bind_entities: ") + cudaGetErrorString(err));
     return OVIS_OK;
 }
 
@@ -693,8 +707,8 @@ int ovis_raster_gbuffer_device(OvisRaster *r, const OvisView *view, const uint32
         return fail(OVIS_ERR_INVALID, "ovis_raster_gbuffer_device: the colour buffers must be 16-byte aligned");
     if (view->vp_width != target->width || view->vp_height != target->height)
         return fail(OVIS_ERR_INVALID, "ovis_raster_gbuffer_device: the view's viewport is not the target's size");
-    if (target->width > 65535 * kTile || target->height > 65535 * kTile)
-        return fail(OVIS_ERR_INVALID, "ovis_raster_gbuffer_device: target too large");
+    if (target->width > 65535 || target->height > 65535)
+        return fail(OVIS_ERR_INVALID, "ovis_raster_gbuffer_device: target too large (65535 pixels a side at most)");
     RS_TRY(use(r));
     unsigned int count = 0;
     RS_CUDA(cudaMemcpyAsync(&count, d_visible_count, sizeof count, cudaMemcpyDeviceToHost, r->stream));
@@ -737,7 +751,7 @@ int ovis_raster_gbuffer_device(OvisRaster *r, const OvisView *view, const uint32
 
 int ovis_raster_shadow_maps_device(OvisRaster *r, int32_t n_views, const OvisView *views, const int64_t *host_offsets,
                                    const uint32_t *d_entities, int32_t shadow_size, float *const *d_maps) {
-    if (!r || n_views < 0 || (n_views > 0 && (!views || !host_offsets || !d_maps)) || shadow_size < 1 || shadow_size > 65535 * kTile)
+    if (!r || n_views < 0 || (n_views > 0 && (!views || !host_offsets || !d_maps)) || shadow_size < 1 || shadow_size > 65535)
         return fail(OVIS_ERR_INVALID, "ovis_raster_shadow_maps_device: bad arguments");
     if (n_views == 0)
         return OVIS_OK;

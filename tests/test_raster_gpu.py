@@ -217,6 +217,62 @@ def test_whole_frame_against_the_restatements(oracle):
     w.close()
 
 
+def test_raster_edge_cases(oracle):
+    """Coplanar duplicates (LessOrEqual: the later draw wins), a degenerate triangle, a NaN vertex, an entity without a
+    mesh, an empty visible list: the same picture as the restatement, and nothing faults."""
+    import torch
+    width, height = 96, 64
+    qp, qn, qi = quad_mesh()
+    bad_p = qp.copy()
+    bad_p[2, 1] = np.nan
+    deg_p = np.zeros_like(qp)                                   # all four vertices in one point
+    meshes = [(qp, qn, qi), (bad_p, qn, qi), (deg_p, qn, qi)]
+    trs = np.zeros((6, 10), dtype=np.float32)
+    trs[:, 3] = 1.0
+    trs[:, 7:10] = (6, 1, 6)
+    trs[:, 0:3] = [(0, -1, -8), (0, -1, -8), (3, -1, -8), (-3, -1, -8), (0, -1, -5), (0, 0.5, -7)]
+    mesh_of = np.array([0, 0, 1, 2, 0, 0], dtype=np.uint32)         # entity 5 stays unbound
+    mat_of = np.array([0, 1, 0, 0, 2, 0], dtype=np.uint32)
+    w = lib.World(0)
+    e0 = w.add_entities(np.tile(np.array([[-0.5, 0, -0.5, 0.5, 0, 0.5]], np.float32), (6, 1)))
+    ids = np.arange(e0, e0 + 6, dtype=np.uint32)
+    w.set_transforms(ids, trs)
+    r = lib.Raster(w)
+    mids = [r.add_mesh(p, n, i) for p, n, i in meshes]
+    mats = np.zeros(3, dtype=lib.MATERIAL_DTYPE)
+    mats[0] = ((1, 0, 0), (0, 0, 0), 0.0, 0)
+    mats[1] = ((0, 1, 0), (0.5, 0.5, 0.5), 8.0, lib.MATERIAL_SPECULAR)
+    mats[2] = ((0, 0, 1), (0, 0, 0), 0.0, 0)
+    for m in mats:
+        r.add_material(m["diffuse"], m["specular"], float(m["shininess"]), int(m["flags"]))
+    r.bind_entities(ids[:5], np.array(mids, np.uint32)[mesh_of[:5]], mat_of[:5])
+    view = scenes.make_view((0, 1.5, 0), scenes.quat_yaw_pitch(0.0, -15.0), 80.0, 0.1, 100.0, width, height)
+    d_list = torch.tensor([6, 0, 1, 2, 3, 4, 5], dtype=torch.int32, device="cuda")     # count, then every entity in order
+    a, b, c = (torch.full((height, width, 4), -1.0, dtype=torch.float32, device="cuda") for _ in range(3))
+    depth = torch.full((height, width), -1.0, dtype=torch.float32, device="cuda")
+    r.gbuffer(view, d_list.data_ptr() + 4, d_list.data_ptr(), width, height, a.data_ptr(), b.data_ptr(), c.data_ptr(), depth.data_ptr())
+    torch.cuda.synchronize()
+    vertices = np.concatenate([np.concatenate([p, n, np.zeros((4, 2), np.float32)], axis=1) for p, n, _ in meshes])
+    indices = np.concatenate([qi, qi, qi])
+    drawn = np.arange(5)
+    matrix = oracle.entity_uniforms(trs[drawn])[:, :16]
+    mesh_ref = np.array([[4 * m, 6 * m, 2] for m in mesh_of[drawn]], dtype=np.int64)
+    material = np.zeros((5, 8), dtype=np.float32)
+    mm = mats[mat_of[drawn]]
+    material[:, 0:3], material[:, 3:6], material[:, 6], material[:, 7] = mm["diffuse"], mm["specular"], mm["shininess"], mm["flags"]
+    ea, eb, ec, ed = oracle.raster(matrix, mesh_ref, material, vertices, indices, oracle.view_matrices(view)[0][2], width, height)
+    assert _same(depth.cpu().numpy(), ed) and _same(a.cpu().numpy(), ea) and _same(b.cpu().numpy(), eb) and _same(c.cpu().numpy(), ec)
+    got_b = b.cpu().numpy()
+    assert (got_b[..., 1] == 1.0).sum() > 200 and (got_b[..., 2] == 1.0).sum() > 50    # the duplicate drawn later (green) shows, and the nearer quad
+    # an empty list clears the target
+    d_list[0] = 0
+    r.gbuffer(view, d_list.data_ptr() + 4, d_list.data_ptr(), width, height, a.data_ptr(), b.data_ptr(), c.data_ptr(), depth.data_ptr())
+    torch.cuda.synchronize()
+    assert float(depth.min()) == 1.0 and float(a.abs().max()) == 0.0
+    r.close()
+    w.close()
+
+
 def test_raster_argument_checks():
     w = lib.World(0)
     w.add_entities(np.array([[-1, -1, -1, 1, 1, 1]], np.float32))
