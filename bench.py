@@ -407,6 +407,8 @@ def run_ours(args, rank: int, local_rank: int, world_size: int):
     e2e_ids = np.concatenate([np.asarray(p) for p in e2e_parts[0]]).copy() if world_size > 1 else pinned.array[:got].copy()
     if world_size > 1:
         barrier()
+        e2e_parts[0] = None                          # the last frame's lists are views into the shared block: let go of them,
+        e2e_frame = None                             # and of the frame function that holds the block's arrays, before unmapping
         seg.close()
     sampler.stop_flag.set()
 
@@ -531,6 +533,29 @@ def run_ours(args, rank: int, local_rank: int, world_size: int):
                     "what": "ovis_sharded_cull(view) from one host thread over all N GPUs -> merged ids in host memory",
                     "ms_per_step": dt / args.steps * 1e3, "tests_per_s": total_entities * args.steps / dt,
                     "list_exact": bool(np.array_equal(out1.array[:got1], exp)) if "parity" in line else None}
+                # configs[4]'s "then 5 views": the camera and four more frusta in one many-view pass per shard, lists spliced
+                # by the calling thread (ovis_sharded_cull_views)
+                try:
+                    five = [view] + [scenes.make_view((x, 40.0, z), scenes.quat_yaw_pitch(yaw, -5.0), 60.0, 0.5, 900.0, 1920, 1080)
+                                     for x, z, yaw in ((1500.0, -800.0, 40.0), (-2200.0, 600.0, 200.0), (300.0, 2500.0, -95.0), (-900.0, -3000.0, 130.0))]
+                    planes5 = np.stack([lib.view_planes(v) for v in five])
+                    off5, ent5 = spw.cull_views(planes5, capacity=max(total_visible * 8, 1 << 16))
+                    t0 = time.perf_counter()
+                    reps = max(args.steps // 10, 5)
+                    for _ in range(reps):
+                        off5, ent5 = spw.cull_views(planes5, capacity=len(ent5) + 1024)
+                    dt5 = time.perf_counter() - t0
+                    ok5 = None
+                    if "parity" in line:
+                        all_boxes = np.concatenate([aabb if r == 0 else shard_scene(r, n)[0] for r in range(world_size)])
+                        ok5 = all(np.array_equal(ent5[off5[v]:off5[v + 1]], oracle.cull_aabb(all_boxes, planes5[v], threads=cores))
+                                  for v in range(5))
+                    line["also"]["single_process_sharded_world"]["five_views"] = {
+                        "what": "ovis_sharded_cull_views: 5 frusta over all shards, merged CSR in host memory",
+                        "ms_per_step": dt5 / reps * 1e3, "entity_view_tests_per_s": 5 * total_entities * reps / dt5,
+                        "visible": [int(off5[v + 1] - off5[v]) for v in range(5)], "lists_exact": ok5}
+                except Exception as e:
+                    line["also"]["single_process_sharded_world"]["five_views"] = {"error": repr(e)}
                 spw.close()
             except Exception as e:
                 line.setdefault("also", {})["single_process_sharded_world"] = {"error": repr(e)}
