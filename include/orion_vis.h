@@ -512,6 +512,18 @@ int ovis_raster_bind_entities(OvisRaster *raster, int64_t n, const uint32_t *ent
  * Synchronises the world's stream (it sizes its scratch from the list). */
 int ovis_raster_gbuffer_device(OvisRaster *raster, const OvisView *view, const uint32_t *d_visible, const uint32_t *d_visible_count,
                                int64_t max_visible, const OvisGBufferTarget *target);
+/* The same pass fed by a draw list: d_draws holds (entity id, pass index) pairs as ovis_build_draw_lists_device writes them
+ * (the deferred list), one draw per pair, in list order. */
+int ovis_raster_gbuffer_draws_device(OvisRaster *raster, const OvisView *view, const uint32_t *d_draws, const uint32_t *d_draw_count,
+                                     int64_t max_draws, const OvisGBufferTarget *target);
+/* DeferredRenderPipeline::renderBasic (render/src/deferred_render_pipeline.cc:506-522): the entities of the basic draw list
+ * drawn with engine/shaders/unlit_vtx.glsl + unlit_frag.glsl (without TEXTURED: fragColour = vec4(diffuseColour, 1)) into
+ * the colour target the light pass wrote, depth-tested (LessOrEqual, with write) against the depth buffer the G-buffer pass
+ * left: d_rgba (4 floats per pixel) and d_depth are read and updated in place. Either an entity list or a draw list. */
+int ovis_raster_basic_device(OvisRaster *raster, const OvisView *view, const uint32_t *d_visible, const uint32_t *d_visible_count,
+                             int64_t max_visible, int32_t width, int32_t height, float *d_rgba, float *d_depth);
+int ovis_raster_basic_draws_device(OvisRaster *raster, const OvisView *view, const uint32_t *d_draws, const uint32_t *d_draw_count,
+                                   int64_t max_draws, int32_t width, int32_t height, float *d_rgba, float *d_depth);
 /* The shadow-map passes: view k draws the entities d_entities[host_offsets[k] .. host_offsets[k + 1]) (the CSR result of
  * ovis_cull_shadow_views_device, shadow casters only) depth-only into d_maps[k]: shadow_size x shadow_size floats, cleared
  * to 1. d_maps is a HOST array of n_views device pointers (a point light's six faces are six consecutive views: point

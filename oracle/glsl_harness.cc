@@ -142,6 +142,12 @@ namespace lit_vtx {
 namespace shadow_vtx {
 #include "_ref/glsl/shadow_vtx.glsl"
 }
+namespace unlit_vtx {
+#include "_ref/glsl/unlit_vtx.glsl"
+}
+namespace unlit_frag {
+#include "_ref/glsl/unlit_frag.glsl"
+}
 namespace lit_frag {
 #include "_ref/glsl/lit_deferred_frag.glsl"
 }
@@ -236,6 +242,21 @@ void orc_glsl_shadow_vertex(const float *transform, const float *view_projection
     shadow_vtx::attribPosition = vec3(position[0], position[1], position[2]);
     shadow_vtx::shader_main();
     out_clip[0] = gl_Position.x; out_clip[1] = gl_Position.y; out_clip[2] = gl_Position.z; out_clip[3] = gl_Position.w;
+}
+
+/* unlit_vtx.glsl + unlit_frag.glsl (the Basic pass) for one vertex / fragment */
+void orc_glsl_unlit(const float *transform, const float *view_projection, const float *position, const float *diffuse,
+                    float *out_clip, float *out_colour) {
+    using namespace glsl;
+    memcpy(&entity.transform, transform, 64);
+    memcpy(&view.viewProjection, view_projection, 64);
+    unlit_vtx::attribPosition = vec3(position[0], position[1], position[2]);
+    unlit_vtx::attribTexcoord = vec2(0.0f);
+    unlit_vtx::shader_main();
+    out_clip[0] = gl_Position.x; out_clip[1] = gl_Position.y; out_clip[2] = gl_Position.z; out_clip[3] = gl_Position.w;
+    diffuseColour = vec3(diffuse[0], diffuse[1], diffuse[2]);
+    unlit_frag::shader_main();
+    memcpy(out_colour, &unlit_frag::fragColour, 16);
 }
 
 /* lit_deferred_frag.glsl's main() for one fragment; material = diffuse rgb, specular rgb, shininess, SPECULAR keyword (0 / 1) */

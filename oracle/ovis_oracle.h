@@ -152,4 +152,7 @@ void orc_raster(int64_t n_instances, const float *matrix, const int64_t *mesh, c
                 const uint32_t *indices, const float *vp, int32_t width, int32_t height, float *out_a, float *out_b, float *out_c,
                 float *out_depth);
 
+void orc_raster_basic(int64_t n_instances, const float *matrix, const int64_t *mesh, const float *material, const float *vertices,
+                      const uint32_t *indices, const float *vp, int32_t width, int32_t height, float *rgba, float *depth_buffer);
+
 #endif

@@ -160,3 +160,37 @@ void orc_raster(int64_t n_instances, const float *matrix, const int64_t *mesh, c
         }
     }
 }
+
+/* DeferredRenderPipeline::renderBasic (render/src/deferred_render_pipeline.cc:506-522) with engine/shaders/unlit_vtx.glsl
+ * (the same gl_Position as lit_vtx.glsl) and unlit_frag.glsl without TEXTURED (fragColour = vec4(diffuseColour, 1.0)):
+ * the instances are drawn into rgba / depth as they stand (what the light pass and the G-buffer pass left), depth test
+ * LessOrEqual with write, no blending. */
+void orc_raster_basic(int64_t n_instances, const float *matrix, const int64_t *mesh, const float *material, const float *vertices,
+                      const uint32_t *indices, const float *vp, int32_t width, int32_t height, float *rgba, float *depth_buffer) {
+    for (int64_t k = 0; k < n_instances; k++) {
+        const float *M = matrix + 16 * k;
+        float mvp[16];
+        mat4_mul(vp, M, mvp);
+        const int64_t first_vertex = mesh[3 * k], first_index = mesh[3 * k + 1], n_tri = mesh[3 * k + 2];
+        const float *mat = material + 8 * k;
+        for (int64_t tix = 0; tix < n_tri; tix++) {
+            tri_t t;
+            const uint32_t *ix = indices + first_index + 3 * tix;
+            setup(mvp, M, vertices + 8 * (first_vertex + ix[0]), vertices + 8 * (first_vertex + ix[1]), vertices + 8 * (first_vertex + ix[2]),
+                  width, height, &t);
+            if (!t.draw)
+                continue;
+            for (int py = 0; py < height; py++)
+                for (int px = 0; px < width; px++) {
+                    float e[3], depth;
+                    if (!sample(&t, px, py, e, &depth))
+                        continue;
+                    const int64_t p = (int64_t)py * width + px;
+                    if (!(depth <= depth_buffer[p]))
+                        continue;
+                    depth_buffer[p] = depth;
+                    rgba[4 * p] = mat[0]; rgba[4 * p + 1] = mat[1]; rgba[4 * p + 2] = mat[2]; rgba[4 * p + 3] = 1.0f;
+                }
+        }
+    }
+}

@@ -262,6 +262,28 @@ class Oracle:
                             C.c_int32(height), _p(a), _p(b), _p(c), _p(depth))
         return a, b, c, depth
 
+    def raster_basic(self, matrix, mesh, material, vertices, indices, vp, rgba, depth):
+        """The Basic (unlit) pass over rgba [h, w, 4] and depth [h, w] as they stand; returns the updated copies."""
+        matrix = _f32(matrix, (-1, 16))
+        n = len(matrix)
+        mesh = np.ascontiguousarray(mesh, dtype=np.int64).reshape(n, 3)
+        material = _f32(material, (n, 8))
+        vertices = _f32(vertices, (-1, 8))
+        indices = np.ascontiguousarray(indices, dtype=np.uint32)
+        vp = _f32(vp, (16,))
+        h, w = depth.shape
+        rgba, depth = _f32(rgba, (h, w, 4)).copy(), _f32(depth, (h, w)).copy()
+        self.lib.orc_raster_basic(C.c_int64(n), _p(matrix), _p(mesh), _p(material), _p(vertices), _p(indices), _p(vp), C.c_int32(w),
+                                  C.c_int32(h), _p(rgba), _p(depth))
+        return rgba, depth
+
+    def glsl_unlit(self, transform, view_projection, position, diffuse):
+        """unlit_vtx.glsl + unlit_frag.glsl from the reference's source (reference tier only) -> (clip[4], colour[4])."""
+        clip, colour = np.zeros(4, dtype=np.float32), np.zeros(4, dtype=np.float32)
+        self.lib.orc_glsl_unlit(_p(_f32(transform, (16,))), _p(_f32(view_projection, (16,))), _p(_f32(position, (3,))),
+                                _p(_f32(diffuse, (3,))), _p(clip), _p(colour))
+        return clip, colour
+
     def raster_vertex(self, transform, view_projection, position, normal, glsl=False, shadow=False):
         """lit_vtx.glsl / shadow_vtx.glsl for one vertex -> (clip[4], world normal[3]); glsl=True runs the reference's shader
         source compiled against GLM (reference tier only)."""

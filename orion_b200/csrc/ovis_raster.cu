@@ -438,6 +438,8 @@ struct OvisRaster {
     unsigned int *d_counters = nullptr;             // [0] items, [1] overflow, [2] instance count of the call
     unsigned long long *d_vis = nullptr;
     int64_t cap_vis = 0;
+    uint32_t *d_dense_ids = nullptr;                // entity ids of a strided (draw-list) input, densified
+    int64_t cap_dense_ids = 0;
 };
 
 namespace {
@@ -453,6 +455,46 @@ __global__ void bind_scatter_kernel(const unsigned int *stage, long long n, unsi
         entity_mesh[stage[i]] = stage[n + i];
         entity_material[stage[i]] = stage[2 * n + i];
     }
+}
+
+// a draw list is (entity, pass index) pairs (ovis_build_draw_lists_device): every `stride`-th word is an entity id
+__global__ void gather_ids_kernel(const unsigned int *src, int stride, long long n, unsigned int *dst) {
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+        dst[i] = src[i * stride];
+}
+
+// Basic pass: the visibility buffer starts from the depth buffer the G-buffer pass left (no triangle: low word all ones)
+__global__ void vis_from_depth_kernel(const float *depth, long long n, unsigned long long *vis) {
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+        vis[i] = ((unsigned long long)__float_as_uint(depth[i]) << 32) | 0xffffffffull;
+}
+
+struct RsBasicArgs {
+    const unsigned long long *vis;
+    const RsTriangle *triangles;
+    const unsigned int *instance_entity;
+    const unsigned int *entity_material;
+    const OvisMaterial *materials;
+    unsigned int id_base;
+    long long pixels;
+    float4 *rgba;
+    float *depth;
+};
+
+// unlit_frag.glsl without TEXTURED: fragColour = vec4(diffuseColour, 1.0), blending off, for the pixels a triangle of this
+// pass won (depth test LessOrEqual against what the G-buffer pass left)
+__global__ void __launch_bounds__(kRasterThreads)
+raster_resolve_basic_kernel(const RsBasicArgs a) {
+    const long long p = (long long)blockIdx.x * kRasterThreads + threadIdx.x;
+    if (p >= a.pixels)
+        return;
+    const unsigned long long key = a.vis[p];
+    if ((unsigned int)key == 0xffffffffu)
+        return;
+    const RsTriangle &t = a.triangles[~(unsigned int)key];
+    const OvisMaterial m = a.materials[a.entity_material[a.instance_entity[t.instance] - a.id_base]];
+    a.rgba[p] = make_float4(m.diffuse[0], m.diffuse[1], m.diffuse[2], 1.0f);
+    a.depth[p] = __uint_as_float((unsigned int)(key >> 32));
 }
 
 int fill_words(unsigned int *dst, int64_t n, unsigned int value, cudaStream_t s) {
@@ -592,7 +634,7 @@ int ovis_raster_destroy(OvisRaster *r) {
     cudaSetDevice(r->device);
     cudaDeviceSynchronize();
     void *bufs[] = { r->d_vertices, r->d_indices, r->d_meshes, r->d_materials, r->d_entity_mesh, r->d_entity_material, r->d_views,
-                     r->d_uniforms, r->d_first_triangle, r->d_triangles, r->d_normals, r->d_items, r->d_counters, r->d_vis };
+                     r->d_uniforms, r->d_first_triangle, r->d_triangles, r->d_normals, r->d_items, r->d_counters, r->d_vis, r->d_dense_ids };
     for (void *b : bufs)
         if (b)
             cudaFree(b);
@@ -698,43 +740,74 @@ int ovis_raster_bind_entities(OvisRaster *r, int64_t n, const uint32_t *entity_i
     return OVIS_OK;
 }
 
-int ovis_raster_gbuffer_device(OvisRaster *r, const OvisView *view, const uint32_t *d_visible, const uint32_t *d_visible_count,
-                               int64_t max_visible, const OvisGBufferTarget *target) {
-    if (!r || !view || !d_visible || !d_visible_count || !target || target->width < 1 || target->height < 1 || !target->d_buffer_a ||
-        !target->d_buffer_b || !target->d_buffer_c || !target->d_depth)
-        return fail(OVIS_ERR_INVALID, "ovis_raster_gbuffer_device: null argument or empty target");
-    if ((((uintptr_t)target->d_buffer_a | (uintptr_t)target->d_buffer_b | (uintptr_t)target->d_buffer_c) & 15u) || ((uintptr_t)target->d_depth & 3u))
-        return fail(OVIS_ERR_INVALID, "ovis_raster_gbuffer_device: the colour buffers must be 16-byte aligned");
-    if (view->vp_width != target->width || view->vp_height != target->height)
-        return fail(OVIS_ERR_INVALID, "ovis_raster_gbuffer_device: the view's viewport is not the target's size");
-    if (target->width > 65535 || target->height > 65535)
-        return fail(OVIS_ERR_INVALID, "ovis_raster_gbuffer_device: target too large (65535 pixels a side at most)");
-    RS_TRY(use(r));
+}  // extern "C"
+
+namespace {
+
+// The instance list of a single-view pass: `count` ids read from every `stride`-th word of d_ids (1 = a visible list,
+// 2 = a draw list of (entity, pass) pairs); returns a dense device list.
+int instance_list(OvisRaster *r, const uint32_t *d_ids, int stride, const uint32_t *d_count, int64_t max_count, const uint32_t **out_dense, int64_t *out_n) {
     unsigned int count = 0;
-    RS_CUDA(cudaMemcpyAsync(&count, d_visible_count, sizeof count, cudaMemcpyDeviceToHost, r->stream));
+    RS_CUDA(cudaMemcpyAsync(&count, d_count, sizeof count, cudaMemcpyDeviceToHost, r->stream));
     RS_CUDA(cudaStreamSynchronize(r->stream));
     int64_t n = count;
-    if (max_visible >= 0)
-        n = std::min<int64_t>(n, max_visible);
+    if (max_count >= 0)
+        n = std::min<int64_t>(n, max_count);
+    *out_n = n;
+    *out_dense = d_ids;
+    if (stride != 1 && n > 0) {
+        RS_TRY(ensure_device(r->d_dense_ids, r->cap_dense_ids, n, 0, r->stream));
+        gather_ids_kernel<<<(unsigned)std::min<int64_t>((n + 255) / 256, 1184), 256, 0, r->stream>>>(d_ids, stride, (long long)n, r->d_dense_ids);
+        RS_CUDA(cudaGetLastError());
+        *out_dense = r->d_dense_ids;
+    }
+    return OVIS_OK;
+}
+
+int check_view_and_size(const char *who, const OvisView *view, int32_t width, int32_t height) {
+    if (width < 1 || height < 1 || width > 65535 || height > 65535)
+        return fail(OVIS_ERR_INVALID, std::string(who) + ": the target must be 1 .. 65535 pixels a side");
+    if (view->vp_width != width || view->vp_height != height)
+        return fail(OVIS_ERR_INVALID, std::string(who) + ": the view's viewport is not the target's size");
+    return OVIS_OK;
+}
+
+int one_view(const OvisView *view, int32_t width, int32_t height, int64_t n, unsigned long long *vis, std::vector<RsView> &views) {
+    float mats[64];
+    RS_TRY(ovis_view_matrices(view, mats, nullptr));
+    views.resize(1);
+    std::memcpy(views[0].vp, mats + 32, sizeof views[0].vp);    // viewProjection
+    views[0].width = width;
+    views[0].height = height;
+    views[0].first_instance = 0;
+    views[0].n_instances = n;
+    views[0].vis = vis;
+    views[0].depth_bits = nullptr;
+    return OVIS_OK;
+}
+
+int gbuffer_pass(OvisRaster *r, const OvisView *view, const uint32_t *d_ids, int stride, const uint32_t *d_count, int64_t max_count,
+                 const OvisGBufferTarget *target) {
+    if (!r || !view || !d_ids || !d_count || !target || !target->d_buffer_a || !target->d_buffer_b || !target->d_buffer_c || !target->d_depth)
+        return fail(OVIS_ERR_INVALID, "ovis_raster_gbuffer: null argument");
+    if ((((uintptr_t)target->d_buffer_a | (uintptr_t)target->d_buffer_b | (uintptr_t)target->d_buffer_c) & 15u) || ((uintptr_t)target->d_depth & 3u))
+        return fail(OVIS_ERR_INVALID, "ovis_raster_gbuffer: the colour buffers must be 16-byte aligned");
+    RS_TRY(check_view_and_size("ovis_raster_gbuffer", view, target->width, target->height));
+    RS_TRY(use(r));
+    const uint32_t *d_list = nullptr;
+    int64_t n = 0;
+    RS_TRY(instance_list(r, d_ids, stride, d_count, max_count, &d_list, &n));
     const int64_t pixels = (int64_t)target->width * target->height;
     RS_TRY(ensure_device(r->d_vis, r->cap_vis, pixels, 0, r->stream));
     RS_CUDA(cudaMemsetAsync(r->d_vis, 0xff, sizeof(unsigned long long) * (size_t)pixels, r->stream));
-    float mats[64];
-    RS_TRY(ovis_view_matrices(view, mats, nullptr));
-    std::vector<RsView> views(1);
-    std::memcpy(views[0].vp, mats + 32, sizeof views[0].vp);    // viewProjection
-    views[0].width = target->width;
-    views[0].height = target->height;
-    views[0].first_instance = 0;
-    views[0].n_instances = n;
-    views[0].vis = r->d_vis;
-    views[0].depth_bits = nullptr;
-    RS_TRY(draw(r, views, n, d_visible));
+    std::vector<RsView> views;
+    RS_TRY(one_view(view, target->width, target->height, n, r->d_vis, views));
+    RS_TRY(draw(r, views, n, d_list));
     RsResolveArgs ra{};
     ra.vis = r->d_vis;
     ra.triangles = r->d_triangles;
     ra.normals = r->d_normals;
-    ra.instance_entity = d_visible;
+    ra.instance_entity = d_list;
     ra.entity_material = r->d_entity_material;
     ra.materials = r->d_materials;
     ra.id_base = r->id_base;
@@ -747,6 +820,64 @@ int ovis_raster_gbuffer_device(OvisRaster *r, const OvisView *view, const uint32
     raster_resolve_kernel<<<(unsigned)((pixels + kRasterThreads - 1) / kRasterThreads), kRasterThreads, 0, r->stream>>>(ra);
     RS_CUDA(cudaGetLastError());
     return OVIS_OK;
+}
+
+int basic_pass(OvisRaster *r, const OvisView *view, const uint32_t *d_ids, int stride, const uint32_t *d_count, int64_t max_count,
+               int32_t width, int32_t height, float *d_rgba, float *d_depth) {
+    if (!r || !view || !d_ids || !d_count || !d_rgba || !d_depth)
+        return fail(OVIS_ERR_INVALID, "ovis_raster_basic: null argument");
+    if (((uintptr_t)d_rgba & 15u) || ((uintptr_t)d_depth & 3u))
+        return fail(OVIS_ERR_INVALID, "ovis_raster_basic: the colour buffer must be 16-byte aligned");
+    RS_TRY(check_view_and_size("ovis_raster_basic", view, width, height));
+    RS_TRY(use(r));
+    const uint32_t *d_list = nullptr;
+    int64_t n = 0;
+    RS_TRY(instance_list(r, d_ids, stride, d_count, max_count, &d_list, &n));
+    if (n == 0)
+        return OVIS_OK;
+    const int64_t pixels = (int64_t)width * height;
+    RS_TRY(ensure_device(r->d_vis, r->cap_vis, pixels, 0, r->stream));
+    vis_from_depth_kernel<<<(unsigned)std::min<int64_t>((pixels + 255) / 256, 4736), 256, 0, r->stream>>>(d_depth, (long long)pixels, r->d_vis);
+    std::vector<RsView> views;
+    RS_TRY(one_view(view, width, height, n, r->d_vis, views));
+    RS_TRY(draw(r, views, n, d_list));
+    RsBasicArgs ba{};
+    ba.vis = r->d_vis;
+    ba.triangles = r->d_triangles;
+    ba.instance_entity = d_list;
+    ba.entity_material = r->d_entity_material;
+    ba.materials = r->d_materials;
+    ba.id_base = r->id_base;
+    ba.pixels = pixels;
+    ba.rgba = reinterpret_cast<float4 *>(d_rgba);
+    ba.depth = d_depth;
+    raster_resolve_basic_kernel<<<(unsigned)((pixels + kRasterThreads - 1) / kRasterThreads), kRasterThreads, 0, r->stream>>>(ba);
+    RS_CUDA(cudaGetLastError());
+    return OVIS_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int ovis_raster_gbuffer_device(OvisRaster *r, const OvisView *view, const uint32_t *d_visible, const uint32_t *d_visible_count,
+                               int64_t max_visible, const OvisGBufferTarget *target) {
+    return gbuffer_pass(r, view, d_visible, 1, d_visible_count, max_visible, target);
+}
+
+int ovis_raster_gbuffer_draws_device(OvisRaster *r, const OvisView *view, const uint32_t *d_draws, const uint32_t *d_draw_count,
+                                     int64_t max_draws, const OvisGBufferTarget *target) {
+    return gbuffer_pass(r, view, d_draws, 2, d_draw_count, max_draws, target);
+}
+
+int ovis_raster_basic_device(OvisRaster *r, const OvisView *view, const uint32_t *d_visible, const uint32_t *d_visible_count,
+                             int64_t max_visible, int32_t width, int32_t height, float *d_rgba, float *d_depth) {
+    return basic_pass(r, view, d_visible, 1, d_visible_count, max_visible, width, height, d_rgba, d_depth);
+}
+
+int ovis_raster_basic_draws_device(OvisRaster *r, const OvisView *view, const uint32_t *d_draws, const uint32_t *d_draw_count,
+                                   int64_t max_draws, int32_t width, int32_t height, float *d_rgba, float *d_depth) {
+    return basic_pass(r, view, d_draws, 2, d_draw_count, max_draws, width, height, d_rgba, d_depth);
 }
 
 int ovis_raster_shadow_maps_device(OvisRaster *r, int32_t n_views, const OvisView *views, const int64_t *host_offsets,

@@ -900,6 +900,21 @@ class Raster:
         _check(self.lib.ovis_raster_gbuffer_device(self.h, _p(view), C.c_void_p(d_visible), C.c_void_p(d_count), C.c_int64(max_visible),
                                                    C.byref(t)))
 
+    def gbuffer_draws(self, view, d_draws: int, d_count: int, width: int, height: int, d_a: int, d_b: int, d_c: int, d_depth: int,
+                      max_draws=-1):
+        """The G-buffer pass fed by a draw list ((entity, pass) pairs of ovis_build_draw_lists_device)."""
+        view = np.ascontiguousarray(view, dtype=VIEW_DTYPE).reshape(1)
+        t = _GBufferTarget(width, height, d_a, d_b, d_c, d_depth)
+        _check(self.lib.ovis_raster_gbuffer_draws_device(self.h, _p(view), C.c_void_p(d_draws), C.c_void_p(d_count), C.c_int64(max_draws),
+                                                         C.byref(t)))
+
+    def basic(self, view, d_ids: int, d_count: int, width: int, height: int, d_rgba: int, d_depth: int, max_count=-1, draws=False):
+        """The Basic (unlit) pass into the colour target and depth buffer as they stand; draws=True: d_ids is a draw list."""
+        view = np.ascontiguousarray(view, dtype=VIEW_DTYPE).reshape(1)
+        fn = self.lib.ovis_raster_basic_draws_device if draws else self.lib.ovis_raster_basic_device
+        _check(fn(self.h, _p(view), C.c_void_p(d_ids), C.c_void_p(d_count), C.c_int64(max_count), C.c_int32(width), C.c_int32(height),
+                  C.c_void_p(d_rgba), C.c_void_p(d_depth)))
+
     def shadow_maps(self, views, host_offsets, d_entities: int, shadow_size: int, d_maps):
         views = np.ascontiguousarray(views, dtype=VIEW_DTYPE).reshape(-1)
         off = np.ascontiguousarray(host_offsets, dtype=np.int64)

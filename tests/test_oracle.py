@@ -259,3 +259,19 @@ def test_raster_shader_stages_equal_reference_glsl(port, ref):
             for o in (port, ref):
                 a, b, c = o.raster_fragment(normal, mat)
                 assert same(a, ga) and same(b, gb) and same(c, gc)
+
+
+def test_basic_pass_shaders_equal_reference_glsl(port, ref):
+    """unlit_vtx.glsl + unlit_frag.glsl (the Basic pass) from the reference's source: the clip position is the one the
+    restatement computes for every pass, the colour is vec4(diffuseColour, 1)."""
+    rng = np.random.default_rng(55)
+    transforms = ref.entity_uniforms(util.random_trs(rng, 50, pos=50.0))[:, :16]
+    for k in range(50):
+        view = scenes.make_view(rng.uniform(-30, 30, 3), scenes.random_unit_quats(rng, 1)[0], 70.0, 0.1, 300.0, 640, 360)
+        vp = ref.view_matrices(view)[0][2]
+        pos = rng.uniform(-3, 3, 3).astype(np.float32)
+        diffuse = rng.uniform(0, 1, 3).astype(np.float32)
+        clip, colour = ref.glsl_unlit(transforms[k], vp, pos, diffuse)
+        for o in (port, ref):
+            assert same(o.raster_vertex(transforms[k], vp, pos, np.zeros(3, np.float32))[0], clip)
+        assert same(colour, np.concatenate([diffuse, [np.float32(1.0)]]).astype(np.float32))

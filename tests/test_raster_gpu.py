@@ -217,6 +217,49 @@ def test_whole_frame_against_the_restatements(oracle):
     w.close()
 
 
+def test_draw_list_input_and_basic_pass(oracle):
+    """The deferred draw list ((entity, pass) pairs from ovis_build_draw_lists_device) feeds the G-buffer pass, the basic
+    draw list the unlit pass, which draws into the colour target and depth buffer the earlier passes left
+    (deferred_render_pipeline.cc:318-330, 506-522)."""
+    import torch
+    rng = np.random.default_rng(903)
+    sc = Scene(rng, 50, 6.0)
+    w, r = sc.build()
+    n = len(sc.trs)
+    basic = np.zeros(n, dtype=bool)
+    basic[1::4] = True                                      # a quarter of the entities use a Basic (unlit) material
+    ids = np.arange(n, dtype=np.uint32)
+    w.set_pass_counts(ids, (~basic).astype(np.uint32), basic.astype(np.uint32), np.ones(n, np.uint32))
+    width, height = 160, 100
+    view = scenes.make_view((0, 2, 22), (1, 0, 0, 0), 70.0, 0.1, 200.0, width, height)
+    d_vis = torch.zeros(n + 1, dtype=torch.int32, device="cuda")
+    w.cull_planes_device(lib.view_planes(view), d_vis.data_ptr() + 4, d_vis.data_ptr())
+    d0 = torch.zeros((n, 2), dtype=torch.int32, device="cuda")
+    d1 = torch.zeros((n, 2), dtype=torch.int32, device="cuda")
+    counts = torch.zeros(2, dtype=torch.int32, device="cuda")
+    w.build_draw_lists_device(0, d0.data_ptr(), n, d1.data_ptr(), n, d_vis.data_ptr() + 4, d_vis.data_ptr(), d_draw_counts=counts.data_ptr())
+    a, b, c = (torch.zeros((height, width, 4), dtype=torch.float32, device="cuda") for _ in range(3))
+    depth = torch.zeros((height, width), dtype=torch.float32, device="cuda")
+    r.gbuffer_draws(view, d0.data_ptr(), counts.data_ptr(), width, height, a.data_ptr(), b.data_ptr(), c.data_ptr(), depth.data_ptr())
+    colour = torch.full((height, width, 4), 0.25, dtype=torch.float32, device="cuda")       # "what the light pass wrote"
+    r.basic(view, d1.data_ptr(), counts.data_ptr() + 4, width, height, colour.data_ptr(), depth.data_ptr(), draws=True)
+    torch.cuda.synchronize()
+    vis = d_vis.cpu().numpy().view(np.uint32)
+    visible = vis[1:1 + vis[0]]
+    deferred, unlit = visible[~basic[visible]], visible[basic[visible]]
+    assert np.array_equal(d0.cpu().numpy().view(np.uint32)[:len(deferred), 0], deferred) and len(unlit) > 3
+    vp = oracle.view_matrices(view)[0][2]
+    ea, eb, ec, ed = oracle.raster(*sc.oracle_inputs(oracle, deferred), sc.vertices, sc.indices, vp, width, height)
+    assert _same(a.cpu().numpy(), ea) and _same(b.cpu().numpy(), eb) and _same(c.cpu().numpy(), ec)
+    e_rgba, e_depth = oracle.raster_basic(*sc.oracle_inputs(oracle, unlit), sc.vertices, sc.indices, vp,
+                                          np.full((height, width, 4), 0.25, np.float32), ed)
+    assert _same(colour.cpu().numpy(), e_rgba) and _same(depth.cpu().numpy(), e_depth)
+    touched = (e_rgba[..., 3] == 1.0)
+    assert 0.01 < touched.mean() < 0.9 and np.any(e_depth < ed)
+    r.close()
+    w.close()
+
+
 def test_raster_edge_cases(oracle):
     """Coplanar duplicates (LessOrEqual: the later draw wins), a degenerate triangle, a NaN vertex, an entity without a
     mesh, an empty visible list: the same picture as the restatement, and nothing faults."""
