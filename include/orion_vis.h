@@ -480,18 +480,22 @@ int ovis_post_effects_device(OvisWorld *world, int64_t n_pixels, const float *d_
  * shadow_vtx.glsl + shadow_frag.glsl, under the reference's default pipeline state (gpu/include/state.h:105-145: depth
  * test LessOrEqual with depth write, back faces culled, counter-clockwise = front; clear depth 1, colours 0). Pixel
  * centres at +0.5, row 0 = the bottom row (GL window coordinates, as ovis_shade_deferred_device reads them), top-left
- * rule, perspective-correct interpolation, near / far clip per pixel. Flat material parameters only: the shader variants
- * without TEXTURED and NORMALMAP. An OvisRaster belongs to one world and is driven from the same host thread; its work is
+ * rule, perspective-correct interpolation, near / far clip per pixel. Materials: flat parameters or base-level bilinear
+ * textures (TEXTURED, NORMALMAP). An OvisRaster belongs to one world and is driven from the same host thread; its work is
  * ordered on the world's stream.
  * ---------------------------------------------------------------------------------------------- */
 typedef struct OvisRaster OvisRaster;
-enum { OVIS_MATERIAL_SPECULAR = 1u };   /* the SPECULAR shader keyword (lit_deferred_frag.glsl:68-73) */
+enum { OVIS_MATERIAL_SPECULAR = 1u,     /* the shader keywords of lit_deferred_frag.glsl: SPECULAR (:68-73), */
+       OVIS_MATERIAL_TEXTURED = 2u,     /* TEXTURED (:46-50: diffuse from diffuse_texture instead of diffuseColour), */
+       OVIS_MATERIAL_NORMALMAP = 4u };  /* NORMALMAP (:52-63: normal from normal_texture in tangent space; the mesh needs tangents) */
 typedef struct OvisMaterial {
     float    diffuse[3];                /* diffuseColour */
     float    specular[3];               /* specularColour */
     float    shininess;
     uint32_t flags;
-} OvisMaterial;                         /* 32 bytes */
+    uint32_t diffuse_texture;           /* ids from ovis_raster_add_texture, read when the flag is set */
+    uint32_t normal_texture;
+} OvisMaterial;                         /* 40 bytes */
 typedef struct OvisGBufferTarget {      /* the writable form of OvisGBuffer: row-major, 16-byte aligned device pointers */
     int32_t width, height;
     float *d_buffer_a, *d_buffer_b, *d_buffer_c;   /* 4 floats per pixel each */
@@ -503,6 +507,16 @@ int ovis_raster_destroy(OvisRaster *raster);
  * normals 3 floats per vertex, texcoords 2 per vertex or NULL, indices 3 per triangle into this mesh's vertices. */
 int ovis_raster_add_mesh(OvisRaster *raster, int64_t n_vertices, const float *positions, const float *normals,
                          const float *texcoords, int64_t n_indices, const uint32_t *indices, uint32_t *out_mesh);
+/* Tangents of a mesh added before (4 floats per vertex: xyz + handedness, e.g. from ovis_mesh_tangents): the kTangentSemantic
+ * attribute lit_vtx.glsl reads under NORMALMAP. Meshes without them have zero tangents. */
+int ovis_raster_set_mesh_tangents(OvisRaster *raster, uint32_t mesh, int64_t n_vertices, const float *tangents);
+/* A 2-D texture from R, G, B, A bytes (rows bottom-up as GL stores them, e.g. ovis_tga_load's output). srgb != 0: the colour
+ * channels are sRGB-encoded and decoded to linear per texel before filtering (TGALoader's default, sRGB = true). wrap != 0:
+ * repeat addressing (kWrap), else clamp to edge. Sampling is bilinear on the base level with texel centres at
+ * (i + 0.5) / size - the reference asks the graphics API for mip-mapped 8x anisotropic filtering (engine/src/texture.cc:41-42),
+ * whose result the API leaves to the implementation; this is the part of it every implementation agrees on up close. */
+int ovis_raster_add_texture(OvisRaster *raster, int32_t width, int32_t height, const uint8_t *rgba, int32_t srgb, int32_t wrap,
+                            uint32_t *out_texture);
 int ovis_raster_add_material(OvisRaster *raster, const OvisMaterial *material, uint32_t *out_material);
 /* RenderEntity(subMesh, material) (graphics/src/mesh_renderer.cc:180-187): what entity ids[i] is drawn with. */
 int ovis_raster_bind_entities(OvisRaster *raster, int64_t n, const uint32_t *entity_ids, const uint32_t *mesh_ids,
@@ -585,6 +599,15 @@ int ovis_obj_submesh_aabbs(const char *obj_path, int32_t capacity, float *out_aa
 int ovis_obj_mesh(const char *obj_path, int64_t cap_vertices, float *out_positions, float *out_normals, float *out_texcoords,
                   int64_t cap_indices, uint32_t *out_indices, int32_t cap_submeshes, int64_t *out_first_index,
                   int64_t *out_n_vertices, int64_t *out_n_indices, int32_t *out_n_submeshes);
+/* MeshLoader::calculateTangents (engine/src/loaders/mesh_loader.cc:201-289; what an OBJLoader with generateTangents
+ * adds): 4 floats per vertex, xyz = normalize(t - n dot(n, t)) with t the sum of the triangles' s-directions, w = the
+ * handedness of the bitangent. Vertex data as ovis_obj_mesh returns it (the indices of all sub-meshes). */
+int ovis_mesh_tangents(int64_t n_vertices, const float *positions, const float *normals, const float *texcoords,
+                       int64_t n_indices, const uint32_t *indices, float *out_tangents);
+/* TGALoader::loadData (engine/src/loaders/tga_loader.cc:60-117): uncompressed 24 / 32-bit true-colour TGA -> R, G, B, A
+ * bytes, rows in file order, alpha 255 for 24-bit files. The size is always returned; OVIS_ERR_CAPACITY if the buffer
+ * (capacity_bytes) is smaller than 4 x width x height. */
+int ovis_tga_load(const char *path, int64_t capacity_bytes, uint8_t *out_rgba, int32_t *out_width, int32_t *out_height);
 /* Diagnostic: the canonical text of a JSON document as the scene loader's own reader sees it (strings byte for byte,
  * members in file order, numbers as the float the reference's JSONSerialiser reads - GetFloat() = (float)double,
  * engine/src/json_serialiser.cc:540 - plus the integer when there is one). The test suite compares it with the same dump

@@ -136,9 +136,65 @@ static thread_local vec3 diffuseColour, specularColour;
 static thread_local float shininess;
 inline void set_rgb(vec4 &dst, const vec3 &v) { dst.x = v.x; dst.y = v.y; dst.z = v.z; }
 
+/* material textures: sampled with the definition oracle/ovis_raster.c states (orc_texture_sample) */
+struct texture_ref { const void *t; };
+static thread_local texture_ref diffuseTexture, normalTexture;
+inline vec4 texture(const texture_ref &s, vec2 uv) {
+    float o[4];
+    orc_texture_sample(s.t, uv.x, uv.y, o);
+    return vec4(o[0], o[1], o[2], o[3]);
+}
+
 namespace lit_vtx {
 #include "_ref/glsl/lit_vtx.glsl"
 }
+namespace lit_vtx_normalmap {
+#define NORMALMAP
+#include "_ref/glsl/lit_vtx.glsl"
+#undef NORMALMAP
+}
+/* (the eight keyword combinations, each in its own namespace) */
+namespace lit_frag_t {
+#define TEXTURED
+#include "_ref/glsl/lit_deferred_frag.glsl"
+#undef TEXTURED
+}
+namespace lit_frag_n {
+#define NORMALMAP
+#include "_ref/glsl/lit_deferred_frag.glsl"
+#undef NORMALMAP
+}
+namespace lit_frag_tn {
+#define TEXTURED
+#define NORMALMAP
+#include "_ref/glsl/lit_deferred_frag.glsl"
+#undef TEXTURED
+#undef NORMALMAP
+}
+namespace lit_frag_st {
+#define SPECULAR
+#define TEXTURED
+#include "_ref/glsl/lit_deferred_frag.glsl"
+#undef TEXTURED
+#undef SPECULAR
+}
+namespace lit_frag_sn {
+#define SPECULAR
+#define NORMALMAP
+#include "_ref/glsl/lit_deferred_frag.glsl"
+#undef NORMALMAP
+#undef SPECULAR
+}
+namespace lit_frag_stn {
+#define SPECULAR
+#define TEXTURED
+#define NORMALMAP
+#include "_ref/glsl/lit_deferred_frag.glsl"
+#undef TEXTURED
+#undef NORMALMAP
+#undef SPECULAR
+}
+
 namespace shadow_vtx {
 #include "_ref/glsl/shadow_vtx.glsl"
 }
@@ -243,6 +299,64 @@ void orc_glsl_shadow_vertex(const float *transform, const float *view_projection
     shadow_vtx::shader_main();
     out_clip[0] = gl_Position.x; out_clip[1] = gl_Position.y; out_clip[2] = gl_Position.z; out_clip[3] = gl_Position.w;
 }
+
+/* lit_vtx.glsl with NORMALMAP for one vertex: world normal, tangent, bitangent */
+void orc_glsl_lit_vertex_normalmap(const float *transform, const float *view_projection, const float *position, const float *normal,
+                                   const float *tangent4, float *out_normal, float *out_tangent, float *out_bitangent) {
+    using namespace glsl;
+    memcpy(&entity.transform, transform, 64);
+    memcpy(&view.viewProjection, view_projection, 64);
+    lit_vtx_normalmap::attribPosition = vec3(position[0], position[1], position[2]);
+    lit_vtx_normalmap::attribNormal = vec3(normal[0], normal[1], normal[2]);
+    lit_vtx_normalmap::attribTexcoord = vec2(0.0f);
+    lit_vtx_normalmap::attribTangent = vec4(tangent4[0], tangent4[1], tangent4[2], tangent4[3]);
+    lit_vtx_normalmap::shader_main();
+    memcpy(out_normal, &lit_vtx_normalmap::vtxNormal, 12);
+    memcpy(out_tangent, &lit_vtx_normalmap::vtxTangent, 12);
+    memcpy(out_bitangent, &lit_vtx_normalmap::vtxBitangent, 12);
+}
+
+/* lit_deferred_frag.glsl for one fragment with any combination of SPECULAR (1) / TEXTURED (2) / NORMALMAP (4) in material[7];
+ * same arguments as orc_raster_fragment_textured */
+#define OVIS_RUN_FRAG(NS)                                                                                                  \
+    do {                                                                                                                   \
+        NS::vtxNormal = n; NS::vtxTexcoord = tc;                                                                           \
+        NS::shader_main();                                                                                                 \
+        a = NS::deferredBufferA; b = NS::deferredBufferB; c = NS::deferredBufferC;                                         \
+    } while (0)
+#define OVIS_RUN_FRAG_N(NS)                                                                                                \
+    do {                                                                                                                   \
+        NS::vtxTangent = tg; NS::vtxBitangent = bt;                                                                        \
+        OVIS_RUN_FRAG(NS);                                                                                                 \
+    } while (0)
+void orc_glsl_lit_fragment_textured(const float *normal, const float *uv, const float *tangent, const float *bitangent,
+                                    const float *material, const void *textures, float *out_a, float *out_b, float *out_c) {
+    using namespace glsl;
+    struct tex_record { const uint8_t *rgba; int32_t width, height, srgb, wrap; };
+    const tex_record *tex = (const tex_record *)textures;
+    diffuseColour = vec3(material[0], material[1], material[2]);
+    specularColour = vec3(material[3], material[4], material[5]);
+    shininess = material[6];
+    const int flags = (int)material[7];
+    if (flags & 2) diffuseTexture.t = tex + (int)material[8];
+    if (flags & 4) normalTexture.t = tex + (int)material[9];
+    const vec3 n(normal[0], normal[1], normal[2]), tg(tangent[0], tangent[1], tangent[2]), bt(bitangent[0], bitangent[1], bitangent[2]);
+    const vec2 tc(uv[0], uv[1]);
+    vec4 a, b, c;
+    switch (flags & 7) {
+    case 0: OVIS_RUN_FRAG(lit_frag); break;
+    case 1: OVIS_RUN_FRAG(lit_frag_specular); break;
+    case 2: OVIS_RUN_FRAG(lit_frag_t); break;
+    case 3: OVIS_RUN_FRAG(lit_frag_st); break;
+    case 4: OVIS_RUN_FRAG_N(lit_frag_n); break;
+    case 5: OVIS_RUN_FRAG_N(lit_frag_sn); break;
+    case 6: OVIS_RUN_FRAG_N(lit_frag_tn); break;
+    default: OVIS_RUN_FRAG_N(lit_frag_stn); break;
+    }
+    memcpy(out_a, &a, 16); memcpy(out_b, &b, 16); memcpy(out_c, &c, 16);
+}
+#undef OVIS_RUN_FRAG
+#undef OVIS_RUN_FRAG_N
 
 /* unlit_vtx.glsl + unlit_frag.glsl (the Basic pass) for one vertex / fragment */
 void orc_glsl_unlit(const float *transform, const float *view_projection, const float *position, const float *diffuse,

@@ -141,9 +141,6 @@ void orc_shade_deferred(int32_t width, int32_t height, const float *buffer_a, co
 void orc_tonemap(int64_t n_pixels, const float *rgba, float exposure, float white_point, float *out_rgba);
 void orc_gamma(int64_t n_pixels, const float *rgba, float gamma, float *out_rgba);
 
-#ifdef __cplusplus
-}
-#endif
 void orc_raster_vertex(const float *transform, const float *view_projection, const float *position, const float *normal,
                        float *out_clip, float *out_normal);
 void orc_raster_fragment(const float *normal, const float *material, float *out_a, float *out_b, float *out_c);
@@ -154,5 +151,18 @@ void orc_raster(int64_t n_instances, const float *matrix, const int64_t *mesh, c
 
 void orc_raster_basic(int64_t n_instances, const float *matrix, const int64_t *mesh, const float *material, const float *vertices,
                       const uint32_t *indices, const float *vp, int32_t width, int32_t height, float *rgba, float *depth_buffer);
+
+void orc_raster_bitangent(const float *world_normal, const float *world_tangent, float handedness, float *out);
+/* textures of the rasteriser's restatement: records of { const uint8_t *rgba; int32_t width, height, srgb, wrap; } */
+void orc_texture_sample(const void *texture, float u, float v, float out[4]);
+void orc_raster_fragment_textured(const float *normal, const float *uv, const float *tangent, const float *bitangent, const float *material,
+                                  const void *textures, float *out_a, float *out_b, float *out_c);
+void orc_raster_textured(int64_t n_instances, const float *matrix, const int64_t *mesh, const float *material, const float *vertices,
+                         const float *tangents, const uint32_t *indices, const void *textures, const float *vp, int32_t width,
+                         int32_t height, float *out_a, float *out_b, float *out_c, float *out_depth);
+
+#ifdef __cplusplus
+}
+#endif
 
 #endif

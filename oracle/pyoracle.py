@@ -262,6 +262,63 @@ class Oracle:
                             C.c_int32(height), _p(a), _p(b), _p(c), _p(depth))
         return a, b, c, depth
 
+    # ---- textured materials
+    class _Tex(C.Structure):
+        _fields_ = [("rgba", C.c_void_p), ("width", C.c_int32), ("height", C.c_int32), ("srgb", C.c_int32), ("wrap", C.c_int32)]
+
+    def _textures(self, textures):
+        """textures: list of (rgba uint8 [h, w, 4], srgb, wrap) -> (ctypes array, keep-alive list)."""
+        arr = (self._Tex * max(len(textures), 1))()
+        keep = []
+        for i, (rgba, srgb, wrap) in enumerate(textures):
+            rgba = np.ascontiguousarray(rgba, dtype=np.uint8)
+            keep.append(rgba)
+            arr[i] = self._Tex(rgba.ctypes.data, rgba.shape[1], rgba.shape[0], int(bool(srgb)), int(bool(wrap)))
+        return arr, keep
+
+    def texture_sample(self, texture, u, v):
+        arr, keep = self._textures([texture])
+        out = np.zeros(4, dtype=np.float32)
+        self.lib.orc_texture_sample(C.byref(arr[0]), C.c_float(u), C.c_float(v), _p(out))
+        return out
+
+    def raster_textured(self, matrix, mesh, material, vertices, tangents, indices, textures, vp, width, height):
+        """orc_raster_textured -> (a, b, c, depth); material [n, 10], tangents [vertices, 4]."""
+        matrix = _f32(matrix, (-1, 16))
+        n = len(matrix)
+        mesh = np.ascontiguousarray(mesh, dtype=np.int64).reshape(n, 3)
+        material = _f32(material, (n, 10))
+        vertices = _f32(vertices, (-1, 8))
+        tangents = _f32(tangents, (len(vertices), 4))
+        indices = np.ascontiguousarray(indices, dtype=np.uint32)
+        vp = _f32(vp, (16,))
+        arr, keep = self._textures(textures)
+        depth = np.zeros((height, width), dtype=np.float32)
+        a, b, c = (np.zeros((height, width, 4), dtype=np.float32) for _ in range(3))
+        self.lib.orc_raster_textured(C.c_int64(n), _p(matrix), _p(mesh), _p(material), _p(vertices), _p(tangents), _p(indices), arr, _p(vp),
+                                     C.c_int32(width), C.c_int32(height), _p(a), _p(b), _p(c), _p(depth))
+        return a, b, c, depth
+
+    def raster_fragment_textured(self, normal, uv, tangent, bitangent, material, textures, glsl=False):
+        arr, keep = self._textures(textures)
+        a, b, c = (np.zeros(4, dtype=np.float32) for _ in range(3))
+        fn = self.lib.orc_glsl_lit_fragment_textured if glsl else self.lib.orc_raster_fragment_textured
+        fn(_p(_f32(normal, (3,))), _p(_f32(uv, (2,))), _p(_f32(tangent, (3,))), _p(_f32(bitangent, (3,))), _p(_f32(material, (10,))), arr,
+           _p(a), _p(b), _p(c))
+        return a, b, c
+
+    def raster_bitangent(self, n, t, w):
+        out = np.zeros(3, dtype=np.float32)
+        self.lib.orc_raster_bitangent(_p(_f32(n, (3,))), _p(_f32(t, (3,))), C.c_float(w), _p(out))
+        return out
+
+    def glsl_vertex_normalmap(self, transform, view_projection, position, normal, tangent4):
+        """lit_vtx.glsl with NORMALMAP from the reference's source -> (world normal, tangent, bitangent)."""
+        n, t, b = (np.zeros(3, dtype=np.float32) for _ in range(3))
+        self.lib.orc_glsl_lit_vertex_normalmap(_p(_f32(transform, (16,))), _p(_f32(view_projection, (16,))), _p(_f32(position, (3,))),
+                                               _p(_f32(normal, (3,))), _p(_f32(tangent4, (4,))), _p(n), _p(t), _p(b))
+        return n, t, b
+
     def raster_basic(self, matrix, mesh, material, vertices, indices, vp, rgba, depth):
         """The Basic (unlit) pass over rgba [h, w, 4] and depth [h, w] as they stand; returns the updated copies."""
         matrix = _f32(matrix, (-1, 16))

@@ -31,6 +31,7 @@
 #include "orion_vis.h"
 
 #include <algorithm>
+#include <cmath>
 #include <cstdio>
 #include <cstring>
 #include <new>
@@ -91,6 +92,17 @@ struct RsNormals {                              // G-buffer passes only: world-s
     float pad[3];
 };
 
+struct RsTexAttribs {                           // G-buffer passes of worlds with textures: what TEXTURED / NORMALMAP interpolate
+    float uv[6];                                // vtxTexcoord of the three vertices
+    float t[9], b[9];                           // vtxTangent, vtxBitangent (lit_vtx.glsl:48-55)
+};
+struct RsTexture {
+    const float4 *texels;                       // decoded to linear float at upload
+    int width, height;
+    int wrap;                                   // repeat addressing, else clamp to edge
+    int pad;
+};
+
 struct RsItem {
     unsigned int triangle;                      // id = first_triangle[instance] + index
     unsigned short tx, ty;                      // tile coordinates
@@ -111,6 +123,8 @@ struct RsArgs {
     long long *first_triangle;                  // [n_instances + 1]: scan of the instances' triangle counts
     RsTriangle *triangles;
     RsNormals *normals;                         // nullptr for depth-only calls
+    RsTexAttribs *tex_attribs;                  // nullptr unless the raster holds textures (and this is a G-buffer pass)
+    const float *tangents;                      // 4 floats per vertex (zeros for meshes that were given none)
     long long triangle_capacity;
     RsItem *items;
     unsigned int item_capacity;
@@ -231,6 +245,7 @@ raster_setup_kernel(const RsArgs a) {
         }
         RsTriangle tri;
         RsNormals nrms;
+        RsTexAttribs ta;
         float X[3], Y[3];
 #pragma unroll
         for (int i = 0; i < 3; i++) {
@@ -243,6 +258,17 @@ raster_setup_kernel(const RsArgs a) {
             tri.z[i] = clip[2];
             tri.w[i] = clip[3];
             nrms.n[3 * i] = nrm[0]; nrms.n[3 * i + 1] = nrm[1]; nrms.n[3 * i + 2] = nrm[2];
+            if (a.tex_attribs) {
+                const float *tg = a.tangents + 4 * (mesh.first_vertex + a.indices[mesh.first_index + 3 * t + i]);
+                float tw[4];
+                mat4_vec4(s_model, tg[0], tg[1], tg[2], 0.0f, tw);        // vtxTangent = vec3(entity.transform * vec4(tangent, 0.0))
+                ta.uv[2 * i] = vtx[6]; ta.uv[2 * i + 1] = vtx[7];
+                ta.t[3 * i] = tw[0]; ta.t[3 * i + 1] = tw[1]; ta.t[3 * i + 2] = tw[2];
+                // vtxBitangent = cross(vtxNormal, vtxTangent) * attribTangent.w (GLM cross: x = a.y b.z - b.y a.z, ...)
+                ta.b[3 * i] = mul(sub(mul(nrm[1], tw[2]), mul(tw[1], nrm[2])), tg[3]);
+                ta.b[3 * i + 1] = mul(sub(mul(nrm[2], tw[0]), mul(tw[2], nrm[0])), tg[3]);
+                ta.b[3 * i + 2] = mul(sub(mul(nrm[0], tw[1]), mul(tw[0], nrm[1])), tg[3]);
+            }
         }
         // edge functions: rows of the adjugate of [X; Y; w] (2-D homogeneous rasterisation)
 #pragma unroll
@@ -281,6 +307,8 @@ raster_setup_kernel(const RsArgs a) {
         a.triangles[id] = tri;
         if (a.normals)
             a.normals[id] = nrms;
+        if (a.tex_attribs)
+            a.tex_attribs[id] = ta;
         const int tx0 = x0 / kTile, tx1 = x1 / kTile, ty0 = y0 / kTile, ty1 = y1 / kTile;
         const unsigned int n_items = (unsigned int)((tx1 - tx0 + 1) * (ty1 - ty0 + 1));
         const unsigned int at = atomicAdd(a.counters, n_items);
@@ -352,10 +380,45 @@ raster_fill_kernel(const RsArgs a) {
     }
 }
 
+// texture(sampler2D, uv) as this library defines it (orion_vis.h, ovis_raster_add_texture): bilinear on the base level
+__device__ __forceinline__ int tex_coord(int i, int size, int wrap) {
+    if (wrap) {
+        i %= size;
+        return i < 0 ? i + size : i;
+    }
+    return min(max(i, 0), size - 1);
+}
+
+__device__ float4 sample_texture(const RsTexture &t, float u, float v) {
+    float x = sub(mul(u, (float)t.width), 0.5f), y = sub(mul(v, (float)t.height), 0.5f);
+    if (!(fabsf(x) < 1.0e9f)) x = 0.0f;                        // NaN or absurd coordinates: texel 0
+    if (!(fabsf(y) < 1.0e9f)) y = 0.0f;
+    const float fx0 = floorf(x), fy0 = floorf(y);
+    const float fx = sub(x, fx0), fy = sub(y, fy0);
+    const int i0 = tex_coord((int)fx0, t.width, t.wrap), i1 = tex_coord((int)fx0 + 1, t.width, t.wrap);
+    const int j0 = tex_coord((int)fy0, t.height, t.wrap), j1 = tex_coord((int)fy0 + 1, t.height, t.wrap);
+    const float4 t00 = t.texels[(long long)j0 * t.width + i0], t10 = t.texels[(long long)j0 * t.width + i1];
+    const float4 t01 = t.texels[(long long)j1 * t.width + i0], t11 = t.texels[(long long)j1 * t.width + i1];
+    const float gx = sub(1.0f, fx), gy = sub(1.0f, fy);
+    float4 r;
+    r.x = add(mul(add(mul(t00.x, gx), mul(t10.x, fx)), gy), mul(add(mul(t01.x, gx), mul(t11.x, fx)), fy));
+    r.y = add(mul(add(mul(t00.y, gx), mul(t10.y, fx)), gy), mul(add(mul(t01.y, gx), mul(t11.y, fx)), fy));
+    r.z = add(mul(add(mul(t00.z, gx), mul(t10.z, fx)), gy), mul(add(mul(t01.z, gx), mul(t11.z, fx)), fy));
+    r.w = add(mul(add(mul(t00.w, gx), mul(t10.w, fx)), gy), mul(add(mul(t01.w, gx), mul(t11.w, fx)), fy));
+    return r;
+}
+
+__device__ __forceinline__ void normalize3(float v[3]) {          // v * inversesqrt(dot(v, v))
+    const float inv = __fdiv_rn(1.0f, __fsqrt_rn(add(add(mul(v[0], v[0]), mul(v[1], v[1])), mul(v[2], v[2]))));
+    v[0] = mul(v[0], inv); v[1] = mul(v[1], inv); v[2] = mul(v[2], inv);
+}
+
 struct RsResolveArgs {
     const unsigned long long *vis;
     const RsTriangle *triangles;
     const RsNormals *normals;
+    const RsTexAttribs *tex_attribs;
+    const RsTexture *textures;
     const unsigned int *instance_entity;
     const unsigned int *entity_material;
     const OvisMaterial *materials;
@@ -387,12 +450,39 @@ raster_resolve_kernel(const RsResolveArgs a) {
 #pragma unroll
     for (int c = 0; c < 3; c++)
         n[c] = add(add(mul(b0, tn.n[c]), mul(b1, tn.n[3 + c])), mul(b2, tn.n[6 + c]));
+    const OvisMaterial m = a.materials[a.entity_material[a.instance_entity[t.instance] - a.id_base]];
+    float diffuse[3] = { m.diffuse[0], m.diffuse[1], m.diffuse[2] };
+    if ((m.flags & (OVIS_MATERIAL_TEXTURED | OVIS_MATERIAL_NORMALMAP)) && a.tex_attribs) {
+        const RsTexAttribs ta = a.tex_attribs[~(unsigned int)key];
+        const float u = add(add(mul(b0, ta.uv[0]), mul(b1, ta.uv[2])), mul(b2, ta.uv[4]));
+        const float v = add(add(mul(b0, ta.uv[1]), mul(b1, ta.uv[3])), mul(b2, ta.uv[5]));
+        if (m.flags & OVIS_MATERIAL_TEXTURED) {                 // diffuse = texture(diffuseTexture, vtxTexcoord)
+            const float4 d = sample_texture(a.textures[m.diffuse_texture], u, v);
+            diffuse[0] = d.x; diffuse[1] = d.y; diffuse[2] = d.z;
+        }
+        if (m.flags & OVIS_MATERIAL_NORMALMAP) {                // lit_deferred_frag.glsl:52-63
+            const float4 sn4 = sample_texture(a.textures[m.normal_texture], u, v);
+            float sn[3] = { sub(mul(sn4.x, 2.0f), 1.0f), sub(mul(sn4.y, 2.0f), 1.0f), sub(mul(sn4.z, 2.0f), 1.0f) };
+            normalize3(sn);
+            float T[3], B[3], N[3] = { n[0], n[1], n[2] };
+#pragma unroll
+            for (int c = 0; c < 3; c++) {
+                T[c] = add(add(mul(b0, ta.t[c]), mul(b1, ta.t[3 + c])), mul(b2, ta.t[6 + c]));
+                B[c] = add(add(mul(b0, ta.b[c]), mul(b1, ta.b[3 + c])), mul(b2, ta.b[6 + c]));
+            }
+            normalize3(T);
+            normalize3(B);
+            normalize3(N);
+#pragma unroll
+            for (int c = 0; c < 3; c++)                          // mat3(T, B, N) * sampledNormal (GLM: m0 * x + m1 * y + m2 * z)
+                n[c] = add(add(mul(T[c], sn[0]), mul(B[c], sn[1])), mul(N[c], sn[2]));
+        }
+    }
     // normalize(normal): v * inversesqrt(dot(v, v)) (GLM func_geometric.inl:95-104, func_exponential.inl: 1 / sqrt)
     const float inv = __fdiv_rn(1.0f, __fsqrt_rn(add(add(mul(n[0], n[0]), mul(n[1], n[1])), mul(n[2], n[2]))));
-    const OvisMaterial m = a.materials[a.entity_material[a.instance_entity[t.instance] - a.id_base]];
     a.buffer_a[p] = make_float4(__fdiv_rn(add(mul(n[0], inv), 1.0f), 2.0f), __fdiv_rn(add(mul(n[1], inv), 1.0f), 2.0f),
                                 __fdiv_rn(add(mul(n[2], inv), 1.0f), 2.0f), 1.0f);
-    a.buffer_b[p] = make_float4(m.diffuse[0], m.diffuse[1], m.diffuse[2], 1.0f);
+    a.buffer_b[p] = make_float4(diffuse[0], diffuse[1], diffuse[2], 1.0f);
     a.buffer_c[p] = (m.flags & OVIS_MATERIAL_SPECULAR) ? make_float4(m.specular[0], m.specular[1], m.specular[2], m.shininess)
                                                        : make_float4(0.f, 0.f, 0.f, 1.0f);
     a.depth[p] = __uint_as_float((unsigned int)(key >> 32));
@@ -420,6 +510,13 @@ struct OvisRaster {
     int64_t cap_meshes = 0;
     OvisMaterial *d_materials = nullptr;
     int64_t cap_materials = 0;
+    float *d_tangents = nullptr;                    // 4 floats per vertex, parallel to d_vertices
+    int64_t cap_tangents = 0;
+    std::vector<RsTexture> textures;                // host mirror of the table (texel pointers are device pointers)
+    RsTexture *d_textures = nullptr;
+    int64_t cap_textures = 0;
+    RsTexAttribs *d_tex_attribs = nullptr;
+    int64_t cap_tex_attribs = 0;
     uint32_t *d_entity_mesh = nullptr, *d_entity_material = nullptr;
     int64_t n_bound = 0;                            // entity slots the two tables cover
     // scratch of a call
@@ -438,6 +535,7 @@ struct OvisRaster {
     unsigned int *d_counters = nullptr;             // [0] items, [1] overflow, [2] instance count of the call
     unsigned long long *d_vis = nullptr;
     int64_t cap_vis = 0;
+    bool want_normals = true;                       // false while the Basic pass draws (it shades with the material colour alone)
     uint32_t *d_dense_ids = nullptr;                // entity ids of a strided (draw-list) input, densified
     int64_t cap_dense_ids = 0;
 };
@@ -571,9 +669,12 @@ int draw(OvisRaster *r, std::vector<RsView> &h_views, int64_t n_instances, const
     if (total_triangles > 0xfffffffell)
         return fail(OVIS_ERR_CAPACITY, "ovis_raster: more than 2^32 triangles in one call");
     RS_TRY(ensure_device(r->d_triangles, r->cap_triangles, total_triangles, 0, s));
-    const bool shaded = h_views[0].vis != nullptr;
+    const bool shaded = h_views[0].vis != nullptr && r->want_normals;
+    const bool textured = shaded && !r->textures.empty();
     if (shaded)
         RS_TRY(ensure_device(r->d_normals, r->cap_normals, total_triangles, 0, s));
+    if (textured)
+        RS_TRY(ensure_device(r->d_tex_attribs, r->cap_tex_attribs, total_triangles, 0, s));
     if (r->cap_items == 0)
         RS_TRY(ensure_device(r->d_items, r->cap_items, (int64_t)1 << 20, 0, s));
     int sms = 0;
@@ -581,6 +682,8 @@ int draw(OvisRaster *r, std::vector<RsView> &h_views, int64_t n_instances, const
     for (int attempt = 0; attempt < 6; attempt++) {
         a.triangles = r->d_triangles;
         a.normals = shaded ? r->d_normals : nullptr;
+        a.tex_attribs = textured ? r->d_tex_attribs : nullptr;
+        a.tangents = r->d_tangents;
         a.triangle_capacity = r->cap_triangles;
         a.items = r->d_items;
         a.item_capacity = (unsigned int)std::min<int64_t>(r->cap_items, 0xffffffffll);
@@ -634,7 +737,9 @@ int ovis_raster_destroy(OvisRaster *r) {
     cudaSetDevice(r->device);
     cudaDeviceSynchronize();
     void *bufs[] = { r->d_vertices, r->d_indices, r->d_meshes, r->d_materials, r->d_entity_mesh, r->d_entity_material, r->d_views,
-                     r->d_uniforms, r->d_first_triangle, r->d_triangles, r->d_normals, r->d_items, r->d_counters, r->d_vis, r->d_dense_ids };
+                     r->d_uniforms, r->d_first_triangle, r->d_triangles, r->d_normals, r->d_items, r->d_counters, r->d_vis, r->d_dense_ids, r->d_tangents, r->d_textures, r->d_tex_attribs };
+    for (const RsTexture &t : r->textures)
+        cudaFree(const_cast<float4 *>(t.texels));
     for (void *b : bufs)
         if (b)
             cudaFree(b);
@@ -661,6 +766,8 @@ int ovis_raster_add_mesh(OvisRaster *r, int64_t n_vertices, const float *positio
     }
     RS_TRY(ensure_device(r->d_vertices, r->cap_vertices, 8 * (r->n_vertices + n_vertices), 8 * r->n_vertices, r->stream));
     RS_TRY(ensure_device(r->d_indices, r->cap_indices, std::max<int64_t>(r->n_indices + n_indices, 1), r->n_indices, r->stream));
+    RS_TRY(ensure_device(r->d_tangents, r->cap_tangents, 4 * (r->n_vertices + n_vertices), 4 * r->n_vertices, r->stream));
+    RS_CUDA(cudaMemsetAsync(r->d_tangents + 4 * r->n_vertices, 0, sizeof(float) * 4 * (size_t)n_vertices, r->stream));
     RS_TRY(ensure_device(r->d_meshes, r->cap_meshes, (int64_t)r->meshes.size() + 1, (int64_t)r->meshes.size(), r->stream));
     RsMeshRef ref{ r->n_vertices, r->n_indices, (int)(n_indices / 3), 0 };
     RS_CUDA(cudaMemcpyAsync(r->d_vertices + 8 * r->n_vertices, packed.data(), sizeof(float) * packed.size(), cudaMemcpyHostToDevice, r->stream));
@@ -676,9 +783,64 @@ int ovis_raster_add_mesh(OvisRaster *r, int64_t n_vertices, const float *positio
     return OVIS_OK;
 }
 
+int ovis_raster_set_mesh_tangents(OvisRaster *r, uint32_t mesh, int64_t n_vertices, const float *tangents) {
+    if (!r || mesh >= r->meshes.size() || !tangents)
+        return fail(OVIS_ERR_INVALID, "ovis_raster_set_mesh_tangents: unknown mesh or null tangents");
+    const int64_t first = r->meshes[mesh].first_vertex;
+    const int64_t count = (mesh + 1 < r->meshes.size() ? r->meshes[mesh + 1].first_vertex : r->n_vertices) - first;
+    if (n_vertices != count)
+        return fail(OVIS_ERR_INVALID, "ovis_raster_set_mesh_tangents: the mesh has " + std::to_string(count) + " vertices");
+    RS_TRY(use(r));
+    RS_CUDA(cudaMemcpyAsync(r->d_tangents + 4 * first, tangents, sizeof(float) * 4 * (size_t)n_vertices, cudaMemcpyHostToDevice, r->stream));
+    RS_CUDA(cudaStreamSynchronize(r->stream));
+    return OVIS_OK;
+}
+
+int ovis_raster_add_texture(OvisRaster *r, int32_t width, int32_t height, const uint8_t *rgba, int32_t srgb, int32_t wrap, uint32_t *out_texture) {
+    if (!r || width < 1 || height < 1 || width > 32768 || height > 32768 || !rgba)
+        return fail(OVIS_ERR_INVALID, "ovis_raster_add_texture: bad arguments (1 .. 32768 texels a side)");
+    RS_TRY(use(r));
+    // texels are decoded once, on the host: c / 255, and for the colour channels of an sRGB texture the transfer function of
+    // the GL / Vulkan specifications (c <= 0.04045 ? c / 12.92 : ((c + 0.055) / 1.055) ^ 2.4) - a 256-entry table
+    float linear[256], decoded[256];
+    for (int i = 0; i < 256; i++) {
+        linear[i] = (float)i / 255.0f;
+        decoded[i] = linear[i] <= 0.04045f ? linear[i] / 12.92f : powf((linear[i] + 0.055f) / 1.055f, 2.4f);
+    }
+    const size_t texels = (size_t)width * (size_t)height;
+    std::vector<float> host(4 * texels);
+    for (size_t i = 0; i < texels; i++) {
+        const float *table = srgb ? decoded : linear;
+        host[4 * i] = table[rgba[4 * i]];
+        host[4 * i + 1] = table[rgba[4 * i + 1]];
+        host[4 * i + 2] = table[rgba[4 * i + 2]];
+        host[4 * i + 3] = linear[rgba[4 * i + 3]];
+    }
+    float4 *d_texels = nullptr;
+    RS_CUDA(cudaMalloc(&d_texels, sizeof(float4) * texels));
+    cudaError_t err = cudaMemcpyAsync(d_texels, host.data(), sizeof(float4) * texels, cudaMemcpyHostToDevice, r->stream);
+    if (err == cudaSuccess)
+        err = cudaStreamSynchronize(r->stream);
+    if (err != cudaSuccess) {
+        cudaFree(d_texels);
+        return fail(OVIS_ERR_CUDA, std::string("ovis_raster_add_texture: ") + cudaGetErrorString(err));
+    }
+    RsTexture t{ d_texels, width, height, wrap ? 1 : 0, 0 };
+    RS_TRY(ensure_device(r->d_textures, r->cap_textures, (int64_t)r->textures.size() + 1, (int64_t)r->textures.size(), r->stream));
+    RS_CUDA(cudaMemcpyAsync(r->d_textures + r->textures.size(), &t, sizeof t, cudaMemcpyHostToDevice, r->stream));
+    RS_CUDA(cudaStreamSynchronize(r->stream));
+    if (out_texture)
+        *out_texture = (uint32_t)r->textures.size();
+    r->textures.push_back(t);
+    return OVIS_OK;
+}
+
 int ovis_raster_add_material(OvisRaster *r, const OvisMaterial *material, uint32_t *out_material) {
     if (!r || !material)
         return fail(OVIS_ERR_INVALID, "ovis_raster_add_material: null argument");
+    if (((material->flags & OVIS_MATERIAL_TEXTURED) && material->diffuse_texture >= r->textures.size()) ||
+        ((material->flags & OVIS_MATERIAL_NORMALMAP) && material->normal_texture >= r->textures.size()))
+        return fail(OVIS_ERR_INVALID, "ovis_raster_add_material: the material names a texture that was not added");
     RS_TRY(use(r));
     RS_TRY(ensure_device(r->d_materials, r->cap_materials, r->n_materials + 1, r->n_materials, r->stream));
     RS_CUDA(cudaMemcpyAsync(r->d_materials + r->n_materials, material, sizeof *material, cudaMemcpyHostToDevice, r->stream));
@@ -807,6 +969,8 @@ int gbuffer_pass(OvisRaster *r, const OvisView *view, const uint32_t *d_ids, int
     ra.vis = r->d_vis;
     ra.triangles = r->d_triangles;
     ra.normals = r->d_normals;
+    ra.tex_attribs = r->textures.empty() ? nullptr : r->d_tex_attribs;
+    ra.textures = r->d_textures;
     ra.instance_entity = d_list;
     ra.entity_material = r->d_entity_material;
     ra.materials = r->d_materials;
@@ -840,7 +1004,10 @@ int basic_pass(OvisRaster *r, const OvisView *view, const uint32_t *d_ids, int s
     vis_from_depth_kernel<<<(unsigned)std::min<int64_t>((pixels + 255) / 256, 4736), 256, 0, r->stream>>>(d_depth, (long long)pixels, r->d_vis);
     std::vector<RsView> views;
     RS_TRY(one_view(view, width, height, n, r->d_vis, views));
-    RS_TRY(draw(r, views, n, d_list));
+    r->want_normals = false;
+    const int rc_draw = draw(r, views, n, d_list);
+    r->want_normals = true;
+    RS_TRY(rc_draw);
     RsBasicArgs ba{};
     ba.vis = r->d_vis;
     ba.triangles = r->d_triangles;

@@ -374,6 +374,83 @@ extern "C" int ovis_obj_mesh(const char *obj_path, int64_t cap_vertices, float *
     return OVIS_OK;
 }
 
+// MeshLoader::calculateTangents (engine/src/loaders/mesh_loader.cc:201-289, Lengyel's method): per triangle the s and t
+// directions are added to its three vertices, then every vertex gets normalize(t - n * dot(n, t)) and the handedness
+// sign of dot(cross(n, t), bitangent) in w. Same float operations in the same order (GLM's dot / cross / normalize).
+extern "C" int ovis_mesh_tangents(int64_t n_vertices, const float *positions, const float *normals, const float *texcoords,
+                                  int64_t n_indices, const uint32_t *indices, float *out_tangents) {
+    if (n_vertices < 0 || n_indices < 0 || n_indices % 3 != 0 || (n_vertices > 0 && (!positions || !normals || !texcoords || !out_tangents)) ||
+        (n_indices > 0 && !indices))
+        return scene_error(OVIS_ERR_INVALID, "ovis_mesh_tangents: bad arguments");
+    for (int64_t i = 0; i < n_indices; i++)
+        if ((int64_t)indices[i] >= n_vertices)
+            return scene_error(OVIS_ERR_INVALID, "ovis_mesh_tangents: index %lld is out of range", (long long)i);
+    using ovis::hm::Vec3;
+    std::vector<Vec3> tangents((size_t)n_vertices, Vec3{ 0.0f, 0.0f, 0.0f }), bitangents((size_t)n_vertices, Vec3{ 0.0f, 0.0f, 0.0f });
+    auto P = [&](uint32_t i) { return Vec3{ positions[3 * i], positions[3 * i + 1], positions[3 * i + 2] }; };
+    for (int64_t i = 0; i < n_indices; i += 3) {
+        const uint32_t i0 = indices[i], i1 = indices[i + 1], i2 = indices[i + 2];
+        const Vec3 p0 = P(i0), p1 = P(i1), p2 = P(i2);
+        const float x1 = p1.x - p0.x, x2 = p2.x - p0.x, y1 = p1.y - p0.y, y2 = p2.y - p0.y, z1 = p1.z - p0.z, z2 = p2.z - p0.z;
+        const float s1 = texcoords[2 * i1] - texcoords[2 * i0], s2 = texcoords[2 * i2] - texcoords[2 * i0];
+        const float t1 = texcoords[2 * i1 + 1] - texcoords[2 * i0 + 1], t2 = texcoords[2 * i2 + 1] - texcoords[2 * i0 + 1];
+        const float r = 1.0f / (s1 * t2 - s2 * t1);
+        const Vec3 sdir{ (t2 * x1 - t1 * x2) * r, (t2 * y1 - t1 * y2) * r, (t2 * z1 - t1 * z2) * r };
+        const Vec3 tdir{ (s1 * x2 - s2 * x1) * r, (s1 * y2 - s2 * y1) * r, (s1 * z2 - s2 * z1) * r };
+        for (uint32_t v : { i0, i1, i2 }) {
+            tangents[v] = tangents[v] + sdir;
+            bitangents[v] = bitangents[v] + tdir;
+        }
+    }
+    for (int64_t i = 0; i < n_vertices; i++) {
+        const Vec3 n{ normals[3 * i], normals[3 * i + 1], normals[3 * i + 2] };
+        const Vec3 t = tangents[(size_t)i];
+        const Vec3 tangent = ovis::hm::normalize(t - n * ovis::hm::dot(n, t));
+        const float handedness = (ovis::hm::dot(ovis::hm::cross(n, t), bitangents[(size_t)i]) < 0.0f) ? -1.0f : 1.0f;
+        out_tangents[4 * i] = tangent.x; out_tangents[4 * i + 1] = tangent.y; out_tangents[4 * i + 2] = tangent.z;
+        out_tangents[4 * i + 3] = handedness;
+    }
+    return OVIS_OK;
+}
+
+// TGALoader::loadData (engine/src/loaders/tga_loader.cc:60-117): uncompressed true-colour images of 24 or 32 bits, pixel
+// data after the ID field and the colour map, rows in file order (the loader does not look at the origin bits); 24-bit
+// pixels get alpha 255. The file stores B, G, R(, A); the output here is R, G, B, A.
+extern "C" int ovis_tga_load(const char *path, int64_t capacity_bytes, uint8_t *out_rgba, int32_t *out_width, int32_t *out_height) {
+    if (!path || capacity_bytes < 0 || !out_width || !out_height)
+        return scene_error(OVIS_ERR_INVALID, "ovis_tga_load: bad arguments");
+    std::string data;
+    if (!read_file(path, data))
+        return scene_error(OVIS_ERR_INVALID, "ovis_tga_load: cannot read %s", path);
+    if (data.size() < 18)
+        return scene_error(OVIS_ERR_INVALID, "%s: not a TGA file", path);
+    const unsigned char *h = reinterpret_cast<const unsigned char *>(data.data());
+    const int id_length = h[0], image_type = h[2], map_length = h[5] | (h[6] << 8), map_depth = h[7];
+    const int width = h[12] | (h[13] << 8), height = h[14] | (h[15] << 8), depth = h[16];
+    if (image_type != 2)
+        return scene_error(OVIS_ERR_INVALID, "%s: unsupported image format (%d)", path, image_type);
+    if (depth != 24 && depth != 32)
+        return scene_error(OVIS_ERR_INVALID, "%s: unsupported depth (%d)", path, depth);
+    *out_width = width;
+    *out_height = height;
+    const size_t pixels = (size_t)width * (size_t)height, bpp = (size_t)depth / 8;
+    const size_t offset = 18 + (size_t)id_length + (size_t)map_length * (size_t)(map_depth / 8);
+    if (offset + pixels * bpp > data.size())
+        return scene_error(OVIS_ERR_INVALID, "%s: truncated", path);
+    if ((int64_t)(pixels * 4) > capacity_bytes)
+        return scene_error(OVIS_ERR_CAPACITY, "%s: %d x %d needs %zu bytes", path, width, height, pixels * 4);
+    if (pixels > 0 && !out_rgba)
+        return scene_error(OVIS_ERR_INVALID, "ovis_tga_load: null output");
+    const unsigned char *src = h + offset;
+    for (size_t i = 0; i < pixels; i++) {
+        out_rgba[4 * i] = src[bpp * i + 2];
+        out_rgba[4 * i + 1] = src[bpp * i + 1];
+        out_rgba[4 * i + 2] = src[bpp * i];
+        out_rgba[4 * i + 3] = bpp == 4 ? src[4 * i + 3] : 255;
+    }
+    return OVIS_OK;
+}
+
 // Canonical text of a parsed document (see ovis_json_canonical in orion_vis.h). Numbers are written as the reference
 // consumes them: GetFloat() = (float)double, plus the integer when the double is one.
 static void json_canonical(const Json &v, std::string &out) {

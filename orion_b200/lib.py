@@ -841,8 +841,9 @@ def _world_shadow_views_host():
 _world_shadow_views_host()
 
 
-MATERIAL_DTYPE = np.dtype([("diffuse", np.float32, 3), ("specular", np.float32, 3), ("shininess", np.float32), ("flags", np.uint32)])
-MATERIAL_SPECULAR = 1
+MATERIAL_DTYPE = np.dtype([("diffuse", np.float32, 3), ("specular", np.float32, 3), ("shininess", np.float32), ("flags", np.uint32),
+                           ("diffuse_texture", np.uint32), ("normal_texture", np.uint32)])
+MATERIAL_SPECULAR, MATERIAL_TEXTURED, MATERIAL_NORMALMAP = 1, 2, 4
 
 
 class _GBufferTarget(C.Structure):
@@ -879,9 +880,23 @@ class Raster:
                                              C.c_int64(len(indices)), _p(indices), C.byref(out)))
         return out.value
 
-    def add_material(self, diffuse, specular=(0.0, 0.0, 0.0), shininess=0.0, flags=0) -> int:
+    def set_mesh_tangents(self, mesh: int, tangents):
+        t = _f32(tangents, (-1, 4))
+        _check(self.lib.ovis_raster_set_mesh_tangents(self.h, C.c_uint32(mesh), C.c_int64(len(t)), _p(t)))
+
+    def add_texture(self, rgba, srgb=True, wrap=True) -> int:
+        """rgba: uint8 [height, width, 4], rows bottom-up (as tga_load returns them)."""
+        rgba = np.ascontiguousarray(rgba, dtype=np.uint8)
+        assert rgba.ndim == 3 and rgba.shape[2] == 4
+        out = C.c_uint32()
+        _check(self.lib.ovis_raster_add_texture(self.h, C.c_int32(rgba.shape[1]), C.c_int32(rgba.shape[0]), _p(rgba), C.c_int32(int(srgb)),
+                                                C.c_int32(int(wrap)), C.byref(out)))
+        return out.value
+
+    def add_material(self, diffuse, specular=(0.0, 0.0, 0.0), shininess=0.0, flags=0, diffuse_texture=0, normal_texture=0) -> int:
         m = np.zeros(1, dtype=MATERIAL_DTYPE)
         m["diffuse"], m["specular"], m["shininess"], m["flags"] = diffuse, specular, shininess, flags
+        m["diffuse_texture"], m["normal_texture"] = diffuse_texture, normal_texture
         out = C.c_uint32()
         _check(self.lib.ovis_raster_add_material(self.h, _p(m), C.byref(out)))
         return out.value
@@ -939,3 +954,23 @@ def obj_mesh(path: str):
     _check(L.ovis_obj_mesh(path.encode(), C.c_int64(nv.value), _p(pos), _p(nrm), _p(tc), C.c_int64(ni.value), _p(idx), C.c_int32(ns.value),
                            _p(first), C.byref(nv), C.byref(ni), C.byref(ns)))
     return pos, nrm, tc, idx, first
+
+
+def mesh_tangents(positions, normals, texcoords, indices) -> np.ndarray:
+    """ovis_mesh_tangents: [n, 4] tangents (xyz + handedness) as the reference's mesh loader generates them."""
+    pos, nrm, tc, idx = _f32(positions, (-1, 3)), _f32(normals, (-1, 3)), _f32(texcoords, (-1, 2)), _u32(indices)
+    out = np.zeros((len(pos), 4), dtype=np.float32)
+    _check(load().ovis_mesh_tangents(C.c_int64(len(pos)), _p(pos), _p(nrm), _p(tc), C.c_int64(len(idx)), _p(idx), _p(out)))
+    return out
+
+
+def tga_load(path: str) -> np.ndarray:
+    """ovis_tga_load: [height, width, 4] uint8 R, G, B, A, rows in file order."""
+    L = load()
+    w, h = C.c_int32(), C.c_int32()
+    rc = L.ovis_tga_load(os.fsencode(path), C.c_int64(0), None, C.byref(w), C.byref(h))
+    if rc not in (OVIS_OK, OVIS_ERR_CAPACITY):
+        _check(rc)
+    out = np.zeros((h.value, w.value, 4), dtype=np.uint8)
+    _check(L.ovis_tga_load(os.fsencode(path), C.c_int64(out.nbytes), _p(out), C.byref(w), C.byref(h)))
+    return out

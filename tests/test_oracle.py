@@ -275,3 +275,33 @@ def test_basic_pass_shaders_equal_reference_glsl(port, ref):
         for o in (port, ref):
             assert same(o.raster_vertex(transforms[k], vp, pos, np.zeros(3, np.float32))[0], clip)
         assert same(colour, np.concatenate([diffuse, [np.float32(1.0)]]).astype(np.float32))
+
+
+def test_textured_shader_variants_equal_reference_glsl(port, ref):
+    """lit_vtx.glsl with NORMALMAP and all eight keyword combinations of lit_deferred_frag.glsl (SPECULAR / TEXTURED /
+    NORMALMAP) from the reference's source against the rasteriser's restatement; the texture sampler is the library's
+    definition on both sides (orc_texture_sample)."""
+    rng = np.random.default_rng(56)
+    textures = [(rng.integers(0, 256, (8, 16, 4), dtype=np.uint8), True, True), (rng.integers(0, 256, (4, 4, 4), dtype=np.uint8), False, False)]
+    transforms = ref.entity_uniforms(util.random_trs(rng, 40, pos=20.0))[:, :16]
+    vp = ref.view_matrices(scenes.make_view((0, 0, 30), (1, 0, 0, 0), 70.0, 0.1, 300.0, 640, 360))[0][2]
+    for k in range(40):
+        pos, nrm = rng.uniform(-2, 2, 3).astype(np.float32), rng.standard_normal(3).astype(np.float32)
+        tan4 = np.concatenate([rng.standard_normal(3), [rng.choice([-1.0, 1.0])]]).astype(np.float32)
+        gn, gt, gb = ref.glsl_vertex_normalmap(transforms[k], vp, pos, nrm, tan4)
+        _, n = port.raster_vertex(transforms[k], vp, pos, nrm)
+        t = port.raster_vertex(transforms[k], vp, pos, tan4[:3])[1]              # vec3(transform * vec4(tangent, 0))
+        assert same(n, gn) and same(t, gt) and same(port.raster_bitangent(n, t, float(tan4[3])), gb)
+        uv = rng.uniform(-2, 3, 2).astype(np.float32)
+        for flags in range(8):
+            mat = np.concatenate([rng.uniform(0, 1, 6), [rng.uniform(1, 128), flags, 0, 1]]).astype(np.float32)
+            g = ref.raster_fragment_textured(gn, uv, gt, gb, mat, textures, glsl=True)
+            for o in (port, ref):
+                got = o.raster_fragment_textured(gn, uv, gt, gb, mat, textures)
+                assert all(same(x, y) for x, y in zip(got, g)), flags
+    # the sampler itself: texel centres reproduce the texel, wrap and clamp addressing
+    rgba, _, _ = textures[1]
+    lin = rgba.astype(np.float32) / np.float32(255.0)
+    assert same(port.texture_sample((rgba, False, False), 0.125, 0.125), lin[0, 0])
+    assert same(port.texture_sample((rgba, False, False), -3.0, 7.0), lin[3, 0])             # clamp
+    assert same(port.texture_sample((rgba, False, True), 1.125, -0.875), lin[0, 0])          # repeat

@@ -43,9 +43,9 @@ class Scene:
     def __init__(self, rng, n_cubes, spread, with_floor=True):
         self.meshes = [cube_mesh(), quad_mesh()]
         self.materials = np.zeros(3, dtype=lib.MATERIAL_DTYPE)
-        self.materials[0] = ((0.8, 0.2, 0.1), (0.5, 0.5, 0.5), 16.0, lib.MATERIAL_SPECULAR)
-        self.materials[1] = ((0.1, 0.6, 0.3), (0.0, 0.0, 0.0), 0.0, 0)
-        self.materials[2] = ((0.4, 0.4, 0.9), (0.25, 0.5, 1.0), 64.0, lib.MATERIAL_SPECULAR)
+        self.materials[0] = ((0.8, 0.2, 0.1), (0.5, 0.5, 0.5), 16.0, lib.MATERIAL_SPECULAR, 0, 0)
+        self.materials[1] = ((0.1, 0.6, 0.3), (0.0, 0.0, 0.0), 0.0, 0, 0, 0)
+        self.materials[2] = ((0.4, 0.4, 0.9), (0.25, 0.5, 1.0), 64.0, lib.MATERIAL_SPECULAR, 0, 0)
         n = n_cubes + (1 if with_floor else 0)
         trs = np.zeros((n, 10), dtype=np.float32)
         trs[:, 0:3] = rng.uniform(-spread, spread, (n, 3))
@@ -260,6 +260,75 @@ def test_draw_list_input_and_basic_pass(oracle):
     w.close()
 
 
+def test_textured_and_normal_mapped_materials(oracle):
+    """The TEXTURED / NORMALMAP variants of lit_deferred_frag.glsl: sRGB diffuse texture with repeat addressing, a linear
+    normal map, tangents as the reference's mesh loader generates them; all four keyword combinations in one picture."""
+    import torch
+    rng = np.random.default_rng(904)
+    width, height = 192, 120
+    qp, qn, qi = quad_mesh()
+    quv = np.array([[0, 0], [0, 4], [4, 4], [4, 0]], np.float32)               # repeats four times across the quad
+    cp, cn, ci = cube_mesh()
+    cuv = np.tile(np.array([[0, 0], [1, 0], [1, 1], [0, 1]], np.float32), (6, 1))
+    meshes = [(qp, qn, qi, quv), (cp, cn, ci, cuv)]
+    tangents = [lib.mesh_tangents(p, n, uv, i) for p, n, i, uv in meshes]
+    assert np.allclose(np.linalg.norm(tangents[1][:, :3], axis=1), 1.0, atol=1e-6) and set(np.unique(tangents[1][:, 3])) <= {-1.0, 1.0}
+    tex_diffuse = (rng.integers(0, 256, (16, 16, 4), dtype=np.uint8), True, True)
+    nm = rng.integers(96, 160, (8, 8, 4), dtype=np.uint8)
+    nm[..., 2] = 255
+    tex_normal = (nm, False, True)
+    w = lib.World(0)
+    n_ent = 13
+    trs = np.zeros((n_ent, 10), dtype=np.float32)
+    trs[:, 0:3] = rng.uniform(-5, 5, (n_ent, 3))
+    trs[:, 2] -= 14
+    trs[:, 3:7] = scenes.random_unit_quats(rng, n_ent)
+    trs[:, 7:10] = rng.uniform(1.5, 3.0, (n_ent, 3))
+    trs[0] = (0, -4, -14, 1, 0, 0, 0, 30, 1, 30)
+    mesh_of = np.array([0] + [1] * (n_ent - 1), dtype=np.uint32)
+    e0 = w.add_entities(np.tile(np.array([[-0.5, -0.5, -0.5, 0.5, 0.5, 0.5]], np.float32), (n_ent, 1)))
+    ids = np.arange(e0, e0 + n_ent, dtype=np.uint32)
+    w.set_transforms(ids, trs)
+    r = lib.Raster(w)
+    mids = [r.add_mesh(p, n, i, uv) for p, n, i, uv in meshes]
+    for m, t in zip(mids, tangents):
+        r.set_mesh_tangents(m, t)
+    t0, t1 = r.add_texture(*tex_diffuse), r.add_texture(*tex_normal)
+    with pytest.raises(lib.OvisError):
+        r.add_material((1, 1, 1), flags=lib.MATERIAL_TEXTURED, diffuse_texture=7)
+    mat_rows = []
+    for flags in (0, 1, 2, 3, 4, 5, 6, 7):
+        d, sp, sh = rng.uniform(0, 1, 3), rng.uniform(0, 1, 3), float(rng.uniform(4, 64))
+        r.add_material(d, sp, sh, flags, t0, t1)
+        mat_rows.append(list(d) + list(sp) + [sh, flags, t0, t1])
+    mat_of = np.array([7] + [k % 8 for k in range(n_ent - 1)], dtype=np.uint32)
+    r.bind_entities(ids, np.array(mids, np.uint32)[mesh_of], mat_of)
+    view = scenes.make_view((0, 1, 4), scenes.quat_yaw_pitch(0.0, -12.0), 75.0, 0.1, 100.0, width, height)
+    d_list = torch.tensor([n_ent] + list(range(n_ent)), dtype=torch.int32, device="cuda")
+    a, b, c = (torch.zeros((height, width, 4), dtype=torch.float32, device="cuda") for _ in range(3))
+    depth = torch.zeros((height, width), dtype=torch.float32, device="cuda")
+    r.gbuffer(view, d_list.data_ptr() + 4, d_list.data_ptr(), width, height, a.data_ptr(), b.data_ptr(), c.data_ptr(), depth.data_ptr())
+    torch.cuda.synchronize()
+    vertices = np.concatenate([np.concatenate([p, n, uv], axis=1) for p, n, i, uv in meshes])
+    all_tangents = np.concatenate(tangents)
+    indices = np.concatenate([qi, ci])
+    mesh_ref = np.array([[0, 0, 2] if m == 0 else [4, 6, 12] for m in mesh_of], dtype=np.int64)
+    material = np.array(mat_rows, dtype=np.float32)[mat_of]
+    matrix = oracle.entity_uniforms(trs)[:, :16]
+    ea, eb, ec, ed = oracle.raster_textured(matrix, mesh_ref, material, vertices, all_tangents, indices, [tex_diffuse, tex_normal],
+                                            oracle.view_matrices(view)[0][2], width, height)
+    assert (ed < 1.0).mean() > 0.4
+    assert _same(depth.cpu().numpy(), ed) and _same(b.cpu().numpy(), eb) and _same(c.cpu().numpy(), ec) and _same(a.cpu().numpy(), ea)
+    # the texture shows: many distinct diffuse values on the floor (material 7), and its normals leave the geometric one
+    floor = (eb[..., 3] == 1.0) & (np.abs(ed - ed) == 0) & (ec[..., 3] == np.float32(mat_rows[7][6]))
+    assert len(np.unique(eb[floor][:, 0])) > 50
+    geometric = oracle.raster(matrix, mesh_ref, material[:, :8] * np.array([1, 1, 1, 1, 1, 1, 1, 0], np.float32) + np.array([0] * 7 + [1], np.float32),
+                              vertices, indices, oracle.view_matrices(view)[0][2], width, height)[0]
+    assert np.abs(ea[floor] - geometric[floor]).max() > 0.02
+    r.close()
+    w.close()
+
+
 def test_raster_edge_cases(oracle):
     """Coplanar duplicates (LessOrEqual: the later draw wins), a degenerate triangle, a NaN vertex, an entity without a
     mesh, an empty visible list: the same picture as the restatement, and nothing faults."""
@@ -283,9 +352,9 @@ def test_raster_edge_cases(oracle):
     r = lib.Raster(w)
     mids = [r.add_mesh(p, n, i) for p, n, i in meshes]
     mats = np.zeros(3, dtype=lib.MATERIAL_DTYPE)
-    mats[0] = ((1, 0, 0), (0, 0, 0), 0.0, 0)
-    mats[1] = ((0, 1, 0), (0.5, 0.5, 0.5), 8.0, lib.MATERIAL_SPECULAR)
-    mats[2] = ((0, 0, 1), (0, 0, 0), 0.0, 0)
+    mats[0] = ((1, 0, 0), (0, 0, 0), 0.0, 0, 0, 0)
+    mats[1] = ((0, 1, 0), (0.5, 0.5, 0.5), 8.0, lib.MATERIAL_SPECULAR, 0, 0)
+    mats[2] = ((0, 0, 1), (0, 0, 0), 0.0, 0, 0, 0)
     for m in mats:
         r.add_material(m["diffuse"], m["specular"], float(m["shininess"]), int(m["flags"]))
     r.bind_entities(ids[:5], np.array(mids, np.uint32)[mesh_of[:5]], mat_of[:5])

@@ -34,7 +34,7 @@ def cube_mesh():
     return np.array(pos, np.float32), np.array(nrm, np.float32), np.array(idx, np.uint32)
 
 
-def builtin_scene(w, r, width, height):
+def builtin_scene(w, r, width, height, textured=False):
     rng = np.random.default_rng(7)
     n = 60
     trs = np.zeros((n + 1, 10), dtype=np.float32)
@@ -54,7 +54,25 @@ def builtin_scene(w, r, width, height):
             r.add_material((0.7, 0.7, 0.7), (0.2, 0.2, 0.2), 64.0, lib.MATERIAL_SPECULAR)]
     which = rng.integers(0, 2, n + 1).astype(np.uint32)
     which[n] = 2
-    r.bind_entities(ids, mesh, np.array(mats, np.uint32)[which])
+    meshes = np.full(n + 1, mesh, dtype=np.uint32)
+    if textured:
+        # the floor as a textured, normal-mapped slab: its own mesh with texture coordinates and generated tangents,
+        # a procedural tile texture (sRGB) and a normal map of shallow bumps
+        pos, nrm, idx = cube_mesh()
+        uv = np.tile(np.array([[0, 0], [24, 0], [24, 24], [0, 24]], np.float32), (6, 1))
+        floor_mesh = r.add_mesh(pos, nrm, idx, uv)
+        r.set_mesh_tangents(floor_mesh, lib.mesh_tangents(pos, nrm, uv, idx))
+        yy, xx = np.mgrid[0:64, 0:64]
+        tile = np.where(((xx // 32) + (yy // 32)) % 2 == 0, 200, 120).astype(np.uint8)
+        grout = (xx % 32 < 2) | (yy % 32 < 2)
+        rgba = np.stack([np.where(grout, 60, tile), np.where(grout, 60, tile), np.where(grout, 64, (tile * 0.95).astype(np.uint8)), np.full_like(tile, 255)], axis=2)
+        bump = np.stack([128 + 40 * np.sin(xx / 64 * 2 * np.pi * 2), 128 + 40 * np.sin(yy / 64 * 2 * np.pi * 2), np.full((64, 64), 235.0),
+                         np.full((64, 64), 255.0)], axis=2).astype(np.uint8)
+        t_d, t_n = r.add_texture(rgba, srgb=True, wrap=True), r.add_texture(bump, srgb=False, wrap=True)
+        mats.append(r.add_material((1, 1, 1), (0.3, 0.3, 0.3), 64.0, lib.MATERIAL_SPECULAR | lib.MATERIAL_TEXTURED | lib.MATERIAL_NORMALMAP, t_d, t_n))
+        which[n] = 3
+        meshes[n] = floor_mesh
+    r.bind_entities(ids, meshes, np.array(mats, np.uint32)[which])
     lights = np.zeros(4, dtype=scenes.LIGHT_DTYPE)
     lights[0] = scenes.make_light(scenes.LIGHT_AMBIENT, colour=(1, 1, 1), intensity=0.08)
     lights[1] = scenes.make_light(scenes.LIGHT_SPOT, position=(0, 14, -2), direction=(0, -1, -0.6), colour=(1, 0.95, 0.8), intensity=2.5,
@@ -63,7 +81,7 @@ def builtin_scene(w, r, width, height):
     lights[3] = scenes.make_light(scenes.LIGHT_POINT, position=(8, 2.5, -16), colour=(1.0, 0.5, 0.3), intensity=2.0, range=25.0, flags=1)
     w.add_lights(lights)
     view = scenes.make_view((0, 4, 4), scenes.quat_yaw_pitch(0.0, -12.0), 80.0, 0.1, 200.0, width, height)
-    builtin_scene.description = dict(trs=trs, mesh=cube_mesh(), material_of=which,
+    builtin_scene.description = dict(trs=trs, mesh=cube_mesh(), material_of=which.copy(),
                                      materials=[((0.85, 0.25, 0.2), (0.5, 0.5, 0.5), 16.0, 1), ((0.2, 0.6, 0.85), (0.5, 0.5, 0.5), 32.0, 1),
                                                 ((0.7, 0.7, 0.7), (0.2, 0.2, 0.2), 64.0, 1)])
     return view, 512
@@ -72,21 +90,54 @@ def builtin_scene(w, r, width, height):
 def imported_scene(w, r, world_path, asset_dir, width, height):
     info, cams = w.import_scene(world_path, asset_dir, width, height)
     parsed = lib.load_scene(world_path, asset_dir, width, height)
-    cache, palette = {}, {}
+    import json
+    cache, palette, textures = {}, {}, {}
     colours = [((0.75, 0.75, 0.78), 64.0), ((0.9, 0.85, 0.8), 16.0), ((0.3, 0.7, 0.4), 32.0)]
+
+    def texture(asset):
+        """game/textures/<name> -> a texture id, if <name>.tga is there (the demo's cube texture is not in the repository)."""
+        if asset not in textures:
+            base = os.path.join(asset_dir, asset[len("game/"):])
+            textures[asset] = None
+            if os.path.exists(base + ".tga"):
+                srgb, wrap = True, False                              # TextureLoader defaults (sRGB on, clamp)
+                if os.path.exists(base + ".loader"):
+                    props = json.load(open(base + ".loader"))[0].get("objectProperties", {})
+                    srgb, wrap = props.get("sRGB", True), props.get("addressMode", "kClamp") == "kWrap"
+                textures[asset] = r.add_texture(lib.tga_load(base + ".tga"), srgb, wrap)
+        return textures[asset]
+
+    def material_for(path, fallback):
+        """materials/<mesh name>.object beside the mesh (the demo names them alike): shader keywords and parameters."""
+        name = os.path.splitext(os.path.basename(path))[0]
+        mpath = os.path.join(asset_dir, "materials", name + ".object")
+        c, sh = fallback
+        if not os.path.exists(mpath):
+            return r.add_material(c, (0.5, 0.5, 0.5), sh, lib.MATERIAL_SPECULAR), False
+        m = json.load(open(mpath))[0]
+        shader, params = m["shader"]["asset"], m.get("parameters", {})
+        flags = lib.MATERIAL_SPECULAR if "specular" in shader else 0
+        d_tex = texture(params["diffuseTexture"]["asset"]) if "diffuseTexture" in params else None
+        n_tex = texture(params["normalTexture"]["asset"]) if "normal" in shader and "normalTexture" in params else None
+        flags |= (lib.MATERIAL_TEXTURED if d_tex is not None else 0) | (lib.MATERIAL_NORMALMAP if n_tex is not None else 0)
+        return r.add_material(params.get("diffuseColour", c), params.get("specularColour", (0.5, 0.5, 0.5)), params.get("shininess", sh), flags,
+                              d_tex or 0, n_tex or 0), n_tex is not None
+
     for e, (path, sub) in enumerate(parsed["entity_mesh"]):
         if not path:
             continue                                                     # the skybox has no mesh to rasterise
         if (path, sub) not in cache:
             pos, nrm, tc, idx, first = lib.obj_mesh(path)
+            palette[(path, sub)], wants_tangents = material_for(path, colours[len(palette) % len(colours)])
             cache[(path, sub)] = r.add_mesh(pos, nrm, idx[first[sub]:first[sub + 1]], tc)
-            c, sh = colours[len(palette) % len(colours)]
-            palette[(path, sub)] = r.add_material(c, (0.5, 0.5, 0.5), sh, lib.MATERIAL_SPECULAR)
+            if wants_tangents:                                           # OBJLoader generateTangents (models/<name>.loader)
+                r.set_mesh_tangents(cache[(path, sub)], lib.mesh_tangents(pos, nrm, tc, idx))
         r.bind_entities([info.first_entity + e], [cache[(path, sub)]], [palette[(path, sub)]])
     return cams[0], (info.shadow_map_resolution or 512)
 
 
-def render(world_path=None, asset_dir=None, out_path=None, width=960, height=540, timing=False, keep_state=None, shadow_size=None):
+def render(world_path=None, asset_dir=None, out_path=None, width=960, height=540, timing=False, keep_state=None, shadow_size=None,
+           textured=False):
     """keep_state: a dict that receives the frame's intermediate results (for tests): the G-buffer tensors, the HDR target,
     the shadow maps by light, the visible lists."""
     dev = "cuda"
@@ -96,7 +147,7 @@ def render(world_path=None, asset_dir=None, out_path=None, width=960, height=540
         view, default_shadow = imported_scene(w, r, world_path, asset_dir, width, height)
         shadow_size = shadow_size or default_shadow
     else:
-        view, default_shadow = builtin_scene(w, r, width, height)
+        view, default_shadow = builtin_scene(w, r, width, height, textured=textured)
         shadow_size = shadow_size or default_shadow
     n_ent, _, n_lights = w.counts()
     d_vis = torch.zeros(n_ent + 1, dtype=torch.int32, device=dev)
@@ -173,5 +224,5 @@ if __name__ == "__main__":
     else:
         out = args[0] if args else os.path.join(ROOT, "gpurun_out", "frame.ppm")
         os.makedirs(os.path.dirname(out), exist_ok=True)
-        img, covered, ms = render(None, None, out, timing=True)
+        img, covered, ms = render(None, None, out, timing=True, textured=True)
     print(f"covered {covered:.3f} of the pixels, mean colour {img.reshape(-1, 3).mean(0)}, {ms:.2f} ms per frame (host loop, synchronous)")
