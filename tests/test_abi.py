@@ -62,3 +62,30 @@ def test_product_package_never_touches_the_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h", ".hpp", ".cc", "Makefile")):
                 text = open(os.path.join(dirpath, f), errors="ignore").read()
                 assert "pyoracle" not in text and "ovis_oracle" not in text and "liborion_ref" not in text, f
+
+
+def test_header_is_plain_c(tmp_path):
+    """include/orion_vis.h is the drop-in boundary: it must compile as C99 (no C++ or CUDA types in a signature), and its
+    structs must have the sizes the bindings assume."""
+    import shutil
+    import subprocess
+    cc = shutil.which("gcc") or shutil.which("cc")
+    if not cc:
+        pytest.skip("no C compiler")
+    src = tmp_path / "abi.c"
+    src.write_text('#include "orion_vis.h"\n#include <stdio.h>\n'
+                   'int main(void) { printf("%zu %zu %zu %zu %zu\\n", sizeof(OvisView), sizeof(OvisLight), sizeof(OvisMaterial), '
+                   'sizeof(OvisSceneInfo), sizeof(OvisGBufferTarget)); return 0; }\n')
+    exe = tmp_path / "abi"
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([cc, "-std=c99", "-Wall", "-Wextra", "-pedantic", "-Werror", f"-I{root}/include", str(src), "-o", str(exe)],
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    sizes = [int(x) for x in subprocess.run([str(exe)], capture_output=True, text=True).stdout.split()]
+    assert sizes[:3] == [lib.VIEW_DTYPE.itemsize, lib.LIGHT_DTYPE.itemsize, lib.MATERIAL_DTYPE.itemsize]
+    assert sizes[3] == C_sizeof_scene_info() and sizes[4] == 40
+
+
+def C_sizeof_scene_info():
+    import ctypes
+    return ctypes.sizeof(lib.SceneInfo)
