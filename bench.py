@@ -508,7 +508,13 @@ def run_ours(args, rank: int, local_rank: int, world_size: int):
                     "ms_per_frame": ms, "pixels_covered": covered,
                     "note": "synchronous host loop through the Python binding; every rasteriser call sizes its scratch from device counts"}
 
-        for key, fn in (("headless_rasteriser", lambda: bench_raster.run(2000, 8)),      # G-buffer + shadow-map passes (ovis_raster.cu)
+        def size_sweep():
+            from tools import size_sweep as sweep
+            return {"what": "the single-view cull of one GPU at other sizes of BASELINE's range (tools/size_sweep.py; 100 M: profiles/r02_size_sweep.json)",
+                    "rows": [sweep.one(int(m * 1e6), oracle, cores, frames=40) for m in (1, 5, 25)]}
+
+        for key, fn in (("size_sweep", size_sweep),
+                        ("headless_rasteriser", lambda: bench_raster.run(2000, 8)),      # G-buffer + shadow-map passes (ovis_raster.cu)
                         ("headless_frame", whole_frame),
                         ("config1", bench_configs.config1),
                         ("config3", lambda: bench_configs.config3(False, full_parity=True)),
