@@ -8,6 +8,7 @@
 #include "orion_vis.h"
 
 #include <algorithm>
+#include <atomic>
 #include <chrono>
 #include <cstdarg>
 #include <cstdio>
@@ -170,6 +171,8 @@ struct OvisWorld {
     unsigned int *d_exchange = nullptr;   // [0] gather done counter, [1] exchange error flag
     uint32_t *h_counts = nullptr;         // pinned mirror
     uint32_t *h_counts_dev = nullptr;     // the same words as the device addresses them (mapped pinned memory)
+    uint32_t host_frame = 0;              // value the gather kernel's last block stores into h_counts[2] for the current cull
+    bool host_flag = true;                // OVIS_HOST_FLAG=0: wait with cudaStreamSynchronize instead of watching that word
     bool direct_host = true;              // OVIS_DIRECT_HOST=0 (tuning) forces the copy path
     bool block_fence_sys = false;         // OVIS_EXCHANGE_BLOCK_FENCE=sys (diagnostic): system fence in every gather block
     uint32_t *d_csr_entities = nullptr;
@@ -1399,8 +1402,8 @@ int ovis_world_create(int device, OvisWorld **out_world) {
     OVIS_CUDA(cudaMemset(w->d_exchange, 0, 2 * sizeof(unsigned int)));
     OVIS_CUDA(cudaMalloc(&w->d_counts, 2 * sizeof(uint32_t)));
     OVIS_CUDA(cudaMemset(w->d_counts, 0, 2 * sizeof(uint32_t)));
-    OVIS_CUDA(cudaMallocHost(&w->h_counts, 2 * sizeof(uint32_t)));
-    w->h_counts[0] = w->h_counts[1] = 0;
+    OVIS_CUDA(cudaMallocHost(&w->h_counts, 4 * sizeof(uint32_t)));     // entity count, light count, frame flag, unused
+    w->h_counts[0] = w->h_counts[1] = w->h_counts[2] = w->h_counts[3] = 0;
     if (cudaHostGetDevicePointer((void **)&w->h_counts_dev, w->h_counts, 0) != cudaSuccess) {
         cudaGetLastError();
         w->h_counts_dev = nullptr;
@@ -1409,6 +1412,8 @@ int ovis_world_create(int device, OvisWorld **out_world) {
         w->block_fence_sys = std::strcmp(v, "sys") == 0;
     if (const char *v = getenv("OVIS_DIRECT_HOST"))
         w->direct_host = atoi(v) != 0;
+    if (const char *v = getenv("OVIS_HOST_FLAG"))
+        w->host_flag = atoi(v) != 0;
     if (const char *v = getenv("OVIS_MV_DENSE")) {
         w->mv_force_dense = atoi(v) != 0;
         w->mv_force_sparse = atoi(v) == 0;
@@ -2217,19 +2222,33 @@ static uint32_t *host_alias(OvisWorld *w, const uint32_t *host) {
 static int cull_to_host(OvisWorld *w, const float planes[24], uint32_t require, bool with_lights,
                         uint32_t *out_entities, int64_t cap_entities, int64_t *out_n_entities,
                         uint32_t *out_lights, int32_t cap_lights, int32_t *out_n_lights) {
+    MvTrace trace;                                             // OVIS_MV_TRACE=1: host-side time stamps on stderr
     OVIS_TRY(flush_transforms(w));
     // Pinned output buffer: the gather kernel stores the ids (and the count) straight into host memory as its second
     // destination, so the frame is two kernels and one synchronise - no copy is enqueued at all.
     uint32_t *alias = cap_entities > 0 ? host_alias(w, out_entities) : nullptr;
+    // With the ids going straight to host memory the only thing left to wait for is the kernel's end. The gather kernel's
+    // last block can say so itself: after a system-scope fence it stores the frame number into a page-locked word, and the
+    // host watches that word instead of asking the driver (cudaStreamSynchronize wakes up a few microseconds later).
+    // Worlds small enough for the single cooperative launch keep it (flags would send them down the two-launch path).
+    const bool watch = alias && !with_lights && w->host_flag && w->n_ent >= (512 << 10);
     if (alias) {
         uint32_t *extra_out[1] = { alias }, *extra_count[1] = { w->h_counts_dev };
+        FlagOpts f;
+        uint32_t *flag_ptr[1] = { w->h_counts_dev + 2 };
+        if (watch) {
+            f.n_signal = 1;
+            f.signal_flags = flag_ptr;
+            f.signal_value = ++w->host_frame;
+        }
         OVIS_TRY(enqueue_cull(w, planes, require, w->d_result, (long long)w->cap_ent, nullptr, nullptr, w->d_counts, 1,
-                              extra_out, extra_count, nullptr, (long long)cap_entities));
+                              extra_out, extra_count, watch ? &f : nullptr, (long long)cap_entities));
     } else {
         OVIS_TRY(enqueue_cull(w, planes, require, w->d_result, (long long)w->cap_ent, nullptr, nullptr, w->d_counts));
     }
     if (with_lights)
         OVIS_TRY(enqueue_light_cull(w, planes));
+    trace.mark("cull: kernels queued");
     // Pageable output buffer: one round trip in the common case. Visible sets change little from cull to cull, so the
     // ids are copied speculatively (a little more than the previous call needed) together with the counts; only a call
     // whose list turns out longer pays a second copy for the remainder.
@@ -2243,7 +2262,21 @@ static int cull_to_host(OvisWorld *w, const float planes[24], uint32_t require, 
         OVIS_CUDA(cudaMemcpyAsync(out_entities, w->d_result, sizeof(uint32_t) * (size_t)spec_e, cudaMemcpyDeviceToHost, w->stream));
     if (spec_l > 0)
         OVIS_CUDA(cudaMemcpyAsync(out_lights, w->d_light_out, sizeof(uint32_t) * (size_t)spec_l, cudaMemcpyDeviceToHost, w->stream));
-    OVIS_CUDA(cudaStreamSynchronize(w->stream));
+    bool arrived = false;
+    if (watch) {
+        const volatile uint32_t *flag = w->h_counts + 2;
+        const auto t0 = std::chrono::steady_clock::now();
+        for (unsigned spins = 0; !arrived; spins++) {
+            arrived = *flag == w->host_frame;
+            if (!arrived && (spins & 1023u) == 1023u &&
+                std::chrono::steady_clock::now() - t0 > std::chrono::milliseconds(50))
+                break;                                         // something is wrong (or very slow): let the driver tell
+        }
+        std::atomic_thread_fence(std::memory_order_acquire);
+    }
+    if (!arrived)
+        OVIS_CUDA(cudaStreamSynchronize(w->stream));
+    trace.mark("cull: synchronised");
     int64_t ne = w->h_counts[0];
     int32_t nl = with_lights ? (int32_t)w->h_counts[1] : 0;
     w->last_visible = ne;

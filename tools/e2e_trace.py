@@ -1,0 +1,15 @@
+import os, sys, time
+sys.path.insert(0, '/root/repo')
+import numpy as np, torch
+from orion_b200 import lib, scenes
+n = 12_500_000
+aabb, flags = scenes.static_boxes(n, 4242, 4000.0)
+w = lib.World(0); w.reserve(n); f = w.add_entities(aabb, flags); w.set_world_aabbs(f, aabb)
+view = scenes.default_camera()
+pinned = lib.PinnedBuffer(1 << 16)
+step = w.bind_cull(view, pinned.array)
+for _ in range(20): step()
+os.environ['X']='1'
+t0=time.perf_counter()
+for _ in range(200): step()
+print("e2e us", (time.perf_counter()-t0)/200*1e6, file=sys.stderr)
