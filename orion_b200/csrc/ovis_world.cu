@@ -90,6 +90,7 @@ struct OvisWorld {
     int num_sms = 0;
     int forced_variant = -1;              // OVIS_CULL_VARIANT (tuning); -1 = pick by size
     bool fused_small = true;              // OVIS_CULL_FUSED=0 (tuning) keeps small worlds on the two-launch path
+    int64_t fused_below = 512 << 10;      // OVIS_FUSED_BELOW (tuning): worlds with fewer entities take the single cooperative launch
     int blocks_per_sm[16][2] = {};         // cull test kernel occupancy per variant: [unmasked, masked]
     int fused_blocks_per_sm[16][2] = {};   // same for the fused (cooperative) kernel; 0 = not available
     int64_t launches = 0;
@@ -771,7 +772,7 @@ int enqueue_cull(OvisWorld *w, const float planes[24], uint32_t require, uint32_
     // Below ~half a million entities the cull is pure latency: one cooperative launch runs both phases with a grid
     // barrier in between. Larger worlds use two launches, the second overlapped with the next cull's first.
     const int fused_per_sm = w->fused_blocks_per_sm[variant][masked ? 1 : 0];
-    const bool fused = w->fused_small && w->n_ent < (512 << 10) && fused_per_sm > 0 && !flags;
+    const bool fused = w->fused_small && w->n_ent < w->fused_below && fused_per_sm > 0 && !flags;
     if (fused) {
         grid = ovis::cull_test_grid(variant, a.num_groups, w->num_sms * fused_per_sm);   // every CTA must be co-resident
         OVIS_CUDA(ovis::launch_cull_fused(a, g, masked, variant, grid, w->stream));
@@ -1412,6 +1413,8 @@ int ovis_world_create(int device, OvisWorld **out_world) {
         w->block_fence_sys = std::strcmp(v, "sys") == 0;
     if (const char *v = getenv("OVIS_DIRECT_HOST"))
         w->direct_host = atoi(v) != 0;
+    if (const char *v = getenv("OVIS_FUSED_BELOW"))
+        w->fused_below = atoll(v);
     if (const char *v = getenv("OVIS_HOST_FLAG"))
         w->host_flag = atoi(v) != 0;
     if (const char *v = getenv("OVIS_MV_DENSE")) {
@@ -2231,7 +2234,7 @@ static int cull_to_host(OvisWorld *w, const float planes[24], uint32_t require, 
     // last block can say so itself: after a system-scope fence it stores the frame number into a page-locked word, and the
     // host watches that word instead of asking the driver (cudaStreamSynchronize wakes up a few microseconds later).
     // Worlds small enough for the single cooperative launch keep it (flags would send them down the two-launch path).
-    const bool watch = alias && !with_lights && w->host_flag && w->n_ent >= (512 << 10);
+    const bool watch = alias && !with_lights && w->host_flag && w->n_ent >= w->fused_below;
     if (alias) {
         uint32_t *extra_out[1] = { alias }, *extra_count[1] = { w->h_counts_dev };
         FlagOpts f;
