@@ -383,21 +383,9 @@ __device__ __forceinline__ void cull_gather_body(const GatherArgs &a, int block,
     }
 }
 
-__global__ void __launch_bounds__(256)
-cull_gather_kernel(const __grid_constant__ GatherArgs a) {
-    __shared__ uint32_t s_ids[kGatherWindow];
-    // Let the next cull's test kernel start now (if it was launched to allow that): it shares nothing with this kernel.
-    asm volatile("griddepcontrol.launch_dependents;");
-    if (a.n_wait) {                                           // peers must be done with the buffer we are about to refill
-        if (threadIdx.x == 0)
-            wait_flags_at_least(a.wait_flags, a.n_wait, a.wait_value, a.error_flag);
-        __syncthreads();
-    }
-    // a CTA takes every gridDim.x-th block (blocks without survivors return at once inside the body)
-    for (int b = blockIdx.x; b < a.num_blocks; b += gridDim.x) {
-        cull_gather_body(a, b, a.num_blocks, s_ids);
-        __syncthreads();                                      // the body's shared arrays are reused by the next block
-    }
+// The last block of a gather (or fused) launch to finish publishes the result: ready flags for peers, the frame word for a
+// watching host.
+__device__ __forceinline__ void signal_when_all_blocks_done(const GatherArgs &a) {
     if (a.n_signal) {                                         // the last block to finish publishes the segment
         __syncthreads();                                      // this block's stores happen-before thread 0's fence
         if (threadIdx.x == 0) {
@@ -419,6 +407,25 @@ cull_gather_kernel(const __grid_constant__ GatherArgs a) {
         }
     }
 }
+
+__global__ void __launch_bounds__(256)
+cull_gather_kernel(const __grid_constant__ GatherArgs a) {
+    __shared__ uint32_t s_ids[kGatherWindow];
+    // Let the next cull's test kernel start now (if it was launched to allow that): it shares nothing with this kernel.
+    asm volatile("griddepcontrol.launch_dependents;");
+    if (a.n_wait) {                                           // peers must be done with the buffer we are about to refill
+        if (threadIdx.x == 0)
+            wait_flags_at_least(a.wait_flags, a.n_wait, a.wait_value, a.error_flag);
+        __syncthreads();
+    }
+    // a CTA takes every gridDim.x-th block (blocks without survivors return at once inside the body)
+    for (int b = blockIdx.x; b < a.num_blocks; b += gridDim.x) {
+        cull_gather_body(a, b, a.num_blocks, s_ids);
+        __syncthreads();                                      // the body's shared arrays are reused by the next block
+    }
+    signal_when_all_blocks_done(a);
+}
+
 
 __global__ void wait_flags_kernel(const uint32_t *flags, int n, uint32_t value, uint32_t *error_flag) {
     wait_flags_at_least(flags, n, value, error_flag);
@@ -465,6 +472,7 @@ cull_fused_kernel(const __grid_constant__ CullArgs a, const __grid_constant__ Ga
         cull_gather_body(g, b, g.num_blocks, s_ids);
         __syncthreads();                                    // shared arrays are reused by the next block
     }
+    signal_when_all_blocks_done(g);
 }
 
 // Launch shapes selectable at run time (OVIS_CULL_VARIANT, tuning only); the world picks by size (cull_default_variant).

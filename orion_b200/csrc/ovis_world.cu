@@ -772,7 +772,7 @@ int enqueue_cull(OvisWorld *w, const float planes[24], uint32_t require, uint32_
     // Below ~half a million entities the cull is pure latency: one cooperative launch runs both phases with a grid
     // barrier in between. Larger worlds use two launches, the second overlapped with the next cull's first.
     const int fused_per_sm = w->fused_blocks_per_sm[variant][masked ? 1 : 0];
-    const bool fused = w->fused_small && w->n_ent < w->fused_below && fused_per_sm > 0 && !flags;
+    const bool fused = w->fused_small && w->n_ent < w->fused_below && fused_per_sm > 0 && (!flags || flags->n_wait == 0);
     if (fused) {
         grid = ovis::cull_test_grid(variant, a.num_groups, w->num_sms * fused_per_sm);   // every CTA must be co-resident
         OVIS_CUDA(ovis::launch_cull_fused(a, g, masked, variant, grid, w->stream));
@@ -2233,8 +2233,7 @@ static int cull_to_host(OvisWorld *w, const float planes[24], uint32_t require, 
     // With the ids going straight to host memory the only thing left to wait for is the kernel's end. The gather kernel's
     // last block can say so itself: after a system-scope fence it stores the frame number into a page-locked word, and the
     // host watches that word instead of asking the driver (cudaStreamSynchronize wakes up a few microseconds later).
-    // Worlds small enough for the single cooperative launch keep it (flags would send them down the two-launch path).
-    const bool watch = alias && !with_lights && w->host_flag && w->n_ent >= w->fused_below;
+    const bool watch = alias && !with_lights && w->host_flag && w->n_ent > 0;      // (an empty world launches no gather)
     if (alias) {
         uint32_t *extra_out[1] = { alias }, *extra_count[1] = { w->h_counts_dev };
         FlagOpts f;
