@@ -632,6 +632,9 @@ int ovis_host_free(void *ptr);
  * rank's kernel writes its own segment, no GPU-to-GPU exchange is needed for a host consumer. No counterpart in the
  * reference. */
 int ovis_host_register(void *ptr, int64_t bytes);
+/* Spin until every one of n words in HOST memory is at least `value` (frame counters other processes or GPUs store: the
+ * hand-over of per-rank segments in one shared block). OVIS_ERR_CAPACITY after timeout_us microseconds (< 0: never). */
+int ovis_host_flags_wait(const uint32_t *flags, int32_t n, uint32_t value, int64_t timeout_us);
 int ovis_host_unregister(void *ptr);
 
 /* Profiling hook (no counterpart in the reference, whose cull path has no timers - SURVEY.md section 5):

@@ -2758,6 +2758,25 @@ int ovis_host_free(void *ptr) {
     return OVIS_OK;
 }
 
+int ovis_host_flags_wait(const uint32_t *flags, int32_t n, uint32_t value, int64_t timeout_us) {
+    if (!flags || n < 0)
+        return fail(OVIS_ERR_INVALID, "ovis_host_flags_wait: bad arguments");
+    const volatile uint32_t *f = flags;
+    const auto t0 = std::chrono::steady_clock::now();
+    for (unsigned spins = 0;; spins++) {
+        bool all = true;
+        for (int32_t i = 0; i < n; i++)
+            all = all && (int32_t)(f[i] - value) >= 0;           // "at least", robust to wrap-around
+        if (all)
+            break;
+        if ((spins & 255u) == 255u && timeout_us >= 0 &&
+            std::chrono::steady_clock::now() - t0 > std::chrono::microseconds(timeout_us))
+            return fail(OVIS_ERR_CAPACITY, "ovis_host_flags_wait: timed out");
+    }
+    std::atomic_thread_fence(std::memory_order_acquire);
+    return OVIS_OK;
+}
+
 int ovis_host_register(void *ptr, int64_t bytes) {
     if (!ptr || bytes <= 0)
         return fail(OVIS_ERR_INVALID, "ovis_host_register: bad arguments");

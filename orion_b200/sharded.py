@@ -195,18 +195,20 @@ class SharedHostSegments:
         lib = self._lib
         state = {"culls": make_culls()}
 
+        import ctypes as C
+        wait = lib.load().ovis_host_flags_wait
+        n_ranks = C.c_int32(self.size)
+
         def step(timeout_s: float = 20.0):
             while True:
+                flags_ptr = C.c_void_p(self.flags.ctypes.data)      # (the block may have been regrown)
                 self.frame += 1
                 f, k = self.frame, self.frame & 1
                 self.sets[k, self.rank, 0] = state["culls"][k]()   # the true count, also when it did not fit
                 self.flags[self.rank] = f                     # after the ids and the count (x86 keeps the store order)
-                t0 = None
-                while int(self.flags.min()) < f:              # every rank has delivered frame f
-                    if t0 is None:
-                        t0 = time.perf_counter()
-                    elif time.perf_counter() - t0 > timeout_s:
-                        raise RuntimeError("a rank did not deliver its segment")
+                # every rank has delivered frame f (spin in C: a Python poll loop costs microseconds per look)
+                if wait(flags_ptr, n_ranks, C.c_uint32(f), C.c_int64(int(timeout_s * 1e6))) != 0:
+                    raise RuntimeError("a rank did not deliver its segment")
                 counts = self.sets[k, :, 0].astype(np.int64)
                 if int(counts.max()) <= self.capacity:
                     return [self.sets[k, r, 1:1 + int(counts[r])] for r in range(self.size)]
