@@ -289,6 +289,7 @@ inline bool lightHasNoEffect(const OvisLight &l) {
     Vec3 c = { l.colour[0], l.colour[1], l.colour[2] };
     return !l.intensity || !std::sqrt(dot(c, c));
 }
+constexpr float kShadowViewNear = 0.1f;                                                   // render_light.cc:273,319
 // render/src/render_light.cc:258-332; viewport square per deferred_render_pipeline.cc:261-265
 inline int shadowViews(const OvisLight &l, int resolution, OvisView out[6]) {
     if (!(l.flags & OVIS_CASTS_SHADOW))
@@ -297,7 +298,7 @@ inline int shadowViews(const OvisLight &l, int resolution, OvisView out[6]) {
     auto fill = [&](OvisView &v, Quat o, float fov) {
         std::memcpy(v.position, l.position, sizeof v.position);
         v.orientation[0] = o.w; v.orientation[1] = o.x; v.orientation[2] = o.y; v.orientation[3] = o.z;
-        v.hfov_deg = fov; v.znear = 0.1f; v.zfar = l.range;
+        v.hfov_deg = fov; v.znear = kShadowViewNear; v.zfar = l.range;
         v.vp_width = resolution; v.vp_height = resolution;
     };
     if (l.type == OVIS_LIGHT_SPOT) {

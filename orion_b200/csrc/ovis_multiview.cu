@@ -422,14 +422,17 @@ __device__ __forceinline__ int cell_of(float v, float inv, float bias, int dim) 
 // odd: a NaN or infinite side (the sum of the sides is then NaN or infinite; so is that of a finite box wider than 1e38,
 // which is merely treated with the same caution).
 __device__ __forceinline__ void inflate_box(const MvGrid &g, const float mn[3], const float mx[3], float lo[3], float hi[3], bool *odd) {
-    const float sx = mx[0] - mn[0], sy = mx[1] - mn[1], sz = mx[2] - mn[2];
-    const float ext = fmaxf(fmaxf(fmaxf(sx, sy), sz), 0.0f);
-    *odd = !(fabsf((sx + sy) + sz) <= 3.0e38f);
+    // An inverted box (min > max on some axis; the reference tests it like any other, its "P-vertex" then being the least
+    // favourable corner) is filtered as the box its two corners span: whatever the reference accepts of the inverted box
+    // it accepts of the spanned one, whose overlap with the cube is what the argument is about.
+    const float sx = fabsf(mx[0] - mn[0]), sy = fabsf(mx[1] - mn[1]), sz = fabsf(mx[2] - mn[2]);
+    const float ext = fmaxf(fmaxf(sx, sy), sz);
+    *odd = !((sx + sy) + sz <= 3.0e38f);
     const float re = __fmaf_rn(ext, 1.004f, g.re_bias);
 #pragma unroll
     for (int c = 0; c < 3; c++) {
-        lo[c] = mn[c] - re;
-        hi[c] = mx[c] + re;
+        lo[c] = fminf(mn[c], mx[c]) - re;
+        hi[c] = fmaxf(mn[c], mx[c]) + re;
     }
 }
 

@@ -1328,7 +1328,11 @@ int shadow_views_device(OvisWorld *w, const std::vector<uint32_t> &light_ids, in
             continue;
         // A point light's six face frusta (fov 90, far = range, apex at the light) only accept boxes that overlap
         // the cube of half-side range + box extent about the light; a spot light's single frustum gets no pre-filter.
-        groups.push_back(make_group(l.type == OVIS_LIGHT_POINT ? l.position : nullptr, l.range, (int)list_light.size(), lv.count));
+        // That holds while far > near: a range at or below the shadow views' near plane (0.1) turns the far plane
+        // round, the frusta open outwards beyond the range (the reference then lists entities any distance away), and
+        // the light is tested without a cube. A NaN range fails the comparison too.
+        const bool bounded = l.type == OVIS_LIGHT_POINT && l.range > ovis::hm::kShadowViewNear;
+        groups.push_back(make_group(bounded ? l.position : nullptr, l.range, (int)list_light.size(), lv.count));
         planes.insert(planes.end(), lv.planes, lv.planes + 24 * lv.count);
         for (int i = 0; i < lv.count; i++) {
             list_light.push_back((int32_t)id);

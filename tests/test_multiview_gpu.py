@@ -113,6 +113,55 @@ def test_sparse_pass_hands_over_when_a_block_is_too_crowded(oracle, monkeypatch)
     w.close()
 
 
+@pytest.mark.parametrize("dense", ["0", "1"])
+def test_point_lights_whose_range_is_below_the_shadow_near_plane(oracle, monkeypatch, dense):
+    """perspective(90, 0.1, range) with range <= 0.1 turns the far plane round: the reference's face frusta then open
+    outwards and list entities any distance from the light (render_light.cc:319 has no guard). Such lights must not be
+    pre-filtered by a cube of their range; ordinary lights in the same call still are."""
+    monkeypatch.setenv("OVIS_MV_DENSE", dense)
+    rng = np.random.default_rng(505)
+    n = 40_000
+    boxes = util.random_boxes(rng, n, extent=120.0, hmax=2.0)
+    flags = np.ones(n, dtype=np.uint32)
+    lights = scenes.point_lights(12, 11, 100.0, 20.0, 60.0)
+    lights["range"][:8] = [0.02, 0.05, 0.07, 0.1, 0.0, -1.0, np.float32(0.1) + np.float32(1e-6), 0.0999]
+    w = _world_static(boxes, flags)
+    w.add_lights(lights)
+    ids = np.arange(len(lights), dtype=np.uint32)
+    ll, lv, off, ent = _shadow_lists(w, ids)
+    expected = _expected_lists(oracle, boxes, flags, lights, ids)
+    assert sum(len(e) for e in expected[:6]) > n // 2          # range 0.02: nearly every entity lands in some face
+    for k, exp in enumerate(expected):
+        assert np.array_equal(ent[off[k]:off[k + 1]], exp), (dense, k)
+    w.close()
+
+
+def test_inverted_boxes_reach_the_lists_through_the_light_grid(oracle, monkeypatch):
+    """min > max on some axes: the reference tests such a box like any other (its P-vertex is then the least favourable
+    corner) and lists it when the whole spanned box is inside a face frustum. The grid must file it under the cells of the
+    spanned box, not under an empty range."""
+    monkeypatch.setenv("OVIS_MV_DENSE", "0")
+    rng = np.random.default_rng(506)
+    n = 30_000
+    boxes = util.random_boxes(rng, n, extent=300.0, hmax=3.0)
+    flip = rng.random((n, 3)) < 0.3
+    lo, hi = boxes[:, :3].copy(), boxes[:, 3:].copy()
+    boxes[:, :3] = np.where(flip, hi, lo)
+    boxes[:, 3:] = np.where(flip, lo, hi)
+    flags = np.ones(n, dtype=np.uint32)
+    lights = scenes.point_lights(24, 12, 280.0, 40.0, 320.0)
+    w = _world_static(boxes, flags)
+    w.add_lights(lights)
+    ids = np.arange(len(lights), dtype=np.uint32)
+    ll, lv, off, ent = _shadow_lists(w, ids)
+    expected = _expected_lists(oracle, boxes, flags, lights, ids)
+    inverted = flip.any(axis=1)
+    assert sum(int(inverted[e].sum()) for e in expected) > 1000
+    for k, exp in enumerate(expected):
+        assert np.array_equal(ent[off[k]:off[k + 1]], exp), k
+    w.close()
+
+
 def test_small_worlds_take_the_dense_pass_and_agree(oracle, monkeypatch):
     """Below ~1e8 entity-view tests the cube groups are tested densely (cheaper than the grid); same lists either way."""
     rng = np.random.default_rng(504)
