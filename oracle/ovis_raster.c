@@ -21,6 +21,9 @@
  *   - coverage by 2-D homogeneous edge functions in float (rows of the adjugate of [X; Y; w] with X = (x_c + w_c) W / 2,
  *     Y = (y_c + w_c) H / 2), a centre exactly on an edge belongs to the triangle for which that edge is a top or left one;
  *     no geometric clipping: a triangle that crosses the near plane is rasterised as it is;
+ *   - with all three vertices in front of the eye (w > 0) only the centres inside the bounding box of the projected
+ *     vertices, widened by a pixel, are tested (setup() below: the box is part of the definition, not an optimisation -
+ *     the edge functions of a triangle far smaller than a pixel are cancellation noise away from it);
  *   - depth = (sum E_i z_i) / (sum E_i w_i) with the clip-space z and w of the vertices (perspective-correct z / w on a
  *     0..1 depth range), fragments with depth outside [0, 1] or a non-positive w are discarded (near / far clip);
  *   - attributes interpolated with the weights E_i / (E_0 + E_1 + E_2);
@@ -121,8 +124,28 @@ static void setup_tan(const float *mvp, const float *model, const float *v0, con
     t->draw = det > 0.0f;
     if (t->z[0] < 0.0f && t->z[1] < 0.0f && t->z[2] < 0.0f) t->draw = 0;
     if (t->z[0] > t->w[0] && t->z[1] > t->w[1] && t->z[2] > t->w[2]) t->draw = 0;
-    /* every pixel is visited here; the bounding box only has to be one the CUDA path's box is inside of */
+    /* The pixels a triangle may touch are part of the definition: with all three vertices in front of the eye, only the
+     * centres inside the box of the projected vertices (one pixel of slack for the rounding of the divisions) are tested.
+     * Without the box a triangle far smaller than a pixel, whose edge functions are all cancellation noise, lights up
+     * centres nowhere near it. A triangle with a vertex at or behind the eye has no finite box: every centre is tested. */
     t->x0 = 0; t->x1 = width - 1; t->y0 = 0; t->y1 = height - 1;
+    if (t->draw && t->w[0] > 0.0f && t->w[1] > 0.0f && t->w[2] > 0.0f) {
+        const float px[3] = { X[0] / t->w[0], X[1] / t->w[1], X[2] / t->w[2] };
+        const float py[3] = { Y[0] / t->w[0], Y[1] / t->w[1], Y[2] / t->w[2] };
+        const float lx = fminf(fminf(px[0], px[1]), px[2]), hx = fmaxf(fmaxf(px[0], px[1]), px[2]);
+        const float ly = fminf(fminf(py[0], py[1]), py[2]), hy = fmaxf(fmaxf(py[0], py[1]), py[2]);
+        if (!(hx >= 0.0f) || !(lx <= (float)width) || !(hy >= 0.0f) || !(ly <= (float)height)) {
+            t->draw = 0;
+        } else {
+            /* (clamped as floats first: a float beyond int's range converts to anything in C; CUDA's conversion saturates) */
+            const int bx0 = (int)fmaxf(floorf(lx - 0.5f), 0.0f), bx1 = (int)fminf(ceilf(hx - 0.5f), (float)(width - 1));
+            const int by0 = (int)fmaxf(floorf(ly - 0.5f), 0.0f), by1 = (int)fminf(ceilf(hy - 0.5f), (float)(height - 1));
+            if (bx0 > t->x0) t->x0 = bx0;
+            if (bx1 < t->x1) t->x1 = bx1;
+            if (by0 > t->y0) t->y0 = by0;
+            if (by1 < t->y1) t->y1 = by1;
+        }
+    }
 }
 
 static int sample(const tri_t *t, int px, int py, float e[3], float *depth) {
@@ -206,8 +229,8 @@ void orc_raster_basic(int64_t n_instances, const float *matrix, const int64_t *m
                   width, height, &t);
             if (!t.draw)
                 continue;
-            for (int py = 0; py < height; py++)
-                for (int px = 0; px < width; px++) {
+            for (int py = t.y0; py <= t.y1; py++)
+                for (int px = t.x0; px <= t.x1; px++) {
                     float e[3], depth;
                     if (!sample(&t, px, py, e, &depth))
                         continue;
@@ -325,8 +348,8 @@ void orc_raster_textured(int64_t n_instances, const float *matrix, const int64_t
                       width, height, &t);
             if (!t.draw)
                 continue;
-            for (int py = 0; py < height; py++)
-                for (int px = 0; px < width; px++) {
+            for (int py = t.y0; py <= t.y1; py++)
+                for (int px = t.x0; px <= t.x1; px++) {
                     float e[3], depth;
                     if (!sample(&t, px, py, e, &depth))
                         continue;
