@@ -43,7 +43,7 @@ int scene_error(int code, const char *fmt, ...) {
     return ovis::report_error(code, buf);
 }
 
-// ---- minimal JSON (RFC 8259 values; numbers through strtod, as rapidjson's default double path yields) -----------
+// ---- minimal JSON: what rapidjson's Document::Parse accepts with the default flags, and the values it yields -------
 
 struct Json {
     enum Kind { Null, Bool, Number, String, Array, Object } kind = Null;
@@ -74,48 +74,255 @@ struct JsonParser {
             error = what;
         return false;
     }
+    // rapidjson's ParseStringToStream (reader.h:839-900 of the vendored copy) with the default flags: the escapes of
+    // RFC 8259 only, \u with exactly four hex digits, a high surrogate must be followed by a low one and the pair becomes
+    // one 4-byte sequence, a lone low surrogate is stored as it stands, bytes below 0x20 are refused, everything else is
+    // copied without validation.
+    bool parseHex4(unsigned &cp) {
+        cp = 0;
+        for (int i = 0; i < 4; i++, p++) {
+            const char c = p < end ? *p : '\0';
+            cp <<= 4;
+            if (c >= '0' && c <= '9') cp += (unsigned)(c - '0');
+            else if (c >= 'A' && c <= 'F') cp += (unsigned)(c - 'A' + 10);
+            else if (c >= 'a' && c <= 'f') cp += (unsigned)(c - 'a' + 10);
+            else return fail("bad \\u escape");
+        }
+        return true;
+    }
+    static void putUtf8(std::string &out, unsigned cp) {
+        if (cp <= 0x7f) {
+            out += (char)cp;
+        } else if (cp <= 0x7ff) {
+            out += (char)(0xc0 | (cp >> 6));
+            out += (char)(0x80 | (cp & 0x3f));
+        } else if (cp <= 0xffff) {
+            out += (char)(0xe0 | (cp >> 12));
+            out += (char)(0x80 | ((cp >> 6) & 0x3f));
+            out += (char)(0x80 | (cp & 0x3f));
+        } else {
+            out += (char)(0xf0 | (cp >> 18));
+            out += (char)(0x80 | ((cp >> 12) & 0x3f));
+            out += (char)(0x80 | ((cp >> 6) & 0x3f));
+            out += (char)(0x80 | (cp & 0x3f));
+        }
+    }
     bool parseString(std::string &out) {
         if (p >= end || *p != '"')
             return fail("expected string");
         p++;
-        while (p < end && *p != '"') {
-            if (*p == '\\') {
-                if (++p >= end)
-                    return fail("bad escape");
-                switch (*p) {
-                case 'n': out += '\n'; break;
-                case 't': out += '\t'; break;
-                case 'r': out += '\r'; break;
-                case 'b': out += '\b'; break;
-                case 'f': out += '\f'; break;
-                case 'u': {                                     // a BMP code point, stored as UTF-8 like rapidjson does
-                    if (end - p < 5)
-                        return fail("bad \\u escape");
-                    char hex[5] = { p[1], p[2], p[3], p[4], 0 };
-                    const unsigned long cp = strtoul(hex, nullptr, 16);
-                    if (cp < 0x80) {
-                        out += (char)cp;
-                    } else if (cp < 0x800) {
-                        out += (char)(0xc0 | (cp >> 6));
-                        out += (char)(0x80 | (cp & 0x3f));
-                    } else {
-                        out += (char)(0xe0 | (cp >> 12));
-                        out += (char)(0x80 | ((cp >> 6) & 0x3f));
-                        out += (char)(0x80 | (cp & 0x3f));
-                    }
-                    p += 4;
-                    break;
-                }
-                default: out += *p; break;                      // \" \\ \/
-                }
+        for (;;) {
+            if (p >= end)
+                return fail("unterminated string");
+            const char c = *p;
+            if (c == '"') {
                 p++;
-            } else {
-                out += *p++;
+                return true;
+            }
+            if ((unsigned char)c < 0x20)
+                return fail("control character in a string");
+            if (c != '\\') {
+                out += c;
+                p++;
+                continue;
+            }
+            if (++p >= end)
+                return fail("bad escape");
+            switch (*p++) {
+            case '"': out += '"'; break;
+            case '\\': out += '\\'; break;
+            case '/': out += '/'; break;
+            case 'n': out += '\n'; break;
+            case 't': out += '\t'; break;
+            case 'r': out += '\r'; break;
+            case 'b': out += '\b'; break;
+            case 'f': out += '\f'; break;
+            case 'u': {
+                unsigned cp;
+                if (!parseHex4(cp))
+                    return false;
+                if (cp >= 0xd800 && cp <= 0xdbff) {
+                    unsigned lo;
+                    if (end - p < 2 || p[0] != '\\' || p[1] != 'u')
+                        return fail("bad surrogate pair");
+                    p += 2;
+                    if (!parseHex4(lo))
+                        return false;
+                    if (lo < 0xdc00 || lo > 0xdfff)
+                        return fail("bad surrogate pair");
+                    cp = (((cp - 0xd800) << 10) | (lo - 0xdc00)) + 0x10000;
+                }
+                putUtf8(out, cp);
+                break;
+            }
+            default:
+                return fail("bad escape");
             }
         }
+    }
+    // rapidjson's ParseNumber (reader.h:1133-1370) with the default flags on a 64-bit build, then the value GetDouble()
+    // returns for it (document.h:1652-1659): integers that fit stay integers (converted exactly, or rounded once from 64
+    // bits), anything with a fraction or an exponent is significand * or / a power of ten in double arithmetic - NOT the
+    // correctly rounded strtod - with at most 17 significant digits taken (internal/strtod.h: StrtodNormalPrecision).
+    static double pow10_table(int n) {
+        static double e[309];
+        static bool ready = false;
+        if (!ready) {
+            char lit[16];
+            for (int i = 0; i <= 308; i++) {
+                snprintf(lit, sizeof lit, "1e%d", i);
+                e[i] = strtod(lit, nullptr);                       // what the literal 1e+i is in pow10.h's table
+            }
+            ready = true;
+        }
+        return e[n];
+    }
+    static double fastPath(double significand, int exp) {
+        if (exp < -308)
+            return 0.0;
+        return exp >= 0 ? significand * pow10_table(exp) : significand / pow10_table(-exp);
+    }
+    bool parseNumber(double &out) {
+        const char *s = p;
+        auto peek = [&]() { return s < end ? *s : '\0'; };
+        auto digit = [&]() { const char c = peek(); return c >= '0' && c <= '9'; };
+        const bool minus = peek() == '-';
+        if (minus)
+            s++;
+        unsigned i = 0;
+        uint64_t i64 = 0;
+        bool use64 = false, useDouble = false;
+        int sig = 0;
+        double d = 0.0;
+        if (peek() == '0') {
+            s++;
+        } else if (peek() >= '1' && peek() <= '9') {
+            i = (unsigned)(*s++ - '0');
+            const unsigned lim = minus ? 214748364u : 429496729u;
+            const char last = minus ? '8' : '5';
+            while (digit()) {
+                if (i >= lim && (i != lim || peek() > last)) {
+                    i64 = i;
+                    use64 = true;
+                    break;
+                }
+                i = i * 10 + (unsigned)(*s++ - '0');
+                sig++;
+            }
+        } else {
+            return fail("unexpected character");
+        }
+        if (use64) {
+            const uint64_t lim = minus ? 0x0CCCCCCCCCCCCCCCull : 0x1999999999999999ull;
+            const char last = minus ? '8' : '5';
+            while (digit()) {
+                if (i64 >= lim && (i64 != lim || peek() > last)) {
+                    d = (double)i64;
+                    useDouble = true;
+                    break;
+                }
+                i64 = i64 * 10 + (unsigned)(*s++ - '0');
+                sig++;
+            }
+        }
+        if (useDouble)
+            while (digit()) {
+                if (d >= 1.7976931348623157e307)
+                    return fail("number too big");
+                d = d * 10 + (*s++ - '0');
+            }
+        int expFrac = 0;
+        if (peek() == '.') {
+            s++;
+            if (!digit())
+                return fail("digits must follow the decimal point");
+            if (!useDouble) {
+                if (!use64)
+                    i64 = i;
+                while (digit()) {
+                    if (i64 > 0x1FFFFFFFFFFFFFull)                  // 2^53 - 1
+                        break;
+                    i64 = i64 * 10 + (unsigned)(*s++ - '0');
+                    --expFrac;
+                    if (i64 != 0)
+                        sig++;
+                }
+                d = (double)i64;
+                useDouble = true;
+            }
+            while (digit()) {
+                if (sig < 17) {
+                    d = d * 10.0 + (*s++ - '0');
+                    --expFrac;
+                    if (d > 0.0)
+                        sig++;
+                } else {
+                    s++;
+                }
+            }
+        }
+        int exp = 0;
+        if (peek() == 'e' || peek() == 'E') {
+            s++;
+            if (!useDouble) {
+                d = use64 ? (double)i64 : (double)i;
+                useDouble = true;
+            }
+            bool expMinus = false;
+            if (peek() == '+')
+                s++;
+            else if (peek() == '-') {
+                expMinus = true;
+                s++;
+            }
+            if (!digit())
+                return fail("digits must follow the exponent mark");
+            exp = *s++ - '0';
+            if (expMinus) {
+                while (digit()) {
+                    exp = exp * 10 + (*s++ - '0');
+                    if (exp >= 214748364)
+                        while (digit())
+                            s++;
+                }
+                exp = -exp;
+            } else {
+                const int maxExp = 308 - expFrac;
+                while (digit()) {
+                    exp = exp * 10 + (*s++ - '0');
+                    if (exp > maxExp)
+                        return fail("number too big");
+                }
+            }
+        }
+        if (useDouble) {
+            const int pw = exp + expFrac;
+            d = pw < -308 ? fastPath(fastPath(d, -308), pw + 308) : fastPath(d, pw);
+            out = minus ? -d : d;
+        } else if (use64) {
+            out = minus ? (double)(int64_t)(~i64 + 1) : (double)i64;
+        } else {
+            out = minus ? (double)(int32_t)(~i + 1) : (double)i;
+        }
+        p = s;
+        return true;
+    }
+    // Document::Parse(text, length) (document.h; the stream skips the bytes of a UTF-8 byte order mark and reads a NUL byte as the end
+    // of the text): one value, white space either side, nothing else.
+    bool parseDocument(Json &doc) {
+        for (unsigned char mark : { 0xefu, 0xbbu, 0xbfu })          // encodedstream.h:72-76: each byte of the mark on its own
+            if (p < end && (unsigned char)*p == mark)
+                p++;
+        if (const void *nul = memchr(p, 0, (size_t)(end - p)))
+            end = static_cast<const char *>(nul);
+        skip();
         if (p >= end)
-            return fail("unterminated string");
-        p++;
+            return fail("the document is empty");
+        if (!parse(doc))
+            return false;
+        skip();
+        if (p != end)
+            return fail("trailing characters after the document");
         return true;
     }
     bool parse(Json &v, int depth = 0) {
@@ -169,12 +376,9 @@ struct JsonParser {
         if (end - p >= 4 && !strncmp(p, "true", 4)) { v.kind = Json::Bool; v.b = true; p += 4; return true; }
         if (end - p >= 5 && !strncmp(p, "false", 5)) { v.kind = Json::Bool; v.b = false; p += 5; return true; }
         if (end - p >= 4 && !strncmp(p, "null", 4)) { v.kind = Json::Null; p += 4; return true; }
-        char *stop = nullptr;
-        v.num = strtod(p, &stop);
-        if (stop == p)
-            return fail("unexpected character");
+        if (!parseNumber(v.num))
+            return false;
         v.kind = Json::Number;
-        p = stop;
         return true;
     }
 };
@@ -511,11 +715,8 @@ extern "C" int ovis_json_canonical(const char *text, int64_t length, char *out, 
         return scene_error(OVIS_ERR_INVALID, "ovis_json_canonical: bad arguments");
     JsonParser parser{ text, text + length, {} };
     Json doc;
-    if (!parser.parse(doc))
+    if (!parser.parseDocument(doc))
         return scene_error(OVIS_ERR_INVALID, "ovis_json_canonical: %s", parser.error.c_str());
-    parser.skip();
-    if (parser.p != parser.end)
-        return scene_error(OVIS_ERR_INVALID, "ovis_json_canonical: trailing characters after the document");
     std::string s;
     json_canonical(doc, s);
     *out_length = (int64_t)s.size();
@@ -803,7 +1004,7 @@ int ovis_scene_load(const char *world_path, const char *game_asset_dir, int32_t 
         return scene_error(OVIS_ERR_INVALID, "ovis_scene_load: cannot read %s", world_path);
     SceneObjects scene;
     JsonParser parser{ text.data(), text.data() + text.size(), {} };
-    if (!parser.parse(scene.root) || scene.root.kind != Json::Array)
+    if (!parser.parseDocument(scene.root) || scene.root.kind != Json::Array)
         return scene_error(OVIS_ERR_INVALID, "%s: not a serialised object file (%s)", world_path,
                            parser.error.empty() ? "top level is not an array" : parser.error.c_str());
     const Json *world_object = nullptr;

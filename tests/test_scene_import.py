@@ -179,6 +179,29 @@ def test_json_layer_against_the_reference_rapidjson(ref):
     for bad in (b'[1, 2', b'{"a" 1}', b'[1,]', b'{"a": tru}', b'', b'[1] x'):
         ours, theirs = _json_both(ref, bad)
         assert ours is None and theirs is None, bad
+    # what tools/fuzz_json.py found: surrogate pairs are one 4-byte sequence, a lone low surrogate stays, unknown escapes /
+    # short \u / raw control characters are refused, numbers with a fraction follow rapidjson's significand * 10^n in
+    # double arithmetic (17 significant digits, not the correctly rounded strtod), the bytes of a byte order mark are
+    # skipped one by one, a NUL byte ends the text
+    for d in (rb'["\ud83d\ude00", "\udc00", "\u00e9"]', b'[0.30000000000000004440892098500626, 123456789012345678901234567890.5e-20]',
+              b'[1.7976931348623157e308, 4.9406564584124654e-324, 1e-400, 2.22507385850720113605740979670913197593481954635164564e-308]',
+              b'\xef\xbb\xbf[1]', b'\xbf4', b'[1]\x00 garbage', b'[18446744073709551615, 18446744073709551616, -9223372036854775808, -9223372036854775809]'):
+        ours, theirs = _json_both(ref, d)
+        assert ours is not None and ours == theirs, d
+    for bad in (rb'["\x41"]', rb'["\u12"]', rb'["\ud83d"]', rb'["\ud83d\u0041"]', b'["a\tb"]', b'[01]', b'[1.]', b'[.5]', b'[+1]', b'[1e]',
+                b'[1e999]', b'[Infinity]', b'[NaN]', b'[0x10]'):
+        ours, theirs = _json_both(ref, bad)
+        assert ours is None and theirs is None, bad
+
+
+def test_json_layer_randomised(ref):
+    """tools/fuzz_json.py in small: generated and damaged documents, accepted or refused alike, same canonical text."""
+    import subprocess
+    import sys
+    out = subprocess.run([sys.executable, os.path.join(os.path.dirname(HERE), "tools", "fuzz_json.py"), "--cases", "1500", "--seed", "7"],
+                         capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0, out.stdout[-2000:] + out.stderr[-2000:]
+    assert '"differences": 0' in out.stdout
 
 
 @pytest.mark.gpu
