@@ -140,6 +140,9 @@ def run_case(oracle, seed):
         w.set_world_aabbs(n_bound + n_direct, static_boxes)
     if len(lights):
         w.add_lights(lights)
+    pass_counts = util.random_pass_counts(rng, n_ent)
+    w.set_pass_counts(np.arange(n_ent), pass_counts & 0xff, (pass_counts >> 8) & 0xff, pass_counts >> 16)
+    identity = np.array([0, 0, 0, 1, 0, 0, 0, 1, 1, 1], dtype=np.float32)
     keep = np.ones(n_ent, dtype=bool)
     node_alive = np.ones(n_nodes, dtype=bool)
     light_alive = np.ones(len(lights), dtype=bool)
@@ -227,6 +230,22 @@ def run_case(oracle, seed):
         exp = exp[keep[exp]]
         if not np.array_equal(ents, exp):
             return desc, f"frame {frame}: cull returned {len(ents)} entities, expected {len(exp)}"
+        # the consumers of the visible list: draw lists (f1) and EntityUniforms blocks (f2), from the cull's own device
+        # result and from the list handed in
+        for mode in (lib.DRAWS_MAIN, lib.DRAWS_SHADOW):
+            e0, e1 = oracle.draw_lists(exp, pass_counts, flags, mode)
+            for vis_arg in (None, exp):
+                d0, d1, counts = util.gpu_draw_lists(w, mode, visible=vis_arg)
+                if counts != (len(e0), len(e1)) or not np.array_equal(d0, e0) or not np.array_equal(d1, e1):
+                    return desc, f"frame {frame}: draw lists of mode {mode} differ ({counts} vs {(len(e0), len(e1))})"
+        trs_of = np.tile(identity, (n_ent, 1))
+        trs_of[:n_bound] = wt[ent_node]
+        trs_of[n_bound:n_bound + n_direct] = direct_trs
+        want_u = oracle.entity_uniforms(trs_of[exp])
+        for vis_arg in (None, exp):
+            got_u = util.gpu_entity_uniforms(w, vis_arg)[:len(exp)]
+            if not util.same(got_u, want_u):
+                return desc, f"frame {frame}: entity uniform blocks differ"
         exp_l = oracle.light_cull(lights, planes) if len(lights) else np.zeros(0, dtype=np.uint32)
         exp_l = exp_l[light_alive[exp_l]] if len(exp_l) else exp_l
         if not np.array_equal(ls, exp_l):
