@@ -214,8 +214,9 @@ int ovis_light_uniforms(const OvisLight *light, const float attenuation[3], floa
  * AABB intersects the view frustum (core/src/math/intersection.cc:42-57); when flags has
  * OVIS_CULL_LIGHTS, out_lights receives ids of lights for which RenderLight::cull is false
  * (render_light.cc:187-209). Counts are always written; if a capacity is too small the call returns
- * OVIS_ERR_CAPACITY and the content of that list is unspecified. out_lights may be NULL when
- * OVIS_CULL_LIGHTS is not set. */
+ * OVIS_ERR_CAPACITY and the content of that list is unspecified. Nothing beyond a buffer's capacity is ever
+ * written; entries between the count and the capacity are unspecified (a small list comes over in one
+ * speculative copy together with its count). out_lights may be NULL when OVIS_CULL_LIGHTS is not set. */
 int ovis_cull(OvisWorld *world, const OvisView *view, uint32_t flags,
               uint32_t *out_entities, int64_t cap_entities, int64_t *out_n_entities,
               uint32_t *out_lights, int32_t cap_lights, int32_t *out_n_lights);
