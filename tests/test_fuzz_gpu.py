@@ -46,3 +46,27 @@ def test_rasteriser_cases(oracle):
     for seed in [10008, 10019, 10053, 10072, 10106] + list(range(90_000, 90_030)):
         desc, err = fuzz_raster.run_case(oracle, seed)
         assert err is None, (seed, desc, err)
+
+
+def test_single_view_cull_cases(oracle):
+    import fuzz_cull
+    others = []
+    for seed in range(60_000, 60_040):
+        desc, err = fuzz_cull.run_case(oracle, seed, others)
+        assert err is None, (seed, desc, err)
+    for w in others:
+        w.close()
+
+
+def test_sharded_world_cases(oracle):
+    import fuzz_sharded
+    for seed in range(50_000, 50_030):
+        desc, err = fuzz_sharded.run_case(oracle, seed)
+        assert err is None, (seed, desc, err)
+
+
+def test_light_pass_cases(oracle):
+    import fuzz_shading
+    for seed in range(40_000, 40_030):
+        desc, err = fuzz_shading.run_case(oracle, seed)
+        assert err is None, (seed, desc, err)
