@@ -161,6 +161,11 @@ double timeFrames(Scene &s, RenderView &view, int frames, size_t *shadowViews, s
 
 int main(int argc, char **argv) {
     const size_t numEntities = argc > 1 ? strtoul(argv[1], nullptr, 10) : 20000;
+    /* a second argument reseeds the scenario and widens it: light ranges down to centimetres (at or below the shadow
+     * views' near plane the reference's face frusta open outwards, render_light.cc:319) */
+    const bool wild = argc > 2;
+    if (wild)
+        rng.seed((unsigned)strtoul(argv[2], nullptr, 10));
     oref_shim_init();
     Scene ref, gpu;
     ref.world.reset(new SimpleRenderWorld);
@@ -185,7 +190,7 @@ int main(int argc, char **argv) {
     for (size_t i = 0; i < 24; i++) {
         RenderLight::Type type = types[i % 6];
         glm::vec3 pos(uni(-40, 40), uni(-40, 40), uni(-40, 40)), dir(uni(-1, 1), uni(-1, 1), uni(-1, 1)), col(uni(0, 1), uni(0, 1), uni(0, 1));
-        float intensity = (i == 7) ? 0.0f : uni(0.1f, 2), range = uni(5, 60), cutoff = uni(5, 45);
+        float intensity = (i == 7) ? 0.0f : uni(0.1f, 2), range = (wild && rng() % 3 == 0) ? uni(0.02f, 0.3f) : uni(5, 60), cutoff = uni(5, 45);
         uint32_t flags = (i % 3) ? RenderLight::kCastsShadows : 0;
         for (Scene *s : { &ref, &gpu }) {
             std::unique_ptr<RenderLight> l(new RenderLight(type));
@@ -253,7 +258,7 @@ int main(int argc, char **argv) {
     compareWorlds(ref, gpu, view, "after respawns");
 
     for (size_t i = 0; i < ref.lights.size(); i += 3) {        /* setters that do NOT notify the world */
-        float range = uni(5, 80);
+        float range = (wild && rng() % 3 == 0) ? uni(0.02f, 0.3f) : uni(5, 80);
         glm::vec3 col = (i == 6) ? glm::vec3(0.0f) : glm::vec3(1.0f);
         for (Scene *s : { &ref, &gpu }) {
             s->lights[i]->setRange(range);

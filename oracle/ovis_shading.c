@@ -62,7 +62,9 @@ static float shadow_lookup_2d(const float *map, int size, float u, float v, floa
     float x = u * (float)size - 0.5f, y = v * (float)size - 0.5f;
     float fx0 = floorf(x), fy0 = floorf(y);
     float wx = x - fx0, wy = y - fy0;
-    int x0 = (int)fx0, y0 = (int)fy0, x1 = x0 + 1, y1 = y0 + 1;
+    /* clamp to edge, in float before the conversion (a float beyond int's range converts to anything in C, and x0 + 1
+     * could overflow): far to the right is the right edge, NaN the left one (its weights are NaN anyway) */
+    int x0 = (int)fminf(fmaxf(fx0, -1.0f), (float)size), y0 = (int)fminf(fmaxf(fy0, -1.0f), (float)size), x1 = x0 + 1, y1 = y0 + 1;
     if (x0 < 0) x0 = 0; if (x0 > size - 1) x0 = size - 1;
     if (x1 < 0) x1 = 0; if (x1 > size - 1) x1 = size - 1;
     if (y0 < 0) y0 = 0; if (y0 > size - 1) y0 = size - 1;

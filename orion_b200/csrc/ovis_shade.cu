@@ -55,7 +55,10 @@ __device__ __forceinline__ float shadow_lookup_2d(const float *__restrict__ map,
     const float x = u * (float)size - 0.5f, y = v * (float)size - 0.5f;
     const float fx0 = floorf(x), fy0 = floorf(y);
     const float wx = x - fx0, wy = y - fy0;
-    int x0 = (int)fx0, y0 = (int)fy0, x1 = x0 + 1, y1 = y0 + 1;
+    // clamp to edge, in float BEFORE the conversion: a coordinate beyond int's range (a light at 1e30, a projective divide
+    // by ~0) converts to INT_MAX, and x0 + 1 is then signed overflow - which the compiler is free to, and did, turn into an
+    // index outside the map. NaN takes the lower edge (fmaxf returns the other operand); its weights are NaN anyway.
+    int x0 = (int)fminf(fmaxf(fx0, -1.0f), (float)size), y0 = (int)fminf(fmaxf(fy0, -1.0f), (float)size), x1 = x0 + 1, y1 = y0 + 1;
     x0 = min(max(x0, 0), size - 1); x1 = min(max(x1, 0), size - 1);
     y0 = min(max(y0, 0), size - 1); y1 = min(max(y1, 0), size - 1);
     const float c00 = ref < __ldg(map + (size_t)y0 * size + x0) ? 1.0f : 0.0f, c10 = ref < __ldg(map + (size_t)y0 * size + x1) ? 1.0f : 0.0f;

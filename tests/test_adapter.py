@@ -43,3 +43,15 @@ def test_cuda_render_world_equals_simple_render_world():
     assert r.returncode == 0, (r.stdout + r.stderr)[-3000:]
     assert "ADAPTER OK" in r.stdout
     assert r.stdout.count("compared") == 7
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n,seed", [(1, 11), (7, 12), (300, 13), (5000, 14), (5000, 15), (60000, 16)])
+def test_cuda_render_world_on_reseeded_scenarios(n, seed):
+    """The same end-to-end comparison on other draws of the scenario, tiny worlds included, with light ranges down to
+    centimetres (shadow views whose far plane lies before their near plane)."""
+    if not os.path.exists(CHECK):
+        pytest.skip("oracle/_ref/adapter_check not built (needs /root/reference at build time)")
+    r = subprocess.run([CHECK, str(n), str(seed)], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, (r.stdout + r.stderr)[-3000:]
+    assert "ADAPTER OK" in r.stdout
