@@ -411,7 +411,10 @@ int ovis_entity_set_pass_counts(OvisWorld *world, int64_t n, const uint32_t *ids
  * pair, readable through ovis_get_draw_counts) always receive the full draw counts, so a caller can
  * detect the overflow and retry. If the device count turns out larger than max_visible (the bound was wrong) only the
  * first max_visible entries, rounded up to 1024, are expanded and both counts read 0xffffffff. Never allocates after the
- * world's arrays exist. */
+ * world's arrays exist.
+ * Ids in a caller's device list that do not name a slot of this world (stale after ovis_world_compact, another shard's)
+ * index nothing: here they expand to no draw, ovis_pack_entity_uniforms_device / ovis_pack_light_uniforms_device write
+ * a zero block for them, ovis_shade_deferred_device skips such a light, the rasteriser such an entity. */
 int ovis_build_draw_lists_device(OvisWorld *world, const uint32_t *d_visible, const uint32_t *d_visible_count, int64_t max_visible,
                                  int32_t mode, OvisDraw *d_draws0, int64_t capacity0, OvisDraw *d_draws1, int64_t capacity1,
                                  uint32_t *d_draw_counts);

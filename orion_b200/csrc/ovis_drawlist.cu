@@ -23,8 +23,10 @@ constexpr int kDrawSingleLaunchTiles = 2;    // measured: re-counting more than 
 
 __device__ __forceinline__ void draw_counts(const DrawArgs &a, uint32_t id, uint32_t &c0, uint32_t &c1) {
     const uint32_t slot = id - a.id_base;
-    const uint32_t pc = a.pass_counts[slot];
     c0 = c1 = 0;
+    if (slot >= a.n_slots)                                   // not an id of this world (stale after a compaction, another shard's)
+        return;
+    const uint32_t pc = a.pass_counts[slot];
     if (a.mode == 0) {
         const uint32_t deferred = pc & 0xffu, basic = (pc >> 8) & 0xffu;
         if (deferred > 0) c0 = deferred;                     // deferred_render_pipeline.cc:322-323
@@ -181,6 +183,11 @@ entity_uniforms_kernel(const __grid_constant__ UniformArgs a) {
     if (i >= m || i >= a.capacity)
         return;
     const uint32_t slot = a.d_visible[i] - a.id_base;
+    float4 *out = reinterpret_cast<float4 *>(a.d_out + 20 * i);
+    if (slot >= a.n_slots) {                                 // not an id of this world: a zero block, no table is read
+        out[0] = out[1] = out[2] = out[3] = out[4] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        return;
+    }
     const uint32_t node = a.entity_node[slot];
     DTrs t = { { 0.0f, 0.0f, 0.0f }, { 1.0f, 0.0f, 0.0f, 0.0f }, { 1.0f, 1.0f, 1.0f } };   // Transform() of an entity never moved
     if (node != kNone) {
@@ -191,7 +198,6 @@ entity_uniforms_kernel(const __grid_constant__ UniformArgs a) {
         t.s = { b[7 * st + node], b[8 * st + node], b[9 * st + node] };
     }
     const DMat4 mtx = trs_matrix(t);                           // Transform::matrix(), render_entity.cc:68
-    float4 *out = reinterpret_cast<float4 *>(a.d_out + 20 * i);
     out[0] = make_float4(mtx.c[0].x, mtx.c[0].y, mtx.c[0].z, mtx.c[0].w);
     out[1] = make_float4(mtx.c[1].x, mtx.c[1].y, mtx.c[1].z, mtx.c[1].w);
     out[2] = make_float4(mtx.c[2].x, mtx.c[2].y, mtx.c[2].z, mtx.c[2].w);
@@ -206,22 +212,24 @@ void launch_entity_uniforms(const UniformArgs &a, int64_t max_visible, cudaStrea
 
 // LightUniforms of the visible lights, in list order: 208-byte blocks gathered from the per-light table (13 float4 each).
 __global__ void __launch_bounds__(256)
-light_uniforms_kernel(const uint32_t *visible, const uint32_t *visible_count, const float4 *table, float4 *out, int64_t capacity) {
+light_uniforms_kernel(const uint32_t *visible, const uint32_t *visible_count, const float4 *table, uint32_t n_lights, float4 *out,
+                      int64_t capacity) {
     const uint32_t m = *visible_count;
     const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const int64_t i = t / 13;
     const int q = (int)(t - i * 13);
     if (i >= m || i >= capacity)
         return;
-    out[i * 13 + q] = table[(int64_t)visible[i] * 13 + q];
+    const uint32_t id = visible[i];
+    out[i * 13 + q] = id < n_lights ? table[(int64_t)id * 13 + q] : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
 }
 
-void launch_light_uniforms(const uint32_t *d_visible, const uint32_t *d_visible_count, const float *d_table, float *d_out,
-                           int64_t max_visible, int64_t capacity, cudaStream_t s) {
+void launch_light_uniforms(const uint32_t *d_visible, const uint32_t *d_visible_count, const float *d_table, uint32_t n_lights,
+                           float *d_out, int64_t max_visible, int64_t capacity, cudaStream_t s) {
     const int64_t threads = std::min(max_visible, capacity) * 13;
     if (threads > 0)
         light_uniforms_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, s>>>(
-            d_visible, d_visible_count, reinterpret_cast<const float4 *>(d_table), reinterpret_cast<float4 *>(d_out), capacity);
+            d_visible, d_visible_count, reinterpret_cast<const float4 *>(d_table), n_lights, reinterpret_cast<float4 *>(d_out), capacity);
 }
 
 }  // namespace ovis

@@ -190,6 +190,7 @@ struct DrawArgs {
     const uint32_t *d_visible;       // ids (slot + id_base), list order
     const uint32_t *d_visible_count; // device count
     uint32_t id_base;
+    uint32_t n_slots;                // ids outside [id_base, id_base + n_slots) expand to nothing (a stale id must not index the tables)
     const uint32_t *pass_counts;     // per slot: numPasses deferred | basic << 8 | shadow caster << 16
     const uint32_t *caster_mask;     // alive & castsShadow bits (mode 1)
     int mode;                        // 0 = prepareEntities (two lists), 1 = shadow-caster list
@@ -203,6 +204,7 @@ struct UniformArgs {
     const uint32_t *d_visible;
     const uint32_t *d_visible_count;
     uint32_t id_base;
+    uint32_t n_slots;                // an id outside [id_base, id_base + n_slots) gets a zero block
     const uint32_t *entity_node;     // per slot: node the entity follows, or kNone
     const float *world_trs;          // 10 x nstride
     int64_t nstride;
@@ -212,8 +214,8 @@ struct UniformArgs {
 
 int launch_draw_lists(const DrawArgs &a, int64_t max_visible, cudaStream_t s);   // returns the launches made
 void launch_entity_uniforms(const UniformArgs &a, int64_t max_visible, cudaStream_t s);
-void launch_light_uniforms(const uint32_t *d_visible, const uint32_t *d_visible_count, const float *d_table, float *d_out,
-                           int64_t max_visible, int64_t capacity, cudaStream_t s);
+void launch_light_uniforms(const uint32_t *d_visible, const uint32_t *d_visible_count, const float *d_table, uint32_t n_lights,
+                           float *d_out, int64_t max_visible, int64_t capacity, cudaStream_t s);
 
 // ---- deferred shading over headless buffers (section 8(f) row 4) ----------------------------------------------------
 struct ShadeArgs {
@@ -224,6 +226,7 @@ struct ShadeArgs {
     const uint32_t *d_visible;                     // light ids, list order
     const uint32_t *d_visible_count;
     int64_t max_visible;
+    uint32_t n_lights;                             // light slots: an id beyond them is skipped
     const float *light_table;                      // 52 floats per light slot
     const int32_t *light_types;                    // OVIS_LIGHT_* per light slot, | kLightSkippable
     const float *const *shadow_maps;               // per light slot: depth image or NULL; NULL = no shadows at all

@@ -275,11 +275,11 @@ shade_deferred_kernel(const __grid_constant__ ShadeArgs a) {
         const int n = (int)min((uint32_t)kShadeChunk, m - base);
         __syncthreads();                                          // the previous chunk has been consumed
         for (int i = tid; i < n * L_FLOATS; i += blockDim.x) {
-            const uint32_t id = a.d_visible[base + i / L_FLOATS];
+            const uint32_t id = min(a.d_visible[base + i / L_FLOATS], a.n_lights - 1u);     // (an id beyond the table: skipped below)
             s_light[i] = __ldg(a.light_table + (size_t)id * L_FLOATS + i % L_FLOATS);
         }
         if (tid < n) {
-            const uint32_t id = a.d_visible[base + tid];
+            const uint32_t listed = a.d_visible[base + tid], id = min(listed, a.n_lights - 1u);
             // every load is issued before any of them is used: one memory round trip, not a chain of them
             const float *light = a.light_table + (size_t)id * L_FLOATS;
             const int packed_type = __ldg(a.light_types + id);
@@ -296,7 +296,7 @@ shade_deferred_kernel(const __grid_constant__ ShadeArgs a) {
             const float g2 = fmaxf(fmaxf(s_box[0][2] - p2, p2 - s_box[0][5]), 0.0f);
             const float d2 = g0 * g0 + g1 * g1 + g2 * g2;
             const bool allowed = s_tile_clean && (packed_type & kLightSkippable) && !((packed_type & 0xff) == OVIS_LIGHT_SPOT && map);
-            s_skip[tid] = (allowed && (r < 0.0f || d2 > r * r * 1.001f)) ? 1 : 0;
+            s_skip[tid] = (listed >= a.n_lights || (allowed && (r < 0.0f || d2 > r * r * 1.001f))) ? 1 : 0;   // not a light of this world: nothing
         }
         __syncthreads();
         if (active)

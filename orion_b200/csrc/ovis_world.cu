@@ -2580,6 +2580,7 @@ int ovis_build_draw_lists_device(OvisWorld *w, const uint32_t *d_visible, const 
     a.d_visible = d_visible;
     a.d_visible_count = d_visible_count;
     a.id_base = w->id_base;
+    a.n_slots = (uint32_t)w->n_ent;
     a.pass_counts = w->d_pass_counts;
     a.caster_mask = w->d_caster_bits;
     a.mode = mode;
@@ -2611,7 +2612,8 @@ int ovis_pack_light_uniforms_device(OvisWorld *w, const uint32_t *d_visible, con
     if (max_visible < 0 || max_visible > n_lights)
         max_visible = n_lights;
     if (n_lights > 0 && std::min(max_visible, capacity) > 0) {
-        ovis::launch_light_uniforms(d_visible, d_visible_count, w->d_light_uniforms, d_uniforms, max_visible, capacity, w->stream);
+        ovis::launch_light_uniforms(d_visible, d_visible_count, w->d_light_uniforms, (uint32_t)n_lights, d_uniforms, max_visible, capacity,
+                                    w->stream);
         w->launches++;
     }
     OVIS_CUDA(cudaGetLastError());
@@ -2653,6 +2655,7 @@ int ovis_shade_deferred_device(OvisWorld *w, const OvisGBuffer *g, const void *d
     a.d_visible = d_visible;
     a.d_visible_count = d_visible_count;
     a.max_visible = n_lights > 0 ? max_visible : 0;              // no lights: the count word is 0 anyway
+    a.n_lights = (uint32_t)n_lights;
     a.light_table = w->d_light_uniforms;
     a.light_types = w->d_light_types;
     a.shadow_maps = d_shadow_maps;
@@ -2728,6 +2731,7 @@ int ovis_pack_entity_uniforms_device(OvisWorld *w, const uint32_t *d_visible, co
     a.d_visible = d_visible;
     a.d_visible_count = d_visible_count;
     a.id_base = w->id_base;
+    a.n_slots = (uint32_t)w->n_ent;
     a.entity_node = w->d_entity_node;
     a.world_trs = w->d_world_trs;
     a.nstride = w->cap_nodes;

@@ -298,3 +298,30 @@ def test_draw_lists_with_an_undersized_bound_say_so(oracle):
         else:
             assert int(c[0]) == 0xffffffff and int(c[1]) == 0xffffffff
     w.close()
+
+
+def test_ids_that_name_no_slot_index_nothing(oracle):
+    """A caller's device list may hold ids that are no longer (or never were) slots of this world - stale after a
+    compaction, another shard's. The consumers must not index their tables with them: no draws, zero blocks, no light."""
+    import torch
+    rng = np.random.default_rng(61)
+    n = 5000
+    w, boxes, flags, pc = _static_world(rng, n)
+    lights = util.random_lights(rng, 30, extent=60.0)
+    w.add_lights(lights)
+    good = rng.choice(n, 700, replace=False).astype(np.uint32)
+    wild = np.array([n, n + 1, 2**31, 2**32 - 1, 123456789], dtype=np.uint32)
+    mixed = np.concatenate([good[:300], wild[:2], good[300:], wild[2:]])
+    for mode in (lib.DRAWS_MAIN, lib.DRAWS_SHADOW):
+        e0, e1 = oracle.draw_lists(good, pc, flags, mode)
+        d0, d1, counts = util.gpu_draw_lists(w, mode, visible=mixed)
+        assert counts == (len(e0), len(e1)) and np.array_equal(d0, e0) and np.array_equal(d1, e1)
+    blocks = util.gpu_entity_uniforms(w, mixed)
+    is_wild = np.isin(mixed, wild)
+    assert np.all(blocks[is_wild] == 0.0)
+    assert same(blocks[~is_wild], oracle.entity_uniforms(np.tile(np.array([0, 0, 0, 1, 0, 0, 0, 1, 1, 1], np.float32), (len(good), 1))))
+    l_mixed = np.array([3, 30, 7, 2**32 - 1, 29], dtype=np.uint32)
+    lb = util.gpu_light_uniforms(w, l_mixed)
+    assert np.all(lb[[1, 3]] == 0)
+    assert np.array_equal(lb[[0, 2, 4]], util.gpu_light_uniforms(w, np.array([3, 7, 29], dtype=np.uint32)))
+    w.close()

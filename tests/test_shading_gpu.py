@@ -269,3 +269,21 @@ def test_coherent_scene_tile_rejection(oracle):
     assert np.array_equal(np.isnan(got), np.isnan(want))
     _close(got, want)
     world.close()
+
+
+def test_light_ids_that_name_no_light_are_skipped(oracle):
+    import torch
+    rng = np.random.default_rng(99)
+    w, h = 64, 40
+    view, gbuf, lights, blocks, world = _scene(rng, oracle, w, h, 20)
+    vb = oracle.view_uniforms(view)
+    good = np.array([4, 0, 19, 7], dtype=np.uint32)
+    mixed = np.array([4, 20, 0, 2**32 - 1, 19, 7, 12345], dtype=np.uint32)
+    want = oracle.shade_deferred(*gbuf, vb, blocks[good], lights["type"][good])
+    _close(_shade(torch, world, w, h, gbuf, vb, mixed), want)
+    size = 8
+    maps = [rng.uniform(0.0, 1.0, (size, size) if l["type"] == scenes.LIGHT_SPOT else (6, size, size)).astype(np.float32)
+            if (l["flags"] & 1 and l["type"] >= scenes.LIGHT_POINT) else None for l in lights]
+    want = oracle.shade_deferred(*gbuf, vb, blocks[good], lights["type"][good], [maps[i] for i in good], size)
+    _close(_shade(torch, world, w, h, gbuf, vb, mixed, maps, size), want)
+    world.close()
