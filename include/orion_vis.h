@@ -117,6 +117,10 @@ int ovis_world_compact(OvisWorld *world, int64_t cap_remap, uint32_t *out_remap,
  * (ovis_entity_set_transforms / ovis_node_bind_entities) or explicit bounds (ovis_entity_set_world_aabbs);
  * until then its world AABB is its local AABB (identity transform, Transform::Transform() transform.h:64-70). */
 int ovis_entity_add(OvisWorld *world, int64_t n, const float *local_aabb, const uint32_t *flags, uint32_t *out_first_id);
+/* The batched setters below (and ovis_node_set_local_trs) check EVERY id before they change anything: one id that names
+ * no live entity refuses the whole call. A batch is a parallel scatter on the device: each id should occur once in it; if
+ * an id is repeated, one of its values is stored, unspecified which (the reference's one-setter-call-at-a-time order has
+ * no counterpart inside a batch - callers that coalesce a frame's changes, like the adapter, keep the last one). */
 /* RenderEntity::~RenderEntity -> setWorld(nullptr) -> removeEntity (render_entity.cc:46-60;
  * simple_render_world.cc:65-67): survivors keep their relative order. */
 int ovis_entity_remove(OvisWorld *world, int64_t n, const uint32_t *ids);

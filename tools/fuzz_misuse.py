@@ -22,8 +22,11 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 
 def wild_ids(rng, n, k):
-    """k ids of which about half are wrong in some way."""
-    good = rng.integers(0, max(n, 1), k).astype(np.int64)
+    """k ids of which about half are wrong in some way; the right ones are distinct (a batch is a parallel scatter: a
+    repeated id stores one of its values, unspecified which)."""
+    good = rng.permutation(max(n, 1))[np.arange(k) % max(n, 1)].astype(np.int64) if k <= max(n, 1) else rng.integers(0, max(n, 1), k).astype(np.int64)
+    if k > max(n, 1):
+        good[max(n, 1):] = n                                   # more ids than entities: the surplus is wrong
     bad = rng.choice(np.array([n, n + 1, n + 1000, 2**31 - 1, 2**31, 2**32 - 1], dtype=np.int64), k)
     return np.where(rng.random(k) < 0.5, good, bad).astype(np.uint32)
 
