@@ -46,6 +46,9 @@ def test_rasteriser_cases(oracle):
     for seed in [10008, 10019, 10053, 10072, 10106] + list(range(90_000, 90_030)):
         desc, err = fuzz_raster.run_case(oracle, seed)
         assert err is None, (seed, desc, err)
+    for seed in range(91_000, 91_015):                      # textured and normal-mapped materials
+        desc, err = fuzz_raster.run_textured_case(oracle, seed)
+        assert err is None, (seed, desc, err)
 
 
 def test_single_view_cull_cases(oracle):

@@ -37,6 +37,91 @@ def cube_mesh():
     return np.array(pos, np.float32), np.array(nrm, np.float32), np.array(idx, np.uint32)
 
 
+def run_textured_case(oracle, seed):
+    """The TEXTURED / NORMALMAP variants: random texture sizes (1 x 1 and non-square included), sRGB or linear, repeat or
+    clamp, texture coordinates far outside [0, 1], all eight keyword combinations, generated or random tangents."""
+    import torch
+    rng = np.random.default_rng(seed)
+    meshes = []
+    cp, cn, ci = cube_mesh()
+    meshes.append((cp, cn, ci, (rng.uniform(-3, 3, (len(cp), 2)) * float(rng.choice([1.0, 40.0]))).astype(np.float32)))
+    for _ in range(int(rng.integers(0, 3))):
+        p_, n_, i_ = soup_mesh(rng)
+        uv = rng.uniform(-2, 2, (len(p_), 2)).astype(np.float32)
+        if rng.random() < 0.3:
+            uv[:] = uv[0]                                           # degenerate mapping: the tangent generator divides by ~0
+        meshes.append((p_, n_, i_, uv))
+    tangents = []
+    for p_, n_, i_, uv in meshes:
+        if rng.random() < 0.6:
+            t = lib.mesh_tangents(p_, n_, uv, i_)
+            t = np.nan_to_num(t, nan=0.0, posinf=1.0, neginf=-1.0).astype(np.float32)      # (NaN payloads differ between CPU and GPU)
+        else:
+            t = np.concatenate([rng.normal(size=(len(p_), 3)), rng.choice([-1.0, 1.0], (len(p_), 1))], axis=1).astype(np.float32)
+        tangents.append(t)
+    textures = []
+    for _ in range(int(rng.integers(2, 5))):
+        tw, th = int(rng.choice([1, 2, 3, 8, 17, 64])), int(rng.choice([1, 2, 5, 8, 33]))
+        textures.append((rng.integers(0, 256, (th, tw, 4), dtype=np.uint8), bool(rng.random() < 0.5), bool(rng.random() < 0.5)))
+    n = int(rng.choice([1, 6, 40]))
+    spread = float(rng.choice([2.0, 8.0]))
+    trs = np.zeros((n, 10), dtype=np.float32)
+    trs[:, 0:3] = rng.uniform(-spread, spread, (n, 3))
+    trs[:, 3:7] = scenes.random_unit_quats(rng, n)
+    trs[:, 7:10] = rng.uniform(0.5, 4.0, (n, 3)) * rng.choice([-1.0, 1.0], (n, 3))
+    mesh_of = rng.integers(0, len(meshes), n).astype(np.uint32)
+    width, height = [(1, 1), (16, 16), (33, 17), (160, 90), (97, 131)][int(rng.integers(0, 5))]
+    view = scenes.make_view((0, 0.2 * spread, 2.5 * spread + 2.0), scenes.quat_yaw_pitch(float(rng.uniform(-15, 15)), float(rng.uniform(-15, 5))),
+                            float(rng.uniform(40, 100)), 0.1, 40.0 * spread + 10, width, height)
+    w = lib.World(0)
+    e0 = w.add_entities(np.tile(np.array([[-1, -1, -1, 1, 1, 1]], np.float32), (n, 1)))
+    ids = np.arange(e0, e0 + n, dtype=np.uint32)
+    w.set_transforms(ids, trs)
+    r = lib.Raster(w)
+    mids = np.array([r.add_mesh(p_, n_, i_, uv) for p_, n_, i_, uv in meshes], dtype=np.uint32)
+    for m, t in zip(mids, tangents):
+        r.set_mesh_tangents(int(m), t)
+    tids = [r.add_texture(*t) for t in textures]
+    n_mat = 8
+    mat_rows = []
+    for flags in range(n_mat):
+        d, sp, sh = rng.uniform(0, 1, 3), rng.uniform(0, 1, 3), float(rng.uniform(1, 64))
+        t0, t1 = int(rng.choice(tids)), int(rng.choice(tids))
+        r.add_material(d, sp, sh, flags, t0, t1)
+        mat_rows.append(list(d) + list(sp) + [sh, flags, t0, t1])
+    mat_of = rng.integers(0, n_mat, n).astype(np.uint32)
+    r.bind_entities(ids, mids[mesh_of], mat_of)
+    order = rng.permutation(n).astype(np.int32)
+    d_list = torch.tensor(np.concatenate([[n], order]).astype(np.int32), device="cuda")
+    a, b, c = (torch.full((height, width, 4), -1.0, dtype=torch.float32, device="cuda") for _ in range(3))
+    depth = torch.full((height, width), -1.0, dtype=torch.float32, device="cuda")
+    r.gbuffer(view, d_list.data_ptr() + 4, d_list.data_ptr(), width, height, a.data_ptr(), b.data_ptr(), c.data_ptr(), depth.data_ptr())
+    torch.cuda.synchronize()
+    vertices = np.concatenate([np.concatenate([p_, n_, uv], axis=1) for p_, n_, i_, uv in meshes])
+    all_tangents = np.concatenate(tangents)
+    indices = np.concatenate([i_ for _, _, i_, _ in meshes])
+    first_v = np.cumsum([0] + [len(m[0]) for m in meshes])
+    first_i = np.cumsum([0] + [len(m[2]) for m in meshes])
+    mesh_ref = np.array([[first_v[m], first_i[m], len(meshes[m][2]) // 3] for m in range(len(meshes))], dtype=np.int64)
+    sel = order.astype(np.int64)
+    material = np.array(mat_rows, dtype=np.float32)[mat_of[sel]]
+    matrix = oracle.entity_uniforms(trs[sel])[:, :16]
+    ea, eb, ec, ed = oracle.raster_textured(matrix, mesh_ref[mesh_of[sel]], material, vertices, all_tangents, indices, textures,
+                                            oracle.view_matrices(view)[0][2], width, height)
+    desc = dict(textured=True, instances=n, meshes=len(meshes), textures=[list(t[0].shape[:2]) for t in textures], size=[width, height],
+                covered=round(float((ed < 1.0).mean()), 3))
+    r.close()
+    w.close()
+    for name, got, exp in (("depth", depth, ed), ("a", a, ea), ("b", b, eb), ("c", c, ec)):
+        g = got.cpu().numpy()
+        both_nan = np.isnan(g) & np.isnan(exp)                      # a zero tangent normalises to NaN on both sides; payloads differ
+        bad = (g.view(np.uint32) != exp.view(np.uint32)) & ~both_nan
+        if bad.any():
+            where = np.argwhere(bad)[0]
+            return desc, f"textured G-buffer target {name}: {int(bad.sum())} words differ, first at {where.tolist()}: {g[tuple(where)]!r} vs {exp[tuple(where)]!r}"
+    return desc, None
+
+
 def soup_mesh(rng):
     nv = int(rng.integers(3, 60))
     nt = int(rng.integers(1, 80))
@@ -154,7 +239,7 @@ def main():
     t0 = time.time()
     done, failures, pixels = 0, [], 0
     for s in seeds:
-        desc, err = run_case(oracle, s)
+        desc, err = run_textured_case(oracle, s) if s % 3 == 2 else run_case(oracle, s)      # every third case: textured materials
         done += 1
         print(s, json.dumps(desc), "FAIL: " + err if err else "ok", flush=True)
         if err:
