@@ -257,24 +257,50 @@ class ShardedWorld:
         self.frame = 0
         self._pinned = None
         self._last_max = 0
+        self.generation = 0                                      # symmetric blocks opened so far (p2p): > 1 after a regrow
         if exchange == "p2p" and world_size > 1:
-            cap = int(min(n_local, p2p_capacity or max(1024, n_local // 8)))
-            opened = open_symmetric_blocks(world_size, cap, group)
-            if opened is not None:
-                self.sym_tensors, self.sym_handles, self.sym_flags, self.flag_handle = opened
-                self.exchange_mode = "p2p"
-                self.capacity = cap
-                seg = (cap + 1) * 4
-                # destination 0 is this rank's own copy; the rest are the peers' copies of segment `rank`
-                order = [rank] + [p for p in range(world_size) if p != rank]
-                self.p2p_out, self.p2p_cnt = [], []
-                for h in self.sym_handles:
-                    ptrs = [int(h.buffer_ptrs[p]) + rank * seg for p in order]
-                    self.p2p_cnt.append(ptrs)
-                    self.p2p_out.append([q + 4 for q in ptrs])
-                self.flag_local = int(self.flag_handle.buffer_ptrs[rank])
-                self.flag_signal = [int(self.flag_handle.buffer_ptrs[p]) + rank * 4 for p in order]
-                self.plans = [world.exchange_plan(self.p2p_out[k], self.p2p_cnt[k], self.flag_signal) for k in range(P2P_BUFFERS)]
+            self._open_p2p(int(min(max(n_local, 1), p2p_capacity or max(1024, n_local // 8))))
+
+    def _open_p2p(self, cap: int) -> bool:
+        """(Re)open the symmetric segment buffers with room for `cap` ids per shard. Collective: every rank calls it at
+        the same frame - they all see the same counts, so they all take the same decision."""
+        opened = open_symmetric_blocks(self.size, cap, self.group)
+        if opened is None:
+            return False
+        rank, world_size, world = self.rank, self.size, self.world
+        self.sym_tensors, self.sym_handles, self.sym_flags, self.flag_handle = opened
+        self.exchange_mode = "p2p"
+        self.capacity = cap
+        self.frame = 0                                           # the new flag words start at 0: frames are numbered afresh
+        self.generation += 1
+        self._pinned = None
+        seg = (cap + 1) * 4
+        # destination 0 is this rank's own copy; the rest are the peers' copies of segment `rank`
+        order = [rank] + [p for p in range(world_size) if p != rank]
+        self.p2p_out, self.p2p_cnt = [], []
+        for h in self.sym_handles:
+            ptrs = [int(h.buffer_ptrs[p]) + rank * seg for p in order]
+            self.p2p_cnt.append(ptrs)
+            self.p2p_out.append([q + 4 for q in ptrs])
+        self.flag_local = int(self.flag_handle.buffer_ptrs[rank])
+        self.flag_signal = [int(self.flag_handle.buffer_ptrs[p]) + rank * 4 for p in order]
+        self.plans = [world.exchange_plan(self.p2p_out[k], self.p2p_cnt[k], self.flag_signal) for k in range(P2P_BUFFERS)]
+        return True
+
+    def _regrow_p2p(self, top: int):
+        """Some shard's list did not fit its segment (the kernels cut the ids at the capacity but deliver the full count, to
+        every rank alike). Every rank has waited for every flag of that frame, so nobody is still storing into anybody's
+        old buffers; all move to larger ones and the frame is redone."""
+        self.stream.synchronize()
+        old = (self.sym_tensors, self.sym_handles, self.sym_flags, self.flag_handle)
+        cap = int(min(max(self.n_local_max(), 1), top + top // 4 + 1024))
+        if not self._open_p2p(max(cap, top)):
+            raise RuntimeError("symmetric memory could not be reopened for a larger segment")
+        del old
+
+    def n_local_max(self) -> int:
+        """The largest shard's size (segments are equally sized on every rank): shards differ by at most one entity."""
+        return self.n_local + 1
 
     def resize(self, capacity: int):
         self.capacity = int(min(max(capacity, 1), self.n_local))
@@ -324,8 +350,9 @@ class ShardedWorld:
             self.world.read_segments_host(blocks.data_ptr(), words, self.size, self._pinned.array, self.flag_local, self.frame)
             counts = host[:, 0].astype(np.int64)
             top = int(counts.max(initial=0))
-            if top > self.capacity:
-                raise RuntimeError(f"visible list of {top} ids exceeds the symmetric segment capacity {self.capacity}")
+            if top > self.capacity:                              # every rank reads the same counts: all regrow, all redo
+                self._regrow_p2p(top)
+                return self.cull_to_host(planes, require)
             return [host[r, 1:1 + int(counts[r])] for r in range(self.size)]
         spec = int(min(self.capacity, self._last_max + self._last_max // 4 + 256))
         if self._pinned is None or self._pinned.shape[1] < words:
@@ -364,6 +391,6 @@ class ShardedWorld:
             if counts.max(initial=0) <= self.capacity:
                 return blocks, counts
             if self.exchange_mode == "p2p":
-                raise RuntimeError(f"visible list of {int(counts.max())} ids exceeds the symmetric segment capacity "
-                                   f"{self.capacity}; create the ShardedWorld with a larger p2p_capacity")
+                self._regrow_p2p(int(counts.max()))
+                continue
             self.resize(int(counts.max() * 1.25) + 1024)

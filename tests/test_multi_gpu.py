@@ -72,6 +72,25 @@ for mode in ("nccl", "p2p"):
         assert seg.generation >= 1
         dist.barrier()
         seg.close()
+    if mode == "p2p":
+        # segments far too small for the lists: every rank sees the same counts, all reopen larger symmetric buffers at the
+        # same frame and redo it - through the device-consumer call and through the host one, several times over
+        for first_call in ("cull", "cull_to_host"):
+            w2 = lib.World(rank)
+            f2 = w2.add_entities(aabb[lo:hi], flags[lo:hi]); w2.set_world_aabbs(f2, aabb[lo:hi])
+            small = ShardedWorld(w2, rank, size, lo, hi - lo, stream=torch.cuda.Stream(), exchange="p2p", p2p_capacity=64)
+            assert small.exchange_mode == "p2p" and small.capacity == 64
+            for i in range(6):
+                planes_i = lib.view_planes(views[i %% 3])
+                if (first_call == "cull") == (i %% 2 == 0):
+                    blocks, counts = small.cull(planes_i)
+                    got = merged_list(blocks, counts)
+                else:
+                    got = np.concatenate(small.cull_to_host(planes_i))
+                assert np.array_equal(got, expected[i %% 3]), (rank, "regrow", first_call, i, len(got), len(expected[i %% 3]))
+            assert small.generation >= 2 and small.capacity >= max(len(e) for e in expected) // size
+            dist.barrier()
+            w2.close()
     dist.barrier()
     w.close()
 if rank == 0:
