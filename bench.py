@@ -281,6 +281,11 @@ def run_ours(args, rank: int, local_rank: int, world_size: int):
         raise SystemExit("bench.py: no CUDA device - the product path has no CPU fallback "
                          "(use --impl reference for the CPU arm)")
     torch.cuda.set_device(local_rank)
+    pinned_cpus = 0
+    if world_size > 1 and os.environ.get("OVIS_BENCH_PIN", "1") != "0":
+        # one process per GPU: keep this rank on its GPU's socket (torchrun places ranks anywhere); before the world and its
+        # page-locked buffers exist, so that they are allocated there too
+        pinned_cpus = lib.pin_thread_near_device(local_rank)
     if world_size > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     peaks = {}
@@ -430,6 +435,9 @@ def run_ours(args, rank: int, local_rank: int, world_size: int):
                          ("gather kernel stores to peers over NVLink + ready flags, no collective" if sw.exchange_mode == "p2p"
                           else "NCCL all-gather")) if world_size > 1 else "1 GPU"),
         "cull_ms_per_frame": elapsed_ms / args.steps,
+        "host_placement": ({"rank0_pinned_to_cpus_next_to_its_gpu": pinned_cpus,
+                            "how": "ovis_host_pin_thread_near_device (PCI local_cpulist); OVIS_BENCH_PIN=0 turns it off"}
+                           if world_size > 1 else None),
         "roofline": {"bound": "hbm", "kernel": "ovis::cull_test_kernel<1,false,5> (dominant: reads every bound once)",
                      "achieved": achieved, "peak": peak_gbs, "unit": "GB/s", "frac": achieved / peak_gbs,
                      "traffic": ncu_traffic_bytes() if n == SHARD_ENTITIES else None,

@@ -643,6 +643,13 @@ int ovis_host_register(void *ptr, int64_t bytes);
 /* Spin until every one of n words in HOST memory is at least `value` (frame counters other processes or GPUs store: the
  * hand-over of per-rank segments in one shared block). OVIS_ERR_CAPACITY after timeout_us microseconds (< 0: never). */
 int ovis_host_flags_wait(const uint32_t *flags, int32_t n, uint32_t value, int64_t timeout_us);
+/* Restrict the calling thread (and the threads it starts afterwards) to the CPUs next to `device`, as the kernel's PCI
+ * topology lists them (/sys/bus/pci/devices/.../local_cpulist), within the CPUs it may already use. A frame is a launch,
+ * a few stores across PCIe and a poll of host memory: from the far socket each of those is slower. out_cpus (optional)
+ * receives the number of CPUs pinned to, 0 when nothing was changed (no topology files, a cpuset that excludes them).
+ * The worker threads of ovis_sharded_create do this for their devices (OVIS_PIN_WORKERS=0 turns it off); a process that
+ * holds one shard calls it once, before it creates its world. No counterpart in the reference. */
+int ovis_host_pin_thread_near_device(int32_t device, int32_t *out_cpus);
 int ovis_host_unregister(void *ptr);
 
 /* Profiling hook (no counterpart in the reference, whose cull path has no timers - SURVEY.md section 5):

@@ -162,6 +162,9 @@ void many_views_job(OvisShardedWorld *sw, int r) {
 
 void worker_loop(OvisShardedWorld *sw, int r) {
     cudaSetDevice(sw->devices[r]);
+    const char *pin = getenv("OVIS_PIN_WORKERS");
+    if (!pin || atoi(pin) != 0)
+        ovis_host_pin_thread_near_device(sw->devices[r], nullptr);   // launches, PCIe stores and the host poll stay on the GPU's socket
     Worker &me = sw->workers[r];
     uint64_t seen = 0;
     while (true) {

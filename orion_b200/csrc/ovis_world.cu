@@ -10,6 +10,8 @@
 #include <algorithm>
 #include <atomic>
 #include <chrono>
+#include <cctype>
+#include <sched.h>
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
@@ -2789,6 +2791,54 @@ int ovis_host_flags_wait(const uint32_t *flags, int32_t n, uint32_t value, int64
             return fail(OVIS_ERR_CAPACITY, "ovis_host_flags_wait: timed out");
     }
     std::atomic_thread_fence(std::memory_order_acquire);
+    return OVIS_OK;
+}
+
+// The CPUs next to a GPU, from the kernel's own topology files: /sys/bus/pci/devices/<domain:bus:device.function>/local_cpulist
+// ("0-31,64-95"). Only CPUs the calling thread is already allowed to run on are kept (containers, cpusets).
+int ovis_host_pin_thread_near_device(int32_t device, int32_t *out_cpus) {
+    if (out_cpus)
+        *out_cpus = 0;
+    char bus[32] = {};
+    OVIS_CUDA(cudaDeviceGetPCIBusId(bus, (int)sizeof bus, device));
+    for (char *c = bus; *c; c++)
+        *c = (char)std::tolower((unsigned char)*c);
+    const std::string path = std::string("/sys/bus/pci/devices/") + bus + "/local_cpulist";
+    FILE *f = std::fopen(path.c_str(), "r");
+    if (!f)
+        return OVIS_OK;                                          // no topology information: leave the thread where it is
+    char line[4096] = {};
+    const bool got = std::fgets(line, (int)sizeof line, f) != nullptr;
+    std::fclose(f);
+    if (!got)
+        return OVIS_OK;
+    cpu_set_t allowed, wanted;
+    CPU_ZERO(&allowed);
+    CPU_ZERO(&wanted);
+    if (sched_getaffinity(0, sizeof allowed, &allowed) != 0)
+        return OVIS_OK;
+    int n = 0;
+    for (const char *p = line; *p;) {
+        char *end = nullptr;
+        const long a = std::strtol(p, &end, 10);
+        if (end == p)
+            break;
+        long b = a;
+        p = end;
+        if (*p == '-') {
+            b = std::strtol(p + 1, &end, 10);
+            p = end;
+        }
+        for (long c = a; c <= b && c < CPU_SETSIZE; c++)
+            if (c >= 0 && CPU_ISSET((int)c, &allowed)) {
+                CPU_SET((int)c, &wanted);
+                n++;
+            }
+        while (*p == ',' || *p == ' ' || *p == '\n')
+            p++;
+    }
+    if (n > 0 && sched_setaffinity(0, sizeof wanted, &wanted) == 0 && out_cpus)
+        *out_cpus = n;
     return OVIS_OK;
 }
 

@@ -225,6 +225,14 @@ class PinnedBuffer:
             pass
 
 
+def pin_thread_near_device(device: int) -> int:
+    """ovis_host_pin_thread_near_device: keep the calling thread (and those it starts later) on the CPUs next to `device`;
+    returns the number of CPUs pinned to (0: nothing changed)."""
+    n = C.c_int32()
+    _check(load().ovis_host_pin_thread_near_device(C.c_int32(device), C.byref(n)))
+    return n.value
+
+
 def host_register(array: np.ndarray):
     """Page-lock (portable, mapped) memory the caller owns, e.g. a shared-memory segment: ovis_host_register."""
     _check(load().ovis_host_register(C.c_void_p(array.ctypes.data), C.c_int64(array.nbytes)))
