@@ -79,7 +79,10 @@ static void launch_chained(Kernel kernel, dim3 grid, size_t smem, cudaStream_t s
 // Products are packed FMUL2, "sum - d" is a packed subtract, "any distance < 0" is "minimum distance < 0" (fminf ignores a
 // NaN operand exactly as a NaN distance rejects nothing). Planes come with doubled components (plain_planes), so a packed
 // operand is a register pair as loaded. Warp-uniform early-out after the two side planes.
-template <int R>
+// SHARED: the R views have bit-identical left / right / top / bottom planes (a camera and the depth slices of its frustum,
+// "cascades": only near and far differ) - the host says so per run. Those four distances are then computed once and serve
+// all R views: 4 + 2 R plane tests instead of 6 R. Same planes, same P-vertex, same operations: same bits.
+template <int R, bool SHARED>
 __device__ __forceinline__ void test_view_run(const MvArgs &a, int pv, uint32_t codes, const float4 &ax, const float4 &ay, const float4 &az,
                                               const float4 &bx, const float4 &by, const float4 &bz, uint32_t alive, uint32_t caster,
                                               int64_t group, int lane) {
@@ -110,6 +113,8 @@ __device__ __forceinline__ void test_view_run(const MvArgs &a, int pv, uint32_t 
                                      z01 = pack2(pz.x, pz.y), z23 = pack2(pz.z, pz.w);
 #pragma unroll
             for (int r = 0; r < R; r++) {
+                if (SHARED && p < 4 && r > 0)
+                    continue;                                          // (compile time: the loops are unrolled)
                 const float4 dd = plane_dist4_packed(__ldg(pl + 12 * r + 2 * p), __ldg(pl + 12 * r + 2 * p + 1), x01, x23, y01, y23, z01, z23);
                 if (p & 1)
                     lowest[r] = min3_4(lowest[r], held[r], dd);
@@ -120,10 +125,15 @@ __device__ __forceinline__ void test_view_run(const MvArgs &a, int pv, uint32_t 
                 uint32_t left = 0;
 #pragma unroll
                 for (int r = 0; r < R; r++)
-                    left |= keep[r] & ~negative_bits(lowest[r]);
+                    left |= keep[r] & ~negative_bits(lowest[SHARED ? 0 : r]);
                 alive_somewhere = __any_sync(0xffffffffu, left != 0u);
                 if (!alive_somewhere)
                     break;
+            }
+            if (SHARED && p == 3) {
+#pragma unroll
+                for (int r = 1; r < R; r++)
+                    lowest[r] = lowest[0];
             }
         }
     }
@@ -186,13 +196,19 @@ mv_plain_test_kernel(const __grid_constant__ MvArgs a) {
             int run = min((int)((m >> 18) & 7u), pv1 - pv);
             if (run >= 4) {
                 run = 4;
-                test_view_run<4>(a, pv, codes, ax, ay, az, bx, by, bz, alive, caster, group, lane);
+                if (m & kPlainSharedSides4)
+                    test_view_run<4, true>(a, pv, codes, ax, ay, az, bx, by, bz, alive, caster, group, lane);
+                else
+                    test_view_run<4, false>(a, pv, codes, ax, ay, az, bx, by, bz, alive, caster, group, lane);
             } else if (run >= 2) {
                 run = 2;
-                test_view_run<2>(a, pv, codes, ax, ay, az, bx, by, bz, alive, caster, group, lane);
+                if (m & kPlainSharedSides2)
+                    test_view_run<2, true>(a, pv, codes, ax, ay, az, bx, by, bz, alive, caster, group, lane);
+                else
+                    test_view_run<2, false>(a, pv, codes, ax, ay, az, bx, by, bz, alive, caster, group, lane);
             } else {
                 run = 1;
-                test_view_run<1>(a, pv, codes, ax, ay, az, bx, by, bz, alive, caster, group, lane);
+                test_view_run<1, false>(a, pv, codes, ax, ay, az, bx, by, bz, alive, caster, group, lane);
             }
             pv += run;
         }

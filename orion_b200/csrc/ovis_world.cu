@@ -92,6 +92,7 @@ struct OvisWorld {
     int num_sms = 0;
     int forced_variant = -1;              // OVIS_CULL_VARIANT (tuning); -1 = pick by size
     bool fused_small = true;              // OVIS_CULL_FUSED=0 (tuning) keeps small worlds on the two-launch path
+    bool mv_shared_sides = true;          // OVIS_MV_SHARED_SIDES=0 (tuning): views with identical side planes are tested like any others
     bool pdl_levels = true;               // OVIS_PDL_LEVELS=0 (tuning): level kernels of an update launched one after the other
     int64_t fused_below = 512 << 10;      // OVIS_FUSED_BELOW (tuning): worlds with fewer entities take the single cooperative launch
     int blocks_per_sm[16][2] = {};         // cull test kernel occupancy per variant: [unmasked, masked]
@@ -1132,7 +1133,13 @@ int cull_views_grouped(OvisWorld *w, int32_t n_views, const float *planes, const
                 meta[v] = ovis::plane_sign_codes(planes + 24 * (size_t)(v0 + v)) | ((require && require[v0 + v]) ? 0x80000000u : 0u);
             // views with equal P-vertex sign codes next to each other: the kernel tests them in runs (a view's bitmap row
             // is its position in this list, its totals row and CSR list are found through the view id, so any order works)
-            std::stable_sort(plain.begin(), plain.end(), [&](uint32_t x, uint32_t y) { return (meta[x] & 0x3ffffu) < (meta[y] & 0x3ffffu); });
+            // ... and among those, views with bit-identical side planes (the depth slices of one frustum) next to each other:
+            // the kernel computes the four side distances of such a run once
+            auto sides = [&](uint32_t x) { return planes + 24 * (size_t)(v0 + x); };          // planes 0-3: 16 floats
+            std::stable_sort(plain.begin(), plain.end(), [&](uint32_t x, uint32_t y) {
+                const uint32_t cx = meta[x] & 0x3ffffu, cy = meta[y] & 0x3ffffu;
+                return cx != cy ? cx < cy : std::memcmp(sides(x), sides(y), 16 * sizeof(float)) < 0;
+            });
             if (!plain.empty())
                 std::memcpy(hs + off_plain, plain.data(), sizeof(uint32_t) * plain.size());
             if (!cubes.empty())
@@ -1148,7 +1155,18 @@ int cull_views_grouped(OvisWorld *w, int32_t n_views, const float *planes, const
                     uint32_t run = 1;
                     if (k + 1 < np && (meta[plain[k + 1]] & 0x3ffffu) == (m & 0x3ffffu))
                         run = std::min<uint32_t>(4u, ((pm[2 * (k + 1)] >> 18) & 7u) + 1u);
-                    pm[2 * k] = (m & 0x8003ffffu) | (run << 18);
+                    auto same_sides = [&](size_t first, size_t count) {
+                        for (size_t j = 1; j < count; j++)
+                            if (std::memcmp(sides(plain[first]), sides(plain[first + j]), 16 * sizeof(float)) != 0)
+                                return false;
+                        return true;
+                    };
+                    uint32_t shared = 0;
+                    if (w->mv_shared_sides && run >= 2 && same_sides(k, 2))
+                        shared |= ovis::kPlainSharedSides2;
+                    if (w->mv_shared_sides && run >= 4 && same_sides(k, 4))
+                        shared |= ovis::kPlainSharedSides4;
+                    pm[2 * k] = (m & 0x8003ffffu) | (run << 18) | shared;
                     pm[2 * k + 1] = plain[k];
                     const float *src = planes + 24 * (size_t)(v0 + plain[k]);
                     for (int c = 0; c < 24; c++)
@@ -1338,8 +1356,21 @@ int shadow_views_device(OvisWorld *w, const std::vector<uint32_t> &light_ids, in
         // That holds while far > near: a range at or below the shadow views' near plane (0.1) turns the far plane
         // round, the frusta open outwards beyond the range (the reference then lists entities any distance away), and
         // the light is tested without a cube. A NaN range fails the comparison too.
-        const bool bounded = l.type == OVIS_LIGHT_POINT && l.range > ovis::hm::kShadowViewNear;
-        groups.push_back(make_group(bounded ? l.position : nullptr, l.range, (int)list_light.size(), lv.count));
+        bool bounded = l.type == OVIS_LIGHT_POINT && l.range > ovis::hm::kShadowViewNear;
+        // How far the faces really reach is what the reference's own far planes say, not the range: they come out of
+        // far / (near - far) + 1 in float, which for range / near ~ 1e6 keeps three or four bits (a range of 90 000 puts the
+        // far plane anywhere between 84 000 and 100 000), and for larger ratios is 0: no far plane at all. The cube is sized
+        // by the largest distance from the light to one of its six far planes; no cube if one of them is degenerate.
+        float reach = l.range;
+        for (int i = 0; bounded && i < lv.count; i++) {
+            const float *fp = lv.planes + 24 * i + 20;
+            const float far_distance = (fp[0] * l.position[0] + fp[1] * l.position[1] + fp[2] * l.position[2]) - fp[3];
+            if (!(far_distance > 0.0f) || !(far_distance <= 8.0f * l.range))
+                bounded = false;                                   // NaN, behind the light, or nowhere near the range
+            else
+                reach = std::max(reach, far_distance);
+        }
+        groups.push_back(make_group(bounded ? l.position : nullptr, reach, (int)list_light.size(), lv.count));
         planes.insert(planes.end(), lv.planes, lv.planes + 24 * lv.count);
         for (int i = 0; i < lv.count; i++) {
             list_light.push_back((int32_t)id);
@@ -1428,6 +1459,8 @@ int ovis_world_create(int device, OvisWorld **out_world) {
         w->fused_below = atoll(v);
     if (const char *v = getenv("OVIS_PDL_LEVELS"))
         w->pdl_levels = atoi(v) != 0;
+    if (const char *v = getenv("OVIS_MV_SHARED_SIDES"))
+        w->mv_shared_sides = atoi(v) != 0;
     if (const char *v = getenv("OVIS_HOST_FLAG"))
         w->host_flag = atoi(v) != 0;
     if (const char *v = getenv("OVIS_MV_DENSE")) {
