@@ -177,9 +177,10 @@ struct MvResetArgs {              // up to four arrays filled with a word (sizes
 };
 void launch_mv_reset(const MvResetArgs &r, int num_sms, cudaStream_t s);
 constexpr uint32_t kMvOverflowPairs = 1u, kMvOverflowItems = 2u, kMvOverflowNodes = 4u, kMvOverflowHits = 8u;
-// plain_meta.x: P-vertex codes (18 bits) | equal codes that follow, capped at 4 (3 bits) | the two views / the four views
-// starting here have bit-identical side planes (left, right, top, bottom) | ... | the view wants shadow casters only (bit 31)
-constexpr uint32_t kPlainSharedSides2 = 1u << 21, kPlainSharedSides4 = 1u << 22;
+// plain_meta.x: P-vertex codes (18 bits) | equal codes that follow, capped at 4 (3 bits) | how many views starting here
+// have bit-identical side planes (left, right, top, bottom), capped at 7 (3 bits; 0 or 1: none) | ... | the view wants
+// shadow casters only (bit 31)
+constexpr int kPlainSharedShift = 21;
 
 void launch_mv_plain_test(const MvArgs &a, int num_sms, cudaStream_t s);
 void launch_mv_bin_lights(const MvArgs &a, cudaStream_t s);

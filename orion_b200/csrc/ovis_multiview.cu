@@ -79,10 +79,7 @@ static void launch_chained(Kernel kernel, dim3 grid, size_t smem, cudaStream_t s
 // Products are packed FMUL2, "sum - d" is a packed subtract, "any distance < 0" is "minimum distance < 0" (fminf ignores a
 // NaN operand exactly as a NaN distance rejects nothing). Planes come with doubled components (plain_planes), so a packed
 // operand is a register pair as loaded. Warp-uniform early-out after the two side planes.
-// SHARED: the R views have bit-identical left / right / top / bottom planes (a camera and the depth slices of its frustum,
-// "cascades": only near and far differ) - the host says so per run. Those four distances are then computed once and serve
-// all R views: 4 + 2 R plane tests instead of 6 R. Same planes, same P-vertex, same operations: same bits.
-template <int R, bool SHARED>
+template <int R>
 __device__ __forceinline__ void test_view_run(const MvArgs &a, int pv, uint32_t codes, const float4 &ax, const float4 &ay, const float4 &az,
                                               const float4 &bx, const float4 &by, const float4 &bz, uint32_t alive, uint32_t caster,
                                               int64_t group, int lane) {
@@ -113,8 +110,6 @@ __device__ __forceinline__ void test_view_run(const MvArgs &a, int pv, uint32_t 
                                      z01 = pack2(pz.x, pz.y), z23 = pack2(pz.z, pz.w);
 #pragma unroll
             for (int r = 0; r < R; r++) {
-                if (SHARED && p < 4 && r > 0)
-                    continue;                                          // (compile time: the loops are unrolled)
                 const float4 dd = plane_dist4_packed(__ldg(pl + 12 * r + 2 * p), __ldg(pl + 12 * r + 2 * p + 1), x01, x23, y01, y23, z01, z23);
                 if (p & 1)
                     lowest[r] = min3_4(lowest[r], held[r], dd);
@@ -125,16 +120,12 @@ __device__ __forceinline__ void test_view_run(const MvArgs &a, int pv, uint32_t 
                 uint32_t left = 0;
 #pragma unroll
                 for (int r = 0; r < R; r++)
-                    left |= keep[r] & ~negative_bits(lowest[SHARED ? 0 : r]);
+                    left |= keep[r] & ~negative_bits(lowest[r]);
                 alive_somewhere = __any_sync(0xffffffffu, left != 0u);
                 if (!alive_somewhere)
                     break;
             }
-            if (SHARED && p == 3) {
-#pragma unroll
-                for (int r = 1; r < R; r++)
-                    lowest[r] = lowest[0];
-            }
+
         }
     }
     // Results: per view four ballots (ballot j = entity 4 * lane + j of every lane), stored as they are - the dense pass's
@@ -153,6 +144,61 @@ __device__ __forceinline__ void test_view_run(const MvArgs &a, int pv, uint32_t 
             *reinterpret_cast<uint4 *>(a.masks + (int64_t)(pv + r) * num_words + group * 4) = b;
             if (total)
                 atomicAdd(a.totals + (int64_t)view[r] * row + group / kMaskBlockGroups, total);
+        }
+    }
+}
+
+// A run of `count` views (2 .. 7) whose left / right / top / bottom planes are bit-identical - a camera and the depth slices
+// of its frustum ("cascades"): only near and far differ; the host says so per run. The four side distances are computed
+// once and serve every view of the run: 4 + 2 * count plane tests instead of 6 * count, and nothing is held per view, so
+// the run can be longer than four. Same planes, same P-vertex, same operations: same bits.
+__device__ __forceinline__ void test_shared_side_run(const MvArgs &a, int pv, int count, uint32_t codes, const float4 &ax, const float4 &ay,
+                                                     const float4 &az, const float4 &bx, const float4 &by, const float4 &bz, uint32_t alive,
+                                                     uint32_t caster, int64_t group, int lane) {
+    const int64_t num_words = (int64_t)a.num_groups128 * 4;
+    const int row = a.num_blocks + 1;
+    const float4 *__restrict__ pl = a.plain_planes + (int64_t)pv * 12;
+    const float inf = __int_as_float(0x7f800000);
+    float4 side = make_float4(inf, inf, inf, inf), held = side;
+    unsigned long long x01[2], x23[2], y01[2], y23[2], z01[2], z23[2];           // P-vertices of the near and the far plane
+    bool alive_somewhere = __any_sync(0xffffffffu, (alive | caster) != 0u);
+    if (alive_somewhere) {
+#pragma unroll
+        for (int p = 0; p < 6; p++) {
+            const bool sx = (codes >> (3 * p)) & 1u, sy = (codes >> (3 * p + 1)) & 1u, sz = (codes >> (3 * p + 2)) & 1u;
+            const float4 px = sx ? bx : ax, py = sy ? by : ay, pz = sz ? bz : az;
+            if (p >= 4) {
+                x01[p - 4] = pack2(px.x, px.y); x23[p - 4] = pack2(px.z, px.w); y01[p - 4] = pack2(py.x, py.y);
+                y23[p - 4] = pack2(py.z, py.w); z01[p - 4] = pack2(pz.x, pz.y); z23[p - 4] = pack2(pz.z, pz.w);
+                continue;
+            }
+            const float4 dd = plane_dist4_packed(__ldg(pl + 2 * p), __ldg(pl + 2 * p + 1), pack2(px.x, px.y), pack2(px.z, px.w),
+                                                 pack2(py.x, py.y), pack2(py.z, py.w), pack2(pz.x, pz.y), pack2(pz.z, pz.w));
+            if (p & 1)
+                side = min3_4(side, held, dd);
+            else
+                held = dd;
+        }
+        alive_somewhere = __any_sync(0xffffffffu, ((alive | caster) & ~negative_bits(side)) != 0u);
+    }
+    for (int r = 0; r < count; r++) {
+        const uint2 m = __ldg(a.plain_meta + pv + r);
+        const uint32_t keep = alive_somewhere ? ((m.x >> 31) ? caster : alive) : 0u;
+        uint4 b = make_uint4(0u, 0u, 0u, 0u);
+        if (alive_somewhere) {
+            const float4 dn = plane_dist4_packed(__ldg(pl + 12 * r + 8), __ldg(pl + 12 * r + 9), x01[0], x23[0], y01[0], y23[0], z01[0], z23[0]);
+            const float4 df = plane_dist4_packed(__ldg(pl + 12 * r + 10), __ldg(pl + 12 * r + 11), x01[1], x23[1], y01[1], y23[1], z01[1], z23[1]);
+            const float4 lowest = min3_4(side, dn, df);
+            b.x = __ballot_sync(0xffffffffu, (keep & 1u) && !(lowest.x < 0.0f));
+            b.y = __ballot_sync(0xffffffffu, (keep & 2u) && !(lowest.y < 0.0f));
+            b.z = __ballot_sync(0xffffffffu, (keep & 4u) && !(lowest.z < 0.0f));
+            b.w = __ballot_sync(0xffffffffu, (keep & 8u) && !(lowest.w < 0.0f));
+        }
+        const uint32_t total = __popc(b.x) + __popc(b.y) + __popc(b.z) + __popc(b.w);
+        if (lane == 0) {
+            *reinterpret_cast<uint4 *>(a.masks + (int64_t)(pv + r) * num_words + group * 4) = b;
+            if (total)
+                atomicAdd(a.totals + (int64_t)m.y * row + group / kMaskBlockGroups, total);
         }
     }
 }
@@ -193,22 +239,22 @@ mv_plain_test_kernel(const __grid_constant__ MvArgs a) {
         for (int pv = chunk * a.views_per_warp; pv < pv1;) {
             const uint32_t m = __ldg(&a.plain_meta[pv].x);
             const uint32_t codes = m & 0x3ffffu;
+            const int shared = min((int)((m >> kPlainSharedShift) & 7u), pv1 - pv);
+            if (shared >= 2) {
+                test_shared_side_run(a, pv, shared, codes, ax, ay, az, bx, by, bz, alive, caster, group, lane);
+                pv += shared;
+                continue;
+            }
             int run = min((int)((m >> 18) & 7u), pv1 - pv);
             if (run >= 4) {
                 run = 4;
-                if (m & kPlainSharedSides4)
-                    test_view_run<4, true>(a, pv, codes, ax, ay, az, bx, by, bz, alive, caster, group, lane);
-                else
-                    test_view_run<4, false>(a, pv, codes, ax, ay, az, bx, by, bz, alive, caster, group, lane);
+                test_view_run<4>(a, pv, codes, ax, ay, az, bx, by, bz, alive, caster, group, lane);
             } else if (run >= 2) {
                 run = 2;
-                if (m & kPlainSharedSides2)
-                    test_view_run<2, true>(a, pv, codes, ax, ay, az, bx, by, bz, alive, caster, group, lane);
-                else
-                    test_view_run<2, false>(a, pv, codes, ax, ay, az, bx, by, bz, alive, caster, group, lane);
+                test_view_run<2>(a, pv, codes, ax, ay, az, bx, by, bz, alive, caster, group, lane);
             } else {
                 run = 1;
-                test_view_run<1, false>(a, pv, codes, ax, ay, az, bx, by, bz, alive, caster, group, lane);
+                test_view_run<1>(a, pv, codes, ax, ay, az, bx, by, bz, alive, caster, group, lane);
             }
             pv += run;
         }

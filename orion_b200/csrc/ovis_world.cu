@@ -1155,18 +1155,12 @@ int cull_views_grouped(OvisWorld *w, int32_t n_views, const float *planes, const
                     uint32_t run = 1;
                     if (k + 1 < np && (meta[plain[k + 1]] & 0x3ffffu) == (m & 0x3ffffu))
                         run = std::min<uint32_t>(4u, ((pm[2 * (k + 1)] >> 18) & 7u) + 1u);
-                    auto same_sides = [&](size_t first, size_t count) {
-                        for (size_t j = 1; j < count; j++)
-                            if (std::memcmp(sides(plain[first]), sides(plain[first + j]), 16 * sizeof(float)) != 0)
-                                return false;
-                        return true;
-                    };
-                    uint32_t shared = 0;
-                    if (w->mv_shared_sides && run >= 2 && same_sides(k, 2))
-                        shared |= ovis::kPlainSharedSides2;
-                    if (w->mv_shared_sides && run >= 4 && same_sides(k, 4))
-                        shared |= ovis::kPlainSharedSides4;
-                    pm[2 * k] = (m & 0x8003ffffu) | (run << 18) | shared;
+                    // how many views from here on (same codes) have the side planes of this one, capped at 7
+                    uint32_t shared = 1;
+                    if (w->mv_shared_sides && k + 1 < np && (meta[plain[k + 1]] & 0x3ffffu) == (m & 0x3ffffu) &&
+                        std::memcmp(sides(plain[k]), sides(plain[k + 1]), 16 * sizeof(float)) == 0)
+                        shared = std::min<uint32_t>(7u, std::max<uint32_t>(1u, (pm[2 * (k + 1)] >> ovis::kPlainSharedShift) & 7u) + 1u);
+                    pm[2 * k] = (m & 0x8003ffffu) | (run << 18) | (shared << ovis::kPlainSharedShift);
                     pm[2 * k + 1] = plain[k];
                     const float *src = planes + 24 * (size_t)(v0 + plain[k]);
                     for (int c = 0; c < 24; c++)
