@@ -202,82 +202,33 @@ __device__ __forceinline__ void entity_bounds_from_trs(const DTrs &w, uint32_t e
     }
 }
 
-// The levels of one update are a chain: level k + 1 is launched with programmatic stream serialization (after_level) and
-// may START while level k runs its last waves. What it reads before griddepcontrol.wait - its nodes' parents, local
-// transforms, bound entities and their local boxes - no level kernel writes; everything a level writes (world transforms,
-// world boxes, dirty marks) is touched after the wait only. Every thread waits before it returns, so "this level finished"
-// still implies "the level before finished". The launch latency and the first wave's loads of the next level disappear
-// behind the tail of this one. Without the launch attribute both instructions do nothing.
 __global__ void __launch_bounds__(256)
 update_level_kernel(LevelArgs a) {
-    asm volatile("griddepcontrol.launch_dependents;");
-    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    const bool in = i < a.count;
-    const bool everything = a.dirty == nullptr;                 // a partial update reads only what it recomputes: after the wait
-    int64_t node = 0;
-    int32_t parent = -1;
-    uint32_t entity = kNone;
-    DTrs w = identity_trs();
-    DAabb box = {};
-    if (in) {
-        node = a.list ? (int64_t)a.list[i] : a.first + i;
-        parent = a.parent[node];
-        if (everything) {
-            w = load_trs(a.local_trs, a.nstride, node);
-            entity = a.node_entity[node];
-            if (entity != kNone)
-#pragma unroll
-                for (int k = 0; k < 3; k++) {
-                    box.mn[k] = a.local_aabb[k * a.estride + entity];
-                    box.mx[k] = a.local_aabb[(k + 3) * a.estride + entity];
-                }
-        }
-    }
-    asm volatile("griddepcontrol.wait;" ::: "memory");
-    if (!in)
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= a.count)
         return;
-    if (!everything) {
+    int64_t node = a.list ? (int64_t)a.list[i] : a.first + i;
+    int32_t parent = a.parent[node];
+    if (a.dirty) {
         // Entity::transformed only runs below a node that was moved (entity.cc:309-363 -> :382-411): a node is
         // recomputed if it changed itself or its parent was recomputed (parents are in an earlier launch).
         bool moved = a.dirty[node] != 0 || (parent >= 0 && a.dirty[parent] != 0);
         if (!moved)
             return;
         a.dirty[node] = 1;
-        w = load_trs(a.local_trs, a.nstride, node);
-        entity = a.node_entity[node];
-        if (entity != kNone)
-#pragma unroll
-            for (int k = 0; k < 3; k++) {
-                box.mn[k] = a.local_aabb[k * a.estride + entity];
-                box.mx[k] = a.local_aabb[(k + 3) * a.estride + entity];
-            }
     }
+    DTrs w = load_trs(a.local_trs, a.nstride, node);
     if (parent >= 0)
         w = compose_trs(load_trs(a.world_trs, a.nstride, parent), w);
     store_trs(a.world_trs, a.nstride, node, w);
-    if (entity != kNone) {
-        const DAabb o = transform_aabb(box, trs_matrix(w));
-#pragma unroll
-        for (int k = 0; k < 3; k++) {
-            a.world_aabb[k * a.estride + entity] = o.mn[k];
-            a.world_aabb[(k + 3) * a.estride + entity] = o.mx[k];
-        }
-    }
+    uint32_t entity = a.node_entity[node];
+    if (entity != kNone)
+        entity_bounds_from_trs(w, entity, a.local_aabb, a.world_aabb, a.estride);
 }
 
-void launch_update_level(const LevelArgs &a, cudaStream_t s, bool after_level) {
-    if (a.count <= 0)
-        return;
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3((unsigned)blocks_for(a.count, 256));
-    cfg.blockDim = dim3(256);
-    cfg.stream = s;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    attr[0].val.programmaticStreamSerializationAllowed = 1;
-    cfg.attrs = attr;
-    cfg.numAttrs = after_level ? 1 : 0;                          // only behind another level kernel (see above)
-    cudaLaunchKernelEx(&cfg, update_level_kernel, a);
+void launch_update_level(const LevelArgs &a, cudaStream_t s) {
+    if (a.count > 0)
+        update_level_kernel<<<blocks_for(a.count, 256), 256, 0, s>>>(a);
 }
 
 // Entities beyond the first bound to a node (a MeshRenderer owns one RenderEntity per sub-mesh,

@@ -273,7 +273,7 @@ void launch_scatter_u32(const uint32_t *src, const uint32_t *ids, int64_t n, uin
 void launch_fill_u32(uint32_t *dst, int64_t n, uint32_t value, cudaStream_t s);
 void launch_identity_bounds(const uint32_t *ids, uint32_t first, int64_t n, const float *local, float *world,
                             int64_t stride, cudaStream_t s);
-void launch_update_level(const LevelArgs &a, cudaStream_t s, bool after_level);   // after_level: the kernel before it in the stream is a level kernel
+void launch_update_level(const LevelArgs &a, cudaStream_t s);
 void launch_extra_bounds(const uint32_t *entities, const uint32_t *nodes, int64_t n, const float *world_trs,
                          int64_t nstride, const float *local, float *world, int64_t estride, const uint8_t *dirty,
                          cudaStream_t s);

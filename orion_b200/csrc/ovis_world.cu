@@ -93,7 +93,6 @@ struct OvisWorld {
     int forced_variant = -1;              // OVIS_CULL_VARIANT (tuning); -1 = pick by size
     bool fused_small = true;              // OVIS_CULL_FUSED=0 (tuning) keeps small worlds on the two-launch path
     bool mv_shared_sides = true;          // OVIS_MV_SHARED_SIDES=0 (tuning): views with identical side planes are tested like any others
-    bool pdl_levels = true;               // OVIS_PDL_LEVELS=0 (tuning): level kernels of an update launched one after the other
     int64_t fused_below = 512 << 10;      // OVIS_FUSED_BELOW (tuning): worlds with fewer entities take the single cooperative launch
     int blocks_per_sm[16][2] = {};         // cull test kernel occupancy per variant: [unmasked, masked]
     int fused_blocks_per_sm[16][2] = {};   // same for the fused (cooperative) kernel; 0 = not available
@@ -600,7 +599,6 @@ int flush_transforms(OvisWorld *w) {
         }
         w->extra_dirty = false;
     }
-    bool after_level = false;
     for (const Level &l : w->levels) {
         ovis::LevelArgs a;
         a.list = l.contiguous ? nullptr : w->d_level_lists + l.list_offset;
@@ -617,8 +615,7 @@ int flush_transforms(OvisWorld *w) {
         a.estride = w->cap_ent;
         if (l.count <= 0)
             continue;
-        ovis::launch_update_level(a, w->stream, after_level && w->pdl_levels);
-        after_level = true;
+        ovis::launch_update_level(a, w->stream);
         w->launches++;
     }
     if (!w->h_extra_entity.empty()) {
@@ -1451,8 +1448,6 @@ int ovis_world_create(int device, OvisWorld **out_world) {
         w->direct_host = atoi(v) != 0;
     if (const char *v = getenv("OVIS_FUSED_BELOW"))
         w->fused_below = atoll(v);
-    if (const char *v = getenv("OVIS_PDL_LEVELS"))
-        w->pdl_levels = atoi(v) != 0;
     if (const char *v = getenv("OVIS_MV_SHARED_SIDES"))
         w->mv_shared_sides = atoi(v) != 0;
     if (const char *v = getenv("OVIS_HOST_FLAG"))

@@ -313,3 +313,43 @@ def test_thousand_culls_back_to_back_with_alternating_views(oracle, n):
     for f in (frames - 2, frames - 1):
         assert np.array_equal(ring[f & 1][:want[f]].cpu().numpy().view(np.uint32), expected[f & 1])
     w.close()
+
+
+@pytest.mark.parametrize("n", [5_000, 400_000])
+def test_depth_slices_of_one_frustum_share_their_side_planes(oracle, monkeypatch, n):
+    """A camera and nine depth slices of its frustum (bit-identical left / right / top / bottom planes: runs of 7 + 3),
+    two more cameras, per-view caster filters and removed entities: the shared-side runs must give the lists of the
+    reference - and of the same call with the sharing turned off."""
+    rng = np.random.default_rng(507)
+    boxes = util.random_boxes(rng, n, extent=300.0, hmax=4.0)
+    e = util.edge_boxes()
+    boxes[:len(e)] = e
+    flags = (rng.random(n) < 0.5).astype(np.uint32)
+    cam = scenes.make_view((10, 5, 280), scenes.quat_yaw_pitch(8.0, -3.0), 80.0, 0.1, 900.0, 1600, 900)
+    cuts = [0.1, 3.0, 20.0, 60.0, 120.0, 200.0, 300.0, 450.0, 600.0, 900.0]
+    views = [cam] + [scenes.make_view(cam["position"], cam["orientation"], 80.0, cuts[i], cuts[i + 1], 1600, 900) for i in range(9)]
+    views += [scenes.make_view((0, 0, 0), scenes.quat_yaw_pitch(120.0, 10.0), 60.0, 0.5, 500.0, 800, 600),
+              scenes.make_view((10, 5, 280), scenes.quat_yaw_pitch(8.0, -3.0), 70.0, 0.1, 900.0, 1600, 900)]   # same pose, other fov
+    planes = np.stack([oracle.view_planes(v) for v in views])
+    assert all(np.array_equal(planes[0, :4], planes[k, :4]) for k in range(1, 10))       # the premise: identical side planes
+    require = rng.integers(0, 2, len(views)).astype(np.uint32)
+    gone = rng.choice(np.arange(20, n), n // 7, replace=False).astype(np.uint32)
+    keep = np.ones(n, dtype=bool)
+    keep[gone] = False
+    got = []
+    for shared in ("1", "0"):
+        monkeypatch.setenv("OVIS_MV_SHARED_SIDES", shared)
+        w = _world_static(boxes, flags)
+        w.remove_entities(gone)
+        off, _, d_ent = w.cull_views_device(planes, require)
+        got.append((off.copy(), w.read_device(d_ent, int(off[-1]))))
+        w.close()
+    assert np.array_equal(got[0][0], got[1][0]) and np.array_equal(got[0][1], got[1][1])
+    off, ent = got[0]
+    listed = 0
+    for k in range(len(views)):
+        exp = oracle.cull_aabb(boxes, planes[k], flags, int(require[k]), threads=8)
+        exp = exp[keep[exp]]
+        assert np.array_equal(ent[off[k]:off[k + 1]], exp), k
+        listed += len(exp)
+    assert listed > n // 10
