@@ -96,6 +96,29 @@ def run_case(oracle, seed, others):
             if np.any(small[cap:] != 0xDEADBEEF):
                 return desc, "undersized buffer: wrote past its end"
         frames += 1
+    if 0 < n <= 1_048_576:
+        # the entry point that may not allocate (caller-owned SoA bounds, scratch inside the library), on the last view:
+        # the same list (it knows no removals), also when the output is clipped by its capacity
+        import torch
+        stride = (n + 255) // 256 * 256
+        soa = np.zeros((6, stride), dtype=np.float32)
+        soa[:, :n] = boxes.T
+        d_bounds = torch.from_numpy(soa).cuda()
+        exp_all = oracle.cull_aabb(boxes, planes, threads=8)
+        for cap in (n, max(1, len(exp_all) // 2)):
+            d_out = torch.full((cap + 4,), -1, dtype=torch.int32, device="cuda")
+            d_count = torch.zeros(1, dtype=torch.int32, device="cuda")
+            base = int(rng.choice([0, 7, 1_000_000]))
+            lib.cull_planes_noalloc(0, 0, d_bounds.data_ptr(), stride, n, planes.reshape(-1), d_out.data_ptr(), cap, d_count.data_ptr(),
+                                    id_base=base)
+            torch.cuda.synchronize()
+            count = int(d_count.item())
+            got = d_out.cpu().numpy()
+            if count != len(exp_all) or not np.array_equal(got[:min(count, cap)].view(np.uint32), exp_all[:cap] + np.uint32(base)):
+                return desc, f"no-allocation cull: {count} ids (capacity {cap}), expected {len(exp_all)}"
+            if np.any(got[cap:] != -1):
+                return desc, "no-allocation cull wrote past its capacity"
+        desc["noalloc"] = True
     desc["frames"] = frames
     return desc, None
 
