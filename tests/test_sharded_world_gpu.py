@@ -122,3 +122,26 @@ def test_sharded_many_views_and_shadow_lists(oracle, n_shards, monkeypatch):
     assert np.array_equal(off, e_off) and np.array_equal(ent, e_ent)
     assert len(ll) > 6 and len(ent) > 0
     sw.close()
+
+
+def test_pinning_a_thread_next_to_its_gpu_stays_within_the_allowed_cpus():
+    """ovis_host_pin_thread_near_device: the thread ends up on a non-empty subset of the CPUs it was allowed before (the
+    GPU's local_cpulist within the cpuset), or where it was when the box has no topology files. Runs in a thread of its own
+    so that the test process keeps its affinity."""
+    import os
+    import threading
+    result = {}
+
+    def body():
+        before = os.sched_getaffinity(0)
+        n = lib.pin_thread_near_device(0)
+        after = os.sched_getaffinity(0)
+        result.update(before=before, after=after, n=n)
+
+    t = threading.Thread(target=body)
+    t.start()
+    t.join()
+    assert result["after"] and result["after"] <= result["before"]
+    assert result["n"] in (0, len(result["after"]))
+    with pytest.raises(lib.OvisError):
+        lib.pin_thread_near_device(99)
