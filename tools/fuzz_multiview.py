@@ -144,6 +144,10 @@ def run_case(oracle, seed, budget_views):
                     tests += len(boxes)
         if k != len(ll):
             return desc, f"{len(ll)} lists, expected {k}"
+        if call == 1:                                        # the host-output form of the same call: the same CSR
+            h_ll, h_lv, h_off, h_ent = w.cull_shadow_views(ids)
+            if not (np.array_equal(h_ll, ll) and np.array_equal(h_lv, lv) and np.array_equal(h_off, off) and np.array_equal(h_ent, ent)):
+                return desc, f"host-output shadow lists differ from the device ones ({len(h_ent)} vs {len(ent)} ids)"
     # plain views: random cameras, duplicates and near-duplicates (runs of views that share P-vertex codes), per-view filters
     nv = int(min(rng.choice([1, 3, 5, 17, 64]), max(1, budget_views // max(len(boxes), 1) // 2)))
     views = util.random_views(rng, nv, extent=desc["extent"])
