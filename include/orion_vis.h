@@ -578,7 +578,12 @@ typedef struct OvisSceneInfo {
  *     node (ovis_light_bind_node) and follows it from then on; attenuation and shadow bias via ovis_light_set_shading;
  *   - one OvisView per Camera (graphics/src/camera.cc:46-57,71-79) with the given viewport size, returned in
  *     out_cameras (up to cap_cameras; OVIS_ERR_CAPACITY if there are more, the world is still complete).
- * Mesh assets "game/<path>" resolve to <game_asset_dir>/<path>.obj. Physics, controllers and post effects are ignored. */
+ * Mesh assets "game/<path>" resolve to <game_asset_dir>/<path>.obj. Physics, controllers and post effects are ignored.
+ * The file is read as the reference's JSONSerialiser reads it (json_serialiser.cc:232-244, 486-626; entity.cc:127-147):
+ * {"objectID": n} is the n-th object of the document; a property of the wrong JSON type keeps its default (a float has to be
+ * written with a fraction or an exponent: 50.0, not 50); a component / child list ends at the first unreadable reference;
+ * files the reference would assert on (an entity attached twice, a null reference in a list, no World first) are refused
+ * with OVIS_ERR_INVALID. */
 int ovis_scene_import(OvisWorld *world, const char *world_path, const char *game_asset_dir, int32_t vp_width,
                       int32_t vp_height, int32_t cap_cameras, OvisView *out_cameras, OvisSceneInfo *out_info);
 /* The same in two steps, for hosts that want the parsed arrays (or have no device yet): ovis_scene_load parses into a

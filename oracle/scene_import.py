@@ -107,49 +107,138 @@ def obj_submesh_aabbs(path: str) -> np.ndarray:
     return np.array(boxes, dtype=np.float32).reshape(-1, 6)
 
 
+class SceneError(ValueError):
+    """A file the reference would refuse or assert on."""
+
+
+# ---- JSONSerialiser::read's type rules (engine/src/json_serialiser.cc:486-626): a value of the wrong JSON type leaves the
+# property at its default. Python's json keeps what rapidjson's flags say: `50` is an int, `50.0` / `5e1` a float.
+def _is_number(x):
+    return isinstance(x, (int, float)) and not isinstance(x, bool)
+
+
+def _is_double(x):                                              # rapidjson IsDouble(): fraction / exponent, or beyond 64 bits
+    return isinstance(x, float) or (_is_number(x) and not (-2 ** 63 <= x <= 2 ** 64 - 1))
+
+
+def _is_uint(x):                                                # rapidjson IsUint()
+    return isinstance(x, int) and not isinstance(x, bool) and 0 <= x <= 0xFFFFFFFF
+
+
+def _get_bool(props, name, default):
+    v = props.get(name)
+    return v if isinstance(v, bool) else default
+
+
+def _get_float(props, name, default):                           # IsFloat() (document.h:971-976), then GetFloat()
+    v = props.get(name)
+    if v is not None and _is_double(v) and -3.4028234e38 <= float(v) <= 3.4028234e38:
+        return np.float32(float(v))
+    return np.float32(default)
+
+
+def _get_floats(props, name, n, default):                       # vec3 / quat: an array of exactly n numbers of any kind
+    v = props.get(name)
+    if isinstance(v, list) and len(v) == n and all(_is_number(x) for x in v):
+        return [np.float32(float(x)) for x in v]
+    return [np.float32(x) for x in default]
+
+
 def import_world(world_path: str, game_dir: str, vp_width: int, vp_height: int, oracle=None) -> dict:
     """The render-world content of a serialised world, in activation order."""
     oracle = oracle or pyoracle.load("best")
-    with open(world_path) as f:
-        objects = json.load(f)
-    by_id = {o["objectID"]: o for o in objects}
-    world = next(o for o in objects if o["objectClass"] == "World")
-    root = by_id[world["root"]["objectID"]]
+    with open(world_path, "rb") as f:
+        raw = f.read()
+    for mark in (0xEF, 0xBB, 0xBF):                             # rapidjson's stream skips these, each on its own
+        if raw[:1] == bytes([mark]):
+            raw = raw[1:]
+    raw = raw.split(b"\0")[0]                                   # ... and reads a NUL as the end of the text
+    def first_wins(pairs):                                      # rapidjson's FindMember returns the FIRST member of that name
+        d = {}
+        for k, v in pairs:
+            d.setdefault(k, v)
+        return d
+
+    # (rapidjson does not validate the encoding of strings)
+    objects = json.loads(raw.decode("utf-8", "surrogateescape"), object_pairs_hook=first_wins)
+    if not isinstance(objects, list):
+        raise SceneError("not an array of objects")
+
+    def scene_object(ref):
+        """findObject (json_serialiser.cc:232-244): {"objectID": uint} names a POSITION in the document."""
+        if not isinstance(ref, dict):
+            return None, None
+        if not ref:
+            raise SceneError("null reference where the reference asserts")
+        i = ref.get("objectID")
+        if not _is_uint(i) or i >= len(objects):
+            return None, None
+        o = objects[i]
+        if not isinstance(o, dict) or not isinstance(o.get("objectClass"), str):
+            return None, None
+        return i, o
+
+    if not objects or not isinstance(objects[0], dict) or objects[0].get("objectClass") != "World":
+        raise SceneError("the first object is not a World")
+    root_ref = objects[0].get("root")
+    if not isinstance(root_ref, dict) or not root_ref:
+        raise SceneError("the World has no root")
+    root_id, root = scene_object(root_ref)
+    if root is None or root["objectClass"] != "Entity":
+        raise SceneError("the World has no root entity")
 
     parent, local, ent_aabb, ent_flags, ent_node = [], [], [], [], []
     pending_lights, pending_cameras = [], []
     meshes = {}
     shadow_res = [0]
+    taken = {root_id}
 
-    def f32(x):
-        return np.float32(x)
+    def props_of(o):
+        p = o.get("objectProperties")
+        return p if isinstance(p, dict) else {}
 
-    def visit(e, parent_node):
-        props = e.get("objectProperties", {})
-        trs = [0, 0, 0, 1, 0, 0, 0, 1, 1, 1]
-        if parent_node >= 0:
-            if not props.get("active", False):
+    def visit(e, parent_node, depth):
+        if depth > 4096:
+            raise SceneError("entity tree too deep")
+        props = props_of(e)
+        trs = [np.float32(x) for x in (0, 0, 0, 1, 0, 0, 0, 1, 1, 1)]
+        if parent_node >= 0:                                    # the root's properties are not read (entity.cc:127-130)
+            if not _get_bool(props, "active", False):
                 return
-            trs = list(props.get("position", [0, 0, 0])) + list(props.get("orientation", [1, 0, 0, 0])) + \
-                list(props.get("scale", [1, 1, 1]))
+            trs = _get_floats(props, "position", 3, (0, 0, 0)) + _get_floats(props, "orientation", 4, (1, 0, 0, 0)) + \
+                _get_floats(props, "scale", 3, (1, 1, 1))
         node = len(parent)
         parent.append(parent_node)
-        local.append([f32(x) for x in trs])
-        for ref in e.get("components", []):
-            c = by_id[ref["objectID"]]
-            cp = c.get("objectProperties", {})
-            if not cp.get("active", False):
+        local.append(trs)
+        # `while (serialiser.pop(x))`: the list ends at the first element that cannot be read (entity.cc:132-147)
+        comps = e.get("components")
+        for ref in comps if isinstance(comps, list) else []:
+            i, c = scene_object(ref)
+            if c is None or c["objectClass"] in ("Entity", "World"):
+                break
+            if i in taken:
+                raise SceneError("a component is attached twice")
+            taken.add(i)
+            cp = props_of(c)
+            if not _get_bool(cp, "active", False):
                 continue
             cls = c["objectClass"]
             if cls in ("MeshRenderer", "Skybox"):
-                flags = CASTS_SHADOW if cp.get("castsShadow", True) else 0
+                flags = CASTS_SHADOW if _get_bool(cp, "castsShadow", True) else 0
                 if cls == "Skybox":
                     boxes = np.array([[-FLT_MAX] * 3 + [FLT_MAX] * 3], dtype=np.float32)
                 else:
-                    asset = cp["mesh"]["asset"]
-                    assert asset.startswith("game/")
+                    mesh = cp.get("mesh")
+                    asset = mesh.get("asset") if isinstance(mesh, dict) else None
+                    if not isinstance(asset, str) or not asset.startswith("game/"):
+                        raise SceneError("MeshRenderer without a usable mesh asset")
                     if asset not in meshes:
-                        meshes[asset] = obj_submesh_aabbs(os.path.join(game_dir, asset[5:] + ".obj"))
+                        path = os.path.join(game_dir, asset[5:] + ".obj")
+                        if not os.path.exists(path):
+                            raise SceneError("missing mesh")
+                        meshes[asset] = obj_submesh_aabbs(path)
+                        if len(meshes[asset]) == 0:
+                            raise SceneError("mesh without faces")
                     boxes = meshes[asset]
                 for b in boxes:
                     ent_aabb.append(b)
@@ -159,13 +248,25 @@ def import_world(world_path: str, game_dir: str, vp_width: int, vp_height: int, 
                 pending_lights.append((node, cls, cp))
             elif cls == "Camera":
                 pending_cameras.append((node, cp))
-                pipe = by_id.get(cp.get("renderPipeline", {}).get("objectID", -1))
+                pipe_ref = cp.get("renderPipeline")
+                pipe = scene_object(pipe_ref)[1] if isinstance(pipe_ref, dict) and pipe_ref else None
                 if pipe is not None and not shadow_res[0]:
-                    shadow_res[0] = int(pipe.get("objectProperties", {}).get("shadowMapResolution", 0))
-        for ref in e.get("children", []):
-            visit(by_id[ref["objectID"]], node)
+                    r = props_of(pipe).get("shadowMapResolution")       # PROPERTY() uint16_t: IsUint(), then truncated
+                    if _is_uint(r):
+                        shadow_res[0] = r & 0xFFFF
+        kids = e.get("children")
+        for ref in kids if isinstance(kids, list) else []:
+            i, k = scene_object(ref)
+            if k is None or k["objectClass"] != "Entity":
+                break
+            if i in taken:
+                raise SceneError("an entity is attached twice")
+            taken.add(i)
+            visit(k, node, depth + 1)
 
-    visit(root, -1)
+    import sys
+    sys.setrecursionlimit(max(sys.getrecursionlimit(), 20000))
+    visit(root, -1, 0)
     parent = np.array(parent, dtype=np.int32)
     local = np.array(local, dtype=np.float32).reshape(-1, 10)
     world_trs = oracle.world_trs(parent, local)
@@ -176,19 +277,21 @@ def import_world(world_path: str, game_dir: str, vp_width: int, vp_height: int, 
         l = lights[i]
         t = LIGHT_TYPES[cls]
         l["type"] = t
-        l["flags"] = CASTS_SHADOW if cp.get("castsShadows", False) else 0
-        l["colour"] = cp.get("colour", [1, 1, 1])
-        l["intensity"] = cp.get("intensity", 0.8)
+        l["flags"] = CASTS_SHADOW if _get_bool(cp, "castsShadows", False) else 0
+        l["colour"] = _get_floats(cp, "colour", 3, (1, 1, 1))
+        l["intensity"] = _get_float(cp, "intensity", 0.8)
         att = [0, 0, 0]
         if t == 2:
-            l["range"] = cp.get("range", 100.0)
+            l["range"] = _get_float(cp, "range", 100.0)
             att = [1.0, 0.045, 0.0075]
         elif t == 3:
-            l["range"] = cp.get("range", 50.0)
+            l["range"] = _get_float(cp, "range", 50.0)
             att = [1.0, 0.09, 0.032]
-            l["cutoff"] = cp.get("cutoff", 20.0)
-        shading[i, :3] = cp.get("attenuation", att)
-        shading[i, 3] = cp.get("shadowBiasConstant", -0.001)
+            l["cutoff"] = _get_float(cp, "cutoff", 20.0)
+            if l["cutoff"] > 45.0:
+                raise SceneError("spot light cutoff must be <= 45 degrees")          # render_light.cc:104
+        shading[i, :3] = _get_floats(cp, "attenuation", 3, att)
+        shading[i, 3] = _get_float(cp, "shadowBiasConstant", -0.001)
         l["position"] = world_trs[node, 0:3]
         l["direction"] = oracle.quat_rotate(world_trs[node, 3:7], [0, 0, -1])
     cameras = np.zeros(len(pending_cameras), dtype=pyoracle.VIEW_DTYPE)
@@ -196,9 +299,9 @@ def import_world(world_path: str, game_dir: str, vp_width: int, vp_height: int, 
         v = cameras[i]
         v["position"] = world_trs[node, 0:3]
         v["orientation"] = world_trs[node, 3:7]
-        v["hfov_deg"] = cp.get("fov", 75.0)
-        v["znear"] = cp.get("zNear", 0.1)
-        v["zfar"] = cp.get("zFar", 1000.0)
+        v["hfov_deg"] = _get_float(cp, "fov", 75.0)
+        v["znear"] = _get_float(cp, "zNear", 0.1)
+        v["zfar"] = _get_float(cp, "zFar", 1000.0)
         v["vp_width"], v["vp_height"] = vp_width, vp_height
     return {"parent": parent, "local_trs": local, "world_trs": world_trs,
             "local_aabb": np.array(ent_aabb, dtype=np.float32).reshape(-1, 6),

@@ -49,6 +49,8 @@ struct Json {
     enum Kind { Null, Bool, Number, String, Array, Object } kind = Null;
     bool b = false;
     double num = 0.0;
+    bool is_double = false;                                     // rapidjson's IsDouble(): written with a fraction or an exponent, or beyond 64 bits
+    bool is_uint = false;                                       // rapidjson's IsUint(): a non-negative integer below 2^32 (and "-0")
     std::string str;
     std::vector<Json> items;                                    // Array
     std::vector<std::pair<std::string, Json>> members;          // Object, in file order
@@ -182,7 +184,7 @@ struct JsonParser {
             return 0.0;
         return exp >= 0 ? significand * pow10_table(exp) : significand / pow10_table(-exp);
     }
-    bool parseNumber(double &out) {
+    bool parseNumber(double &out, bool *is_double = nullptr, bool *is_uint = nullptr) {
         const char *s = p;
         auto peek = [&]() { return s < end ? *s : '\0'; };
         auto digit = [&]() { const char c = peek(); return c >= '0' && c <= '9'; };
@@ -295,6 +297,10 @@ struct JsonParser {
                 }
             }
         }
+        if (is_double)
+            *is_double = useDouble;
+        if (is_uint)
+            *is_uint = !useDouble && !use64 && (!minus || i == 0);   // Int(0) carries the unsigned flags too (document.h: GenericValue(int))
         if (useDouble) {
             const int pw = exp + expFrac;
             d = pw < -308 ? fastPath(fastPath(d, -308), pw + 308) : fastPath(d, pw);
@@ -376,7 +382,7 @@ struct JsonParser {
         if (end - p >= 4 && !strncmp(p, "true", 4)) { v.kind = Json::Bool; v.b = true; p += 4; return true; }
         if (end - p >= 5 && !strncmp(p, "false", 5)) { v.kind = Json::Bool; v.b = false; p += 5; return true; }
         if (end - p >= 4 && !strncmp(p, "null", 4)) { v.kind = Json::Null; p += 4; return true; }
-        if (!parseNumber(v.num))
+        if (!parseNumber(v.num, &v.is_double, &v.is_uint))
             return false;
         v.kind = Json::Number;
         return true;
@@ -751,8 +757,7 @@ using ovis::hm::Trs;
 using ovis::hm::Vec3;
 
 struct SceneObjects {
-    Json root;
-    std::unordered_map<long long, const Json *> by_id;
+    Json root;                                                   // the document: an array of serialised objects
 };
 
 const Json *props(const Json &o) { return o.get("objectProperties"); }
@@ -763,10 +768,16 @@ bool prop_bool(const Json &o, const char *name, bool fallback) {
     return (v && v->kind == Json::Bool) ? v->b : fallback;
 }
 
+// JSONSerialiser::read (json_serialiser.cc:486-626) is strict about JSON types, and a value of the wrong type leaves the
+// property at its default: bool wants IsBool(); float wants IsFloat() - a number WRITTEN as a double (fraction or
+// exponent: `50` is not one, `50.0` is) within the float range (rapidjson document.h:971-976); vec3 / vec4 / quat want an
+// array of exactly that many numbers of any kind (GetFloat()); unsigned integers want IsUint().
 float prop_float(const Json &o, const char *name, float fallback) {
     const Json *p = props(o);
     const Json *v = p ? p->get(name) : nullptr;
-    return (v && v->kind == Json::Number) ? (float)v->num : fallback;   // double -> float, as the serialiser's read<float>
+    if (!v || v->kind != Json::Number || !v->is_double || !(v->num >= -3.4028234e38 && v->num <= 3.4028234e38))
+        return fallback;
+    return (float)v->num;                                         // GetFloat(): double -> float
 }
 
 bool prop_floats(const Json &o, const char *name, int n, float *out) {
@@ -775,13 +786,31 @@ bool prop_floats(const Json &o, const char *name, int n, float *out) {
     if (!v || v->kind != Json::Array || (int)v->items.size() != n)
         return false;
     for (int i = 0; i < n; i++)
+        if (v->items[(size_t)i].kind != Json::Number)
+            return false;
+    for (int i = 0; i < n; i++)
         out[i] = (float)v->items[(size_t)i].num;
     return true;
 }
 
-long long ref_id(const Json *ref) {                               // {"objectID": n}; {} is a null reference
-    const Json *id = ref ? ref->get("objectID") : nullptr;
-    return (id && id->kind == Json::Number) ? (long long)id->num : -1;
+bool prop_uint(const Json &o, const char *name, uint32_t *out) {
+    const Json *p = props(o);
+    const Json *v = p ? p->get(name) : nullptr;
+    if (!v || v->kind != Json::Number || !v->is_uint)
+        return false;
+    *out = (uint32_t)v->num;
+    return true;
+}
+
+// {"objectID": n}: n is a uint32 (json_serialiser.cc:456-458) and names the n-th object of the document (findObject,
+// :232-244: `document[id]`, not a search for a member). -1: no usable reference; -2: the empty object, a null reference.
+long long ref_id(const Json *ref) {
+    if (!ref || ref->kind != Json::Object)
+        return -1;
+    if (ref->members.empty())
+        return -2;
+    const Json *id = ref->get("objectID");
+    return (id && id->kind == Json::Number && id->is_uint) ? (long long)id->num : -1;
 }
 
 struct Importer {
@@ -918,17 +947,26 @@ struct Importer {
             cameras.push_back(v);
             const Json *p = props(c);
             const Json *pipe = scene_object(ref_id(p ? p->get("renderPipeline") : nullptr));
-            if (pipe && !shadow_map_resolution)
-                shadow_map_resolution = (int)prop_float(*pipe, "shadowMapResolution", 0.0f);
+            if (pipe && !shadow_map_resolution) {                 // PROPERTY() uint16_t, deferred_render_pipeline.h:68
+                uint32_t res = 0;
+                if (prop_uint(*pipe, "shadowMapResolution", &res))
+                    shadow_map_resolution = (int)(uint16_t)res;
+            }
             return true;
         }
         return true;                                              // physics, controllers, post effects: not on the path
     }
 
+    // findObject (json_serialiser.cc:232-244): the id is a position in the document; the object must say what class it is
     const Json *scene_object(long long id) const {
-        auto it = scene.by_id.find(id);
-        return it == scene.by_id.end() ? nullptr : it->second;
+        if (id < 0 || id >= (long long)scene.root.items.size())
+            return nullptr;
+        const Json &o = scene.root.items[(size_t)id];
+        const Json *cls = o.kind == Json::Object ? o.get("objectClass") : nullptr;
+        return (cls && cls->kind == Json::String) ? &o : nullptr;
     }
+    static const std::string &class_of(const Json &o) { return o.get("objectClass")->str; }
+    std::vector<char> taken;                                      // per document position: already someone's child or component
 
     // Entity::activated order; `parent_node` < 0 for the root.
     bool entity(const Json &e, int32_t parent_node, const Trs *parent_world, int depth) {
@@ -950,19 +988,37 @@ struct Importer {
                                 local.s.x, local.s.y, local.s.z };
         node_trs.insert(node_trs.end(), trs, trs + 10);
         node_world.push_back(world_trs);
-        if (const Json *comps = e.get("components"))
+        // `while (serialiser.pop(component)) addComponent(...)` (entity.cc:132-138; children :141-147): the list ends at the
+        // first element that cannot be read - a reference that is not {"objectID": uint}, names no object of the document,
+        // or an object of the wrong kind - and what follows it is never seen. A null reference ({}) or an object that is
+        // already attached somewhere would be handed to addComponent / addChild, which assert: refused here.
+        if (taken.size() != scene.root.items.size())
+            taken.assign(scene.root.items.size(), 0);
+        const Json *comps = e.get("components");
+        if (comps && comps->kind == Json::Array)
             for (const Json &ref : comps->items) {
-                const Json *c = scene_object(ref_id(&ref));
-                if (!c)
-                    return fail("dangling component reference");
+                const long long id = ref_id(&ref);
+                if (id == -2)
+                    return fail("null component reference");
+                const Json *c = scene_object(id);
+                if (!c || class_of(*c) == "Entity" || class_of(*c) == "World")
+                    break;
+                if (taken[(size_t)id]++)
+                    return fail("a component is attached twice");
                 if (!component(*c, node, world_trs))
                     return false;
             }
-        if (const Json *kids = e.get("children"))
+        const Json *kids = e.get("children");
+        if (kids && kids->kind == Json::Array)
             for (const Json &ref : kids->items) {
-                const Json *k = scene_object(ref_id(&ref));
-                if (!k)
-                    return fail("dangling child reference");
+                const long long id = ref_id(&ref);
+                if (id == -2)
+                    return fail("null child reference");
+                const Json *k = scene_object(id);
+                if (!k || class_of(*k) != "Entity")
+                    break;
+                if (taken[(size_t)id]++)
+                    return fail("an entity is attached twice (or is its own ancestor)");
                 if (!entity(*k, (int32_t)node, &world_trs, depth + 1))
                     return false;
             }
@@ -1007,22 +1063,17 @@ int ovis_scene_load(const char *world_path, const char *game_asset_dir, int32_t 
     if (!parser.parseDocument(scene.root) || scene.root.kind != Json::Array)
         return scene_error(OVIS_ERR_INVALID, "%s: not a serialised object file (%s)", world_path,
                            parser.error.empty() ? "top level is not an array" : parser.error.c_str());
-    const Json *world_object = nullptr;
-    for (const Json &o : scene.root.items) {
-        const Json *id = o.kind == Json::Object ? o.get("objectID") : nullptr;
-        if (!id || id->kind != Json::Number)
-            return scene_error(OVIS_ERR_INVALID, "%s: object without an objectID", world_path);
-        scene.by_id[(long long)id->num] = &o;
-        const Json *cls = o.get("objectClass");
-        if (!world_object && cls && cls->str == "World")          // the primary object of a world asset
-            world_object = &o;
-    }
-    if (!world_object)
-        return scene_error(OVIS_ERR_INVALID, "%s: no World object", world_path);
     Importer imp{ nullptr, scene, game_asset_dir, vp_width, vp_height };
-    const Json *root = imp.scene_object(ref_id(world_object->get("root")));   // world.cc:60-61
-    if (!root)
+    // "The object to return is the first object in the file" (json_serialiser.cc:221): a world asset starts with its World
+    const Json *world_object = imp.scene_object(0);
+    if (!world_object || Importer::class_of(*world_object) != "World")
+        return scene_error(OVIS_ERR_INVALID, "%s: the first object of the file is not a World", world_path);
+    const long long root_id = ref_id(world_object->get("root"));                // world.cc:60-61
+    const Json *root = imp.scene_object(root_id);
+    if (!root || Importer::class_of(*root) != "Entity")
         return scene_error(OVIS_ERR_INVALID, "%s: the World has no root entity", world_path);
+    imp.taken.assign(scene.root.items.size(), 0);
+    imp.taken[(size_t)root_id] = 1;
     if (!imp.entity(*root, -1, nullptr, 0))
         return scene_error(OVIS_ERR_INVALID, "%s: %s", world_path, imp.error.c_str());
     OvisScene *sc = new OvisScene;

@@ -219,3 +219,91 @@ def test_cubes_demo_world_on_the_device_matches_golden_cull():
     ents, ls = w.cull(c["cameras"][0])
     assert np.array_equal(ents, g["cubes_entities"]) and np.array_equal(ls, g["cubes_lights"])
     w.close()
+
+
+def _write_world(tmp_path, objects, name="w.object"):
+    import json
+    p = tmp_path / name
+    p.write_text(json.dumps(objects))
+    return str(p)
+
+
+def test_loader_follows_the_reference_serialisers_type_and_reference_rules(tmp_path, port):
+    """JSONSerialiser::read is strict (json_serialiser.cc:486-626): a float property written as `50` (an integer to
+    rapidjson) or a bool written as 1 keeps its default; a vec3 needs three numbers; {"objectID": n} names the n-th object
+    of the document whatever that object's own objectID member says (findObject, :232-244); `while (pop(...))` ends a
+    component / child list at the first reference that cannot be read (entity.cc:132-147); what the reference would
+    assert on (an entity attached twice, a null reference in a list) is refused."""
+    import json
+    from oracle import scene_import
+    base = json.load(open(FOREST))
+
+    def both(objects):
+        path = _write_world(tmp_path, objects)
+        ours = lib.load_scene(path, SCENE, 640, 360)
+        theirs = scene_import.import_world(path, SCENE, 640, 360, oracle=port)
+        for k in KEYS:
+            assert _equal(ours[k], theirs[k]), k
+        return ours
+
+    ref = both(base)
+    lights = [i for i, o in enumerate(base) if o["objectClass"] == "PointLight" and o["objectProperties"].get("active")]
+    cams = [i for i, o in enumerate(base) if o["objectClass"] == "Camera"]
+    # 1. integer-literal floats and non-boolean bools fall back to the defaults
+    w = json.loads(json.dumps(base))
+    w[lights[0]]["objectProperties"]["range"] = 7                  # IsFloat() is false for 7: PointLight's default 100 stays
+    w[lights[0]]["objectProperties"]["intensity"] = 2              # ... Light's default 0.8
+    w[lights[1]]["objectProperties"]["castsShadows"] = 1           # not a bool: default false
+    w[cams[0]]["objectProperties"]["fov"] = 90                     # default 75
+    got = both(w)
+    k0 = [i for i, o in enumerate([o for o in base if o["objectClass"] in ("AmbientLight", "DirectionalLight", "PointLight", "SpotLight")
+                                   and o["objectProperties"].get("active")]) if o is base[lights[0]]][0]
+    assert got["lights"]["range"][k0] == np.float32(100.0) and got["lights"]["intensity"][k0] == np.float32(0.8)
+    assert got["cameras"]["hfov_deg"][0] == np.float32(75.0)
+    # 2. a vec3 with a non-number element: the default position
+    ent = next(i for i, o in enumerate(base) if o["objectClass"] == "Entity" and o.get("parent") and o["objectProperties"].get("active")
+               and o["objectProperties"]["position"] != [0.0, 0.0, 0.0])
+    w = json.loads(json.dumps(base))
+    w[ent]["objectProperties"]["position"] = [1.0, "2", 3.0]
+    got = both(w)
+    assert not _equal(got["local_trs"], ref["local_trs"]) and (got["local_trs"][:, :3] == 0).all(axis=1).sum() == (ref["local_trs"][:, :3] == 0).all(axis=1).sum() + 1
+    # 3. the objectID members of the objects themselves are never read
+    w = json.loads(json.dumps(base))
+    for i, o in enumerate(w):
+        o["objectID"] = (i * 7 + 3) % len(w)
+    got = both(w)
+    for k in KEYS:
+        assert _equal(got[k], ref[k]), k
+    # 4. a reference that cannot be read ends the list: the children after it are never seen
+    w = json.loads(json.dumps(base))
+    root = w[w[0]["root"]["objectID"]]
+    assert len(root["children"]) > 4
+    root["children"][2] = {"objectID": 10 ** 6}
+    got = both(w)
+    assert 0 < len(got["parent"]) < len(ref["parent"])
+    # 5. what the reference asserts on is refused
+    for damage in ("twice", "null", "first"):
+        w = json.loads(json.dumps(base))
+        root = w[w[0]["root"]["objectID"]]
+        if damage == "twice":
+            root["children"].append(root["children"][0])
+        elif damage == "null":
+            root["children"].insert(1, {})
+        else:
+            w[0], w[1] = w[1], w[0]                             # the first object of the file is no longer the World
+        path = _write_world(tmp_path, w, damage + ".object")
+        with pytest.raises(lib.OvisError):
+            lib.load_scene(path, SCENE, 640, 360)
+        with pytest.raises(scene_import.SceneError):
+            scene_import.import_world(path, SCENE, 640, 360, oracle=port)
+
+
+def test_loader_on_damaged_worlds_randomised():
+    """tools/fuzz_scene.py in small: damaged copies of the fixture are loaded or refused - never a crash - and the loader
+    and the restatement of the reference's loader accept the same files with the same arrays."""
+    import subprocess
+    import sys
+    out = subprocess.run([sys.executable, os.path.join(os.path.dirname(HERE), "tools", "fuzz_scene.py"), "--cases", "150", "--seed", "11"],
+                         capture_output=True, text=True, timeout=900)
+    assert out.returncode == 0, out.stdout[-2000:] + out.stderr[-2000:]
+    assert '"problems": []' in out.stdout
