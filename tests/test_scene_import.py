@@ -307,3 +307,14 @@ def test_loader_on_damaged_worlds_randomised():
                          capture_output=True, text=True, timeout=900)
     assert out.returncode == 0, out.stdout[-2000:] + out.stderr[-2000:]
     assert '"problems": []' in out.stdout
+
+
+def test_obj_reader_on_damaged_meshes_randomised():
+    """tools/fuzz_obj.py in small: damaged copies of the fixture meshes are read or refused - never a crash - and the
+    reader and the restatement of the reference's OBJLoader accept the same files with the same boxes."""
+    import subprocess
+    import sys
+    out = subprocess.run([sys.executable, os.path.join(os.path.dirname(HERE), "tools", "fuzz_obj.py"), "--cases", "400", "--seed", "13"],
+                         capture_output=True, text=True, timeout=900)
+    assert out.returncode == 0, out.stdout[-2000:] + out.stderr[-2000:]
+    assert '"problems": []' in out.stdout
