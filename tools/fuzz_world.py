@@ -205,6 +205,21 @@ def run_case(oracle, seed):
             if len(gone):
                 w.remove_entities(gone)
                 keep[gone] = False
+            if not keep.all() and rng.random() < 0.4:
+                # slot reclamation: the survivors move up in order, the remap says where; every id after this is a new one
+                remap, new_n = w.compact()
+                survivors = np.flatnonzero(keep)
+                want = np.full(n_ent, 0xFFFFFFFF, dtype=np.uint32)
+                want[survivors] = np.arange(len(survivors), dtype=np.uint32)
+                if new_n != len(survivors) or len(remap) != n_ent or not np.array_equal(remap, want):
+                    return desc, f"frame {frame}: compaction left {new_n} entities, expected {len(survivors)}, or a wrong remap"
+                kb, kd, ks = keep[:n_bound], keep[n_bound:n_bound + n_direct], keep[n_bound + n_direct:]
+                boxes, flags, pass_counts = boxes[keep], flags[keep], pass_counts[keep]
+                ent_node, direct_trs, static_boxes = ent_node[kb], direct_trs[kd], static_boxes[ks]
+                n_bound, n_direct, n_ent = int(kb.sum()), int(kd.sum()), len(boxes)
+                direct_ids = np.arange(n_bound, n_bound + n_direct, dtype=np.uint32)
+                keep = np.ones(n_ent, dtype=bool)
+                desc["compacted"] = desc.get("compacted", 0) + 1
             for _ in range(int(rng.integers(0, 4))):
                 if not light_alive.any():
                     break
