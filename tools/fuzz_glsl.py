@@ -92,7 +92,43 @@ def main():
             print(json.dumps({"case": case, "what": "gamma"}))
             sys.exit(1)
         pixels += w * h
-    print(json.dumps({"cases": a.cases, "pixels": pixels, "differences": 0}))
+    # the rasteriser's shader stages: lit_vtx / shadow_vtx / unlit, lit_deferred_frag in all eight keyword combinations
+    port = pyoracle.load("port")
+    stages = 0
+    for case in range(a.cases * 4):
+        trs = util.random_trs(rng, 1, pos=float(rng.choice([1.0, 50.0, 1e5])))
+        if rng.random() < 0.2:
+            trs[0, rng.integers(0, 10)] = float(rng.choice([np.nan, np.inf, 0.0, 1e30, -1e30]))
+        transform = ref.entity_uniforms(trs)[0, :16]
+        view = scenes.make_view(rng.uniform(-30, 30, 3), scenes.random_unit_quats(rng, 1)[0], float(rng.uniform(10, 150)),
+                                float(rng.uniform(0.01, 2.0)), float(rng.uniform(3.0, 3000.0)), int(rng.choice([1, 17, 640])), int(rng.choice([1, 9, 360])))
+        vp = ref.view_matrices(view)[0][2]
+        pos = (rng.uniform(-3, 3, 3) * float(rng.choice([1.0, 1e-6, 1e6]))).astype(np.float32)
+        nrm = (rng.standard_normal(3) * float(rng.choice([1.0, 0.0, 1e-30, 1e20]))).astype(np.float32)
+        tan4 = np.concatenate([rng.standard_normal(3) * float(rng.choice([1.0, 0.0, 1e-25])), [rng.choice([-1.0, 1.0])]]).astype(np.float32)
+        g_clip, g_n = ref.raster_vertex(transform, vp, pos, nrm, glsl=True)
+        s_clip, _ = ref.raster_vertex(transform, vp, pos, nrm, glsl=True, shadow=True)
+        u_clip, _ = ref.glsl_unlit(transform, vp, pos, np.ones(3, np.float32))
+        gn, gt, gb = ref.glsl_vertex_normalmap(transform, vp, pos, nrm, tan4)
+        textures = [(rng.integers(0, 256, (int(rng.choice([1, 3, 8])), int(rng.choice([1, 5, 16])), 4), dtype=np.uint8), bool(rng.random() < 0.5),
+                     bool(rng.random() < 0.5)) for _ in range(2)]
+        uv = (rng.uniform(-3, 4, 2) * float(rng.choice([1.0, 100.0, 1e-6]))).astype(np.float32)
+        for o in (port, ref):
+            clip, n = o.raster_vertex(transform, vp, pos, nrm)
+            t = o.raster_vertex(transform, vp, pos, tan4[:3])[1]
+            ok = same_bits(clip, g_clip) and same_bits(n, g_n) and same_bits(clip, s_clip) and same_bits(clip, u_clip) and \
+                same_bits(n, gn) and same_bits(t, gt) and same_bits(o.raster_bitangent(n, t, float(tan4[3])), gb)
+            for flags in range(8):
+                mat8 = np.concatenate([rng.uniform(0, 1, 6), [rng.uniform(1, 128), flags & 1]]).astype(np.float32)
+                mat10 = np.concatenate([mat8[:7], [flags, 0, 1]]).astype(np.float32)
+                ok = ok and all(same_bits(x, y) for x, y in zip(o.raster_fragment(gn, mat8), ref.raster_fragment(gn, mat8, glsl=True)))
+                ok = ok and all(same_bits(x, y) for x, y in zip(o.raster_fragment_textured(gn, uv, gt, gb, mat10, textures),
+                                                               ref.raster_fragment_textured(gn, uv, gt, gb, mat10, textures, glsl=True)))
+            if not ok:
+                print(json.dumps({"case": case, "what": "rasteriser shader stages", "oracle": o.name}))
+                sys.exit(1)
+        stages += 1
+    print(json.dumps({"cases": a.cases, "pixels": pixels, "shader_stage_cases": stages, "differences": 0}))
 
 
 if __name__ == "__main__":
