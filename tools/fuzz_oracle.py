@@ -98,7 +98,20 @@ def main():
                 ents, _ = w.cull(view, flags=0)
                 if not np.array_equal(ents, ref.cull_aabb(wb_r, planes_r)):
                     what = what or "tier A world cull vs flat cull"
-        checks += 9
+        # the consumers' restatements: draw lists (the reference's DrawList::add on real RenderEntity objects) and uniform blocks
+        visible = np.flatnonzero(rng.random(n) < rng.choice([0.0, 0.3, 1.0])).astype(np.uint32)
+        pc = util.random_pass_counts(rng, n)
+        for mode in (0, 1):
+            for x, y in zip(port.draw_lists(visible, pc, flags, mode), ref.draw_lists(visible, pc, flags, mode)):
+                if not np.array_equal(x, y):
+                    what = what or "draw_lists"
+        att = tuple(float(x) for x in rng.uniform(0, 1, 3))
+        for l in lights[:6]:
+            if not same(port.light_uniforms(l, att, -0.002).view(np.float32), ref.light_uniforms(l, att, -0.002).view(np.float32)):
+                what = what or "light_uniforms"
+        if not same(port.view_uniforms(view, (3, 4)).view(np.float32), ref.view_uniforms(view, (3, 4)).view(np.float32)):
+            what = what or "view_uniforms"
+        checks += 12
         if what:
             print(json.dumps({"case": case, "what": what, "n": n, "kind": kind}))
             sys.exit(1)
