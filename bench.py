@@ -285,7 +285,10 @@ def run_ours(args, rank: int, local_rank: int, world_size: int):
     if world_size > 1 and os.environ.get("OVIS_BENCH_PIN", "1") != "0":
         # one process per GPU: keep this rank on its GPU's socket (torchrun places ranks anywhere); before the world and its
         # page-locked buffers exist, so that they are allocated there too
-        pinned_cpus = lib.pin_thread_near_device(local_rank)
+        try:
+            pinned_cpus = lib.pin_thread_near_device(local_rank)
+        except Exception:                                        # placement is an optimisation: never let it stop the run
+            pinned_cpus = 0
     if world_size > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     peaks = {}
