@@ -1,3 +1,5 @@
+"""Host-side trace of one end-to-end cull (ovis_cull with host output, 12.5 M entities): how long the two launches take to
+queue and when the result is there (OVIS_MV_TRACE=1 prints the library's own marks). Numbers in profiles/r02_cull_notes.md."""
 import os, sys, time
 sys.path.insert(0, '/root/repo')
 import numpy as np, torch

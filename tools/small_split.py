@@ -1,3 +1,5 @@
+"""Test-kernel / gather-kernel split of the single-view cull at small sizes (0.1, 1 and 4 M entities, config-2 distribution),
+from the library's CUDA events: where the single-launch path and the two-kernel path cross."""
 import sys, numpy as np, torch
 sys.path.insert(0, "/root/repo")
 from orion_b200 import lib, scenes
