@@ -65,7 +65,7 @@ def load() -> C.CDLL:
 
 def _check(rc: int):
     if rc != OVIS_OK:
-        raise OvisError(rc, load().ovis_last_error().decode())
+        raise OvisError(rc, load().ovis_last_error().decode("utf-8", "replace"))
 
 
 def _p(a):
