@@ -167,17 +167,16 @@ struct JsonParser {
     // bits), anything with a fraction or an exponent is significand * or / a power of ten in double arithmetic - NOT the
     // correctly rounded strtod - with at most 17 significant digits taken (internal/strtod.h: StrtodNormalPrecision).
     static double pow10_table(int n) {
-        static double e[309];
-        static bool ready = false;
-        if (!ready) {
+        static const std::array<double, 309> e = [] {             // (initialised once, safely, whichever thread comes first)
+            std::array<double, 309> t{};
             char lit[16];
             for (int i = 0; i <= 308; i++) {
                 snprintf(lit, sizeof lit, "1e%d", i);
-                e[i] = strtod(lit, nullptr);                       // what the literal 1e+i is in pow10.h's table
+                t[(size_t)i] = strtod(lit, nullptr);               // what the literal 1e+i is in pow10.h's table
             }
-            ready = true;
-        }
-        return e[n];
+            return t;
+        }();
+        return e[(size_t)n];
     }
     static double fastPath(double significand, int exp) {
         if (exp < -308)
